@@ -1,0 +1,143 @@
+/* kws_b200.h -- C ABI of libkws_b200.so: the B200 (sm_100a) hot path of z430/keyword-spotting.
+ *
+ * PCM -> MFCC (pre-emphasis, framing, window, 512-point real FFT, power spectrum, mel bank,
+ * log, DCT-II, lifter) -> depthwise-separable KWS network -> logits.
+ *
+ * The reference has no FFI for this path: its boundary is three in-process Python call
+ * sites.  Each entry point below names the reference interface it stands in for
+ * (paths relative to the reference repository):
+ *
+ *   kws_features_*, kws_mfcc*      kws/libs/audio_processor.py:235-278  AudioProcessor.extract_features
+ *                                  kws/libs/signal_handler.py:112-131   AudioProcessor.to_mfcc (legacy twin)
+ *                                  -> python_speech_features==0.6 mfcc/fbank/logfbank (third party)
+ *   kws_sigproc_*                  kws/libs/speech_features/sigproc.py:14-103  framesig/magspec/powspec/preemphasis
+ *   kws_model_*                    kws/libs/models.py:75-183  DepthwiseSeparableConvBlock / DepthwiseSeparableConv
+ *   kws_pcm_to_logits              audio_processor.py:235-278 followed by models.py:160-183 (fused, no HBM round trip)
+ *
+ * Conventions
+ *   - plain C types only; every pointer named *_dev is a CUDA device pointer owned by the
+ *     caller, *_host is host memory owned by the caller.  The library allocates nothing
+ *     persistent except what hangs off an opaque handle.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).
+ *   - every function returns 0 on success and a negative kws_status otherwise;
+ *     kws_last_error() returns a thread-local message.  CUDA errors never abort the process.
+ *   - one host thread per handle; handles are independent (one per device / per stream).
+ *   - there is NO CPU fallback: compute entry points fail with KWS_ERR_CUDA without a GPU.
+ */
+#ifndef KWS_B200_H_
+#define KWS_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KWS_B200_VERSION 100 /* 0.1.0 */
+
+typedef enum {
+  KWS_OK = 0,
+  KWS_ERR_INVALID = -1,     /* bad argument / unsupported configuration */
+  KWS_ERR_CUDA = -2,        /* CUDA runtime error (message holds cudaGetErrorString) */
+  KWS_ERR_STATE = -3,       /* call order: features not configured, weights missing ... */
+  KWS_ERR_ALLOC = -4
+} kws_status;
+
+typedef struct kws_handle_s* kws_handle_t;
+
+/* Feature parameters = the arguments python_speech_features.mfcc receives from
+ * extract_features (audio_processor.py:270-278) plus the psf defaults it leaves alone. */
+typedef struct {
+  int32_t sample_rate;   /* 16000 */
+  int32_t frame_len;     /* samples; psf round_half_up(winlen*sr) = 400 */
+  int32_t frame_step;    /* samples; psf round_half_up(winstep*sr) = 160 */
+  int32_t nfft;          /* 512 (fast path).  extract_features forces max(512,int(winlen*sr)) */
+  int32_t nfilt;         /* mel filters M (26 default, 40 for "40-MFCC") */
+  int32_t numcep;        /* C; output has min(C, M) columns like psf */
+  float preemph;         /* 0.97; 0 disables */
+  int32_t ceplifter;     /* 22; 0 disables */
+  int32_t append_energy; /* 1: c0 := log(frame energy) */
+  double lowfreq;        /* 0 */
+  double highfreq;       /* <=0 means sample_rate/2 */
+  const float* window_host; /* frame_len window values or NULL = rectangular (psf default) */
+} kws_feature_config;
+
+void kws_feature_config_default(kws_feature_config* cfg);
+
+/* ---- library / handle ------------------------------------------------------------- */
+int kws_version(void);
+const char* kws_last_error(void);
+int kws_create(int device, kws_handle_t* out);
+int kws_destroy(kws_handle_t h);
+/* number of this library's kernels launched through the handle since creation */
+int64_t kws_launch_count(kws_handle_t h);
+
+/* ---- host-side helpers (pure CPU arithmetic, usable without a GPU) ------------------ */
+/* psf sigproc.round_half_up (decimal ROUND_HALF_UP) */
+int64_t kws_round_half_up(double v);
+/* frame count rule of psf framesig == sigproc.py:31-35 */
+int64_t kws_num_frames(int64_t n, int64_t frame_len, int64_t frame_step);
+/* nfilt+2 FFT-bin edges of psf get_filterbanks: floor((nfft+1)*mel2hz(linspace)/sr) */
+int kws_mel_bin_edges(int nfilt, int nfft, int sample_rate, double lowfreq, double highfreq,
+                      int32_t* edges_out /* [nfilt+2] */);
+/* dense [nfilt, nfft/2+1] float64 filterbank of psf get_filterbanks */
+int kws_mel_filterbank(int nfilt, int nfft, int sample_rate, double lowfreq, double highfreq,
+                       double* fb_out);
+/* orthonormal DCT-II matrix [nfilt, ncep] with the lifter folded in (float64) */
+int kws_dct_lifter_matrix(int nfilt, int ncep, int ceplifter, double* out);
+
+/* ---- features: replaces AudioProcessor.extract_features / to_mfcc ------------------- */
+int kws_features_configure(kws_handle_t h, const kws_feature_config* cfg);
+/* output columns = min(numcep, nfilt) */
+int kws_features_ncep(kws_handle_t h);
+/* pcm_dev: [B, N] float32 rows `pcm_stride` floats apart; out_dev: [B, nframes, ncep] float32 */
+int kws_mfcc(kws_handle_t h, const float* pcm_dev, int64_t B, int64_t N, int64_t pcm_stride,
+             float* out_dev, void* stream);
+/* psf logfbank ("log-mel"): out_dev [B, nframes, nfilt] */
+int kws_logfbank(kws_handle_t h, const float* pcm_dev, int64_t B, int64_t N, int64_t pcm_stride,
+                 float* out_dev, void* stream);
+/* int16 PCM ingest (librosa.load scaling x/32768, audio_processor.py:145) fused in front */
+int kws_mfcc_i16(kws_handle_t h, const int16_t* pcm_dev, int64_t B, int64_t N, int64_t pcm_stride,
+                 float* out_dev, void* stream);
+/* end-to-end with HOST buffers: chunked H2D -> kernel -> D2H, double-buffered on two streams.
+ * pcm_host / out_host should be pinned for full PCIe rate but need not be. */
+int kws_mfcc_host(kws_handle_t h, const float* pcm_host, int64_t B, int64_t N, float* out_host);
+
+/* ---- sigproc: replaces kws/libs/speech_features/sigproc.py -------------------------- */
+/* dtype: 0 = float32, 1 = float64 (the torch helpers follow the input dtype) */
+int kws_sigproc_preemphasis(int dtype, const void* in_dev, void* out_dev, int64_t B, int64_t N,
+                            double coeff, void* stream);
+/* in [B,N] -> out [B, nframes, frame_len]; window_dev: frame_len values of `dtype` or NULL */
+int kws_sigproc_framesig(int dtype, const void* in_dev, int64_t B, int64_t N, int64_t frame_len,
+                         int64_t frame_step, const void* window_dev, void* out_dev, void* stream);
+/* frames [R, L] -> [R, nfft/2+1]; power=0: |rfft|, power=1: |rfft|^2/nfft */
+int kws_sigproc_spec(int dtype, const void* frames_dev, int64_t R, int64_t L, int64_t nfft,
+                     int power, void* out_dev, void* stream);
+
+/* kernels launched by the handle-free kws_sigproc_* entry points since load */
+int64_t kws_sigproc_launch_count(void);
+
+/* ---- model: replaces DepthwiseSeparableConv (models.py:122-183) --------------------- */
+/* channels=64, num_blocks=4 is the reference network; other values are the "DS-CNN-L" style
+ * extension that keeps every quirk (pointwise padding=1, no activation after depthwise). */
+int kws_model_create(kws_handle_t h, int num_classes, int channels, int num_blocks);
+/* name = reference state_dict key (models.py:135-144), data_host float32 in torch layout */
+int kws_model_load_tensor(kws_handle_t h, const char* name, const float* data_host,
+                          const int64_t* shape, int ndim);
+int kws_model_finalize(kws_handle_t h);
+/* feats_dev [B,1,T,F] float32 contiguous -> logits_dev [B,num_classes] */
+int kws_model_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t T, int64_t F,
+                      float* logits_dev, void* stream);
+/* bytes of scratch the forward needs for batch B (allocated lazily on the handle) */
+int64_t kws_model_workspace_bytes(kws_handle_t h, int64_t B, int64_t T, int64_t F);
+
+/* ---- fused path: PCM -> logits ------------------------------------------------------ */
+int kws_pcm_to_logits(kws_handle_t h, const float* pcm_dev, int64_t B, int64_t N,
+                      int64_t pcm_stride, float* logits_dev, void* stream);
+int kws_pcm_to_logits_host(kws_handle_t h, const float* pcm_host, int64_t B, int64_t N,
+                           float* logits_host);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KWS_B200_H_ */

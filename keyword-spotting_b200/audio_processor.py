@@ -1,0 +1,194 @@
+"""Feature extraction with the reference's call signatures, computed by the sm_100a kernel.
+
+Mirrors ``kws/libs/audio_processor.py`` of the reference:
+  * ``AudioConfig``                       (``:20-72``)   -- same fields and defaults
+  * ``AudioProcessor.extract_features``   (``:235-278``) -- same keyword arguments, same
+    ``x or config`` defaulting, same ``nfft = max(config.fft_size, int(winlen*samplerate))``
+    override of the ``nfft`` argument, then the psf 0.6 ``mfcc`` defaults (rectangular window,
+    preemph 0.97, ceplifter 22, appendEnergy, lowfreq 0, highfreq sr/2)
+  * ``AudioProcessor.to_mfcc``            (``kws/libs/signal_handler.py:112-131``, legacy twin)
+
+Additions: a leading batch dimension (``[B, N] -> [B, nframes, C]``, each row equal to the
+per-clip result), CUDA tensors in / CUDA float32 tensors out, int16 PCM input, and
+``extract_logfbank`` (psf ``logfbank``).  numpy in -> numpy out (float64 dtype like psf, values
+computed in float32 on the device).  File loading, time shift and noise mixing
+(``:103-233``) are host-side augmentation and stay out of scope.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from pathlib import Path
+from typing import Any, Dict, Optional
+
+import numpy as np
+import torch
+
+from . import _native
+from .common.errors import AudioProcessingError
+
+
+@dataclass
+class AudioConfig:
+    """Same record as the reference ``AudioConfig`` (audio_processor.py:20-72)."""
+
+    background_volume: float = 0.1
+    background_frequency: float = 0.8
+    use_background_noise: bool = True
+    sample_rate: int = 16000
+    clip_duration_ms: int = 1000
+    time_shift_ms: float = 100
+    frame_length: float = 0.025
+    frame_step: float = 0.01
+    num_cepstral_coeffs: int = 10
+    num_mel_filters: int = 26
+    fft_size: int = 512
+
+    @property
+    def time_shift(self) -> int:
+        return int((self.time_shift_ms * self.sample_rate) / 1000)
+
+    @property
+    def desired_samples(self) -> int:
+        return int(self.sample_rate * self.clip_duration_ms / 1000)
+
+    def to_dict(self) -> Dict[str, Any]:
+        return {k: getattr(self, k) for k in (
+            "background_volume", "background_frequency", "use_background_noise", "sample_rate",
+            "clip_duration_ms", "time_shift_ms", "frame_length", "frame_step",
+            "num_cepstral_coeffs", "num_mel_filters", "fft_size")}
+
+
+class _FeaturePlan:
+    """One native handle configured for one (sr, frame_len, hop, nfft, nfilt, numcep) tuple."""
+
+    def __init__(self, device_index: int, key):
+        lib = _native.lib()
+        self.handle = _native.Handle(device_index)
+        cfg = _native.FeatureConfig()
+        lib.kws_feature_config_default(C.byref(cfg))
+        (cfg.sample_rate, cfg.frame_len, cfg.frame_step, cfg.nfft, cfg.nfilt, cfg.numcep) = key
+        _native.check(lib.kws_features_configure(self.handle.ptr, C.byref(cfg)), AudioProcessingError)
+        self.frame_len, self.frame_step, self.nfilt = cfg.frame_len, cfg.frame_step, cfg.nfilt
+        self.ncep = int(lib.kws_features_ncep(self.handle.ptr))
+
+
+class AudioProcessor:
+    """Drop-in for the feature half of the reference ``AudioProcessor``."""
+
+    def __init__(self, dataset_path: Optional[Path] = None, config: Optional[AudioConfig] = None,
+                 device: Optional[torch.device] = None):
+        self.config = config if config is not None else AudioConfig()
+        self.dataset_path = dataset_path
+        self.device = torch.device(device) if device is not None else torch.device("cuda", 0)
+        if self.device.type != "cuda":
+            raise AudioProcessingError("kws_b200 runs on CUDA devices only (no CPU fallback)")
+        self._plans: Dict[tuple, _FeaturePlan] = {}
+
+    # -- plumbing -----------------------------------------------------------------------
+    def _dev_index(self) -> int:
+        return self.device.index if self.device.index is not None else torch.cuda.current_device()
+
+    def _plan(self, samplerate, numcep, winlen, winstep, nfilt) -> _FeaturePlan:
+        lib = _native.lib()
+        nfft = max(self.config.fft_size, int(winlen * samplerate))      # audio_processor.py:268
+        key = (int(samplerate), int(lib.kws_round_half_up(winlen * samplerate)),
+               int(lib.kws_round_half_up(winstep * samplerate)), int(nfft), int(nfilt), int(numcep))
+        plan = self._plans.get(key)
+        if plan is None:
+            plan = _FeaturePlan(self._dev_index(), key)
+            self._plans[key] = plan
+        return plan
+
+    def _run(self, signal, plan: _FeaturePlan, logmel: bool):
+        lib = _native.lib()
+        is_numpy = not isinstance(signal, torch.Tensor)
+        x = torch.as_tensor(np.asarray(signal)) if is_numpy else signal
+        if x.dim() not in (1, 2):
+            raise AudioProcessingError(f"expected a [N] or [B, N] signal, got shape {tuple(x.shape)}")
+        single = x.dim() == 1
+        if single:
+            x = x.unsqueeze(0)
+        if x.shape[1] < 1:
+            raise AudioProcessingError("empty signal")
+        i16 = x.dtype == torch.int16
+        if not i16:
+            x = x.to(torch.float32)
+        x = x.to(self.device, non_blocking=True).contiguous()
+        B, N = x.shape
+        nframes = int(lib.kws_num_frames(N, plan.frame_len, plan.frame_step))
+        cols = plan.nfilt if logmel else plan.ncep
+        out = torch.empty((B, nframes, cols), dtype=torch.float32, device=self.device)
+        if B > 0:
+            stream = _native.current_stream_ptr(self._dev_index())
+            if logmel:
+                if i16:
+                    x = x.to(torch.float32) / 32768.0
+                fn = lib.kws_logfbank
+            else:
+                fn = lib.kws_mfcc_i16 if i16 else lib.kws_mfcc
+            with torch.cuda.device(self.device):
+                _native.check(fn(plan.handle.ptr, C.c_void_p(x.data_ptr()), B, N, x.stride(0),
+                                 C.c_void_p(out.data_ptr()), stream), AudioProcessingError)
+        if single:
+            out = out[0]
+        if is_numpy:
+            return out.cpu().numpy().astype(np.float64)
+        return out
+
+    # -- reference API --------------------------------------------------------------------
+    def extract_features(self, signal, samplerate: int = None, numcep: int = None, nfft: int = None,
+                         winlen: float = None, winstep: float = None, nfilt: int = None):
+        """MFCC features, ``[nframes, min(numcep, nfilt)]`` (or ``[B, nframes, .]``)."""
+        samplerate = samplerate or self.config.sample_rate
+        numcep = numcep or self.config.num_cepstral_coeffs
+        nfft = nfft or self.config.fft_size      # accepted and ignored, like the reference (:268)
+        winlen = winlen or self.config.frame_length
+        winstep = winstep or self.config.frame_step
+        nfilt = nfilt or self.config.num_mel_filters
+        return self._run(signal, self._plan(samplerate, numcep, winlen, winstep, nfilt), logmel=False)
+
+    def extract_logfbank(self, signal, samplerate: int = None, winlen: float = None,
+                         winstep: float = None, nfilt: int = None):
+        """psf ``logfbank`` ("log-mel"): the intermediate of ``mfcc`` just before the DCT."""
+        samplerate = samplerate or self.config.sample_rate
+        winlen = winlen or self.config.frame_length
+        winstep = winstep or self.config.frame_step
+        nfilt = nfilt or self.config.num_mel_filters
+        return self._run(signal, self._plan(samplerate, nfilt, winlen, winstep, nfilt), logmel=True)
+
+    def to_mfcc(self, signal, samplerate=16000, numcep=10, nfft=512, winlen=0.025, winstep=0.01,
+                nfilt=26):
+        """Legacy spelling (signal_handler.py:112-131): fixed defaults, ``max(512, .)`` override."""
+        lib = _native.lib()
+        key = (int(samplerate), int(lib.kws_round_half_up(winlen * samplerate)),
+               int(lib.kws_round_half_up(winstep * samplerate)), max(512, int(winlen * samplerate)),
+               int(nfilt), int(numcep))
+        plan = self._plans.get(key)
+        if plan is None:
+            plan = self._plans[key] = _FeaturePlan(self._dev_index(), key)
+        return self._run(signal, plan, logmel=False)
+
+    def extract_features_host(self, pcm: torch.Tensor, out: Optional[torch.Tensor] = None, **kw):
+        """End-to-end variant on HOST tensors (ideally pinned): chunked H2D -> kernel -> D2H
+        pipelined inside the library (``kws_mfcc_host``).  ``pcm`` float32 ``[B, N]`` on the CPU."""
+        lib = _native.lib()
+        if pcm.device.type != "cpu" or pcm.dtype != torch.float32 or pcm.dim() != 2:
+            raise AudioProcessingError("extract_features_host expects a float32 [B, N] CPU tensor")
+        pcm = pcm.contiguous()
+        plan = self._plan(kw.get("samplerate") or self.config.sample_rate,
+                          kw.get("numcep") or self.config.num_cepstral_coeffs,
+                          kw.get("winlen") or self.config.frame_length,
+                          kw.get("winstep") or self.config.frame_step,
+                          kw.get("nfilt") or self.config.num_mel_filters)
+        B, N = pcm.shape
+        nframes = int(lib.kws_num_frames(N, plan.frame_len, plan.frame_step))
+        if out is None:
+            out = torch.empty((B, nframes, plan.ncep), dtype=torch.float32, pin_memory=True)
+        with torch.cuda.device(self.device):
+            _native.check(lib.kws_mfcc_host(plan.handle.ptr, C.c_void_p(pcm.data_ptr()), B, N,
+                                            C.c_void_p(out.data_ptr())), AudioProcessingError)
+        return out
+
+    def launch_count(self) -> int:
+        return sum(p.handle.launch_count() for p in self._plans.values())

@@ -1,0 +1,103 @@
+// Internal declarations shared by the translation units of libkws_b200.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "kws_b200.h"
+
+namespace kws {
+
+void set_error(const char* fmt, ...);
+int fail(int code, const char* fmt, ...);
+
+#define KWS_CUDA(expr)                                                                      \
+  do {                                                                                      \
+    cudaError_t _e = (expr);                                                                \
+    if (_e != cudaSuccess)                                                                  \
+      return ::kws::fail(KWS_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), \
+                         __FILE__, __LINE__);                                               \
+  } while (0)
+
+#define KWS_CHECK_LAUNCH(h)                                                       \
+  do {                                                                            \
+    cudaError_t _e = cudaGetLastError();                                          \
+    if (_e != cudaSuccess)                                                        \
+      return ::kws::fail(KWS_ERR_CUDA, "kernel launch failed: %s (%s:%d)",        \
+                         cudaGetErrorString(_e), __FILE__, __LINE__);             \
+    (h)->launches++;                                                              \
+  } while (0)
+
+// ---- feature tables -------------------------------------------------------------------
+constexpr int kNfft = 512;          // fast path: 512-point real FFT as a 256-point complex FFT
+constexpr int kBins = kNfft / 2 + 1;  // 257
+constexpr int kMaxFilt = 80;        // scratch budget of the fused kernel (see mfcc.cu)
+constexpr int kFramesPerTile = 20;  // frames one CTA pass consumes (5 warps x 4 frames)
+
+struct FeatureTables {
+  bool ready = false;
+  kws_feature_config cfg{};
+  int ncep = 0;              // min(numcep, nfilt)
+  int ncep_pad = 0;          // DCT matrix row pitch
+  int load_len = 0;          // min(frame_len, nfft): samples of a frame that enter the FFT
+  // device tables
+  float* d_window = nullptr;    // [frame_len] or null
+  float2* d_tw256 = nullptr;    // W256^t, t = 0..255 (cos, -sin)
+  float2* d_tw512 = nullptr;    // W512^t, t = 0..255
+  float2* d_melw = nullptr;     // [257] (rising weight, falling weight) of the bin's segment
+  int* d_segedge = nullptr;     // [nfilt+2] bin edges
+  float* d_dct = nullptr;       // [nfilt][ncep_pad], lifter folded in
+  std::vector<int> h_edges;
+};
+
+// ---- model ----------------------------------------------------------------------------
+struct ModelWeights {
+  bool created = false, finalized = false;
+  int num_classes = 0, channels = 0, num_blocks = 0;
+  std::vector<std::vector<float>> host;   // staged tensors by slot
+  std::vector<std::string> names;
+  std::vector<bool> loaded;
+  // packed device weights
+  float* d_conv1_w = nullptr;   // [100][C]   (tap-major, channel-minor)
+  float* d_conv1_b = nullptr;   // [C]
+  float* d_dw_w = nullptr;      // [nb][9][C]
+  float* d_dw_b = nullptr;      // [nb][C]
+  float* d_pw_w = nullptr;      // [nb][Cin][Cout]  (k-major)
+  float* d_pw_b = nullptr;      // [nb][C]
+  float* d_pw_beff = nullptr;   // [nb][C]   pointwise bias with the depthwise bias folded through
+  float* d_fc_w = nullptr;      // [C][num_classes]
+  float* d_fc_b = nullptr;      // [num_classes]
+  // workspace
+  void* d_ws = nullptr;
+  size_t ws_bytes = 0;
+};
+
+}  // namespace kws
+
+struct kws_handle_s {
+  int device = 0;
+  int sm_count = 0;
+  int64_t launches = 0;
+  kws::FeatureTables feat;
+  kws::ModelWeights model;
+  // staging for the *_host entry points
+  cudaStream_t s_copy[2] = {nullptr, nullptr};
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  void* d_stage_in[2] = {nullptr, nullptr};
+  void* d_stage_out[2] = {nullptr, nullptr};
+  size_t stage_in_bytes = 0, stage_out_bytes = 0;
+  float* d_feat_tmp = nullptr;   // features scratch for the unfused pcm->logits path
+  size_t feat_tmp_bytes = 0;
+};
+
+namespace kws {
+// mfcc.cu
+enum FeatureMode { kModeMfcc = 0, kModeLogMel = 1 };
+int launch_mfcc(kws_handle_t h, const void* pcm_dev, bool is_i16, int64_t B, int64_t N,
+                int64_t pcm_stride, float* out_dev, int mode, cudaStream_t stream);
+// tables.cu
+int build_feature_tables(kws_handle_t h, const kws_feature_config* cfg);
+void free_feature_tables(FeatureTables& t);
+}  // namespace kws

@@ -1,0 +1,360 @@
+// Forward pass of the reference KWS network, DepthwiseSeparableConv
+// (kws/libs/models.py:122-183): conv1 10x10 s2 p2 + ReLU -> num_blocks x [depthwise 3x3 p1
+// (+bias, no activation) -> pointwise 1x1 with padding=1 (+bias) -> ReLU] -> global average
+// pool -> fc.  Each block grows H and W by 2 and its border pixels equal ReLU(pointwise bias)
+// (models.py:104-106; SURVEY.md a-M2).  Logits are returned, no softmax (models.py:181).
+//
+// Layer-by-layer fp32 path: activations NHWC [B, H, W, C] in a ping-pong workspace.
+// Weights are repacked at kws_model_finalize() so the channel index is innermost.
+#include <cuda_runtime.h>
+
+#include <cstring>
+#include <string>
+
+#include "common.cuh"
+
+namespace kws {
+
+// conv1: in [B, T, F] (single input channel) -> out [B, H1, W1, C], ReLU.
+// thread = (pixel, 4 consecutive output channels)
+__global__ void conv1_relu_kernel(const float* __restrict__ in, float* __restrict__ out,
+                                  const float* __restrict__ w /*[100][C]*/,
+                                  const float* __restrict__ bias, long long B, int T, int F, int H1,
+                                  int W1, int C) {
+  const int cq = C / 4;
+  const long long total = B * H1 * W1 * (long long)cq;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int q = (int)(i % cq);
+    const long long pix = i / cq;
+    const int wo = (int)(pix % W1);
+    const int ho = (int)((pix / W1) % H1);
+    const long long b = pix / ((long long)W1 * H1);
+    float4 acc = __ldg(reinterpret_cast<const float4*>(bias) + q);
+    const float* img = in + b * (long long)T * F;
+#pragma unroll 2
+    for (int ki = 0; ki < 10; ++ki) {
+      const int hi = 2 * ho - 2 + ki;
+      if (hi < 0 || hi >= T) continue;
+#pragma unroll
+      for (int kj = 0; kj < 10; ++kj) {
+        const int wi = 2 * wo - 2 + kj;
+        if (wi < 0 || wi >= F) continue;
+        const float x = __ldg(img + hi * F + wi);
+        const float4 wv = __ldg(reinterpret_cast<const float4*>(w + (ki * 10 + kj) * C) + q);
+        acc.x = fmaf(x, wv.x, acc.x);
+        acc.y = fmaf(x, wv.y, acc.y);
+        acc.z = fmaf(x, wv.z, acc.z);
+        acc.w = fmaf(x, wv.w, acc.w);
+      }
+    }
+    acc.x = fmaxf(acc.x, 0.f); acc.y = fmaxf(acc.y, 0.f);
+    acc.z = fmaxf(acc.z, 0.f); acc.w = fmaxf(acc.w, 0.f);
+    reinterpret_cast<float4*>(out)[i] = acc;
+  }
+}
+
+// One DS block: in [B,H,W,C] -> out [B,H+2,W+2,C].
+// CTA = PIX output pixels x C/4 channel quads; the depthwise result of each pixel is shared
+// through shared memory so it is computed once and consumed by all output channels.
+constexpr int kBlkPix = 8;
+__global__ void dsblock_kernel(const float* __restrict__ in, float* __restrict__ out,
+                               const float* __restrict__ dw_w /*[9][C]*/,
+                               const float* __restrict__ dw_b, const float* __restrict__ pw_w /*[C][C]*/,
+                               const float* __restrict__ pw_b, long long B, int H, int W, int C) {
+  extern __shared__ __align__(16) float s_d[];  // [kBlkPix][C]
+  const int cq = C / 4;
+  const int Ho = H + 2, Wo = W + 2;
+  const long long npix = B * Ho * (long long)Wo;
+  const long long ngroups = (npix + kBlkPix - 1) / kBlkPix;
+  for (long long grp = blockIdx.x; grp < ngroups; grp += gridDim.x) {
+    __syncthreads();
+    // phase 1: depthwise 3x3 (zero padding 1) + bias for interior pixels
+    for (int t = threadIdx.x; t < kBlkPix * cq; t += blockDim.x) {
+      const int pl = t / cq, q = t - pl * cq;
+      const long long pix = grp * kBlkPix + pl;
+      float4 d = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (pix < npix) {
+        const int wo = (int)(pix % Wo), ho = (int)((pix / Wo) % Ho);
+        const long long b = pix / ((long long)Wo * Ho);
+        if (ho >= 1 && ho <= H && wo >= 1 && wo <= W) {
+          const int h = ho - 1, wc = wo - 1;
+          d = __ldg(reinterpret_cast<const float4*>(dw_b) + q);
+#pragma unroll
+          for (int i = 0; i < 3; ++i) {
+            const int hi = h + i - 1;
+            if (hi < 0 || hi >= H) continue;
+#pragma unroll
+            for (int j = 0; j < 3; ++j) {
+              const int wi = wc + j - 1;
+              if (wi < 0 || wi >= W) continue;
+              const float4 x = __ldg(reinterpret_cast<const float4*>(in + ((b * H + hi) * W + wi) * C) + q);
+              const float4 k = __ldg(reinterpret_cast<const float4*>(dw_w + (i * 3 + j) * C) + q);
+              d.x = fmaf(x.x, k.x, d.x); d.y = fmaf(x.y, k.y, d.y);
+              d.z = fmaf(x.z, k.z, d.z); d.w = fmaf(x.w, k.w, d.w);
+            }
+          }
+        }
+      }
+      reinterpret_cast<float4*>(s_d + pl * C)[q] = d;
+    }
+    __syncthreads();
+    // phase 2: pointwise 1x1 (+bias) + ReLU; border pixels see zero input -> ReLU(bias)
+    for (int t = threadIdx.x; t < kBlkPix * cq; t += blockDim.x) {
+      const int pl = t / cq, q = t - pl * cq;
+      const long long pix = grp * kBlkPix + pl;
+      if (pix >= npix) continue;
+      const int wo = (int)(pix % Wo), ho = (int)((pix / Wo) % Ho);
+      float4 acc = __ldg(reinterpret_cast<const float4*>(pw_b) + q);
+      if (ho >= 1 && ho <= H && wo >= 1 && wo <= W) {
+        const float* d = s_d + pl * C;
+#pragma unroll 4
+        for (int c = 0; c < C; ++c) {
+          const float dv = d[c];
+          const float4 wv = __ldg(reinterpret_cast<const float4*>(pw_w + (size_t)c * C) + q);
+          acc.x = fmaf(dv, wv.x, acc.x); acc.y = fmaf(dv, wv.y, acc.y);
+          acc.z = fmaf(dv, wv.z, acc.z); acc.w = fmaf(dv, wv.w, acc.w);
+        }
+      }
+      acc.x = fmaxf(acc.x, 0.f); acc.y = fmaxf(acc.y, 0.f);
+      acc.z = fmaxf(acc.z, 0.f); acc.w = fmaxf(acc.w, 0.f);
+      reinterpret_cast<float4*>(out + pix * C)[q] = acc;
+    }
+  }
+}
+
+// adaptive_avg_pool2d(1,1) + fc: one CTA per clip
+__global__ void pool_fc_kernel(const float* __restrict__ in, float* __restrict__ logits,
+                               const float* __restrict__ fc_w /*[C][ncls]*/,
+                               const float* __restrict__ fc_b, long long B, int HW, int C, int ncls) {
+  extern __shared__ __align__(16) float s_pool[];  // [C]
+  for (long long b = blockIdx.x; b < B; b += gridDim.x) {
+    __syncthreads();
+    const float* x = in + b * (long long)HW * C;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+      float s = 0.f;
+      for (int p = 0; p < HW; ++p) s += x[(size_t)p * C + c];
+      s_pool[c] = s / (float)HW;
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < ncls; k += blockDim.x) {
+      float acc = fc_b[k];
+      for (int c = 0; c < C; ++c) acc = fmaf(s_pool[c], fc_w[c * ncls + k], acc);
+      logits[b * ncls + k] = acc;
+    }
+  }
+}
+
+static void conv_out_hw(int T, int F, int nb, int* H1, int* W1, int* Hl, int* Wl) {
+  *H1 = (T + 4 - 10) / 2 + 1;
+  *W1 = (F + 4 - 10) / 2 + 1;
+  *Hl = *H1 + 2 * nb;
+  *Wl = *W1 + 2 * nb;
+}
+
+static int slot_of(const ModelWeights& m, const std::string& name) {
+  for (size_t i = 0; i < m.names.size(); ++i)
+    if (m.names[i] == name) return (int)i;
+  return -1;
+}
+
+static void model_free(ModelWeights& m) {
+  void* ptrs[] = {m.d_conv1_w, m.d_conv1_b, m.d_dw_w, m.d_dw_b, m.d_pw_w, m.d_pw_b, m.d_pw_beff,
+                  m.d_fc_w,    m.d_fc_b,    m.d_ws};
+  for (void* p : ptrs)
+    if (p) cudaFree(p);
+  m = ModelWeights();
+}
+
+constexpr int64_t kModelChunk = 2048;  // clips per pass through the ping-pong workspace
+
+}  // namespace kws
+
+using namespace kws;
+
+extern "C" {
+
+void kws_model_free_internal(kws_handle_t h) {
+  if (h) model_free(h->model);
+}
+
+int kws_model_create(kws_handle_t h, int num_classes, int channels, int num_blocks) {
+  if (!h) return fail(KWS_ERR_INVALID, "null handle");
+  if (num_classes < 1 || channels < 4 || channels % 4 != 0 || num_blocks < 0 || num_blocks > 16)
+    return fail(KWS_ERR_INVALID, "model: need num_classes>=1, channels a multiple of 4, 0<=num_blocks<=16");
+  KWS_CUDA(cudaSetDevice(h->device));
+  model_free(h->model);
+  ModelWeights& m = h->model;
+  m.num_classes = num_classes;
+  m.channels = channels;
+  m.num_blocks = num_blocks;
+  m.names = {"conv1.weight", "conv1.bias"};
+  for (int i = 1; i <= num_blocks; ++i) {
+    const std::string p = "dsconv" + std::to_string(i);
+    m.names.push_back(p + ".depthwise.weight");
+    m.names.push_back(p + ".depthwise.bias");
+    m.names.push_back(p + ".pointwise.weight");
+    m.names.push_back(p + ".pointwise.bias");
+  }
+  m.names.push_back("fc.weight");
+  m.names.push_back("fc.bias");
+  m.host.assign(m.names.size(), std::vector<float>());
+  m.loaded.assign(m.names.size(), false);
+  m.created = true;
+  return KWS_OK;
+}
+
+int kws_model_load_tensor(kws_handle_t h, const char* name, const float* data, const int64_t* shape,
+                          int ndim) {
+  if (!h || !h->model.created) return fail(KWS_ERR_STATE, "model not created");
+  if (!name || !data || !shape) return fail(KWS_ERR_INVALID, "null argument");
+  ModelWeights& m = h->model;
+  const int s = slot_of(m, name);
+  if (s < 0) return fail(KWS_ERR_INVALID, "unexpected key '%s' in state_dict", name);
+  const int64_t C = m.channels, K = m.num_classes;
+  std::vector<int64_t> want;
+  const std::string n(name);
+  if (n == "conv1.weight") want = {C, 1, 10, 10};
+  else if (n == "fc.weight") want = {K, C};
+  else if (n == "fc.bias") want = {K};
+  else if (n.find("depthwise.weight") != std::string::npos) want = {C, 1, 3, 3};
+  else if (n.find("pointwise.weight") != std::string::npos) want = {C, C, 1, 1};
+  else want = {C};
+  bool ok = (int)want.size() == ndim;
+  int64_t numel = 1;
+  for (int i = 0; ok && i < ndim; ++i) {
+    ok = shape[i] == want[i];
+    numel *= want[i];
+  }
+  if (!ok) return fail(KWS_ERR_INVALID, "size mismatch for %s", name);
+  m.host[s].assign(data, data + numel);
+  m.loaded[s] = true;
+  m.finalized = false;
+  return KWS_OK;
+}
+
+int kws_model_finalize(kws_handle_t h) {
+  if (!h || !h->model.created) return fail(KWS_ERR_STATE, "model not created");
+  ModelWeights& m = h->model;
+  for (size_t i = 0; i < m.names.size(); ++i)
+    if (!m.loaded[i]) return fail(KWS_ERR_STATE, "missing key '%s' in state_dict", m.names[i].c_str());
+  KWS_CUDA(cudaSetDevice(h->device));
+  const int C = m.channels, K = m.num_classes, nb = m.num_blocks;
+  auto up = [&](float** dst, const std::vector<float>& v) -> int {
+    if (*dst) cudaFree(*dst);
+    *dst = nullptr;
+    if (v.empty()) return KWS_OK;
+    KWS_CUDA(cudaMalloc((void**)dst, v.size() * 4));
+    KWS_CUDA(cudaMemcpy(*dst, v.data(), v.size() * 4, cudaMemcpyHostToDevice));
+    return KWS_OK;
+  };
+  int rc;
+  {  // conv1.weight [C,1,10,10] -> [100][C]
+    const std::vector<float>& w = m.host[slot_of(m, "conv1.weight")];
+    std::vector<float> p((size_t)100 * C);
+    for (int c = 0; c < C; ++c)
+      for (int t = 0; t < 100; ++t) p[(size_t)t * C + c] = w[(size_t)c * 100 + t];
+    if ((rc = up(&m.d_conv1_w, p))) return rc;
+    if ((rc = up(&m.d_conv1_b, m.host[slot_of(m, "conv1.bias")]))) return rc;
+  }
+  std::vector<float> dww((size_t)nb * 9 * C), dwb((size_t)nb * C), pww((size_t)nb * C * C), pwb((size_t)nb * C);
+  for (int i = 0; i < nb; ++i) {
+    const std::string pre = "dsconv" + std::to_string(i + 1);
+    const std::vector<float>& a = m.host[slot_of(m, pre + ".depthwise.weight")];  // [C,1,3,3]
+    const std::vector<float>& ab = m.host[slot_of(m, pre + ".depthwise.bias")];
+    const std::vector<float>& b = m.host[slot_of(m, pre + ".pointwise.weight")];  // [Cout,Cin,1,1]
+    const std::vector<float>& bb = m.host[slot_of(m, pre + ".pointwise.bias")];
+    for (int c = 0; c < C; ++c) {
+      for (int t = 0; t < 9; ++t) dww[((size_t)i * 9 + t) * C + c] = a[(size_t)c * 9 + t];
+      dwb[(size_t)i * C + c] = ab[c];
+      pwb[(size_t)i * C + c] = bb[c];
+      for (int ci = 0; ci < C; ++ci) pww[((size_t)i * C + ci) * C + c] = b[(size_t)c * C + ci];
+    }
+  }
+  if ((rc = up(&m.d_dw_w, dww))) return rc;
+  if ((rc = up(&m.d_dw_b, dwb))) return rc;
+  if ((rc = up(&m.d_pw_w, pww))) return rc;
+  if ((rc = up(&m.d_pw_b, pwb))) return rc;
+  {  // fc.weight [K,C] -> [C][K]
+    const std::vector<float>& w = m.host[slot_of(m, "fc.weight")];
+    std::vector<float> p((size_t)C * K);
+    for (int k = 0; k < K; ++k)
+      for (int c = 0; c < C; ++c) p[(size_t)c * K + k] = w[(size_t)k * C + c];
+    if ((rc = up(&m.d_fc_w, p))) return rc;
+    if ((rc = up(&m.d_fc_b, m.host[slot_of(m, "fc.bias")]))) return rc;
+  }
+  m.finalized = true;
+  return KWS_OK;
+}
+
+int64_t kws_model_workspace_bytes(kws_handle_t h, int64_t B, int64_t T, int64_t F) {
+  if (!h || !h->model.created) return fail(KWS_ERR_STATE, "model not created");
+  int H1, W1, Hl, Wl;
+  conv_out_hw((int)T, (int)F, h->model.num_blocks, &H1, &W1, &Hl, &Wl);
+  if (H1 < 1 || W1 < 1) return fail(KWS_ERR_INVALID, "input %lldx%lld too small for conv1", (long long)T, (long long)F);
+  const int64_t chunk = B < kModelChunk ? B : kModelChunk;
+  return 2 * chunk * Hl * Wl * h->model.channels * 4;
+}
+
+int kws_model_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t T, int64_t F,
+                      float* logits_dev, void* stream) {
+  if (!h || !h->model.created) return fail(KWS_ERR_STATE, "model not created");
+  ModelWeights& m = h->model;
+  if (!m.finalized) return fail(KWS_ERR_STATE, "model weights not finalized");
+  if (B < 0 || T < 1 || F < 1) return fail(KWS_ERR_INVALID, "bad B/T/F");
+  if (B == 0) return KWS_OK;
+  if (!feats_dev || !logits_dev) return fail(KWS_ERR_INVALID, "null device pointer");
+  KWS_CUDA(cudaSetDevice(h->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  const int C = m.channels, nb = m.num_blocks, K = m.num_classes;
+  int H1, W1, Hl, Wl;
+  conv_out_hw((int)T, (int)F, nb, &H1, &W1, &Hl, &Wl);
+  if (H1 < 1 || W1 < 1) return fail(KWS_ERR_INVALID, "input %lldx%lld too small for conv1 (10x10, stride 2, pad 2)", (long long)T, (long long)F);
+  const int64_t need = kws_model_workspace_bytes(h, B, T, F);
+  if ((size_t)need > m.ws_bytes) {
+    if (m.d_ws) KWS_CUDA(cudaFree(m.d_ws));
+    m.d_ws = nullptr;
+    m.ws_bytes = 0;
+    KWS_CUDA(cudaMalloc(&m.d_ws, (size_t)need));
+    m.ws_bytes = (size_t)need;
+  }
+  const int64_t chunk = B < kModelChunk ? B : kModelChunk;
+  float* buf0 = (float*)m.d_ws;
+  float* buf1 = buf0 + chunk * Hl * Wl * C;
+  const int cq = C / 4;
+  for (int64_t b0 = 0; b0 < B; b0 += chunk) {
+    const int64_t nbat = (B - b0 < chunk) ? B - b0 : chunk;
+    {
+      const long long total = nbat * H1 * W1 * (long long)cq;
+      long long g = (total + 255) / 256;
+      if (g > h->sm_count * 16LL) g = h->sm_count * 16LL;
+      conv1_relu_kernel<<<(unsigned)g, 256, 0, st>>>(feats_dev + b0 * T * F, buf0, m.d_conv1_w, m.d_conv1_b,
+                                                     nbat, (int)T, (int)F, H1, W1, C);
+      KWS_CHECK_LAUNCH(h);
+    }
+    float *cur = buf0, *nxt = buf1;
+    int H = H1, W = W1;
+    for (int i = 0; i < nb; ++i) {
+      const long long npix = nbat * (long long)(H + 2) * (W + 2);
+      long long g = (npix + kBlkPix - 1) / kBlkPix;
+      if (g > h->sm_count * 16LL) g = h->sm_count * 16LL;
+      int threads = kBlkPix * cq;
+      if (threads > 512) threads = 512;
+      dsblock_kernel<<<(unsigned)g, threads, kBlkPix * C * 4, st>>>(
+          cur, nxt, m.d_dw_w + (size_t)i * 9 * C, m.d_dw_b + (size_t)i * C, m.d_pw_w + (size_t)i * C * C,
+          m.d_pw_b + (size_t)i * C, nbat, H, W, C);
+      KWS_CHECK_LAUNCH(h);
+      float* t = cur; cur = nxt; nxt = t;
+      H += 2; W += 2;
+    }
+    {
+      long long g = nbat < h->sm_count * 8LL ? nbat : h->sm_count * 8LL;
+      pool_fc_kernel<<<(unsigned)g, 128, C * 4, st>>>(cur, logits_dev + b0 * K, m.d_fc_w, m.d_fc_b, nbat,
+                                                      H * W, C, K);
+      KWS_CHECK_LAUNCH(h);
+    }
+  }
+  return KWS_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,167 @@
+"""The reference KWS network with its call signatures, forward computed by sm_100a kernels.
+
+Mirrors ``kws/libs/models.py`` of the reference:
+  * ``KeywordSpottingModel``          (``:13-72``)   -- ``num_classes``, ``save``, ``load`` (errors
+    wrapped in ``ModelError`` with the same message prefixes)
+  * ``DepthwiseSeparableConvBlock``   (``:75-119``)  -- depthwise 3x3 -> pointwise 1x1 carrying the
+    block's ``padding`` (so H and W grow by 2) -> ReLU
+  * ``DepthwiseSeparableConv``        (``:122-183``) -- conv1 10x10 s2 p2, four blocks, global
+    average pool, fc; same ``state_dict`` keys and shapes, same initialiser (``:149-158``)
+
+The modules only hold parameters; ``forward`` hands them to ``libkws_b200.so``
+(``kws_model_forward``) and returns logits (no softmax, like the reference).  Inference only:
+the output does not carry autograd history.  ``channels`` / ``num_blocks`` are extension
+arguments (defaults = the reference network) for the "DS-CNN-L"-style configuration.
+"""
+from __future__ import annotations
+
+import abc
+import ctypes as C
+from typing import Optional
+
+import torch
+import torch.nn as nn
+
+from . import _native
+from .common.errors import ModelError
+
+
+class KeywordSpottingModel(nn.Module, abc.ABC):
+    """Base class (reference models.py:13-72)."""
+
+    def __init__(self, num_classes: int, **kwargs):
+        super().__init__()
+        self.num_classes = num_classes
+
+    @abc.abstractmethod
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        pass
+
+    def save(self, path: str) -> None:
+        try:
+            torch.save(self.state_dict(), path)
+        except Exception as e:
+            raise ModelError(f"Failed to save model to {path}: {str(e)}") from e
+
+    def load(self, path: str, device: Optional[torch.device] = None) -> None:
+        try:
+            if device is None:
+                device = torch.device("cuda" if torch.cuda.is_available() else "cpu")
+            self.load_state_dict(torch.load(path, map_location=device))
+            self.to(device)
+        except Exception as e:
+            raise ModelError(f"Failed to load model from {path}: {str(e)}") from e
+
+
+class _ConvParams(nn.Module):
+    """Parameter holder with ``nn.Conv2d``'s ``weight``/``bias`` names and shapes."""
+
+    def __init__(self, out_ch, in_ch_per_group, kh, kw):
+        super().__init__()
+        self.weight = nn.Parameter(torch.empty(out_ch, in_ch_per_group, kh, kw))
+        self.bias = nn.Parameter(torch.zeros(out_ch))
+
+
+class _LinearParams(nn.Module):
+    def __init__(self, in_f, out_f):
+        super().__init__()
+        self.weight = nn.Parameter(torch.empty(out_f, in_f))
+        self.bias = nn.Parameter(torch.zeros(out_f))
+
+
+class DepthwiseSeparableConvBlock(nn.Module):
+    """Parameters of one block (reference models.py:75-119).  The fused kernels implement
+    ``kernel_size=3, stride=1, padding=1`` with ``in_channels == out_channels``, which is the
+    only configuration the reference instantiates (``:138-141``)."""
+
+    def __init__(self, in_channels: int, out_channels: int, kernel_size: int = 3, stride: int = 1,
+                 padding: int = 1):
+        super().__init__()
+        if (kernel_size, stride, padding) != (3, 1, 1) or in_channels != out_channels:
+            raise ModelError("only the 3x3 / stride 1 / padding 1 / square block of the reference "
+                             "network is implemented")
+        self.depthwise = _ConvParams(in_channels, 1, kernel_size, kernel_size)
+        self.pointwise = _ConvParams(out_channels, in_channels, 1, 1)
+
+    def forward(self, x):  # pragma: no cover - blocks are executed by the fused forward
+        raise ModelError("DepthwiseSeparableConvBlock is executed inside DepthwiseSeparableConv.forward")
+
+
+class DepthwiseSeparableConv(KeywordSpottingModel):
+    """Drop-in for the reference ``DepthwiseSeparableConv`` (models.py:122-183)."""
+
+    def __init__(self, num_classes: int = 12, input_channels: int = 1, channels: int = 64,
+                 num_blocks: int = 4):
+        super().__init__(num_classes)
+        if input_channels != 1:
+            raise ModelError("input_channels must be 1 (mono features), as in the reference pipeline")
+        self.channels, self.num_blocks = channels, num_blocks
+        self.conv1 = _ConvParams(channels, input_channels, 10, 10)
+        for i in range(1, num_blocks + 1):
+            setattr(self, f"dsconv{i}", DepthwiseSeparableConvBlock(channels, channels))
+        self.fc = _LinearParams(channels, num_classes)
+        self._initialize_weights()
+        self._native = None          # (_native.Handle, device index)
+        self._packed_version = None
+
+    def _initialize_weights(self):
+        """Reference initialiser (models.py:149-158)."""
+        for m in self.modules():
+            if isinstance(m, _ConvParams):
+                nn.init.kaiming_normal_(m.weight, mode="fan_out", nonlinearity="relu")
+                nn.init.constant_(m.bias, 0)
+            elif isinstance(m, _LinearParams):
+                nn.init.normal_(m.weight, 0, 0.01)
+                nn.init.constant_(m.bias, 0)
+
+    # -- native plumbing ------------------------------------------------------------------
+    def _param_version(self):
+        return tuple((p.data_ptr(), p._version) for p in self.parameters())
+
+    def _ensure_packed(self, dev_index: int):
+        lib = _native.lib()
+        if self._native is None or self._native[1] != dev_index:
+            h = _native.Handle(dev_index)
+            _native.check(lib.kws_model_create(h.ptr, self.num_classes, self.channels, self.num_blocks),
+                          ModelError)
+            self._native = (h, dev_index)
+            self._packed_version = None
+        ver = self._param_version()
+        if ver != self._packed_version:
+            h = self._native[0]
+            for name, t in self.state_dict().items():
+                a = t.detach().to("cpu", torch.float32).contiguous()
+                shape = (C.c_int64 * a.dim())(*a.shape)
+                _native.check(lib.kws_model_load_tensor(h.ptr, name.encode(), C.c_void_p(a.data_ptr()),
+                                                        shape, a.dim()), ModelError)
+            _native.check(lib.kws_model_finalize(h.ptr), ModelError)
+            self._packed_version = ver
+        return self._native[0]
+
+    def native_handle(self, device: Optional[torch.device] = None) -> "_native.Handle":
+        dev = torch.device(device) if device is not None else self.conv1.weight.device
+        if dev.type != "cuda":
+            raise ModelError("kws_b200 runs on CUDA devices only (no CPU fallback)")
+        idx = dev.index if dev.index is not None else torch.cuda.current_device()
+        return self._ensure_packed(idx)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        """``x[B, 1, T, F]`` float32 on CUDA -> logits ``[B, num_classes]``."""
+        if x.dim() != 4 or x.shape[1] != 1:
+            raise ModelError(f"expected input of shape (batch, 1, time, features), got {tuple(x.shape)}")
+        if x.device.type != "cuda":
+            raise ModelError(f"input is on {x.device}; kws_b200 has no CPU fallback")
+        idx = x.device.index
+        h = self._ensure_packed(idx)
+        x = x.to(torch.float32).contiguous()
+        B, _, T, F = x.shape
+        out = torch.empty((B, self.num_classes), dtype=torch.float32, device=x.device)
+        if B:
+            with torch.cuda.device(x.device):
+                _native.check(_native.lib().kws_model_forward(
+                    h.ptr, C.c_void_p(x.data_ptr()), B, T, F, C.c_void_p(out.data_ptr()),
+                    _native.current_stream_ptr(idx)), ModelError)
+        return out
+
+    def launch_count(self) -> int:
+        return self._native[0].launch_count() if self._native else 0

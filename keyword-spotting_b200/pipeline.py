@@ -1,0 +1,69 @@
+"""PCM -> logits in one call: the reference's ``extract_features`` (audio_processor.py:235-278)
+followed by ``DepthwiseSeparableConv.forward`` (models.py:160-183), with the features never
+leaving the device (``kws_pcm_to_logits``).  Batch-sharded across ranks by the caller: clips are
+independent, so there is no collective on this path."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+
+from . import _native
+from .audio_processor import AudioConfig
+from .common.errors import AudioProcessingError, ModelError
+from .models import DepthwiseSeparableConv
+
+
+class KeywordSpotter:
+    def __init__(self, model: DepthwiseSeparableConv, config: Optional[AudioConfig] = None,
+                 numcep: Optional[int] = None, nfilt: Optional[int] = None,
+                 device: Optional[torch.device] = None):
+        self.model = model
+        self.config = config if config is not None else AudioConfig()
+        self.device = torch.device(device) if device is not None else torch.device("cuda", 0)
+        if self.device.type != "cuda":
+            raise ModelError("kws_b200 runs on CUDA devices only (no CPU fallback)")
+        idx = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        self._idx = idx
+        lib = _native.lib()
+        self._h = model.native_handle(self.device)          # model weights live on this handle
+        cfg = _native.FeatureConfig()
+        lib.kws_feature_config_default(C.byref(cfg))
+        sr = self.config.sample_rate
+        cfg.sample_rate = sr
+        cfg.frame_len = int(lib.kws_round_half_up(self.config.frame_length * sr))
+        cfg.frame_step = int(lib.kws_round_half_up(self.config.frame_step * sr))
+        cfg.nfft = max(self.config.fft_size, int(self.config.frame_length * sr))
+        cfg.nfilt = int(nfilt or self.config.num_mel_filters)
+        cfg.numcep = int(numcep or self.config.num_cepstral_coeffs)
+        _native.check(lib.kws_features_configure(self._h.ptr, C.byref(cfg)), AudioProcessingError)
+
+    def __call__(self, pcm: torch.Tensor) -> torch.Tensor:
+        """``pcm[B, N]`` float32 on the device -> logits ``[B, num_classes]``."""
+        lib = _native.lib()
+        self._h = self.model.native_handle(self.device)     # re-pack if the weights changed
+        x = pcm.to(self.device, torch.float32).contiguous()
+        if x.dim() == 1:
+            x = x.unsqueeze(0)
+        B, N = x.shape
+        out = torch.empty((B, self.model.num_classes), dtype=torch.float32, device=self.device)
+        if B:
+            with torch.cuda.device(self.device):
+                _native.check(lib.kws_pcm_to_logits(
+                    self._h.ptr, C.c_void_p(x.data_ptr()), B, N, x.stride(0), C.c_void_p(out.data_ptr()),
+                    _native.current_stream_ptr(self._idx)), ModelError)
+        return out
+
+    def infer_host(self, pcm: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """HOST float32 ``[B, N]`` (ideally pinned) -> HOST logits; copies pipelined in the library."""
+        lib = _native.lib()
+        self._h = self.model.native_handle(self.device)
+        pcm = pcm.contiguous()
+        B, N = pcm.shape
+        if out is None:
+            out = torch.empty((B, self.model.num_classes), dtype=torch.float32, pin_memory=True)
+        with torch.cuda.device(self.device):
+            _native.check(lib.kws_pcm_to_logits_host(self._h.ptr, C.c_void_p(pcm.data_ptr()), B, N,
+                                                     C.c_void_p(out.data_ptr())), ModelError)
+        return out
