@@ -1,0 +1,150 @@
+"""GPU parity: the fused MFCC / log-mel kernel (through the C ABI) against the psf-0.6 oracle
+on the same seeded inputs.  Tolerance = north_star: 1e-3 relative / 1e-4 absolute (fp32 GPU
+vs float64 oracle); frame count and indexing are exact."""
+import numpy as np
+import pytest
+import torch
+
+from kws_b200.audio_processor import AudioConfig, AudioProcessor
+from kws_b200.common.errors import AudioProcessingError
+from kws_b200.utils import synth
+from oracle import psf_mfcc
+
+pytestmark = pytest.mark.gpu
+
+RTOL, ATOL = 1e-3, 1e-4
+
+
+def _close(got, want, what=""):
+    got = np.asarray(got, dtype=np.float64)
+    err = np.abs(got - want)
+    bound = ATOL + RTOL * np.abs(want)
+    bad = err > bound
+    assert not bad.any(), (f"{what}: {bad.sum()} of {bad.size} outside tolerance; worst abs err "
+                           f"{err.max():.3e} at {np.unravel_index(err.argmax(), err.shape)}")
+
+
+@pytest.fixture(scope="module")
+def proc():
+    return AudioProcessor(None, AudioConfig(), device="cuda:0")
+
+
+@pytest.mark.parametrize("numcep,nfilt", [(None, None), (40, 40), (13, 26), (40, None), (12, 40)])
+def test_mfcc_parity_set(proc, numcep, nfilt):
+    pcm = synth.parity_pcm(64)
+    got = proc.extract_features(pcm.cuda(), numcep=numcep, nfilt=nfilt)
+    want = psf_mfcc.extract_features_batch(pcm.numpy(), numcep=numcep, nfilt=nfilt)
+    assert got.dtype == torch.float32 and tuple(got.shape) == want.shape
+    assert want.shape[1] == 99
+    _close(got.cpu().numpy(), want, f"mfcc numcep={numcep} nfilt={nfilt}")
+
+
+def test_all_zero_clip_exact(proc):
+    z = torch.zeros(3, 16000)
+    got = proc.extract_features(z.cuda(), numcep=40, nfilt=40).cpu().numpy()
+    assert got.shape == (3, 99, 40)
+    np.testing.assert_allclose(got[:, :, 0], -36.04365338911715, rtol=0, atol=4e-6)
+    assert np.abs(got[:, :, 1:]).max() == 0.0
+
+
+def test_zero_frames_inside_nonzero_clip(proc):
+    """Time-shift augmentation pads with exact zeros (audio_processor.py:172-188): frames that
+    are entirely zero must give log(eps) rows next to ordinary frames."""
+    pcm = synth.uniform_pcm(2, seed=3)
+    pcm[0, :1600] = 0.0
+    pcm[1, -2000:] = 0.0
+    got = proc.extract_features(pcm.cuda()).cpu().numpy()
+    want = psf_mfcc.extract_features_batch(pcm.numpy())
+    _close(got, want, "zero-padded clips")
+    assert got[0, 0, 0] == pytest.approx(-36.0436533, abs=4e-6) and got[1, 98, 0] == pytest.approx(-36.0436533, abs=4e-6)
+
+
+def test_single_clip_numpy_in_numpy_out(proc):
+    x = synth.uniform_pcm(1, seed=5)[0].numpy()
+    got = proc.extract_features(x)
+    assert isinstance(got, np.ndarray) and got.shape == (99, 10) and got.dtype == np.float64
+    _close(got, psf_mfcc.extract_features(x), "single clip")
+    # legacy spelling and the ignored nfft argument (audio_processor.py:268, signal_handler.py:122)
+    np.testing.assert_array_equal(proc.to_mfcc(x), got)
+    np.testing.assert_array_equal(proc.extract_features(x, nfft=1024), got)
+
+
+def test_batch_rows_equal_single_rows(proc):
+    pcm = synth.uniform_pcm(5, seed=7).cuda()
+    b = proc.extract_features(pcm, numcep=40, nfilt=40)
+    for i in range(5):
+        assert torch.equal(b[i], proc.extract_features(pcm[i], numcep=40, nfilt=40))
+
+
+@pytest.mark.parametrize("n", [1, 399, 400, 401, 560, 561, 3203, 8000, 16001, 20000, 48000])
+def test_ragged_lengths(proc, n):
+    pcm = synth.uniform_pcm(3, n=n, seed=n)
+    got = proc.extract_features(pcm.cuda(), numcep=13).cpu().numpy()
+    want = psf_mfcc.extract_features_batch(pcm.numpy(), numcep=13)
+    assert got.shape == want.shape == (3, psf_mfcc.num_frames(n, 400, 160), 13)
+    _close(got, want, f"N={n}")
+
+
+@pytest.mark.parametrize("winlen,winstep", [(0.02, 0.01), (0.032, 0.016), (0.025, 0.0125), (0.03, 0.02)])
+def test_other_frame_sizes(proc, winlen, winstep):
+    pcm = synth.uniform_pcm(4, seed=11)
+    got = proc.extract_features(pcm.cuda(), winlen=winlen, winstep=winstep).cpu().numpy()
+    want = psf_mfcc.extract_features_batch(pcm.numpy(), winlen=winlen, winstep=winstep)
+    assert got.shape == want.shape
+    _close(got, want, f"winlen={winlen} winstep={winstep}")
+
+
+def test_logfbank(proc):
+    pcm = synth.parity_pcm(16)
+    got = proc.extract_logfbank(pcm.cuda(), nfilt=40).cpu().numpy()
+    want = np.stack([psf_mfcc.logfbank(x, nfilt=40) for x in pcm.numpy()])
+    assert got.shape == want.shape == (16, 99, 40)
+    _close(got, want, "logfbank")
+
+
+def test_int16_ingest(proc):
+    g = torch.Generator().manual_seed(0)
+    i16 = torch.randint(-32768, 32767, (4, 16000), generator=g, dtype=torch.int16)
+    got = proc.extract_features(i16.cuda()).cpu().numpy()
+    as_float = (i16.numpy().astype(np.float32) / 32768.0)       # librosa.load scaling
+    _close(got, psf_mfcc.extract_features_batch(as_float), "int16")
+    assert torch.equal(proc.extract_features(i16.cuda()), proc.extract_features(torch.from_numpy(as_float).cuda()))
+
+
+def test_strided_rows_and_host_path(proc):
+    big = synth.uniform_pcm(6, n=16384, seed=13).cuda()
+    view = big[:, :16000]                       # row stride 16384
+    a = proc.extract_features(view)
+    b = proc.extract_features(view.contiguous())
+    assert torch.equal(a, b)
+    host = synth.uniform_pcm(9000, seed=17)[:5000].pin_memory()   # > one pipeline chunk
+    out = proc.extract_features_host(host, numcep=40, nfilt=40)
+    ref = proc.extract_features(host[:64].cuda(), numcep=40, nfilt=40).cpu()
+    assert torch.equal(out[:64], ref)
+    tail = proc.extract_features(host[-3:].cuda(), numcep=40, nfilt=40).cpu()
+    assert torch.equal(out[-3:], tail)
+
+
+def test_errors(proc):
+    with pytest.raises(AudioProcessingError, match="unsupported nfft"):
+        proc.extract_features(torch.zeros(16000).cuda(), winlen=0.04)     # nfft -> 640
+    with pytest.raises(AudioProcessingError, match="nfilt"):
+        proc.extract_features(torch.zeros(16000).cuda(), nfilt=200)
+    with pytest.raises(AudioProcessingError):
+        proc.extract_features(torch.zeros(2, 3, 16000).cuda())
+    assert proc.extract_features(torch.zeros(0, 16000).cuda()).shape == (0, 99, 10)
+
+
+def test_full_size_properties(proc):
+    """BASELINE config 2 size (65 536 clips): size-independent checks -- duplicated clips give
+    identical rows, a sampled subset matches the oracle, and everything is finite."""
+    B = 65536
+    base = synth.uniform_pcm(1024, seed=19).cuda()
+    pcm = base.repeat(B // 1024, 1)
+    out = proc.extract_features(pcm, numcep=40, nfilt=40)
+    assert tuple(out.shape) == (B, 99, 40) and bool(torch.isfinite(out).all())
+    assert torch.equal(out[:1024], out[-1024:]) and torch.equal(out[1024:2048], out[:1024])
+    idx = [0, 511, 1023]
+    want = psf_mfcc.extract_features_batch(base[idx].cpu().numpy(), numcep=40, nfilt=40)
+    _close(out[idx].cpu().numpy(), want, "full-size sample")
+    assert proc.launch_count() > 0

@@ -1,0 +1,109 @@
+"""GPU parity of the model forward (through the C ABI) against the reference network: golden
+logits produced by the reference class itself, and the oracle restatement on seeded inputs.
+Tolerance = north_star: logits within 1e-3, identical argmax."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from kws_b200.common.errors import ModelError
+from kws_b200.models import DepthwiseSeparableConv
+from kws_b200.pipeline import KeywordSpotter
+from kws_b200.audio_processor import AudioConfig, AudioProcessor
+from kws_b200.utils import synth
+from oracle import dscnn_ref, psf_mfcc
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-3
+
+
+def _golden_model(golden_dir):
+    g = np.load(os.path.join(golden_dir, "dscnn_ref.npz"))
+    sd = {k[3:]: torch.from_numpy(g[k]) for k in g.files if k.startswith("sd.")}
+    m = DepthwiseSeparableConv(num_classes=12)
+    m.load_state_dict(sd)
+    return g, sd, m.cuda()
+
+
+@pytest.mark.parametrize("tag", ["f10", "f40"])
+def test_golden_logits_from_reference(golden_dir, tag):
+    g, sd, m = _golden_model(golden_dir)
+    x = torch.from_numpy(g[f"{tag}.x"]).cuda()
+    got = m(x).cpu().numpy()
+    np.testing.assert_allclose(got, g[f"{tag}.logits"], rtol=0, atol=TOL)
+    assert (got.argmax(1) == g[f"{tag}.logits"].argmax(1)).all()
+    assert m.launch_count() > 0
+
+
+@pytest.mark.parametrize("T,F,B", [(99, 10, 33), (99, 40, 17), (49, 10, 5), (6, 6, 3), (99, 13, 2)])
+def test_against_oracle_seeded(T, F, B):
+    sd = dscnn_ref.init_state_dict(seed=T * 100 + F)
+    m = DepthwiseSeparableConv()
+    m.load_state_dict(sd)
+    m = m.cuda()
+    g = torch.Generator().manual_seed(B)
+    x = torch.randn(B, 1, T, F, generator=g) * 3.0
+    want = dscnn_ref.forward({k: v.double() for k, v in sd.items()}, x.double()).numpy()
+    got = m(x.cuda()).cpu().numpy()
+    np.testing.assert_allclose(got, want, rtol=0, atol=TOL)
+    margin = np.sort(want, axis=1)
+    safe = (margin[:, -1] - margin[:, -2]) > 2 * TOL
+    assert (got.argmax(1)[safe] == want.argmax(1)[safe]).all()
+
+
+def test_extension_channels_blocks():
+    """'DS-CNN-L'-style generalisation (SURVEY a-X1): only channels/num_blocks change."""
+    sd = dscnn_ref.init_state_dict(channels=96, num_blocks=5, seed=4)
+    m = DepthwiseSeparableConv(channels=96, num_blocks=5)
+    m.load_state_dict(sd)
+    x = torch.randn(3, 1, 99, 40, generator=torch.Generator().manual_seed(1))
+    want = dscnn_ref.forward({k: v.double() for k, v in sd.items()}, x.double()).numpy()
+    np.testing.assert_allclose(m.cuda()(x.cuda()).cpu().numpy(), want, rtol=0, atol=TOL)
+
+
+def test_weight_update_is_seen():
+    m = DepthwiseSeparableConv().cuda()
+    x = torch.randn(2, 1, 99, 10).cuda()
+    a = m(x)
+    with torch.no_grad():
+        m.fc.bias.add_(1.0)
+    b = m(x)
+    np.testing.assert_allclose((b - a).cpu().numpy(), 1.0, atol=1e-6)
+
+
+def test_errors():
+    m = DepthwiseSeparableConv().cuda()
+    with pytest.raises(ModelError, match="expected input of shape"):
+        m(torch.zeros(2, 99, 10).cuda())
+    with pytest.raises(ModelError, match="too small"):
+        m(torch.zeros(1, 1, 4, 4).cuda())
+    with pytest.raises(ModelError, match="no CPU fallback"):
+        m(torch.zeros(1, 1, 99, 10))
+    assert m(torch.zeros(0, 1, 99, 10).cuda()).shape == (0, 12)
+
+
+@pytest.mark.parametrize("numcep,nfilt", [(10, 26), (40, 40)])
+def test_pcm_to_logits(numcep, nfilt):
+    """Config 1 shape: PCM -> MFCC -> network -> logits, batch 256, against psf-oracle features
+    fed to the model oracle (float64)."""
+    sd = dscnn_ref.init_state_dict(seed=9)
+    m = DepthwiseSeparableConv()
+    m.load_state_dict(sd)
+    ks = KeywordSpotter(m.cuda(), AudioConfig(), numcep=numcep, nfilt=nfilt, device="cuda:0")
+    pcm = synth.parity_pcm(256)
+    got = ks(pcm.cuda()).cpu().numpy()
+    n_chk = 48
+    feats = psf_mfcc.extract_features_batch(pcm[:n_chk].numpy(), numcep=numcep, nfilt=nfilt)
+    want = dscnn_ref.forward({k: v.double() for k, v in sd.items()},
+                             torch.from_numpy(feats).unsqueeze(1)).numpy()
+    np.testing.assert_allclose(got[:n_chk], want, rtol=0, atol=TOL)
+    margin = np.sort(want, axis=1)
+    safe = (margin[:, -1] - margin[:, -2]) > 2 * TOL
+    assert (got[:n_chk].argmax(1)[safe] == want.argmax(1)[safe]).all()
+    # the fused entry point equals features -> model through the two public objects
+    proc = AudioProcessor(None, AudioConfig(), device="cuda:0")
+    two_step = m(proc.extract_features(pcm.cuda(), numcep=numcep, nfilt=nfilt).unsqueeze(1))
+    np.testing.assert_allclose(got, two_step.cpu().numpy(), rtol=0, atol=1e-5)
+    host = ks.infer_host(pcm.pin_memory())
+    np.testing.assert_allclose(host.numpy(), got, rtol=0, atol=1e-6)
