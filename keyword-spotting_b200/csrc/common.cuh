@@ -49,6 +49,8 @@ struct FeatureTables {
   float2* d_melw = nullptr;     // [257] (rising weight, falling weight) of the bin's segment
   int* d_segedge = nullptr;     // [nfilt+2] bin edges
   float* d_dct = nullptr;       // [nfilt][ncep_pad], lifter folded in
+  float* d_dctB = nullptr;      // tensor-core DCT B operand image (hi, lo), null when nfilt > 48
+  int dct_kpad = 0;             // K of that GEMM: nfilt rounded up to 8
   std::vector<int> h_edges;
 };
 
@@ -97,6 +99,9 @@ namespace kws {
 enum FeatureMode { kModeMfcc = 0, kModeLogMel = 1 };
 int launch_mfcc(kws_handle_t h, const void* pcm_dev, bool is_i16, int64_t B, int64_t N,
                 int64_t pcm_stride, float* out_dev, int mode, cudaStream_t stream);
+// mfcc_fast.cu: 1 = handled, 0 = configuration needs the generic kernel, <0 = error
+int launch_mfcc_fast(kws_handle_t h, const float* pcm_dev, int64_t B, int64_t N, int64_t pcm_stride,
+                     float* out_dev, int mode, cudaStream_t stream);
 // tables.cu
 int build_feature_tables(kws_handle_t h, const kws_feature_config* cfg);
 void free_feature_tables(FeatureTables& t);

@@ -64,6 +64,7 @@ void free_feature_tables(FeatureTables& t) {
   free_dev(t.d_melw);
   free_dev(t.d_segedge);
   free_dev(t.d_dct);
+  free_dev(t.d_dctB);
   t = FeatureTables();
 }
 
@@ -135,6 +136,32 @@ int build_feature_tables(kws_handle_t h, const kws_feature_config* cfg) {
   if ((rc = upload(&t.d_melw, melw))) return rc;
   if ((rc = upload(&t.d_segedge, iedges))) return rc;
   if ((rc = upload(&t.d_dct, dctf))) return rc;
+  if (M <= 48) {
+    // B operand of the tensor-core DCT (mfcc_fast.cu): B[n][k] = lifter*dct[k][n], n = coefficient
+    // (48 rows), k = mel index (kpad columns), split into tf32 hi + lo and laid out in the
+    // canonical K-major no-swizzle UMMA layout: 8-row groups of kpad/4 core matrices (8 x 16 B).
+    auto tf32_rn = [](float v) {
+      uint32_t b;
+      std::memcpy(&b, &v, 4);
+      b = (b + 0x1000u) & 0xffffe000u;  // round to nearest (ties away), like cvt.rna.tf32.f32
+      float r;
+      std::memcpy(&r, &b, 4);
+      return r;
+    };
+    const int kpad = (M + 7) & ~7;
+    const size_t group = (size_t)(kpad / 4) * 32;  // floats per 8-row group
+    std::vector<float> img(2 * 6 * group, 0.f);
+    for (int n = 0; n < t.ncep; ++n)
+      for (int k = 0; k < M; ++k) {
+        const float v = (float)dct[(size_t)k * t.ncep + n];
+        const float hi = tf32_rn(v), lo = tf32_rn(v - hi);
+        const size_t idx = (size_t)(n / 8) * group + (size_t)(k / 4) * 32 + (size_t)(n % 8) * 4 + (k % 4);
+        img[idx] = hi;
+        img[6 * group + idx] = lo;
+      }
+    if ((rc = upload(&t.d_dctB, img))) return rc;
+    t.dct_kpad = kpad;
+  }
   if (cfg->window_host) {
     std::vector<float> w(cfg->window_host, cfg->window_host + cfg->frame_len);
     if ((rc = upload(&t.d_window, w))) return rc;

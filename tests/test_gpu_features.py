@@ -108,7 +108,9 @@ def test_int16_ingest(proc):
     got = proc.extract_features(i16.cuda()).cpu().numpy()
     as_float = (i16.numpy().astype(np.float32) / 32768.0)       # librosa.load scaling
     _close(got, psf_mfcc.extract_features_batch(as_float), "int16")
-    assert torch.equal(proc.extract_features(i16.cuda()), proc.extract_features(torch.from_numpy(as_float).cuda()))
+    # int16 ingest runs the generic kernel, float32 input the fast one: same features within fp32 noise
+    torch.testing.assert_close(proc.extract_features(i16.cuda()),
+                               proc.extract_features(torch.from_numpy(as_float).cuda()), rtol=1e-4, atol=2e-5)
 
 
 def test_strided_rows_and_host_path(proc):
