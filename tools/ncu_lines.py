@@ -35,8 +35,9 @@ out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_ou
 rows = list(csv.reader(out.splitlines()))
 hdr = rows[1]
 ia, ii, isamp = hdr.index("Address"), hdr.index("Instructions Executed"), hdr.index("# Samples")
+iw, ie = hdr.index("L1 Wavefronts Shared"), hdr.index("L1 Wavefronts Shared Excessive")
 base = None
-agg = collections.defaultdict(lambda: [0, 0])
+agg = collections.defaultdict(lambda: [0, 0, 0, 0])
 tot_i = tot_s = 0
 for r in rows[2:]:
     if len(r) <= isamp or not r[ia].startswith("0x"):
@@ -45,8 +46,10 @@ for r in rows[2:]:
     if base is None:
         base = a
     key = line_of.get(a - base)
-    agg[key][0] += int(r[ii]); agg[key][1] += int(r[isamp])
+    agg[key][0] += int(r[ii]); agg[key][1] += int(r[isamp]); agg[key][2] += int(r[iw] or 0); agg[key][3] += int(r[ie] or 0)
     tot_i += int(r[ii]); tot_s += int(r[isamp])
 print(f"total warp-instr {tot_i}, samples {tot_s}")
-for k, (i, s) in sorted(agg.items(), key=lambda kv: -kv[1][0])[:top]:
-    print(f"{str(k):34s} instr {100*i/tot_i:5.1f}%  samples {100*s/max(tot_s,1):5.1f}%")
+tot_w = sum(v[2] for v in agg.values())
+print(f"shared wavefronts {tot_w}")
+for k, (i, s, w, e) in sorted(agg.items(), key=lambda kv: -kv[1][0])[:top]:
+    print(f"{str(k):34s} instr {100*i/tot_i:5.1f}%  samples {100*s/max(tot_s,1):5.1f}%  smem-wf {100*w/max(tot_w,1):5.1f}% (excess {100*e/max(tot_w,1):4.1f}%)")
