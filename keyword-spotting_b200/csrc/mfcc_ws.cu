@@ -1,0 +1,501 @@
+// Fast, warp-specialised variant of the fused PCM -> MFCC kernel (see mfcc.cu for the algorithm
+// and the reference call chain it replaces: kws/libs/audio_processor.py:235-278 -> psf.mfcc).
+//
+// Same decomposition as mfcc.cu (tile = 20 frames of one clip, warp = 4 frames, half-warp =
+// 2 frames packed in f32x2 registers, 256-point complex FFT = 16 lanes x radix-16 twice).  The
+// kernel is bound by instruction issue and shared-memory bandwidth, not HBM, so
+// this variant removes instructions, exposed latency and every CTA-wide barrier:
+//   * 6 warps per CTA, 2 CTAs per SM.  Warp 0 is a SERVICE warp: it streams raw PCM tiles into a
+//     2-stage shared-memory ring with TMA bulk copies (cp.async.bulk + mbarrier full/empty pairs),
+//     issues the tensor-core DCT of each finished tile and drains its accumulator from TMEM to
+//     global memory.  Warps 1..5 are COMPUTE warps that never wait for each other: they only meet
+//     at mbarriers (tile landed / A rows written / previous MMA retired).
+//   * each compute warp pre-emphasises (fp32, two roundings = psf's float32 step) exactly the
+//     880 samples its 4 frames span and stores them interleaved, S2[i] = (y[i], y[i+hop]), in its
+//     private scratch, so one LDS.128 yields the packed (re, im) pair of both frames;
+//   * FADD2/FFMA2 operand modifiers (negate, scalar broadcast) keep twiddles and weights scalar;
+//   * the real-FFT split computes X[k] and X[256-k] together from one shuffled mirror value;
+//   * DCT-II (+lifter) of the tile, [20 x M] x [M x C], on the tensor core: tcgen05.mma kind::tf32
+//     with a 3-term hi/lo split (fp32-grade), K-major no-swizzle operands, accumulator in TMEM,
+//     tcgen05.commit -> mbarrier, tcgen05.ld epilogue in the service warp;
+//   * log is a range-reduced MUFU.LG2.
+// Configurations it does not cover (window function, frame_len != 400, nfilt > 48, unaligned
+// input, hop > 344) fall back to the generic kernel in mfcc.cu.
+#include "mfcc_dev.cuh"
+
+namespace kws {
+
+struct FastParams {
+  const float* pcm;
+  float* out;
+  long long B, N, stride, total_tiles;
+  int nframes, tiles_per_clip, hop, M, ncep, mode, append_energy;
+  float preemph;
+  const float2* tw256;
+  const float2* twp;    // [128] W512^k
+  const float2* melw;   // [257] (rising, falling) weight of the bin's segment
+  const int* edges;     // [M+2]
+  const float* dctB;    // B operand image: hi then lo, canonical K-major layout [48 x Kpad] each
+  int kpad, tile_len, raw_stride;  // raw_stride: bytes between the two raw stages
+  int off_a, off_scratch, off_b, off_melw, off_edges, off_twp, off_c0;
+};
+
+constexpr int kCWarps = kFramesPerTile / 4;        // 5 compute warps
+constexpr int kWsThreads = (kCWarps + 1) * 32;     // + service warp
+constexpr int kWarpScratch = 2 * 16 * 17 * 16;     // bytes: two half-warp transposes (also holds S2)
+constexpr float kFEps = 2.220446049250313e-16f;
+
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+
+template <int LOAD_LEN, int ROUNDS>
+__global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastParams p) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  // [0,1] raw stage full, [2,3] raw stage empty, [4] A rows of the tile written, [5] tile MMAs retired
+  __shared__ __align__(8) unsigned long long s_bar[6];
+  __shared__ uint32_t s_tmem;
+  const float2* s_melw = reinterpret_cast<const float2*>(smem + p.off_melw);
+  const int* s_edges = reinterpret_cast<const int*>(smem + p.off_edges);
+  const float2* s_twp = reinterpret_cast<const float2*>(smem + p.off_twp);
+  float* s_c0 = reinterpret_cast<float*>(smem + p.off_c0);  // [2][20]
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const bool do_dct = (p.mode == kModeMfcc);
+  const uint32_t bar_full = smem_u32(&s_bar[0]), bar_empty = smem_u32(&s_bar[2]);
+  const uint32_t bar_afull = smem_u32(&s_bar[4]), bar_mma = smem_u32(&s_bar[5]);
+  const int hop = p.hop;
+  const uint32_t sbo = (uint32_t)(p.kpad / 4) * 128u;  // bytes between 8-row groups of A and B
+
+  if (tid == 0) {
+    mbar_init(bar_full, 1);
+    mbar_init(bar_full + 8, 1);
+    mbar_init(bar_empty, kCWarps);
+    mbar_init(bar_empty + 8, kCWarps);
+    mbar_init(bar_afull, kCWarps);
+    mbar_init(bar_mma, 1);
+    fence_mbar_init();
+  }
+  if (warp == 0 && do_dct) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)),
+                 "n"(kTmemCols));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  {
+    float2* d = reinterpret_cast<float2*>(smem + p.off_melw);
+    for (int i = tid; i < kBins; i += kWsThreads) d[i] = p.melw[i];
+    int* e = reinterpret_cast<int*>(smem + p.off_edges);
+    for (int i = tid; i < p.M + 2; i += kWsThreads) e[i] = p.edges[i];
+    float2* t = reinterpret_cast<float2*>(smem + p.off_twp);
+    for (int i = tid; i < 128; i += kWsThreads) t[i] = p.twp[i];
+    float* b = reinterpret_cast<float*>(smem + p.off_b);
+    for (int i = tid; i < 2 * kDctN * p.kpad; i += kWsThreads) b[i] = p.dctB[i];
+    float* a = reinterpret_cast<float*>(smem + p.off_a);
+    for (int i = tid; i < 2 * 24 * p.kpad; i += kWsThreads) a[i] = 0.f;
+  }
+  fence_proxy_async();  // B (and the zeroed A) were written through the generic proxy
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = do_dct ? s_tmem : 0u;
+  // tiles of this CTA: blockIdx.x + it * gridDim.x, it = 0 .. n_it-1
+  const int n_it = (p.total_tiles > (long long)blockIdx.x)
+                       ? (int)((p.total_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x)
+                       : 0;
+
+  if (warp == 0) {
+    // =========================== service warp ===========================
+    auto issue_tma = [&](int it) {  // one thread: raw[stage][j] = x[s0 - 4 + j]
+      const long long tile_id = (long long)blockIdx.x + (long long)it * gridDim.x;
+      const long long clip = tile_id / p.tiles_per_clip;
+      const int t = (int)(tile_id - clip * p.tiles_per_clip);
+      const long long s0 = (long long)t * kFramesPerTile * hop;
+      const long long first = s0 >= 4 ? s0 - 4 : 0;
+      long long end = s0 + p.tile_len;
+      if (end > p.N) end = p.N;
+      const uint32_t bytes = (uint32_t)(end - first) * 4u;
+      const uint32_t bar = bar_full + 8u * (it & 1);
+      float* raw = reinterpret_cast<float*>(smem + (size_t)(it & 1) * p.raw_stride);
+      mbar_expect_tx(bar, bytes);
+      tma_load_1d(smem_u32(raw + (s0 >= 4 ? 0 : 4)), p.pcm + clip * p.stride + first, bytes, bar);
+    };
+    auto issue_mma = [&]() {  // one thread: D[128 x 48] = Ahi*Bhi + Alo*Bhi + Ahi*Blo over Kpad
+      tc_fence_after();
+      const uint32_t a_hi = smem_u32(smem + p.off_a), a_lo = a_hi + 3u * sbo;
+      const uint32_t b_hi = smem_u32(smem + p.off_b), b_lo = b_hi + (uint32_t)(kDctN / 8) * sbo;
+      const int ksteps = p.kpad / 8;
+      uint32_t acc = 0;
+#pragma unroll 1
+      for (int term = 0; term < 3; ++term) {
+        const uint32_t ab = term == 1 ? a_lo : a_hi, bb = term == 2 ? b_lo : b_hi;
+        for (int ks = 0; ks < ksteps; ++ks) {
+          tc_mma_tf32(tmem, umma_desc(ab + ks * 256u, 128u, sbo), umma_desc(bb + ks * 256u, 128u, sbo), kIdesc, acc);
+          acc = 1;
+        }
+      }
+      tc_commit(bar_mma);
+    };
+    if (lane == 0) {
+      if (n_it > 0) issue_tma(0);
+      if (n_it > 1) issue_tma(1);
+    }
+    for (int it = 0; it < n_it; ++it) {
+      const long long tile_id = (long long)blockIdx.x + (long long)it * gridDim.x;
+      const long long clip = tile_id / p.tiles_per_clip;
+      const int t = (int)(tile_id - clip * p.tiles_per_clip);
+      if (it + 2 < n_it) {  // refill this stage as soon as every compute warp has converted tile `it`
+        mbar_wait(bar_empty + 8u * (it & 1), (it >> 1) & 1);
+        if (lane == 0) {
+          fence_proxy_async();
+          issue_tma(it + 2);
+        }
+        __syncwarp();
+      }
+      if (do_dct) {
+        mbar_wait(bar_afull, it & 1);
+        if (lane == 0) issue_mma();
+        __syncwarp();
+        mbar_wait(bar_mma, it & 1);
+        // ---- epilogue (lane = frame row of the tile): TMEM -> registers -> global ----
+        float v[kDctN];
+        tc_fence_after();
+        {
+          float q[16];
+#pragma unroll
+          for (int c = 0; c < kDctN / 16; ++c) {
+            tc_ld16(tmem + c * 16, q);
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[c * 16 + i] = q[i];
+          }
+        }
+        tc_wait_ld();
+        tc_fence_before();
+        const int f = t * kFramesPerTile + lane;
+        if (lane < kFramesPerTile && f < p.nframes) {
+          const float c0 = s_c0[(it & 1) * kFramesPerTile + lane];
+          v[0] = p.append_energy ? c0 : v[0] + c0;
+          float* o = p.out + ((size_t)clip * p.nframes + f) * p.ncep;
+          if ((p.ncep & 3) == 0) {
+#pragma unroll
+            for (int c = 0; c < kDctN; c += 4)
+              if (c < p.ncep) *reinterpret_cast<float4*>(o + c) = make_float4(v[c], v[c + 1], v[c + 2], v[c + 3]);
+          } else {
+#pragma unroll
+            for (int c = 0; c < kDctN; ++c)
+              if (c < p.ncep) o[c] = v[c];
+          }
+        }
+      }
+    }
+  } else {
+    // =========================== compute warps ===========================
+    const int cw = warp - 1, half = lane >> 4, l = lane & 15;
+    unsigned char* wscratch = smem + p.off_scratch + cw * kWarpScratch;
+    float2* s2 = reinterpret_cast<float2*>(wscratch);               // private interleaved samples
+    unsigned char* scratch = wscratch + half * (kWarpScratch / 2);  // this half-warp's transpose area
+    float4* s_tr = reinterpret_cast<float4*>(scratch);
+    V* s_P = reinterpret_cast<V*>(scratch);
+    V* s_R = reinterpret_cast<V*>(scratch + 2064);
+    V* s_F = s_R + (16 * ROUNDS + 1);
+    float twr[16], twi[16];  // W256^(l k1); FFMA2 takes a scalar register as a broadcast operand
+#pragma unroll
+    for (int k = 1; k < 16; ++k) {
+      const float2 w = p.tw256[(l * k) & 255];
+      twr[k] = w.x;
+      twi[k] = w.y;
+    }
+    const float pre = p.preemph;
+    const int n = (int)p.N;
+    const int conv_len = 2 * hop + LOAD_LEN;  // S2 entries this warp's two frame pairs read
+    const int wbase = 4 * cw * hop;           // tile-local sample index of the warp's first frame
+
+    for (int it = 0; it < n_it; ++it) {
+      const long long tile_id = (long long)blockIdx.x + (long long)it * gridDim.x;
+      const long long clip = tile_id / p.tiles_per_clip;
+      const int t = (int)(tile_id - clip * p.tiles_per_clip);
+      const int s0 = t * kFramesPerTile * hop;
+      const float* raw = reinterpret_cast<const float*>(smem + (size_t)(it & 1) * p.raw_stride);
+      __syncwarp();  // previous tile: every lane is done with the scratch this conversion overwrites
+      mbar_wait(bar_full + 8u * (it & 1), (it >> 1) & 1);
+      // ---- conversion: S2[j] = (y[b+j], y[b+j+hop]), y = pre-emphasised signal, b = wbase ----
+      {
+        const int g0 = s0 + wbase;
+        const bool tail = g0 + conv_len + hop > n;  // samples >= N: the raw stage holds stale data there
+        const float* rb = raw + 4 + wbase;
+        if (!tail) {
+#pragma unroll 4
+          for (int j = lane * 2; j < conv_len; j += 64) {
+            const float* r = rb + j;
+            const float2 va = *reinterpret_cast<const float2*>(r);
+            const float2 vb = *reinterpret_cast<const float2*>(r + hop);
+            float am = r[-1];
+            const float bm = r[hop - 1];
+            if (g0 + j == 0) am = 0.f;  // y[0] = x[0]
+            float4 o;
+            o.x = __fsub_rn(va.x, __fmul_rn(pre, am));    // y[g]
+            o.y = __fsub_rn(vb.x, __fmul_rn(pre, bm));    // y[g+hop]
+            o.z = __fsub_rn(va.y, __fmul_rn(pre, va.x));  // y[g+1]
+            o.w = __fsub_rn(vb.y, __fmul_rn(pre, vb.x));  // y[g+hop+1]
+            *reinterpret_cast<float4*>(s2 + j) = o;
+          }
+        } else {
+          for (int j = lane * 2; j < conv_len; j += 64) {
+            const int g = g0 + j;
+            const float* r = rb + j;
+            const float2 va = *reinterpret_cast<const float2*>(r);
+            const float2 vb = *reinterpret_cast<const float2*>(r + hop);
+            const float am = (g > 0) ? r[-1] : 0.f, bm = r[hop - 1];
+            float4 o;
+            o.x = (g < n) ? __fsub_rn(va.x, __fmul_rn(pre, am)) : 0.f;
+            o.y = (g + hop < n) ? __fsub_rn(vb.x, __fmul_rn(pre, bm)) : 0.f;
+            o.z = (g + 1 < n) ? __fsub_rn(va.y, __fmul_rn(pre, va.x)) : 0.f;
+            o.w = (g + hop + 1 < n) ? __fsub_rn(vb.y, __fmul_rn(pre, vb.x)) : 0.f;
+            *reinterpret_cast<float4*>(s2 + j) = o;
+          }
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_empty + 8u * (it & 1));  // this warp no longer reads the raw stage
+
+      const int fa_local = cw * 4 + half * 2;
+      const int fA = t * kFramesPerTile + fa_local, fB = fA + 1;
+      const bool active = (t * kFramesPerTile + cw * 4) < p.nframes;  // warp-uniform
+      V lm[ROUNDS];
+      V mean = fsplat(0.f), esum = fsplat(0.f);
+      if (active) {
+        const float2* pa = s2 + half * 2 * hop;
+        CF x16[16];
+#pragma unroll
+        for (int m = 0; m < 16; ++m) {
+          const int idx = 32 * m + 2 * l;
+          float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (32 * m + 31 < LOAD_LEN) {
+            v = *reinterpret_cast<const float4*>(pa + idx);
+          } else if (32 * m < LOAD_LEN) {
+            if (idx + 1 < LOAD_LEN) v = *reinterpret_cast<const float4*>(pa + idx);
+            else if (idx < LOAD_LEN) { const float2 u = pa[idx]; v.x = u.x; v.y = u.y; }
+          }
+          x16[m].re = make_float2(v.x, v.y);
+          x16[m].im = make_float2(v.z, v.w);
+        }
+        __syncwarp();  // S2 lives in the transpose area: all loads before the first transposed store
+        dft16(x16);
+#pragma unroll
+        for (int k1 = 0; k1 < 16; ++k1) {
+          CF y = x16[Q16(k1)];
+          if (k1 > 0) {
+            CF z;
+            z.re = ffma(fneg(y.im), fsplat(twi[k1]), fmul(y.re, fsplat(twr[k1])));
+            z.im = ffma(y.im, fsplat(twr[k1]), fmul(y.re, fsplat(twi[k1])));
+            y = z;
+          }
+          s_tr[k1 * 17 + l] = make_float4(y.re.x, y.re.y, y.im.x, y.im.y);
+        }
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const float4 v = s_tr[l * 17 + j];
+          x16[j].re = make_float2(v.x, v.y);
+          x16[j].im = make_float2(v.z, v.w);
+        }
+        __syncwarp();
+        dft16(x16);  // Z[l + 16 k2] at x16[Q16(k2)]
+
+        // ---- real-FFT split, two bins per step: k = l + 16 k2 and 256 - k ----
+        const int partner = (lane & 16) | ((16 - l) & 15);
+        const bool l0 = (l == 0);
+        const V sc = fsplat(1.0f / 2048.0f);
+#pragma unroll
+        for (int k2 = 0; k2 < 8; ++k2) {
+          const CF zk = x16[Q16(k2)];
+          const CF own = x16[Q16((16 - k2) & 15)];
+          const CF oth = x16[Q16(15 - k2)];
+          CF zp;
+          zp.re.x = __shfl_sync(0xffffffffu, l0 ? own.re.x : oth.re.x, partner);
+          zp.re.y = __shfl_sync(0xffffffffu, l0 ? own.re.y : oth.re.y, partner);
+          zp.im.x = __shfl_sync(0xffffffffu, l0 ? own.im.x : oth.im.x, partner);
+          zp.im.y = __shfl_sync(0xffffffffu, l0 ? own.im.y : oth.im.y, partner);
+          const float2 w = s_twp[l + 16 * k2];
+          const V wr = fsplat(w.x), wi = fsplat(w.y);
+          const V sr = fadd(zk.re, zp.re), si = fsub(zk.im, zp.im);
+          const V dr = fsub(zk.re, zp.re), di = fadd(zk.im, zp.im);
+          const V tr = ffma(di, wr, fmul(dr, wi));          // T = -i W D
+          const V ti = ffma(di, wi, fneg(fmul(dr, wr)));
+          const V ar = fadd(sr, tr), ai = fadd(si, ti);     // 2 X[k]
+          const V br = fsub(sr, tr), bi = fsub(si, ti);     // conj(2 X[256-k])
+          const V pk = fmul(ffma(ai, ai, fmul(ar, ar)), sc);
+          const V pm = fmul(ffma(bi, bi, fmul(br, br)), sc);
+          s_P[l + 16 * k2] = pk;
+          s_P[256 - l - 16 * k2] = pm;
+          esum = fadd(esum, fadd(pk, pm));
+        }
+        if (l0) {  // bin 128 is its own mirror: |X[128]|^2 = |Z[128]|^2
+          const CF z8 = x16[Q16(8)];
+          const V p8 = fmul(ffma(z8.im, z8.im, fmul(z8.re, z8.re)), fsplat(1.0f / 512.0f));
+          s_P[128] = p8;
+          esum = fadd(esum, p8);
+        }
+#pragma unroll
+        for (int o = 8; o >= 1; o >>= 1) {
+          esum.x += __shfl_xor_sync(0xffffffffu, esum.x, o);
+          esum.y += __shfl_xor_sync(0xffffffffu, esum.y, o);
+        }
+        __syncwarp();
+
+        // ---- mel bank by segment ----
+        for (int s = l; s <= p.M; s += 16) {
+          V r = fsplat(0.f), f = fsplat(0.f);
+          const int k1 = s_edges[s + 1];
+          for (int k = s_edges[s]; k < k1; ++k) {
+            const V pw = s_P[k];
+            const float2 w = s_melw[k];
+            r = ffma(pw, fsplat(w.x), r);
+            f = ffma(pw, fsplat(w.y), f);
+          }
+          s_R[s] = r;
+          s_F[s] = f;
+        }
+        __syncwarp();
+        V msum = fsplat(0.f);
+#pragma unroll
+        for (int r = 0; r < ROUNDS; ++r) {
+          const int j = l + 16 * r;
+          lm[r] = fsplat(0.f);
+          if (j < p.M) {
+            V m = fadd(s_R[j], s_F[j + 1]);
+            m.x = (m.x == 0.f) ? kFEps : m.x;
+            m.y = (m.y == 0.f) ? kFEps : m.y;
+            lm[r] = make_float2(fast_log(m.x), fast_log(m.y));
+            msum = fadd(msum, lm[r]);
+          }
+        }
+        if (!do_dct) {
+#pragma unroll
+          for (int r = 0; r < ROUNDS; ++r) {
+            const int j = l + 16 * r;
+            if (j < p.M) {
+              if (fA < p.nframes) p.out[((size_t)clip * p.nframes + fA) * p.M + j] = lm[r].x;
+              if (fB < p.nframes) p.out[((size_t)clip * p.nframes + fB) * p.M + j] = lm[r].y;
+            }
+          }
+        } else {
+#pragma unroll
+          for (int o = 8; o >= 1; o >>= 1) {
+            msum.x += __shfl_xor_sync(0xffffffffu, msum.x, o);
+            msum.y += __shfl_xor_sync(0xffffffffu, msum.y, o);
+          }
+          mean = fmul(msum, fsplat(1.0f / (float)p.M));
+        }
+      }
+
+      if (do_dct) {
+        // the previous tile's MMAs must have retired before its A rows are overwritten
+        if (it > 0) mbar_wait(bar_mma, (it - 1) & 1);
+        if (active) {
+          // A rows fa_local (x) and fa_local+1 (y): centred log-mel split into tf32 hi + lo
+          unsigned char* abase = smem + p.off_a;
+#pragma unroll
+          for (int r = 0; r < ROUNDS; ++r) {
+            const int nn = l + 16 * r;
+            if (nn < p.M) {
+              const V xc = fsub(lm[r], mean);
+              const float hx = to_tf32(xc.x), hy = to_tf32(xc.y);
+              const float lx = to_tf32(xc.x - hx), ly = to_tf32(xc.y - hy);
+              const uint32_t col = (uint32_t)(nn >> 2) * 128u + (uint32_t)(nn & 3) * 4u;
+              const uint32_t oa = (uint32_t)(fa_local >> 3) * sbo + (uint32_t)(fa_local & 7) * 16u + col;
+              const uint32_t ob = (uint32_t)((fa_local + 1) >> 3) * sbo + (uint32_t)((fa_local + 1) & 7) * 16u + col;
+              *reinterpret_cast<float*>(abase + oa) = hx;
+              *reinterpret_cast<float*>(abase + ob) = hy;
+              *reinterpret_cast<float*>(abase + 3u * sbo + oa) = lx;
+              *reinterpret_cast<float*>(abase + 3u * sbo + ob) = ly;
+            }
+          }
+          if (l == 0) {
+            const float eA = (esum.x == 0.f) ? kFEps : esum.x, eB = (esum.y == 0.f) ? kFEps : esum.y;
+            const float sq = sqrtf((float)p.M);
+            float* c0 = s_c0 + (it & 1) * kFramesPerTile + fa_local;
+            c0[0] = p.append_energy ? fast_log(eA) : sq * mean.x;  // else: the removed mean only moves c0
+            c0[1] = p.append_energy ? fast_log(eB) : sq * mean.y;
+          }
+        }
+        fence_proxy_async();  // generic-proxy writes of A must be visible to the tensor core
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_afull);
+      }
+    }
+  }
+  __syncthreads();
+  if (warp == 0 && do_dct)
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(kTmemCols));
+}
+
+// returns 1 when the fast kernel handled the launch, 0 when the configuration needs the generic
+// kernel, negative on error
+int launch_mfcc_fast(kws_handle_t h, const float* pcm_dev, int64_t B, int64_t N, int64_t pcm_stride,
+                     float* out_dev, int mode, cudaStream_t stream) {
+  const FeatureTables& t = h->feat;
+  const int M = t.cfg.nfilt, hop = t.cfg.frame_step;
+  if (t.d_window != nullptr || t.load_len != 400 || M > 48 || t.d_dctB == nullptr) return 0;
+  // TMA bulk copies need 16-byte aligned sources and sizes; the interleaved tile needs an even hop
+  if ((hop & 3) != 0 || (N & 3) != 0 || (pcm_stride & 3) != 0 || (reinterpret_cast<size_t>(pcm_dev) & 15) != 0)
+    return 0;
+  if ((size_t)(2 * hop + 400) * 8 > (size_t)kWarpScratch || N >= (1ll << 30)) return 0;
+  constexpr int ROUNDS = 3;
+  FastParams p{};
+  p.pcm = pcm_dev;
+  p.out = out_dev;
+  p.B = B;
+  p.N = N;
+  p.stride = pcm_stride;
+  p.nframes = (int)kws_num_frames(N, t.cfg.frame_len, t.cfg.frame_step);
+  p.tiles_per_clip = (p.nframes + kFramesPerTile - 1) / kFramesPerTile;
+  p.total_tiles = (long long)B * p.tiles_per_clip;
+  p.hop = hop;
+  p.M = M;
+  p.ncep = t.ncep;
+  p.mode = mode;
+  p.append_energy = t.cfg.append_energy;
+  p.preemph = t.cfg.preemph;
+  p.tw256 = t.d_tw256;
+  p.twp = t.d_tw512;
+  p.melw = t.d_melw;
+  p.edges = t.d_segedge;
+  p.dctB = t.d_dctB;
+  p.kpad = t.dct_kpad;
+  p.tile_len = (kFramesPerTile - 1) * hop + 400;  // samples a tile's 20 frames span
+  const uint32_t sbo = (uint32_t)(p.kpad / 4) * 128u;
+  p.raw_stride = (int)(((size_t)(p.tile_len + 4) * 4 + 127) & ~(size_t)127);
+  size_t off = (size_t)2 * p.raw_stride;           // two raw stages at offset 0
+  p.off_a = (int)off;                              // A hi rows 0..23, then A lo rows 0..23
+  off += (size_t)6 * sbo;
+  p.off_scratch = (int)off;
+  off += (size_t)kCWarps * kWarpScratch;
+  p.off_b = (int)off;                              // B hi [48 x kpad], then B lo
+  off += (size_t)2 * (kDctN / 8) * sbo;
+  p.off_melw = (int)off;
+  off += (size_t)kBins * 8 + 8;
+  p.off_edges = (int)off;
+  off += ((size_t)(M + 2) * 4 + 15) & ~(size_t)15;
+  p.off_twp = (int)off;
+  off += 128 * 8;
+  p.off_c0 = (int)off;
+  off += 2 * kFramesPerTile * 4;
+  const size_t smem_bytes = off;
+  static_assert(2064 + 2 * (16 * ROUNDS + 1) * 8 <= kWarpScratch / 2, "scratch layout overflow");
+  // the tensor core reads 128 rows of A: 16 row groups past each base must stay inside the CTA's
+  // shared memory (rows >= 24 are don't-care values that only reach accumulator rows we never read)
+  if ((size_t)p.off_a + (size_t)(3 + 16) * sbo > smem_bytes || smem_bytes > 112 * 1024) return 0;
+
+  auto kern = mfcc512_ws_kernel<400, ROUNDS>;
+  KWS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+  // two CTAs per SM by construction (<= 112 KB shared memory and <= 168 registers each); ask for
+  // the full shared-memory carve-out so the second CTA is not refused
+  KWS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+  long long grid = (long long)h->sm_count * 2;
+  if (grid > p.total_tiles) grid = p.total_tiles;
+  kern<<<(unsigned)grid, kWsThreads, smem_bytes, stream>>>(p);
+  KWS_CHECK_LAUNCH(h);
+  return 1;
+}
+
+}  // namespace kws
