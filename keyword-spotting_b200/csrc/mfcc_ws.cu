@@ -55,7 +55,7 @@ __global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastPar
   // [0,1] raw stage full, [2,3] raw stage empty, [4] A rows of the tile written, [5] tile MMAs retired
   __shared__ __align__(8) unsigned long long s_bar[6];
   __shared__ uint32_t s_tmem;
-  const float2* s_melw = reinterpret_cast<const float2*>(smem + p.off_melw);
+  const float* s_inv = reinterpret_cast<const float*>(smem + p.off_melw);  // [M+1] 1 / segment length
   const int* s_edges = reinterpret_cast<const int*>(smem + p.off_edges);
   const float2* s_twp = reinterpret_cast<const float2*>(smem + p.off_twp);
   float* s_c0 = reinterpret_cast<float*>(smem + p.off_c0);  // [2][20]
@@ -82,8 +82,8 @@ __global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastPar
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
   }
   {
-    float2* d = reinterpret_cast<float2*>(smem + p.off_melw);
-    for (int i = tid; i < kBins; i += kWsThreads) d[i] = p.melw[i];
+    float* d = reinterpret_cast<float*>(smem + p.off_melw);
+    for (int i = tid; i <= p.M; i += kWsThreads) d[i] = 1.0f / (float)(p.edges[i + 1] - p.edges[i]);
     int* e = reinterpret_cast<int*>(smem + p.off_edges);
     for (int i = tid; i < p.M + 2; i += kWsThreads) e[i] = p.edges[i];
     float2* t = reinterpret_cast<float2*>(smem + p.off_twp);
@@ -106,9 +106,9 @@ __global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastPar
   if (warp == 0) {
     // =========================== service warp ===========================
     auto issue_tma = [&](int it) {  // one thread: raw[stage][j] = x[s0 - 4 + j]
-      const long long tile_id = (long long)blockIdx.x + (long long)it * gridDim.x;
-      const long long clip = tile_id / p.tiles_per_clip;
-      const int t = (int)(tile_id - clip * p.tiles_per_clip);
+      const unsigned tile_id = blockIdx.x + (unsigned)it * gridDim.x;  // launcher: total_tiles < 2^31
+      const unsigned clip = tile_id / (unsigned)p.tiles_per_clip;
+      const int t = (int)(tile_id - clip * (unsigned)p.tiles_per_clip);
       const long long s0 = (long long)t * kFramesPerTile * hop;
       const long long first = s0 >= 4 ? s0 - 4 : 0;
       long long end = s0 + p.tile_len;
@@ -117,7 +117,7 @@ __global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastPar
       const uint32_t bar = bar_full + 8u * (it & 1);
       float* raw = reinterpret_cast<float*>(smem + (size_t)(it & 1) * p.raw_stride);
       mbar_expect_tx(bar, bytes);
-      tma_load_1d(smem_u32(raw + (s0 >= 4 ? 0 : 4)), p.pcm + clip * p.stride + first, bytes, bar);
+      tma_load_1d(smem_u32(raw + (s0 >= 4 ? 0 : 4)), p.pcm + (size_t)clip * p.stride + first, bytes, bar);
     };
     auto issue_mma = [&]() {  // one thread: D[128 x 48] = Ahi*Bhi + Alo*Bhi + Ahi*Blo over Kpad
       tc_fence_after();
@@ -140,9 +140,9 @@ __global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastPar
       if (n_it > 1) issue_tma(1);
     }
     for (int it = 0; it < n_it; ++it) {
-      const long long tile_id = (long long)blockIdx.x + (long long)it * gridDim.x;
-      const long long clip = tile_id / p.tiles_per_clip;
-      const int t = (int)(tile_id - clip * p.tiles_per_clip);
+      const unsigned tile_id = blockIdx.x + (unsigned)it * gridDim.x;  // launcher: total_tiles < 2^31
+      const unsigned clip = tile_id / (unsigned)p.tiles_per_clip;
+      const int t = (int)(tile_id - clip * (unsigned)p.tiles_per_clip);
       if (it + 2 < n_it) {  // refill this stage as soon as every compute warp has converted tile `it`
         mbar_wait(bar_empty + 8u * (it & 1), (it >> 1) & 1);
         if (lane == 0) {
@@ -191,7 +191,6 @@ __global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastPar
     // =========================== compute warps ===========================
     const int cw = warp - 1, half = lane >> 4, l = lane & 15;
     unsigned char* wscratch = smem + p.off_scratch + cw * kWarpScratch;
-    float2* s2 = reinterpret_cast<float2*>(wscratch);               // private interleaved samples
     unsigned char* scratch = wscratch + half * (kWarpScratch / 2);  // this half-warp's transpose area
     float4* s_tr = reinterpret_cast<float4*>(scratch);
     V* s_P = reinterpret_cast<V*>(scratch);
@@ -206,79 +205,68 @@ __global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastPar
     }
     const float pre = p.preemph;
     const int n = (int)p.N;
-    const int conv_len = 2 * hop + LOAD_LEN;  // S2 entries this warp's two frame pairs read
-    const int wbase = 4 * cw * hop;           // tile-local sample index of the warp's first frame
 
     for (int it = 0; it < n_it; ++it) {
-      const long long tile_id = (long long)blockIdx.x + (long long)it * gridDim.x;
-      const long long clip = tile_id / p.tiles_per_clip;
-      const int t = (int)(tile_id - clip * p.tiles_per_clip);
+      const unsigned tile_id = blockIdx.x + (unsigned)it * gridDim.x;  // launcher: total_tiles < 2^31
+      const unsigned clip = tile_id / (unsigned)p.tiles_per_clip;
+      const int t = (int)(tile_id - clip * (unsigned)p.tiles_per_clip);
       const int s0 = t * kFramesPerTile * hop;
-      const float* raw = reinterpret_cast<const float*>(smem + (size_t)(it & 1) * p.raw_stride);
+      float* raw_w = reinterpret_cast<float*>(smem + (size_t)(it & 1) * p.raw_stride);
+      const float* raw = raw_w;
       __syncwarp();  // previous tile: every lane is done with the scratch this conversion overwrites
       mbar_wait(bar_full + 8u * (it & 1), (it >> 1) & 1);
-      // ---- conversion: S2[j] = (y[b+j], y[b+j+hop]), y = pre-emphasised signal, b = wbase ----
-      {
-        const int g0 = s0 + wbase;
-        const bool tail = g0 + conv_len + hop > n;  // samples >= N: the raw stage holds stale data there
-        const float* rb = raw + 4 + wbase;
-        if (!tail) {
-#pragma unroll 4
-          for (int j = lane * 2; j < conv_len; j += 64) {
-            const float* r = rb + j;
-            const float2 va = *reinterpret_cast<const float2*>(r);
-            const float2 vb = *reinterpret_cast<const float2*>(r + hop);
-            float am = r[-1];
-            const float bm = r[hop - 1];
-            if (g0 + j == 0) am = 0.f;  // y[0] = x[0]
-            float4 o;
-            o.x = __fsub_rn(va.x, __fmul_rn(pre, am));    // y[g]
-            o.y = __fsub_rn(vb.x, __fmul_rn(pre, bm));    // y[g+hop]
-            o.z = __fsub_rn(va.y, __fmul_rn(pre, va.x));  // y[g+1]
-            o.w = __fsub_rn(vb.y, __fmul_rn(pre, vb.x));  // y[g+hop+1]
-            *reinterpret_cast<float4*>(s2 + j) = o;
-          }
-        } else {
-          for (int j = lane * 2; j < conv_len; j += 64) {
-            const int g = g0 + j;
-            const float* r = rb + j;
-            const float2 va = *reinterpret_cast<const float2*>(r);
-            const float2 vb = *reinterpret_cast<const float2*>(r + hop);
-            const float am = (g > 0) ? r[-1] : 0.f, bm = r[hop - 1];
-            float4 o;
-            o.x = (g < n) ? __fsub_rn(va.x, __fmul_rn(pre, am)) : 0.f;
-            o.y = (g + hop < n) ? __fsub_rn(vb.x, __fmul_rn(pre, bm)) : 0.f;
-            o.z = (g + 1 < n) ? __fsub_rn(va.y, __fmul_rn(pre, va.x)) : 0.f;
-            o.w = (g + hop + 1 < n) ? __fsub_rn(vb.y, __fmul_rn(pre, vb.x)) : 0.f;
-            *reinterpret_cast<float4*>(s2 + j) = o;
-          }
-        }
+      if (s0 == 0 && cw == 0) {  // y[0] = x[0] - pre * 0: give the clip's first sample a zero predecessor
+        if (lane == 0) raw_w[3] = 0.f;
+        __syncwarp();
       }
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bar_empty + 8u * (it & 1));  // this warp no longer reads the raw stage
 
       const int fa_local = cw * 4 + half * 2;
       const int fA = t * kFramesPerTile + fa_local, fB = fA + 1;
       const bool active = (t * kFramesPerTile + cw * 4) < p.nframes;  // warp-uniform
+      if (!active && lane == 0) mbar_arrive(bar_empty + 8u * (it & 1));
       V lm[ROUNDS];
       V mean = fsplat(0.f), esum = fsplat(0.f);
       if (active) {
-        const float2* pa = s2 + half * 2 * hop;
+        // ---- pass-1 loads straight from the raw stage with pre-emphasis on the fly:
+        //      z[16 m + l] = (y[32m + 2l], y[32m + 2l + 1]),  y[i] = x[i] - pre * x[i-1]  (fp32, the
+        //      product rounded before the subtraction = psf's float32 step); frame A in .x, B in .y
+        const float* qa = raw + 4 + fa_local * hop + 2 * l;
+        const int gA = s0 + fa_local * hop + 2 * l;  // clip sample index of this lane's first sample
         CF x16[16];
+        if (gA - 2 * l + hop + LOAD_LEN <= n) {      // both frames entirely inside the clip (half-warp uniform)
 #pragma unroll
-        for (int m = 0; m < 16; ++m) {
-          const int idx = 32 * m + 2 * l;
-          float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (32 * m + 31 < LOAD_LEN) {
-            v = *reinterpret_cast<const float4*>(pa + idx);
-          } else if (32 * m < LOAD_LEN) {
-            if (idx + 1 < LOAD_LEN) v = *reinterpret_cast<const float4*>(pa + idx);
-            else if (idx < LOAD_LEN) { const float2 u = pa[idx]; v.x = u.x; v.y = u.y; }
+          for (int m = 0; m < 16; ++m) {
+            x16[m].re = fsplat(0.f);
+            x16[m].im = fsplat(0.f);
+            if (32 * m + 31 < LOAD_LEN || (32 * m < LOAD_LEN && 32 * m + 2 * l + 1 < LOAD_LEN)) {
+              const float2 a = *reinterpret_cast<const float2*>(qa + 32 * m);
+              const float2 b = *reinterpret_cast<const float2*>(qa + 32 * m + hop);
+              const float am = qa[32 * m - 1], bm = qa[32 * m + hop - 1];
+              x16[m].re.x = __fsub_rn(a.x, __fmul_rn(pre, am));
+              x16[m].im.x = __fsub_rn(a.y, __fmul_rn(pre, a.x));
+              x16[m].re.y = __fsub_rn(b.x, __fmul_rn(pre, bm));
+              x16[m].im.y = __fsub_rn(b.y, __fmul_rn(pre, b.x));
+            }
           }
-          x16[m].re = make_float2(v.x, v.y);
-          x16[m].im = make_float2(v.z, v.w);
+        } else {  // the clip ends inside these frames: samples >= N are zero AFTER pre-emphasis (psf pads y)
+#pragma unroll
+          for (int m = 0; m < 16; ++m) {
+            x16[m].re = fsplat(0.f);
+            x16[m].im = fsplat(0.f);
+            if (32 * m + 31 < LOAD_LEN || (32 * m < LOAD_LEN && 32 * m + 2 * l + 1 < LOAD_LEN)) {
+              const int g = gA + 32 * m;
+              const float2 a = *reinterpret_cast<const float2*>(qa + 32 * m);
+              const float2 b = *reinterpret_cast<const float2*>(qa + 32 * m + hop);
+              const float am = qa[32 * m - 1], bm = qa[32 * m + hop - 1];
+              x16[m].re.x = (g < n) ? __fsub_rn(a.x, __fmul_rn(pre, am)) : 0.f;
+              x16[m].im.x = (g + 1 < n) ? __fsub_rn(a.y, __fmul_rn(pre, a.x)) : 0.f;
+              x16[m].re.y = (g + hop < n) ? __fsub_rn(b.x, __fmul_rn(pre, bm)) : 0.f;
+              x16[m].im.y = (g + hop + 1 < n) ? __fsub_rn(b.y, __fmul_rn(pre, b.x)) : 0.f;
+            }
+          }
         }
-        __syncwarp();  // S2 lives in the transpose area: all loads before the first transposed store
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_empty + 8u * (it & 1));  // this warp no longer reads the raw stage
         dft16(x16);
 #pragma unroll
         for (int k1 = 0; k1 < 16; ++k1) {
@@ -343,17 +331,31 @@ __global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastPar
         __syncwarp();
 
         // ---- mel bank by segment ----
+        // bin k of segment [e_s, e_{s+1}) feeds filter s with r = (k - e_s)/len (psf's rising edge)
+        // and filter s-1 with 1 - r (psf's falling edge): R = sum r P, F = sum P - R.  Four bins per
+        // step keep several shared-memory loads in flight.
         for (int s = l; s <= p.M; s += 16) {
-          V r = fsplat(0.f), f = fsplat(0.f);
-          const int k1 = s_edges[s + 1];
-          for (int k = s_edges[s]; k < k1; ++k) {
-            const V pw = s_P[k];
-            const float2 w = s_melw[k];
-            r = ffma(pw, fsplat(w.x), r);
-            f = ffma(pw, fsplat(w.y), f);
+          const int k0 = s_edges[s], k1 = s_edges[s + 1];
+          const float inv = s_inv[s];
+          V a0 = fsplat(0.f), a1 = fsplat(0.f), r0 = fsplat(0.f), r1 = fsplat(0.f);
+          float w = 0.f;
+          for (int k = k0; k < k1; k += 4) {
+            const V z = fsplat(0.f);
+            const V p0 = s_P[k];
+            const V p1 = (k + 1 < k1) ? s_P[k + 1] : z;
+            const V p2 = (k + 2 < k1) ? s_P[k + 2] : z;
+            const V p3 = (k + 3 < k1) ? s_P[k + 3] : z;
+            a0 = fadd(a0, fadd(p0, p1));
+            a1 = fadd(a1, fadd(p2, p3));
+            r0 = ffma(p0, fsplat(w * inv), r0);
+            r1 = ffma(p1, fsplat((w + 1.f) * inv), r1);
+            r0 = ffma(p2, fsplat((w + 2.f) * inv), r0);
+            r1 = ffma(p3, fsplat((w + 3.f) * inv), r1);
+            w += 4.f;
           }
+          const V a = fadd(a0, a1), r = fadd(r0, r1);
           s_R[s] = r;
-          s_F[s] = f;
+          s_F[s] = fsub(a, r);
         }
         __syncwarp();
         V msum = fsplat(0.f);
@@ -439,7 +441,7 @@ int launch_mfcc_fast(kws_handle_t h, const float* pcm_dev, int64_t B, int64_t N,
   // TMA bulk copies need 16-byte aligned sources and sizes; the interleaved tile needs an even hop
   if ((hop & 3) != 0 || (N & 3) != 0 || (pcm_stride & 3) != 0 || (reinterpret_cast<size_t>(pcm_dev) & 15) != 0)
     return 0;
-  if ((size_t)(2 * hop + 400) * 8 > (size_t)kWarpScratch || N >= (1ll << 30)) return 0;
+  if (N >= (1ll << 30)) return 0;
   constexpr int ROUNDS = 3;
   FastParams p{};
   p.pcm = pcm_dev;
@@ -450,6 +452,7 @@ int launch_mfcc_fast(kws_handle_t h, const float* pcm_dev, int64_t B, int64_t N,
   p.nframes = (int)kws_num_frames(N, t.cfg.frame_len, t.cfg.frame_step);
   p.tiles_per_clip = (p.nframes + kFramesPerTile - 1) / kFramesPerTile;
   p.total_tiles = (long long)B * p.tiles_per_clip;
+  if (p.total_tiles >= (1ll << 31) - 4096) return 0;
   p.hop = hop;
   p.M = M;
   p.ncep = t.ncep;

@@ -110,7 +110,7 @@ def test_int16_ingest(proc):
     _close(got, psf_mfcc.extract_features_batch(as_float), "int16")
     # int16 ingest runs the generic kernel, float32 input the fast one: same features within fp32 noise
     torch.testing.assert_close(proc.extract_features(i16.cuda()),
-                               proc.extract_features(torch.from_numpy(as_float).cuda()), rtol=1e-4, atol=2e-5)
+                               proc.extract_features(torch.from_numpy(as_float).cuda()), rtol=1e-3, atol=1e-4)
 
 
 def test_strided_rows_and_host_path(proc):
