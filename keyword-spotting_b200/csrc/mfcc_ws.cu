@@ -144,7 +144,7 @@ __global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastPar
       const unsigned clip = tile_id / (unsigned)p.tiles_per_clip;
       const int t = (int)(tile_id - clip * (unsigned)p.tiles_per_clip);
       if (it + 2 < n_it) {  // refill this stage as soon as every compute warp has converted tile `it`
-        mbar_wait(bar_empty + 8u * (it & 1), (it >> 1) & 1);
+        mbar_wait_idle(bar_empty + 8u * (it & 1), (it >> 1) & 1);
         if (lane == 0) {
           fence_proxy_async();
           issue_tma(it + 2);
@@ -152,7 +152,7 @@ __global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastPar
         __syncwarp();
       }
       if (do_dct) {
-        mbar_wait(bar_afull, it & 1);
+        mbar_wait_idle(bar_afull, it & 1);
         if (lane == 0) issue_mma();
         __syncwarp();
         mbar_wait(bar_mma, it & 1);
