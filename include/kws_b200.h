@@ -125,6 +125,9 @@ int kws_model_create(kws_handle_t h, int num_classes, int channels, int num_bloc
 int kws_model_load_tensor(kws_handle_t h, const char* name, const float* data_host,
                           const int64_t* shape, int ndim);
 int kws_model_finalize(kws_handle_t h);
+/* kernel selection: 0 = auto (the fused tcgen05 kernel for the reference shape: 64 channels, 4 blocks,
+ * F in {40, 10}; layered kernels otherwise), 1 = always the layered kernels (cross-check path) */
+int kws_model_set_path(kws_handle_t h, int path);
 /* feats_dev [B,1,T,F] float32 contiguous -> logits_dev [B,num_classes] */
 int kws_model_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t T, int64_t F,
                       float* logits_dev, void* stream);

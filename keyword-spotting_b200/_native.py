@@ -67,6 +67,7 @@ SIGNATURES = {
     "kws_model_create": (_i32, [_vp, _i32, _i32, _i32]),
     "kws_model_load_tensor": (_i32, [_vp, C.c_char_p, _vp, C.POINTER(_i64), _i32]),
     "kws_model_finalize": (_i32, [_vp]),
+    "kws_model_set_path": (_i32, [_vp, _i32]),
     "kws_model_forward": (_i32, [_vp, _vp, _i64, _i64, _i64, _vp, _vp]),
     "kws_model_workspace_bytes": (_i64, [_vp, _i64, _i64, _i64]),
     "kws_pcm_to_logits": (_i32, [_vp, _vp, _i64, _i64, _i64, _vp, _vp]),

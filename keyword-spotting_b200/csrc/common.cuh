@@ -71,6 +71,12 @@ struct ModelWeights {
   float* d_pw_beff = nullptr;   // [nb][C]   pointwise bias with the depthwise bias folded through
   float* d_fc_w = nullptr;      // [C][num_classes]
   float* d_fc_b = nullptr;      // [num_classes]
+  // fused kernel images (model_fused.cu), built when channels == 64 and num_blocks == 4
+  float* d_fused_a = nullptr;       // tf32 A-operand images: conv1, then the four pointwise layers
+  float* d_fused_dw = nullptr;      // [4][9][64]
+  float* d_fused_actb = nullptr;    // [5][64]
+  float* d_fused_border = nullptr;  // [5][64]
+  int path = 0;                     // 0 = auto (fused when applicable), 1 = force the layered kernels
   // workspace
   void* d_ws = nullptr;
   size_t ws_bytes = 0;
@@ -102,6 +108,12 @@ int launch_mfcc(kws_handle_t h, const void* pcm_dev, bool is_i16, int64_t B, int
 // mfcc_fast.cu: 1 = handled, 0 = configuration needs the generic kernel, <0 = error
 int launch_mfcc_fast(kws_handle_t h, const float* pcm_dev, int64_t B, int64_t N, int64_t pcm_stride,
                      float* out_dev, int mode, cudaStream_t stream);
+// model_fused.cu: 1 = handled, 0 = configuration outside the fused kernel, <0 = error
+int launch_dscnn_fused(kws_handle_t h, const float* feats_dev, int64_t B, int64_t T, int64_t F, float* logits_dev,
+                       cudaStream_t stream);
+int build_fused_model(ModelWeights& m, const std::vector<float>& conv1_w, const std::vector<float>& conv1_b,
+                      const std::vector<const float*>& dw_w, const std::vector<const float*>& dw_b,
+                      const std::vector<const float*>& pw_w, const std::vector<const float*>& pw_b);
 // tables.cu
 int build_feature_tables(kws_handle_t h, const kws_feature_config* cfg);
 void free_feature_tables(FeatureTables& t);

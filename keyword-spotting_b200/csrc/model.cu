@@ -160,7 +160,7 @@ static int slot_of(const ModelWeights& m, const std::string& name) {
 
 static void model_free(ModelWeights& m) {
   void* ptrs[] = {m.d_conv1_w, m.d_conv1_b, m.d_dw_w, m.d_dw_b, m.d_pw_w, m.d_pw_b, m.d_pw_beff,
-                  m.d_fc_w,    m.d_fc_b,    m.d_ws};
+                  m.d_fc_w,    m.d_fc_b,    m.d_ws,     m.d_fused_a, m.d_fused_dw, m.d_fused_actb, m.d_fused_border};
   for (void* p : ptrs)
     if (p) cudaFree(p);
   m = ModelWeights();
@@ -283,7 +283,26 @@ int kws_model_finalize(kws_handle_t h) {
     if ((rc = up(&m.d_fc_w, p))) return rc;
     if ((rc = up(&m.d_fc_b, m.host[slot_of(m, "fc.bias")]))) return rc;
   }
+  if (C == 64 && nb == 4) {  // parameter images of the fused tensor-core kernel (model_fused.cu)
+    std::vector<const float*> a, ab, b, bb;
+    for (int i = 0; i < nb; ++i) {
+      const std::string pre = "dsconv" + std::to_string(i + 1);
+      a.push_back(m.host[slot_of(m, pre + ".depthwise.weight")].data());
+      ab.push_back(m.host[slot_of(m, pre + ".depthwise.bias")].data());
+      b.push_back(m.host[slot_of(m, pre + ".pointwise.weight")].data());
+      bb.push_back(m.host[slot_of(m, pre + ".pointwise.bias")].data());
+    }
+    if ((rc = build_fused_model(m, m.host[slot_of(m, "conv1.weight")], m.host[slot_of(m, "conv1.bias")], a, ab, b, bb)))
+      return rc;
+  }
   m.finalized = true;
+  return KWS_OK;
+}
+
+int kws_model_set_path(kws_handle_t h, int path) {
+  if (!h || !h->model.created) return fail(KWS_ERR_STATE, "model not created");
+  if (path != 0 && path != 1) return fail(KWS_ERR_INVALID, "path must be 0 (auto) or 1 (layered)");
+  h->model.path = path;
   return KWS_OK;
 }
 
@@ -310,6 +329,10 @@ int kws_model_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t
   int H1, W1, Hl, Wl;
   conv_out_hw((int)T, (int)F, nb, &H1, &W1, &Hl, &Wl);
   if (H1 < 1 || W1 < 1) return fail(KWS_ERR_INVALID, "input %lldx%lld too small for conv1 (10x10, stride 2, pad 2)", (long long)T, (long long)F);
+  if (m.path == 0) {  // fused tensor-core kernel when the configuration is the reference network
+    const int rc = launch_dscnn_fused(h, feats_dev, B, T, F, logits_dev, st);
+    if (rc != 0) return rc < 0 ? rc : KWS_OK;
+  }
   const int64_t need = kws_model_workspace_bytes(h, B, T, F);
   if ((size_t)need > m.ws_bytes) {
     if (m.d_ws) KWS_CUDA(cudaFree(m.d_ws));

@@ -1,0 +1,394 @@
+// Fused forward of the reference KWS network (kws/libs/models.py:122-183) for channels = 64,
+// four blocks: features [B, T, F] -> logits [B, num_classes] in ONE kernel, every activation
+// on-chip (tensor memory + registers + shared memory), HBM sees only the features and the logits.
+//
+// Formulation.  Every GEMM-able layer (conv1 10x10 s2 p2 as an im2col GEMM with K = 100, the
+// four pointwise 1x1 convs with K = 64) is computed TRANSPOSED on the tensor core:
+//     D[c_out, pixel] = W[c_out, k] . X[pixel, k]^T      tcgen05.mma kind::tf32, M = 64, N = one
+// output row of pixels (padded to 24, or 16 for F = 10), accumulator in TMEM.  With M = 64 the
+// accumulator row c_out lives in TMEM lane 32*(c/16) + c%16 and a second, independent M = 64 tile
+// sits at lane offset 16 (tools/umma_probe.cu pins both facts on the device), so a CTA works on a
+// PAIR of clips ("slots") and thread (warp quarter q, lane) of every warp owns
+//     slot = lane / 16,  channel = 16 q + lane % 16
+// -- the depthwise 3x3 is per channel, so the thread that reads a channel's accumulator row from
+// TMEM (tcgen05.ld 32x32b: one lane per thread) applies bias + ReLU and runs the 3x3 stencil on
+// rows it holds in registers, with no inter-thread exchange at all, then stores the depthwise
+// result as the K-major B operand of the next pointwise GEMM (one 4-byte store per pixel, the
+// 144-byte K-chunk pitch puts the 16 channels of a quarter on 16 different banks).
+//
+// Schedule.  The network is streamed row by row through all layers (a skewed wavefront): in
+// step t the CTA prepares and issues
+//     conv1 row t | depthwise+pointwise of block l on row t-(l+1), l = 1..4 | pooling of row t-6
+// which are mutually independent, so one step = one compute phase (16 warps: warp/4 = the block
+// whose depthwise it runs, warp%4 = lane quarter; all warps share the conv1 im2col), one barrier,
+// ten MMA groups (5 layers x 2 slots, issued by ten different elected lanes), one mbarrier wait.
+// TMEM holds, per layer, a ring of the last four raw accumulator rows (4 x 24 columns), i.e. the
+// rows the next block's 3x3 stencil still needs; the last layer's row is pooled as soon as it
+// retires.  The pointwise padding=1 quirk (models.py:104-106: each block grows H and W by 2 and
+// the new border pixels are ReLU(bias)) is handled in registers: border rows/columns are a
+// per-channel constant.  The depthwise bias is folded through the pointwise weights on the host.
+//
+// Precision: tf32 operands (cvt.rna), fp32 accumulate; logits agree with the fp32 reference to
+// ~3e-6 absolute / 2e-4 relative (tests/test_gpu_model.py; north_star tolerance 1e-3).
+#include <cstring>
+#include <vector>
+
+#include "mfcc_dev.cuh"
+
+namespace kws {
+
+constexpr int kFC = 64;                      // channels of the reference network
+constexpr int kFThreads = 512;
+constexpr int kLboB = 144;                   // K-chunk pitch of the B tiles (bank spreading)
+constexpr int kKC1 = 104;                    // conv1 K (100 taps) padded to a multiple of 8
+constexpr int kSboA1 = (kKC1 / 4) * 128;     // 8-row group pitch: conv1 weights
+constexpr int kSboAp = (kFC / 4) * 128;      //                    pointwise weights
+constexpr int kSboB1 = (kKC1 / 4) * kLboB;   //                    conv1 im2col tile
+constexpr int kSboBp = (kFC / 4) * kLboB;    //                    depthwise-output tile
+constexpr int kAImgBytes = 8 * kSboA1 + 4 * 8 * kSboAp;
+
+struct FusedParams {
+  const float* feats;     // [B, T, F]
+  float* logits;          // [B, ncls]
+  long long B;
+  int T, H0, ncls;
+  const float* a_img;     // tf32 A-operand images: conv1 then 4 pointwise, K-major no-swizzle
+  const float* dw_w;      // [4][9][64]
+  const float* act_bias;  // [5][64] conv1 bias, then pointwise bias with the depthwise bias folded through
+  const float* border;    // [5][64] row 0 unused; ReLU(pointwise bias) of block l
+  const float* fc_w;      // [64][ncls]
+  const float* fc_b;      // [ncls]
+};
+
+template <int N>
+__device__ __forceinline__ void tc_ld_row(uint32_t taddr, float (&v)[N]);
+template <>
+__device__ __forceinline__ void tc_ld_row<16>(uint32_t taddr, float (&v)[16]) {
+  tc_ld16(taddr, v);
+}
+template <>
+__device__ __forceinline__ void tc_ld_row<24>(uint32_t taddr, float (&v)[24]) {
+  uint32_t r[24];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23])
+               : "r"(taddr + 16)
+               : "memory");
+#pragma unroll
+  for (int i = 0; i < 24; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// Depthwise 3x3 (zero padding 1) of output row r of one block for this thread's (slot, channel).
+// Input layer rows come from the TMEM ring of raw accumulator rows of the producing GEMM:
+//   BORDER = false (block 1 reads conv1's output): layer row i = raw row i, value ReLU(raw + bias);
+//   BORDER = true  (blocks 2..4 read a padded-pointwise output): layer has HIN + 2 rows and
+//                  WIN + 2 columns, its outermost ring is the constant `bval`, the interior row i
+//                  is raw row i - 1 shifted right by one column.
+// The result (WL pixels) is written tf32-rounded into column `c` of the K-major B tile `bt`.
+template <int WIN, bool BORDER, int NPIX>
+__device__ __forceinline__ void dw_row(uint32_t ring, int r, int HIN, float bias, float bval, const float (&w)[9],
+                                       unsigned char* bt, int c) {
+  constexpr int WL = BORDER ? WIN + 2 : WIN;
+  constexpr int OFF = BORDER ? 2 : 1;  // a[.][OFF + x] = raw column x; a[.][0] and a[.][WL + 1] are the zero padding
+  const int HL = BORDER ? HIN + 2 : HIN;
+  float a[3][WL + 2];
+#pragma unroll
+  for (int dr = 0; dr < 3; ++dr) {
+    const int i = r + dr - 1;
+    if (i < 0 || i >= HL) {
+#pragma unroll
+      for (int j = 0; j < WL + 2; ++j) a[dr][j] = 0.f;
+    } else if (BORDER && (i == 0 || i == HL - 1)) {
+      a[dr][0] = 0.f;
+      a[dr][WL + 1] = 0.f;
+#pragma unroll
+      for (int j = 1; j <= WL; ++j) a[dr][j] = bval;
+    } else {
+      const int rho = BORDER ? i - 1 : i;
+      float raw[NPIX];
+      tc_ld_row<NPIX>(ring + (uint32_t)((rho & 3) * NPIX), raw);
+      tc_wait_ld();
+      a[dr][0] = 0.f;
+      a[dr][WL + 1] = 0.f;
+      if (BORDER) {
+        a[dr][1] = bval;
+        a[dr][WL] = bval;
+      }
+#pragma unroll
+      for (int x = 0; x < WIN; ++x) a[dr][OFF + x] = fmaxf(raw[x] + bias, 0.f);
+    }
+  }
+  unsigned char* dst = bt + (c >> 2) * kLboB + (c & 3) * 4;
+#pragma unroll
+  for (int x = 0; x < WL; ++x) {
+    float o = 0.f;
+#pragma unroll
+    for (int dr = 0; dr < 3; ++dr)
+#pragma unroll
+      for (int dx = 0; dx < 3; ++dx) o = fmaf(w[dr * 3 + dx], a[dr][x + dx], o);
+    *reinterpret_cast<float*>(dst + (x >> 3) * kSboBp + (x & 7) * 16) = to_tf32(o);
+  }
+}
+
+template <int NPIX>
+struct FusedLayout {
+  static constexpr int b1_tile = (NPIX / 8) * kSboB1, b1_stride = b1_tile + 64;
+  static constexpr int bp_tile = (NPIX / 8) * kSboBp, bp_stride = bp_tile + 64;
+  static constexpr int off_a1 = 0;
+  static constexpr int off_ap = 8 * kSboA1;
+  static constexpr int off_b1 = kAImgBytes;
+  static constexpr int off_bp = off_b1 + 2 * b1_stride;
+  static constexpr int off_pool = off_bp + 8 * bp_stride;
+  static constexpr int off_feat = off_pool + 2 * kFC * 4;
+};
+
+template <int F, int NPIX>
+__global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedParams p) {
+  constexpr int W0 = (F - 6) / 2 + 1;
+  static_assert(W0 + 6 <= NPIX && NPIX % 8 == 0, "row of the widest layer must fit the MMA N");
+  using L = FusedLayout<NPIX>;
+  extern __shared__ __align__(128) unsigned char smem[];
+  __shared__ __align__(8) unsigned long long s_bar;
+  __shared__ uint32_t s_tmem;
+  float* s_feat = reinterpret_cast<float*>(smem + L::off_feat);  // [2][T * F]
+  float* s_pool = reinterpret_cast<float*>(smem + L::off_pool);  // [2][64]
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int g = warp >> 2, q = warp & 3, sl = lane >> 4, c = q * 16 + (lane & 15);
+  const uint32_t bar = smem_u32(&s_bar);
+  const int T = p.T, H0 = p.H0, TF = T * F;
+
+  if (tid == 0) {
+    mbar_init(bar, 10);
+    fence_mbar_init();
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "n"(512));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  {
+    const uint4* src = reinterpret_cast<const uint4*>(p.a_img);
+    uint4* dst = reinterpret_cast<uint4*>(smem);
+    for (int i = tid; i < kAImgBytes / 16; i += kFThreads) dst[i] = src[i];
+    uint4* z = reinterpret_cast<uint4*>(smem + L::off_b1);
+    for (int i = tid; i < (L::off_pool - L::off_b1) / 16; i += kFThreads) z[i] = make_uint4(0, 0, 0, 0);
+  }
+  float w[9];
+#pragma unroll
+  for (int i = 0; i < 9; ++i) w[i] = p.dw_w[(g * 9 + i) * kFC + c];
+  const float in_bias = p.act_bias[g * kFC + c], in_border = p.border[g * kFC + c];
+  const float pool_bias = p.act_bias[4 * kFC + c], pool_border = p.border[4 * kFC + c];
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = s_tmem;
+  const uint32_t my_tmem = tmem + ((uint32_t)(q * 32) << 16);      // this warp's lane quarter
+  const uint32_t my_ring = my_tmem + (uint32_t)(g * 4 * NPIX);     // input ring of the block this warp runs
+  const uint32_t my_acc4 = my_tmem + (uint32_t)(16 * NPIX);
+  unsigned char* my_bt = smem + L::off_bp + (g * 2 + sl) * L::bp_stride;
+  constexpr uint32_t kIdescF = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(NPIX >> 3) << 17) | ((64u >> 4) << 24);
+
+  const int nsteps = H0 + 12;
+  const int H3 = H0 + 6, W3 = W0 + 6;
+  const float nborder = (float)((H3 + 2) * (W3 + 2) - H3 * W3);
+  const float inv_area = 1.0f / (float)((H3 + 2) * (W3 + 2));
+  const long long npairs = (p.B + 1) / 2;
+  uint32_t phase = 0;
+
+  for (long long pair = blockIdx.x; pair < npairs; pair += gridDim.x) {
+    // ---- features of the two clips -> shared memory ----
+    {
+      const long long nvalid = (2 * pair + 1 < p.B) ? 2LL * TF : (long long)TF;
+      const float* src = p.feats + 2 * pair * TF;
+      for (int i = tid; i < 2 * TF; i += kFThreads) s_feat[i] = (i < nvalid) ? __ldg(src + i) : 0.f;
+    }
+    float psum = 0.f;
+    __syncthreads();
+
+    for (int t = 0; t < nsteps; ++t) {
+      // ================= compute phase =================
+      if (t < H0) {  // im2col of conv1 output row t: one 16-byte K-chunk (4 taps) per item
+        for (int idx = tid; idx < 2 * W0 * 25; idx += kFThreads) {
+          const int s = idx / (W0 * 25), rem = idx - s * (W0 * 25);
+          const int x = rem / 25, kc = rem - x * 25;
+          const float* fsrc = s_feat + s * TF;
+          float v[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int k = 4 * kc + e, ki = k / 10, kj = k - 10 * ki;
+            const int fr = 2 * t - 2 + ki, fcol = 2 * x - 2 + kj;
+            const bool ok = fr >= 0 && fr < T && fcol >= 0 && fcol < F;
+            v[e] = ok ? to_tf32(fsrc[fr * F + fcol]) : 0.f;
+          }
+          *reinterpret_cast<float4*>(smem + L::off_b1 + s * L::b1_stride + (x >> 3) * kSboB1 + kc * kLboB + (x & 7) * 16) =
+              make_float4(v[0], v[1], v[2], v[3]);
+        }
+      }
+      {  // depthwise of block g+1 on row t-(g+2)
+        const int r = t - (g + 2);
+        if (r >= 0 && r < H0 + 2 * g) {
+          if (g == 0) dw_row<W0, false, NPIX>(my_ring, r, H0, in_bias, 0.f, w, my_bt, c);
+          else if (g == 1) dw_row<W0, true, NPIX>(my_ring, r, H0, in_bias, in_border, w, my_bt, c);
+          else if (g == 2) dw_row<W0 + 2, true, NPIX>(my_ring, r, H0 + 2, in_bias, in_border, w, my_bt, c);
+          else dw_row<W0 + 4, true, NPIX>(my_ring, r, H0 + 4, in_bias, in_border, w, my_bt, c);
+        }
+      }
+      if (g == 0) {  // pooling of the last block's row t-6 (interior pixels; the border is added at the end)
+        const int r = t - 6;
+        if (r >= 0 && r < H3) {
+          float raw[NPIX];
+          tc_ld_row<NPIX>(my_acc4, raw);
+          tc_wait_ld();
+#pragma unroll
+          for (int x = 0; x < W3; ++x) psum += fmaxf(raw[x] + pool_bias, 0.f);
+        }
+      }
+      fence_proxy_async();
+      tc_fence_before();
+      __syncthreads();
+      // ================= MMA phase: stage s = warp/2 (0 = conv1, 1..4 = pointwise), slot = warp%2 =================
+      if (warp < 10 && lane == 0) {
+        const int s = warp >> 1, ms = warp & 1;
+        const int r = (s == 0) ? t : t - (s + 1);
+        const int nrows = (s == 0) ? H0 : H0 + 2 * (s - 1);
+        if (r >= 0 && r < nrows) {
+          tc_fence_after();
+          const uint32_t d = tmem + ((uint32_t)(ms * 16) << 16) + (uint32_t)(s < 4 ? (s * 4 + (r & 3)) * NPIX : 16 * NPIX);
+          if (s == 0) {
+            const uint32_t ab = smem_u32(smem + L::off_a1), bb = smem_u32(smem + L::off_b1 + ms * L::b1_stride);
+#pragma unroll 1
+            for (int ks = 0; ks < kKC1 / 8; ++ks)
+              tc_mma_tf32(d, umma_desc(ab + ks * 256u, 128u, kSboA1), umma_desc(bb + ks * 2u * kLboB, kLboB, kSboB1), kIdescF,
+                          ks > 0);
+          } else {
+            const uint32_t ab = smem_u32(smem + L::off_ap + (s - 1) * 8 * kSboAp);
+            const uint32_t bb = smem_u32(smem + L::off_bp + ((s - 1) * 2 + ms) * L::bp_stride);
+#pragma unroll 1
+            for (int ks = 0; ks < kFC / 8; ++ks)
+              tc_mma_tf32(d, umma_desc(ab + ks * 256u, 128u, kSboAp), umma_desc(bb + ks * 2u * kLboB, kLboB, kSboBp), kIdescF,
+                          ks > 0);
+          }
+          tc_commit(bar);
+        } else {
+          asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+        }
+      }
+      mbar_wait(bar, phase & 1);
+      ++phase;
+      tc_fence_after();
+    }
+
+    // ---- global average pool (interior sum + border constant) and fc ----
+    if (g == 0) s_pool[sl * kFC + c] = (psum + nborder * pool_border) * inv_area;
+    __syncthreads();
+    for (int i = tid; i < 2 * p.ncls; i += kFThreads) {
+      const int s = i / p.ncls, k = i - s * p.ncls;
+      const long long b = 2 * pair + s;
+      if (b < p.B) {
+        float acc = p.fc_b[k];
+        for (int ch = 0; ch < kFC; ++ch) acc = fmaf(s_pool[s * kFC + ch], p.fc_w[ch * p.ncls + k], acc);
+        p.logits[b * p.ncls + k] = acc;
+      }
+    }
+    // the next pair's feature load overwrites s_feat / s_pool only after this barrier
+    __syncthreads();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(512));
+}
+
+// ---- host side ------------------------------------------------------------------------------
+static float host_tf32(float x) {  // cvt.rna.tf32.f32: round to nearest, ties away, 10 mantissa bits
+  uint32_t u;
+  memcpy(&u, &x, 4);
+  if ((u & 0x7f800000u) != 0x7f800000u) u = (u + 0x1000u) & ~0x1fffu;
+  memcpy(&x, &u, 4);
+  return x;
+}
+
+// Pack the fused kernel's parameter images from the staged state_dict tensors (torch layout).
+int build_fused_model(ModelWeights& m, const std::vector<float>& conv1_w, const std::vector<float>& conv1_b,
+                      const std::vector<const float*>& dw_w, const std::vector<const float*>& dw_b,
+                      const std::vector<const float*>& pw_w, const std::vector<const float*>& pw_b) {
+  std::vector<float> img(kAImgBytes / 4, 0.f);
+  auto put = [&](size_t base, int sbo, int mrow, int k, float v) {
+    img[(base + (size_t)(mrow >> 3) * sbo + (size_t)(k >> 2) * 128 + (mrow & 7) * 16 + (k & 3) * 4) / 4] = host_tf32(v);
+  };
+  for (int co = 0; co < kFC; ++co)
+    for (int k = 0; k < 100; ++k) put(0, kSboA1, co, k, conv1_w[(size_t)co * 100 + k]);
+  std::vector<float> dww(4 * 9 * kFC), actb(5 * kFC), border(5 * kFC, 0.f);
+  for (int co = 0; co < kFC; ++co) actb[co] = conv1_b[co];
+  for (int l = 0; l < 4; ++l) {
+    const size_t base = (size_t)8 * kSboA1 + (size_t)l * 8 * kSboAp;
+    for (int co = 0; co < kFC; ++co) {
+      double be = pw_b[l][co];
+      for (int ci = 0; ci < kFC; ++ci) {
+        put(base, kSboAp, co, ci, pw_w[l][(size_t)co * kFC + ci]);
+        be += (double)pw_w[l][(size_t)co * kFC + ci] * (double)dw_b[l][ci];
+      }
+      actb[(l + 1) * kFC + co] = (float)be;
+      border[(l + 1) * kFC + co] = pw_b[l][co] > 0.f ? pw_b[l][co] : 0.f;
+      for (int tap = 0; tap < 9; ++tap) dww[((size_t)l * 9 + tap) * kFC + co] = dw_w[l][(size_t)co * 9 + tap];
+    }
+  }
+  auto up = [&](float** dst, const std::vector<float>& v) -> int {
+    if (*dst) cudaFree(*dst);
+    *dst = nullptr;
+    KWS_CUDA(cudaMalloc((void**)dst, v.size() * 4));
+    KWS_CUDA(cudaMemcpy(*dst, v.data(), v.size() * 4, cudaMemcpyHostToDevice));
+    return KWS_OK;
+  };
+  int rc;
+  if ((rc = up(&m.d_fused_a, img))) return rc;
+  if ((rc = up(&m.d_fused_dw, dww))) return rc;
+  if ((rc = up(&m.d_fused_actb, actb))) return rc;
+  if ((rc = up(&m.d_fused_border, border))) return rc;
+  return KWS_OK;
+}
+
+template <int F, int NPIX>
+static int launch_fused_t(kws_handle_t h, const FusedParams& p, cudaStream_t stream) {
+  using L = FusedLayout<NPIX>;
+  const size_t smem_bytes = (size_t)L::off_feat + (size_t)2 * p.T * F * 4;
+  if (smem_bytes > 227 * 1024) return 0;
+  auto kern = dscnn_fused_kernel<F, NPIX>;
+  KWS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+  const long long npairs = (p.B + 1) / 2;
+  long long grid = h->sm_count;
+  if (grid > npairs) grid = npairs;
+  kern<<<(unsigned)grid, kFThreads, smem_bytes, stream>>>(p);
+  KWS_CHECK_LAUNCH(h);
+  return 1;
+}
+
+// 1 = handled, 0 = shape/configuration outside the fused kernel (caller uses the layered path), < 0 = error
+int launch_dscnn_fused(kws_handle_t h, const float* feats_dev, int64_t B, int64_t T, int64_t F, float* logits_dev,
+                       cudaStream_t stream) {
+  const ModelWeights& m = h->model;
+  if (m.channels != kFC || m.num_blocks != 4 || m.d_fused_a == nullptr) return 0;
+  if (T < 6 || T > 4096 || (F != 40 && F != 10)) return 0;
+  FusedParams p{};
+  p.feats = feats_dev;
+  p.logits = logits_dev;
+  p.B = B;
+  p.T = (int)T;
+  p.H0 = (int)((T + 4 - 10) / 2 + 1);
+  p.ncls = m.num_classes;
+  p.a_img = m.d_fused_a;
+  p.dw_w = m.d_fused_dw;
+  p.act_bias = m.d_fused_actb;
+  p.border = m.d_fused_border;
+  p.fc_w = m.d_fc_w;
+  p.fc_b = m.d_fc_b;
+  if (F == 40) return launch_fused_t<40, 24>(h, p, stream);
+  return launch_fused_t<10, 16>(h, p, stream);
+}
+
+}  // namespace kws

@@ -103,6 +103,7 @@ class DepthwiseSeparableConv(KeywordSpottingModel):
         self._initialize_weights()
         self._native = None          # (_native.Handle, device index)
         self._packed_version = None
+        self._kernel_path = 0        # 0 = auto (fused tcgen05 kernel when applicable), 1 = layered kernels
 
     def _initialize_weights(self):
         """Reference initialiser (models.py:149-158)."""
@@ -136,7 +137,15 @@ class DepthwiseSeparableConv(KeywordSpottingModel):
                                                         shape, a.dim()), ModelError)
             _native.check(lib.kws_model_finalize(h.ptr), ModelError)
             self._packed_version = ver
+        _native.check(lib.kws_model_set_path(self._native[0].ptr, self._kernel_path), ModelError)
         return self._native[0]
+
+    def set_kernel_path(self, path: str) -> None:
+        """``"auto"``: the fused tensor-core kernel for the reference shape, layered kernels
+        otherwise; ``"layered"``: always the layer-by-layer fp32 kernels (cross-check path)."""
+        if path not in ("auto", "layered"):
+            raise ModelError(f"unknown kernel path {path!r}")
+        self._kernel_path = 0 if path == "auto" else 1
 
     def native_handle(self, device: Optional[torch.device] = None) -> "_native.Handle":
         dev = torch.device(device) if device is not None else self.conv1.weight.device

@@ -52,6 +52,23 @@ def test_against_oracle_seeded(T, F, B):
     assert (got.argmax(1)[safe] == want.argmax(1)[safe]).all()
 
 
+@pytest.mark.parametrize("T,F,B", [(99, 40, 64), (99, 40, 1), (99, 10, 7), (31, 40, 4), (7, 10, 3), (120, 40, 5)])
+def test_fused_equals_layered(T, F, B):
+    """The fused tcgen05 kernel (tf32 operands) against the layered fp32 kernels and the float64
+    oracle: odd batch sizes exercise the half-empty clip pair, short/long T the row pipeline."""
+    sd = dscnn_ref.init_state_dict(seed=T + F + B)
+    m = DepthwiseSeparableConv()
+    m.load_state_dict(sd)
+    m = m.cuda()
+    x = torch.randn(B, 1, T, F, generator=torch.Generator().manual_seed(B + 1)) * 5.0
+    fused = m(x.cuda()).cpu().numpy()
+    m.set_kernel_path("layered")
+    layered = m(x.cuda()).cpu().numpy()
+    want = dscnn_ref.forward({k: v.double() for k, v in sd.items()}, x.double()).numpy()
+    np.testing.assert_allclose(layered, want, rtol=0, atol=2e-5)
+    np.testing.assert_allclose(fused, want, rtol=1e-3, atol=1e-4)
+
+
 def test_extension_channels_blocks():
     """'DS-CNN-L'-style generalisation (SURVEY a-X1): only channels/num_blocks change."""
     sd = dscnn_ref.init_state_dict(channels=96, num_blocks=5, seed=4)
