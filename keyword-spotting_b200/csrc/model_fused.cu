@@ -83,60 +83,61 @@ __device__ __forceinline__ void tc_ld_row<24>(uint32_t taddr, float (&v)[24]) {
   for (int i = 0; i < 24; ++i) v[i] = __uint_as_float(r[i]);
 }
 
-// Depthwise 3x3 (zero padding 1) of output row r of one block for this thread's (slot, channel).
-// Input layer rows come from the TMEM ring of raw accumulator rows of the producing GEMM:
+// One step of the depthwise 3x3 (zero padding 1) of a block for this thread's (slot, channel):
+// consume INPUT row i of the block's input layer and finish OUTPUT row i - 1.
+// The stencil is accumulated per input row: with v = the activated input row,
+//     out[x]  = P[x] + sum_dx w[2][dx] v[x+dx]     (output row i-1 complete -> B tile of the pointwise GEMM)
+//     P'[x]   = R[x] + sum_dx w[1][dx] v[x+dx]     (output row i, two of three rows in)
+//     R'[x]   =        sum_dx w[0][dx] v[x+dx]     (output row i+1, one row in)
+// so every input row is read from TMEM and activated exactly once and nothing is ever moved.
+// The input row is the raw accumulator row of the producing GEMM in the TMEM ring:
 //   BORDER = false (block 1 reads conv1's output): layer row i = raw row i, value ReLU(raw + bias);
-//   BORDER = true  (blocks 2..4 read a padded-pointwise output): layer has HIN + 2 rows and
-//                  WIN + 2 columns, its outermost ring is the constant `bval`, the interior row i
-//                  is raw row i - 1 shifted right by one column.
-// The result (WL pixels) is written tf32-rounded into column `c` of the K-major B tile `bt`.
-template <int WIN, bool BORDER, int NPIX>
-__device__ __forceinline__ void dw_row(uint32_t ring, int r, int HIN, float bias, float bval, const float (&w)[9],
-                                       unsigned char* bt, int c) {
+//   BORDER = true  (blocks 2..4 read a padded-pointwise output): the layer has HIN + 2 rows and
+//                  WIN + 2 columns, its outermost ring is the constant `bval`, interior row i is raw
+//                  row i - 1 shifted right by one column.
+// Row classes are CTA-uniform and folded into scalars (v = max(raw * m + be, 0)): interior m = 1,
+// be = bias; constant border row m = 0, be = bval; the zero row i = HL that flushes the last
+// output row m = be = 0.  (TMEM is zeroed at kernel start, so raw is always finite.)
+template <int WIN, bool BORDER, int NPIX, int WMAX>
+__device__ __forceinline__ void dw_step(uint32_t ring, int i, int HIN, float bias, float bval, const float (&w)[9],
+                                        unsigned char* dst, float (&P)[WMAX], float (&R)[WMAX]) {
   constexpr int WL = BORDER ? WIN + 2 : WIN;
-  constexpr int OFF = BORDER ? 2 : 1;  // a[.][OFF + x] = raw column x; a[.][0] and a[.][WL + 1] are the zero padding
+  constexpr int OFF = BORDER ? 2 : 1;  // v[OFF + x] = raw column x; v[0] and v[WL + 1] are the zero padding
+  static_assert(WL <= WMAX, "row state too small");
   const int HL = BORDER ? HIN + 2 : HIN;
-  float a[3][WL + 2];
-#pragma unroll
-  for (int dr = 0; dr < 3; ++dr) {
-    const int i = r + dr - 1;
-    if (i < 0 || i >= HL) {
-#pragma unroll
-      for (int j = 0; j < WL + 2; ++j) a[dr][j] = 0.f;
-    } else if (BORDER && (i == 0 || i == HL - 1)) {
-      a[dr][0] = 0.f;
-      a[dr][WL + 1] = 0.f;
-#pragma unroll
-      for (int j = 1; j <= WL; ++j) a[dr][j] = bval;
-    } else {
-      const int rho = BORDER ? i - 1 : i;
-      float raw[NPIX];
-      tc_ld_row<NPIX>(ring + (uint32_t)((rho & 3) * NPIX), raw);
-      tc_wait_ld();
-      a[dr][0] = 0.f;
-      a[dr][WL + 1] = 0.f;
-      if (BORDER) {
-        a[dr][1] = bval;
-        a[dr][WL] = bval;
-      }
-#pragma unroll
-      for (int x = 0; x < WIN; ++x) a[dr][OFF + x] = fmaxf(raw[x] + bias, 0.f);
+  const bool flush = i >= HL;
+  const bool cst = BORDER && !flush && (i == 0 || i == HL - 1);
+  const float m = (flush || cst) ? 0.f : 1.f;
+  const float be = flush ? 0.f : (cst ? bval : bias);
+  const float edge = flush ? 0.f : bval;
+  const int rho = BORDER ? i - 1 : i;
+  float v[WL + 2];
+  {
+    float raw[NPIX];
+    tc_ld_row<NPIX>(ring + (uint32_t)((rho & 3) * NPIX), raw);
+    tc_wait_ld();
+    v[0] = 0.f;
+    v[WL + 1] = 0.f;
+    if (BORDER) {
+      v[1] = edge;
+      v[WL] = edge;
     }
+#pragma unroll
+    for (int x = 0; x < WIN; ++x) v[OFF + x] = fmaxf(fmaf(raw[x], m, be), 0.f);
   }
-  unsigned char* dst = bt + (c >> 2) * kLboB + (c & 3) * 4;
+  const bool st = i >= 1;
 #pragma unroll
   for (int x = 0; x < WL; ++x) {
-    float o = 0.f;
-#pragma unroll
-    for (int dr = 0; dr < 3; ++dr)
-#pragma unroll
-      for (int dx = 0; dx < 3; ++dx) o = fmaf(w[dr * 3 + dx], a[dr][x + dx], o);
-    *reinterpret_cast<float*>(dst + (x >> 3) * kSboBp + (x & 7) * 16) = to_tf32(o);
+    const float o = fmaf(w[8], v[x + 2], fmaf(w[7], v[x + 1], fmaf(w[6], v[x], P[x])));
+    P[x] = fmaf(w[5], v[x + 2], fmaf(w[4], v[x + 1], fmaf(w[3], v[x], R[x])));
+    R[x] = fmaf(w[2], v[x + 2], fmaf(w[1], v[x + 1], w[0] * v[x]));
+    if (st) *reinterpret_cast<float*>(dst + (x >> 3) * kSboBp + (x & 7) * 16) = to_tf32(o);
   }
 }
 
-template <int NPIX>
+template <int F, int NPIX>
 struct FusedLayout {
+  static constexpr int FP = F + 4;  // feature row pitch: 2 zero columns left, >= 2 right (conv1 padding 2)
   static constexpr int b1_tile = (NPIX / 8) * kSboB1, b1_stride = b1_tile + 64;
   static constexpr int bp_tile = (NPIX / 8) * kSboBp, bp_stride = bp_tile + 64;
   static constexpr int off_a1 = 0;
@@ -145,23 +146,45 @@ struct FusedLayout {
   static constexpr int off_bp = off_b1 + 2 * b1_stride;
   static constexpr int off_pool = off_bp + 8 * bp_stride;
   static constexpr int off_feat = off_pool + 2 * kFC * 4;
+  // zero-padded feature map of one clip: rows -2 .. T+1
+  static constexpr size_t feat_floats(int T) { return (size_t)(T + 4) * FP; }
 };
+
+template <bool ACC>
+__device__ __forceinline__ void tc_mma_tf32_c(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "n"(ACC ? 1 : 0)
+      : "memory");
+}
+// one GEMM: NK k-steps of 8; the descriptors' address fields advance by 256 B (A) / 2 * 144 B (B)
+template <int NK>
+__device__ __forceinline__ void issue_gemm(uint32_t d, uint64_t adesc, uint64_t bdesc, uint32_t idesc) {
+  tc_mma_tf32_c<false>(d, adesc, bdesc, idesc);
+#pragma unroll
+  for (int ks = 1; ks < NK; ++ks)
+    tc_mma_tf32_c<true>(d, adesc + (uint64_t)(ks * (256 >> 4)), bdesc + (uint64_t)(ks * ((2 * kLboB) >> 4)), idesc);
+}
 
 template <int F, int NPIX>
 __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedParams p) {
-  constexpr int W0 = (F - 6) / 2 + 1;
-  static_assert(W0 + 6 <= NPIX && NPIX % 8 == 0, "row of the widest layer must fit the MMA N");
-  using L = FusedLayout<NPIX>;
+  constexpr int W0 = (F - 6) / 2 + 1, WMAX = W0 + 6;
+  static_assert(WMAX <= NPIX && NPIX % 8 == 0, "row of the widest layer must fit the MMA N");
+  using L = FusedLayout<F, NPIX>;
+  constexpr int FP = L::FP;
   extern __shared__ __align__(128) unsigned char smem[];
   __shared__ __align__(8) unsigned long long s_bar;
   __shared__ uint32_t s_tmem;
-  float* s_feat = reinterpret_cast<float*>(smem + L::off_feat);  // [2][T * F]
+  float* s_feat = reinterpret_cast<float*>(smem + L::off_feat);  // [2][(T + 4) * FP], zero padded, tf32-rounded
   float* s_pool = reinterpret_cast<float*>(smem + L::off_pool);  // [2][64]
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int g = warp >> 2, q = warp & 3, sl = lane >> 4, c = q * 16 + (lane & 15);
   const uint32_t bar = smem_u32(&s_bar);
   const int T = p.T, H0 = p.H0, TF = T * F;
+  const int feat_stride = (int)L::feat_floats(T);
 
   if (tid == 0) {
     mbar_init(bar, 10);
@@ -176,7 +199,8 @@ __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedPa
     uint4* dst = reinterpret_cast<uint4*>(smem);
     for (int i = tid; i < kAImgBytes / 16; i += kFThreads) dst[i] = src[i];
     uint4* z = reinterpret_cast<uint4*>(smem + L::off_b1);
-    for (int i = tid; i < (L::off_pool - L::off_b1) / 16; i += kFThreads) z[i] = make_uint4(0, 0, 0, 0);
+    const int nz = (L::off_feat - L::off_b1) / 16 + (2 * feat_stride * 4 + 15) / 16;  // B tiles, pool, feature pads
+    for (int i = tid; i < nz; i += kFThreads) z[i] = make_uint4(0, 0, 0, 0);
   }
   float w[9];
 #pragma unroll
@@ -191,8 +215,45 @@ __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedPa
   const uint32_t my_tmem = tmem + ((uint32_t)(q * 32) << 16);      // this warp's lane quarter
   const uint32_t my_ring = my_tmem + (uint32_t)(g * 4 * NPIX);     // input ring of the block this warp runs
   const uint32_t my_acc4 = my_tmem + (uint32_t)(16 * NPIX);
-  unsigned char* my_bt = smem + L::off_bp + (g * 2 + sl) * L::bp_stride;
+  unsigned char* my_dst = smem + L::off_bp + (g * 2 + sl) * L::bp_stride + (c >> 2) * kLboB + (c & 3) * 4;
   constexpr uint32_t kIdescF = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(NPIX >> 3) << 17) | ((64u >> 4) << 24);
+  if (g == 0) {  // zero the accumulator rings once: dw_step multiplies not-yet-written rows by 0
+    for (int col = 0; col < 512; col += 16) {
+      asm volatile(
+          "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1};" ::"r"(my_tmem + col),
+          "r"(0)
+          : "memory");
+    }
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+  }
+
+  // conv1 im2col item of this thread: slot, 16-byte K-chunk (4 taps) and a pixel column group
+  const bool im_on = tid < 500;
+  const int im_s = tid / 250, im_kc = (tid % 250) % 25, im_xg = (tid % 250) / 25;
+  int im_off[4];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const int k = 4 * im_kc + e, ki = k / 10, kj = k - 10 * ki;
+    im_off[e] = ki * FP + kj;
+  }
+  const float* im_src = s_feat + im_s * feat_stride;
+  unsigned char* im_dst = smem + L::off_b1 + im_s * L::b1_stride + im_kc * kLboB;
+
+  // MMA issue role of warps 0..9 (lane 0): stage = warp / 2 (0 = conv1, 1..4 = pointwise), slot = warp % 2
+  const int ms_stage = warp >> 1, ms_slot = warp & 1;
+  uint64_t ms_adesc = 0, ms_bdesc = 0;
+  if (warp < 10) {
+    if (ms_stage == 0) {
+      ms_adesc = umma_desc(smem_u32(smem + L::off_a1), 128u, kSboA1);
+      ms_bdesc = umma_desc(smem_u32(smem + L::off_b1 + ms_slot * L::b1_stride), kLboB, kSboB1);
+    } else {
+      ms_adesc = umma_desc(smem_u32(smem + L::off_ap + (ms_stage - 1) * 8 * kSboAp), 128u, kSboAp);
+      ms_bdesc = umma_desc(smem_u32(smem + L::off_bp + ((ms_stage - 1) * 2 + ms_slot) * L::bp_stride), kLboB, kSboBp);
+    }
+  }
+  const uint32_t ms_d = tmem + ((uint32_t)(ms_slot * 16) << 16) + (uint32_t)(ms_stage * 4 * NPIX);
+  const int ms_lag = ms_stage == 0 ? 0 : ms_stage + 1;
+  const int ms_rows = ms_stage == 0 ? H0 : H0 + 2 * (ms_stage - 1);
 
   const int nsteps = H0 + 12;
   const int H3 = H0 + 6, W3 = W0 + 6;
@@ -200,43 +261,43 @@ __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedPa
   const float inv_area = 1.0f / (float)((H3 + 2) * (W3 + 2));
   const long long npairs = (p.B + 1) / 2;
   uint32_t phase = 0;
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
 
   for (long long pair = blockIdx.x; pair < npairs; pair += gridDim.x) {
-    // ---- features of the two clips -> shared memory ----
+    // ---- features of the two clips -> zero-padded, tf32-rounded map in shared memory ----
     {
-      const long long nvalid = (2 * pair + 1 < p.B) ? 2LL * TF : (long long)TF;
+      const int nvalid = (2 * pair + 1 < p.B) ? 2 * TF : TF;
       const float* src = p.feats + 2 * pair * TF;
-      for (int i = tid; i < 2 * TF; i += kFThreads) s_feat[i] = (i < nvalid) ? __ldg(src + i) : 0.f;
+      for (int i = tid; i < 2 * TF; i += kFThreads) {
+        const int s = i >= TF, rem = i - s * TF, fr = rem / F, fc = rem - fr * F;
+        s_feat[s * feat_stride + (fr + 2) * FP + fc + 2] = (i < nvalid) ? to_tf32(__ldg(src + i)) : 0.f;
+      }
     }
     float psum = 0.f;
+    float P[WMAX], R[WMAX];
+#pragma unroll
+    for (int x = 0; x < WMAX; ++x) P[x] = R[x] = 0.f;
     __syncthreads();
 
     for (int t = 0; t < nsteps; ++t) {
       // ================= compute phase =================
-      if (t < H0) {  // im2col of conv1 output row t: one 16-byte K-chunk (4 taps) per item
-        for (int idx = tid; idx < 2 * W0 * 25; idx += kFThreads) {
-          const int s = idx / (W0 * 25), rem = idx - s * (W0 * 25);
-          const int x = rem / 25, kc = rem - x * 25;
-          const float* fsrc = s_feat + s * TF;
-          float v[4];
-#pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const int k = 4 * kc + e, ki = k / 10, kj = k - 10 * ki;
-            const int fr = 2 * t - 2 + ki, fcol = 2 * x - 2 + kj;
-            const bool ok = fr >= 0 && fr < T && fcol >= 0 && fcol < F;
-            v[e] = ok ? to_tf32(fsrc[fr * F + fcol]) : 0.f;
-          }
-          *reinterpret_cast<float4*>(smem + L::off_b1 + s * L::b1_stride + (x >> 3) * kSboB1 + kc * kLboB + (x & 7) * 16) =
-              make_float4(v[0], v[1], v[2], v[3]);
+      if (t < H0 && im_on) {  // im2col of conv1 output row t
+        const float* rowp = im_src + 2 * t * FP;
+        for (int x = im_xg; x < W0; x += 10) {
+          const float* q4 = rowp + 2 * x;
+          *reinterpret_cast<float4*>(im_dst + (x >> 3) * kSboB1 + (x & 7) * 16) =
+              make_float4(q4[im_off[0]], q4[im_off[1]], q4[im_off[2]], q4[im_off[3]]);
         }
       }
-      {  // depthwise of block g+1 on row t-(g+2)
-        const int r = t - (g + 2);
-        if (r >= 0 && r < H0 + 2 * g) {
-          if (g == 0) dw_row<W0, false, NPIX>(my_ring, r, H0, in_bias, 0.f, w, my_bt, c);
-          else if (g == 1) dw_row<W0, true, NPIX>(my_ring, r, H0, in_bias, in_border, w, my_bt, c);
-          else if (g == 2) dw_row<W0 + 2, true, NPIX>(my_ring, r, H0 + 2, in_bias, in_border, w, my_bt, c);
-          else dw_row<W0 + 4, true, NPIX>(my_ring, r, H0 + 4, in_bias, in_border, w, my_bt, c);
+      {  // depthwise of block g+1: input row t-(g+1) of its input layer, finishing output row t-(g+2)
+        const int i = t - (g + 1);
+        if (i >= 0 && i <= H0 + 2 * g) {
+          if (g == 0) dw_step<W0, false, NPIX, WMAX>(my_ring, i, H0, in_bias, 0.f, w, my_dst, P, R);
+          else if (g == 1) dw_step<W0, true, NPIX, WMAX>(my_ring, i, H0, in_bias, in_border, w, my_dst, P, R);
+          else if (g == 2) dw_step<W0 + 2, true, NPIX, WMAX>(my_ring, i, H0 + 2, in_bias, in_border, w, my_dst, P, R);
+          else dw_step<W0 + 4, true, NPIX, WMAX>(my_ring, i, H0 + 4, in_bias, in_border, w, my_dst, P, R);
         }
       }
       if (g == 0) {  // pooling of the last block's row t-6 (interior pixels; the border is added at the end)
@@ -252,28 +313,13 @@ __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedPa
       fence_proxy_async();
       tc_fence_before();
       __syncthreads();
-      // ================= MMA phase: stage s = warp/2 (0 = conv1, 1..4 = pointwise), slot = warp%2 =================
+      // ================= MMA phase =================
       if (warp < 10 && lane == 0) {
-        const int s = warp >> 1, ms = warp & 1;
-        const int r = (s == 0) ? t : t - (s + 1);
-        const int nrows = (s == 0) ? H0 : H0 + 2 * (s - 1);
-        if (r >= 0 && r < nrows) {
+        const int r = t - ms_lag;
+        if (r >= 0 && r < ms_rows) {
           tc_fence_after();
-          const uint32_t d = tmem + ((uint32_t)(ms * 16) << 16) + (uint32_t)(s < 4 ? (s * 4 + (r & 3)) * NPIX : 16 * NPIX);
-          if (s == 0) {
-            const uint32_t ab = smem_u32(smem + L::off_a1), bb = smem_u32(smem + L::off_b1 + ms * L::b1_stride);
-#pragma unroll 1
-            for (int ks = 0; ks < kKC1 / 8; ++ks)
-              tc_mma_tf32(d, umma_desc(ab + ks * 256u, 128u, kSboA1), umma_desc(bb + ks * 2u * kLboB, kLboB, kSboB1), kIdescF,
-                          ks > 0);
-          } else {
-            const uint32_t ab = smem_u32(smem + L::off_ap + (s - 1) * 8 * kSboAp);
-            const uint32_t bb = smem_u32(smem + L::off_bp + ((s - 1) * 2 + ms) * L::bp_stride);
-#pragma unroll 1
-            for (int ks = 0; ks < kFC / 8; ++ks)
-              tc_mma_tf32(d, umma_desc(ab + ks * 256u, 128u, kSboAp), umma_desc(bb + ks * 2u * kLboB, kLboB, kSboBp), kIdescF,
-                          ks > 0);
-          }
+          if (ms_stage == 0) issue_gemm<kKC1 / 8>(ms_d + (uint32_t)((r & 3) * NPIX), ms_adesc, ms_bdesc, kIdescF);
+          else issue_gemm<kFC / 8>(ms_d + (uint32_t)(ms_stage < 4 ? (r & 3) * NPIX : 0), ms_adesc, ms_bdesc, kIdescF);
           tc_commit(bar);
         } else {
           asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
@@ -355,8 +401,8 @@ int build_fused_model(ModelWeights& m, const std::vector<float>& conv1_w, const 
 
 template <int F, int NPIX>
 static int launch_fused_t(kws_handle_t h, const FusedParams& p, cudaStream_t stream) {
-  using L = FusedLayout<NPIX>;
-  const size_t smem_bytes = (size_t)L::off_feat + (size_t)2 * p.T * F * 4;
+  using L = FusedLayout<F, NPIX>;
+  const size_t smem_bytes = (size_t)L::off_feat + 2 * L::feat_floats(p.T) * 4;
   if (smem_bytes > 227 * 1024) return 0;
   auto kern = dscnn_fused_kernel<F, NPIX>;
   KWS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
