@@ -38,7 +38,6 @@
 namespace kws {
 
 constexpr int kFC = 64;                      // channels of the reference network
-constexpr int kFThreads = 512;
 constexpr int kLboB = 144;                   // K-chunk pitch of the B tiles (bank spreading)
 constexpr int kKC1 = 104;                    // conv1 K (100 taps) padded to a multiple of 8
 constexpr int kSboA1 = (kKC1 / 4) * 128;     // 8-row group pitch: conv1 weights
@@ -60,80 +59,75 @@ struct FusedParams {
   const float* fc_b;      // [ncls]
 };
 
-template <int N>
-__device__ __forceinline__ void tc_ld_row(uint32_t taddr, float (&v)[N]);
-template <>
-__device__ __forceinline__ void tc_ld_row<16>(uint32_t taddr, float (&v)[16]) {
-  tc_ld16(taddr, v);
-}
-template <>
-__device__ __forceinline__ void tc_ld_row<24>(uint32_t taddr, float (&v)[24]) {
-  uint32_t r[24];
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-      : "r"(taddr)
-      : "memory");
-  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-               : "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23])
-               : "r"(taddr + 16)
-               : "memory");
-#pragma unroll
-  for (int i = 0; i < 24; ++i) v[i] = __uint_as_float(r[i]);
-}
-
-// One step of the depthwise 3x3 (zero padding 1) of a block for this thread's (slot, channel):
-// consume INPUT row i of the block's input layer and finish OUTPUT row i - 1.
-// The stencil is accumulated per input row: with v = the activated input row,
+// One step of the depthwise 3x3 (zero padding 1) of a block for this thread's (slot, channel) on
+// its warp's 8-pixel column segment [8j, 8j+8): consume INPUT row i of the block's input layer and
+// finish OUTPUT row i - 1.  The stencil is accumulated per input row: with v = the activated row,
 //     out[x]  = P[x] + sum_dx w[2][dx] v[x+dx]     (output row i-1 complete -> B tile of the pointwise GEMM)
 //     P'[x]   = R[x] + sum_dx w[1][dx] v[x+dx]     (output row i, two of three rows in)
 //     R'[x]   =        sum_dx w[0][dx] v[x+dx]     (output row i+1, one row in)
 // so every input row is read from TMEM and activated exactly once and nothing is ever moved.
 // The input row is the raw accumulator row of the producing GEMM in the TMEM ring:
-//   BORDER = false (block 1 reads conv1's output): layer row i = raw row i, value ReLU(raw + bias);
+//   BORDER = false (block 1 reads conv1's output): layer column gx = raw column gx, ReLU(raw + bias);
 //   BORDER = true  (blocks 2..4 read a padded-pointwise output): the layer has HIN + 2 rows and
-//                  WIN + 2 columns, its outermost ring is the constant `bval`, interior row i is raw
-//                  row i - 1 shifted right by one column.
+//                  WIN + 2 columns, its outermost ring is the constant `bval`, interior (i, gx) is raw
+//                  (i - 1, gx - 1).
 // Row classes are CTA-uniform and folded into scalars (v = max(raw * m + be, 0)): interior m = 1,
 // be = bias; constant border row m = 0, be = bval; the zero row i = HL that flushes the last
-// output row m = be = 0.  (TMEM is zeroed at kernel start, so raw is always finite.)
-template <int WIN, bool BORDER, int NPIX, int WMAX>
-__device__ __forceinline__ void dw_step(uint32_t ring, int i, int HIN, float bias, float bval, const float (&w)[9],
-                                        unsigned char* dst, float (&P)[WMAX], float (&R)[WMAX]) {
+// output row m = be = 0 (TMEM is zeroed at kernel start, so raw is always finite).  Column classes
+// (left/right border, columns past the layer) depend only on the warp's segment j and are patched
+// with warp-uniform predicated moves.  `par` points at this channel's [w0..w8, bias, border] column.
+template <int WIN, bool BORDER>
+__device__ __forceinline__ void dw_seg(uint32_t taddr, int j, int i, int HIN, const float* par, unsigned char* dst,
+                                       float (&P)[8], float (&R)[8]) {
   constexpr int WL = BORDER ? WIN + 2 : WIN;
-  constexpr int OFF = BORDER ? 2 : 1;  // v[OFF + x] = raw column x; v[0] and v[WL + 1] are the zero padding
-  static_assert(WL <= WMAX, "row state too small");
+  constexpr int JL = (WL - 1) / 8, KL = WL - 8 * JL;  // segment and v-index of the layer's last column
+  constexpr int RO = BORDER ? 2 : 3;                   // v[k] (layer column 8j-1+k) = raw[k + RO]; raw[0] = column 8j-4
   const int HL = BORDER ? HIN + 2 : HIN;
   const bool flush = i >= HL;
   const bool cst = BORDER && !flush && (i == 0 || i == HL - 1);
+  const float bias = par[9 * kFC], bval = BORDER ? par[10 * kFC] : 0.f;
   const float m = (flush || cst) ? 0.f : 1.f;
   const float be = flush ? 0.f : (cst ? bval : bias);
   const float edge = flush ? 0.f : bval;
-  const int rho = BORDER ? i - 1 : i;
-  float v[WL + 2];
+  float v[10];
   {
-    float raw[NPIX];
-    tc_ld_row<NPIX>(ring + (uint32_t)((rho & 3) * NPIX), raw);
+    float raw[16];
+    tc_ld16(taddr, raw);
     tc_wait_ld();
-    v[0] = 0.f;
-    v[WL + 1] = 0.f;
-    if (BORDER) {
-      v[1] = edge;
-      v[WL] = edge;
-    }
 #pragma unroll
-    for (int x = 0; x < WIN; ++x) v[OFF + x] = fmaxf(fmaf(raw[x], m, be), 0.f);
+    for (int k = 0; k < 10; ++k) v[k] = fmaxf(fmaf(raw[k + RO], m, be), 0.f);
   }
+  if (j == 0) {
+    v[0] = 0.f;
+    if (BORDER) v[1] = edge;
+  }
+  if (j == JL) {
+    if (BORDER) v[KL] = edge;
+#pragma unroll
+    for (int k = KL + 1; k < 10; ++k) v[k] = 0.f;
+  }
+  if (j > JL) {
+#pragma unroll
+    for (int k = 0; k < 10; ++k) v[k] = 0.f;
+  }
+  float w[9];
+#pragma unroll
+  for (int k = 0; k < 9; ++k) w[k] = par[k * kFC];
   const bool st = i >= 1;
 #pragma unroll
-  for (int x = 0; x < WL; ++x) {
+  for (int x = 0; x < 8; ++x) {
     const float o = fmaf(w[8], v[x + 2], fmaf(w[7], v[x + 1], fmaf(w[6], v[x], P[x])));
     P[x] = fmaf(w[5], v[x + 2], fmaf(w[4], v[x + 1], fmaf(w[3], v[x], R[x])));
     R[x] = fmaf(w[2], v[x + 2], fmaf(w[1], v[x + 1], w[0] * v[x]));
-    if (st) *reinterpret_cast<float*>(dst + (x >> 3) * kSboBp + (x & 7) * 16) = to_tf32(o);
+    if (st) *reinterpret_cast<float*>(dst + x * 16) = to_tf32(o);
   }
 }
+
+constexpr int kCWarps = 12;                       // compute warps: 3 column segments x 4 lane quarters
+constexpr int kCThreads = kCWarps * 32;
+constexpr int kFThreads = (kCWarps + 2) * 32;     // + one MMA-issue warp per clip slot
+constexpr int kRingCols = 64;                     // per layer: 2 row slots x (8 margin + 24) columns
+constexpr int kAcc4Col = 4 * kRingCols;           // last pointwise layer's row (pooled at once)
 
 template <int F, int NPIX>
 struct FusedLayout {
@@ -144,8 +138,9 @@ struct FusedLayout {
   static constexpr int off_ap = 8 * kSboA1;
   static constexpr int off_b1 = kAImgBytes;
   static constexpr int off_bp = off_b1 + 2 * b1_stride;
-  static constexpr int off_pool = off_bp + 8 * bp_stride;
-  static constexpr int off_feat = off_pool + 2 * kFC * 4;
+  static constexpr int off_par = off_bp + 8 * bp_stride;          // [4][11][64] depthwise taps, input bias, border
+  static constexpr int off_pool = off_par + 4 * 11 * kFC * 4;     // [3][2][64] pooling partials
+  static constexpr int off_feat = off_pool + 3 * 2 * kFC * 4;
   // zero-padded feature map of one clip: rows -2 .. T+1
   static constexpr size_t feat_floats(int T) { return (size_t)(T + 4) * FP; }
 };
@@ -168,26 +163,81 @@ __device__ __forceinline__ void issue_gemm(uint32_t d, uint64_t adesc, uint64_t 
     tc_mma_tf32_c<true>(d, adesc + (uint64_t)(ks * (256 >> 4)), bdesc + (uint64_t)(ks * ((2 * kLboB) >> 4)), idesc);
 }
 
+// Stage schedule (step t of a clip pair; phase A then phase B inside a step):
+//   conv1 im2col + GEMM row t                    (B)      | dw1: input row t-2 (A), pw1 GEMM row t-3 (end of A)
+//   dw2: input row t-3 (B), pw2 GEMM row t-4 (end of B)    | dw3: input row t-5 (A), pw3 GEMM row t-6 (end of A)
+//   dw4: input row t-6 (B), pw4 GEMM row t-7 (end of B)    | pooling of pw4 row t-8 (B)
+// GEMMs issued at the end of a phase run on the tensor core while the compute warps execute the
+// next phase, whose stages never touch what those GEMMs read or write.
+template <int F, int NPIX, int SLOT>
+__device__ __forceinline__ void fused_mma_warp(unsigned char* smem, uint32_t tmem, uint32_t barO, uint32_t barE, int H0,
+                                               long long npairs, int lane) {
+  using L = FusedLayout<F, NPIX>;
+  constexpr uint32_t kIdescF = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(NPIX >> 3) << 17) | ((64u >> 4) << 24);
+  const uint32_t sbase = smem_u32(smem);
+  const uint64_t a1 = umma_desc(sbase + L::off_a1, 128u, kSboA1);
+  const uint64_t b1 = umma_desc(sbase + L::off_b1 + SLOT * L::b1_stride, kLboB, kSboB1);
+  uint64_t ap[4], bp[4];
+#pragma unroll
+  for (int l = 0; l < 4; ++l) {
+    ap[l] = umma_desc(sbase + L::off_ap + l * 8 * kSboAp, 128u, kSboAp);
+    bp[l] = umma_desc(sbase + L::off_bp + (l * 2 + SLOT) * L::bp_stride, kLboB, kSboBp);
+  }
+  const uint32_t d0 = tmem + ((uint32_t)(SLOT * 16) << 16) + 8u;  // ring rows start after an 8-column margin
+  const int nsteps = H0 + 14;
+  for (long long pair = blockIdx.x; pair < npairs; pair += gridDim.x) {
+    __syncthreads();  // features loaded
+    for (int t = 0; t < nsteps; ++t) {
+      __syncthreads();  // phase A written
+      if (lane == 0) {
+        tc_fence_after();
+        int r = t - 3;
+        if (r >= 0 && r < H0) issue_gemm<kFC / 8>(d0 + 1 * kRingCols + (r & 1) * 32, ap[0], bp[0], kIdescF);
+        r = t - 6;
+        if (r >= 0 && r < H0 + 4) issue_gemm<kFC / 8>(d0 + 3 * kRingCols + (r & 1) * 32, ap[2], bp[2], kIdescF);
+        tc_commit(barO);
+      }
+      __syncwarp();
+      __syncthreads();  // phase B written
+      if (lane == 0) {
+        tc_fence_after();
+        int r = t;
+        if (r < H0) issue_gemm<kKC1 / 8>(d0 + (r & 1) * 32, a1, b1, kIdescF);
+        r = t - 4;
+        if (r >= 0 && r < H0 + 2) issue_gemm<kFC / 8>(d0 + 2 * kRingCols + (r & 1) * 32, ap[1], bp[1], kIdescF);
+        r = t - 7;
+        if (r >= 0 && r < H0 + 6) issue_gemm<kFC / 8>(d0 - 8u + kAcc4Col, ap[3], bp[3], kIdescF);
+        tc_commit(barE);
+      }
+      __syncwarp();
+    }
+    __syncthreads();  // pooling partials written
+    __syncthreads();  // logits written
+  }
+}
+
 template <int F, int NPIX>
 __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedParams p) {
-  constexpr int W0 = (F - 6) / 2 + 1, WMAX = W0 + 6;
-  static_assert(WMAX <= NPIX && NPIX % 8 == 0, "row of the widest layer must fit the MMA N");
+  constexpr int W0 = (F - 6) / 2 + 1, W3 = W0 + 6, NSEG = NPIX / 8;
+  static_assert(W3 <= NPIX && NPIX % 8 == 0 && NSEG <= 3, "row of the widest layer must fit the MMA N");
   using L = FusedLayout<F, NPIX>;
   constexpr int FP = L::FP;
   extern __shared__ __align__(128) unsigned char smem[];
-  __shared__ __align__(8) unsigned long long s_bar;
+  __shared__ __align__(8) unsigned long long s_bar[2];
   __shared__ uint32_t s_tmem;
   float* s_feat = reinterpret_cast<float*>(smem + L::off_feat);  // [2][(T + 4) * FP], zero padded, tf32-rounded
-  float* s_pool = reinterpret_cast<float*>(smem + L::off_pool);  // [2][64]
+  float* s_pool = reinterpret_cast<float*>(smem + L::off_pool);  // [3][2][64]
+  float* s_par = reinterpret_cast<float*>(smem + L::off_par);    // [4][11][64]
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int g = warp >> 2, q = warp & 3, sl = lane >> 4, c = q * 16 + (lane & 15);
-  const uint32_t bar = smem_u32(&s_bar);
+  const uint32_t barO = smem_u32(&s_bar[0]), barE = smem_u32(&s_bar[1]);
   const int T = p.T, H0 = p.H0, TF = T * F;
   const int feat_stride = (int)L::feat_floats(T);
+  const long long npairs = (p.B + 1) / 2;
 
   if (tid == 0) {
-    mbar_init(bar, 10);
+    mbar_init(barO, 2);
+    mbar_init(barE, 2);
     fence_mbar_init();
   }
   if (warp == 0) {
@@ -202,148 +252,168 @@ __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedPa
     const int nz = (L::off_feat - L::off_b1) / 16 + (2 * feat_stride * 4 + 15) / 16;  // B tiles, pool, feature pads
     for (int i = tid; i < nz; i += kFThreads) z[i] = make_uint4(0, 0, 0, 0);
   }
-  float w[9];
-#pragma unroll
-  for (int i = 0; i < 9; ++i) w[i] = p.dw_w[(g * 9 + i) * kFC + c];
-  const float in_bias = p.act_bias[g * kFC + c], in_border = p.border[g * kFC + c];
-  const float pool_bias = p.act_bias[4 * kFC + c], pool_border = p.border[4 * kFC + c];
+  __syncthreads();
+  for (int i = tid; i < 4 * 11 * kFC; i += kFThreads) {
+    const int l = i / (11 * kFC), k = (i / kFC) % 11, ch = i % kFC;
+    s_par[i] = k < 9 ? p.dw_w[(l * 9 + k) * kFC + ch] : (k == 9 ? p.act_bias[l * kFC + ch] : p.border[l * kFC + ch]);
+  }
   fence_proxy_async();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = s_tmem;
-  const uint32_t my_tmem = tmem + ((uint32_t)(q * 32) << 16);      // this warp's lane quarter
-  const uint32_t my_ring = my_tmem + (uint32_t)(g * 4 * NPIX);     // input ring of the block this warp runs
-  const uint32_t my_acc4 = my_tmem + (uint32_t)(16 * NPIX);
-  unsigned char* my_dst = smem + L::off_bp + (g * 2 + sl) * L::bp_stride + (c >> 2) * kLboB + (c & 3) * 4;
-  constexpr uint32_t kIdescF = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(NPIX >> 3) << 17) | ((64u >> 4) << 24);
-  if (g == 0) {  // zero the accumulator rings once: dw_step multiplies not-yet-written rows by 0
+  if (warp < 4) {  // zero the accumulator rings once: dw_seg multiplies not-yet-written rows by 0
     for (int col = 0; col < 512; col += 16) {
       asm volatile(
-          "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1};" ::"r"(my_tmem + col),
+          "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1};" ::"r"(
+              tmem + ((uint32_t)(warp * 32) << 16) + col),
           "r"(0)
           : "memory");
     }
     asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
   }
-
-  // conv1 im2col item of this thread: slot, 16-byte K-chunk (4 taps) and a pixel column group
-  const bool im_on = tid < 500;
-  const int im_s = tid / 250, im_kc = (tid % 250) % 25, im_xg = (tid % 250) / 25;
-  int im_off[4];
-#pragma unroll
-  for (int e = 0; e < 4; ++e) {
-    const int k = 4 * im_kc + e, ki = k / 10, kj = k - 10 * ki;
-    im_off[e] = ki * FP + kj;
-  }
-  const float* im_src = s_feat + im_s * feat_stride;
-  unsigned char* im_dst = smem + L::off_b1 + im_s * L::b1_stride + im_kc * kLboB;
-
-  // MMA issue role of warps 0..9 (lane 0): stage = warp / 2 (0 = conv1, 1..4 = pointwise), slot = warp % 2
-  const int ms_stage = warp >> 1, ms_slot = warp & 1;
-  uint64_t ms_adesc = 0, ms_bdesc = 0;
-  if (warp < 10) {
-    if (ms_stage == 0) {
-      ms_adesc = umma_desc(smem_u32(smem + L::off_a1), 128u, kSboA1);
-      ms_bdesc = umma_desc(smem_u32(smem + L::off_b1 + ms_slot * L::b1_stride), kLboB, kSboB1);
-    } else {
-      ms_adesc = umma_desc(smem_u32(smem + L::off_ap + (ms_stage - 1) * 8 * kSboAp), 128u, kSboAp);
-      ms_bdesc = umma_desc(smem_u32(smem + L::off_bp + ((ms_stage - 1) * 2 + ms_slot) * L::bp_stride), kLboB, kSboBp);
-    }
-  }
-  const uint32_t ms_d = tmem + ((uint32_t)(ms_slot * 16) << 16) + (uint32_t)(ms_stage * 4 * NPIX);
-  const int ms_lag = ms_stage == 0 ? 0 : ms_stage + 1;
-  const int ms_rows = ms_stage == 0 ? H0 : H0 + 2 * (ms_stage - 1);
-
-  const int nsteps = H0 + 12;
-  const int H3 = H0 + 6, W3 = W0 + 6;
-  const float nborder = (float)((H3 + 2) * (W3 + 2) - H3 * W3);
-  const float inv_area = 1.0f / (float)((H3 + 2) * (W3 + 2));
-  const long long npairs = (p.B + 1) / 2;
-  uint32_t phase = 0;
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
 
-  for (long long pair = blockIdx.x; pair < npairs; pair += gridDim.x) {
-    // ---- features of the two clips -> zero-padded, tf32-rounded map in shared memory ----
-    {
-      const int nvalid = (2 * pair + 1 < p.B) ? 2 * TF : TF;
-      const float* src = p.feats + 2 * pair * TF;
-      for (int i = tid; i < 2 * TF; i += kFThreads) {
-        const int s = i >= TF, rem = i - s * TF, fr = rem / F, fc = rem - fr * F;
-        s_feat[s * feat_stride + (fr + 2) * FP + fc + 2] = (i < nvalid) ? to_tf32(__ldg(src + i)) : 0.f;
-      }
+  if (warp == kCWarps) {
+    fused_mma_warp<F, NPIX, 0>(smem, tmem, barO, barE, H0, npairs, lane);
+  } else if (warp == kCWarps + 1) {
+    fused_mma_warp<F, NPIX, 1>(smem, tmem, barO, barE, H0, npairs, lane);
+  } else {
+    // =========================== compute warps ===========================
+    const int j = warp >> 2, q = warp & 3, sl = lane >> 4, c = q * 16 + (lane & 15);
+    const bool seg_on = j < NSEG;
+    // TMEM: this warp's lane quarter; ring row slot s of layer l starts at column l*64 + s*32 + 8;
+    // a 16-column load from (segment start - 4) covers the segment and its halo
+    const uint32_t my_tmem = tmem + ((uint32_t)(q * 32) << 16);
+    const uint32_t my_ld = my_tmem + 8u + (uint32_t)(8 * j) - 4u;
+    unsigned char* my_dst = smem + L::off_bp + sl * L::bp_stride + j * kSboBp + (c >> 2) * kLboB + (c & 3) * 4;
+    const float* my_par = s_par + c;
+    // conv1 im2col item of this thread: slot, 16-byte K-chunk (4 taps), pixel columns xg, xg+7, xg+14
+    const bool im_on = tid < 350;
+    const int im_s = tid / 175, im_kc = (tid % 175) % 25, im_xg = (tid % 175) / 25;
+    int im_off[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int k = 4 * im_kc + e, ki = k / 10, kj = k - 10 * ki;
+      im_off[e] = ki * FP + kj;
     }
-    float psum = 0.f;
-    float P[WMAX], R[WMAX];
-#pragma unroll
-    for (int x = 0; x < WMAX; ++x) P[x] = R[x] = 0.f;
-    __syncthreads();
+    const float* im_src = s_feat + im_s * feat_stride;
+    unsigned char* im_dst = smem + L::off_b1 + im_s * L::b1_stride + im_kc * kLboB;
 
-    for (int t = 0; t < nsteps; ++t) {
-      // ================= compute phase =================
-      if (t < H0 && im_on) {  // im2col of conv1 output row t
-        const float* rowp = im_src + 2 * t * FP;
-        for (int x = im_xg; x < W0; x += 10) {
-          const float* q4 = rowp + 2 * x;
-          *reinterpret_cast<float4*>(im_dst + (x >> 3) * kSboB1 + (x & 7) * 16) =
-              make_float4(q4[im_off[0]], q4[im_off[1]], q4[im_off[2]], q4[im_off[3]]);
+    const int nsteps = H0 + 14;
+    const int H3 = H0 + 6;
+    const float nborder = (float)((H3 + 2) * (W3 + 2) - H3 * W3);
+    const float inv_area = 1.0f / (float)((H3 + 2) * (W3 + 2));
+    uint32_t nO = 0, nE = 0;  // completed waits on the two MMA-group barriers
+
+    for (long long pair = blockIdx.x; pair < npairs; pair += gridDim.x) {
+      // ---- features of the two clips -> zero-padded, tf32-rounded map in shared memory ----
+      {
+        const int nvalid = (2 * pair + 1 < p.B) ? 2 * TF : TF;
+        const float* src = p.feats + 2 * pair * TF;
+        for (int i = tid; i < 2 * TF; i += kCThreads) {
+          const int s = i >= TF, rem = i - s * TF, fr = rem / F, fc = rem - fr * F;
+          s_feat[s * feat_stride + (fr + 2) * FP + fc + 2] = (i < nvalid) ? to_tf32(__ldg(src + i)) : 0.f;
         }
       }
-      {  // depthwise of block g+1: input row t-(g+1) of its input layer, finishing output row t-(g+2)
-        const int i = t - (g + 1);
-        if (i >= 0 && i <= H0 + 2 * g) {
-          if (g == 0) dw_step<W0, false, NPIX, WMAX>(my_ring, i, H0, in_bias, 0.f, w, my_dst, P, R);
-          else if (g == 1) dw_step<W0, true, NPIX, WMAX>(my_ring, i, H0, in_bias, in_border, w, my_dst, P, R);
-          else if (g == 2) dw_step<W0 + 2, true, NPIX, WMAX>(my_ring, i, H0 + 2, in_bias, in_border, w, my_dst, P, R);
-          else dw_step<W0 + 4, true, NPIX, WMAX>(my_ring, i, H0 + 4, in_bias, in_border, w, my_dst, P, R);
-        }
-      }
-      if (g == 0) {  // pooling of the last block's row t-6 (interior pixels; the border is added at the end)
-        const int r = t - 6;
-        if (r >= 0 && r < H3) {
-          float raw[NPIX];
-          tc_ld_row<NPIX>(my_acc4, raw);
-          tc_wait_ld();
+      float psum = 0.f;
+      float P[4][8], R[4][8];
 #pragma unroll
-          for (int x = 0; x < W3; ++x) psum += fmaxf(raw[x] + pool_bias, 0.f);
-        }
-      }
-      fence_proxy_async();
-      tc_fence_before();
+      for (int l = 0; l < 4; ++l)
+#pragma unroll
+        for (int x = 0; x < 8; ++x) P[l][x] = R[l][x] = 0.f;
       __syncthreads();
-      // ================= MMA phase =================
-      if (warp < 10 && lane == 0) {
-        const int r = t - ms_lag;
-        if (r >= 0 && r < ms_rows) {
+
+      for (int t = 0; t < nsteps; ++t) {
+        // ================= phase A: depthwise of blocks 1 and 3 =================
+        if (t > 0) {  // the GEMMs issued after the previous phase A (pw1, pw3) have retired
+          mbar_wait(barO, nO & 1);
+          ++nO;
           tc_fence_after();
-          if (ms_stage == 0) issue_gemm<kKC1 / 8>(ms_d + (uint32_t)((r & 3) * NPIX), ms_adesc, ms_bdesc, kIdescF);
-          else issue_gemm<kFC / 8>(ms_d + (uint32_t)(ms_stage < 4 ? (r & 3) * NPIX : 0), ms_adesc, ms_bdesc, kIdescF);
-          tc_commit(bar);
-        } else {
-          asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+        }
+        if (seg_on) {
+          int i = t - 2;
+          if (i >= 0 && i <= H0)
+            dw_seg<W0, false>(my_ld + 0 * kRingCols + (uint32_t)((i & 1) * 32), j, i, H0, my_par + 0 * 11 * kFC,
+                              my_dst + 0 * 2 * L::bp_stride, P[0], R[0]);
+          i = t - 5;
+          if (i >= 0 && i <= H0 + 4)
+            dw_seg<W0 + 2, true>(my_ld + 2 * kRingCols + (uint32_t)(((i - 1) & 1) * 32), j, i, H0 + 2, my_par + 2 * 11 * kFC,
+                                 my_dst + 2 * 2 * L::bp_stride, P[2], R[2]);
+        }
+        fence_proxy_async();
+        tc_fence_before();
+        __syncthreads();
+        // ================= phase B: conv1 im2col, depthwise of blocks 2 and 4, pooling =================
+        if (t > 0) {  // the GEMMs issued after the previous phase B (conv1, pw2, pw4) have retired
+          mbar_wait(barE, nE & 1);
+          ++nE;
+          tc_fence_after();
+        }
+        if (t < H0 && im_on) {
+          const float* rowp = im_src + 2 * t * FP;
+          for (int x = im_xg; x < W0; x += 7) {
+            const float* q4 = rowp + 2 * x;
+            *reinterpret_cast<float4*>(im_dst + (x >> 3) * kSboB1 + (x & 7) * 16) =
+                make_float4(q4[im_off[0]], q4[im_off[1]], q4[im_off[2]], q4[im_off[3]]);
+          }
+        }
+        if (seg_on) {
+          int i = t - 3;
+          if (i >= 0 && i <= H0 + 2)
+            dw_seg<W0, true>(my_ld + 1 * kRingCols + (uint32_t)(((i - 1) & 1) * 32), j, i, H0, my_par + 1 * 11 * kFC,
+                             my_dst + 1 * 2 * L::bp_stride, P[1], R[1]);
+          i = t - 6;
+          if (i >= 0 && i <= H0 + 6)
+            dw_seg<W0 + 4, true>(my_ld + 3 * kRingCols + (uint32_t)(((i - 1) & 1) * 32), j, i, H0 + 4, my_par + 3 * 11 * kFC,
+                                 my_dst + 3 * 2 * L::bp_stride, P[3], R[3]);
+          const int r = t - 8;
+          if (r >= 0 && r < H3) {  // pooling of the last block's row r (interior pixels; the border is added at the end)
+            uint32_t raw[8];
+            asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                         : "=r"(raw[0]), "=r"(raw[1]), "=r"(raw[2]), "=r"(raw[3]), "=r"(raw[4]), "=r"(raw[5]), "=r"(raw[6]),
+                           "=r"(raw[7])
+                         : "r"(my_tmem + (uint32_t)kAcc4Col + (uint32_t)(8 * j))
+                         : "memory");
+            tc_wait_ld();
+            const float pb = p.act_bias[4 * kFC + c];
+#pragma unroll
+            for (int x = 0; x < 8; ++x)
+              if (8 * j + x < W3) psum += fmaxf(__uint_as_float(raw[x]) + pb, 0.f);
+          }
+        }
+        fence_proxy_async();
+        tc_fence_before();
+        __syncthreads();
+      }
+      // drain the last step's (empty) GEMM groups so the barrier phases stay in step
+      mbar_wait(barO, nO & 1);
+      ++nO;
+      mbar_wait(barE, nE & 1);
+      ++nE;
+      tc_fence_after();
+
+      // ---- global average pool (interior sum + border constant) and fc ----
+      s_pool[(j * 2 + sl) * kFC + c] = psum;
+      __syncthreads();
+      for (int i = tid; i < 2 * p.ncls; i += kCThreads) {
+        const int s = i / p.ncls, k = i - s * p.ncls;
+        const long long b = 2 * pair + s;
+        if (b < p.B) {
+          float acc = p.fc_b[k];
+          for (int ch = 0; ch < kFC; ++ch) {
+            const float pooled = (s_pool[s * kFC + ch] + s_pool[(2 + s) * kFC + ch] + s_pool[(4 + s) * kFC + ch] +
+                                  nborder * p.border[4 * kFC + ch]) * inv_area;
+            acc = fmaf(pooled, p.fc_w[ch * p.ncls + k], acc);
+          }
+          p.logits[b * p.ncls + k] = acc;
         }
       }
-      mbar_wait(bar, phase & 1);
-      ++phase;
-      tc_fence_after();
+      // the next pair's feature load overwrites s_feat / s_pool only after this barrier
+      __syncthreads();
     }
-
-    // ---- global average pool (interior sum + border constant) and fc ----
-    if (g == 0) s_pool[sl * kFC + c] = (psum + nborder * pool_border) * inv_area;
-    __syncthreads();
-    for (int i = tid; i < 2 * p.ncls; i += kFThreads) {
-      const int s = i / p.ncls, k = i - s * p.ncls;
-      const long long b = 2 * pair + s;
-      if (b < p.B) {
-        float acc = p.fc_b[k];
-        for (int ch = 0; ch < kFC; ++ch) acc = fmaf(s_pool[s * kFC + ch], p.fc_w[ch * p.ncls + k], acc);
-        p.logits[b * p.ncls + k] = acc;
-      }
-    }
-    // the next pair's feature load overwrites s_feat / s_pool only after this barrier
-    __syncthreads();
   }
   tc_fence_before();
   __syncthreads();
