@@ -77,25 +77,32 @@ struct FusedParams {
 // (left/right border, columns past the layer) depend only on the warp's segment j and are patched
 // with warp-uniform predicated moves.  `par` points at this channel's [w0..w8, bias, border] column.
 template <int WIN, bool BORDER>
-__device__ __forceinline__ void dw_seg(uint32_t taddr, int j, int i, int HIN, const float* par, unsigned char* dst,
-                                       float (&P)[8], float (&R)[8]) {
+__device__ __forceinline__ void dw_seg(uint32_t taddr, int j, int i, int HIN, const float4* par, unsigned char* dst,
+                                       V (&P)[4], V (&R)[4]) {
   constexpr int WL = BORDER ? WIN + 2 : WIN;
   constexpr int JL = (WL - 1) / 8, KL = WL - 8 * JL;  // segment and v-index of the layer's last column
-  constexpr int RO = BORDER ? 2 : 3;                   // v[k] (layer column 8j-1+k) = raw[k + RO]; raw[0] = column 8j-4
   const int HL = BORDER ? HIN + 2 : HIN;
   const bool flush = i >= HL;
   const bool cst = BORDER && !flush && (i == 0 || i == HL - 1);
-  const float bias = par[9 * kFC], bval = BORDER ? par[10 * kFC] : 0.f;
+  const float4 w0 = par[0], w1 = par[1], w2 = par[2];  // taps 0..8, input bias, border constant
+  const float bias = w2.y, bval = BORDER ? w2.z : 0.f;
   const float m = (flush || cst) ? 0.f : 1.f;
   const float be = flush ? 0.f : (cst ? bval : bias);
   const float edge = flush ? 0.f : bval;
+  // v[k] = layer column 8j-1+k, k = 0..9, kept as aligned pairs E[p] = (v[2p], v[2p+1]); the load
+  // starts two columns left of v[0] so that the pairs fall on even registers
   float v[10];
   {
     float raw[16];
     tc_ld16(taddr, raw);
     tc_wait_ld();
+    const V m2 = fsplat(m), be2 = fsplat(be);
 #pragma unroll
-    for (int k = 0; k < 10; ++k) v[k] = fmaxf(fmaf(raw[k + RO], m, be), 0.f);
+    for (int pp = 0; pp < 5; ++pp) {
+      const V a = ffma(make_float2(raw[2 * pp + 2], raw[2 * pp + 3]), m2, be2);
+      v[2 * pp] = fmaxf(a.x, 0.f);
+      v[2 * pp + 1] = fmaxf(a.y, 0.f);
+    }
   }
   if (j == 0) {
     v[0] = 0.f;
@@ -110,16 +117,18 @@ __device__ __forceinline__ void dw_seg(uint32_t taddr, int j, int i, int HIN, co
 #pragma unroll
     for (int k = 0; k < 10; ++k) v[k] = 0.f;
   }
-  float w[9];
-#pragma unroll
-  for (int k = 0; k < 9; ++k) w[k] = par[k * kFC];
   const bool st = i >= 1;
 #pragma unroll
-  for (int x = 0; x < 8; ++x) {
-    const float o = fmaf(w[8], v[x + 2], fmaf(w[7], v[x + 1], fmaf(w[6], v[x], P[x])));
-    P[x] = fmaf(w[5], v[x + 2], fmaf(w[4], v[x + 1], fmaf(w[3], v[x], R[x])));
-    R[x] = fmaf(w[2], v[x + 2], fmaf(w[1], v[x + 1], w[0] * v[x]));
-    if (st) *reinterpret_cast<float*>(dst + x * 16) = to_tf32(o);
+  for (int pp = 0; pp < 4; ++pp) {  // output pixels 2pp, 2pp+1 of the segment, packed f32x2
+    const V e0 = make_float2(v[2 * pp], v[2 * pp + 1]), od = make_float2(v[2 * pp + 1], v[2 * pp + 2]);
+    const V e1 = make_float2(v[2 * pp + 2], v[2 * pp + 3]);
+    const V o = ffma(fsplat(w2.x), e1, ffma(fsplat(w1.w), od, ffma(fsplat(w1.z), e0, P[pp])));
+    P[pp] = ffma(fsplat(w1.y), e1, ffma(fsplat(w1.x), od, ffma(fsplat(w0.w), e0, R[pp])));
+    R[pp] = ffma(fsplat(w0.z), e1, ffma(fsplat(w0.y), od, fmul(fsplat(w0.x), e0)));
+    if (st) {  // tf32 round-to-nearest (ties away) = add half an ulp of the 10-bit mantissa; the MMA drops the low 13 bits
+      *reinterpret_cast<uint32_t*>(dst + (2 * pp) * 16) = __float_as_uint(o.x) + 0x1000u;
+      *reinterpret_cast<uint32_t*>(dst + (2 * pp + 1) * 16) = __float_as_uint(o.y) + 0x1000u;
+    }
   }
 }
 
@@ -138,8 +147,8 @@ struct FusedLayout {
   static constexpr int off_ap = 8 * kSboA1;
   static constexpr int off_b1 = kAImgBytes;
   static constexpr int off_bp = off_b1 + 2 * b1_stride;
-  static constexpr int off_par = off_bp + 8 * bp_stride;          // [4][11][64] depthwise taps, input bias, border
-  static constexpr int off_pool = off_par + 4 * 11 * kFC * 4;     // [3][2][64] pooling partials
+  static constexpr int off_par = off_bp + 8 * bp_stride;          // [4][64][12] depthwise taps, input bias, border, pad
+  static constexpr int off_pool = off_par + 4 * kFC * 12 * 4;     // [3][2][64] pooling partials
   static constexpr int off_feat = off_pool + 3 * 2 * kFC * 4;
   // zero-padded feature map of one clip: rows -2 .. T+1
   static constexpr size_t feat_floats(int T) { return (size_t)(T + 4) * FP; }
@@ -227,7 +236,7 @@ __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedPa
   __shared__ uint32_t s_tmem;
   float* s_feat = reinterpret_cast<float*>(smem + L::off_feat);  // [2][(T + 4) * FP], zero padded, tf32-rounded
   float* s_pool = reinterpret_cast<float*>(smem + L::off_pool);  // [3][2][64]
-  float* s_par = reinterpret_cast<float*>(smem + L::off_par);    // [4][11][64]
+  float* s_par = reinterpret_cast<float*>(smem + L::off_par);    // [4][64][12]
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t barO = smem_u32(&s_bar[0]), barE = smem_u32(&s_bar[1]);
@@ -253,9 +262,10 @@ __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedPa
     for (int i = tid; i < nz; i += kFThreads) z[i] = make_uint4(0, 0, 0, 0);
   }
   __syncthreads();
-  for (int i = tid; i < 4 * 11 * kFC; i += kFThreads) {
-    const int l = i / (11 * kFC), k = (i / kFC) % 11, ch = i % kFC;
-    s_par[i] = k < 9 ? p.dw_w[(l * 9 + k) * kFC + ch] : (k == 9 ? p.act_bias[l * kFC + ch] : p.border[l * kFC + ch]);
+  for (int i = tid; i < 4 * kFC * 12; i += kFThreads) {
+    const int l = i / (12 * kFC), ch = (i / 12) % kFC, k = i % 12;
+    s_par[i] = k < 9 ? p.dw_w[(l * 9 + k) * kFC + ch]
+                     : (k == 9 ? p.act_bias[l * kFC + ch] : (k == 10 ? p.border[l * kFC + ch] : 0.f));
   }
   fence_proxy_async();
   tc_fence_before();
@@ -287,9 +297,9 @@ __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedPa
     // TMEM: this warp's lane quarter; ring row slot s of layer l starts at column l*64 + s*32 + 8;
     // a 16-column load from (segment start - 4) covers the segment and its halo
     const uint32_t my_tmem = tmem + ((uint32_t)(q * 32) << 16);
-    const uint32_t my_ld = my_tmem + 8u + (uint32_t)(8 * j) - 4u;
+    const uint32_t my_ld = my_tmem + 8u + (uint32_t)(8 * j);  // + (-3 | -4): see dw_seg
     unsigned char* my_dst = smem + L::off_bp + sl * L::bp_stride + j * kSboBp + (c >> 2) * kLboB + (c & 3) * 4;
-    const float* my_par = s_par + c;
+    const float4* my_par = reinterpret_cast<const float4*>(s_par) + c * 3;
     // conv1 im2col item of this thread: slot, 16-byte K-chunk (4 taps), pixel columns xg, xg+7, xg+14
     const bool im_on = tid < 350;
     const int im_s = tid / 175, im_kc = (tid % 175) % 25, im_xg = (tid % 175) / 25;
@@ -319,11 +329,11 @@ __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedPa
         }
       }
       float psum = 0.f;
-      float P[4][8], R[4][8];
+      V P[4][4], R[4][4];
 #pragma unroll
       for (int l = 0; l < 4; ++l)
 #pragma unroll
-        for (int x = 0; x < 8; ++x) P[l][x] = R[l][x] = 0.f;
+        for (int x = 0; x < 4; ++x) P[l][x] = R[l][x] = fsplat(0.f);
       __syncthreads();
 
       for (int t = 0; t < nsteps; ++t) {
@@ -336,11 +346,11 @@ __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedPa
         if (seg_on) {
           int i = t - 2;
           if (i >= 0 && i <= H0)
-            dw_seg<W0, false>(my_ld + 0 * kRingCols + (uint32_t)((i & 1) * 32), j, i, H0, my_par + 0 * 11 * kFC,
+            dw_seg<W0, false>(my_ld - 3u + 0 * kRingCols + (uint32_t)((i & 1) * 32), j, i, H0, my_par + 0 * 3 * kFC,
                               my_dst + 0 * 2 * L::bp_stride, P[0], R[0]);
           i = t - 5;
           if (i >= 0 && i <= H0 + 4)
-            dw_seg<W0 + 2, true>(my_ld + 2 * kRingCols + (uint32_t)(((i - 1) & 1) * 32), j, i, H0 + 2, my_par + 2 * 11 * kFC,
+            dw_seg<W0 + 2, true>(my_ld - 4u + 2 * kRingCols + (uint32_t)(((i - 1) & 1) * 32), j, i, H0 + 2, my_par + 2 * 3 * kFC,
                                  my_dst + 2 * 2 * L::bp_stride, P[2], R[2]);
         }
         fence_proxy_async();
@@ -363,11 +373,11 @@ __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedPa
         if (seg_on) {
           int i = t - 3;
           if (i >= 0 && i <= H0 + 2)
-            dw_seg<W0, true>(my_ld + 1 * kRingCols + (uint32_t)(((i - 1) & 1) * 32), j, i, H0, my_par + 1 * 11 * kFC,
+            dw_seg<W0, true>(my_ld - 4u + 1 * kRingCols + (uint32_t)(((i - 1) & 1) * 32), j, i, H0, my_par + 1 * 3 * kFC,
                              my_dst + 1 * 2 * L::bp_stride, P[1], R[1]);
           i = t - 6;
           if (i >= 0 && i <= H0 + 6)
-            dw_seg<W0 + 4, true>(my_ld + 3 * kRingCols + (uint32_t)(((i - 1) & 1) * 32), j, i, H0 + 4, my_par + 3 * 11 * kFC,
+            dw_seg<W0 + 4, true>(my_ld - 4u + 3 * kRingCols + (uint32_t)(((i - 1) & 1) * 32), j, i, H0 + 4, my_par + 3 * 3 * kFC,
                                  my_dst + 3 * 2 * L::bp_stride, P[3], R[3]);
           const int r = t - 8;
           if (r >= 0 && r < H3) {  // pooling of the last block's row r (interior pixels; the border is added at the end)
