@@ -215,6 +215,55 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_value = world * Be * args.steps / float(te.item())
+    # ---- secondary (not the headline): BASELINE configs[0]/[2] shape, PCM -> MFCC -> DS-CNN logits ----
+    extra = None
+    try:
+        from kws_b200.models import DepthwiseSeparableConv
+        from kws_b200.pipeline import KeywordSpotter
+        torch.manual_seed(0)
+        model = DepthwiseSeparableConv().to(dev)
+        with torch.no_grad():
+            for prm in model.parameters():
+                if prm.dim() == 1:
+                    prm.normal_(0, 0.1)
+        ks = KeywordSpotter(model, AudioConfig(), numcep=NUMCEP, nfilt=NFILT, device=dev)
+        Bm = min(B, 16384)
+        feats = step()[:Bm].unsqueeze(1).contiguous()
+
+        def timed(fn, reps=5):
+            for _ in range(2):
+                fn()
+            barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(reps):
+                fn()
+            e1.record()
+            barrier()
+            t_ms = torch.tensor([e0.elapsed_time(e1) / reps], device=dev, dtype=torch.float64)
+            if world > 1:
+                dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
+            return float(t_ms.item())
+
+        l1 = model.launch_count()
+        ms_model = timed(lambda: model(feats))
+        ms_e2l = timed(lambda: ks(pcm[:Bm]))
+        tf32_peak = None
+        try:
+            tf32_peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops"]) / 2.0
+        except Exception:
+            pass
+        model_cps = world * Bm / (ms_model * 1e-3)
+        extra = {"workload": "mfcc40 + reference DS-CNN (64 ch, 4 blocks), %d clips/GPU" % Bm,
+                 "model_forward_clips_per_s": model_cps,
+                 "pcm_to_logits_clips_per_s": world * Bm / (ms_e2l * 1e-3),
+                 "model_kernel": "dscnn_fused_kernel (tcgen05 kind::tf32)",
+                 "model_gemm_flop_per_clip": 45.4e6,
+                 "model_tensor_frac_of_tf32_peak": (model_cps / world * 45.4e6 / (tf32_peak * 1e12)) if tf32_peak else None,
+                 "tf32_peak_tflops": tf32_peak, "tf32_peak_source": "MEASURED_PEAKS.json bf16_tflops / 2",
+                 "model_launches": int(model.launch_count() - l1)}
+    except Exception as e:  # the headline line must still print
+        extra = {"error": repr(e)}
     clocks = sampler.stop() if sampler else None
 
     if rank == 0:
@@ -245,6 +294,7 @@ def run_ours(args):
                     "d2h_bytes_per_step": Be * NFRAMES * NUMCEP * 4},
             "gpu_launches": int(launches),
             "clocks": clocks,
+            "extra": extra,
         }
         print(json.dumps(line), flush=True)
     if world > 1:

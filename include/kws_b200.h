@@ -134,6 +134,22 @@ int kws_model_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t
 /* bytes of scratch the forward needs for batch B (allocated lazily on the handle) */
 int64_t kws_model_workspace_bytes(kws_handle_t h, int64_t B, int64_t T, int64_t F);
 
+/* ---- training step: replaces the body of KWSTrainer.train_epoch (kws/libs/training.py:285-297;
+ * train.py:39-49): forward, CrossEntropyLoss (mean), backward, Adam.  Reference network only
+ * (64 channels, 4 blocks).  Parameters / gradients / Adam moments are caller-owned flat float32
+ * device buffers in state_dict order (models.py:135-144, torch layouts), kws_train_num_params()
+ * elements each, so the data-parallel exchange is one allreduce of the gradient buffer issued by
+ * the caller between the two calls (grad_scale = 1/world_size folds the mean into Adam). ------- */
+int64_t kws_train_num_params(kws_handle_t h);
+/* feats_dev [B,1,T,F] float32, labels_dev [B] int64 -> grads_dev (overwritten), loss_dev[1] (mean CE),
+ * logits_out_dev [B,num_classes] or NULL */
+int kws_train_forward_backward(kws_handle_t h, const float* params_dev, const float* feats_dev,
+                               const int64_t* labels_dev, int64_t B, int64_t T, int64_t F, float* grads_dev,
+                               float* loss_dev, float* logits_out_dev, void* stream);
+/* torch.optim.Adam (weight_decay 0, amsgrad off) update number `step` (1-based) on the flat buffers */
+int kws_train_adam(kws_handle_t h, float* params_dev, const float* grads_dev, float* m_dev, float* v_dev, int64_t n,
+                   int64_t step, float lr, float beta1, float beta2, float eps, float grad_scale, void* stream);
+
 /* ---- fused path: PCM -> logits ------------------------------------------------------ */
 int kws_pcm_to_logits(kws_handle_t h, const float* pcm_dev, int64_t B, int64_t N,
                       int64_t pcm_stride, float* logits_dev, void* stream);

@@ -39,7 +39,7 @@ class FeatureConfig(C.Structure):
     ]
 
 
-_vp, _i64, _i32, _dbl = C.c_void_p, C.c_int64, C.c_int, C.c_double
+_vp, _i64, _i32, _dbl, _f32 = C.c_void_p, C.c_int64, C.c_int, C.c_double, C.c_float
 
 # name -> (restype, argtypes); every symbol include/kws_b200.h declares
 SIGNATURES = {
@@ -68,6 +68,9 @@ SIGNATURES = {
     "kws_model_load_tensor": (_i32, [_vp, C.c_char_p, _vp, C.POINTER(_i64), _i32]),
     "kws_model_finalize": (_i32, [_vp]),
     "kws_model_set_path": (_i32, [_vp, _i32]),
+    "kws_train_num_params": (_i64, [_vp]),
+    "kws_train_forward_backward": (_i32, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _vp, _vp, _vp, _vp]),
+    "kws_train_adam": (_i32, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _f32, _f32, _f32, _f32, _f32, _vp]),
     "kws_model_forward": (_i32, [_vp, _vp, _i64, _i64, _i64, _vp, _vp]),
     "kws_model_workspace_bytes": (_i64, [_vp, _i64, _i64, _i64]),
     "kws_pcm_to_logits": (_i32, [_vp, _vp, _i64, _i64, _i64, _vp, _vp]),

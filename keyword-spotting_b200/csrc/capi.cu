@@ -78,6 +78,7 @@ int kws_destroy(kws_handle_t h) {
     if (h->d_stage_out[i]) cudaFree(h->d_stage_out[i]);
   }
   if (h->d_feat_tmp) cudaFree(h->d_feat_tmp);
+  if (h->train.base) cudaFree(h->train.base);
   delete h;
   return KWS_OK;
 }

@@ -82,6 +82,18 @@ struct ModelWeights {
   size_t ws_bytes = 0;
 };
 
+// ---- training step workspace (train.cu) -------------------------------------------------
+struct TrainWorkspace {
+  void* base = nullptr;
+  size_t bytes = 0;
+  float* L[5] = {};      // saved activations: conv1 output and the four block outputs (post-ReLU), NHWC
+  float* D[4] = {};      // saved depthwise outputs (pointwise inputs); overwritten by their gradients
+  float* dX[2] = {};     // ping-pong gradient w.r.t. a block input
+  float* pooled = nullptr;   // [B, C]
+  float* dpooled = nullptr;  // [B, C]
+  float* logits = nullptr;   // [B, K]
+};
+
 }  // namespace kws
 
 struct kws_handle_s {
@@ -98,6 +110,7 @@ struct kws_handle_s {
   size_t stage_in_bytes = 0, stage_out_bytes = 0;
   float* d_feat_tmp = nullptr;   // features scratch for the unfused pcm->logits path
   size_t feat_tmp_bytes = 0;
+  kws::TrainWorkspace train;
 };
 
 namespace kws {
@@ -114,6 +127,9 @@ int launch_dscnn_fused(kws_handle_t h, const float* feats_dev, int64_t B, int64_
 int build_fused_model(ModelWeights& m, const std::vector<float>& conv1_w, const std::vector<float>& conv1_b,
                       const std::vector<const float*>& dw_w, const std::vector<const float*>& dw_b,
                       const std::vector<const float*>& pw_w, const std::vector<const float*>& pw_b);
+// model.cu: layered forward that keeps every activation (training), logits/pooled into the workspace
+int train_forward_layers(kws_handle_t h, const float* feats_dev, int64_t B, int T, int F, TrainWorkspace& w,
+                         cudaStream_t st);
 // tables.cu
 int build_feature_tables(kws_handle_t h, const kws_feature_config* cfg);
 void free_feature_tables(FeatureTables& t);

@@ -61,7 +61,8 @@ constexpr int kBlkPix = 8;
 __global__ void dsblock_kernel(const float* __restrict__ in, float* __restrict__ out,
                                const float* __restrict__ dw_w /*[9][C]*/,
                                const float* __restrict__ dw_b, const float* __restrict__ pw_w /*[C][C]*/,
-                               const float* __restrict__ pw_b, long long B, int H, int W, int C) {
+                               const float* __restrict__ pw_b, long long B, int H, int W, int C,
+                               float* __restrict__ dsave /* [B,H,W,C] depthwise output for training, or null */) {
   extern __shared__ __align__(16) float s_d[];  // [kBlkPix][C]
   const int cq = C / 4;
   const int Ho = H + 2, Wo = W + 2;
@@ -94,6 +95,7 @@ __global__ void dsblock_kernel(const float* __restrict__ in, float* __restrict__
               d.z = fmaf(x.z, k.z, d.z); d.w = fmaf(x.w, k.w, d.w);
             }
           }
+          if (dsave) reinterpret_cast<float4*>(dsave + ((b * H + h) * W + wc) * C)[q] = d;
         }
       }
       reinterpret_cast<float4*>(s_d + pl * C)[q] = d;
@@ -126,7 +128,8 @@ __global__ void dsblock_kernel(const float* __restrict__ in, float* __restrict__
 // adaptive_avg_pool2d(1,1) + fc: one CTA per clip
 __global__ void pool_fc_kernel(const float* __restrict__ in, float* __restrict__ logits,
                                const float* __restrict__ fc_w /*[C][ncls]*/,
-                               const float* __restrict__ fc_b, long long B, int HW, int C, int ncls) {
+                               const float* __restrict__ fc_b, long long B, int HW, int C, int ncls,
+                               float* __restrict__ pooled_out /* [B,C] for training, or null */) {
   extern __shared__ __align__(16) float s_pool[];  // [C]
   for (long long b = blockIdx.x; b < B; b += gridDim.x) {
     __syncthreads();
@@ -135,6 +138,7 @@ __global__ void pool_fc_kernel(const float* __restrict__ in, float* __restrict__
       float s = 0.f;
       for (int p = 0; p < HW; ++p) s += x[(size_t)p * C + c];
       s_pool[c] = s / (float)HW;
+      if (pooled_out) pooled_out[b * C + c] = s_pool[c];
     }
     __syncthreads();
     for (int k = threadIdx.x; k < ncls; k += blockDim.x) {
@@ -167,6 +171,39 @@ static void model_free(ModelWeights& m) {
 }
 
 constexpr int64_t kModelChunk = 2048;  // clips per pass through the ping-pong workspace
+
+int train_forward_layers(kws_handle_t h, const float* feats_dev, int64_t B, int T, int F, TrainWorkspace& w,
+                         cudaStream_t st) {
+  ModelWeights& m = h->model;
+  const int C = m.channels, nb = m.num_blocks, K = m.num_classes, cq = C / 4;
+  int H1, W1, Hl, Wl;
+  conv_out_hw(T, F, nb, &H1, &W1, &Hl, &Wl);
+  {
+    const long long total = B * H1 * W1 * (long long)cq;
+    long long g = (total + 255) / 256;
+    if (g > h->sm_count * 16LL) g = h->sm_count * 16LL;
+    conv1_relu_kernel<<<(unsigned)g, 256, 0, st>>>(feats_dev, w.L[0], m.d_conv1_w, m.d_conv1_b, B, T, F, H1, W1, C);
+    KWS_CHECK_LAUNCH(h);
+  }
+  int H = H1, W = W1;
+  for (int i = 0; i < nb; ++i) {
+    const long long npix = B * (long long)(H + 2) * (W + 2);
+    long long g = (npix + kBlkPix - 1) / kBlkPix;
+    if (g > h->sm_count * 16LL) g = h->sm_count * 16LL;
+    int threads = kBlkPix * cq;
+    if (threads > 512) threads = 512;
+    dsblock_kernel<<<(unsigned)g, threads, kBlkPix * C * 4, st>>>(
+        w.L[i], w.L[i + 1], m.d_dw_w + (size_t)i * 9 * C, m.d_dw_b + (size_t)i * C, m.d_pw_w + (size_t)i * C * C,
+        m.d_pw_b + (size_t)i * C, B, H, W, C, w.D[i]);
+    KWS_CHECK_LAUNCH(h);
+    H += 2;
+    W += 2;
+  }
+  long long g = B < h->sm_count * 8LL ? B : h->sm_count * 8LL;
+  pool_fc_kernel<<<(unsigned)g, 128, C * 4, st>>>(w.L[nb], w.logits, m.d_fc_w, m.d_fc_b, B, H * W, C, K, w.pooled);
+  KWS_CHECK_LAUNCH(h);
+  return KWS_OK;
+}
 
 }  // namespace kws
 
@@ -365,7 +402,7 @@ int kws_model_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t
       if (threads > 512) threads = 512;
       dsblock_kernel<<<(unsigned)g, threads, kBlkPix * C * 4, st>>>(
           cur, nxt, m.d_dw_w + (size_t)i * 9 * C, m.d_dw_b + (size_t)i * C, m.d_pw_w + (size_t)i * C * C,
-          m.d_pw_b + (size_t)i * C, nbat, H, W, C);
+          m.d_pw_b + (size_t)i * C, nbat, H, W, C, nullptr);
       KWS_CHECK_LAUNCH(h);
       float* t = cur; cur = nxt; nxt = t;
       H += 2; W += 2;
@@ -373,7 +410,7 @@ int kws_model_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t
     {
       long long g = nbat < h->sm_count * 8LL ? nbat : h->sm_count * 8LL;
       pool_fc_kernel<<<(unsigned)g, 128, C * 4, st>>>(cur, logits_dev + b0 * K, m.d_fc_w, m.d_fc_b, nbat,
-                                                      H * W, C, K);
+                                                      H * W, C, K, nullptr);
       KWS_CHECK_LAUNCH(h);
     }
   }
