@@ -131,8 +131,23 @@ int kws_model_set_path(kws_handle_t h, int path);
 /* feats_dev [B,1,T,F] float32 contiguous -> logits_dev [B,num_classes] */
 int kws_model_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t T, int64_t F,
                       float* logits_dev, void* stream);
+/* optional epilogue: row-wise softmax of [B,K] logits (the reference's torch path never applies one:
+ * logits go to CrossEntropyLoss / torch.max, kws/libs/training.py:293,301) */
+int kws_softmax(kws_handle_t h, const float* logits_dev, int64_t B, int64_t K, float* out_dev, void* stream);
 /* bytes of scratch the forward needs for batch B (allocated lazily on the handle) */
 int64_t kws_model_workspace_bytes(kws_handle_t h, int64_t B, int64_t T, int64_t F);
+
+/* ---- CRNN / GRU model: BASELINE config 4 ("log-mel + CRNN/GRU").  The reference has no recurrent model;
+ * this is an extension in its idiom (a KeywordSpottingModel subclass, kws/libs/models.py:13-72): the
+ * reference's conv1 (10x10 s2 p2 + ReLU, models.py:135,170) -> torch.nn.GRU(conv_channels * W1, hidden,
+ * num_layers, batch_first) over the time axis -> fc on the last hidden state.  state_dict keys:
+ * conv1.{weight,bias}, gru.{weight_ih,weight_hh,bias_ih,bias_hh}_l{k}, fc.{weight,bias}. -------------- */
+int kws_crnn_create(kws_handle_t h, int num_classes, int conv_channels, int hidden, int num_layers, int n_features);
+int kws_crnn_load_tensor(kws_handle_t h, const char* name, const float* data_host, const int64_t* shape, int ndim);
+int kws_crnn_finalize(kws_handle_t h);
+/* feats_dev [B,1,T,F] float32 (e.g. kws_logfbank output) -> logits_dev [B,num_classes] */
+int kws_crnn_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t T, int64_t F, float* logits_dev,
+                     void* stream);
 
 /* ---- training step: replaces the body of KWSTrainer.train_epoch (kws/libs/training.py:285-297;
  * train.py:39-49): forward, CrossEntropyLoss (mean), backward, Adam.  Reference network only

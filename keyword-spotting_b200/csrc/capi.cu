@@ -66,12 +66,14 @@ int kws_create(int device, kws_handle_t* out) {
 }
 
 void kws_model_free_internal(kws_handle_t h);  // model.cu
+void kws_crnn_free_internal(kws_handle_t h);   // crnn.cu
 
 int kws_destroy(kws_handle_t h) {
   if (!h) return KWS_OK;
   cudaSetDevice(h->device);
   free_feature_tables(h->feat);
   kws_model_free_internal(h);
+  kws_crnn_free_internal(h);
   for (int i = 0; i < 2; ++i) {
     if (h->s_copy[i]) cudaStreamDestroy(h->s_copy[i]);
     if (h->d_stage_in[i]) cudaFree(h->d_stage_in[i]);

@@ -111,6 +111,7 @@ struct kws_handle_s {
   float* d_feat_tmp = nullptr;   // features scratch for the unfused pcm->logits path
   size_t feat_tmp_bytes = 0;
   kws::TrainWorkspace train;
+  void* crnn = nullptr;          // kws::CrnnWeights, owned by crnn.cu
 };
 
 namespace kws {
@@ -130,6 +131,9 @@ int build_fused_model(ModelWeights& m, const std::vector<float>& conv1_w, const 
 // model.cu: layered forward that keeps every activation (training), logits/pooled into the workspace
 int train_forward_layers(kws_handle_t h, const float* feats_dev, int64_t B, int T, int F, TrainWorkspace& w,
                          cudaStream_t st);
+// model.cu: conv 10x10 s2 p2 (one input channel) + ReLU, NHWC output [B, H1, W1, C]
+int launch_conv1_relu(kws_handle_t h, const float* in, float* out, const float* w_packed, const float* bias, int64_t B,
+                      int T, int F, int H1, int W1, int C, cudaStream_t st);
 // tables.cu
 int build_feature_tables(kws_handle_t h, const kws_feature_config* cfg);
 void free_feature_tables(FeatureTables& t);

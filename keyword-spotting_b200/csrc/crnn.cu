@@ -1,0 +1,354 @@
+// CRNN / GRU keyword-spotting model (SURVEY.md a-X3; BASELINE config 4 "log-mel + CRNN/GRU").
+// The reference has NO recurrent model (grep GRU|LSTM|RNN over its tree returns nothing), so this is
+// an extension authored in the reference's idiom -- a KeywordSpottingModel subclass
+// (kws/libs/models.py:13-72) whose front end is the reference's own first layer:
+//     conv1 10x10 s2 p2 (1 -> Cc) + ReLU          (models.py:135,170)
+//     -> per time step t the feature vector x_t[c * W1 + w] = conv[c, t, w]   (I = Cc * W1)
+//     -> num_layers x torch.nn.GRU(I, H, batch_first=True) semantics, h_0 = 0
+//     -> fc(h_T)                                   (models.py:144,181)
+// Parity is against the builder's PyTorch definition (oracle/crnn_ref.py); the reference pins nothing.
+//
+// Kernels: conv front end = conv1_relu_kernel of model.cu (NHWC, so x_t is [w][c]-ordered and W_ih's
+// columns are permuted to match at finalize); gru_inproj_kernel = the time-parallel half of the GRU, one
+// [B*T', I] x [I, 3H] GEMM (+ b_ih) -- shared-memory tiled fp32; gru_recurrent_kernel = the sequential
+// half: W_hh resident in shared memory, a tile of clips per CTA, hidden state in shared memory, gates
+// in registers (r, z sigmoid; n = tanh(xn + r * (W_hn h + b_hn)); h' = (1 - z) n + z h).
+#include <cuda_runtime.h>
+
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+
+namespace kws {
+
+struct CrnnWeights {
+  bool created = false, finalized = false;
+  int num_classes = 0, cc = 0, hidden = 0, layers = 0, w1 = 0;  // w1: conv output width the GRU was sized for
+  std::vector<std::string> names;
+  std::vector<std::vector<float>> host;
+  std::vector<bool> loaded;
+  float* d_conv_w = nullptr;   // [100][Cc]
+  float* d_conv_b = nullptr;   // [Cc]
+  float* d_wih[2] = {};        // [I][3H]  (k-major; layer 0 columns in [w][c] order)
+  float* d_whh[2] = {};        // [H][3H]  (k-major)
+  float* d_bih[2] = {};        // [3H]
+  float* d_bhh[2] = {};        // [3H]
+  float* d_fc_w = nullptr;     // [H][K]
+  float* d_fc_b = nullptr;     // [K]
+  void* d_ws = nullptr;
+  size_t ws_bytes = 0;
+};
+
+// C[M, N] = A[M, K] * Bm[K, N] + bias[N]; 64 x 64 tile, 256 threads, 4 x 4 outputs per thread
+__global__ void __launch_bounds__(256) gru_inproj_kernel(const float* __restrict__ A, const float* __restrict__ Bm,
+                                                         const float* __restrict__ bias, float* __restrict__ Cout,
+                                                         long long M, int N, int K) {
+  __shared__ float sA[16][64 + 4];
+  __shared__ __align__(16) float sB[16][64];
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const long long m0 = (long long)blockIdx.x * 64;
+  const int n0 = blockIdx.y * 64;
+  float acc[4][4] = {};
+  for (int k0 = 0; k0 < K; k0 += 16) {
+    for (int i = tid; i < 64 * 16; i += 256) {
+      const int r = i >> 4, kk = i & 15;
+      const long long m = m0 + r;
+      sA[kk][r] = (m < M && k0 + kk < K) ? A[m * K + k0 + kk] : 0.f;
+    }
+    for (int i = tid; i < 16 * 64; i += 256) {
+      const int kk = i >> 6, c = i & 63;
+      sB[kk][c] = (k0 + kk < K && n0 + c < N) ? Bm[(size_t)(k0 + kk) * N + n0 + c] : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < 16; ++kk) {
+      float a[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) a[i] = sA[kk][ty * 4 + i];
+      const float4 b = *reinterpret_cast<const float4*>(&sB[kk][tx * 4]);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        acc[i][0] = fmaf(a[i], b.x, acc[i][0]);
+        acc[i][1] = fmaf(a[i], b.y, acc[i][1]);
+        acc[i][2] = fmaf(a[i], b.z, acc[i][2]);
+        acc[i][3] = fmaf(a[i], b.w, acc[i][3]);
+      }
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const long long m = m0 + ty * 4 + i;
+    if (m >= M) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int n = n0 + tx * 4 + j;
+      if (n < N) Cout[m * N + n] = acc[i][j] + bias[n];
+    }
+  }
+}
+
+// Sequential half of one GRU layer.  xp [B, T, 3H] = W_ih x_t + b_ih (gate order r, z, n like torch).
+// CTA = NB clips; thread = (clip group, hidden unit j); W_hh [H][3H] and h [NB][H] in shared memory.
+// hseq (nullable) [B, T, H] receives every h_t (input of the next layer); hlast [B, H] the final state.
+constexpr int kGruNB = 16;
+__global__ void __launch_bounds__(256) gru_recurrent_kernel(const float* __restrict__ xp, const float* __restrict__ whh,
+                                                            const float* __restrict__ bhh, float* __restrict__ hseq,
+                                                            float* __restrict__ hlast, long long B, int T, int H) {
+  extern __shared__ __align__(16) float sm_gru[];
+  float* s_w = sm_gru;                     // [H][3H]
+  float* s_h = s_w + (size_t)H * 3 * H;    // [2][NB][H]
+  const int tid = threadIdx.x;
+  for (int i = tid; i < H * 3 * H; i += 256) s_w[i] = whh[i];
+  for (int i = tid; i < 2 * kGruNB * H; i += 256) s_h[i] = 0.f;
+  __syncthreads();
+  const long long b0 = (long long)blockIdx.x * kGruNB;
+  const int nitems = kGruNB * H;           // (clip, unit) pairs of this CTA
+  for (int t = 0; t < T; ++t) {
+    const float* hc = s_h + (t & 1) * kGruNB * H;
+    float* hn = s_h + ((t + 1) & 1) * kGruNB * H;
+    for (int it = tid; it < nitems; it += 256) {
+      const int cb = it / H, j = it - cb * H;
+      const long long b = b0 + cb;
+      if (b >= B) continue;
+      float ar = bhh[j], az = bhh[H + j], an = bhh[2 * H + j];
+      const float* hrow = hc + cb * H;
+      for (int k = 0; k < H; ++k) {
+        const float hv = hrow[k];
+        const float* wr = s_w + (size_t)k * 3 * H;
+        ar = fmaf(hv, wr[j], ar);
+        az = fmaf(hv, wr[H + j], az);
+        an = fmaf(hv, wr[2 * H + j], an);
+      }
+      const float* x = xp + (b * T + t) * 3 * H;
+      const float r = 1.f / (1.f + expf(-(x[j] + ar)));
+      const float z = 1.f / (1.f + expf(-(x[H + j] + az)));
+      const float n = tanhf(x[2 * H + j] + r * an);
+      const float hnew = (1.f - z) * n + z * hrow[j];
+      hn[cb * H + j] = hnew;
+      if (hseq) hseq[(b * T + t) * H + j] = hnew;
+      if (t == T - 1) hlast[b * H + j] = hnew;
+    }
+    __syncthreads();
+  }
+}
+
+__global__ void crnn_fc_kernel(const float* __restrict__ h, const float* __restrict__ w /*[H][K]*/,
+                               const float* __restrict__ bias, float* __restrict__ logits, long long B, int H, int K) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < B * K; i += (long long)gridDim.x * blockDim.x) {
+    const long long b = i / K;
+    const int k = (int)(i - b * K);
+    float acc = bias[k];
+    for (int c = 0; c < H; ++c) acc = fmaf(h[b * H + c], w[c * K + k], acc);
+    logits[i] = acc;
+  }
+}
+
+
+static CrnnWeights* crnn_of(kws_handle_t h) { return reinterpret_cast<CrnnWeights*>(h->crnn); }
+
+static void crnn_free(CrnnWeights* m) {
+  if (!m) return;
+  void* ptrs[] = {m->d_conv_w, m->d_conv_b, m->d_wih[0], m->d_wih[1], m->d_whh[0], m->d_whh[1], m->d_bih[0],
+                  m->d_bih[1],  m->d_bhh[0], m->d_bhh[1], m->d_fc_w,   m->d_fc_b,   m->d_ws};
+  for (void* p : ptrs)
+    if (p) cudaFree(p);
+  delete m;
+}
+
+static int crnn_slot(const CrnnWeights& m, const std::string& n) {
+  for (size_t i = 0; i < m.names.size(); ++i)
+    if (m.names[i] == n) return (int)i;
+  return -1;
+}
+
+}  // namespace kws
+
+using namespace kws;
+
+extern "C" {
+
+void kws_crnn_free_internal(kws_handle_t h) {
+  if (h && h->crnn) {
+    crnn_free(crnn_of(h));
+    h->crnn = nullptr;
+  }
+}
+
+int kws_crnn_create(kws_handle_t h, int num_classes, int conv_channels, int hidden, int num_layers, int n_features) {
+  if (!h) return fail(KWS_ERR_INVALID, "null handle");
+  if (num_classes < 1 || conv_channels < 4 || conv_channels % 4 != 0 || hidden < 1 || hidden > 128 || num_layers < 1 ||
+      num_layers > 2 || n_features < 6)
+    return fail(KWS_ERR_INVALID, "crnn: need conv_channels a multiple of 4, 1<=hidden<=128, 1<=num_layers<=2, n_features>=6");
+  KWS_CUDA(cudaSetDevice(h->device));
+  kws_crnn_free_internal(h);
+  CrnnWeights* m = new (std::nothrow) CrnnWeights();
+  if (!m) return fail(KWS_ERR_ALLOC, "out of host memory");
+  m->num_classes = num_classes;
+  m->cc = conv_channels;
+  m->hidden = hidden;
+  m->layers = num_layers;
+  m->w1 = (n_features + 4 - 10) / 2 + 1;
+  m->names = {"conv1.weight", "conv1.bias"};
+  for (int l = 0; l < num_layers; ++l) {
+    const std::string s = "_l" + std::to_string(l);
+    m->names.push_back("gru.weight_ih" + s);
+    m->names.push_back("gru.weight_hh" + s);
+    m->names.push_back("gru.bias_ih" + s);
+    m->names.push_back("gru.bias_hh" + s);
+  }
+  m->names.push_back("fc.weight");
+  m->names.push_back("fc.bias");
+  m->host.assign(m->names.size(), std::vector<float>());
+  m->loaded.assign(m->names.size(), false);
+  m->created = true;
+  h->crnn = m;
+  return KWS_OK;
+}
+
+int kws_crnn_load_tensor(kws_handle_t h, const char* name, const float* data, const int64_t* shape, int ndim) {
+  if (!h || !h->crnn) return fail(KWS_ERR_STATE, "crnn not created");
+  if (!name || !data || !shape) return fail(KWS_ERR_INVALID, "null argument");
+  CrnnWeights& m = *crnn_of(h);
+  const int s = crnn_slot(m, name);
+  if (s < 0) return fail(KWS_ERR_INVALID, "unexpected key '%s' in state_dict", name);
+  const int64_t H = m.hidden, I0 = (int64_t)m.cc * m.w1;
+  const std::string n(name);
+  std::vector<int64_t> want;
+  if (n == "conv1.weight") want = {m.cc, 1, 10, 10};
+  else if (n == "conv1.bias") want = {m.cc};
+  else if (n == "fc.weight") want = {m.num_classes, H};
+  else if (n == "fc.bias") want = {m.num_classes};
+  else if (n.rfind("gru.weight_ih", 0) == 0) want = {3 * H, n.back() == '0' ? I0 : H};
+  else if (n.rfind("gru.weight_hh", 0) == 0) want = {3 * H, H};
+  else want = {3 * H};
+  bool ok = (int)want.size() == ndim;
+  int64_t numel = 1;
+  for (int i = 0; ok && i < ndim; ++i) {
+    ok = shape[i] == want[i];
+    numel *= want[i];
+  }
+  if (!ok) return fail(KWS_ERR_INVALID, "size mismatch for %s", name);
+  m.host[s].assign(data, data + numel);
+  m.loaded[s] = true;
+  m.finalized = false;
+  return KWS_OK;
+}
+
+int kws_crnn_finalize(kws_handle_t h) {
+  if (!h || !h->crnn) return fail(KWS_ERR_STATE, "crnn not created");
+  CrnnWeights& m = *crnn_of(h);
+  for (size_t i = 0; i < m.names.size(); ++i)
+    if (!m.loaded[i]) return fail(KWS_ERR_STATE, "missing key '%s' in state_dict", m.names[i].c_str());
+  KWS_CUDA(cudaSetDevice(h->device));
+  auto up = [&](float** dst, const std::vector<float>& v) -> int {
+    if (*dst) cudaFree(*dst);
+    *dst = nullptr;
+    KWS_CUDA(cudaMalloc((void**)dst, v.size() * 4));
+    KWS_CUDA(cudaMemcpy(*dst, v.data(), v.size() * 4, cudaMemcpyHostToDevice));
+    return KWS_OK;
+  };
+  int rc;
+  const int Cc = m.cc, H = m.hidden, K = m.num_classes, W1 = m.w1;
+  {
+    const std::vector<float>& w = m.host[crnn_slot(m, "conv1.weight")];
+    std::vector<float> p((size_t)100 * Cc);
+    for (int c = 0; c < Cc; ++c)
+      for (int t = 0; t < 100; ++t) p[(size_t)t * Cc + c] = w[(size_t)c * 100 + t];
+    if ((rc = up(&m.d_conv_w, p))) return rc;
+    if ((rc = up(&m.d_conv_b, m.host[crnn_slot(m, "conv1.bias")]))) return rc;
+  }
+  for (int l = 0; l < m.layers; ++l) {
+    const std::string s = "_l" + std::to_string(l);
+    const int I = l == 0 ? Cc * W1 : H;
+    const std::vector<float>& wih = m.host[crnn_slot(m, "gru.weight_ih" + s)];  // [3H][I], I index = c*W1 + w (layer 0)
+    std::vector<float> p((size_t)I * 3 * H);
+    for (int g = 0; g < 3 * H; ++g)
+      for (int i = 0; i < I; ++i) {
+        int dst = i;  // our conv output is NHWC: feature index w*Cc + c
+        if (l == 0) {
+          const int c = i / W1, w = i - c * W1;
+          dst = w * Cc + c;
+        }
+        p[(size_t)dst * 3 * H + g] = wih[(size_t)g * I + i];
+      }
+    if ((rc = up(&m.d_wih[l], p))) return rc;
+    const std::vector<float>& whh = m.host[crnn_slot(m, "gru.weight_hh" + s)];  // [3H][H]
+    std::vector<float> q((size_t)H * 3 * H);
+    for (int g = 0; g < 3 * H; ++g)
+      for (int k = 0; k < H; ++k) q[(size_t)k * 3 * H + g] = whh[(size_t)g * H + k];
+    if ((rc = up(&m.d_whh[l], q))) return rc;
+    if ((rc = up(&m.d_bih[l], m.host[crnn_slot(m, "gru.bias_ih" + s)]))) return rc;
+    if ((rc = up(&m.d_bhh[l], m.host[crnn_slot(m, "gru.bias_hh" + s)]))) return rc;
+  }
+  {
+    const std::vector<float>& w = m.host[crnn_slot(m, "fc.weight")];  // [K][H]
+    std::vector<float> p((size_t)H * K);
+    for (int k = 0; k < K; ++k)
+      for (int c = 0; c < H; ++c) p[(size_t)c * K + k] = w[(size_t)k * H + c];
+    if ((rc = up(&m.d_fc_w, p))) return rc;
+    if ((rc = up(&m.d_fc_b, m.host[crnn_slot(m, "fc.bias")]))) return rc;
+  }
+  m.finalized = true;
+  return KWS_OK;
+}
+
+int kws_crnn_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t T, int64_t F, float* logits_dev,
+                     void* stream) {
+  if (!h || !h->crnn) return fail(KWS_ERR_STATE, "crnn not created");
+  CrnnWeights& m = *crnn_of(h);
+  if (!m.finalized) return fail(KWS_ERR_STATE, "crnn weights not finalized");
+  if (B < 0 || T < 6 || F < 6) return fail(KWS_ERR_INVALID, "bad B/T/F");
+  const int H1 = (int)((T + 4 - 10) / 2 + 1), W1 = (int)((F + 4 - 10) / 2 + 1);
+  if (W1 != m.w1) return fail(KWS_ERR_INVALID, "crnn was built for %d conv columns, input gives %d", m.w1, W1);
+  if (B == 0) return KWS_OK;
+  if (!feats_dev || !logits_dev) return fail(KWS_ERR_INVALID, "null device pointer");
+  KWS_CUDA(cudaSetDevice(h->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  const int Cc = m.cc, H = m.hidden, K = m.num_classes, I0 = Cc * W1;
+  const int64_t chunk = B < 4096 ? B : 4096;
+  // workspace per chunk: conv output [chunk, H1, I0], projections [chunk, H1, 3H], hidden sequence, last state
+  size_t need = 0;
+  auto take = [&](size_t floats) { size_t o = need; need += (floats * 4 + 255) & ~(size_t)255; return o; };
+  const size_t o_conv = take((size_t)chunk * H1 * I0), o_xp = take((size_t)chunk * H1 * 3 * H),
+               o_seq = take((size_t)chunk * H1 * H), o_last = take((size_t)chunk * H);
+  if (need > m.ws_bytes) {
+    if (m.d_ws) KWS_CUDA(cudaFree(m.d_ws));
+    m.d_ws = nullptr;
+    m.ws_bytes = 0;
+    KWS_CUDA(cudaMalloc(&m.d_ws, need));
+    m.ws_bytes = need;
+  }
+  char* ws = (char*)m.d_ws;
+  float *d_conv = (float*)(ws + o_conv), *d_xp = (float*)(ws + o_xp), *d_seq = (float*)(ws + o_seq),
+        *d_last = (float*)(ws + o_last);
+  const size_t gru_smem = ((size_t)H * 3 * H + 2 * kGruNB * H) * 4;
+  KWS_CUDA(cudaFuncSetAttribute(gru_recurrent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gru_smem));
+  for (int64_t b0 = 0; b0 < B; b0 += chunk) {
+    const int64_t nb = (B - b0 < chunk) ? B - b0 : chunk;
+    int rc = launch_conv1_relu(h, feats_dev + b0 * T * F, d_conv, m.d_conv_w, m.d_conv_b, nb, (int)T, (int)F, H1, W1, Cc, st);
+    if (rc) return rc;
+    const float* x = d_conv;
+    int I = I0;
+    for (int l = 0; l < m.layers; ++l) {
+      const long long M = nb * H1;
+      dim3 grid((unsigned)((M + 63) / 64), (unsigned)((3 * H + 63) / 64));
+      gru_inproj_kernel<<<grid, 256, 0, st>>>(x, m.d_wih[l], m.d_bih[l], d_xp, M, 3 * H, I);
+      KWS_CHECK_LAUNCH(h);
+      const bool more = l + 1 < m.layers;
+      gru_recurrent_kernel<<<(unsigned)((nb + kGruNB - 1) / kGruNB), 256, gru_smem, st>>>(
+          d_xp, m.d_whh[l], m.d_bhh[l], more ? d_seq : nullptr, d_last, nb, H1, H);
+      KWS_CHECK_LAUNCH(h);
+      x = d_seq;
+      I = H;
+    }
+    long long g = (nb * K + 127) / 128;
+    crnn_fc_kernel<<<(unsigned)g, 128, 0, st>>>(d_last, m.d_fc_w, m.d_fc_b, logits_dev + b0 * K, nb, H, K);
+    KWS_CHECK_LAUNCH(h);
+  }
+  return KWS_OK;
+}
+
+}  // extern "C"

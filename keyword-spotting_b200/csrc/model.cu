@@ -149,6 +149,20 @@ __global__ void pool_fc_kernel(const float* __restrict__ in, float* __restrict__
   }
 }
 
+// optional epilogue (SURVEY a-X4): row-wise softmax of the logits.  The reference never applies it on
+// the torch path (logits go to CrossEntropyLoss / torch.max, training.py:293,301); not part of parity.
+__global__ void softmax_kernel(const float* __restrict__ logits, float* __restrict__ out, long long B, int K) {
+  for (long long b = blockIdx.x * (long long)blockDim.x + threadIdx.x; b < B; b += (long long)gridDim.x * blockDim.x) {
+    const float* x = logits + b * K;
+    float mx = x[0];
+    for (int k = 1; k < K; ++k) mx = fmaxf(mx, x[k]);
+    float se = 0.f;
+    for (int k = 0; k < K; ++k) se += expf(x[k] - mx);
+    const float inv = 1.0f / se;
+    for (int k = 0; k < K; ++k) out[b * K + k] = expf(x[k] - mx) * inv;
+  }
+}
+
 static void conv_out_hw(int T, int F, int nb, int* H1, int* W1, int* Hl, int* Wl) {
   *H1 = (T + 4 - 10) / 2 + 1;
   *W1 = (F + 4 - 10) / 2 + 1;
@@ -171,6 +185,16 @@ static void model_free(ModelWeights& m) {
 }
 
 constexpr int64_t kModelChunk = 2048;  // clips per pass through the ping-pong workspace
+
+int launch_conv1_relu(kws_handle_t h, const float* in, float* out, const float* w_packed, const float* bias, int64_t B,
+                      int T, int F, int H1, int W1, int C, cudaStream_t st) {
+  const long long total = B * H1 * W1 * (long long)(C / 4);
+  long long g = (total + 255) / 256;
+  if (g > h->sm_count * 16LL) g = h->sm_count * 16LL;
+  conv1_relu_kernel<<<(unsigned)g, 256, 0, st>>>(in, out, w_packed, bias, B, T, F, H1, W1, C);
+  KWS_CHECK_LAUNCH(h);
+  return KWS_OK;
+}
 
 int train_forward_layers(kws_handle_t h, const float* feats_dev, int64_t B, int T, int F, TrainWorkspace& w,
                          cudaStream_t st) {
@@ -333,6 +357,19 @@ int kws_model_finalize(kws_handle_t h) {
       return rc;
   }
   m.finalized = true;
+  return KWS_OK;
+}
+
+int kws_softmax(kws_handle_t h, const float* logits_dev, int64_t B, int64_t K, float* out_dev, void* stream) {
+  if (!h) return fail(KWS_ERR_INVALID, "null handle");
+  if (B < 0 || K < 1) return fail(KWS_ERR_INVALID, "bad B/K");
+  if (B == 0) return KWS_OK;
+  if (!logits_dev || !out_dev) return fail(KWS_ERR_INVALID, "null device pointer");
+  KWS_CUDA(cudaSetDevice(h->device));
+  long long g = (B + 127) / 128;
+  if (g > h->sm_count * 16LL) g = h->sm_count * 16LL;
+  softmax_kernel<<<(unsigned)g, 128, 0, (cudaStream_t)stream>>>(logits_dev, out_dev, B, (int)K);
+  KWS_CHECK_LAUNCH(h);
   return KWS_OK;
 }
 

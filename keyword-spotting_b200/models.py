@@ -172,5 +172,85 @@ class DepthwiseSeparableConv(KeywordSpottingModel):
                     _native.current_stream_ptr(idx)), ModelError)
         return out
 
+    def predict_proba(self, x: torch.Tensor) -> torch.Tensor:
+        """Softmax of ``forward(x)`` (optional epilogue; the reference returns logits only)."""
+        logits = self.forward(x)
+        out = torch.empty_like(logits)
+        if logits.shape[0]:
+            with torch.cuda.device(logits.device):
+                _native.check(_native.lib().kws_softmax(
+                    self._native[0].ptr, C.c_void_p(logits.data_ptr()), logits.shape[0], logits.shape[1],
+                    C.c_void_p(out.data_ptr()), _native.current_stream_ptr(logits.device.index)), ModelError)
+        return out
+
+    def launch_count(self) -> int:
+        return self._native[0].launch_count() if self._native else 0
+
+
+class CRNN(KeywordSpottingModel):
+    """CRNN / GRU keyword-spotting model (SURVEY.md a-X3, BASELINE config 4).
+
+    The reference ships no recurrent model; this subclass of its ``KeywordSpottingModel`` base
+    (models.py:13-72) reuses its first layer and initialiser: ``conv1`` 10x10 stride 2 padding 2
+    (1 -> ``conv_channels``) + ReLU (models.py:135,170), the conv output read as a sequence over time
+    (``x_t[c * W1 + w]``), ``torch.nn.GRU(conv_channels * W1, hidden, num_layers, batch_first=True)``
+    with ``h_0 = 0``, and ``fc`` on the last hidden state.  ``self.gru`` is a real ``nn.GRU`` used only
+    as the parameter holder (torch's key names and default initialiser); ``forward`` runs
+    ``kws_crnn_forward``.  Intended input: log-mel features ``[B, 1, T, n_features]``
+    (``AudioProcessor.extract_logfbank``).
+    """
+
+    def __init__(self, num_classes: int = 12, n_features: int = 40, conv_channels: int = 16, hidden: int = 64,
+                 num_layers: int = 1):
+        super().__init__(num_classes)
+        self.n_features, self.conv_channels, self.hidden, self.num_layers = n_features, conv_channels, hidden, num_layers
+        self.w1 = (n_features + 4 - 10) // 2 + 1
+        if self.w1 < 1:
+            raise ModelError("n_features too small for conv1 (10x10, stride 2, padding 2)")
+        self.conv1 = _ConvParams(conv_channels, 1, 10, 10)
+        self.gru = nn.GRU(conv_channels * self.w1, hidden, num_layers, batch_first=True)
+        self.fc = _LinearParams(hidden, num_classes)
+        nn.init.kaiming_normal_(self.conv1.weight, mode="fan_out", nonlinearity="relu")
+        nn.init.normal_(self.fc.weight, 0, 0.01)
+        self._native = None
+        self._packed_version = None
+
+    def _ensure_packed(self, dev_index: int):
+        lib = _native.lib()
+        if self._native is None or self._native[1] != dev_index:
+            h = _native.Handle(dev_index)
+            _native.check(lib.kws_crnn_create(h.ptr, self.num_classes, self.conv_channels, self.hidden,
+                                              self.num_layers, self.n_features), ModelError)
+            self._native = (h, dev_index)
+            self._packed_version = None
+        ver = tuple((p.data_ptr(), p._version) for p in self.parameters())
+        if ver != self._packed_version:
+            h = self._native[0]
+            for name, t in self.state_dict().items():
+                a = t.detach().to("cpu", torch.float32).contiguous()
+                shape = (C.c_int64 * a.dim())(*a.shape)
+                _native.check(lib.kws_crnn_load_tensor(h.ptr, name.encode(), C.c_void_p(a.data_ptr()), shape, a.dim()),
+                              ModelError)
+            _native.check(lib.kws_crnn_finalize(h.ptr), ModelError)
+            self._packed_version = ver
+        return self._native[0]
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        """``x[B, 1, T, n_features]`` float32 on CUDA -> logits ``[B, num_classes]``."""
+        if x.dim() != 4 or x.shape[1] != 1:
+            raise ModelError(f"expected input of shape (batch, 1, time, features), got {tuple(x.shape)}")
+        if x.device.type != "cuda":
+            raise ModelError(f"input is on {x.device}; kws_b200 has no CPU fallback")
+        h = self._ensure_packed(x.device.index)
+        x = x.to(torch.float32).contiguous()
+        B, _, T, F = x.shape
+        out = torch.empty((B, self.num_classes), dtype=torch.float32, device=x.device)
+        if B:
+            with torch.cuda.device(x.device):
+                _native.check(_native.lib().kws_crnn_forward(
+                    h.ptr, C.c_void_p(x.data_ptr()), B, T, F, C.c_void_p(out.data_ptr()),
+                    _native.current_stream_ptr(x.device.index)), ModelError)
+        return out
+
     def launch_count(self) -> int:
         return self._native[0].launch_count() if self._native else 0

@@ -79,6 +79,23 @@ def test_extension_channels_blocks():
     np.testing.assert_allclose(m.cuda()(x.cuda()).cpu().numpy(), want, rtol=0, atol=TOL)
 
 
+def test_softmax_epilogue_and_permutation_invariance():
+    """Optional softmax epilogue (a-X4) and a size-independent property of the fused kernel at a large,
+    odd batch: a clip's logits do not depend on its position or on its pair partner (bit-exact)."""
+    sd = dscnn_ref.init_state_dict(seed=11)
+    m = DepthwiseSeparableConv()
+    m.load_state_dict(sd)
+    m = m.cuda()
+    B = 4099
+    x = torch.randn(B, 1, 99, 40, generator=torch.Generator().manual_seed(5)).cuda() * 4.0
+    a = m(x)
+    perm = torch.randperm(B, generator=torch.Generator().manual_seed(6)).cuda()
+    b = m(x[perm].contiguous())
+    assert torch.equal(a[perm], b)
+    p = m.predict_proba(x[:33])
+    np.testing.assert_allclose(p.cpu().numpy(), torch.softmax(a[:33], 1).cpu().numpy(), rtol=1e-5, atol=1e-7)
+
+
 def test_weight_update_is_seen():
     m = DepthwiseSeparableConv().cuda()
     x = torch.randn(2, 1, 99, 10).cuda()

@@ -132,3 +132,24 @@ def test_state_dict_roundtrip_with_reference_keys(golden_dir, tmp_path):
     if not torch.cuda.is_available():
         with pytest.raises(ModelError, match="no CPU fallback"):
             m2(torch.zeros(1, 1, 99, 10))
+
+
+def test_batchnorm_folding_matches_torch_eval():
+    """a-X4: conv + BatchNorm2d(eval) == folded conv (what the kernels consume)."""
+    import torch
+    from kws_b200.utils.bnfold import fold_state_dict
+    torch.manual_seed(0)
+    conv = torch.nn.Conv2d(8, 8, 3, padding=1, groups=8)
+    bn = torch.nn.BatchNorm2d(8)
+    with torch.no_grad():
+        bn.weight.normal_(1, 0.2); bn.bias.normal_(0, 0.3)
+        bn.running_mean.normal_(0, 0.5); bn.running_var.uniform_(0.5, 2.0)
+    bn.eval()
+    sd = {f"c.{k}": v for k, v in conv.state_dict().items()}
+    sd.update({f"b.{k}": v for k, v in bn.state_dict().items()})
+    folded = fold_state_dict(sd, {"c": "b"}, eps=bn.eps)
+    assert set(folded) == {"c.weight", "c.bias"}
+    x = torch.randn(2, 8, 9, 7)
+    want = bn(conv(x))
+    got = torch.nn.functional.conv2d(x, folded["c.weight"], folded["c.bias"], padding=1, groups=8)
+    assert torch.allclose(got, want, atol=1e-5, rtol=1e-5)

@@ -127,3 +127,22 @@ def test_pointwise_border_is_relu_bias(golden_dir):
     b = torch.relu(sd["dsconv1.pointwise.bias"])
     np.testing.assert_allclose(layers[1][0, :, 0, 0].numpy(), b.numpy(), rtol=0, atol=0)
     np.testing.assert_allclose(layers[1][0, :, -1, 2].numpy(), b.numpy(), rtol=0, atol=0)
+
+
+def test_crnn_oracle_matches_torch_gru():
+    """The explicit-matmul GRU of oracle/crnn_ref.py is torch.nn.GRU (the a-X3 definition)."""
+    import torch
+    from oracle import crnn_ref
+    torch.manual_seed(0)
+    conv = torch.nn.Conv2d(1, 8, 10, stride=2, padding=2).double()
+    gru = torch.nn.GRU(8 * 18, 24, 2, batch_first=True).double()
+    fc = torch.nn.Linear(24, 12).double()
+    sd = {f"conv1.{k}": v for k, v in conv.state_dict().items()}
+    sd.update({f"gru.{k}": v for k, v in gru.state_dict().items()})
+    sd.update({f"fc.{k}": v for k, v in fc.state_dict().items()})
+    x = torch.randn(3, 1, 99, 40, dtype=torch.float64)
+    y = torch.relu(conv(x))
+    seq = y.permute(0, 2, 1, 3).reshape(3, y.shape[2], -1)
+    want = fc(gru(seq)[0][:, -1])
+    got = crnn_ref.forward(sd, x)
+    assert torch.allclose(got, want, atol=1e-10)
