@@ -103,6 +103,18 @@ int kws_mfcc_i16(kws_handle_t h, const int16_t* pcm_dev, int64_t B, int64_t N, i
  * pcm_host / out_host should be pinned for full PCIe rate but need not be. */
 int kws_mfcc_host(kws_handle_t h, const float* pcm_host, int64_t B, int64_t N, float* out_host);
 
+/* same with int16 HOST buffers (the on-disk sample format of Speech Commands; halves the PCIe bytes) */
+int kws_mfcc_host_i16(kws_handle_t h, const int16_t* pcm_host, int64_t B, int64_t N, float* out_host);
+
+/* ---- augmentation: replaces the silence / time-shift / background-noise stages of
+ * AudioProcessor.transform (kws/libs/audio_processor.py:150-159, 172-233).  The random draws are the
+ * caller's (per-clip arrays), the kernel is a pure function: out[b,i] = (silence[b] ? 0 : x[b, i - shift[b]])
+ * + bank[start[b] + (offset[b] + i) % len[b]] * volume[b]; NULL shift / silence / bank skip that stage. */
+int kws_augment(kws_handle_t h, const float* pcm_dev, int64_t B, int64_t N, int64_t pcm_stride,
+                const int32_t* shift_dev, const uint8_t* silence_dev, const float* noise_bank_dev,
+                const int64_t* noise_start_dev, const int64_t* noise_len_dev, const int64_t* noise_offset_dev,
+                const float* noise_volume_dev, float* out_dev, void* stream);
+
 /* ---- sigproc: replaces kws/libs/speech_features/sigproc.py -------------------------- */
 /* dtype: 0 = float32, 1 = float64 (the torch helpers follow the input dtype) */
 int kws_sigproc_preemphasis(int dtype, const void* in_dev, void* out_dev, int64_t B, int64_t N,

@@ -173,8 +173,8 @@ class AudioProcessor:
         """End-to-end variant on HOST tensors (ideally pinned): chunked H2D -> kernel -> D2H
         pipelined inside the library (``kws_mfcc_host``).  ``pcm`` float32 ``[B, N]`` on the CPU."""
         lib = _native.lib()
-        if pcm.device.type != "cpu" or pcm.dtype != torch.float32 or pcm.dim() != 2:
-            raise AudioProcessingError("extract_features_host expects a float32 [B, N] CPU tensor")
+        if pcm.device.type != "cpu" or pcm.dtype not in (torch.float32, torch.int16) or pcm.dim() != 2:
+            raise AudioProcessingError("extract_features_host expects a float32 (or int16 PCM) [B, N] CPU tensor")
         pcm = pcm.contiguous()
         plan = self._plan(kw.get("samplerate") or self.config.sample_rate,
                           kw.get("numcep") or self.config.num_cepstral_coeffs,
@@ -186,8 +186,71 @@ class AudioProcessor:
         if out is None:
             out = torch.empty((B, nframes, plan.ncep), dtype=torch.float32, pin_memory=True)
         with torch.cuda.device(self.device):
-            _native.check(lib.kws_mfcc_host(plan.handle.ptr, C.c_void_p(pcm.data_ptr()), B, N,
-                                            C.c_void_p(out.data_ptr())), AudioProcessingError)
+            fn = lib.kws_mfcc_host_i16 if pcm.dtype == torch.int16 else lib.kws_mfcc_host
+            _native.check(fn(plan.handle.ptr, C.c_void_p(pcm.data_ptr()), B, N, C.c_void_p(out.data_ptr())),
+                          AudioProcessingError)
+        return out
+
+    # -- augmentation: the stages of the reference ``transform`` before the features ----
+    def set_background_data(self, clips) -> None:
+        """Device-resident noise bank = the reference's ``background_data`` list (audio_processor.py:103-128),
+        concatenated; clips shorter than ``desired_samples`` are read modulo their length (``np.tile``)."""
+        clips = [torch.as_tensor(c, dtype=torch.float32).reshape(-1) for c in clips]
+        if any(c.numel() == 0 for c in clips):
+            raise AudioProcessingError("empty background clip")
+        self._bank_len = torch.tensor([c.numel() for c in clips], dtype=torch.int64)
+        self._bank_start = torch.cumsum(self._bank_len, 0) - self._bank_len
+        self._bank = torch.cat(clips).to(self.device) if clips else None
+
+    def draw_augmentation(self, labels: torch.Tensor, generator: Optional[torch.Generator] = None) -> Dict[str, torch.Tensor]:
+        """Per-clip random draws with the reference's distributions (audio_processor.py:181-183, 207-231):
+        shift ~ U{-time_shift .. time_shift-1}; noise clip uniform; offset ~ U{0 .. len'-N-1} over the tiled
+        length; volume ~ U(0,1) for silence, else U(0, background_volume) with probability
+        background_frequency, else 0.  (The reference uses the global numpy/random state; parity is
+        distributional)"""
+        cfg, N = self.config, self.config.desired_samples
+        labels = torch.as_tensor(labels).to("cpu", torch.int64)
+        B = labels.numel()
+        ts = cfg.time_shift
+        g = generator
+        shift = torch.randint(-ts, ts, (B,), generator=g, dtype=torch.int32) if ts > 0 else torch.zeros(B, dtype=torch.int32)
+        silence = (labels == 0)
+        draws = {"shift": shift, "silence": silence.to(torch.uint8)}
+        bank = getattr(self, "_bank", None)
+        if bank is not None:
+            idx = torch.randint(0, self._bank_len.numel(), (B,), generator=g)
+            ln = self._bank_len[idx]
+            tiled = torch.where(ln <= N, ((N + ln - 1) // ln) * ln, ln)
+            span = torch.clamp(tiled - N, min=1)
+            off = (torch.rand(B, generator=g, dtype=torch.float64) * span).to(torch.int64).clamp_(max=span - 1)
+            u1, u2 = torch.rand(B, generator=g), torch.rand(B, generator=g)
+            vol = torch.where(silence, u2, torch.where(u1 < cfg.background_frequency, u2 * cfg.background_volume,
+                                                       torch.zeros(B)))
+            use = silence | torch.tensor(bool(cfg.use_background_noise))
+            draws.update({"noise_start": self._bank_start[idx], "noise_len": torch.where(use, ln, torch.zeros_like(ln)),
+                          "noise_offset": off, "noise_volume": vol.float()})
+        return draws
+
+    def augment(self, pcm: torch.Tensor, draws: Dict[str, torch.Tensor]) -> torch.Tensor:
+        """Apply silence zeroing, time shift and background-noise mix on the device (``kws_augment``);
+        ``pcm[B, N]`` float32 CUDA, ``draws`` from :meth:`draw_augmentation` (or hand-made)."""
+        lib = _native.lib()
+        x = pcm.to(self.device, torch.float32)
+        if x.dim() != 2 or x.stride(1) != 1:
+            x = x.reshape(-1, x.shape[-1]).contiguous()
+        B, N = x.shape
+        dev = {k: v.to(self.device).contiguous() for k, v in draws.items()}
+        out = torch.empty((B, N), dtype=torch.float32, device=self.device)
+        bank = getattr(self, "_bank", None) if "noise_start" in dev else None
+        ptr = lambda k: C.c_void_p(dev[k].data_ptr()) if k in dev else None  # noqa: E731
+        plan = self._plan(self.config.sample_rate, self.config.num_cepstral_coeffs, self.config.frame_length,
+                          self.config.frame_step, self.config.num_mel_filters)
+        with torch.cuda.device(self.device):
+            _native.check(lib.kws_augment(
+                plan.handle.ptr, C.c_void_p(x.data_ptr()), B, N, x.stride(0), ptr("shift"), ptr("silence"),
+                C.c_void_p(bank.data_ptr()) if bank is not None else None, ptr("noise_start"), ptr("noise_len"),
+                ptr("noise_offset"), ptr("noise_volume"), C.c_void_p(out.data_ptr()),
+                _native.current_stream_ptr(self._dev_index())), AudioProcessingError)
         return out
 
     def launch_count(self) -> int:

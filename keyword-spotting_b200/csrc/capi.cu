@@ -113,7 +113,7 @@ int kws_mfcc_i16(kws_handle_t h, const int16_t* pcm_dev, int64_t B, int64_t N, i
   return launch_mfcc(h, pcm_dev, true, B, N, pcm_stride, out_dev, kModeMfcc, (cudaStream_t)stream);
 }
 
-int kws_mfcc_host(kws_handle_t h, const float* pcm_host, int64_t B, int64_t N, float* out_host) {
+static int mfcc_host_impl(kws_handle_t h, const void* pcm_host, bool is_i16, int64_t B, int64_t N, float* out_host) {
   if (!h) return fail(KWS_ERR_INVALID, "null handle");
   if (!h->feat.ready) return fail(KWS_ERR_STATE, "features not configured");
   if (B < 0 || N < 1) return fail(KWS_ERR_INVALID, "bad B/N");
@@ -122,6 +122,7 @@ int kws_mfcc_host(kws_handle_t h, const float* pcm_host, int64_t B, int64_t N, f
   KWS_CUDA(cudaSetDevice(h->device));
   int rc = ensure_streams(h);
   if (rc) return rc;
+  const size_t esz = is_i16 ? 2 : 4;
   const int64_t nframes = kws_num_frames(N, h->feat.cfg.frame_len, h->feat.cfg.frame_step);
   const int64_t ocols = h->feat.ncep;
   const int64_t chunk = std::min<int64_t>(B, kHostChunkClips);
@@ -132,9 +133,9 @@ int kws_mfcc_host(kws_handle_t h, const float* pcm_host, int64_t B, int64_t N, f
     const int64_t nb = std::min<int64_t>(chunk, B - b0);
     const int s = i & 1;
     cudaStream_t st = h->s_copy[s];
-    KWS_CUDA(cudaMemcpyAsync(h->d_stage_in[s], pcm_host + b0 * N, (size_t)nb * N * 4,
+    KWS_CUDA(cudaMemcpyAsync(h->d_stage_in[s], (const char*)pcm_host + (size_t)b0 * N * esz, (size_t)nb * N * esz,
                              cudaMemcpyHostToDevice, st));
-    rc = launch_mfcc(h, h->d_stage_in[s], false, nb, N, N, (float*)h->d_stage_out[s], kModeMfcc, st);
+    rc = launch_mfcc(h, h->d_stage_in[s], is_i16, nb, N, N, (float*)h->d_stage_out[s], kModeMfcc, st);
     if (rc) return rc;
     KWS_CUDA(cudaMemcpyAsync(out_host + b0 * nframes * ocols, h->d_stage_out[s],
                              (size_t)nb * nframes * ocols * 4, cudaMemcpyDeviceToHost, st));
@@ -142,6 +143,14 @@ int kws_mfcc_host(kws_handle_t h, const float* pcm_host, int64_t B, int64_t N, f
   KWS_CUDA(cudaStreamSynchronize(h->s_copy[0]));
   KWS_CUDA(cudaStreamSynchronize(h->s_copy[1]));
   return KWS_OK;
+}
+
+int kws_mfcc_host(kws_handle_t h, const float* pcm_host, int64_t B, int64_t N, float* out_host) {
+  return mfcc_host_impl(h, pcm_host, false, B, N, out_host);
+}
+
+int kws_mfcc_host_i16(kws_handle_t h, const int16_t* pcm_host, int64_t B, int64_t N, float* out_host) {
+  return mfcc_host_impl(h, pcm_host, true, B, N, out_host);
 }
 
 

@@ -53,6 +53,22 @@ class KeywordSpottingModel(nn.Module, abc.ABC):
             raise ModelError(f"Failed to load model from {path}: {str(e)}") from e
 
 
+def load_reference_checkpoint(model: "KeywordSpottingModel", path: str, device=None) -> dict:
+    """Load either checkpoint flavour the reference writes: a bare ``state_dict``
+    (``KeywordSpottingModel.save`` models.py:41-53, ``train.py:77``) or the trainer's dict
+    ``{model_state_dict, optimizer_state_dict, metrics, config, epoch}`` (training.py:199-216).
+    Returns the remaining checkpoint entries (empty for a bare state_dict)."""
+    try:
+        ckpt = torch.load(path, map_location=device or "cpu")
+        if isinstance(ckpt, dict) and "model_state_dict" in ckpt:
+            model.load_state_dict(ckpt["model_state_dict"])
+            return {k: v for k, v in ckpt.items() if k != "model_state_dict"}
+        model.load_state_dict(ckpt)
+        return {}
+    except Exception as e:
+        raise ModelError(f"Failed to load model from {path}: {str(e)}") from e
+
+
 class _ConvParams(nn.Module):
     """Parameter holder with ``nn.Conv2d``'s ``weight``/``bias`` names and shapes."""
 

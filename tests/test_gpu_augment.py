@@ -1,0 +1,79 @@
+"""GPU augmentation against a numpy restatement of the reference's
+_apply_time_shift / _add_background_noise (kws/libs/audio_processor.py:172-233) with the same draws
+(bit-exact), int16 host ingest, and the reference's two checkpoint flavours."""
+import numpy as np
+import pytest
+import torch
+
+from kws_b200.audio_processor import AudioConfig, AudioProcessor
+from kws_b200.models import DepthwiseSeparableConv, load_reference_checkpoint
+from kws_b200.utils import synth
+from oracle import psf_mfcc
+
+pytestmark = pytest.mark.gpu
+
+
+def _ref_augment(audio, shift, silent, bg, offset, volume, N):
+    if silent:
+        audio = np.zeros_like(audio)                                   # :151-152
+    padding = [max(0, shift), max(0, -shift)]                         # :184-188
+    off = max(0, -shift)
+    audio = np.pad(audio, padding, "constant")[off:off + N]
+    if bg is not None:
+        if len(bg) <= N:                                              # :210-216
+            bg = np.tile(bg, int(np.ceil(N / len(bg))))
+        audio = audio + (bg[offset:offset + N] * volume)              # :219-233
+    return audio
+
+
+def test_augment_bit_exact_with_reference_semantics():
+    N, B = 16000, 24
+    proc = AudioProcessor(None, AudioConfig(), device="cuda:0")
+    rs = np.random.RandomState(0)
+    bank = [rs.randn(n).astype(np.float32) * 0.1 for n in (48000, 16000, 5000, 16001)]
+    proc.set_background_data(bank)
+    pcm = synth.uniform_pcm(B, N, seed=3)
+    labels = torch.tensor([0, 1, 2, 3] * 6)
+    draws = proc.draw_augmentation(labels, generator=torch.Generator().manual_seed(7))
+    assert draws["shift"].min() >= -1600 and draws["shift"].max() < 1600
+    draws["shift"][:4] = torch.tensor([-1600, 1599, 0, 37], dtype=torch.int32)   # the extremes
+    got = proc.augment(pcm.cuda(), draws).cpu().numpy()
+    starts = np.cumsum([0] + [len(b) for b in bank])
+    for b in range(B):
+        k = int(np.searchsorted(starts, int(draws["noise_start"][b]), side="right") - 1)
+        used = int(draws["noise_len"][b]) > 0
+        want = _ref_augment(pcm[b].numpy(), int(draws["shift"][b]), bool(draws["silence"][b]),
+                            bank[k] if used else None, int(draws["noise_offset"][b]),
+                            np.float32(draws["noise_volume"][b]), N)
+        np.testing.assert_array_equal(got[b], want.astype(np.float32), err_msg=f"clip {b}")
+    # silence clips carry noise only; volume rule of :222-229
+    assert (draws["noise_volume"][labels != 0] <= 0.1 + 1e-7).all()
+    # without a bank / without draws the stages are skipped
+    same = proc.augment(pcm.cuda(), {"shift": torch.zeros(B, dtype=torch.int32)}).cpu()
+    assert torch.equal(same, pcm)
+
+
+def test_int16_host_ingest_matches_float_path():
+    proc = AudioProcessor(None, AudioConfig(), device="cuda:0")
+    i16 = (synth.uniform_pcm(37, seed=2) * 32767).round().to(torch.int16)
+    got = proc.extract_features_host(i16.pin_memory(), numcep=40, nfilt=40).numpy()
+    f32 = (i16.float() / 32768.0)
+    want = psf_mfcc.extract_features_batch(f32.numpy(), numcep=40, nfilt=40)
+    err = np.abs(got - want)
+    assert (err <= 1e-4 + 1e-3 * np.abs(want)).all()
+
+
+def test_reference_checkpoint_flavours(tmp_path):
+    src = DepthwiseSeparableConv()
+    bare, full = tmp_path / "model.pth", tmp_path / "best_model.pth"
+    torch.save(src.state_dict(), bare)
+    torch.save({"model_state_dict": src.state_dict(), "optimizer_state_dict": {}, "metrics": {"val_acc": [1.0]},
+                "config": {}, "epoch": 3}, full)
+    for path, extra in ((bare, {}), (full, {"epoch": 3})):
+        m = DepthwiseSeparableConv()
+        rest = load_reference_checkpoint(m, str(path))
+        assert all(torch.equal(a, b) for a, b in zip(m.state_dict().values(), src.state_dict().values()))
+        for k, v in extra.items():
+            assert rest[k] == v
+    x = torch.randn(3, 1, 99, 10).cuda()
+    assert torch.equal(m.cuda()(x), src.cuda()(x))
