@@ -76,7 +76,8 @@ struct ModelWeights {
   float* d_fused_dw = nullptr;      // [4][9][64]
   float* d_fused_actb = nullptr;    // [5][64]
   float* d_fused_border = nullptr;  // [5][64]
-  int path = 0;                     // 0 = auto (fused when applicable), 1 = force the layered kernels
+  int path = 0;                     // 0 = auto (fused / tensor-core GEMM when applicable), 1 = layered fp32 kernels
+  void* gemm = nullptr;             // kws::GemmModel (model_gemm.cu): chunked tf32 weight images for any channel count
   // workspace
   void* d_ws = nullptr;
   size_t ws_bytes = 0;
@@ -134,6 +135,13 @@ int train_forward_layers(kws_handle_t h, const float* feats_dev, int64_t B, int 
 // model.cu: conv 10x10 s2 p2 (one input channel) + ReLU, NHWC output [B, H1, W1, C]
 int launch_conv1_relu(kws_handle_t h, const float* in, float* out, const float* w_packed, const float* bias, int64_t B,
                       int T, int F, int H1, int W1, int C, cudaStream_t st);
+// model_gemm.cu: layer-by-layer tcgen05 forward for any channel count (1 = handled, 0 = n/a, <0 = error)
+int build_gemm_model(ModelWeights& m, const std::vector<float>& conv1_w, const std::vector<float>& conv1_b,
+                     const std::vector<const float*>& dw_b, const std::vector<const float*>& pw_w,
+                     const std::vector<const float*>& pw_b);
+void free_gemm_model(void* gm);
+int launch_dscnn_gemm(kws_handle_t h, const float* feats_dev, int64_t B, int T, int F, float* buf0, float* buf1,
+                      float** last_out, cudaStream_t st);
 // tables.cu
 int build_feature_tables(kws_handle_t h, const kws_feature_config* cfg);
 void free_feature_tables(FeatureTables& t);

@@ -181,6 +181,7 @@ static void model_free(ModelWeights& m) {
                   m.d_fc_w,    m.d_fc_b,    m.d_ws,     m.d_fused_a, m.d_fused_dw, m.d_fused_actb, m.d_fused_border};
   for (void* p : ptrs)
     if (p) cudaFree(p);
+  free_gemm_model(m.gemm);
   m = ModelWeights();
 }
 
@@ -344,7 +345,7 @@ int kws_model_finalize(kws_handle_t h) {
     if ((rc = up(&m.d_fc_w, p))) return rc;
     if ((rc = up(&m.d_fc_b, m.host[slot_of(m, "fc.bias")]))) return rc;
   }
-  if (C == 64 && nb == 4) {  // parameter images of the fused tensor-core kernel (model_fused.cu)
+  {
     std::vector<const float*> a, ab, b, bb;
     for (int i = 0; i < nb; ++i) {
       const std::string pre = "dsconv" + std::to_string(i + 1);
@@ -353,7 +354,12 @@ int kws_model_finalize(kws_handle_t h) {
       b.push_back(m.host[slot_of(m, pre + ".pointwise.weight")].data());
       bb.push_back(m.host[slot_of(m, pre + ".pointwise.bias")].data());
     }
-    if ((rc = build_fused_model(m, m.host[slot_of(m, "conv1.weight")], m.host[slot_of(m, "conv1.bias")], a, ab, b, bb)))
+    if (C == 64 && nb == 4) {  // parameter images of the fused tensor-core kernel (model_fused.cu)
+      if ((rc = build_fused_model(m, m.host[slot_of(m, "conv1.weight")], m.host[slot_of(m, "conv1.bias")], a, ab, b, bb)))
+        return rc;
+    }
+    // chunked weight images of the layer-by-layer tensor-core path (model_gemm.cu), any channel count
+    if ((rc = build_gemm_model(m, m.host[slot_of(m, "conv1.weight")], m.host[slot_of(m, "conv1.bias")], ab, b, bb)))
       return rc;
   }
   m.finalized = true;
@@ -421,6 +427,18 @@ int kws_model_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t
   const int cq = C / 4;
   for (int64_t b0 = 0; b0 < B; b0 += chunk) {
     const int64_t nbat = (B - b0 < chunk) ? B - b0 : chunk;
+    if (m.path == 0 && m.gemm) {  // layer-by-layer tensor-core path (model_gemm.cu)
+      float* last = nullptr;
+      const int rc = launch_dscnn_gemm(h, feats_dev + b0 * T * F, nbat, (int)T, (int)F, buf0, buf1, &last, st);
+      if (rc < 0) return rc;
+      if (rc == 1) {
+        long long g = nbat < h->sm_count * 8LL ? nbat : h->sm_count * 8LL;
+        pool_fc_kernel<<<(unsigned)g, 128, C * 4, st>>>(last, logits_dev + b0 * K, m.d_fc_w, m.d_fc_b, nbat, Hl * Wl, C, K,
+                                                        nullptr);
+        KWS_CHECK_LAUNCH(h);
+        continue;
+      }
+    }
     {
       const long long total = nbat * H1 * W1 * (long long)cq;
       long long g = (total + 255) / 256;

@@ -1,0 +1,363 @@
+// Tensor-core forward of the depthwise-separable network for ANY channel count (multiple of 4, <= 512) and
+// block count -- the "DS-CNN-L"-style generalisation of kws/libs/models.py:122-183 (SURVEY.md a-X1, BASELINE
+// config 2: 276 channels, 5 blocks) and the reference shape at feature widths the fused kernel does not
+// cover.  Layer by layer, activations NHWC in HBM (at 276 channels one layer of one clip is 1.6 MB: it cannot
+// stay on chip), every GEMM on tcgen05:
+//     conv1     D[pixel, c_out] = im2col[pixel, 100 taps]      . W1[c_out, tap]^T
+//     block l   D[pixel, c_out] = depthwise3x3(x)[pixel, c_in] . Wpw[c_out, c_in]^T      (+bias, ReLU in the epilogue)
+// M = 128 output pixels per tile (flattened over the batch), N = channels padded to 32 (two N halves when
+// > 256), K streamed in chunks of 32: for every chunk the CTA copies the chunk of the pre-packed tf32 weight
+// image to shared memory, computes the A chunk on the CUDA cores (the 3x3 depthwise stencil straight from
+// the NHWC input through L1/L2, or the im2col gather) into the K-major UMMA layout, and one thread issues
+// the chunk's tcgen05.mma kind::tf32 into the TMEM accumulator.  A and B chunks are double-buffered and
+// tcgen05.commit -> mbarrier releases a buffer, so chunk k+1 is produced while chunk k multiplies.
+// Epilogue: tcgen05.ld (lane = pixel) + bias + ReLU -> NHWC stores at the padded position (y+1, x+1) of the
+// (H+2) x (W+2) output; the border pixels, ReLU(pointwise bias) (models.py:104-106), are written by
+// border_fill_kernel.  The depthwise bias is folded through the pointwise weights on the host.
+#include <cstring>
+#include <vector>
+
+#include "mfcc_dev.cuh"
+
+namespace kws {
+
+constexpr int kGT = 256;                   // threads per CTA
+constexpr int kGKC = 32;                   // K chunk (4 MMA k-steps)
+constexpr int kGSbo = (kGKC / 4) * 128;    // 8-row group pitch of A and B chunks
+constexpr int kGABytes = 16 * kGSbo;       // A chunk: 128 pixels x 32 k
+
+struct GemmParams {
+  const float* in;     // MODE 1: [B,H,W,C] NHWC block input; MODE 0: features [B,T,F]
+  float* out;          // MODE 1: [B,H+2,W+2,C]; MODE 0: [B,H,W,C]
+  const float* wimg;   // weight chunks, tf32, K-major: [nchunks][npad/8][kGSbo bytes]
+  const float* dw_w;   // MODE 1: [9][C] depthwise taps
+  const float* bias;   // [C] epilogue bias
+  long long npix;      // B*H*W output (interior) pixels
+  int H, W, C, T, F;
+  int kvalid, npad, nh, nhalf, nchunks, tmem_cols;
+};
+
+template <int MODE>
+__global__ void __launch_bounds__(kGT, 1) dscnn_gemm_kernel(const GemmParams p) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  __shared__ __align__(8) unsigned long long s_bar[2];
+  __shared__ uint32_t s_tmem;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int bbytes = (p.npad / 8) * kGSbo;
+  unsigned char* sA = smem;                      // [2][kGABytes]
+  unsigned char* sB = smem + 2 * kGABytes;       // [2][bbytes]
+  const uint32_t bar0 = smem_u32(&s_bar[0]);
+  if (tid == 0) {
+    mbar_init(bar0, 1);
+    mbar_init(bar0 + 8, 1);
+    fence_mbar_init();
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)),
+                 "r"((uint32_t)p.tmem_cols));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = s_tmem;
+  const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(p.nhalf >> 3) << 17) | ((128u >> 4) << 24);
+  const int H = p.H, W = p.W, C = p.C;
+  const int px = tid & 127, kg = tid >> 7;       // A-chunk ownership: pixel row, 16-wide half of the chunk
+  const long long ntiles = (p.npix + 127) / 128;
+  uint32_t cnt = 0;                              // chunks issued so far: buffer = cnt & 1, its phase = cnt >> 1
+
+  for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const long long gp = tile * 128 + px;
+    const bool valid = gp < p.npix;
+    int x = 0, y = 0;
+    long long b = 0;
+    if (valid) {
+      x = (int)(gp % W);
+      y = (int)((gp / W) % H);
+      b = gp / ((long long)W * H);
+    }
+    for (int kc = 0; kc < p.nchunks; ++kc, ++cnt) {
+      const int buf = cnt & 1;
+      if (cnt >= 2) mbar_wait(bar0 + 8u * buf, ((cnt - 2) >> 1) & 1);  // the MMAs that read this buffer retired
+      {  // weight chunk -> shared memory
+        const uint4* src = reinterpret_cast<const uint4*>(p.wimg) + (size_t)kc * (bbytes / 16);
+        uint4* dst = reinterpret_cast<uint4*>(sB + (size_t)buf * bbytes);
+        for (int i = tid; i < bbytes / 16; i += kGT) dst[i] = __ldg(src + i);
+      }
+      unsigned char* arow = sA + buf * kGABytes + (px >> 3) * kGSbo + (px & 7) * 16;
+#pragma unroll
+      for (int g4 = 0; g4 < 4; ++g4) {
+        const int kl = kg * 16 + g4 * 4, k = kc * kGKC + kl;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (valid && k < p.kvalid) {
+          if (MODE == 1) {  // depthwise 3x3, zero padding 1, channels k..k+3
+#pragma unroll
+            for (int i = 0; i < 3; ++i) {
+              const int yy = y + i - 1;
+              if (yy < 0 || yy >= H) continue;
+#pragma unroll
+              for (int j = 0; j < 3; ++j) {
+                const int xx = x + j - 1;
+                if (xx < 0 || xx >= W) continue;
+                const float4 a = __ldg(reinterpret_cast<const float4*>(p.in + ((b * H + yy) * W + xx) * C + k));
+                const float4 w = __ldg(reinterpret_cast<const float4*>(p.dw_w + (i * 3 + j) * C + k));
+                v.x = fmaf(a.x, w.x, v.x);
+                v.y = fmaf(a.y, w.y, v.y);
+                v.z = fmaf(a.z, w.z, v.z);
+                v.w = fmaf(a.w, w.w, v.w);
+              }
+            }
+          } else {  // im2col of the 10x10 stride-2 padding-2 window, taps k..k+3
+            float t4[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const int kk = k + e, ki = kk / 10, kj = kk - 10 * ki;
+              const int fr = 2 * y - 2 + ki, fc = 2 * x - 2 + kj;
+              t4[e] = (kk < p.kvalid && fr >= 0 && fr < p.T && fc >= 0 && fc < p.F) ? __ldg(p.in + (b * p.T + fr) * p.F + fc) : 0.f;
+            }
+            v = make_float4(t4[0], t4[1], t4[2], t4[3]);
+          }
+        }
+        uint4 r;  // tf32 round-to-nearest: add half an ulp of the 10-bit mantissa, the MMA drops the low 13 bits
+        r.x = __float_as_uint(v.x) + 0x1000u;
+        r.y = __float_as_uint(v.y) + 0x1000u;
+        r.z = __float_as_uint(v.z) + 0x1000u;
+        r.w = __float_as_uint(v.w) + 0x1000u;
+        *reinterpret_cast<uint4*>(arow + (kl >> 2) * 128) = r;
+      }
+      fence_proxy_async();
+      __syncthreads();
+      if (tid == 0) {
+        tc_fence_after();
+        const uint32_t ab = smem_u32(sA + buf * kGABytes), bb = smem_u32(sB + (size_t)buf * bbytes);
+#pragma unroll 1
+        for (int ks = 0; ks < kGKC / 8; ++ks)
+          for (int hf = 0; hf < p.nh; ++hf)
+            tc_mma_tf32(tmem + (uint32_t)(hf * p.nhalf), umma_desc(ab + ks * 256u, 128u, kGSbo),
+                        umma_desc(bb + (uint32_t)(hf * (p.nhalf / 8)) * kGSbo + ks * 256u, 128u, kGSbo), idesc,
+                        (kc > 0 || ks > 0) ? 1u : 0u);
+        tc_commit(bar0 + 8u * buf);
+      }
+    }
+    {  // all MMAs of the tile have retired when the last chunk's commit arrives
+      const uint32_t last = cnt - 1;
+      mbar_wait(bar0 + 8u * (last & 1), (last >> 1) & 1);
+      tc_fence_after();
+    }
+    {  // epilogue: lane = pixel row, warp / 4 = column half
+      const int row = (warp & 3) * 32 + lane, chalf = warp >> 2;
+      const long long gq = tile * 128 + row;
+      float* orow = nullptr;
+      if (gq < p.npix) {
+        if (MODE == 1) {
+          const int xq = (int)(gq % W), yq = (int)((gq / W) % H);
+          const long long bq = gq / ((long long)W * H);
+          orow = p.out + ((bq * (H + 2) + yq + 1) * (W + 2) + xq + 1) * C;
+        } else {
+          orow = p.out + gq * C;
+        }
+      }
+      const int c0 = chalf * (p.npad / 2), c1 = c0 + p.npad / 2;
+      const uint32_t taddr = tmem + ((uint32_t)((warp & 3) * 32) << 16);
+      for (int c = c0; c < c1; c += 16) {
+        float q[16];
+        tc_ld16(taddr + (uint32_t)c, q);
+        tc_wait_ld();
+        if (orow) {
+#pragma unroll
+          for (int e = 0; e < 16; e += 4) {
+            if (c + e < C) {
+              const float4 bz = __ldg(reinterpret_cast<const float4*>(p.bias + c + e));
+              *reinterpret_cast<float4*>(orow + c + e) =
+                  make_float4(fmaxf(q[e] + bz.x, 0.f), fmaxf(q[e + 1] + bz.y, 0.f), fmaxf(q[e + 2] + bz.z, 0.f),
+                              fmaxf(q[e + 3] + bz.w, 0.f));
+            }
+          }
+        }
+      }
+    }
+    tc_fence_before();
+    __syncthreads();  // the next tile's first MMA overwrites the accumulator
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0)
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((uint32_t)p.tmem_cols));
+}
+
+// border of a block output [B, Ho, Wo, C]: ReLU(pointwise bias)
+__global__ void border_fill_kernel(float* __restrict__ out, const float* __restrict__ relu_bias, long long B, int Ho,
+                                   int Wo, int C) {
+  const int cq = C / 4, nb = 2 * Wo + 2 * (Ho - 2);
+  const long long total = B * nb * (long long)cq;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int q = (int)(i % cq);
+    const int e = (int)((i / cq) % nb);
+    const long long b = i / ((long long)cq * nb);
+    int y, x;
+    if (e < Wo) { y = 0; x = e; }
+    else if (e < 2 * Wo) { y = Ho - 1; x = e - Wo; }
+    else { const int r = e - 2 * Wo; y = 1 + (r >> 1); x = (r & 1) ? Wo - 1 : 0; }
+    reinterpret_cast<float4*>(out + ((b * Ho + y) * Wo + x) * C)[q] = reinterpret_cast<const float4*>(relu_bias)[q];
+  }
+}
+
+
+// ---- host side ------------------------------------------------------------------------------
+struct GemmModel {
+  int C = 0, nb = 0, npad = 0, nh = 0, nhalf = 0, tmem_cols = 0;
+  std::vector<float*> wimg;     // conv1, then one per block
+  std::vector<int> kvalid, nchunks;
+  float* d_bias = nullptr;      // [1 + nb][C]: conv1 bias, then pointwise bias with the depthwise bias folded through
+  float* d_border = nullptr;    // [nb][C] ReLU(pointwise bias)
+};
+
+static float gemm_host_tf32(float x) {
+  uint32_t u;
+  memcpy(&u, &x, 4);
+  if ((u & 0x7f800000u) != 0x7f800000u) u = (u + 0x1000u) & ~0x1fffu;
+  memcpy(&x, &u, 4);
+  return x;
+}
+
+void free_gemm_model(void* gm) {
+  GemmModel* g = reinterpret_cast<GemmModel*>(gm);
+  if (!g) return;
+  for (float* p : g->wimg)
+    if (p) cudaFree(p);
+  if (g->d_bias) cudaFree(g->d_bias);
+  if (g->d_border) cudaFree(g->d_border);
+  delete g;
+}
+
+// weight [N rows][K] (torch [c_out][k]) -> chunked K-major tf32 image
+static int upload_wimg(GemmModel& g, const float* w, int N, int K) {
+  const int nchunks = (K + kGKC - 1) / kGKC;
+  const size_t chunk_floats = (size_t)(g.npad / 8) * kGSbo / 4;
+  std::vector<float> img(chunk_floats * nchunks, 0.f);
+  for (int n = 0; n < N; ++n)
+    for (int k = 0; k < K; ++k) {
+      const int kc = k / kGKC, kl = k % kGKC;
+      img[kc * chunk_floats + ((size_t)(n >> 3) * kGSbo + (kl >> 2) * 128 + (n & 7) * 16 + (kl & 3) * 4) / 4] =
+          gemm_host_tf32(w[(size_t)n * K + k]);
+    }
+  float* d = nullptr;
+  KWS_CUDA(cudaMalloc((void**)&d, img.size() * 4));
+  KWS_CUDA(cudaMemcpy(d, img.data(), img.size() * 4, cudaMemcpyHostToDevice));
+  g.wimg.push_back(d);
+  g.kvalid.push_back(K);
+  g.nchunks.push_back(nchunks);
+  return KWS_OK;
+}
+
+int build_gemm_model(ModelWeights& m, const std::vector<float>& conv1_w, const std::vector<float>& conv1_b,
+                     const std::vector<const float*>& dw_b, const std::vector<const float*>& pw_w,
+                     const std::vector<const float*>& pw_b) {
+  free_gemm_model(m.gemm);
+  m.gemm = nullptr;
+  const int C = m.channels, nb = m.num_blocks;
+  if (C % 4 != 0 || C > 512) return KWS_OK;  // outside the tensor-core path: layered kernels only
+  GemmModel* g = new (std::nothrow) GemmModel();
+  if (!g) return fail(KWS_ERR_ALLOC, "out of host memory");
+  g->C = C;
+  g->nb = nb;
+  g->npad = (C + 31) / 32 * 32;
+  g->nh = g->npad > 256 ? 2 : 1;
+  g->nhalf = g->npad / g->nh;
+  g->tmem_cols = 32;
+  while (g->tmem_cols < g->npad) g->tmem_cols *= 2;
+  int rc = upload_wimg(*g, conv1_w.data(), C, 100);
+  std::vector<float> bias((size_t)(1 + nb) * C), border((size_t)(nb > 0 ? nb : 1) * C, 0.f);
+  for (int c = 0; c < C; ++c) bias[c] = conv1_b[c];
+  for (int l = 0; l < nb && rc == KWS_OK; ++l) {
+    rc = upload_wimg(*g, pw_w[l], C, C);
+    for (int co = 0; co < C; ++co) {
+      double be = pw_b[l][co];
+      for (int ci = 0; ci < C; ++ci) be += (double)pw_w[l][(size_t)co * C + ci] * (double)dw_b[l][ci];
+      bias[(size_t)(l + 1) * C + co] = (float)be;
+      border[(size_t)l * C + co] = pw_b[l][co] > 0.f ? pw_b[l][co] : 0.f;
+    }
+  }
+  if (rc == KWS_OK && cudaMalloc((void**)&g->d_bias, bias.size() * 4) != cudaSuccess) rc = fail(KWS_ERR_CUDA, "cudaMalloc failed");
+  if (rc == KWS_OK && cudaMalloc((void**)&g->d_border, border.size() * 4) != cudaSuccess) rc = fail(KWS_ERR_CUDA, "cudaMalloc failed");
+  if (rc == KWS_OK) {
+    cudaMemcpy(g->d_bias, bias.data(), bias.size() * 4, cudaMemcpyHostToDevice);
+    cudaMemcpy(g->d_border, border.data(), border.size() * 4, cudaMemcpyHostToDevice);
+  }
+  if (rc != KWS_OK) {
+    free_gemm_model(g);
+    return rc;
+  }
+  m.gemm = g;
+  return KWS_OK;
+}
+
+// 1 = handled, 0 = not applicable, < 0 = error.  buf0/buf1: ping-pong NHWC workspaces of the caller.
+int launch_dscnn_gemm(kws_handle_t h, const float* feats_dev, int64_t B, int T, int F, float* buf0, float* buf1,
+                      float** last_out, cudaStream_t st) {
+  ModelWeights& m = h->model;
+  GemmModel* g = reinterpret_cast<GemmModel*>(m.gemm);
+  if (!g) return 0;
+  const int C = g->C, nb = g->nb;
+  const int H1 = (T + 4 - 10) / 2 + 1, W1 = (F + 4 - 10) / 2 + 1;
+  const size_t smem_bytes = 2 * kGABytes + 2 * (size_t)(g->npad / 8) * kGSbo;
+  KWS_CUDA(cudaFuncSetAttribute(dscnn_gemm_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+  KWS_CUDA(cudaFuncSetAttribute(dscnn_gemm_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+  const int ctas_per_sm = (g->tmem_cols <= 256 && smem_bytes <= 100 * 1024) ? 2 : 1;
+  GemmParams p{};
+  p.C = C;
+  p.T = T;
+  p.F = F;
+  p.npad = g->npad;
+  p.nh = g->nh;
+  p.nhalf = g->nhalf;
+  p.tmem_cols = g->tmem_cols;
+  auto grid_for = [&](long long npix) {
+    long long t = (npix + 127) / 128, gmax = (long long)h->sm_count * ctas_per_sm;
+    return (unsigned)(t < gmax ? t : gmax);
+  };
+  // conv1
+  p.in = feats_dev;
+  p.out = buf0;
+  p.wimg = g->wimg[0];
+  p.dw_w = nullptr;
+  p.bias = g->d_bias;
+  p.H = H1;
+  p.W = W1;
+  p.npix = B * (long long)H1 * W1;
+  p.kvalid = g->kvalid[0];
+  p.nchunks = g->nchunks[0];
+  dscnn_gemm_kernel<0><<<grid_for(p.npix), kGT, smem_bytes, st>>>(p);
+  KWS_CHECK_LAUNCH(h);
+  float *cur = buf0, *nxt = buf1;
+  int H = H1, W = W1;
+  for (int l = 0; l < nb; ++l) {
+    p.in = cur;
+    p.out = nxt;
+    p.wimg = g->wimg[l + 1];
+    p.dw_w = m.d_dw_w + (size_t)l * 9 * C;
+    p.bias = g->d_bias + (size_t)(l + 1) * C;
+    p.H = H;
+    p.W = W;
+    p.npix = B * (long long)H * W;
+    p.kvalid = g->kvalid[l + 1];
+    p.nchunks = g->nchunks[l + 1];
+    dscnn_gemm_kernel<1><<<grid_for(p.npix), kGT, smem_bytes, st>>>(p);
+    KWS_CHECK_LAUNCH(h);
+    const long long nborder = B * (long long)(2 * (W + 2) + 2 * H) * (C / 4);
+    long long gb = (nborder + 255) / 256;
+    if (gb > h->sm_count * 8LL) gb = h->sm_count * 8LL;
+    border_fill_kernel<<<(unsigned)gb, 256, 0, st>>>(nxt, g->d_border + (size_t)l * C, B, H + 2, W + 2, C);
+    KWS_CHECK_LAUNCH(h);
+    float* t = cur;
+    cur = nxt;
+    nxt = t;
+    H += 2;
+    W += 2;
+  }
+  *last_out = cur;
+  return 1;
+}
+
+}  // namespace kws

@@ -69,6 +69,24 @@ def test_fused_equals_layered(T, F, B):
     np.testing.assert_allclose(fused, want, rtol=1e-3, atol=1e-4)
 
 
+@pytest.mark.parametrize("channels,blocks,T,F,B", [(276, 5, 99, 40, 3), (64, 4, 99, 13, 9), (32, 2, 49, 26, 5),
+                                                  (100, 3, 31, 40, 2), (512, 1, 20, 12, 2)])
+def test_tensor_core_gemm_path_any_channels(channels, blocks, T, F, B):
+    """Layer-by-layer tcgen05 path (model_gemm.cu; BASELINE config 2 'DS-CNN-L' = 276 channels, 5 blocks)
+    against the layered fp32 kernels and the float64 oracle."""
+    sd = dscnn_ref.init_state_dict(channels=channels, num_blocks=blocks, seed=channels + blocks)
+    m = DepthwiseSeparableConv(channels=channels, num_blocks=blocks)
+    m.load_state_dict(sd)
+    m = m.cuda()
+    x = torch.randn(B, 1, T, F, generator=torch.Generator().manual_seed(B)) * 3.0
+    fast = m(x.cuda()).cpu().numpy()
+    m.set_kernel_path("layered")
+    layered = m(x.cuda()).cpu().numpy()
+    want = dscnn_ref.forward({k: v.double() for k, v in sd.items()}, x.double()).numpy()
+    np.testing.assert_allclose(layered, want, rtol=0, atol=5e-5)
+    np.testing.assert_allclose(fast, want, rtol=1e-3, atol=2e-4)
+
+
 def test_extension_channels_blocks():
     """'DS-CNN-L'-style generalisation (SURVEY a-X1): only channels/num_blocks change."""
     sd = dscnn_ref.init_state_dict(channels=96, num_blocks=5, seed=4)
