@@ -21,10 +21,12 @@
 
 namespace kws {
 
-constexpr int kGT = 256;                   // threads per CTA
+constexpr int kGT = 512;                   // threads per CTA
 constexpr int kGKC = 32;                   // K chunk (4 MMA k-steps)
-constexpr int kGSbo = (kGKC / 4) * 128;    // 8-row group pitch of A and B chunks
-constexpr int kGABytes = 16 * kGSbo;       // A chunk: 128 pixels x 32 k
+constexpr int kGSbo = (kGKC / 4) * 128;    // 8-row group pitch of the B (weight) chunks
+constexpr int kGLboA = 144;                // K-chunk pitch of the A chunks (bank spreading for the stencil stores)
+constexpr int kGSboA = (kGKC / 4) * kGLboA;
+constexpr int kGABytes = 16 * kGSboA;      // A chunk: 128 pixels x 32 k
 
 struct GemmParams {
   const float* in;     // MODE 1: [B,H,W,C] NHWC block input; MODE 0: features [B,T,F]
@@ -32,24 +34,28 @@ struct GemmParams {
   const float* wimg;   // weight chunks, tf32, K-major: [nchunks][npad/8][kGSbo bytes]
   const float* dw_w;   // MODE 1: [9][C] depthwise taps
   const float* bias;   // [C] epilogue bias
-  long long npix;      // B*H*W output (interior) pixels
-  int H, W, C, T, F;
+  long long B;
+  int H, W, C, T, F;   // H x W: output (interior) grid of the layer
+  int R, nbands;       // tile = R whole rows of one clip (R * W <= 128), nbands = ceil(H / R)
   int kvalid, npad, nh, nhalf, nchunks, tmem_cols;
 };
 
 template <int MODE>
 __global__ void __launch_bounds__(kGT, 1) dscnn_gemm_kernel(const GemmParams p) {
   extern __shared__ __align__(128) unsigned char smem[];
-  __shared__ __align__(8) unsigned long long s_bar[2];
+  __shared__ __align__(8) unsigned long long s_bar[4];  // [0,1] MMAs of buffer retired, [2,3] weight chunk landed
   __shared__ uint32_t s_tmem;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int bbytes = (p.npad / 8) * kGSbo;
   unsigned char* sA = smem;                      // [2][kGABytes]
   unsigned char* sB = smem + 2 * kGABytes;       // [2][bbytes]
-  const uint32_t bar0 = smem_u32(&s_bar[0]);
+  float* sW = reinterpret_cast<float*>(sB + 2 * (size_t)bbytes);  // [2][9][32] depthwise taps of the chunk
+  const uint32_t bar0 = smem_u32(&s_bar[0]), barB = smem_u32(&s_bar[2]);
   if (tid == 0) {
     mbar_init(bar0, 1);
     mbar_init(bar0 + 8, 1);
+    mbar_init(barB, 1);
+    mbar_init(barB + 8, 1);
     fence_mbar_init();
   }
   if (warp == 0) {
@@ -62,79 +68,116 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_gemm_kernel(const GemmParams p) 
   tc_fence_after();
   const uint32_t tmem = s_tmem;
   const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(p.nhalf >> 3) << 17) | ((128u >> 4) << 24);
-  const int H = p.H, W = p.W, C = p.C;
-  const int px = tid & 127, kg = tid >> 7;       // A-chunk ownership: pixel row, 16-wide half of the chunk
-  const long long ntiles = (p.npix + 127) / 128;
+  const int H = p.H, W = p.W, C = p.C, R = p.R;
+  const long long ntiles = p.B * p.nbands;
+  // MODE 1 ownership: channel quad q of the chunk, column x, row group rg (rows rg*RG .. of the band)
+  const int q = tid & 7, cx = tid >> 3, NG = 64 / W > 0 ? 64 / W : 1, RG = (R + NG - 1) / NG;
+  const int rg = cx / W, x = cx - rg * W;
+  // MODE 0 ownership: pixel row of the tile, 8-wide quarter of the chunk
+  const int px = tid & 127, kg = tid >> 7;
   uint32_t cnt = 0;                              // chunks issued so far: buffer = cnt & 1, its phase = cnt >> 1
 
   for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-    const long long gp = tile * 128 + px;
-    const bool valid = gp < p.npix;
-    int x = 0, y = 0;
-    long long b = 0;
-    if (valid) {
-      x = (int)(gp % W);
-      y = (int)((gp / W) % H);
-      b = gp / ((long long)W * H);
-    }
+    const long long b = tile / p.nbands;
+    const int r0 = (int)(tile - b * p.nbands) * R;
     for (int kc = 0; kc < p.nchunks; ++kc, ++cnt) {
       const int buf = cnt & 1;
       if (cnt >= 2) mbar_wait(bar0 + 8u * buf, ((cnt - 2) >> 1) & 1);  // the MMAs that read this buffer retired
-      {  // weight chunk -> shared memory
-        const uint4* src = reinterpret_cast<const uint4*>(p.wimg) + (size_t)kc * (bbytes / 16);
-        uint4* dst = reinterpret_cast<uint4*>(sB + (size_t)buf * bbytes);
-        for (int i = tid; i < bbytes / 16; i += kGT) dst[i] = __ldg(src + i);
+      if (tid == 0) {  // weight chunk: one TMA bulk copy
+        mbar_expect_tx(barB + 8u * buf, (uint32_t)bbytes);
+        tma_load_1d(smem_u32(sB + (size_t)buf * bbytes), reinterpret_cast<const unsigned char*>(p.wimg) + (size_t)kc * bbytes,
+                    (uint32_t)bbytes, barB + 8u * buf);
       }
-      unsigned char* arow = sA + buf * kGABytes + (px >> 3) * kGSbo + (px & 7) * 16;
+      unsigned char* abuf = sA + buf * kGABytes;
+      if (MODE == 1) {
+        if (tid < 9 * kGKC) {
+          const int t = tid / kGKC, kl = tid - t * kGKC, k = kc * kGKC + kl;
+          sW[buf * 9 * kGKC + tid] = k < C ? __ldg(p.dw_w + t * C + k) : 0.f;
+        }
+        __syncthreads();  // the chunk's depthwise taps are in shared memory
+        // depthwise 3x3 (zero padding 1) of channels k..k+3 down this thread's column: every input row is
+        // loaded once (3 coalesced float4 per row) and accumulated into the three output rows it feeds
+        const int k = kc * kGKC + 4 * q;
+        if (rg < NG && k < p.kvalid) {
+          float4 wv[9];
 #pragma unroll
-      for (int g4 = 0; g4 < 4; ++g4) {
-        const int kl = kg * 16 + g4 * 4, k = kc * kGKC + kl;
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (valid && k < p.kvalid) {
-          if (MODE == 1) {  // depthwise 3x3, zero padding 1, channels k..k+3
-#pragma unroll
-            for (int i = 0; i < 3; ++i) {
-              const int yy = y + i - 1;
-              if (yy < 0 || yy >= H) continue;
-#pragma unroll
-              for (int j = 0; j < 3; ++j) {
-                const int xx = x + j - 1;
-                if (xx < 0 || xx >= W) continue;
-                const float4 a = __ldg(reinterpret_cast<const float4*>(p.in + ((b * H + yy) * W + xx) * C + k));
-                const float4 w = __ldg(reinterpret_cast<const float4*>(p.dw_w + (i * 3 + j) * C + k));
-                v.x = fmaf(a.x, w.x, v.x);
-                v.y = fmaf(a.y, w.y, v.y);
-                v.z = fmaf(a.z, w.z, v.z);
-                v.w = fmaf(a.w, w.w, v.w);
-              }
+          for (int t = 0; t < 9; ++t) wv[t] = *reinterpret_cast<const float4*>(sW + (buf * 9 + t) * kGKC + 4 * q);
+          const int rl0 = rg * RG, rl1 = min(rl0 + RG, R);
+          float4 accP = make_float4(0.f, 0.f, 0.f, 0.f), accR = accP;  // output rows i-1 (two rows in) and i (one row in)
+          unsigned char* acol = abuf + q * kGLboA;
+          for (int i = rl0 - 1; i <= rl1; ++i) {  // input row r0 + i; finishes output row i - 1
+            const int yy = r0 + i;
+            float4 vm = make_float4(0.f, 0.f, 0.f, 0.f), v0 = vm, vp = vm;
+            if (yy >= 0 && yy < H) {
+              const float* rowp = p.in + ((b * H + yy) * W) * (long long)C + k;
+              v0 = __ldg(reinterpret_cast<const float4*>(rowp + (long long)x * C));
+              if (x > 0) vm = __ldg(reinterpret_cast<const float4*>(rowp + (long long)(x - 1) * C));
+              if (x + 1 < W) vp = __ldg(reinterpret_cast<const float4*>(rowp + (long long)(x + 1) * C));
             }
-          } else {  // im2col of the 10x10 stride-2 padding-2 window, taps k..k+3
-            float t4[4];
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const int kk = k + e, ki = kk / 10, kj = kk - 10 * ki;
-              const int fr = 2 * y - 2 + ki, fc = 2 * x - 2 + kj;
-              t4[e] = (kk < p.kvalid && fr >= 0 && fr < p.T && fc >= 0 && fc < p.F) ? __ldg(p.in + (b * p.T + fr) * p.F + fc) : 0.f;
+#define KWS_ROW3(acc, t0)                                                                                      \
+  acc.x = fmaf(vm.x, wv[t0].x, fmaf(v0.x, wv[t0 + 1].x, fmaf(vp.x, wv[t0 + 2].x, acc.x)));                     \
+  acc.y = fmaf(vm.y, wv[t0].y, fmaf(v0.y, wv[t0 + 1].y, fmaf(vp.y, wv[t0 + 2].y, acc.y)));                     \
+  acc.z = fmaf(vm.z, wv[t0].z, fmaf(v0.z, wv[t0 + 1].z, fmaf(vp.z, wv[t0 + 2].z, acc.z)));                     \
+  acc.w = fmaf(vm.w, wv[t0].w, fmaf(v0.w, wv[t0 + 1].w, fmaf(vp.w, wv[t0 + 2].w, acc.w)));
+            float4 o = accP;
+            KWS_ROW3(o, 6)          // input row i is the bottom row (taps 6..8) of output row i - 1
+            accP = accR;
+            KWS_ROW3(accP, 3)       // ... the middle row of output row i
+            accR = make_float4(0.f, 0.f, 0.f, 0.f);
+            KWS_ROW3(accR, 0)       // ... the top row of output row i + 1
+#undef KWS_ROW3
+            const int ro = i - 1;
+            if (ro >= rl0 && ro < rl1) {
+              const int pp = ro * W + x;
+              uint4 r;  // tf32 round-to-nearest: add half an ulp of the 10-bit mantissa, the MMA drops the low 13 bits
+              const bool live = r0 + ro < H;
+              r.x = live ? __float_as_uint(o.x) + 0x1000u : 0u;
+              r.y = live ? __float_as_uint(o.y) + 0x1000u : 0u;
+              r.z = live ? __float_as_uint(o.z) + 0x1000u : 0u;
+              r.w = live ? __float_as_uint(o.w) + 0x1000u : 0u;
+              *reinterpret_cast<uint4*>(acol + (pp >> 3) * kGSboA + (pp & 7) * 16) = r;
             }
-            v = make_float4(t4[0], t4[1], t4[2], t4[3]);
+          }
+        } else if (rg < NG) {  // K padding beyond the channel count
+          const int rl0 = rg * RG, rl1 = min(rl0 + RG, R);
+          for (int ro = rl0; ro < rl1; ++ro) {
+            const int pp = ro * W + x;
+            *reinterpret_cast<uint4*>(abuf + q * kGLboA + (pp >> 3) * kGSboA + (pp & 7) * 16) = make_uint4(0, 0, 0, 0);
           }
         }
-        uint4 r;  // tf32 round-to-nearest: add half an ulp of the 10-bit mantissa, the MMA drops the low 13 bits
-        r.x = __float_as_uint(v.x) + 0x1000u;
-        r.y = __float_as_uint(v.y) + 0x1000u;
-        r.z = __float_as_uint(v.z) + 0x1000u;
-        r.w = __float_as_uint(v.w) + 0x1000u;
-        *reinterpret_cast<uint4*>(arow + (kl >> 2) * 128) = r;
+      } else {  // im2col of the 10x10 stride-2 padding-2 window
+        const int rl = px / W, xq = px - rl * W, y = r0 + rl;
+        const bool valid = rl < R && y < H;
+        unsigned char* arow = abuf + (px >> 3) * kGSboA + (px & 7) * 16;
+#pragma unroll
+        for (int g4 = 0; g4 < 2; ++g4) {
+          const int kl = kg * 8 + g4 * 4, k = kc * kGKC + kl;
+          float t4[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int kk = k + e, ki = kk / 10, kj = kk - 10 * ki;
+            const int fr = 2 * y - 2 + ki, fc = 2 * xq - 2 + kj;
+            t4[e] = (valid && kk < p.kvalid && fr >= 0 && fr < p.T && fc >= 0 && fc < p.F) ? __ldg(p.in + (b * p.T + fr) * p.F + fc)
+                                                                                            : 0.f;
+          }
+          uint4 r;
+          r.x = __float_as_uint(t4[0]) + 0x1000u;
+          r.y = __float_as_uint(t4[1]) + 0x1000u;
+          r.z = __float_as_uint(t4[2]) + 0x1000u;
+          r.w = __float_as_uint(t4[3]) + 0x1000u;
+          *reinterpret_cast<uint4*>(arow + (kl >> 2) * kGLboA) = r;
+        }
       }
       fence_proxy_async();
       __syncthreads();
       if (tid == 0) {
+        mbar_wait(barB + 8u * buf, (cnt >> 1) & 1);
         tc_fence_after();
-        const uint32_t ab = smem_u32(sA + buf * kGABytes), bb = smem_u32(sB + (size_t)buf * bbytes);
+        const uint32_t ab = smem_u32(abuf), bb = smem_u32(sB + (size_t)buf * bbytes);
 #pragma unroll 1
         for (int ks = 0; ks < kGKC / 8; ++ks)
           for (int hf = 0; hf < p.nh; ++hf)
-            tc_mma_tf32(tmem + (uint32_t)(hf * p.nhalf), umma_desc(ab + ks * 256u, 128u, kGSbo),
+            tc_mma_tf32(tmem + (uint32_t)(hf * p.nhalf), umma_desc(ab + ks * 2u * kGLboA, kGLboA, kGSboA),
                         umma_desc(bb + (uint32_t)(hf * (p.nhalf / 8)) * kGSbo + ks * 256u, 128u, kGSbo), idesc,
                         (kc > 0 || ks > 0) ? 1u : 0u);
         tc_commit(bar0 + 8u * buf);
@@ -145,24 +188,18 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_gemm_kernel(const GemmParams p) 
       mbar_wait(bar0 + 8u * (last & 1), (last >> 1) & 1);
       tc_fence_after();
     }
-    {  // epilogue: lane = pixel row, warp / 4 = column half
+    if (warp < 8) {  // epilogue: lane = pixel row of the tile, warp / 4 = column half
       const int row = (warp & 3) * 32 + lane, chalf = warp >> 2;
-      const long long gq = tile * 128 + row;
+      const int rl = row / W, xq = row - rl * W, y = r0 + rl;
       float* orow = nullptr;
-      if (gq < p.npix) {
-        if (MODE == 1) {
-          const int xq = (int)(gq % W), yq = (int)((gq / W) % H);
-          const long long bq = gq / ((long long)W * H);
-          orow = p.out + ((bq * (H + 2) + yq + 1) * (W + 2) + xq + 1) * C;
-        } else {
-          orow = p.out + gq * C;
-        }
-      }
+      if (rl < R && y < H)
+        orow = MODE == 1 ? p.out + ((b * (H + 2) + y + 1) * (W + 2) + xq + 1) * (long long)C
+                         : p.out + ((b * H + y) * W + xq) * (long long)C;
       const int c0 = chalf * (p.npad / 2), c1 = c0 + p.npad / 2;
       const uint32_t taddr = tmem + ((uint32_t)((warp & 3) * 32) << 16);
       for (int c = c0; c < c1; c += 16) {
-        float q[16];
-        tc_ld16(taddr + (uint32_t)c, q);
+        float v[16];
+        tc_ld16(taddr + (uint32_t)c, v);
         tc_wait_ld();
         if (orow) {
 #pragma unroll
@@ -170,8 +207,8 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_gemm_kernel(const GemmParams p) 
             if (c + e < C) {
               const float4 bz = __ldg(reinterpret_cast<const float4*>(p.bias + c + e));
               *reinterpret_cast<float4*>(orow + c + e) =
-                  make_float4(fmaxf(q[e] + bz.x, 0.f), fmaxf(q[e + 1] + bz.y, 0.f), fmaxf(q[e + 2] + bz.z, 0.f),
-                              fmaxf(q[e + 3] + bz.w, 0.f));
+                  make_float4(fmaxf(v[e] + bz.x, 0.f), fmaxf(v[e + 1] + bz.y, 0.f), fmaxf(v[e + 2] + bz.z, 0.f),
+                              fmaxf(v[e + 3] + bz.w, 0.f));
             }
           }
         }
@@ -301,7 +338,8 @@ int launch_dscnn_gemm(kws_handle_t h, const float* feats_dev, int64_t B, int T, 
   if (!g) return 0;
   const int C = g->C, nb = g->nb;
   const int H1 = (T + 4 - 10) / 2 + 1, W1 = (F + 4 - 10) / 2 + 1;
-  const size_t smem_bytes = 2 * kGABytes + 2 * (size_t)(g->npad / 8) * kGSbo;
+  if (W1 + 2 * nb > 64) return 0;  // one thread column per pixel column (64 columns per CTA)
+  const size_t smem_bytes = 2 * kGABytes + 2 * (size_t)(g->npad / 8) * kGSbo + 2 * 9 * kGKC * 4;
   KWS_CUDA(cudaFuncSetAttribute(dscnn_gemm_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
   KWS_CUDA(cudaFuncSetAttribute(dscnn_gemm_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
   const int ctas_per_sm = (g->tmem_cols <= 256 && smem_bytes <= 100 * 1024) ? 2 : 1;
@@ -313,8 +351,14 @@ int launch_dscnn_gemm(kws_handle_t h, const float* feats_dev, int64_t B, int T, 
   p.nh = g->nh;
   p.nhalf = g->nhalf;
   p.tmem_cols = g->tmem_cols;
-  auto grid_for = [&](long long npix) {
-    long long t = (npix + 127) / 128, gmax = (long long)h->sm_count * ctas_per_sm;
+  p.B = B;
+  auto set_grid = [&](int Hh, int Ww) {  // tile = R whole rows; returns the grid size
+    p.H = Hh;
+    p.W = Ww;
+    p.R = 128 / Ww > 0 ? 128 / Ww : 1;
+    if (p.R > Hh) p.R = Hh;
+    p.nbands = (Hh + p.R - 1) / p.R;
+    const long long t = B * p.nbands, gmax = (long long)h->sm_count * ctas_per_sm;
     return (unsigned)(t < gmax ? t : gmax);
   };
   // conv1
@@ -323,12 +367,9 @@ int launch_dscnn_gemm(kws_handle_t h, const float* feats_dev, int64_t B, int T, 
   p.wimg = g->wimg[0];
   p.dw_w = nullptr;
   p.bias = g->d_bias;
-  p.H = H1;
-  p.W = W1;
-  p.npix = B * (long long)H1 * W1;
   p.kvalid = g->kvalid[0];
   p.nchunks = g->nchunks[0];
-  dscnn_gemm_kernel<0><<<grid_for(p.npix), kGT, smem_bytes, st>>>(p);
+  dscnn_gemm_kernel<0><<<set_grid(H1, W1), kGT, smem_bytes, st>>>(p);
   KWS_CHECK_LAUNCH(h);
   float *cur = buf0, *nxt = buf1;
   int H = H1, W = W1;
@@ -338,12 +379,9 @@ int launch_dscnn_gemm(kws_handle_t h, const float* feats_dev, int64_t B, int T, 
     p.wimg = g->wimg[l + 1];
     p.dw_w = m.d_dw_w + (size_t)l * 9 * C;
     p.bias = g->d_bias + (size_t)(l + 1) * C;
-    p.H = H;
-    p.W = W;
-    p.npix = B * (long long)H * W;
     p.kvalid = g->kvalid[l + 1];
     p.nchunks = g->nchunks[l + 1];
-    dscnn_gemm_kernel<1><<<grid_for(p.npix), kGT, smem_bytes, st>>>(p);
+    dscnn_gemm_kernel<1><<<set_grid(H, W), kGT, smem_bytes, st>>>(p);
     KWS_CHECK_LAUNCH(h);
     const long long nborder = B * (long long)(2 * (W + 2) + 2 * H) * (C / 4);
     long long gb = (nborder + 255) / 256;
