@@ -49,7 +49,7 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_gemm_kernel(const GemmParams p) 
   const int bbytes = (p.npad / 8) * kGSbo;
   unsigned char* sA = smem;                      // [2][kGABytes]
   unsigned char* sB = smem + 2 * kGABytes;       // [2][bbytes]
-  float* sW = reinterpret_cast<float*>(sB + 2 * (size_t)bbytes);  // [2][9][32] depthwise taps of the chunk
+  float* sW = reinterpret_cast<float*>(sB + 2 * (size_t)bbytes);  // [9][nchunks * 32] depthwise taps of the layer
   const uint32_t bar0 = smem_u32(&s_bar[0]), barB = smem_u32(&s_bar[2]);
   if (tid == 0) {
     mbar_init(bar0, 1);
@@ -63,6 +63,12 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_gemm_kernel(const GemmParams p) 
                  "r"((uint32_t)p.tmem_cols));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
   }
+  const int kpad = p.nchunks * kGKC;
+  if (MODE == 1)
+    for (int i = tid; i < 9 * kpad; i += kGT) {
+      const int t = i / kpad, k = i - t * kpad;
+      sW[i] = k < p.C ? __ldg(p.dw_w + t * p.C + k) : 0.f;
+    }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -90,47 +96,45 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_gemm_kernel(const GemmParams p) 
       }
       unsigned char* abuf = sA + buf * kGABytes;
       if (MODE == 1) {
-        if (tid < 9 * kGKC) {
-          const int t = tid / kGKC, kl = tid - t * kGKC, k = kc * kGKC + kl;
-          sW[buf * 9 * kGKC + tid] = k < C ? __ldg(p.dw_w + t * C + k) : 0.f;
-        }
-        __syncthreads();  // the chunk's depthwise taps are in shared memory
-        // depthwise 3x3 (zero padding 1) of channels k..k+3 down this thread's column: every input row is
-        // loaded once (3 coalesced float4 per row) and accumulated into the three output rows it feeds
+        // depthwise 3x3 (zero padding 1) of channels k..k+3 down this thread's column: every input row of the
+        // row group (<= 3 output rows + 2 halo rows) is fetched up front -- 3 coalesced float4 per row, all in
+        // flight together -- and accumulated into the output rows it feeds
         const int k = kc * kGKC + 4 * q;
         if (rg < NG && k < p.kvalid) {
-          float4 wv[9];
-#pragma unroll
-          for (int t = 0; t < 9; ++t) wv[t] = *reinterpret_cast<const float4*>(sW + (buf * 9 + t) * kGKC + 4 * q);
           const int rl0 = rg * RG, rl1 = min(rl0 + RG, R);
-          float4 accP = make_float4(0.f, 0.f, 0.f, 0.f), accR = accP;  // output rows i-1 (two rows in) and i (one row in)
-          unsigned char* acol = abuf + q * kGLboA;
-          for (int i = rl0 - 1; i <= rl1; ++i) {  // input row r0 + i; finishes output row i - 1
-            const int yy = r0 + i;
-            float4 vm = make_float4(0.f, 0.f, 0.f, 0.f), v0 = vm, vp = vm;
-            if (yy >= 0 && yy < H) {
+          float4 vin[5][3];
+#pragma unroll
+          for (int ii = 0; ii < 5; ++ii) {
+            const int yy = r0 + rl0 - 1 + ii;
+            const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+            vin[ii][0] = vin[ii][1] = vin[ii][2] = z;
+            if (ii <= rl1 - rl0 + 1 && yy >= 0 && yy < H) {
               const float* rowp = p.in + ((b * H + yy) * W) * (long long)C + k;
-              v0 = __ldg(reinterpret_cast<const float4*>(rowp + (long long)x * C));
-              if (x > 0) vm = __ldg(reinterpret_cast<const float4*>(rowp + (long long)(x - 1) * C));
-              if (x + 1 < W) vp = __ldg(reinterpret_cast<const float4*>(rowp + (long long)(x + 1) * C));
+              vin[ii][1] = __ldg(reinterpret_cast<const float4*>(rowp + (long long)x * C));
+              if (x > 0) vin[ii][0] = __ldg(reinterpret_cast<const float4*>(rowp + (long long)(x - 1) * C));
+              if (x + 1 < W) vin[ii][2] = __ldg(reinterpret_cast<const float4*>(rowp + (long long)(x + 1) * C));
             }
-#define KWS_ROW3(acc, t0)                                                                                      \
-  acc.x = fmaf(vm.x, wv[t0].x, fmaf(v0.x, wv[t0 + 1].x, fmaf(vp.x, wv[t0 + 2].x, acc.x)));                     \
-  acc.y = fmaf(vm.y, wv[t0].y, fmaf(v0.y, wv[t0 + 1].y, fmaf(vp.y, wv[t0 + 2].y, acc.y)));                     \
-  acc.z = fmaf(vm.z, wv[t0].z, fmaf(v0.z, wv[t0 + 1].z, fmaf(vp.z, wv[t0 + 2].z, acc.z)));                     \
-  acc.w = fmaf(vm.w, wv[t0].w, fmaf(v0.w, wv[t0 + 1].w, fmaf(vp.w, wv[t0 + 2].w, acc.w)));
-            float4 o = accP;
-            KWS_ROW3(o, 6)          // input row i is the bottom row (taps 6..8) of output row i - 1
-            accP = accR;
-            KWS_ROW3(accP, 3)       // ... the middle row of output row i
-            accR = make_float4(0.f, 0.f, 0.f, 0.f);
-            KWS_ROW3(accR, 0)       // ... the top row of output row i + 1
-#undef KWS_ROW3
-            const int ro = i - 1;
-            if (ro >= rl0 && ro < rl1) {
-              const int pp = ro * W + x;
+          }
+          unsigned char* acol = abuf + q * kGLboA;
+          const float* wq = sW + kc * kGKC + 4 * q;
+#pragma unroll
+          for (int ro = 0; ro < 3; ++ro) {  // output row rl0 + ro from input rows ro, ro+1, ro+2 of the group
+            if (rl0 + ro < rl1) {
+              float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+              for (int i = 0; i < 3; ++i)
+#pragma unroll
+                for (int j = 0; j < 3; ++j) {
+                  const float4 w = *reinterpret_cast<const float4*>(wq + (i * 3 + j) * kpad);
+                  const float4 a = vin[ro + i][j];
+                  o.x = fmaf(a.x, w.x, o.x);
+                  o.y = fmaf(a.y, w.y, o.y);
+                  o.z = fmaf(a.z, w.z, o.z);
+                  o.w = fmaf(a.w, w.w, o.w);
+                }
+              const int pp = (rl0 + ro) * W + x;
               uint4 r;  // tf32 round-to-nearest: add half an ulp of the 10-bit mantissa, the MMA drops the low 13 bits
-              const bool live = r0 + ro < H;
+              const bool live = r0 + rl0 + ro < H;
               r.x = live ? __float_as_uint(o.x) + 0x1000u : 0u;
               r.y = live ? __float_as_uint(o.y) + 0x1000u : 0u;
               r.z = live ? __float_as_uint(o.z) + 0x1000u : 0u;
@@ -339,7 +343,7 @@ int launch_dscnn_gemm(kws_handle_t h, const float* feats_dev, int64_t B, int T, 
   const int C = g->C, nb = g->nb;
   const int H1 = (T + 4 - 10) / 2 + 1, W1 = (F + 4 - 10) / 2 + 1;
   if (W1 + 2 * nb > 64) return 0;  // one thread column per pixel column (64 columns per CTA)
-  const size_t smem_bytes = 2 * kGABytes + 2 * (size_t)(g->npad / 8) * kGSbo + 2 * 9 * kGKC * 4;
+  const size_t smem_bytes = 2 * kGABytes + 2 * (size_t)(g->npad / 8) * kGSbo + (size_t)9 * ((C + kGKC - 1) / kGKC * kGKC) * 4;
   KWS_CUDA(cudaFuncSetAttribute(dscnn_gemm_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
   KWS_CUDA(cudaFuncSetAttribute(dscnn_gemm_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
   const int ctas_per_sm = (g->tmem_cols <= 256 && smem_bytes <= 100 * 1024) ? 2 : 1;
