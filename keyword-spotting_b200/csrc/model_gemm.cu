@@ -37,7 +37,7 @@ struct GemmParams {
   long long B;
   int H, W, C, T, F;   // H x W: output (interior) grid of the layer
   int R, nbands;       // tile = R whole rows of one clip (R * W <= 128), nbands = ceil(H / R)
-  int kvalid, npad, nh, nhalf, nchunks, tmem_cols;
+  int kvalid, npad, nh, nhalf, nchunks, tmem_cols, patch_bytes;
 };
 
 template <int MODE>
@@ -77,22 +77,71 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_gemm_kernel(const GemmParams p) 
   const int H = p.H, W = p.W, C = p.C, R = p.R;
   const long long ntiles = p.B * p.nbands;
   // MODE 1 ownership: channel quad q of the chunk, column x, row group rg (rows rg*RG .. of the band)
-  const int q = tid & 7, cx = tid >> 3, NG = 64 / W > 0 ? 64 / W : 1, RG = (R + NG - 1) / NG;
+  // warps 0..14 produce (stage, stencil, im2col); warp 15 only issues TMA / MMA, so that issue latency
+  // (descriptor setup, the weight-chunk wait) never delays a producer's arrival at the chunk barrier
+  constexpr int kProd = kGT - 32, kIssuer = kGT - 32;
+  const bool producer = tid < kProd;
+  const int q = tid & 7, cx = tid >> 3, NG = (kProd / 8) / W > 0 ? (kProd / 8) / W : 1, RG = (R + NG - 1) / NG;
   const int rg = cx / W, x = cx - rg * W;
-  // MODE 0 ownership: pixel row of the tile, 8-wide quarter of the chunk
-  const int px = tid & 127, kg = tid >> 7;
   uint32_t cnt = 0;                              // chunks issued so far: buffer = cnt & 1, its phase = cnt >> 1
+
+  // MODE 1 input staging: the (R+2) x W x 32-channel input patch of a chunk is copied to shared memory with
+  // cp.async two chunks ahead of its use (3 patch buffers), so HBM/L2 latency is off the critical path and
+  // every input element is fetched once per chunk (the 3x3 reuse happens in shared memory).
+  unsigned char* sP = reinterpret_cast<unsigned char*>(sW + 9 * kpad);
+  const int patch_bytes = p.patch_bytes;
+  const long long my_tiles = blockIdx.x < ntiles ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  const long long total_chunks = my_tiles * p.nchunks;
+  // this thread's (up to 4) 16-byte pieces of a patch are the same for every chunk: patch row, global
+  // offset relative to the first patch row, channel quad
+  constexpr int kPieces = 4;
+  int pf_row[kPieces], pf_off[kPieces];
+  const int np = (R + 2) * W * 8;
+#pragma unroll
+  for (int i = 0; i < kPieces; ++i) {
+    const int e = tid + i * kProd, pxl = e >> 3, ii = pxl / W, xx = pxl - ii * W;
+    pf_row[i] = (producer && e < np) ? ii : -1;
+    pf_off[i] = (ii * W + xx) * C + 4 * (e & 7);
+  }
+  auto prefetch_patch = [&](long long fc) {  // flat chunk index of this CTA
+    if (MODE == 1 && producer && fc < total_chunks) {
+      const long long lt = fc / p.nchunks;
+      const int kcp = (int)(fc - lt * p.nchunks);
+      const long long tl = blockIdx.x + lt * gridDim.x, bp = tl / p.nbands;
+      const int rp = (int)(tl - bp * p.nbands) * R;
+      const uint32_t dst0 = smem_u32(sP + (size_t)(fc % 3) * patch_bytes) + (uint32_t)tid * 16u;
+      const float* base = p.in + ((bp * H + rp - 1) * W) * (long long)C + kcp * kGKC;  // row rp - 1 (may lie outside)
+      const int kq = kcp * kGKC + 4 * (tid & 7);
+#pragma unroll
+      for (int i = 0; i < kPieces; ++i) {
+        if (pf_row[i] >= 0) {
+          const int yy = rp - 1 + pf_row[i];
+          const bool ok = yy >= 0 && yy < H && kq < C;
+          const float* src = ok ? base + pf_off[i] : p.in;
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst0 + (uint32_t)(i * kProd) * 16u), "l"(src),
+                       "r"(ok ? 16 : 0)
+                       : "memory");
+        }
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");  // always commit: keeps the group count in step
+  };
+  prefetch_patch(0);
+  prefetch_patch(1);
+  asm volatile("cp.async.wait_group 1;" ::: "memory");
+  __syncthreads();
+  long long fchunk = 0;
 
   for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const long long b = tile / p.nbands;
     const int r0 = (int)(tile - b * p.nbands) * R;
-    for (int kc = 0; kc < p.nchunks; ++kc, ++cnt) {
+    for (int kc = 0; kc < p.nchunks; ++kc, ++cnt, ++fchunk) {
       const int buf = cnt & 1;
+      prefetch_patch(fchunk + 2);
       if (cnt >= 2) mbar_wait(bar0 + 8u * buf, ((cnt - 2) >> 1) & 1);  // the MMAs that read this buffer retired
-      if (tid == 0) {  // weight chunk: one TMA bulk copy
-        mbar_expect_tx(barB + 8u * buf, (uint32_t)bbytes);
-        tma_load_1d(smem_u32(sB + (size_t)buf * bbytes), reinterpret_cast<const unsigned char*>(p.wimg) + (size_t)kc * bbytes,
-                    (uint32_t)bbytes, barB + 8u * buf);
+      if (tid == kIssuer && cnt == 0) {  // first weight chunk (later ones are requested one chunk ahead, see below)
+        mbar_expect_tx(barB, (uint32_t)bbytes);
+        tma_load_1d(smem_u32(sB), p.wimg, (uint32_t)bbytes, barB);
       }
       unsigned char* abuf = sA + buf * kGABytes;
       if (MODE == 1) {
@@ -100,38 +149,43 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_gemm_kernel(const GemmParams p) 
         // row group (<= 3 output rows + 2 halo rows) is fetched up front -- 3 coalesced float4 per row, all in
         // flight together -- and accumulated into the output rows it feeds
         const int k = kc * kGKC + 4 * q;
-        if (rg < NG && k < p.kvalid) {
+        if (producer && rg < NG && k < p.kvalid) {
           const int rl0 = rg * RG, rl1 = min(rl0 + RG, R);
+          const float4* patch = reinterpret_cast<const float4*>(sP + (size_t)(fchunk % 3) * patch_bytes);
           float4 vin[5][3];
 #pragma unroll
           for (int ii = 0; ii < 5; ++ii) {
-            const int yy = r0 + rl0 - 1 + ii;
             const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
             vin[ii][0] = vin[ii][1] = vin[ii][2] = z;
-            if (ii <= rl1 - rl0 + 1 && yy >= 0 && yy < H) {
-              const float* rowp = p.in + ((b * H + yy) * W) * (long long)C + k;
-              vin[ii][1] = __ldg(reinterpret_cast<const float4*>(rowp + (long long)x * C));
-              if (x > 0) vin[ii][0] = __ldg(reinterpret_cast<const float4*>(rowp + (long long)(x - 1) * C));
-              if (x + 1 < W) vin[ii][2] = __ldg(reinterpret_cast<const float4*>(rowp + (long long)(x + 1) * C));
+            if (ii <= rl1 - rl0 + 1) {  // patch row rl0 + ii is input row r0 + rl0 - 1 + ii (zero-filled outside the image)
+              const float4* prow = patch + ((rl0 + ii) * W + x) * 8 + q;
+              vin[ii][1] = prow[0];
+              if (x > 0) vin[ii][0] = prow[-8];
+              if (x + 1 < W) vin[ii][2] = prow[8];
             }
           }
           unsigned char* acol = abuf + q * kGLboA;
           const float* wq = sW + kc * kGKC + 4 * q;
+          V wlo[9], whi[9];  // taps of channels (k, k+1) and (k+2, k+3): packed f32x2 FMAs over channel pairs
+#pragma unroll
+          for (int t = 0; t < 9; ++t) {
+            const float4 w = *reinterpret_cast<const float4*>(wq + t * kpad);
+            wlo[t] = make_float2(w.x, w.y);
+            whi[t] = make_float2(w.z, w.w);
+          }
 #pragma unroll
           for (int ro = 0; ro < 3; ++ro) {  // output row rl0 + ro from input rows ro, ro+1, ro+2 of the group
             if (rl0 + ro < rl1) {
-              float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+              V olo = fsplat(0.f), ohi = fsplat(0.f);
 #pragma unroll
               for (int i = 0; i < 3; ++i)
 #pragma unroll
                 for (int j = 0; j < 3; ++j) {
-                  const float4 w = *reinterpret_cast<const float4*>(wq + (i * 3 + j) * kpad);
                   const float4 a = vin[ro + i][j];
-                  o.x = fmaf(a.x, w.x, o.x);
-                  o.y = fmaf(a.y, w.y, o.y);
-                  o.z = fmaf(a.z, w.z, o.z);
-                  o.w = fmaf(a.w, w.w, o.w);
+                  olo = ffma(make_float2(a.x, a.y), wlo[i * 3 + j], olo);
+                  ohi = ffma(make_float2(a.z, a.w), whi[i * 3 + j], ohi);
                 }
+              const float4 o = make_float4(olo.x, olo.y, ohi.x, ohi.y);
               const int pp = (rl0 + ro) * W + x;
               uint4 r;  // tf32 round-to-nearest: add half an ulp of the 10-bit mantissa, the MMA drops the low 13 bits
               const bool live = r0 + rl0 + ro < H;
@@ -142,39 +196,43 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_gemm_kernel(const GemmParams p) 
               *reinterpret_cast<uint4*>(acol + (pp >> 3) * kGSboA + (pp & 7) * 16) = r;
             }
           }
-        } else if (rg < NG) {  // K padding beyond the channel count
+        } else if (producer && rg < NG) {  // K padding beyond the channel count
           const int rl0 = rg * RG, rl1 = min(rl0 + RG, R);
           for (int ro = rl0; ro < rl1; ++ro) {
             const int pp = ro * W + x;
             *reinterpret_cast<uint4*>(abuf + q * kGLboA + (pp >> 3) * kGSboA + (pp & 7) * 16) = make_uint4(0, 0, 0, 0);
           }
         }
-      } else {  // im2col of the 10x10 stride-2 padding-2 window
-        const int rl = px / W, xq = px - rl * W, y = r0 + rl;
-        const bool valid = rl < R && y < H;
-        unsigned char* arow = abuf + (px >> 3) * kGSboA + (px & 7) * 16;
+      } else if (producer) {  // im2col of the 10x10 stride-2 padding-2 window: item = (pixel row, 8-wide K slice)
+        for (int item = tid; item < 512; item += kProd) {
+          const int px = item & 127, kg = item >> 7;
+          const int rl = px / W, xq = px - rl * W, y = r0 + rl;
+          const bool valid = rl < R && y < H;
+          unsigned char* arow = abuf + (px >> 3) * kGSboA + (px & 7) * 16;
 #pragma unroll
-        for (int g4 = 0; g4 < 2; ++g4) {
-          const int kl = kg * 8 + g4 * 4, k = kc * kGKC + kl;
-          float t4[4];
+          for (int g4 = 0; g4 < 2; ++g4) {
+            const int kl = kg * 8 + g4 * 4, k = kc * kGKC + kl;
+            float t4[4];
 #pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const int kk = k + e, ki = kk / 10, kj = kk - 10 * ki;
-            const int fr = 2 * y - 2 + ki, fc = 2 * xq - 2 + kj;
-            t4[e] = (valid && kk < p.kvalid && fr >= 0 && fr < p.T && fc >= 0 && fc < p.F) ? __ldg(p.in + (b * p.T + fr) * p.F + fc)
-                                                                                            : 0.f;
+            for (int e = 0; e < 4; ++e) {
+              const int kk = k + e, ki = kk / 10, kj = kk - 10 * ki;
+              const int fr = 2 * y - 2 + ki, fc = 2 * xq - 2 + kj;
+              t4[e] = (valid && kk < p.kvalid && fr >= 0 && fr < p.T && fc >= 0 && fc < p.F) ? __ldg(p.in + (b * p.T + fr) * p.F + fc)
+                                                                                              : 0.f;
+            }
+            uint4 r;
+            r.x = __float_as_uint(t4[0]) + 0x1000u;
+            r.y = __float_as_uint(t4[1]) + 0x1000u;
+            r.z = __float_as_uint(t4[2]) + 0x1000u;
+            r.w = __float_as_uint(t4[3]) + 0x1000u;
+            *reinterpret_cast<uint4*>(arow + (kl >> 2) * kGLboA) = r;
           }
-          uint4 r;
-          r.x = __float_as_uint(t4[0]) + 0x1000u;
-          r.y = __float_as_uint(t4[1]) + 0x1000u;
-          r.z = __float_as_uint(t4[2]) + 0x1000u;
-          r.w = __float_as_uint(t4[3]) + 0x1000u;
-          *reinterpret_cast<uint4*>(arow + (kl >> 2) * kGLboA) = r;
         }
       }
       fence_proxy_async();
+      asm volatile("cp.async.wait_group 1;" ::: "memory");  // this thread's share of the NEXT chunk's patch has landed
       __syncthreads();
-      if (tid == 0) {
+      if (tid == kIssuer) {
         mbar_wait(barB + 8u * buf, (cnt >> 1) & 1);
         tc_fence_after();
         const uint32_t ab = smem_u32(abuf), bb = smem_u32(sB + (size_t)buf * bbytes);
@@ -185,6 +243,15 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_gemm_kernel(const GemmParams p) 
                         umma_desc(bb + (uint32_t)(hf * (p.nhalf / 8)) * kGSbo + ks * 256u, 128u, kGSbo), idesc,
                         (kc > 0 || ks > 0) ? 1u : 0u);
         tc_commit(bar0 + 8u * buf);
+        // request the NEXT chunk's weights now (TMA bulk copy), a full chunk ahead of their use: their buffer
+        // is free once the MMAs of chunk cnt - 1 have retired, which happened while this chunk was produced
+        if (fchunk + 1 < total_chunks) {
+          const int nb2 = buf ^ 1, kn = kc + 1 < p.nchunks ? kc + 1 : 0;
+          if (cnt >= 1) mbar_wait(bar0 + 8u * nb2, ((cnt - 1) >> 1) & 1);
+          mbar_expect_tx(barB + 8u * nb2, (uint32_t)bbytes);
+          tma_load_1d(smem_u32(sB + (size_t)nb2 * bbytes), reinterpret_cast<const unsigned char*>(p.wimg) + (size_t)kn * bbytes,
+                      (uint32_t)bbytes, barB + 8u * nb2);
+        }
       }
     }
     {  // all MMAs of the tile have retired when the last chunk's commit arrives
@@ -342,8 +409,18 @@ int launch_dscnn_gemm(kws_handle_t h, const float* feats_dev, int64_t B, int T, 
   if (!g) return 0;
   const int C = g->C, nb = g->nb;
   const int H1 = (T + 4 - 10) / 2 + 1, W1 = (F + 4 - 10) / 2 + 1;
-  if (W1 + 2 * nb > 64) return 0;  // one thread column per pixel column (64 columns per CTA)
-  const size_t smem_bytes = 2 * kGABytes + 2 * (size_t)(g->npad / 8) * kGSbo + (size_t)9 * ((C + kGKC - 1) / kGKC * kGKC) * 4;
+  if (W1 + 2 * nb > 60) return 0;  // one thread column per pixel column (60 producer columns per CTA)
+  int patch_bytes = 0;  // largest (R + 2) x W x 32-channel input patch over the layers
+  for (int l = 0; l < nb; ++l) {
+    const int Ww = W1 + 2 * l, Hh = H1 + 2 * l;
+    int Rr = 128 / Ww > 0 ? 128 / Ww : 1;
+    if (Rr > Hh) Rr = Hh;
+    const int pb = (Rr + 2) * Ww * 128;
+    if (pb > patch_bytes) patch_bytes = pb;
+  }
+  const size_t smem_bytes = 2 * kGABytes + 2 * (size_t)(g->npad / 8) * kGSbo + (size_t)9 * ((C + kGKC - 1) / kGKC * kGKC) * 4 +
+                            (size_t)3 * patch_bytes;
+  if (smem_bytes > 227 * 1024) return 0;
   KWS_CUDA(cudaFuncSetAttribute(dscnn_gemm_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
   KWS_CUDA(cudaFuncSetAttribute(dscnn_gemm_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
   const int ctas_per_sm = (g->tmem_cols <= 256 && smem_bytes <= 100 * 1024) ? 2 : 1;
@@ -355,6 +432,7 @@ int launch_dscnn_gemm(kws_handle_t h, const float* feats_dev, int64_t B, int T, 
   p.nh = g->nh;
   p.nhalf = g->nhalf;
   p.tmem_cols = g->tmem_cols;
+  p.patch_bytes = patch_bytes;
   p.B = B;
   auto set_grid = [&](int Hh, int Ww) {  // tile = R whole rows; returns the grid size
     p.H = Hh;
