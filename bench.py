@@ -308,7 +308,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--clips", type=int, default=65536, help="clips per GPU per step")
-    ap.add_argument("--e2e-clips", type=int, default=16384, help="clips per step of the host-buffer path")
+    ap.add_argument("--e2e-clips", type=int, default=32768, help="clips per step of the host-buffer path")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
