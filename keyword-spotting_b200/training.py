@@ -79,7 +79,17 @@ class KWSTrainStep:
             raise ModelError("kws_b200 runs on CUDA devices only (no CPU fallback)")
         self._idx = self.device.index if self.device.index is not None else torch.cuda.current_device()
         self.model = model.to(self.device)
-        self._h = self.model.native_handle(self.device)
+        # a native handle of its own: the step repacks the flat parameters into this handle's kernel
+        # layouts every iteration, which must not disturb the weights the module's inference handle holds
+        lib = _native.lib()
+        self._h = _native.Handle(self._idx)
+        _native.check(lib.kws_model_create(self._h.ptr, model.num_classes, model.channels, model.num_blocks), ModelError)
+        for name, t in self.model.state_dict().items():
+            a = t.detach().to("cpu", torch.float32).contiguous()
+            shape = (C.c_int64 * a.dim())(*a.shape)
+            _native.check(lib.kws_model_load_tensor(self._h.ptr, name.encode(), C.c_void_p(a.data_ptr()), shape, a.dim()),
+                          ModelError)
+        _native.check(lib.kws_model_finalize(self._h.ptr), ModelError)
         self._keys = list(self.model.state_dict().keys())
         self._shapes = [tuple(v.shape) for v in self.model.state_dict().values()]
         self.params = flatten_state_dict(self.model.state_dict(), self.device)

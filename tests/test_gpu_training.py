@@ -74,3 +74,20 @@ def test_flat_layout_is_state_dict_order():
     m.load_state_dict(sd)
     ts = KWSTrainStep(m.cuda(), device="cuda:0")
     np.testing.assert_array_equal(ts.params.cpu().numpy(), flat.numpy())
+
+
+def test_training_does_not_disturb_the_inference_handle_until_sync():
+    """The step trains on its own native handle: the module keeps answering with the weights it holds
+    until ``sync_to_model()`` copies the trained parameters back."""
+    sd, m, x, y = _setup(8, 99, 10, seed=21)
+    m = m.cuda()
+    before = m(x.cuda()).cpu().numpy()
+    ts = KWSTrainStep(m, TrainingConfig(learning_rate=1e-2), device="cuda:0")
+    for _ in range(3):
+        ts.step(x, y)
+    np.testing.assert_array_equal(m(x.cuda()).cpu().numpy(), before)
+    ts.sync_to_model()
+    after = m(x.cuda()).cpu().numpy()
+    assert np.abs(after - before).max() > 1e-3
+    want = dscnn_ref.forward({k: v.cpu().double() for k, v in ts.state_dict().items()}, x.double()).numpy()
+    np.testing.assert_allclose(after, want, rtol=1e-3, atol=2e-4)
