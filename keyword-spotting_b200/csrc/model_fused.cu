@@ -16,17 +16,28 @@
 // result as the K-major B operand of the next pointwise GEMM (one 4-byte store per pixel, the
 // 144-byte K-chunk pitch puts the 16 channels of a quarter on 16 different banks).
 //
-// Schedule.  The network is streamed row by row through all layers (a skewed wavefront): in
-// step t the CTA prepares and issues
-//     conv1 row t | depthwise+pointwise of block l on row t-(l+1), l = 1..4 | pooling of row t-6
-// which are mutually independent, so one step = one compute phase (16 warps: warp/4 = the block
-// whose depthwise it runs, warp%4 = lane quarter; all warps share the conv1 im2col), one barrier,
-// ten MMA groups (5 layers x 2 slots, issued by ten different elected lanes), one mbarrier wait.
-// TMEM holds, per layer, a ring of the last four raw accumulator rows (4 x 24 columns), i.e. the
-// rows the next block's 3x3 stencil still needs; the last layer's row is pooled as soon as it
-// retires.  The pointwise padding=1 quirk (models.py:104-106: each block grows H and W by 2 and
-// the new border pixels are ReLU(bias)) is handled in registers: border rows/columns are a
-// per-channel constant.  The depthwise bias is folded through the pointwise weights on the host.
+// Schedule.  The network is streamed row by row through all layers (a skewed wavefront, see the
+// stage table above fused_mma_warp): a step has two phases, each = depthwise stencils of two
+// blocks by the twelve compute warps, one CTA barrier, and the GEMMs of the rows just finished,
+// issued by the two MMA warps (one per clip slot) and retired while the other phase computes.
+// TMEM holds, per layer, a ring of the last two raw accumulator rows; the last layer's row is
+// pooled as soon as it retires.
+//
+// Bias, ReLU and the padding=1 quirk.  The pointwise padding=1 quirk (models.py:104-106: each block
+// grows H and W by 2 and the new border pixels are ReLU(bias)) and every bias are folded INTO the
+// GEMMs, so the depthwise stage reads a finished padded layer row from TMEM and its activation is
+// a bare max(raw, 0) -- no bias add, no border patching, no column masks in the CUDA-core code:
+//   * each pointwise GEMM has K = 64 + 8: B-tile K-slots 64..67 hold the indicators
+//     (interior, border, interior, border) of the output pixel and the A image holds
+//     (folded bias hi, border bias hi, folded bias lo, border bias lo) there (hi + lo = the fp32
+//     bias as two tf32 terms; "folded" = pointwise bias + W_pw . depthwise bias, on the host);
+//   * the depthwise result of pixel x is stored as B-tile pixel row x + 1; rows 0 and W + 1 carry
+//     only the border indicator, rows past the layer carry nothing, so the GEMM row IS the padded
+//     layer row: [ReLU-able border bias | W interior pixels | border bias | zeros];
+//   * conv1 uses its four spare K slots (100..103) the same way; the margin column left of a ring
+//     row is never written and stays zero = the depthwise conv's own zero padding;
+//   * the constant top/bottom border rows and the all-zero row that flushes the stencil are
+//     constant TMEM rows written once at kernel start; a stage just picks the row address.
 //
 // Precision: tf32 operands (cvt.rna), fp32 accumulate; logits agree with the fp32 reference to
 // ~3e-6 absolute / 2e-4 relative (tests/test_gpu_model.py; north_star tolerance 1e-3).
@@ -39,11 +50,14 @@ namespace kws {
 
 constexpr int kFC = 64;                      // channels of the reference network
 constexpr int kLboB = 144;                   // K-chunk pitch of the B tiles (bank spreading)
-constexpr int kKC1 = 104;                    // conv1 K (100 taps) padded to a multiple of 8
+constexpr int kKC1 = 104;                    // conv1 K: 100 taps + (bias hi, 0, bias lo, 0)
+constexpr int kKCp = 72;                     // pointwise K: 64 channels + 4 bias/indicator slots + 4 zero slots
 constexpr int kSboA1 = (kKC1 / 4) * 128;     // 8-row group pitch: conv1 weights
-constexpr int kSboAp = (kFC / 4) * 128;      //                    pointwise weights
+// pointwise weights: 17 stored K-chunks; the 18th (K slots 68..71) aliases the next group's first
+// chunk -- finite numbers that meet the B tile's real zeros there
+constexpr int kSboAp = (kKCp / 4 - 1) * 128;
 constexpr int kSboB1 = (kKC1 / 4) * kLboB;   //                    conv1 im2col tile
-constexpr int kSboBp = (kFC / 4) * kLboB;    //                    depthwise-output tile
+constexpr int kSboBp = (kKCp / 4) * kLboB;   //                    depthwise-output tile
 constexpr int kAImgBytes = 8 * kSboA1 + 4 * 8 * kSboAp;
 
 struct FusedParams {
@@ -51,84 +65,62 @@ struct FusedParams {
   float* logits;          // [B, ncls]
   long long B;
   int T, H0, ncls;
-  const float* a_img;     // tf32 A-operand images: conv1 then 4 pointwise, K-major no-swizzle
+  const float* a_img;     // tf32 A-operand images: conv1 then 4 pointwise, K-major no-swizzle, biases in the K tail
   const float* dw_w;      // [4][9][64]
-  const float* act_bias;  // [5][64] conv1 bias, then pointwise bias with the depthwise bias folded through
   const float* border;    // [5][64] row 0 unused; ReLU(pointwise bias) of block l
   const float* fc_w;      // [64][ncls]
   const float* fc_b;      // [ncls]
 };
 
 // One step of the depthwise 3x3 (zero padding 1) of a block for this thread's (slot, channel) on
-// its warp's 8-pixel column segment [8j, 8j+8): consume INPUT row i of the block's input layer and
-// finish OUTPUT row i - 1.  The stencil is accumulated per input row: with v = the activated row,
+// its warp's 8-pixel column segment [8j, 8j+8): consume one INPUT row of the block's input layer
+// and finish the OUTPUT row above it.  The stencil is accumulated per input row: with v = the
+// activated row,
 //     out[x]  = P[x] + sum_dx w[2][dx] v[x+dx]     (output row i-1 complete -> B tile of the pointwise GEMM)
 //     P'[x]   = R[x] + sum_dx w[1][dx] v[x+dx]     (output row i, two of three rows in)
 //     R'[x]   =        sum_dx w[0][dx] v[x+dx]     (output row i+1, one row in)
 // so every input row is read from TMEM and activated exactly once and nothing is ever moved.
-// The input row is the raw accumulator row of the producing GEMM in the TMEM ring:
-//   BORDER = false (block 1 reads conv1's output): layer column gx = raw column gx, ReLU(raw + bias);
-//   BORDER = true  (blocks 2..4 read a padded-pointwise output): the layer has HIN + 2 rows and
-//                  WIN + 2 columns, its outermost ring is the constant `bval`, interior (i, gx) is raw
-//                  (i - 1, gx - 1).
-// Row classes are CTA-uniform and folded into scalars (v = max(raw * m + be, 0)): interior m = 1,
-// be = bias; constant border row m = 0, be = bval; the zero row i = HL that flushes the last
-// output row m = be = 0 (TMEM is zeroed at kernel start, so raw is always finite).  Column classes
-// (left/right border, columns past the layer) depend only on the warp's segment j and are patched
-// with warp-uniform predicated moves.  `par` points at this channel's [w0..w8, bias, border] column.
-template <int WIN, bool BORDER>
-__device__ __forceinline__ void dw_seg(uint32_t taddr, int j, int i, int HIN, const float4* par, unsigned char* dst,
+// `taddr` is the TMEM address of layer column 8j - 1 of the input row (a ring row, a constant border
+// row or the zero row -- the caller picks); layer column = TMEM column for every layer, the bias is
+// already in the accumulator, so v = max(raw, 0).  The stencil runs on packed f32x2 pairs of
+// adjacent pixels: E[p] = (v[2p], v[2p+1]) and the odd-aligned O[p] = (v[2p+1], v[2p+2]) are both
+// produced straight by the max, so no register pair is ever re-assembled.
+// W = width of the layer (= number of valid output pixels), SHIFT = pixel offset of the result in the
+// B tile (1 where the following pointwise output carries a border column).  `par` points at this
+// channel's [w0..w8] column.
+template <int W, int SHIFT>
+__device__ __forceinline__ void dw_seg(uint32_t taddr, int j, bool st, const float4* par, unsigned char* dst,
                                        V (&P)[4], V (&R)[4]) {
-  constexpr int WL = BORDER ? WIN + 2 : WIN;
-  constexpr int JL = (WL - 1) / 8, KL = WL - 8 * JL;  // segment and v-index of the layer's last column
-  const int HL = BORDER ? HIN + 2 : HIN;
-  const bool flush = i >= HL;
-  const bool cst = BORDER && !flush && (i == 0 || i == HL - 1);
-  const float4 w0 = par[0], w1 = par[1], w2 = par[2];  // taps 0..8, input bias, border constant
-  const float bias = w2.y, bval = BORDER ? w2.z : 0.f;
-  const float m = (flush || cst) ? 0.f : 1.f;
-  const float be = flush ? 0.f : (cst ? bval : bias);
-  const float edge = flush ? 0.f : bval;
-  // v[k] = layer column 8j-1+k, k = 0..9, kept as aligned pairs E[p] = (v[2p], v[2p+1]); the load
-  // starts two columns left of v[0] so that the pairs fall on even registers
-  float v[10];
-  {
-    float raw[16];
-    tc_ld16(taddr, raw);
-    tc_wait_ld();
-    const V m2 = fsplat(m), be2 = fsplat(be);
+  constexpr int JL = (W - 1) / 8, KL = W - 8 * JL;  // last segment with valid pixels, and how many it has
+  const float4 w0 = par[0], w1 = par[1];
+  const float w8 = reinterpret_cast<const float*>(par)[8];
+  // E pairs from a load at column 8j-1, O pairs from a second load one column to the right; the max is
+  // done in place on the load's registers so that each pair stays the aligned register pair it arrived as
+  float ra[16], rb[8];
+  tc_ld16(taddr, ra);
+  tc_ld8(taddr + 1u, rb);
+  tc_wait_ld();
 #pragma unroll
-    for (int pp = 0; pp < 5; ++pp) {
-      const V a = ffma(make_float2(raw[2 * pp + 2], raw[2 * pp + 3]), m2, be2);
-      v[2 * pp] = fmaxf(a.x, 0.f);
-      v[2 * pp + 1] = fmaxf(a.y, 0.f);
-    }
-  }
-  if (j == 0) {
-    v[0] = 0.f;
-    if (BORDER) v[1] = edge;
-  }
-  if (j == JL) {
-    if (BORDER) v[KL] = edge;
+  for (int k = 0; k < 10; ++k) asm("max.f32 %0, %0, 0f00000000;" : "+f"(ra[k]));
 #pragma unroll
-    for (int k = KL + 1; k < 10; ++k) v[k] = 0.f;
-  }
-  if (j > JL) {
+  for (int k = 0; k < 8; ++k) asm("max.f32 %0, %0, 0f00000000;" : "+f"(rb[k]));
+  V E[5], O[4];
 #pragma unroll
-    for (int k = 0; k < 10; ++k) v[k] = 0.f;
-  }
-  const bool st = i >= 1;
+  for (int pp = 0; pp < 5; ++pp) E[pp] = make_float2(ra[2 * pp], ra[2 * pp + 1]);
+#pragma unroll
+  for (int pp = 0; pp < 4; ++pp) O[pp] = make_float2(rb[2 * pp], rb[2 * pp + 1]);
+  const bool st_lo = st && j <= JL, st_hi = st && j < JL;  // pixels x < KL / x >= KL of the segment
 #pragma unroll
   for (int pp = 0; pp < 4; ++pp) {  // output pixels 2pp, 2pp+1 of the segment, packed f32x2
-    const V e0 = make_float2(v[2 * pp], v[2 * pp + 1]), od = make_float2(v[2 * pp + 1], v[2 * pp + 2]);
-    const V e1 = make_float2(v[2 * pp + 2], v[2 * pp + 3]);
-    const V o = ffma(fsplat(w2.x), e1, ffma(fsplat(w1.w), od, ffma(fsplat(w1.z), e0, P[pp])));
-    P[pp] = ffma(fsplat(w1.y), e1, ffma(fsplat(w1.x), od, ffma(fsplat(w0.w), e0, R[pp])));
-    R[pp] = ffma(fsplat(w0.z), e1, ffma(fsplat(w0.y), od, fmul(fsplat(w0.x), e0)));
-    if (st) {  // tf32 round-to-nearest (ties away) = add half an ulp of the 10-bit mantissa; the MMA drops the low 13 bits
-      *reinterpret_cast<uint32_t*>(dst + (2 * pp) * 16) = __float_as_uint(o.x) + 0x1000u;
-      *reinterpret_cast<uint32_t*>(dst + (2 * pp + 1) * 16) = __float_as_uint(o.y) + 0x1000u;
-    }
+    const V o = ffma(fsplat(w8), E[pp + 1], ffma(fsplat(w1.w), O[pp], ffma(fsplat(w1.z), E[pp], P[pp])));
+    P[pp] = ffma(fsplat(w1.y), E[pp + 1], ffma(fsplat(w1.x), O[pp], ffma(fsplat(w0.w), E[pp], R[pp])));
+    R[pp] = ffma(fsplat(w0.z), E[pp + 1], ffma(fsplat(w0.y), O[pp], fmul(fsplat(w0.x), E[pp])));
+    // tf32 round-to-nearest (ties away) = add half an ulp of the 10-bit mantissa; the MMA drops the low 13 bits
+    const int x0 = 2 * pp, x1 = 2 * pp + 1;
+    if (x0 < KL ? st_lo : st_hi)
+      *reinterpret_cast<uint32_t*>(dst + ((x0 + SHIFT) >> 3) * kSboBp + ((x0 + SHIFT) & 7) * 16) = __float_as_uint(o.x) + 0x1000u;
+    if (x1 < KL ? st_lo : st_hi)
+      *reinterpret_cast<uint32_t*>(dst + ((x1 + SHIFT) >> 3) * kSboBp + ((x1 + SHIFT) & 7) * 16) = __float_as_uint(o.y) + 0x1000u;
   }
 }
 
@@ -136,7 +128,9 @@ constexpr int kCWarps = 12;                       // compute warps: 3 column seg
 constexpr int kCThreads = kCWarps * 32;
 constexpr int kFThreads = (kCWarps + 2) * 32;     // + one MMA-issue warp per clip slot
 constexpr int kRingCols = 64;                     // per layer: 2 row slots x (8 margin + 24) columns
-constexpr int kAcc4Col = 4 * kRingCols;           // last pointwise layer's row (pooled at once)
+constexpr int kAcc4Col = 4 * kRingCols;           // last pointwise layer's row (pooled at once), 32 columns
+constexpr int kConstCol = kAcc4Col + 32;          // constant border rows of the three padded layers, 32 columns each
+constexpr int kZeroCol = kConstCol + 3 * 32;      // the all-zero row that flushes a stencil
 
 template <int F, int NPIX>
 struct FusedLayout {
@@ -154,13 +148,25 @@ struct FusedLayout {
   static constexpr size_t feat_floats(int T) { return (size_t)(T + 4) * FP; }
 };
 
+// The MMA warps run their issue code CONVERGED (all 32 lanes, warp-uniform operands, so ptxas keeps the
+// descriptors in uniform registers) and every tcgen05 instruction is predicated on an elected lane.  Issuing
+// from inside an `if (lane == 0)` region instead makes ptxas wrap each MMA in a per-thread waterfall loop
+// (4x R2UR + ELECT + branch per instruction), which made MMA issue the critical path of a step.
 template <bool ACC>
 __device__ __forceinline__ void tc_mma_tf32_c(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc) {
   asm volatile(
-      "{\n\t.reg .pred p;\n\t"
+      "{\n\t.reg .pred p, pe;\n\t"
+      "elect.sync _|pe, 0xffffffff;\n\t"
       "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "@pe tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
       "l"(adesc), "l"(bdesc), "r"(idesc), "n"(ACC ? 1 : 0)
+      : "memory");
+}
+__device__ __forceinline__ void tc_commit_elect(uint32_t bar) {
+  asm volatile(
+      "{\n\t.reg .pred pe;\n\t"
+      "elect.sync _|pe, 0xffffffff;\n\t"
+      "@pe tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(bar)
       : "memory");
 }
 // one GEMM: NK k-steps of 8; the descriptors' address fields advance by 256 B (A) / 2 * 144 B (B)
@@ -198,31 +204,43 @@ __device__ __forceinline__ void fused_mma_warp(unsigned char* smem, uint32_t tme
     __syncthreads();  // features loaded
     for (int t = 0; t < nsteps; ++t) {
       __syncthreads();  // phase A written
-      if (lane == 0) {
-        tc_fence_after();
+      tc_fence_after();
+      {
         int r = t - 3;
-        if (r >= 0 && r < H0) issue_gemm<kFC / 8>(d0 + 1 * kRingCols + (r & 1) * 32, ap[0], bp[0], kIdescF);
+        if (r >= 0 && r < H0) issue_gemm<kKCp / 8>(d0 + 1 * kRingCols + (r & 1) * 32, ap[0], bp[0], kIdescF);
         r = t - 6;
-        if (r >= 0 && r < H0 + 4) issue_gemm<kFC / 8>(d0 + 3 * kRingCols + (r & 1) * 32, ap[2], bp[2], kIdescF);
-        tc_commit(barO);
+        if (r >= 0 && r < H0 + 4) issue_gemm<kKCp / 8>(d0 + 3 * kRingCols + (r & 1) * 32, ap[2], bp[2], kIdescF);
+        tc_commit_elect(barO);
       }
-      __syncwarp();
       __syncthreads();  // phase B written
-      if (lane == 0) {
-        tc_fence_after();
+      tc_fence_after();
+      {
         int r = t;
         if (r < H0) issue_gemm<kKC1 / 8>(d0 + (r & 1) * 32, a1, b1, kIdescF);
         r = t - 4;
-        if (r >= 0 && r < H0 + 2) issue_gemm<kFC / 8>(d0 + 2 * kRingCols + (r & 1) * 32, ap[1], bp[1], kIdescF);
+        if (r >= 0 && r < H0 + 2) issue_gemm<kKCp / 8>(d0 + 2 * kRingCols + (r & 1) * 32, ap[1], bp[1], kIdescF);
         r = t - 7;
-        if (r >= 0 && r < H0 + 6) issue_gemm<kFC / 8>(d0 - 8u + kAcc4Col, ap[3], bp[3], kIdescF);
-        tc_commit(barE);
+        if (r >= 0 && r < H0 + 6) issue_gemm<kKCp / 8>(d0 - 8u + kAcc4Col, ap[3], bp[3], kIdescF);
+        tc_commit_elect(barE);
       }
-      __syncwarp();
     }
     __syncthreads();  // pooling partials written
     __syncthreads();  // logits written
   }
+}
+
+// TMEM column (relative to the lane quarter's base) of input row i of a depthwise stage: `ring` is the
+// input layer's ring; BORDER layers have HIN + 2 rows whose first and last are the constant row `cst`;
+// row HL (one past the end) is the zero row that flushes the last output row.
+template <bool BORDER>
+__device__ __forceinline__ uint32_t dw_row_col(int i, int HIN, uint32_t ring, uint32_t cst) {
+  const int HL = BORDER ? HIN + 2 : HIN;
+  if (i >= HL) return (uint32_t)kZeroCol;
+  if (BORDER) {
+    if (i == 0 || i == HL - 1) return cst;
+    return ring + (uint32_t)(((i - 1) & 1) * 32);
+  }
+  return ring + (uint32_t)((i & 1) * 32);
 }
 
 template <int F, int NPIX>
@@ -264,21 +282,56 @@ __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedPa
   __syncthreads();
   for (int i = tid; i < 4 * kFC * 12; i += kFThreads) {
     const int l = i / (12 * kFC), ch = (i / 12) % kFC, k = i % 12;
-    s_par[i] = k < 9 ? p.dw_w[(l * 9 + k) * kFC + ch]
-                     : (k == 9 ? p.act_bias[l * kFC + ch] : (k == 10 ? p.border[l * kFC + ch] : 0.f));
+    s_par[i] = k < 9 ? p.dw_w[(l * 9 + k) * kFC + ch] : 0.f;
+  }
+  // constant K tail of the B tiles: (interior, border, interior, border) indicators of every pixel row
+  for (int i = tid; i < 2 * 5 * NPIX; i += kFThreads) {
+    const int s = i / (5 * NPIX), l = (i / NPIX) % 5, px = i % NPIX;  // l = 0: conv1 tile, 1..4: tile of pointwise l
+    float in = 0.f, bo = 0.f;
+    unsigned char* tile;
+    int chunk, sbo;
+    if (l == 0) {
+      tile = smem + L::off_b1 + s * L::b1_stride, chunk = 25, sbo = kSboB1;
+      in = px < W0 ? 1.f : 0.f;
+    } else {
+      tile = smem + L::off_bp + ((l - 1) * 2 + s) * L::bp_stride, chunk = 16, sbo = kSboBp;
+      const int Wl = W0 + 2 * (l - 1);  // width of the depthwise output feeding pointwise l
+      if (l < 4) {
+        in = (px >= 1 && px <= Wl) ? 1.f : 0.f;
+        bo = (px == 0 || px == Wl + 1) ? 1.f : 0.f;
+      } else {
+        in = px < Wl ? 1.f : 0.f;
+      }
+    }
+    *reinterpret_cast<float4*>(tile + (px >> 3) * sbo + chunk * kLboB + (px & 7) * 16) = make_float4(in, bo, in, bo);
   }
   fence_proxy_async();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = s_tmem;
-  if (warp < 4) {  // zero the accumulator rings once: dw_seg multiplies not-yet-written rows by 0
+  if (warp < 4) {  // zero all of tensor memory once, then the constant border rows of the three padded layers
     for (int col = 0; col < 512; col += 16) {
       asm volatile(
           "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1};" ::"r"(
               tmem + ((uint32_t)(warp * 32) << 16) + col),
           "r"(0)
           : "memory");
+    }
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+    const int ch = warp * 16 + (lane & 15);
+    for (int l = 1; l < 4; ++l) {
+      const uint32_t bv = __float_as_uint(p.border[l * kFC + ch]);
+      const int WL = W0 + 2 * l;
+      for (int x0 = 0; x0 < NPIX; x0 += 8) {
+        uint32_t v[8];
+#pragma unroll
+        for (int x = 0; x < 8; ++x) v[x] = (x0 + x < WL) ? bv : 0u;
+        asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"r"(
+                         tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)(kConstCol + (l - 1) * 32 + 8 + x0)),
+                     "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
+                     : "memory");
+      }
     }
     asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
   }
@@ -294,10 +347,10 @@ __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedPa
     // =========================== compute warps ===========================
     const int j = warp >> 2, q = warp & 3, sl = lane >> 4, c = q * 16 + (lane & 15);
     const bool seg_on = j < NSEG;
-    // TMEM: this warp's lane quarter; ring row slot s of layer l starts at column l*64 + s*32 + 8;
-    // a 16-column load from (segment start - 4) covers the segment and its halo
+    // TMEM: this warp's lane quarter; ring row slot s of layer l starts at column l*64 + s*32, its data
+    // after an 8-column margin; a 16-column load from (segment start - 1) covers the segment and its halo
     const uint32_t my_tmem = tmem + ((uint32_t)(q * 32) << 16);
-    const uint32_t my_ld = my_tmem + 8u + (uint32_t)(8 * j);  // + (-3 | -4): see dw_seg
+    const uint32_t my_ld = my_tmem + 7u + (uint32_t)(8 * j);
     unsigned char* my_dst = smem + L::off_bp + sl * L::bp_stride + j * kSboBp + (c >> 2) * kLboB + (c & 3) * 4;
     const float4* my_par = reinterpret_cast<const float4*>(s_par) + c * 3;
     // conv1 im2col item of this thread: slot, 16-byte K-chunk (4 taps), pixel columns xg, xg+7, xg+14
@@ -346,12 +399,12 @@ __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedPa
         if (seg_on) {
           int i = t - 2;
           if (i >= 0 && i <= H0)
-            dw_seg<W0, false>(my_ld - 3u + 0 * kRingCols + (uint32_t)((i & 1) * 32), j, i, H0, my_par + 0 * 3 * kFC,
-                              my_dst + 0 * 2 * L::bp_stride, P[0], R[0]);
+            dw_seg<W0, 1>(my_ld + dw_row_col<false>(i, H0, 0 * kRingCols, 0), j, i >= 1, my_par + 0 * 3 * kFC,
+                          my_dst + 0 * 2 * L::bp_stride, P[0], R[0]);
           i = t - 5;
           if (i >= 0 && i <= H0 + 4)
-            dw_seg<W0 + 2, true>(my_ld - 4u + 2 * kRingCols + (uint32_t)(((i - 1) & 1) * 32), j, i, H0 + 2, my_par + 2 * 3 * kFC,
-                                 my_dst + 2 * 2 * L::bp_stride, P[2], R[2]);
+            dw_seg<W0 + 4, 1>(my_ld + dw_row_col<true>(i, H0 + 2, 2 * kRingCols, kConstCol + 32), j, i >= 1,
+                              my_par + 2 * 3 * kFC, my_dst + 2 * 2 * L::bp_stride, P[2], R[2]);
         }
         fence_proxy_async();
         tc_fence_before();
@@ -373,12 +426,12 @@ __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedPa
         if (seg_on) {
           int i = t - 3;
           if (i >= 0 && i <= H0 + 2)
-            dw_seg<W0, true>(my_ld - 4u + 1 * kRingCols + (uint32_t)(((i - 1) & 1) * 32), j, i, H0, my_par + 1 * 3 * kFC,
-                             my_dst + 1 * 2 * L::bp_stride, P[1], R[1]);
+            dw_seg<W0 + 2, 1>(my_ld + dw_row_col<true>(i, H0, 1 * kRingCols, kConstCol), j, i >= 1, my_par + 1 * 3 * kFC,
+                              my_dst + 1 * 2 * L::bp_stride, P[1], R[1]);
           i = t - 6;
           if (i >= 0 && i <= H0 + 6)
-            dw_seg<W0 + 4, true>(my_ld - 4u + 3 * kRingCols + (uint32_t)(((i - 1) & 1) * 32), j, i, H0 + 4, my_par + 3 * 3 * kFC,
-                                 my_dst + 3 * 2 * L::bp_stride, P[3], R[3]);
+            dw_seg<W0 + 6, 0>(my_ld + dw_row_col<true>(i, H0 + 4, 3 * kRingCols, kConstCol + 64), j, i >= 1,
+                              my_par + 3 * 3 * kFC, my_dst + 3 * 2 * L::bp_stride, P[3], R[3]);
           const int r = t - 8;
           if (r >= 0 && r < H3) {  // pooling of the last block's row r (interior pixels; the border is added at the end)
             uint32_t raw[8];
@@ -388,10 +441,8 @@ __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedPa
                          : "r"(my_tmem + (uint32_t)kAcc4Col + (uint32_t)(8 * j))
                          : "memory");
             tc_wait_ld();
-            const float pb = p.act_bias[4 * kFC + c];
 #pragma unroll
-            for (int x = 0; x < 8; ++x)
-              if (8 * j + x < W3) psum += fmaxf(__uint_as_float(raw[x]) + pb, 0.f);
+            for (int x = 0; x < 8; ++x) psum += fmaxf(__uint_as_float(raw[x]), 0.f);  // columns past the layer are 0
           }
         }
         fence_proxy_async();
@@ -447,8 +498,16 @@ int build_fused_model(ModelWeights& m, const std::vector<float>& conv1_w, const 
   auto put = [&](size_t base, int sbo, int mrow, int k, float v) {
     img[(base + (size_t)(mrow >> 3) * sbo + (size_t)(k >> 2) * 128 + (mrow & 7) * 16 + (k & 3) * 4) / 4] = host_tf32(v);
   };
-  for (int co = 0; co < kFC; ++co)
+  // a bias enters its GEMM as two tf32 terms (hi + lo = the fp32 value to ~2^-22) against constant-1 K slots
+  auto put_bias = [&](size_t base, int sbo, int mrow, int k, float b) {
+    const float hi = host_tf32(b);
+    put(base, sbo, mrow, k, hi);
+    put(base, sbo, mrow, k + 2, b - hi);
+  };
+  for (int co = 0; co < kFC; ++co) {
     for (int k = 0; k < 100; ++k) put(0, kSboA1, co, k, conv1_w[(size_t)co * 100 + k]);
+    put_bias(0, kSboA1, co, 100, conv1_b[co]);
+  }
   std::vector<float> dww(4 * 9 * kFC), actb(5 * kFC), border(5 * kFC, 0.f);
   for (int co = 0; co < kFC; ++co) actb[co] = conv1_b[co];
   for (int l = 0; l < 4; ++l) {
@@ -460,6 +519,8 @@ int build_fused_model(ModelWeights& m, const std::vector<float>& conv1_w, const 
         be += (double)pw_w[l][(size_t)co * kFC + ci] * (double)dw_b[l][ci];
       }
       actb[(l + 1) * kFC + co] = (float)be;
+      put_bias(base, kSboAp, co, kFC, (float)be);          // interior pixels: pointwise bias + W_pw . depthwise bias
+      put_bias(base, kSboAp, co, kFC + 1, pw_b[l][co]);    // padding=1 border pixels: the pointwise bias alone
       border[(l + 1) * kFC + co] = pw_b[l][co] > 0.f ? pw_b[l][co] : 0.f;
       for (int tap = 0; tap < 9; ++tap) dww[((size_t)l * 9 + tap) * kFC + co] = dw_w[l][(size_t)co * 9 + tap];
     }
@@ -509,7 +570,6 @@ int launch_dscnn_fused(kws_handle_t h, const float* feats_dev, int64_t B, int64_
   p.ncls = m.num_classes;
   p.a_img = m.d_fused_a;
   p.dw_w = m.d_fused_dw;
-  p.act_bias = m.d_fused_actb;
   p.border = m.d_fused_border;
   p.fc_w = m.d_fc_w;
   p.fc_b = m.d_fc_b;
