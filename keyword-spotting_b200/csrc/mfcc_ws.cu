@@ -119,7 +119,7 @@ __global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastPar
       mbar_expect_tx(bar, bytes);
       tma_load_1d(smem_u32(raw + (s0 >= 4 ? 0 : 4)), p.pcm + (size_t)clip * p.stride + first, bytes, bar);
     };
-    auto issue_mma = [&]() {  // one thread: D[128 x 48] = Ahi*Bhi + Alo*Bhi + Ahi*Blo over Kpad
+    auto issue_mma = [&]() {  // converged warp, elected lane: D[128 x 48] = Ahi*Bhi + Alo*Bhi + Ahi*Blo over Kpad
       tc_fence_after();
       const uint32_t a_hi = smem_u32(smem + p.off_a), a_lo = a_hi + 3u * sbo;
       const uint32_t b_hi = smem_u32(smem + p.off_b), b_lo = b_hi + (uint32_t)(kDctN / 8) * sbo;
@@ -129,11 +129,11 @@ __global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastPar
       for (int term = 0; term < 3; ++term) {
         const uint32_t ab = term == 1 ? a_lo : a_hi, bb = term == 2 ? b_lo : b_hi;
         for (int ks = 0; ks < ksteps; ++ks) {
-          tc_mma_tf32(tmem, umma_desc(ab + ks * 256u, 128u, sbo), umma_desc(bb + ks * 256u, 128u, sbo), kIdesc, acc);
+          tc_mma_tf32_elect(tmem, umma_desc(ab + ks * 256u, 128u, sbo), umma_desc(bb + ks * 256u, 128u, sbo), kIdesc, acc);
           acc = 1;
         }
       }
-      tc_commit(bar_mma);
+      tc_commit_elect(bar_mma);
     };
     if (lane == 0) {
       if (n_it > 0) issue_tma(0);
@@ -153,8 +153,7 @@ __global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastPar
       }
       if (do_dct) {
         mbar_wait_idle(bar_afull, it & 1);
-        if (lane == 0) issue_mma();
-        __syncwarp();
+        issue_mma();
         mbar_wait(bar_mma, it & 1);
         // ---- epilogue (lane = frame row of the tile): TMEM -> registers -> global ----
         float v[kDctN];

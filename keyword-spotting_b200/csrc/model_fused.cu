@@ -148,10 +148,9 @@ struct FusedLayout {
   static constexpr size_t feat_floats(int T) { return (size_t)(T + 4) * FP; }
 };
 
-// The MMA warps run their issue code CONVERGED (all 32 lanes, warp-uniform operands, so ptxas keeps the
-// descriptors in uniform registers) and every tcgen05 instruction is predicated on an elected lane.  Issuing
-// from inside an `if (lane == 0)` region instead makes ptxas wrap each MMA in a per-thread waterfall loop
-// (4x R2UR + ELECT + branch per instruction), which made MMA issue the critical path of a step.
+// The MMA warps run their issue code CONVERGED and every tcgen05 instruction is predicated on an elected lane
+// (see tc_mma_tf32_elect in mfcc_dev.cuh): issued from inside `if (lane == 0)`, MMA issue was the critical
+// path of a step.  ACC is an immediate here.
 template <bool ACC>
 __device__ __forceinline__ void tc_mma_tf32_c(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc) {
   asm volatile(
@@ -160,13 +159,6 @@ __device__ __forceinline__ void tc_mma_tf32_c(uint32_t d_tmem, uint64_t adesc, u
       "setp.ne.b32 p, %4, 0;\n\t"
       "@pe tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
       "l"(adesc), "l"(bdesc), "r"(idesc), "n"(ACC ? 1 : 0)
-      : "memory");
-}
-__device__ __forceinline__ void tc_commit_elect(uint32_t bar) {
-  asm volatile(
-      "{\n\t.reg .pred pe;\n\t"
-      "elect.sync _|pe, 0xffffffff;\n\t"
-      "@pe tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(bar)
       : "memory");
 }
 // one GEMM: NK k-steps of 8; the descriptors' address fields advance by 256 B (A) / 2 * 144 B (B)

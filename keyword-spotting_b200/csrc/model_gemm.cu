@@ -232,25 +232,29 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_gemm_kernel(const GemmParams p) 
       fence_proxy_async();
       asm volatile("cp.async.wait_group 1;" ::: "memory");  // this thread's share of the NEXT chunk's patch has landed
       __syncthreads();
-      if (tid == kIssuer) {
+      if (warp == kIssuer / 32) {  // the issue warp runs converged; one elected lane issues (tc_mma_tf32_elect)
         mbar_wait(barB + 8u * buf, (cnt >> 1) & 1);
         tc_fence_after();
         const uint32_t ab = smem_u32(abuf), bb = smem_u32(sB + (size_t)buf * bbytes);
 #pragma unroll 1
         for (int ks = 0; ks < kGKC / 8; ++ks)
           for (int hf = 0; hf < p.nh; ++hf)
-            tc_mma_tf32(tmem + (uint32_t)(hf * p.nhalf), umma_desc(ab + ks * 2u * kGLboA, kGLboA, kGSboA),
-                        umma_desc(bb + (uint32_t)(hf * (p.nhalf / 8)) * kGSbo + ks * 256u, 128u, kGSbo), idesc,
-                        (kc > 0 || ks > 0) ? 1u : 0u);
-        tc_commit(bar0 + 8u * buf);
+            tc_mma_tf32_elect(tmem + (uint32_t)(hf * p.nhalf), umma_desc(ab + ks * 2u * kGLboA, kGLboA, kGSboA),
+                              umma_desc(bb + (uint32_t)(hf * (p.nhalf / 8)) * kGSbo + ks * 256u, 128u, kGSbo), idesc,
+                              (kc > 0 || ks > 0) ? 1u : 0u);
+        tc_commit_elect(bar0 + 8u * buf);
         // request the NEXT chunk's weights now (TMA bulk copy), a full chunk ahead of their use: their buffer
         // is free once the MMAs of chunk cnt - 1 have retired, which happened while this chunk was produced
         if (fchunk + 1 < total_chunks) {
           const int nb2 = buf ^ 1, kn = kc + 1 < p.nchunks ? kc + 1 : 0;
           if (cnt >= 1) mbar_wait(bar0 + 8u * nb2, ((cnt - 1) >> 1) & 1);
-          mbar_expect_tx(barB + 8u * nb2, (uint32_t)bbytes);
-          tma_load_1d(smem_u32(sB + (size_t)nb2 * bbytes), reinterpret_cast<const unsigned char*>(p.wimg) + (size_t)kn * bbytes,
-                      (uint32_t)bbytes, barB + 8u * nb2);
+          if (lane == 0) {
+            mbar_expect_tx(barB + 8u * nb2, (uint32_t)bbytes);
+            tma_load_1d(smem_u32(sB + (size_t)nb2 * bbytes),
+                        reinterpret_cast<const unsigned char*>(p.wimg) + (size_t)kn * bbytes, (uint32_t)bbytes,
+                        barB + 8u * nb2);
+          }
+          __syncwarp();
         }
       }
     }
