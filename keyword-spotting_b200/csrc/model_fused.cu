@@ -348,10 +348,12 @@ __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedPa
     // conv1 im2col item of this thread: slot, 16-byte K-chunk (4 taps), pixel columns xg, xg+7, xg+14
     const bool im_on = tid < 350;
     const int im_s = tid / 175, im_kc = (tid % 175) % 25, im_xg = (tid % 175) / 25;
-    int im_off[4];
+    // taps 4kc .. 4kc+3 are two pairs of horizontally adjacent taps (a window row has 10 taps and 4kc is even),
+    // each pair one aligned 8-byte read of the padded feature row
+    int im_off[2];
 #pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      const int k = 4 * im_kc + e, ki = k / 10, kj = k - 10 * ki;
+    for (int e = 0; e < 2; ++e) {
+      const int k = 4 * im_kc + 2 * e, ki = k / 10, kj = k - 10 * ki;
       im_off[e] = ki * FP + kj;
     }
     const float* im_src = s_feat + im_s * feat_stride;
@@ -411,8 +413,9 @@ __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedPa
           const float* rowp = im_src + 2 * t * FP;
           for (int x = im_xg; x < W0; x += 7) {
             const float* q4 = rowp + 2 * x;
-            *reinterpret_cast<float4*>(im_dst + (x >> 3) * kSboB1 + (x & 7) * 16) =
-                make_float4(q4[im_off[0]], q4[im_off[1]], q4[im_off[2]], q4[im_off[3]]);
+            const float2 lo = *reinterpret_cast<const float2*>(q4 + im_off[0]);
+            const float2 hi = *reinterpret_cast<const float2*>(q4 + im_off[1]);
+            *reinterpret_cast<float4*>(im_dst + (x >> 3) * kSboB1 + (x & 7) * 16) = make_float4(lo.x, lo.y, hi.x, hi.y);
           }
         }
         if (seg_on) {
