@@ -170,15 +170,34 @@ __device__ __forceinline__ void issue_gemm(uint32_t d, uint64_t adesc, uint64_t 
     tc_mma_tf32_c<true>(d, adesc + (uint64_t)(ks * (256 >> 4)), bdesc + (uint64_t)(ks * ((2 * kLboB) >> 4)), idesc);
 }
 
-// Stage schedule (step t of a clip pair; phase A then phase B inside a step):
+// Stage schedule (local step t of a clip pair; phase A then phase B inside a step):
 //   conv1 im2col + GEMM row t                    (B)      | dw1: input row t-2 (A), pw1 GEMM row t-3 (end of A)
 //   dw2: input row t-3 (B), pw2 GEMM row t-4 (end of B)    | dw3: input row t-5 (A), pw3 GEMM row t-6 (end of A)
 //   dw4: input row t-6 (B), pw4 GEMM row t-7 (end of B)    | pooling of pw4 row t-8 (B)
 // GEMMs issued at the end of a phase run on the tensor core while the compute warps execute the
 // next phase, whose stages never touch what those GEMMs read or write.
+//
+// The clip pairs of a CTA are streamed back to back with period PER = H0 + 7 steps (the longest stage,
+// dw4, has exactly PER rows), so the pipeline never drains between pairs: with tl = global step mod PER
+// and n = global step / PER, a stage with lag g works on row i = tl - g of pair n, or, while that is
+// negative, on row i + PER of pair n - 1.  Every stage resets itself (the zero flush row clears the
+// stencil state), so nothing else marks the boundary between two pairs.
+struct StageRow {
+  int i;      // row index inside the stage's pair (valid when on)
+  bool on;
+};
+__device__ __forceinline__ StageRow stage_row(int tl, int n, int npair, int per, int g, int len) {
+  int i = tl - g, cn = n;
+  if (i < 0) {
+    i += per;
+    cn = n - 1;
+  }
+  return StageRow{i, cn >= 0 && cn < npair && i < len};
+}
+
 template <int F, int NPIX, int SLOT>
 __device__ __forceinline__ void fused_mma_warp(unsigned char* smem, uint32_t tmem, uint32_t barO, uint32_t barE, int H0,
-                                               long long npairs, int lane) {
+                                               int my_pairs) {
   using L = FusedLayout<F, NPIX>;
   constexpr uint32_t kIdescF = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(NPIX >> 3) << 17) | ((64u >> 4) << 24);
   const uint32_t sbase = smem_u32(smem);
@@ -191,33 +210,34 @@ __device__ __forceinline__ void fused_mma_warp(unsigned char* smem, uint32_t tme
     bp[l] = umma_desc(sbase + L::off_bp + (l * 2 + SLOT) * L::bp_stride, kLboB, kSboBp);
   }
   const uint32_t d0 = tmem + ((uint32_t)(SLOT * 16) << 16) + 8u;  // ring rows start after an 8-column margin
-  const int nsteps = H0 + 14;
-  for (long long pair = blockIdx.x; pair < npairs; pair += gridDim.x) {
-    __syncthreads();  // features loaded
-    for (int t = 0; t < nsteps; ++t) {
-      __syncthreads();  // phase A written
-      tc_fence_after();
-      {
-        int r = t - 3;
-        if (r >= 0 && r < H0) issue_gemm<kKCp / 8>(d0 + 1 * kRingCols + (r & 1) * 32, ap[0], bp[0], kIdescF);
-        r = t - 6;
-        if (r >= 0 && r < H0 + 4) issue_gemm<kKCp / 8>(d0 + 3 * kRingCols + (r & 1) * 32, ap[2], bp[2], kIdescF);
-        tc_commit_elect(barO);
-      }
-      __syncthreads();  // phase B written
-      tc_fence_after();
-      {
-        int r = t;
-        if (r < H0) issue_gemm<kKC1 / 8>(d0 + (r & 1) * 32, a1, b1, kIdescF);
-        r = t - 4;
-        if (r >= 0 && r < H0 + 2) issue_gemm<kKCp / 8>(d0 + 2 * kRingCols + (r & 1) * 32, ap[1], bp[1], kIdescF);
-        r = t - 7;
-        if (r >= 0 && r < H0 + 6) issue_gemm<kKCp / 8>(d0 - 8u + kAcc4Col, ap[3], bp[3], kIdescF);
-        tc_commit_elect(barE);
-      }
+  const int per = H0 + 7, total = my_pairs * per + 7;
+  __syncthreads();  // features of the first pair loaded
+  int tl = 0, n = 0;
+  for (int tg = 0; tg < total; ++tg) {
+    __syncthreads();  // phase A written
+    tc_fence_after();
+    {
+      StageRow r = stage_row(tl, n, my_pairs, per, 3, H0);
+      if (r.on) issue_gemm<kKCp / 8>(d0 + 1 * kRingCols + (r.i & 1) * 32, ap[0], bp[0], kIdescF);
+      r = stage_row(tl, n, my_pairs, per, 6, H0 + 4);
+      if (r.on) issue_gemm<kKCp / 8>(d0 + 3 * kRingCols + (r.i & 1) * 32, ap[2], bp[2], kIdescF);
+      tc_commit_elect(barO);
     }
-    __syncthreads();  // pooling partials written
-    __syncthreads();  // logits written
+    __syncthreads();  // phase B written
+    tc_fence_after();
+    {
+      StageRow r = stage_row(tl, n, my_pairs, per, 0, H0);
+      if (r.on) issue_gemm<kKC1 / 8>(d0 + (r.i & 1) * 32, a1, b1, kIdescF);
+      r = stage_row(tl, n, my_pairs, per, 4, H0 + 2);
+      if (r.on) issue_gemm<kKCp / 8>(d0 + 2 * kRingCols + (r.i & 1) * 32, ap[1], bp[1], kIdescF);
+      r = stage_row(tl, n, my_pairs, per, 7, H0 + 6);
+      if (r.on) issue_gemm<kKCp / 8>(d0 - 8u + kAcc4Col, ap[3], bp[3], kIdescF);
+      tc_commit_elect(barE);
+    }
+    if (++tl == per) {
+      tl = 0;
+      ++n;
+    }
   }
 }
 
@@ -331,10 +351,12 @@ __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedPa
   __syncthreads();
   tc_fence_after();
 
+  // pairs of this CTA: blockIdx.x, + gridDim.x, ... (the launcher keeps gridDim.x <= npairs)
+  const int my_pairs = (int)((npairs - blockIdx.x + gridDim.x - 1) / gridDim.x);
   if (warp == kCWarps) {
-    fused_mma_warp<F, NPIX, 0>(smem, tmem, barO, barE, H0, npairs, lane);
+    fused_mma_warp<F, NPIX, 0>(smem, tmem, barO, barE, H0, my_pairs);
   } else if (warp == kCWarps + 1) {
-    fused_mma_warp<F, NPIX, 1>(smem, tmem, barO, barE, H0, npairs, lane);
+    fused_mma_warp<F, NPIX, 1>(smem, tmem, barO, barE, H0, my_pairs);
   } else {
     // =========================== compute warps ===========================
     const int j = warp >> 2, q = warp & 3, sl = lane >> 4, c = q * 16 + (lane & 15);
@@ -358,118 +380,140 @@ __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedPa
     }
     const float* im_src = s_feat + im_s * feat_stride;
     unsigned char* im_dst = smem + L::off_b1 + im_s * L::b1_stride + im_kc * kLboB;
+    // rolling feature load: while pair n runs, the two feature-map rows conv1 has just left behind are
+    // refilled with rows 2tl-4, 2tl-3 of pair n+1 (thread = slot, row parity, column)
+    const bool fl_on = tid < 4 * F;
+    const int fl_s = tid / (2 * F), fl_r = (tid / F) & 1, fl_c = tid % F;
 
-    const int nsteps = H0 + 14;
+    const int per = H0 + 7, total = my_pairs * per + 7;
     const int H3 = H0 + 6;
     const float nborder = (float)((H3 + 2) * (W3 + 2) - H3 * W3);
     const float inv_area = 1.0f / (float)((H3 + 2) * (W3 + 2));
     uint32_t nO = 0, nE = 0;  // completed waits on the two MMA-group barriers
 
-    for (long long pair = blockIdx.x; pair < npairs; pair += gridDim.x) {
-      // ---- features of the two clips -> zero-padded, tf32-rounded map in shared memory ----
-      {
-        const int nvalid = (2 * pair + 1 < p.B) ? 2 * TF : TF;
-        const float* src = p.feats + 2 * pair * TF;
-        for (int i = tid; i < 2 * TF; i += kCThreads) {
-          const int s = i >= TF, rem = i - s * TF, fr = rem / F, fc = rem - fr * F;
-          s_feat[s * feat_stride + (fr + 2) * FP + fc + 2] = (i < nvalid) ? to_tf32(__ldg(src + i)) : 0.f;
+    // global average pool (interior sum + border constant) and fc of the pair whose pooling has finished:
+    // warp w takes outputs w, w + 12, ...; a lane sums two channels, the warp reduces
+    auto pool_fc = [&](long long pair) {
+      for (int o = warp; o < 2 * p.ncls; o += kCWarps) {
+        const int s = o / p.ncls, k = o - s * p.ncls;
+        float acc = 0.f;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const int ch = lane + 32 * h;
+          const float pooled = (s_pool[s * kFC + ch] + s_pool[(2 + s) * kFC + ch] + s_pool[(4 + s) * kFC + ch] +
+                                nborder * p.border[4 * kFC + ch]) * inv_area;
+          acc = fmaf(pooled, p.fc_w[ch * p.ncls + k], acc);
+        }
+#pragma unroll
+        for (int d = 16; d >= 1; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
+        const long long b = 2 * pair + s;
+        if (lane == 0 && b < p.B) p.logits[b * p.ncls + k] = acc + p.fc_b[k];
+      }
+    };
+
+    {  // features of the first pair -> zero-padded, tf32-rounded map in shared memory
+      const long long pair = blockIdx.x;
+      const int nvalid = (2 * pair + 1 < p.B) ? 2 * TF : TF;
+      const float* src = p.feats + 2 * pair * TF;
+      for (int i = tid; i < 2 * TF; i += kCThreads) {
+        const int s = i >= TF, rem = i - s * TF, fr = rem / F, fc = rem - fr * F;
+        s_feat[s * feat_stride + (fr + 2) * FP + fc + 2] = (i < nvalid) ? to_tf32(__ldg(src + i)) : 0.f;
+      }
+    }
+    float psum = 0.f;
+    V P[4][4], R[4][4];
+#pragma unroll
+    for (int l = 0; l < 4; ++l)
+#pragma unroll
+      for (int x = 0; x < 4; ++x) P[l][x] = R[l][x] = fsplat(0.f);
+    __syncthreads();
+
+    int tl = 0, n = 0, fc_n = -1;  // fc_n: pair (CTA-local index) whose pooled sums wait in s_pool
+    for (int tg = 0; tg < total; ++tg) {
+      // ================= phase A: depthwise of blocks 1 and 3 =================
+      float fl_v = 0.f;
+      const int fl_fr = 2 * tl - 4 + fl_r;
+      const bool fl_do = fl_on && n + 1 < my_pairs && fl_fr >= 0 && fl_fr < T;
+      if (fl_do) {
+        const long long clip = 2 * ((long long)blockIdx.x + (long long)(n + 1) * gridDim.x) + fl_s;
+        if (clip < p.B) fl_v = __ldg(p.feats + clip * TF + fl_fr * F + fl_c);
+      }
+      if (tg > 0) {  // the GEMMs issued after the previous phase A (pw1, pw3) have retired
+        mbar_wait(barO, nO & 1);
+        ++nO;
+        tc_fence_after();
+      }
+      if (seg_on) {
+        StageRow r = stage_row(tl, n, my_pairs, per, 2, H0 + 1);
+        if (r.on)
+          dw_seg<W0, 1>(my_ld + dw_row_col<false>(r.i, H0, 0 * kRingCols, 0), j, r.i >= 1, my_par + 0 * 3 * kFC,
+                        my_dst + 0 * 2 * L::bp_stride, P[0], R[0]);
+        r = stage_row(tl, n, my_pairs, per, 5, H0 + 5);
+        if (r.on)
+          dw_seg<W0 + 4, 1>(my_ld + dw_row_col<true>(r.i, H0 + 2, 2 * kRingCols, kConstCol + 32), j, r.i >= 1,
+                            my_par + 2 * 3 * kFC, my_dst + 2 * 2 * L::bp_stride, P[2], R[2]);
+      }
+      if (fc_n >= 0) {
+        pool_fc((long long)blockIdx.x + (long long)fc_n * gridDim.x);
+        fc_n = -1;
+      }
+      if (fl_do) s_feat[fl_s * feat_stride + (fl_fr + 2) * FP + fl_c + 2] = to_tf32(fl_v);
+      fence_proxy_async();
+      tc_fence_before();
+      __syncthreads();
+      // ================= phase B: conv1 im2col, depthwise of blocks 2 and 4, pooling =================
+      if (tg > 0) {  // the GEMMs issued after the previous phase B (conv1, pw2, pw4) have retired
+        mbar_wait(barE, nE & 1);
+        ++nE;
+        tc_fence_after();
+      }
+      if (tl < H0 && n < my_pairs && im_on) {
+        const float* rowp = im_src + 2 * tl * FP;
+        for (int x = im_xg; x < W0; x += 7) {
+          const float* q4 = rowp + 2 * x;
+          const float2 lo = *reinterpret_cast<const float2*>(q4 + im_off[0]);
+          const float2 hi = *reinterpret_cast<const float2*>(q4 + im_off[1]);
+          *reinterpret_cast<float4*>(im_dst + (x >> 3) * kSboB1 + (x & 7) * 16) = make_float4(lo.x, lo.y, hi.x, hi.y);
         }
       }
-      float psum = 0.f;
-      V P[4][4], R[4][4];
-#pragma unroll
-      for (int l = 0; l < 4; ++l)
-#pragma unroll
-        for (int x = 0; x < 4; ++x) P[l][x] = R[l][x] = fsplat(0.f);
-      __syncthreads();
-
-      for (int t = 0; t < nsteps; ++t) {
-        // ================= phase A: depthwise of blocks 1 and 3 =================
-        if (t > 0) {  // the GEMMs issued after the previous phase A (pw1, pw3) have retired
-          mbar_wait(barO, nO & 1);
-          ++nO;
-          tc_fence_after();
-        }
-        if (seg_on) {
-          int i = t - 2;
-          if (i >= 0 && i <= H0)
-            dw_seg<W0, 1>(my_ld + dw_row_col<false>(i, H0, 0 * kRingCols, 0), j, i >= 1, my_par + 0 * 3 * kFC,
-                          my_dst + 0 * 2 * L::bp_stride, P[0], R[0]);
-          i = t - 5;
-          if (i >= 0 && i <= H0 + 4)
-            dw_seg<W0 + 4, 1>(my_ld + dw_row_col<true>(i, H0 + 2, 2 * kRingCols, kConstCol + 32), j, i >= 1,
-                              my_par + 2 * 3 * kFC, my_dst + 2 * 2 * L::bp_stride, P[2], R[2]);
-        }
-        fence_proxy_async();
-        tc_fence_before();
-        __syncthreads();
-        // ================= phase B: conv1 im2col, depthwise of blocks 2 and 4, pooling =================
-        if (t > 0) {  // the GEMMs issued after the previous phase B (conv1, pw2, pw4) have retired
-          mbar_wait(barE, nE & 1);
-          ++nE;
-          tc_fence_after();
-        }
-        if (t < H0 && im_on) {
-          const float* rowp = im_src + 2 * t * FP;
-          for (int x = im_xg; x < W0; x += 7) {
-            const float* q4 = rowp + 2 * x;
-            const float2 lo = *reinterpret_cast<const float2*>(q4 + im_off[0]);
-            const float2 hi = *reinterpret_cast<const float2*>(q4 + im_off[1]);
-            *reinterpret_cast<float4*>(im_dst + (x >> 3) * kSboB1 + (x & 7) * 16) = make_float4(lo.x, lo.y, hi.x, hi.y);
-          }
-        }
-        if (seg_on) {
-          int i = t - 3;
-          if (i >= 0 && i <= H0 + 2)
-            dw_seg<W0 + 2, 1>(my_ld + dw_row_col<true>(i, H0, 1 * kRingCols, kConstCol), j, i >= 1, my_par + 1 * 3 * kFC,
-                              my_dst + 1 * 2 * L::bp_stride, P[1], R[1]);
-          i = t - 6;
-          if (i >= 0 && i <= H0 + 6)
-            dw_seg<W0 + 6, 0>(my_ld + dw_row_col<true>(i, H0 + 4, 3 * kRingCols, kConstCol + 64), j, i >= 1,
-                              my_par + 3 * 3 * kFC, my_dst + 3 * 2 * L::bp_stride, P[3], R[3]);
-          const int r = t - 8;
-          if (r >= 0 && r < H3) {  // pooling of the last block's row r (interior pixels; the border is added at the end)
-            uint32_t raw[8];
-            asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                         : "=r"(raw[0]), "=r"(raw[1]), "=r"(raw[2]), "=r"(raw[3]), "=r"(raw[4]), "=r"(raw[5]), "=r"(raw[6]),
-                           "=r"(raw[7])
-                         : "r"(my_tmem + (uint32_t)kAcc4Col + (uint32_t)(8 * j))
-                         : "memory");
+      {
+        StageRow r = stage_row(tl, n, my_pairs, per, 3, H0 + 3);
+        if (seg_on && r.on)
+          dw_seg<W0 + 2, 1>(my_ld + dw_row_col<true>(r.i, H0, 1 * kRingCols, kConstCol), j, r.i >= 1, my_par + 1 * 3 * kFC,
+                            my_dst + 1 * 2 * L::bp_stride, P[1], R[1]);
+        r = stage_row(tl, n, my_pairs, per, 6, H0 + 7);
+        if (seg_on && r.on)
+          dw_seg<W0 + 6, 0>(my_ld + dw_row_col<true>(r.i, H0 + 4, 3 * kRingCols, kConstCol + 64), j, r.i >= 1,
+                            my_par + 3 * 3 * kFC, my_dst + 3 * 2 * L::bp_stride, P[3], R[3]);
+        r = stage_row(tl, n, my_pairs, per, 8, H3);
+        if (r.on) {  // pooling of the last block's row (interior pixels; the border is added in pool_fc)
+          if (seg_on) {
+            float raw[8];
+            tc_ld8(my_tmem + (uint32_t)kAcc4Col + (uint32_t)(8 * j), raw);
             tc_wait_ld();
 #pragma unroll
-            for (int x = 0; x < 8; ++x) psum += fmaxf(__uint_as_float(raw[x]), 0.f);  // columns past the layer are 0
+            for (int x = 0; x < 8; ++x) psum += fmaxf(raw[x], 0.f);  // columns past the layer are 0
+          }
+          if (r.i == H3 - 1) {  // last row of the pair: hand the sums to pool_fc (next phase A)
+            s_pool[(j * 2 + sl) * kFC + c] = psum;
+            psum = 0.f;
+            fc_n = tl >= 8 ? n : n - 1;
           }
         }
-        fence_proxy_async();
-        tc_fence_before();
-        __syncthreads();
       }
-      // drain the last step's (empty) GEMM groups so the barrier phases stay in step
-      mbar_wait(barO, nO & 1);
-      ++nO;
-      mbar_wait(barE, nE & 1);
-      ++nE;
-      tc_fence_after();
-
-      // ---- global average pool (interior sum + border constant) and fc ----
-      s_pool[(j * 2 + sl) * kFC + c] = psum;
+      fence_proxy_async();
+      tc_fence_before();
       __syncthreads();
-      for (int i = tid; i < 2 * p.ncls; i += kCThreads) {
-        const int s = i / p.ncls, k = i - s * p.ncls;
-        const long long b = 2 * pair + s;
-        if (b < p.B) {
-          float acc = p.fc_b[k];
-          for (int ch = 0; ch < kFC; ++ch) {
-            const float pooled = (s_pool[s * kFC + ch] + s_pool[(2 + s) * kFC + ch] + s_pool[(4 + s) * kFC + ch] +
-                                  nborder * p.border[4 * kFC + ch]) * inv_area;
-            acc = fmaf(pooled, p.fc_w[ch * p.ncls + k], acc);
-          }
-          p.logits[b * p.ncls + k] = acc;
-        }
+      if (++tl == per) {
+        tl = 0;
+        ++n;
       }
-      // the next pair's feature load overwrites s_feat / s_pool only after this barrier
-      __syncthreads();
     }
+    // the last step's GEMM groups are empty; wait for them so that nothing is in flight at dealloc
+    mbar_wait(barO, nO & 1);
+    mbar_wait(barE, nE & 1);
+    tc_fence_after();
+    if (fc_n >= 0) pool_fc((long long)blockIdx.x + (long long)fc_n * gridDim.x);
   }
   tc_fence_before();
   __syncthreads();

@@ -69,6 +69,27 @@ def test_fused_equals_layered(T, F, B):
     np.testing.assert_allclose(fused, want, rtol=1e-3, atol=1e-4)
 
 
+@pytest.mark.parametrize("T,F,B", [(99, 40, 893), (31, 10, 1201), (7, 40, 601)])
+def test_fused_streams_clip_pairs_back_to_back(T, F, B):
+    """More clip pairs than SMs: every CTA of the fused kernel streams several pairs through its row pipeline
+    without draining it (period H0 + 7 steps), refilling the feature map row by row behind conv1; odd B
+    leaves the last pair half empty.  Checked against the layered fp32 kernels on every clip and against
+    the float64 oracle on the first and last clips."""
+    sd = dscnn_ref.init_state_dict(seed=T + F)
+    m = DepthwiseSeparableConv()
+    m.load_state_dict(sd)
+    m = m.cuda()
+    x = torch.randn(B, 1, T, F, generator=torch.Generator().manual_seed(B)) * 4.0
+    fused = m(x.cuda()).cpu().numpy()
+    m.set_kernel_path("layered")
+    layered = m(x.cuda()).cpu().numpy()
+    np.testing.assert_allclose(fused, layered, rtol=1e-3, atol=1e-4)
+    idx = list(range(8)) + list(range(B - 8, B))
+    want = dscnn_ref.forward({k: v.double() for k, v in sd.items()}, x[idx].double()).numpy()
+    np.testing.assert_allclose(fused[idx], want, rtol=1e-3, atol=1e-4)
+    assert (fused.argmax(1) == layered.argmax(1)).mean() > 0.999
+
+
 @pytest.mark.parametrize("channels,blocks,T,F,B", [(276, 5, 99, 40, 3), (64, 4, 99, 13, 9), (32, 2, 49, 26, 5),
                                                   (100, 3, 31, 40, 2), (512, 1, 20, 12, 2)])
 def test_tensor_core_gemm_path_any_channels(channels, blocks, T, F, B):
