@@ -19,7 +19,7 @@
 // per partial, so results are deterministic only up to fp32 summation order.
 #include <cstring>
 
-#include "common.cuh"
+#include "mfcc_dev.cuh"
 
 namespace kws {
 
@@ -119,33 +119,47 @@ __global__ void ce_fc_bwd_kernel(const float* __restrict__ logits, const long lo
 }
 
 
-// Pointwise (1x1, padding=1) + ReLU backward of one block, 32 output pixels per tile.
+// Pointwise (1x1, padding=1) + ReLU backward of one block, kPwTP output pixels per tile.
 //   out  [B, H+2, W+2, C]  saved block output (post-ReLU)        d_io [B, H, W, C] saved depthwise output,
 //   dout same shape (or, LAST, dpooled[b][c] * inv_area)           overwritten with its gradient dD
+// Two register-tiled fp32 GEMMs per tile run side by side on the two halves of the CTA (packed f32x2 FMAs,
+// one 16-byte + two 16-byte shared loads per 32 FMAs):
+//   threads   0..127  dD[px][ci]  = sum_co dY[px][co] W[co][ci]   4 px x 8 ci per thread, K = co, written per tile
+//   threads 128..255  dW[co][ci] += sum_px dY[px][co] D[px][ci]   4 co x 8 ci per thread, K = px, kept in registers
+// dY is staged both as [px][co] and transposed [co][px] so that each GEMM reads its K rows as float4.
+constexpr int kPwTP = 64;                      // pixels per tile
+constexpr int kPwLd = kPwTP + 4;               // row pitch of the transposed dY tile (16-byte aligned, bank spread)
+constexpr size_t kPwSmem = (size_t)(kTC * kTC + 2 * kPwTP * kTC + kTC * kPwLd) * 4;
+
 __global__ void __launch_bounds__(256) pw_bwd_kernel(const float* __restrict__ out, const float* __restrict__ dout,
                                                      const float* __restrict__ dpooled, float inv_area,
                                                      float* __restrict__ d_io, const float* __restrict__ w_flat /*[co][ci]*/,
                                                      float* __restrict__ g_w, float* __restrict__ g_b, long long B, int H,
                                                      int W) {
-  constexpr int C = kTC, TP = 32;
+  constexpr int C = kTC, TP = kPwTP;
   extern __shared__ __align__(16) float sm_pw[];
-  float* s_w = sm_pw;                 // [64][64]
-  float* s_dy = s_w + C * C;          // [32][64]
-  float* s_d = s_dy + TP * C;         // [32][64]
+  float* s_w = sm_pw;                 // [64 co][64 ci]
+  float* s_dy = s_w + C * C;          // [TP px][64 co]
+  float* s_d = s_dy + TP * C;         // [TP px][64 ci]
+  float* s_dyT = s_d + TP * C;        // [64 co][TP (+4) px]
   const int tid = threadIdx.x;
   const int Ho = H + 2, Wo = W + 2;
   const long long npix = B * Ho * (long long)Wo, ntiles = (npix + TP - 1) / TP;
   for (int i = tid; i < C * C / 4; i += 256) reinterpret_cast<float4*>(s_w)[i] = reinterpret_cast<const float4*>(w_flat)[i];
-  float accw[16];
+  const bool wgrad = tid >= 128;
+  const int t7 = tid & 127, rg = t7 >> 3, cig = (t7 & 7) * 8;  // row group (4 px or 4 co), first of 8 ci
+  V accw[4][4];                        // wgrad threads: dW[4 co][8 ci] as ci pairs
+  float accb[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-  for (int i = 0; i < 16; ++i) accw[i] = 0.f;
-  float accb = 0.f;
-  const int wco = tid >> 2, wci = (tid & 3) * 16;   // weight-gradient ownership
-  const int dpx = tid >> 3, dci = (tid & 7) * 8;     // input-gradient ownership
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int jx = 0; jx < 4; ++jx) accw[i][jx] = fsplat(0.f);
+  const int q = tid & 15, px0 = tid >> 4;  // staging: channel quad, first pixel (then +16, +32, +48)
   for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     __syncthreads();
-    for (int idx = tid; idx < TP * (C / 4); idx += 256) {
-      const int px = idx >> 4, q = idx & 15;
+#pragma unroll
+    for (int it = 0; it < TP / 16; ++it) {
+      const int px = px0 + 16 * it;
       const long long gp = tile * TP + px;
       float4 dy = make_float4(0.f, 0.f, 0.f, 0.f), dv = dy;
       if (gp < npix) {
@@ -165,51 +179,71 @@ __global__ void __launch_bounds__(256) pw_bwd_kernel(const float* __restrict__ o
       }
       reinterpret_cast<float4*>(s_dy + px * C)[q] = dy;
       reinterpret_cast<float4*>(s_d + px * C)[q] = dv;
+      s_dyT[(4 * q + 0) * kPwLd + px] = dy.x;
+      s_dyT[(4 * q + 1) * kPwLd + px] = dy.y;
+      s_dyT[(4 * q + 2) * kPwLd + px] = dy.z;
+      s_dyT[(4 * q + 3) * kPwLd + px] = dy.w;
     }
     __syncthreads();
-    if (tid < C) {
-#pragma unroll 8
-      for (int px = 0; px < TP; ++px) accb += s_dy[px * C + tid];
-    }
-    {  // dD[px][ci] = sum_co dY[px][co] W[co][ci]  (interior pixels only)
-      const long long gp = tile * TP + dpx;
-      if (gp < npix) {
-        const int wo = (int)(gp % Wo), ho = (int)((gp / Wo) % Ho);
-        const long long b = gp / ((long long)Wo * Ho);
-        if (ho >= 1 && ho <= H && wo >= 1 && wo <= W) {
-          float dd[8];
+    if (!wgrad) {  // dD[4 px][8 ci] = sum_co dY[px][co] W[co][ci]
+      V acc[4][4];
 #pragma unroll
-          for (int i = 0; i < 8; ++i) dd[i] = 0.f;
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int jx = 0; jx < 4; ++jx) acc[i][jx] = fsplat(0.f);
 #pragma unroll 4
-          for (int co = 0; co < C; ++co) {
-            const float a = s_dy[dpx * C + co];
-            const float4 w0 = *reinterpret_cast<const float4*>(s_w + co * C + dci);
-            const float4 w1 = *reinterpret_cast<const float4*>(s_w + co * C + dci + 4);
-            dd[0] = fmaf(a, w0.x, dd[0]); dd[1] = fmaf(a, w0.y, dd[1]); dd[2] = fmaf(a, w0.z, dd[2]); dd[3] = fmaf(a, w0.w, dd[3]);
-            dd[4] = fmaf(a, w1.x, dd[4]); dd[5] = fmaf(a, w1.y, dd[5]); dd[6] = fmaf(a, w1.z, dd[6]); dd[7] = fmaf(a, w1.w, dd[7]);
+      for (int co = 0; co < C; ++co) {
+        const float4 a = *reinterpret_cast<const float4*>(s_dyT + co * kPwLd + 4 * rg);
+        const float4 w0 = *reinterpret_cast<const float4*>(s_w + co * C + cig);
+        const float4 w1 = *reinterpret_cast<const float4*>(s_w + co * C + cig + 4);
+        const V wv[4] = {make_float2(w0.x, w0.y), make_float2(w0.z, w0.w), make_float2(w1.x, w1.y), make_float2(w1.z, w1.w)};
+        const float av[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int jx = 0; jx < 4; ++jx) acc[i][jx] = ffma(fsplat(av[i]), wv[jx], acc[i][jx]);
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {  // interior pixels only: the border's input is the zero padding
+        const long long gp = tile * TP + 4 * rg + i;
+        if (gp < npix) {
+          const int wo = (int)(gp % Wo), ho = (int)((gp / Wo) % Ho);
+          const long long b = gp / ((long long)Wo * Ho);
+          if (ho >= 1 && ho <= H && wo >= 1 && wo <= W) {
+            float* dst = d_io + ((b * H + ho - 1) * W + wo - 1) * C + cig;
+            *reinterpret_cast<float4*>(dst) = make_float4(acc[i][0].x, acc[i][0].y, acc[i][1].x, acc[i][1].y);
+            *reinterpret_cast<float4*>(dst + 4) = make_float4(acc[i][2].x, acc[i][2].y, acc[i][3].x, acc[i][3].y);
           }
-          float* dst = d_io + ((b * H + ho - 1) * W + wo - 1) * C + dci;
-          *reinterpret_cast<float4*>(dst) = make_float4(dd[0], dd[1], dd[2], dd[3]);
-          *reinterpret_cast<float4*>(dst + 4) = make_float4(dd[4], dd[5], dd[6], dd[7]);
+        }
+      }
+    } else {  // dW[4 co][8 ci] += sum_px dY[px][co] D[px][ci]  (D is zero for border pixels); bias gradient alongside
+#pragma unroll 4
+      for (int px = 0; px < TP; ++px) {
+        const float4 a = *reinterpret_cast<const float4*>(s_dy + px * C + 4 * rg);
+        const float4 d0 = *reinterpret_cast<const float4*>(s_d + px * C + cig);
+        const float4 d1 = *reinterpret_cast<const float4*>(s_d + px * C + cig + 4);
+        const V dv[4] = {make_float2(d0.x, d0.y), make_float2(d0.z, d0.w), make_float2(d1.x, d1.y), make_float2(d1.z, d1.w)};
+        const float av[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+#pragma unroll
+          for (int jx = 0; jx < 4; ++jx) accw[i][jx] = ffma(fsplat(av[i]), dv[jx], accw[i][jx]);
+          accb[i] += av[i];
         }
       }
     }
-#pragma unroll 4
-    for (int px = 0; px < TP; ++px) {  // dW[co][ci] += dY[px][co] D[px][ci]  (D is zero for border pixels)
-      const float a = s_dy[px * C + wco];
+  }
+  if (wgrad) {
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const float4 dv = *reinterpret_cast<const float4*>(s_d + px * C + wci + 4 * i);
-        accw[4 * i + 0] = fmaf(a, dv.x, accw[4 * i + 0]);
-        accw[4 * i + 1] = fmaf(a, dv.y, accw[4 * i + 1]);
-        accw[4 * i + 2] = fmaf(a, dv.z, accw[4 * i + 2]);
-        accw[4 * i + 3] = fmaf(a, dv.w, accw[4 * i + 3]);
+    for (int i = 0; i < 4; ++i) {
+#pragma unroll
+      for (int jx = 0; jx < 4; ++jx) {
+        atomicAdd(&g_w[(4 * rg + i) * C + cig + 2 * jx], accw[i][jx].x);
+        atomicAdd(&g_w[(4 * rg + i) * C + cig + 2 * jx + 1], accw[i][jx].y);
       }
+      if (cig == 0) atomicAdd(&g_b[4 * rg + i], accb[i]);
     }
   }
-#pragma unroll
-  for (int i = 0; i < 16; ++i) atomicAdd(&g_w[wco * C + wci + i], accw[i]);
-  if (tid < C) atomicAdd(&g_b[tid], accb);
 }
 
 // Depthwise 3x3 (padding 1) backward: thread = (pixel slot, channel quad).
@@ -416,13 +450,13 @@ int kws_train_forward_backward(kws_handle_t h, const float* params_dev, const fl
                                                 1.0f / (float)B);
     KWS_CHECK_LAUNCH(h);
   }
-  const size_t pw_smem = (size_t)(C * C + 2 * 32 * C) * 4;
+  const size_t pw_smem = kPwSmem;
   KWS_CUDA(cudaFuncSetAttribute(pw_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pw_smem));
   const float* dout = nullptr;
   for (int l = nb - 1; l >= 0; --l) {
     const int H = H1 + 2 * l, W = W1 + 2 * l;  // block input size; output is (H+2) x (W+2)
-    const long long ntiles = (B * (long long)(H + 2) * (W + 2) + 31) / 32;
-    long long g = ntiles < h->sm_count * 4LL ? ntiles : h->sm_count * 4LL;
+    const long long ntiles = (B * (long long)(H + 2) * (W + 2) + kPwTP - 1) / kPwTP;
+    long long g = ntiles < h->sm_count * 3LL ? ntiles : h->sm_count * 3LL;
     const bool last = (l == nb - 1);
     pw_bwd_kernel<<<(unsigned)g, 256, pw_smem, st>>>(w.L[l + 1], dout, last ? w.dpooled : nullptr,
                                                      1.0f / (float)((H + 2) * (W + 2)), w.D[l], params_dev + fl.pww(l),
