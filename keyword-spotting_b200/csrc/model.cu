@@ -11,7 +11,7 @@
 #include <cstring>
 #include <string>
 
-#include "common.cuh"
+#include "mfcc_dev.cuh"
 
 namespace kws {
 
@@ -125,18 +125,34 @@ __global__ void dsblock_kernel(const float* __restrict__ in, float* __restrict__
   }
 }
 
-// adaptive_avg_pool2d(1,1) + fc: one CTA per clip
+// adaptive_avg_pool2d(1,1) + fc: one CTA per clip; the pixels are split over blockDim / C thread groups
 __global__ void pool_fc_kernel(const float* __restrict__ in, float* __restrict__ logits,
                                const float* __restrict__ fc_w /*[C][ncls]*/,
                                const float* __restrict__ fc_b, long long B, int HW, int C, int ncls,
                                float* __restrict__ pooled_out /* [B,C] for training, or null */) {
-  extern __shared__ __align__(16) float s_pool[];  // [C]
+  extern __shared__ __align__(16) float s_pool[];  // [C] means, then [npg][C] partial sums
+  float* s_part = s_pool + C;
+  const int npg = C <= (int)blockDim.x ? (int)blockDim.x / C : 1;
   for (long long b = blockIdx.x; b < B; b += gridDim.x) {
     __syncthreads();
     const float* x = in + b * (long long)HW * C;
+    for (int t = threadIdx.x; t < npg * C; t += blockDim.x) {
+      const int pg = t / C, c = t - pg * C;
+      float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+      int p = pg;
+      for (; p + 3 * npg < HW; p += 4 * npg) {
+        s0 += x[(size_t)p * C + c];
+        s1 += x[(size_t)(p + npg) * C + c];
+        s2 += x[(size_t)(p + 2 * npg) * C + c];
+        s3 += x[(size_t)(p + 3 * npg) * C + c];
+      }
+      for (; p < HW; p += npg) s0 += x[(size_t)p * C + c];
+      s_part[pg * C + c] = (s0 + s1) + (s2 + s3);
+    }
+    __syncthreads();
     for (int c = threadIdx.x; c < C; c += blockDim.x) {
       float s = 0.f;
-      for (int p = 0; p < HW; ++p) s += x[(size_t)p * C + c];
+      for (int pg = 0; pg < npg; ++pg) s += s_part[pg * C + c];
       s_pool[c] = s / (float)HW;
       if (pooled_out) pooled_out[b * C + c] = s_pool[c];
     }
@@ -145,6 +161,104 @@ __global__ void pool_fc_kernel(const float* __restrict__ in, float* __restrict__
       float acc = fc_b[k];
       for (int c = 0; c < C; ++c) acc = fmaf(s_pool[c], fc_w[c * ncls + k], acc);
       logits[b * ncls + k] = acc;
+    }
+  }
+}
+constexpr int kPoolThreads = 256;
+static size_t pool_smem(int C) { return (size_t)((C <= kPoolThreads ? kPoolThreads / C : 1) + 1) * C * 4; }
+
+// Training forward of one block for C = 64 (the reference network): depthwise 3x3 into a transposed shared
+// tile, then the pointwise 1x1 as a register-tiled fp32 GEMM (4 px x 8 co per thread, packed f32x2 FMAs,
+// weights in shared memory).  Same results as dsblock_kernel up to fp32 summation order; saves the depthwise
+// output for the backward pass.
+constexpr int kB64Pix = 128;
+constexpr size_t kB64Smem = (size_t)(64 * 64 + 64 * kB64Pix) * 4;
+__global__ void __launch_bounds__(256) dsblock64_kernel(const float* __restrict__ in, float* __restrict__ out,
+                                                        const float* __restrict__ dw_w /*[9][64]*/,
+                                                        const float* __restrict__ dw_b,
+                                                        const float* __restrict__ pw_w /*[ci][co]*/,
+                                                        const float* __restrict__ pw_b, long long B, int H, int W,
+                                                        float* __restrict__ dsave) {
+  constexpr int C = 64, TP = kB64Pix;
+  extern __shared__ __align__(16) float s_b64[];
+  float* s_w = s_b64;            // [64 ci][64 co]
+  float* s_dT = s_w + C * C;     // [64 ci][TP px], px index XOR-swizzled per channel quad
+  const int tid = threadIdx.x;
+  const int Ho = H + 2, Wo = W + 2;
+  const long long npix = B * Ho * (long long)Wo, ntiles = (npix + TP - 1) / TP;
+  for (int i = tid; i < C * C / 4; i += 256) reinterpret_cast<float4*>(s_w)[i] = __ldg(reinterpret_cast<const float4*>(pw_w) + i);
+  const int q = tid & 15, px0 = tid >> 4;
+  const int rg = tid >> 3, cg = (tid & 7) * 4;  // GEMM ownership: pixels 4rg..4rg+3, co = cg..cg+3 and 32+cg..32+cg+3
+  float4 kw[9];
+#pragma unroll
+  for (int t = 0; t < 9; ++t) kw[t] = __ldg(reinterpret_cast<const float4*>(dw_w + t * C) + q);
+  const float4 kb = __ldg(reinterpret_cast<const float4*>(dw_b) + q);
+  const float4 b0 = __ldg(reinterpret_cast<const float4*>(pw_b + cg)), b1 = __ldg(reinterpret_cast<const float4*>(pw_b + 32 + cg));
+  for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    __syncthreads();
+#pragma unroll 2
+    for (int it = 0; it < TP / 16; ++it) {
+      const int pl = px0 + 16 * it;
+      const long long pix = tile * TP + pl;
+      float4 d = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (pix < npix) {
+        const int wo = (int)(pix % Wo), ho = (int)((pix / Wo) % Ho);
+        const long long b = pix / ((long long)Wo * Ho);
+        if (ho >= 1 && ho <= H && wo >= 1 && wo <= W) {
+          const int h = ho - 1, wc = wo - 1;
+          d = kb;
+#pragma unroll
+          for (int i = 0; i < 3; ++i) {
+            const int hi = h + i - 1;
+            if (hi < 0 || hi >= H) continue;
+#pragma unroll
+            for (int jx = 0; jx < 3; ++jx) {
+              const int wi = wc + jx - 1;
+              if (wi < 0 || wi >= W) continue;
+              const float4 x = __ldg(reinterpret_cast<const float4*>(in + ((b * H + hi) * W + wi) * C) + q);
+              const float4 k = kw[i * 3 + jx];
+              d.x = fmaf(x.x, k.x, d.x); d.y = fmaf(x.y, k.y, d.y);
+              d.z = fmaf(x.z, k.z, d.z); d.w = fmaf(x.w, k.w, d.w);
+            }
+          }
+          if (dsave) reinterpret_cast<float4*>(dsave + ((b * H + h) * W + wc) * C)[q] = d;
+        }
+      }
+      const int pls = pl ^ (4 * (q & 7));
+      s_dT[(4 * q + 0) * TP + pls] = d.x;
+      s_dT[(4 * q + 1) * TP + pls] = d.y;
+      s_dT[(4 * q + 2) * TP + pls] = d.z;
+      s_dT[(4 * q + 3) * TP + pls] = d.w;
+    }
+    __syncthreads();
+    V acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      acc[i][0] = make_float2(b0.x, b0.y); acc[i][1] = make_float2(b0.z, b0.w);
+      acc[i][2] = make_float2(b1.x, b1.y); acc[i][3] = make_float2(b1.z, b1.w);
+    }
+#pragma unroll 4
+    for (int ci = 0; ci < C; ++ci) {
+      const float4 a = *reinterpret_cast<const float4*>(s_dT + ci * TP + ((4 * rg) ^ (4 * ((ci >> 2) & 7))));
+      const float4 w0 = *reinterpret_cast<const float4*>(s_w + ci * C + cg);
+      const float4 w1 = *reinterpret_cast<const float4*>(s_w + ci * C + 32 + cg);
+      const V wv[4] = {make_float2(w0.x, w0.y), make_float2(w0.z, w0.w), make_float2(w1.x, w1.y), make_float2(w1.z, w1.w)};
+      const float av[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int jx = 0; jx < 4; ++jx) acc[i][jx] = ffma(fsplat(av[i]), wv[jx], acc[i][jx]);
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {  // border pixels had a zero depthwise row: ReLU(bias), the padding=1 quirk
+      const long long pix = tile * TP + 4 * rg + i;
+      if (pix < npix) {
+        float* dst = out + pix * C;
+        *reinterpret_cast<float4*>(dst + cg) = make_float4(fmaxf(acc[i][0].x, 0.f), fmaxf(acc[i][0].y, 0.f),
+                                                           fmaxf(acc[i][1].x, 0.f), fmaxf(acc[i][1].y, 0.f));
+        *reinterpret_cast<float4*>(dst + 32 + cg) = make_float4(fmaxf(acc[i][2].x, 0.f), fmaxf(acc[i][2].y, 0.f),
+                                                                fmaxf(acc[i][3].x, 0.f), fmaxf(acc[i][3].y, 0.f));
+      }
     }
   }
 }
@@ -215,17 +329,26 @@ int train_forward_layers(kws_handle_t h, const float* feats_dev, int64_t B, int 
     const long long npix = B * (long long)(H + 2) * (W + 2);
     long long g = (npix + kBlkPix - 1) / kBlkPix;
     if (g > h->sm_count * 16LL) g = h->sm_count * 16LL;
-    int threads = kBlkPix * cq;
-    if (threads > 512) threads = 512;
-    dsblock_kernel<<<(unsigned)g, threads, kBlkPix * C * 4, st>>>(
-        w.L[i], w.L[i + 1], m.d_dw_w + (size_t)i * 9 * C, m.d_dw_b + (size_t)i * C, m.d_pw_w + (size_t)i * C * C,
-        m.d_pw_b + (size_t)i * C, B, H, W, C, w.D[i]);
+    if (C == 64) {
+      const long long nt = (npix + kB64Pix - 1) / kB64Pix;
+      const long long g64 = nt < h->sm_count * 3LL ? nt : h->sm_count * 3LL;
+      KWS_CUDA(cudaFuncSetAttribute(dsblock64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kB64Smem));
+      dsblock64_kernel<<<(unsigned)g64, 256, kB64Smem, st>>>(w.L[i], w.L[i + 1], m.d_dw_w + (size_t)i * 9 * C,
+                                                            m.d_dw_b + (size_t)i * C, m.d_pw_w + (size_t)i * C * C,
+                                                            m.d_pw_b + (size_t)i * C, B, H, W, w.D[i]);
+    } else {
+      int threads = kBlkPix * cq;
+      if (threads > 512) threads = 512;
+      dsblock_kernel<<<(unsigned)g, threads, kBlkPix * C * 4, st>>>(
+          w.L[i], w.L[i + 1], m.d_dw_w + (size_t)i * 9 * C, m.d_dw_b + (size_t)i * C, m.d_pw_w + (size_t)i * C * C,
+          m.d_pw_b + (size_t)i * C, B, H, W, C, w.D[i]);
+    }
     KWS_CHECK_LAUNCH(h);
     H += 2;
     W += 2;
   }
   long long g = B < h->sm_count * 8LL ? B : h->sm_count * 8LL;
-  pool_fc_kernel<<<(unsigned)g, 128, C * 4, st>>>(w.L[nb], w.logits, m.d_fc_w, m.d_fc_b, B, H * W, C, K, w.pooled);
+  pool_fc_kernel<<<(unsigned)g, kPoolThreads, pool_smem(C), st>>>(w.L[nb], w.logits, m.d_fc_w, m.d_fc_b, B, H * W, C, K, w.pooled);
   KWS_CHECK_LAUNCH(h);
   return KWS_OK;
 }
@@ -433,7 +556,7 @@ int kws_model_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t
       if (rc < 0) return rc;
       if (rc == 1) {
         long long g = nbat < h->sm_count * 8LL ? nbat : h->sm_count * 8LL;
-        pool_fc_kernel<<<(unsigned)g, 128, C * 4, st>>>(last, logits_dev + b0 * K, m.d_fc_w, m.d_fc_b, nbat, Hl * Wl, C, K,
+        pool_fc_kernel<<<(unsigned)g, kPoolThreads, pool_smem(C), st>>>(last, logits_dev + b0 * K, m.d_fc_w, m.d_fc_b, nbat, Hl * Wl, C, K,
                                                         nullptr);
         KWS_CHECK_LAUNCH(h);
         continue;
@@ -464,7 +587,7 @@ int kws_model_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t
     }
     {
       long long g = nbat < h->sm_count * 8LL ? nbat : h->sm_count * 8LL;
-      pool_fc_kernel<<<(unsigned)g, 128, C * 4, st>>>(cur, logits_dev + b0 * K, m.d_fc_w, m.d_fc_b, nbat,
+      pool_fc_kernel<<<(unsigned)g, kPoolThreads, pool_smem(C), st>>>(cur, logits_dev + b0 * K, m.d_fc_w, m.d_fc_b, nbat,
                                                       H * W, C, K, nullptr);
       KWS_CHECK_LAUNCH(h);
     }

@@ -128,7 +128,7 @@ __global__ void ce_fc_bwd_kernel(const float* __restrict__ logits, const long lo
 //   threads 128..255  dW[co][ci] += sum_px dY[px][co] D[px][ci]   4 co x 8 ci per thread, K = px, kept in registers
 // dY is staged both as [px][co] and transposed [co][px] so that each GEMM reads its K rows as float4.
 constexpr int kPwTP = 64;                      // pixels per tile
-constexpr int kPwLd = kPwTP + 4;               // row pitch of the transposed dY tile (16-byte aligned, bank spread)
+constexpr int kPwLd = kPwTP;                   // row pitch of the transposed dY tile (px index XOR-swizzled per channel quad)
 constexpr size_t kPwSmem = (size_t)(kTC * kTC + 2 * kPwTP * kTC + kTC * kPwLd) * 4;
 
 __global__ void __launch_bounds__(256) pw_bwd_kernel(const float* __restrict__ out, const float* __restrict__ dout,
@@ -147,7 +147,7 @@ __global__ void __launch_bounds__(256) pw_bwd_kernel(const float* __restrict__ o
   const long long npix = B * Ho * (long long)Wo, ntiles = (npix + TP - 1) / TP;
   for (int i = tid; i < C * C / 4; i += 256) reinterpret_cast<float4*>(s_w)[i] = reinterpret_cast<const float4*>(w_flat)[i];
   const bool wgrad = tid >= 128;
-  const int t7 = tid & 127, rg = t7 >> 3, cig = (t7 & 7) * 8;  // row group (4 px or 4 co), first of 8 ci
+  const int t7 = tid & 127, rg = t7 >> 3, cig = (t7 & 7) * 4;  // row group (4 px or 4 co); ci = cig..cig+3 and 32+cig..32+cig+3
   V accw[4][4];                        // wgrad threads: dW[4 co][8 ci] as ci pairs
   float accb[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
@@ -179,10 +179,11 @@ __global__ void __launch_bounds__(256) pw_bwd_kernel(const float* __restrict__ o
       }
       reinterpret_cast<float4*>(s_dy + px * C)[q] = dy;
       reinterpret_cast<float4*>(s_d + px * C)[q] = dv;
-      s_dyT[(4 * q + 0) * kPwLd + px] = dy.x;
-      s_dyT[(4 * q + 1) * kPwLd + px] = dy.y;
-      s_dyT[(4 * q + 2) * kPwLd + px] = dy.z;
-      s_dyT[(4 * q + 3) * kPwLd + px] = dy.w;
+      const int pxs = px ^ (4 * (q & 7));  // swizzle: the 16 channel quads of a warp hit 8 different bank groups
+      s_dyT[(4 * q + 0) * kPwLd + pxs] = dy.x;
+      s_dyT[(4 * q + 1) * kPwLd + pxs] = dy.y;
+      s_dyT[(4 * q + 2) * kPwLd + pxs] = dy.z;
+      s_dyT[(4 * q + 3) * kPwLd + pxs] = dy.w;
     }
     __syncthreads();
     if (!wgrad) {  // dD[4 px][8 ci] = sum_co dY[px][co] W[co][ci]
@@ -193,9 +194,9 @@ __global__ void __launch_bounds__(256) pw_bwd_kernel(const float* __restrict__ o
         for (int jx = 0; jx < 4; ++jx) acc[i][jx] = fsplat(0.f);
 #pragma unroll 4
       for (int co = 0; co < C; ++co) {
-        const float4 a = *reinterpret_cast<const float4*>(s_dyT + co * kPwLd + 4 * rg);
+        const float4 a = *reinterpret_cast<const float4*>(s_dyT + co * kPwLd + ((4 * rg) ^ (4 * ((co >> 2) & 7))));
         const float4 w0 = *reinterpret_cast<const float4*>(s_w + co * C + cig);
-        const float4 w1 = *reinterpret_cast<const float4*>(s_w + co * C + cig + 4);
+        const float4 w1 = *reinterpret_cast<const float4*>(s_w + co * C + 32 + cig);
         const V wv[4] = {make_float2(w0.x, w0.y), make_float2(w0.z, w0.w), make_float2(w1.x, w1.y), make_float2(w1.z, w1.w)};
         const float av[4] = {a.x, a.y, a.z, a.w};
 #pragma unroll
@@ -212,7 +213,7 @@ __global__ void __launch_bounds__(256) pw_bwd_kernel(const float* __restrict__ o
           if (ho >= 1 && ho <= H && wo >= 1 && wo <= W) {
             float* dst = d_io + ((b * H + ho - 1) * W + wo - 1) * C + cig;
             *reinterpret_cast<float4*>(dst) = make_float4(acc[i][0].x, acc[i][0].y, acc[i][1].x, acc[i][1].y);
-            *reinterpret_cast<float4*>(dst + 4) = make_float4(acc[i][2].x, acc[i][2].y, acc[i][3].x, acc[i][3].y);
+            *reinterpret_cast<float4*>(dst + 32) = make_float4(acc[i][2].x, acc[i][2].y, acc[i][3].x, acc[i][3].y);
           }
         }
       }
@@ -221,7 +222,7 @@ __global__ void __launch_bounds__(256) pw_bwd_kernel(const float* __restrict__ o
       for (int px = 0; px < TP; ++px) {
         const float4 a = *reinterpret_cast<const float4*>(s_dy + px * C + 4 * rg);
         const float4 d0 = *reinterpret_cast<const float4*>(s_d + px * C + cig);
-        const float4 d1 = *reinterpret_cast<const float4*>(s_d + px * C + cig + 4);
+        const float4 d1 = *reinterpret_cast<const float4*>(s_d + px * C + 32 + cig);
         const V dv[4] = {make_float2(d0.x, d0.y), make_float2(d0.z, d0.w), make_float2(d1.x, d1.y), make_float2(d1.z, d1.w)};
         const float av[4] = {a.x, a.y, a.z, a.w};
 #pragma unroll
@@ -238,8 +239,9 @@ __global__ void __launch_bounds__(256) pw_bwd_kernel(const float* __restrict__ o
     for (int i = 0; i < 4; ++i) {
 #pragma unroll
       for (int jx = 0; jx < 4; ++jx) {
-        atomicAdd(&g_w[(4 * rg + i) * C + cig + 2 * jx], accw[i][jx].x);
-        atomicAdd(&g_w[(4 * rg + i) * C + cig + 2 * jx + 1], accw[i][jx].y);
+        const int ci = cig + (jx >> 1) * 32 + (jx & 1) * 2;
+        atomicAdd(&g_w[(4 * rg + i) * C + ci], accw[i][jx].x);
+        atomicAdd(&g_w[(4 * rg + i) * C + ci + 1], accw[i][jx].y);
       }
       if (cig == 0) atomicAdd(&g_b[4 * rg + i], accb[i]);
     }
