@@ -90,7 +90,10 @@ int kws_dct_lifter_matrix(int nfilt, int ncep, int ceplifter, double* out);
 int kws_features_configure(kws_handle_t h, const kws_feature_config* cfg);
 /* output columns = min(numcep, nfilt) */
 int kws_features_ncep(kws_handle_t h);
-/* pcm_dev: [B, N] float32 rows `pcm_stride` floats apart; out_dev: [B, nframes, ncep] float32 */
+/* pcm_dev: [B, N] float32 rows `pcm_stride` floats apart; out_dev: [B, nframes, ncep] float32.
+ * Rows may overlap (1 <= pcm_stride < N): B sliding windows of one long recording, hop = pcm_stride, are
+ * read in place -- the batch form of the reference's 1 s sliding-window inference concept
+ * (kws/inference/inference_local.py:114-188).  The same holds for kws_pcm_to_logits. */
 int kws_mfcc(kws_handle_t h, const float* pcm_dev, int64_t B, int64_t N, int64_t pcm_stride,
              float* out_dev, void* stream);
 /* psf logfbank ("log-mel"): out_dev [B, nframes, nfilt] */

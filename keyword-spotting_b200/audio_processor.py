@@ -136,6 +136,30 @@ class AudioProcessor:
             return out.cpu().numpy().astype(np.float64)
         return out
 
+    def sliding_features(self, recording: torch.Tensor, hop_samples: int, window_samples: Optional[int] = None,
+                         **kw) -> torch.Tensor:
+        """MFCCs of every ``window_samples`` window taken every ``hop_samples`` from a device-resident
+        recording ``[L]``: ``[nwin, nframes, numcep]``, row ``k`` = ``extract_features(recording[k*hop:...])``.
+        The windows are read in place as overlapping rows."""
+        lib = _native.lib()
+        plan = self._plan(kw.get("samplerate") or self.config.sample_rate,
+                          kw.get("numcep") or self.config.num_cepstral_coeffs,
+                          kw.get("winlen") or self.config.frame_length,
+                          kw.get("winstep") or self.config.frame_step,
+                          kw.get("nfilt") or self.config.num_mel_filters)
+        N, hop = int(window_samples or self.config.desired_samples), int(hop_samples)
+        x = recording.to(self.device, torch.float32).contiguous()
+        if x.dim() != 1 or x.shape[0] < N or hop < 1:
+            raise AudioProcessingError(f"expected a [L] recording with L >= {N} and hop >= 1")
+        nwin = (x.shape[0] - N) // hop + 1
+        nframes = int(lib.kws_num_frames(N, plan.frame_len, plan.frame_step))
+        out = torch.empty((nwin, nframes, plan.ncep), dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            _native.check(lib.kws_mfcc(plan.handle.ptr, C.c_void_p(x.data_ptr()), nwin, N, hop,
+                                       C.c_void_p(out.data_ptr()), _native.current_stream_ptr(self._dev_index())),
+                          AudioProcessingError)
+        return out
+
     # -- reference API --------------------------------------------------------------------
     def extract_features(self, signal, samplerate: int = None, numcep: int = None, nfft: int = None,
                          winlen: float = None, winstep: float = None, nfilt: int = None):

@@ -373,7 +373,8 @@ int launch_mfcc(kws_handle_t h, const void* pcm_dev, bool is_i16, int64_t B, int
   if (!h) return fail(KWS_ERR_INVALID, "null handle");
   const FeatureTables& t = h->feat;
   if (!t.ready) return fail(KWS_ERR_STATE, "features not configured: call kws_features_configure first");
-  if (B < 0 || N < 1 || pcm_stride < N) return fail(KWS_ERR_INVALID, "bad B/N/stride");
+  // rows may overlap (1 <= pcm_stride < N): the sliding windows of one long recording are read in place
+  if (B < 0 || N < 1 || pcm_stride < 1) return fail(KWS_ERR_INVALID, "bad B/N/stride");
   if (B == 0) return KWS_OK;
   if (!pcm_dev || !out_dev) return fail(KWS_ERR_INVALID, "null device pointer");
 

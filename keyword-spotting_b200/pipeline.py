@@ -55,6 +55,39 @@ class KeywordSpotter:
                     _native.current_stream_ptr(self._idx)), ModelError)
         return out
 
+    def sliding_logits(self, recording: torch.Tensor, hop_samples: int,
+                       window_samples: Optional[int] = None) -> torch.Tensor:
+        """Sliding-window inference over long recordings (the batch form of the reference's
+        1 s window concept, kws/inference/inference_local.py:114-188): every window of ``window_samples``
+        (default ``config.desired_samples``) starting at ``k * hop_samples`` is classified.
+
+        ``recording`` is ``[L]`` or ``[S, L]`` float32; returns ``[nwin, K]`` (``[S, nwin, K]``) with
+        ``nwin = (L - window) // hop + 1``.  The windows are never materialised: the kernels read them in
+        place as overlapping rows (row stride = hop), so HBM holds the recording once.  Row ``k`` equals
+        ``self(recording[k*hop : k*hop + window])`` (bit for bit when hop is a multiple of 4 samples, i.e.
+        when both run on the TMA-fed kernel)."""
+        lib = _native.lib()
+        self._h = self.model.native_handle(self.device)
+        N = int(window_samples or self.config.desired_samples)
+        hop = int(hop_samples)
+        if hop < 1:
+            raise AudioProcessingError("hop_samples must be >= 1")
+        x = recording.to(self.device, torch.float32).contiguous()
+        single = x.dim() == 1
+        if single:
+            x = x.unsqueeze(0)
+        if x.dim() != 2 or x.shape[1] < N:
+            raise AudioProcessingError(f"expected a [L] or [S, L] recording with L >= {N}, got {tuple(recording.shape)}")
+        S, L = x.shape
+        nwin = (L - N) // hop + 1
+        out = torch.empty((S, nwin, self.model.num_classes), dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            for s in range(S):
+                _native.check(lib.kws_pcm_to_logits(
+                    self._h.ptr, C.c_void_p(x[s].data_ptr()), nwin, N, hop, C.c_void_p(out[s].data_ptr()),
+                    _native.current_stream_ptr(self._idx)), ModelError)
+        return out[0] if single else out
+
     def infer_host(self, pcm: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         """HOST float32 ``[B, N]`` (ideally pinned) -> HOST logits; copies pipelined in the library."""
         lib = _native.lib()
