@@ -128,7 +128,9 @@ constexpr int kCWarps = 12;                       // compute warps: 3 column seg
 constexpr int kCThreads = kCWarps * 32;
 constexpr int kFThreads = (kCWarps + 2) * 32;     // + one MMA-issue warp per clip slot
 constexpr int kRingCols = 64;                     // per layer: 2 row slots x (8 margin + 24) columns
-constexpr int kAcc4Col = 4 * kRingCols;           // last pointwise layer's row (pooled at once), 32 columns
+// last pointwise layer's row (pooled at once): 8-column margin + 24, like a ring slot.  The margin is load-bearing:
+// the right halo of ring 3's second slot (layer column 24 of the widest layer) falls on it and must read zero.
+constexpr int kAcc4Col = 4 * kRingCols;
 constexpr int kConstCol = kAcc4Col + 32;          // constant border rows of the three padded layers, 32 columns each
 constexpr int kZeroCol = kConstCol + 3 * 32;      // the all-zero row that flushes a stencil
 
@@ -231,7 +233,7 @@ __device__ __forceinline__ void fused_mma_warp(unsigned char* smem, uint32_t tme
       r = stage_row(tl, n, my_pairs, per, 4, H0 + 2);
       if (r.on) issue_gemm<kKCp / 8>(d0 + 2 * kRingCols + (r.i & 1) * 32, ap[1], bp[1], kIdescF);
       r = stage_row(tl, n, my_pairs, per, 7, H0 + 6);
-      if (r.on) issue_gemm<kKCp / 8>(d0 - 8u + kAcc4Col, ap[3], bp[3], kIdescF);
+      if (r.on) issue_gemm<kKCp / 8>(d0 + kAcc4Col, ap[3], bp[3], kIdescF);
       tc_commit_elect(barE);
     }
     if (++tl == per) {
@@ -489,7 +491,7 @@ __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedPa
         if (r.on) {  // pooling of the last block's row (interior pixels; the border is added in pool_fc)
           if (seg_on) {
             float raw[8];
-            tc_ld8(my_tmem + (uint32_t)kAcc4Col + (uint32_t)(8 * j), raw);
+            tc_ld8(my_tmem + (uint32_t)kAcc4Col + 8u + (uint32_t)(8 * j), raw);
             tc_wait_ld();
 #pragma unroll
             for (int x = 0; x < 8; ++x) psum += fmaxf(raw[x], 0.f);  // columns past the layer are 0

@@ -67,6 +67,10 @@ def test_fused_equals_layered(T, F, B):
     want = dscnn_ref.forward({k: v.double() for k, v in sd.items()}, x.double()).numpy()
     np.testing.assert_allclose(layered, want, rtol=0, atol=2e-5)
     np.testing.assert_allclose(fused, want, rtol=1e-3, atol=1e-4)
+    # tf32 rounding errors are unbiased and average out over the pooled pixels: the fused logits sit within a
+    # few 1e-6 of the fp32 kernels.  A systematic error (a halo column reading a neighbouring TMEM region
+    # once cost 3e-5 here while staying inside the parity tolerance) shows up against this tighter bound.
+    np.testing.assert_allclose(fused, layered, rtol=0, atol=1e-5)
 
 
 @pytest.mark.parametrize("T,F,B", [(99, 40, 893), (31, 10, 1201), (7, 40, 601)])
