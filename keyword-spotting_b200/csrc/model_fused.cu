@@ -88,10 +88,18 @@ struct FusedParams {
 // W = width of the layer (= number of valid output pixels), SHIFT = pixel offset of the result in the
 // B tile (1 where the following pointwise output carries a border column).  `par` points at this
 // channel's [w0..w8] column.
-template <int W, int SHIFT>
+// Clips per slot: with PACK = 2 (narrow feature maps, F = 10) two clips sit side by side in one GEMM row, the
+// second at column kPackOff; the indicator scheme leaves the columns between them zero, which is each clip's
+// own zero padding, so the stencil needs no change -- only "which pixels are real" does.
+constexpr int kPackOff = 12;
+template <int W, int PACK>
+__host__ __device__ constexpr bool px_valid(int px) {
+  return PACK == 1 ? px < W : (px < W || (px >= kPackOff && px < kPackOff + W));
+}
+
+template <int W, int SHIFT, int PACK>
 __device__ __forceinline__ void dw_seg(uint32_t taddr, int j, bool st, const float4* par, unsigned char* dst,
                                        V (&P)[4], V (&R)[4]) {
-  constexpr int JL = (W - 1) / 8, KL = W - 8 * JL;  // last segment with valid pixels, and how many it has
   const float4 w0 = par[0], w1 = par[1];
   const float w8 = reinterpret_cast<const float*>(par)[8];
   // E pairs from a load at column 8j-1, O pairs from a second load one column to the right; the max is
@@ -109,18 +117,27 @@ __device__ __forceinline__ void dw_seg(uint32_t taddr, int j, bool st, const flo
   for (int pp = 0; pp < 5; ++pp) E[pp] = make_float2(ra[2 * pp], ra[2 * pp + 1]);
 #pragma unroll
   for (int pp = 0; pp < 4; ++pp) O[pp] = make_float2(rb[2 * pp], rb[2 * pp + 1]);
-  const bool st_lo = st && j <= JL, st_hi = st && j < JL;  // pixels x < KL / x >= KL of the segment
+  // warp-uniform store predicates.  PACK = 1: pixels x < KL of the last valid segment JL, all pixels of the
+  // segments before it; PACK = 2: per segment, from the compile-time validity of its eight columns
+  constexpr int JL = (W - 1) / 8, KL = W - 8 * JL;
+  const bool st_lo = st && j <= JL, st_hi = st && j < JL;
+  const bool s0 = st && j == 0, s1 = st && j == 1, s2 = st && j == 2;
 #pragma unroll
   for (int pp = 0; pp < 4; ++pp) {  // output pixels 2pp, 2pp+1 of the segment, packed f32x2
     const V o = ffma(fsplat(w8), E[pp + 1], ffma(fsplat(w1.w), O[pp], ffma(fsplat(w1.z), E[pp], P[pp])));
     P[pp] = ffma(fsplat(w1.y), E[pp + 1], ffma(fsplat(w1.x), O[pp], ffma(fsplat(w0.w), E[pp], R[pp])));
     R[pp] = ffma(fsplat(w0.z), E[pp + 1], ffma(fsplat(w0.y), O[pp], fmul(fsplat(w0.x), E[pp])));
     // tf32 round-to-nearest (ties away) = add half an ulp of the 10-bit mantissa; the MMA drops the low 13 bits
-    const int x0 = 2 * pp, x1 = 2 * pp + 1;
-    if (x0 < KL ? st_lo : st_hi)
-      *reinterpret_cast<uint32_t*>(dst + ((x0 + SHIFT) >> 3) * kSboBp + ((x0 + SHIFT) & 7) * 16) = __float_as_uint(o.x) + 0x1000u;
-    if (x1 < KL ? st_lo : st_hi)
-      *reinterpret_cast<uint32_t*>(dst + ((x1 + SHIFT) >> 3) * kSboBp + ((x1 + SHIFT) & 7) * 16) = __float_as_uint(o.y) + 0x1000u;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int x = 2 * pp + h;
+      // pixels past the layer are never stored: their B-tile rows stay zero (or hold the border indicator)
+      const bool on = PACK == 1 ? (x < KL ? st_lo : st_hi)
+                                : ((px_valid<W, PACK>(x) && s0) || (px_valid<W, PACK>(8 + x) && s1) || (px_valid<W, PACK>(16 + x) && s2));
+      if (on)
+        *reinterpret_cast<uint32_t*>(dst + ((x + SHIFT) >> 3) * kSboBp + ((x + SHIFT) & 7) * 16) =
+            __float_as_uint(h ? o.y : o.x) + 0x1000u;
+    }
   }
 }
 
@@ -134,18 +151,19 @@ constexpr int kAcc4Col = 4 * kRingCols;
 constexpr int kConstCol = kAcc4Col + 32;          // constant border rows of the three padded layers, 32 columns each
 constexpr int kZeroCol = kConstCol + 3 * 32;      // the all-zero row that flushes a stencil
 
-template <int F, int NPIX>
+template <int F, int NPIX, int PACK>
 struct FusedLayout {
   static constexpr int FP = F + 4;  // feature row pitch: 2 zero columns left, >= 2 right (conv1 padding 2)
+  static constexpr int CL = 2 * PACK;  // clips per CTA step: 2 slots x PACK side by side
   static constexpr int b1_tile = (NPIX / 8) * kSboB1, b1_stride = b1_tile + 64;
   static constexpr int bp_tile = (NPIX / 8) * kSboBp, bp_stride = bp_tile + 64;
   static constexpr int off_a1 = 0;
   static constexpr int off_ap = 8 * kSboA1;
   static constexpr int off_b1 = kAImgBytes;
   static constexpr int off_bp = off_b1 + 2 * b1_stride;
-  static constexpr int off_par = off_bp + 8 * bp_stride;          // [4][64][12] depthwise taps, input bias, border, pad
-  static constexpr int off_pool = off_par + 4 * kFC * 12 * 4;     // [3][2][64] pooling partials
-  static constexpr int off_feat = off_pool + 3 * 2 * kFC * 4;
+  static constexpr int off_par = off_bp + 8 * bp_stride;          // [4][64][12] depthwise taps (9 used)
+  static constexpr int off_pool = off_par + 4 * kFC * 12 * 4;     // [3][2][PACK][64] pooling partials
+  static constexpr int off_feat = off_pool + 3 * CL * kFC * 4;
   // zero-padded feature map of one clip: rows -2 .. T+1
   static constexpr size_t feat_floats(int T) { return (size_t)(T + 4) * FP; }
 };
@@ -197,10 +215,10 @@ __device__ __forceinline__ StageRow stage_row(int tl, int n, int npair, int per,
   return StageRow{i, cn >= 0 && cn < npair && i < len};
 }
 
-template <int F, int NPIX, int SLOT>
+template <int F, int NPIX, int PACK, int SLOT>
 __device__ __forceinline__ void fused_mma_warp(unsigned char* smem, uint32_t tmem, uint32_t barO, uint32_t barE, int H0,
                                                int my_pairs) {
-  using L = FusedLayout<F, NPIX>;
+  using L = FusedLayout<F, NPIX, PACK>;
   constexpr uint32_t kIdescF = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(NPIX >> 3) << 17) | ((64u >> 4) << 24);
   const uint32_t sbase = smem_u32(smem);
   const uint64_t a1 = umma_desc(sbase + L::off_a1, 128u, kSboA1);
@@ -257,24 +275,25 @@ __device__ __forceinline__ uint32_t dw_row_col(int i, int HIN, uint32_t ring, ui
   return ring + (uint32_t)((i & 1) * 32);
 }
 
-template <int F, int NPIX>
+template <int F, int NPIX, int PACK>
 __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedParams p) {
   constexpr int W0 = (F - 6) / 2 + 1, W3 = W0 + 6, NSEG = NPIX / 8;
   static_assert(W3 <= NPIX && NPIX % 8 == 0 && NSEG <= 3, "row of the widest layer must fit the MMA N");
-  using L = FusedLayout<F, NPIX>;
-  constexpr int FP = L::FP;
+  static_assert(PACK == 1 || (PACK == 2 && W3 + 2 < kPackOff && kPackOff + W3 <= NPIX), "two clips per slot need a zero gap");
+  using L = FusedLayout<F, NPIX, PACK>;
+  constexpr int FP = L::FP, CL = L::CL;
   extern __shared__ __align__(128) unsigned char smem[];
   __shared__ __align__(8) unsigned long long s_bar[2];
   __shared__ uint32_t s_tmem;
-  float* s_feat = reinterpret_cast<float*>(smem + L::off_feat);  // [2][(T + 4) * FP], zero padded, tf32-rounded
-  float* s_pool = reinterpret_cast<float*>(smem + L::off_pool);  // [3][2][64]
+  float* s_feat = reinterpret_cast<float*>(smem + L::off_feat);  // [CL][(T + 4) * FP], zero padded, tf32-rounded
+  float* s_pool = reinterpret_cast<float*>(smem + L::off_pool);  // [3][2][PACK][64]
   float* s_par = reinterpret_cast<float*>(smem + L::off_par);    // [4][64][12]
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t barO = smem_u32(&s_bar[0]), barE = smem_u32(&s_bar[1]);
   const int T = p.T, H0 = p.H0, TF = T * F;
   const int feat_stride = (int)L::feat_floats(T);
-  const long long npairs = (p.B + 1) / 2;
+  const long long npairs = (p.B + CL - 1) / CL;  // groups of CL clips ("pairs" when PACK = 1)
 
   if (tid == 0) {
     mbar_init(barO, 2);
@@ -290,7 +309,7 @@ __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedPa
     uint4* dst = reinterpret_cast<uint4*>(smem);
     for (int i = tid; i < kAImgBytes / 16; i += kFThreads) dst[i] = src[i];
     uint4* z = reinterpret_cast<uint4*>(smem + L::off_b1);
-    const int nz = (L::off_feat - L::off_b1) / 16 + (2 * feat_stride * 4 + 15) / 16;  // B tiles, pool, feature pads
+    const int nz = (L::off_feat - L::off_b1) / 16 + (CL * feat_stride * 4 + 15) / 16;  // B tiles, pool, feature pads
     for (int i = tid; i < nz; i += kFThreads) z[i] = make_uint4(0, 0, 0, 0);
   }
   __syncthreads();
@@ -301,20 +320,21 @@ __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedPa
   // constant K tail of the B tiles: (interior, border, interior, border) indicators of every pixel row
   for (int i = tid; i < 2 * 5 * NPIX; i += kFThreads) {
     const int s = i / (5 * NPIX), l = (i / NPIX) % 5, px = i % NPIX;  // l = 0: conv1 tile, 1..4: tile of pointwise l
+    const int pl = (PACK == 2 && px >= kPackOff) ? px - kPackOff : px;  // column inside its clip
     float in = 0.f, bo = 0.f;
     unsigned char* tile;
     int chunk, sbo;
     if (l == 0) {
       tile = smem + L::off_b1 + s * L::b1_stride, chunk = 25, sbo = kSboB1;
-      in = px < W0 ? 1.f : 0.f;
+      in = pl < W0 ? 1.f : 0.f;
     } else {
       tile = smem + L::off_bp + ((l - 1) * 2 + s) * L::bp_stride, chunk = 16, sbo = kSboBp;
       const int Wl = W0 + 2 * (l - 1);  // width of the depthwise output feeding pointwise l
       if (l < 4) {
-        in = (px >= 1 && px <= Wl) ? 1.f : 0.f;
-        bo = (px == 0 || px == Wl + 1) ? 1.f : 0.f;
+        in = (pl >= 1 && pl <= Wl) ? 1.f : 0.f;
+        bo = (pl == 0 || pl == Wl + 1) ? 1.f : 0.f;
       } else {
-        in = px < Wl ? 1.f : 0.f;
+        in = pl < Wl ? 1.f : 0.f;
       }
     }
     *reinterpret_cast<float4*>(tile + (px >> 3) * sbo + chunk * kLboB + (px & 7) * 16) = make_float4(in, bo, in, bo);
@@ -340,7 +360,7 @@ __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedPa
       for (int x0 = 0; x0 < NPIX; x0 += 8) {
         uint32_t v[8];
 #pragma unroll
-        for (int x = 0; x < 8; ++x) v[x] = (x0 + x < WL) ? bv : 0u;
+        for (int x = 0; x < 8; ++x) v[x] = (x0 + x < WL || (PACK == 2 && x0 + x >= kPackOff && x0 + x < kPackOff + WL)) ? bv : 0u;
         asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"r"(
                          tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)(kConstCol + (l - 1) * 32 + 8 + x0)),
                      "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
@@ -356,9 +376,9 @@ __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedPa
   // pairs of this CTA: blockIdx.x, + gridDim.x, ... (the launcher keeps gridDim.x <= npairs)
   const int my_pairs = (int)((npairs - blockIdx.x + gridDim.x - 1) / gridDim.x);
   if (warp == kCWarps) {
-    fused_mma_warp<F, NPIX, 0>(smem, tmem, barO, barE, H0, my_pairs);
+    fused_mma_warp<F, NPIX, PACK, 0>(smem, tmem, barO, barE, H0, my_pairs);
   } else if (warp == kCWarps + 1) {
-    fused_mma_warp<F, NPIX, 1>(smem, tmem, barO, barE, H0, my_pairs);
+    fused_mma_warp<F, NPIX, PACK, 1>(smem, tmem, barO, barE, H0, my_pairs);
   } else {
     // =========================== compute warps ===========================
     const int j = warp >> 2, q = warp & 3, sl = lane >> 4, c = q * 16 + (lane & 15);
@@ -369,9 +389,17 @@ __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedPa
     const uint32_t my_ld = my_tmem + 7u + (uint32_t)(8 * j);
     unsigned char* my_dst = smem + L::off_bp + sl * L::bp_stride + j * kSboBp + (c >> 2) * kLboB + (c & 3) * 4;
     const float4* my_par = reinterpret_cast<const float4*>(s_par) + c * 3;
-    // conv1 im2col item of this thread: slot, 16-byte K-chunk (4 taps), pixel columns xg, xg+7, xg+14
-    const bool im_on = tid < 350;
-    const int im_s = tid / 175, im_kc = (tid % 175) % 25, im_xg = (tid % 175) / 25;
+    // conv1 im2col item of this thread: clip, 16-byte K-chunk (4 taps), pixel column(s).
+    //   PACK = 1: 2 clips x 25 chunks x 7 column groups (columns xg, xg+7, xg+14)
+    //   PACK = 2: 4 clips x 25 chunks x W0 columns, one item per thread; clip u of a slot sits at row u * kPackOff
+    constexpr int kImItems = PACK == 1 ? 350 : CL * 25 * W0;
+    static_assert(kImItems <= kCThreads, "im2col items must fit the compute threads");
+    const bool im_on = tid < kImItems;
+    const int im_kc = tid % 25;
+    const int im_r = tid / 25;                                   // PACK 1: slot * 7 + xg;  PACK 2: clip * W0 + x
+    const int im_sc = PACK == 1 ? im_r / 7 : im_r / W0;          // clip of the CTA step (slot * PACK + u)
+    const int im_x0 = PACK == 1 ? im_r % 7 : im_r % W0;
+    const int im_row0 = PACK == 1 ? 0 : (im_sc % PACK) * kPackOff;
     // taps 4kc .. 4kc+3 are two pairs of horizontally adjacent taps (a window row has 10 taps and 4kc is even),
     // each pair one aligned 8-byte read of the padded feature row
     int im_off[2];
@@ -380,11 +408,11 @@ __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedPa
       const int k = 4 * im_kc + 2 * e, ki = k / 10, kj = k - 10 * ki;
       im_off[e] = ki * FP + kj;
     }
-    const float* im_src = s_feat + im_s * feat_stride;
-    unsigned char* im_dst = smem + L::off_b1 + im_s * L::b1_stride + im_kc * kLboB;
+    const float* im_src = s_feat + im_sc * feat_stride;
+    unsigned char* im_dst = smem + L::off_b1 + (im_sc / PACK) * L::b1_stride + im_kc * kLboB;
     // rolling feature load: while pair n runs, the two feature-map rows conv1 has just left behind are
-    // refilled with rows 2tl-4, 2tl-3 of pair n+1 (thread = slot, row parity, column)
-    const bool fl_on = tid < 4 * F;
+    // refilled with rows 2tl-4, 2tl-3 of pair n+1 (thread = clip, row parity, column)
+    const bool fl_on = tid < CL * 2 * F;
     const int fl_s = tid / (2 * F), fl_r = (tid / F) & 1, fl_c = tid % F;
 
     const int per = H0 + 7, total = my_pairs * per + 7;
@@ -393,36 +421,37 @@ __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedPa
     const float inv_area = 1.0f / (float)((H3 + 2) * (W3 + 2));
     uint32_t nO = 0, nE = 0;  // completed waits on the two MMA-group barriers
 
-    // global average pool (interior sum + border constant) and fc of the pair whose pooling has finished:
+    // global average pool (interior sum + border constant) and fc of the group whose pooling has finished:
     // warp w takes outputs w, w + 12, ...; a lane sums two channels, the warp reduces
     auto pool_fc = [&](long long pair) {
-      for (int o = warp; o < 2 * p.ncls; o += kCWarps) {
-        const int s = o / p.ncls, k = o - s * p.ncls;
+      for (int o = warp; o < CL * p.ncls; o += kCWarps) {
+        const int sc = o / p.ncls, k = o - sc * p.ncls;   // sc = slot * PACK + u
         float acc = 0.f;
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
           const int ch = lane + 32 * h;
-          const float pooled = (s_pool[s * kFC + ch] + s_pool[(2 + s) * kFC + ch] + s_pool[(4 + s) * kFC + ch] +
+          const float pooled = (s_pool[sc * kFC + ch] + s_pool[(CL + sc) * kFC + ch] + s_pool[(2 * CL + sc) * kFC + ch] +
                                 nborder * p.border[4 * kFC + ch]) * inv_area;
           acc = fmaf(pooled, p.fc_w[ch * p.ncls + k], acc);
         }
 #pragma unroll
         for (int d = 16; d >= 1; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
-        const long long b = 2 * pair + s;
+        const long long b = CL * pair + sc;
         if (lane == 0 && b < p.B) p.logits[b * p.ncls + k] = acc + p.fc_b[k];
       }
     };
 
-    {  // features of the first pair -> zero-padded, tf32-rounded map in shared memory
-      const long long pair = blockIdx.x;
-      const int nvalid = (2 * pair + 1 < p.B) ? 2 * TF : TF;
-      const float* src = p.feats + 2 * pair * TF;
-      for (int i = tid; i < 2 * TF; i += kCThreads) {
-        const int s = i >= TF, rem = i - s * TF, fr = rem / F, fc = rem - fr * F;
-        s_feat[s * feat_stride + (fr + 2) * FP + fc + 2] = (i < nvalid) ? to_tf32(__ldg(src + i)) : 0.f;
+    {  // features of the first group -> zero-padded, tf32-rounded maps in shared memory
+      const long long first = (long long)CL * blockIdx.x;
+      const float* src = p.feats + first * TF;
+      for (int i = tid; i < CL * TF; i += kCThreads) {
+        const int sc = i / TF, rem = i - sc * TF, fr = rem / F, fc = rem - fr * F;
+        s_feat[sc * feat_stride + (fr + 2) * FP + fc + 2] = (first + sc < p.B) ? to_tf32(__ldg(src + i)) : 0.f;
       }
     }
-    float psum = 0.f;
+    float psum[PACK];
+#pragma unroll
+    for (int u = 0; u < PACK; ++u) psum[u] = 0.f;
     V P[4][4], R[4][4];
 #pragma unroll
     for (int l = 0; l < 4; ++l)
@@ -430,14 +459,14 @@ __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedPa
       for (int x = 0; x < 4; ++x) P[l][x] = R[l][x] = fsplat(0.f);
     __syncthreads();
 
-    int tl = 0, n = 0, fc_n = -1;  // fc_n: pair (CTA-local index) whose pooled sums wait in s_pool
+    int tl = 0, n = 0, fc_n = -1;  // fc_n: group (CTA-local index) whose pooled sums wait in s_pool
     for (int tg = 0; tg < total; ++tg) {
       // ================= phase A: depthwise of blocks 1 and 3 =================
       float fl_v = 0.f;
       const int fl_fr = 2 * tl - 4 + fl_r;
       const bool fl_do = fl_on && n + 1 < my_pairs && fl_fr >= 0 && fl_fr < T;
       if (fl_do) {
-        const long long clip = 2 * ((long long)blockIdx.x + (long long)(n + 1) * gridDim.x) + fl_s;
+        const long long clip = CL * ((long long)blockIdx.x + (long long)(n + 1) * gridDim.x) + fl_s;
         if (clip < p.B) fl_v = __ldg(p.feats + clip * TF + fl_fr * F + fl_c);
       }
       if (tg > 0) {  // the GEMMs issued after the previous phase A (pw1, pw3) have retired
@@ -448,12 +477,12 @@ __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedPa
       if (seg_on) {
         StageRow r = stage_row(tl, n, my_pairs, per, 2, H0 + 1);
         if (r.on)
-          dw_seg<W0, 1>(my_ld + dw_row_col<false>(r.i, H0, 0 * kRingCols, 0), j, r.i >= 1, my_par + 0 * 3 * kFC,
-                        my_dst + 0 * 2 * L::bp_stride, P[0], R[0]);
+          dw_seg<W0, 1, PACK>(my_ld + dw_row_col<false>(r.i, H0, 0 * kRingCols, 0), j, r.i >= 1, my_par + 0 * 3 * kFC,
+                              my_dst + 0 * 2 * L::bp_stride, P[0], R[0]);
         r = stage_row(tl, n, my_pairs, per, 5, H0 + 5);
         if (r.on)
-          dw_seg<W0 + 4, 1>(my_ld + dw_row_col<true>(r.i, H0 + 2, 2 * kRingCols, kConstCol + 32), j, r.i >= 1,
-                            my_par + 2 * 3 * kFC, my_dst + 2 * 2 * L::bp_stride, P[2], R[2]);
+          dw_seg<W0 + 4, 1, PACK>(my_ld + dw_row_col<true>(r.i, H0 + 2, 2 * kRingCols, kConstCol + 32), j, r.i >= 1,
+                                  my_par + 2 * 3 * kFC, my_dst + 2 * 2 * L::bp_stride, P[2], R[2]);
       }
       if (fc_n >= 0) {
         pool_fc((long long)blockIdx.x + (long long)fc_n * gridDim.x);
@@ -471,34 +500,56 @@ __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedPa
       }
       if (tl < H0 && n < my_pairs && im_on) {
         const float* rowp = im_src + 2 * tl * FP;
-        for (int x = im_xg; x < W0; x += 7) {
-          const float* q4 = rowp + 2 * x;
+        if (PACK == 1) {
+          for (int x = im_x0; x < W0; x += 7) {
+            const float* q4 = rowp + 2 * x;
+            const float2 lo = *reinterpret_cast<const float2*>(q4 + im_off[0]);
+            const float2 hi = *reinterpret_cast<const float2*>(q4 + im_off[1]);
+            *reinterpret_cast<float4*>(im_dst + (x >> 3) * kSboB1 + (x & 7) * 16) = make_float4(lo.x, lo.y, hi.x, hi.y);
+          }
+        } else {
+          const float* q4 = rowp + 2 * im_x0;
           const float2 lo = *reinterpret_cast<const float2*>(q4 + im_off[0]);
           const float2 hi = *reinterpret_cast<const float2*>(q4 + im_off[1]);
-          *reinterpret_cast<float4*>(im_dst + (x >> 3) * kSboB1 + (x & 7) * 16) = make_float4(lo.x, lo.y, hi.x, hi.y);
+          const int row = im_row0 + im_x0;
+          *reinterpret_cast<float4*>(im_dst + (row >> 3) * kSboB1 + (row & 7) * 16) = make_float4(lo.x, lo.y, hi.x, hi.y);
         }
       }
       {
         StageRow r = stage_row(tl, n, my_pairs, per, 3, H0 + 3);
         if (seg_on && r.on)
-          dw_seg<W0 + 2, 1>(my_ld + dw_row_col<true>(r.i, H0, 1 * kRingCols, kConstCol), j, r.i >= 1, my_par + 1 * 3 * kFC,
-                            my_dst + 1 * 2 * L::bp_stride, P[1], R[1]);
+          dw_seg<W0 + 2, 1, PACK>(my_ld + dw_row_col<true>(r.i, H0, 1 * kRingCols, kConstCol), j, r.i >= 1,
+                                  my_par + 1 * 3 * kFC, my_dst + 1 * 2 * L::bp_stride, P[1], R[1]);
         r = stage_row(tl, n, my_pairs, per, 6, H0 + 7);
         if (seg_on && r.on)
-          dw_seg<W0 + 6, 0>(my_ld + dw_row_col<true>(r.i, H0 + 4, 3 * kRingCols, kConstCol + 64), j, r.i >= 1,
-                            my_par + 3 * 3 * kFC, my_dst + 3 * 2 * L::bp_stride, P[3], R[3]);
+          dw_seg<W0 + 6, 0, PACK>(my_ld + dw_row_col<true>(r.i, H0 + 4, 3 * kRingCols, kConstCol + 64), j, r.i >= 1,
+                                  my_par + 3 * 3 * kFC, my_dst + 3 * 2 * L::bp_stride, P[3], R[3]);
         r = stage_row(tl, n, my_pairs, per, 8, H3);
         if (r.on) {  // pooling of the last block's row (interior pixels; the border is added in pool_fc)
           if (seg_on) {
             float raw[8];
             tc_ld8(my_tmem + (uint32_t)kAcc4Col + 8u + (uint32_t)(8 * j), raw);
             tc_wait_ld();
+            // columns past a clip's layer are 0; with two clips per slot columns < kPackOff belong to the first
+            float lo4 = 0.f, hi4 = 0.f;
 #pragma unroll
-            for (int x = 0; x < 8; ++x) psum += fmaxf(raw[x], 0.f);  // columns past the layer are 0
+            for (int x = 0; x < 4; ++x) {
+              lo4 += fmaxf(raw[x], 0.f);
+              hi4 += fmaxf(raw[4 + x], 0.f);
+            }
+            if (PACK == 1) {
+              psum[0] += lo4 + hi4;
+            } else {
+              psum[0] += (j < 2 ? lo4 : 0.f) + (j < 1 ? hi4 : 0.f);
+              psum[PACK - 1] += (j >= 2 ? lo4 : 0.f) + (j >= 1 ? hi4 : 0.f);
+            }
           }
-          if (r.i == H3 - 1) {  // last row of the pair: hand the sums to pool_fc (next phase A)
-            s_pool[(j * 2 + sl) * kFC + c] = psum;
-            psum = 0.f;
+          if (r.i == H3 - 1) {  // last row of the group: hand the sums to pool_fc (next phase A)
+#pragma unroll
+            for (int u = 0; u < PACK; ++u) {
+              s_pool[((j * 2 + sl) * PACK + u) * kFC + c] = psum[u];
+              psum[u] = 0.f;
+            }
             fc_n = tl >= 8 ? n : n - 1;
           }
         }
@@ -581,16 +632,17 @@ int build_fused_model(ModelWeights& m, const std::vector<float>& conv1_w, const 
   return KWS_OK;
 }
 
-template <int F, int NPIX>
+template <int F, int NPIX, int PACK>
 static int launch_fused_t(kws_handle_t h, const FusedParams& p, cudaStream_t stream) {
-  using L = FusedLayout<F, NPIX>;
-  const size_t smem_bytes = (size_t)L::off_feat + 2 * L::feat_floats(p.T) * 4;
+  using L = FusedLayout<F, NPIX, PACK>;
+  const size_t smem_bytes = (size_t)L::off_feat + L::CL * L::feat_floats(p.T) * 4;
   if (smem_bytes > 227 * 1024) return 0;
-  auto kern = dscnn_fused_kernel<F, NPIX>;
+  auto kern = dscnn_fused_kernel<F, NPIX, PACK>;
   KWS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
-  const long long npairs = (p.B + 1) / 2;
+  const long long ngroups = (p.B + L::CL - 1) / L::CL;
+  if (ngroups > 0x7fffffffLL / 64) return 0;
   long long grid = h->sm_count;
-  if (grid > npairs) grid = npairs;
+  if (grid > ngroups) grid = ngroups;
   kern<<<(unsigned)grid, kFThreads, smem_bytes, stream>>>(p);
   KWS_CHECK_LAUNCH(h);
   return 1;
@@ -614,8 +666,10 @@ int launch_dscnn_fused(kws_handle_t h, const float* feats_dev, int64_t B, int64_
   p.border = m.d_fused_border;
   p.fc_w = m.d_fc_w;
   p.fc_b = m.d_fc_b;
-  if (F == 40) return launch_fused_t<40, 24>(h, p, stream);
-  return launch_fused_t<10, 16>(h, p, stream);
+  if (F == 40) return launch_fused_t<40, 24, 1>(h, p, stream);
+  // 99x10 features (the reference's default): the widest layer is 9 columns, two clips share a slot's 24-column row
+  const int rc = launch_fused_t<10, 24, 2>(h, p, stream);
+  return rc != 0 ? rc : launch_fused_t<10, 16, 1>(h, p, stream);
 }
 
 }  // namespace kws
