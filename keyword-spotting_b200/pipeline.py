@@ -37,12 +37,22 @@ class KeywordSpotter:
         cfg.nfft = max(self.config.fft_size, int(self.config.frame_length * sr))
         cfg.nfilt = int(nfilt or self.config.num_mel_filters)
         cfg.numcep = int(numcep or self.config.num_cepstral_coeffs)
-        _native.check(lib.kws_features_configure(self._h.ptr, C.byref(cfg)), AudioProcessingError)
+        self._cfg = cfg
+        self._bind()
+
+    def _bind(self) -> None:
+        """The feature plan lives on the model's native handle: (re)install this spotter's configuration when
+        another spotter of the same model, or a re-pack of the weights, was there last."""
+        self._h = self.model.native_handle(self.device)     # re-pack if the weights changed
+        if getattr(self.model, "_feature_cfg_owner", None) is not self or getattr(self, "_bound_h", None) is not self._h:
+            _native.check(_native.lib().kws_features_configure(self._h.ptr, C.byref(self._cfg)), AudioProcessingError)
+            self.model._feature_cfg_owner = self
+            self._bound_h = self._h
 
     def __call__(self, pcm: torch.Tensor) -> torch.Tensor:
         """``pcm[B, N]`` float32 on the device -> logits ``[B, num_classes]``."""
         lib = _native.lib()
-        self._h = self.model.native_handle(self.device)     # re-pack if the weights changed
+        self._bind()
         x = pcm.to(self.device, torch.float32).contiguous()
         if x.dim() == 1:
             x = x.unsqueeze(0)
@@ -67,7 +77,7 @@ class KeywordSpotter:
         ``self(recording[k*hop : k*hop + window])`` (bit for bit when hop is a multiple of 4 samples, i.e.
         when both run on the TMA-fed kernel)."""
         lib = _native.lib()
-        self._h = self.model.native_handle(self.device)
+        self._bind()
         N = int(window_samples or self.config.desired_samples)
         hop = int(hop_samples)
         if hop < 1:
@@ -91,7 +101,7 @@ class KeywordSpotter:
     def infer_host(self, pcm: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         """HOST float32 ``[B, N]`` (ideally pinned) -> HOST logits; copies pipelined in the library."""
         lib = _native.lib()
-        self._h = self.model.native_handle(self.device)
+        self._bind()
         pcm = pcm.contiguous()
         B, N = pcm.shape
         if out is None:

@@ -184,3 +184,22 @@ def test_pcm_to_logits(numcep, nfilt):
     np.testing.assert_allclose(got, two_step.cpu().numpy(), rtol=0, atol=1e-5)
     host = ks.infer_host(pcm.pin_memory())
     np.testing.assert_allclose(host.numpy(), got, rtol=0, atol=1e-6)
+
+
+def test_two_spotters_share_one_model():
+    """Two KeywordSpotters with different feature configurations on the same model (and therefore the same
+    native handle) must not see each other's feature plan."""
+    sd = dscnn_ref.init_state_dict(seed=5)
+    m = DepthwiseSeparableConv()
+    m.load_state_dict(sd)
+    m = m.cuda()
+    pcm = synth.parity_pcm(16).cuda()
+    ks40 = KeywordSpotter(m, AudioConfig(), numcep=40, nfilt=40, device="cuda:0")
+    a40 = ks40(pcm)
+    ks10 = KeywordSpotter(m, AudioConfig(), numcep=10, nfilt=26, device="cuda:0")
+    a10 = ks10(pcm)
+    assert torch.equal(ks40(pcm), a40) and torch.equal(ks10(pcm), a10)
+    proc = AudioProcessor(None, AudioConfig(), device="cuda:0")
+    two_step = m(proc.extract_features(pcm, numcep=10, nfilt=26).unsqueeze(1))
+    np.testing.assert_allclose(a10.cpu().numpy(), two_step.cpu().numpy(), rtol=0, atol=1e-5)
+    assert (a10 - a40).abs().max() > 1e-4
