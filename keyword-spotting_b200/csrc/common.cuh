@@ -10,6 +10,25 @@
 
 namespace kws {
 
+// (clip, row, column) of a linear NHWC pixel index.  32-bit unsigned division when the index fits (it does for
+// every realistic batch: 64-bit integer division costs ~100 instructions and used to dominate the per-tile
+// staging of the training kernels), 64-bit otherwise.
+__host__ __device__ __forceinline__ void split_pixel(long long gp, int Wd, int Hd, long long* b, int* row, int* col) {
+  if (gp < 0x7fffffffLL) {
+    const unsigned g = (unsigned)gp, r = g / (unsigned)Wd;
+    *col = (int)(g - r * (unsigned)Wd);
+    const unsigned bb = r / (unsigned)Hd;
+    *row = (int)(r - bb * (unsigned)Hd);
+    *b = (long long)bb;
+  } else {
+    const long long r = gp / Wd;
+    *col = (int)(gp - r * Wd);
+    *b = r / Hd;
+    *row = (int)(r - *b * Hd);
+  }
+}
+
+
 void set_error(const char* fmt, ...);
 int fail(int code, const char* fmt, ...);
 

@@ -76,8 +76,9 @@ __global__ void dsblock_kernel(const float* __restrict__ in, float* __restrict__
       const long long pix = grp * kBlkPix + pl;
       float4 d = make_float4(0.f, 0.f, 0.f, 0.f);
       if (pix < npix) {
-        const int wo = (int)(pix % Wo), ho = (int)((pix / Wo) % Ho);
-        const long long b = pix / ((long long)Wo * Ho);
+        int wo, ho;
+        long long b;
+        split_pixel(pix, Wo, Ho, &b, &ho, &wo);
         if (ho >= 1 && ho <= H && wo >= 1 && wo <= W) {
           const int h = ho - 1, wc = wo - 1;
           d = __ldg(reinterpret_cast<const float4*>(dw_b) + q);
@@ -106,7 +107,9 @@ __global__ void dsblock_kernel(const float* __restrict__ in, float* __restrict__
       const int pl = t / cq, q = t - pl * cq;
       const long long pix = grp * kBlkPix + pl;
       if (pix >= npix) continue;
-      const int wo = (int)(pix % Wo), ho = (int)((pix / Wo) % Ho);
+      int wo, ho;
+      long long b_unused;
+      split_pixel(pix, Wo, Ho, &b_unused, &ho, &wo);
       float4 acc = __ldg(reinterpret_cast<const float4*>(pw_b) + q);
       if (ho >= 1 && ho <= H && wo >= 1 && wo <= W) {
         const float* d = s_d + pl * C;
@@ -173,7 +176,7 @@ static size_t pool_smem(int C) { return (size_t)((C <= kPoolThreads ? kPoolThrea
 // output for the backward pass.
 constexpr int kB64Pix = 128;
 constexpr size_t kB64Smem = (size_t)(64 * 64 + 64 * kB64Pix) * 4;
-__global__ void __launch_bounds__(256) dsblock64_kernel(const float* __restrict__ in, float* __restrict__ out,
+__global__ void __launch_bounds__(256, 3) dsblock64_kernel(const float* __restrict__ in, float* __restrict__ out,
                                                         const float* __restrict__ dw_w /*[9][64]*/,
                                                         const float* __restrict__ dw_b,
                                                         const float* __restrict__ pw_w /*[ci][co]*/,
@@ -202,8 +205,9 @@ __global__ void __launch_bounds__(256) dsblock64_kernel(const float* __restrict_
       const long long pix = tile * TP + pl;
       float4 d = make_float4(0.f, 0.f, 0.f, 0.f);
       if (pix < npix) {
-        const int wo = (int)(pix % Wo), ho = (int)((pix / Wo) % Ho);
-        const long long b = pix / ((long long)Wo * Ho);
+        int wo, ho;
+        long long b;
+        split_pixel(pix, Wo, Ho, &b, &ho, &wo);
         if (ho >= 1 && ho <= H && wo >= 1 && wo <= W) {
           const int h = ho - 1, wc = wo - 1;
           d = kb;

@@ -131,7 +131,7 @@ constexpr int kPwTP = 64;                      // pixels per tile
 constexpr int kPwLd = kPwTP;                   // row pitch of the transposed dY tile (px index XOR-swizzled per channel quad)
 constexpr size_t kPwSmem = (size_t)(kTC * kTC + 2 * kPwTP * kTC + kTC * kPwLd) * 4;
 
-__global__ void __launch_bounds__(256) pw_bwd_kernel(const float* __restrict__ out, const float* __restrict__ dout,
+__global__ void __launch_bounds__(256, 3) pw_bwd_kernel(const float* __restrict__ out, const float* __restrict__ dout,
                                                      const float* __restrict__ dpooled, float inv_area,
                                                      float* __restrict__ d_io, const float* __restrict__ w_flat /*[co][ci]*/,
                                                      float* __restrict__ g_w, float* __restrict__ g_b, long long B, int H,
@@ -163,8 +163,9 @@ __global__ void __launch_bounds__(256) pw_bwd_kernel(const float* __restrict__ o
       const long long gp = tile * TP + px;
       float4 dy = make_float4(0.f, 0.f, 0.f, 0.f), dv = dy;
       if (gp < npix) {
-        const int wo = (int)(gp % Wo), ho = (int)((gp / Wo) % Ho);
-        const long long b = gp / ((long long)Wo * Ho);
+        int wo, ho;
+        long long b;
+        split_pixel(gp, Wo, Ho, &b, &ho, &wo);
         const float4 o = reinterpret_cast<const float4*>(out + gp * C)[q];
         float4 g;
         if (dpooled) {
@@ -208,8 +209,9 @@ __global__ void __launch_bounds__(256) pw_bwd_kernel(const float* __restrict__ o
       for (int i = 0; i < 4; ++i) {  // interior pixels only: the border's input is the zero padding
         const long long gp = tile * TP + 4 * rg + i;
         if (gp < npix) {
-          const int wo = (int)(gp % Wo), ho = (int)((gp / Wo) % Ho);
-          const long long b = gp / ((long long)Wo * Ho);
+          int wo, ho;
+          long long b;
+          split_pixel(gp, Wo, Ho, &b, &ho, &wo);
           if (ho >= 1 && ho <= H && wo >= 1 && wo <= W) {
             float* dst = d_io + ((b * H + ho - 1) * W + wo - 1) * C + cig;
             *reinterpret_cast<float4*>(dst) = make_float4(acc[i][0].x, acc[i][0].y, acc[i][1].x, acc[i][1].y);
@@ -265,8 +267,9 @@ __global__ void __launch_bounds__(256) dw_bwd_kernel(const float* __restrict__ x
   for (int t = 0; t < 9; ++t) wacc[t] = make_float4(0.f, 0.f, 0.f, 0.f);
   const long long npix = B * H * (long long)W;
   for (long long gp = blockIdx.x * 16LL + ps; gp < npix; gp += gridDim.x * 16LL) {
-    const int xx = (int)(gp % W), yy = (int)((gp / W) % H);
-    const long long b = gp / ((long long)W * H);
+    int xx, yy;
+    long long b;
+    split_pixel(gp, W, H, &b, &yy, &xx);
     const float4 xv = reinterpret_cast<const float4*>(x + gp * C)[q];
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
