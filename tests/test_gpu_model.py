@@ -52,7 +52,8 @@ def test_against_oracle_seeded(T, F, B):
     assert (got.argmax(1)[safe] == want.argmax(1)[safe]).all()
 
 
-@pytest.mark.parametrize("T,F,B", [(99, 40, 64), (99, 40, 1), (99, 10, 7), (31, 40, 4), (7, 10, 3), (120, 40, 5)])
+@pytest.mark.parametrize("T,F,B", [(99, 40, 64), (99, 40, 1), (99, 10, 7), (31, 40, 4), (7, 10, 3), (120, 40, 5),
+                                   (200, 10, 5)])   # 200x10: too long for two clips per slot, one clip per slot fits
 def test_fused_equals_layered(T, F, B):
     """The fused tcgen05 kernel (tf32 operands) against the layered fp32 kernels and the float64
     oracle: odd batch sizes exercise the half-empty clip pair, short/long T the row pipeline."""
