@@ -19,7 +19,7 @@
 #include <string>
 #include <vector>
 
-#include "common.cuh"
+#include "mfcc_dev.cuh"
 
 namespace kws {
 
@@ -87,6 +87,77 @@ __global__ void __launch_bounds__(256) gru_inproj_kernel(const float* __restrict
       const int n = n0 + tx * 4 + j;
       if (n < N) Cout[m * N + n] = acc[i][j] + bias[n];
     }
+  }
+}
+
+// The same GEMM, register-tiled: 128 x 64 tile, 8 x 4 outputs per thread as packed f32x2 pairs, K in slices
+// of 16 through two shared-memory buffers (the next slice's global loads are in flight while the current one
+// is multiplied).  Requires K % 16 == 0 and N % 64 == 0 (288 -> 192 and 64 -> 192 of the CRNN do).
+__global__ void __launch_bounds__(256) gru_inproj_tiled_kernel(const float* __restrict__ A, const float* __restrict__ Bm,
+                                                               const float* __restrict__ bias, float* __restrict__ Cout,
+                                                               long long M, int N, int K) {
+  constexpr int TM = 128, TN = 64, TK = 16, LDA = TM + 4;
+  __shared__ __align__(16) float sA[2][TK][LDA];   // [k][m]
+  __shared__ __align__(16) float sB[2][TK][TN];    // [k][n]
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const long long m0 = (long long)blockIdx.x * TM;
+  const int n0 = blockIdx.y * TN;
+  // global -> register staging: A rows (2 float4 along k per thread), B rows (1 float4 along n)
+  const int ar = tid >> 2, ak = (tid & 3) * 4;         // rows ar and ar + 64, k offset ak
+  const int bk = tid >> 4, bn = (tid & 15) * 4;
+  float4 ra[2], rb;
+  auto gload = [&](int k0) {
+#pragma unroll
+    for (int hh = 0; hh < 2; ++hh) {
+      const long long m = m0 + ar + 64 * hh;
+      ra[hh] = m < M ? *reinterpret_cast<const float4*>(A + m * K + k0 + ak) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    rb = *reinterpret_cast<const float4*>(Bm + (size_t)(k0 + bk) * N + n0 + bn);
+  };
+  auto sstore = [&](int buf) {
+#pragma unroll
+    for (int hh = 0; hh < 2; ++hh) {
+      const int r = ar + 64 * hh;
+      sA[buf][ak + 0][r] = ra[hh].x;
+      sA[buf][ak + 1][r] = ra[hh].y;
+      sA[buf][ak + 2][r] = ra[hh].z;
+      sA[buf][ak + 3][r] = ra[hh].w;
+    }
+    *reinterpret_cast<float4*>(&sB[buf][bk][bn]) = rb;
+  };
+  V acc[8][2];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i][0] = acc[i][1] = fsplat(0.f);
+  gload(0);
+  sstore(0);
+  __syncthreads();
+  const int nk = K / TK;
+  for (int kt = 0; kt < nk; ++kt) {
+    const int buf = kt & 1;
+    if (kt + 1 < nk) gload((kt + 1) * TK);
+#pragma unroll
+    for (int kk = 0; kk < TK; ++kk) {
+      const float4 a0 = *reinterpret_cast<const float4*>(&sA[buf][kk][ty * 8]);
+      const float4 a1 = *reinterpret_cast<const float4*>(&sA[buf][kk][ty * 8 + 4]);
+      const float4 b = *reinterpret_cast<const float4*>(&sB[buf][kk][tx * 4]);
+      const V b0 = make_float2(b.x, b.y), b1 = make_float2(b.z, b.w);
+      const float av[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        acc[i][0] = ffma(fsplat(av[i]), b0, acc[i][0]);
+        acc[i][1] = ffma(fsplat(av[i]), b1, acc[i][1]);
+      }
+    }
+    if (kt + 1 < nk) sstore(buf ^ 1);   // the other buffer was last read one iteration ago (barrier below)
+    __syncthreads();
+  }
+  const float4 bv = *reinterpret_cast<const float4*>(bias + n0 + tx * 4);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const long long m = m0 + ty * 8 + i;
+    if (m < M)
+      *reinterpret_cast<float4*>(Cout + m * N + n0 + tx * 4) =
+          make_float4(acc[i][0].x + bv.x, acc[i][0].y + bv.y, acc[i][1].x + bv.z, acc[i][1].y + bv.w);
   }
 }
 
@@ -334,8 +405,13 @@ int kws_crnn_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t 
     int I = I0;
     for (int l = 0; l < m.layers; ++l) {
       const long long M = nb * H1;
-      dim3 grid((unsigned)((M + 63) / 64), (unsigned)((3 * H + 63) / 64));
-      gru_inproj_kernel<<<grid, 256, 0, st>>>(x, m.d_wih[l], m.d_bih[l], d_xp, M, 3 * H, I);
+      if (I % 16 == 0 && (3 * H) % 64 == 0) {
+        dim3 grid((unsigned)((M + 127) / 128), (unsigned)(3 * H / 64));
+        gru_inproj_tiled_kernel<<<grid, 256, 0, st>>>(x, m.d_wih[l], m.d_bih[l], d_xp, M, 3 * H, I);
+      } else {
+        dim3 grid((unsigned)((M + 63) / 64), (unsigned)((3 * H + 63) / 64));
+        gru_inproj_kernel<<<grid, 256, 0, st>>>(x, m.d_wih[l], m.d_bih[l], d_xp, M, 3 * H, I);
+      }
       KWS_CHECK_LAUNCH(h);
       const bool more = l + 1 < m.layers;
       gru_recurrent_kernel<<<(unsigned)((nb + kGruNB - 1) / kGruNB), 256, gru_smem, st>>>(
