@@ -162,24 +162,82 @@ __global__ void __launch_bounds__(256) gru_inproj_tiled_kernel(const float* __re
 }
 
 // Sequential half of one GRU layer.  xp [B, T, 3H] = W_ih x_t + b_ih (gate order r, z, n like torch).
-// CTA = NB clips; thread = (clip group, hidden unit j); W_hh [H][3H] and h [NB][H] in shared memory.
-// hseq (nullable) [B, T, H] receives every h_t (input of the next layer); hlast [B, H] the final state.
-constexpr int kGruNB = 16;
+// CTA = kGruNB clips; W_hh [H][3H] and the hidden state (transposed, [H][NB], double-buffered) live in shared
+// memory.  Thread = (hidden unit j, group of 8 clips): per k it reads its three gate weights once and eight
+// states as two float4, 24 FMAs per 5 shared loads; all lanes of a warp share the clip group, so the state
+// reads are broadcasts.  hseq (nullable) [B, T, H] receives every h_t; hlast [B, H] the final state.
+// H == 64 (the reference-idiom CRNN); other sizes use gru_recurrent_generic_kernel.
+constexpr int kGruNB = 32;
 __global__ void __launch_bounds__(256) gru_recurrent_kernel(const float* __restrict__ xp, const float* __restrict__ whh,
                                                             const float* __restrict__ bhh, float* __restrict__ hseq,
-                                                            float* __restrict__ hlast, long long B, int T, int H) {
+                                                            float* __restrict__ hlast, long long B, int T) {
+  constexpr int H = 64, NB = kGruNB;
+  extern __shared__ __align__(16) float sm_gru[];
+  float* s_w = sm_gru;                     // [H][3H]
+  float* s_h = s_w + (size_t)H * 3 * H;    // [2][H][NB]
+  const int tid = threadIdx.x, j = tid & 63, cg = tid >> 6;   // clips cg*8 .. cg*8+7 of the CTA
+  for (int i = tid; i < H * 3 * H; i += 256) s_w[i] = whh[i];
+  for (int i = tid; i < 2 * NB * H; i += 256) s_h[i] = 0.f;
+  __syncthreads();
+  const long long b0 = (long long)blockIdx.x * NB + cg * 8;
+  const float br = bhh[j], bz = bhh[H + j], bn = bhh[2 * H + j];
+  for (int t = 0; t < T; ++t) {
+    const float* hc = s_h + (t & 1) * NB * H;
+    float* hn = s_h + ((t + 1) & 1) * NB * H;
+    float ar[8], az[8], an[8];
+#pragma unroll
+    for (int c = 0; c < 8; ++c) ar[c] = br, az[c] = bz, an[c] = bn;
+#pragma unroll 4
+    for (int k = 0; k < H; ++k) {
+      const float wr = s_w[k * 3 * H + j], wz = s_w[k * 3 * H + H + j], wn = s_w[k * 3 * H + 2 * H + j];
+      const float4 h0 = *reinterpret_cast<const float4*>(hc + k * NB + cg * 8);
+      const float4 h1 = *reinterpret_cast<const float4*>(hc + k * NB + cg * 8 + 4);
+      const float hv[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        ar[c] = fmaf(hv[c], wr, ar[c]);
+        az[c] = fmaf(hv[c], wz, az[c]);
+        an[c] = fmaf(hv[c], wn, an[c]);
+      }
+    }
+    float hnew[8];
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      const long long b = b0 + c;
+      hnew[c] = 0.f;
+      if (b < B) {
+        const float* x = xp + (b * T + t) * 3 * H;
+        const float r = 1.f / (1.f + expf(-(x[j] + ar[c])));
+        const float z = 1.f / (1.f + expf(-(x[H + j] + az[c])));
+        const float n = tanhf(x[2 * H + j] + r * an[c]);
+        hnew[c] = (1.f - z) * n + z * hc[j * NB + cg * 8 + c];
+        if (hseq) hseq[(b * T + t) * H + j] = hnew[c];
+        if (t == T - 1) hlast[b * H + j] = hnew[c];
+      }
+    }
+    *reinterpret_cast<float4*>(hn + j * NB + cg * 8) = make_float4(hnew[0], hnew[1], hnew[2], hnew[3]);
+    *reinterpret_cast<float4*>(hn + j * NB + cg * 8 + 4) = make_float4(hnew[4], hnew[5], hnew[6], hnew[7]);
+    __syncthreads();
+  }
+}
+
+// Any hidden size: thread = (clip, unit) items strided over the CTA, 16 clips per CTA.
+constexpr int kGruNBg = 16;
+__global__ void __launch_bounds__(256) gru_recurrent_generic_kernel(const float* __restrict__ xp, const float* __restrict__ whh,
+                                                                    const float* __restrict__ bhh, float* __restrict__ hseq,
+                                                                    float* __restrict__ hlast, long long B, int T, int H) {
   extern __shared__ __align__(16) float sm_gru[];
   float* s_w = sm_gru;                     // [H][3H]
   float* s_h = s_w + (size_t)H * 3 * H;    // [2][NB][H]
   const int tid = threadIdx.x;
   for (int i = tid; i < H * 3 * H; i += 256) s_w[i] = whh[i];
-  for (int i = tid; i < 2 * kGruNB * H; i += 256) s_h[i] = 0.f;
+  for (int i = tid; i < 2 * kGruNBg * H; i += 256) s_h[i] = 0.f;
   __syncthreads();
-  const long long b0 = (long long)blockIdx.x * kGruNB;
-  const int nitems = kGruNB * H;           // (clip, unit) pairs of this CTA
+  const long long b0 = (long long)blockIdx.x * kGruNBg;
+  const int nitems = kGruNBg * H;           // (clip, unit) pairs of this CTA
   for (int t = 0; t < T; ++t) {
-    const float* hc = s_h + (t & 1) * kGruNB * H;
-    float* hn = s_h + ((t + 1) & 1) * kGruNB * H;
+    const float* hc = s_h + (t & 1) * kGruNBg * H;
+    float* hn = s_h + ((t + 1) & 1) * kGruNBg * H;
     for (int it = tid; it < nitems; it += 256) {
       const int cb = it / H, j = it - cb * H;
       const long long b = b0 + cb;
@@ -379,7 +437,7 @@ int kws_crnn_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t 
   KWS_CUDA(cudaSetDevice(h->device));
   cudaStream_t st = (cudaStream_t)stream;
   const int Cc = m.cc, H = m.hidden, K = m.num_classes, I0 = Cc * W1;
-  const int64_t chunk = B < 4096 ? B : 4096;
+  const int64_t chunk = B < 8192 ? B : 8192;
   // workspace per chunk: conv output [chunk, H1, I0], projections [chunk, H1, 3H], hidden sequence, last state
   size_t need = 0;
   auto take = [&](size_t floats) { size_t o = need; need += (floats * 4 + 255) & ~(size_t)255; return o; };
@@ -395,8 +453,12 @@ int kws_crnn_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t 
   char* ws = (char*)m.d_ws;
   float *d_conv = (float*)(ws + o_conv), *d_xp = (float*)(ws + o_xp), *d_seq = (float*)(ws + o_seq),
         *d_last = (float*)(ws + o_last);
-  const size_t gru_smem = ((size_t)H * 3 * H + 2 * kGruNB * H) * 4;
-  KWS_CUDA(cudaFuncSetAttribute(gru_recurrent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gru_smem));
+  const int gnb = H == 64 ? kGruNB : kGruNBg;
+  const size_t gru_smem = ((size_t)H * 3 * H + 2 * (size_t)gnb * H) * 4;
+  if (H == 64)
+    KWS_CUDA(cudaFuncSetAttribute(gru_recurrent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gru_smem));
+  else
+    KWS_CUDA(cudaFuncSetAttribute(gru_recurrent_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gru_smem));
   for (int64_t b0 = 0; b0 < B; b0 += chunk) {
     const int64_t nb = (B - b0 < chunk) ? B - b0 : chunk;
     int rc = launch_conv1_relu(h, feats_dev + b0 * T * F, d_conv, m.d_conv_w, m.d_conv_b, nb, (int)T, (int)F, H1, W1, Cc, st);
@@ -414,8 +476,12 @@ int kws_crnn_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t 
       }
       KWS_CHECK_LAUNCH(h);
       const bool more = l + 1 < m.layers;
-      gru_recurrent_kernel<<<(unsigned)((nb + kGruNB - 1) / kGruNB), 256, gru_smem, st>>>(
-          d_xp, m.d_whh[l], m.d_bhh[l], more ? d_seq : nullptr, d_last, nb, H1, H);
+      if (H == 64)
+        gru_recurrent_kernel<<<(unsigned)((nb + kGruNB - 1) / kGruNB), 256, gru_smem, st>>>(
+            d_xp, m.d_whh[l], m.d_bhh[l], more ? d_seq : nullptr, d_last, nb, H1);
+      else
+        gru_recurrent_generic_kernel<<<(unsigned)((nb + kGruNBg - 1) / kGruNBg), 256, gru_smem, st>>>(
+            d_xp, m.d_whh[l], m.d_bhh[l], more ? d_seq : nullptr, d_last, nb, H1, H);
       KWS_CHECK_LAUNCH(h);
       x = d_seq;
       I = H;
