@@ -306,85 +306,129 @@ static void model_free(ModelWeights& m) {
 constexpr int64_t kModelChunk = 2048;  // clips per pass through the ping-pong workspace
 
 // conv1 (10x10, stride 2, padding 2, one input channel) + ReLU, tiled: a CTA takes RB output rows of one clip,
-// stages the 2*RB+8 zero-padded input rows and the [100][C] weights in shared memory once, and every thread
-// produces 16 channels of one output pixel (100 taps x 16 packed-f32x2 FMAs per 1 input read + 4 broadcast
-// weight reads).  Lanes of a warp are consecutive pixels of one channel group, so the weight reads are uniform.
-// Same sums in the same order as conv1_relu_kernel (bias first, taps row-major).  C % 16 == 0.
-__global__ void __launch_bounds__(256) conv1_tile_kernel(const float* __restrict__ in, float* __restrict__ out,
-                                                         const float* __restrict__ w /*[100][C]*/,
-                                                         const float* __restrict__ bias, long long B, int T, int F, int H1,
-                                                         int W1, int C, int RB) {
+// keeps the [100][C] weights in shared memory and double-buffers the 2*RB+8 zero-padded input rows (the next
+// tile's rows are fetched into registers while the current tile is computed).  A thread produces 16 channels of
+// two horizontally adjacent output pixels: per tap 4 broadcast weight reads + 2 input reads feed 16 packed
+// f32x2 FMAs.  Lanes of a warp are consecutive pixel pairs of one channel group, so the weight reads are uniform.
+// Same sums in the same order as conv1_relu_kernel (bias first, taps row-major; a padded tap adds 0).  C % 16 == 0.
+constexpr int kC1Threads = 128, kC1Slack = 16;
+__global__ void __launch_bounds__(kC1Threads) conv1_tile_kernel(const float* __restrict__ in, float* __restrict__ out,
+                                                               const float* __restrict__ w /*[100][C]*/,
+                                                               const float* __restrict__ bias, long long B, int T, int F,
+                                                               int H1, int W1, int C, int RB) {
   extern __shared__ __align__(16) float s_c1[];
-  const int FP = F + 4, NR = 2 * RB + 8;
-  float* s_w = s_c1;               // [100][C]
-  float* s_in = s_w + 100 * C;     // [NR][FP]: input rows 2*r0-2 .. , columns -2 .. F+1
-  const int tid = threadIdx.x, ng = C / 16;
-  for (int i = tid; i < 100 * C / 4; i += 256) reinterpret_cast<float4*>(s_w)[i] = __ldg(reinterpret_cast<const float4*>(w) + i);
+  constexpr int kMaxPre = 16;                       // staged floats per thread and tile (launcher guarantees the bound)
+  const int FP = F + 4, NR = 2 * RB + 8, npatch = NR * FP;
+  float* s_w = s_c1;                                // [100][C]
+  float* s_in = s_w + 100 * C;                      // [2][NR * FP + slack]: input rows 2*r0-2 .., columns -2 .. F+1
+  const int pstride = npatch + kC1Slack;
+  const int tid = threadIdx.x, ng = C / 16, wg = (W1 + 1) / 2;
+  for (int i = tid; i < 100 * C / 4; i += kC1Threads) reinterpret_cast<float4*>(s_w)[i] = __ldg(reinterpret_cast<const float4*>(w) + i);
+  for (int i = tid; i < 2 * pstride; i += kC1Threads) s_in[i] = 0.f;
   const int nrb = (H1 + RB - 1) / RB;
   const long long ntiles = B * nrb;
-  for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+  float pre[kMaxPre];
+  auto fetch = [&](long long tile) {  // the tile's input rows -> registers (zero outside the image)
     const long long b = tile / nrb;
     const int r0 = (int)(tile - b * nrb) * RB;
-    __syncthreads();
     const float* img = in + b * (long long)T * F;
-    for (int i = tid; i < NR * FP; i += 256) {
-      const int rr = i / FP, cc = i - rr * FP;
-      const int hi = 2 * r0 - 2 + rr, wi = cc - 2;
-      s_in[i] = (hi >= 0 && hi < T && wi >= 0 && wi < F) ? __ldg(img + hi * F + wi) : 0.f;
+#pragma unroll
+    for (int u = 0; u < kMaxPre; ++u) {
+      const int i = tid + u * kC1Threads;
+      float v = 0.f;
+      if (i < npatch) {
+        const int rr = i / FP, cc = i - rr * FP;
+        const int hi = 2 * r0 - 2 + rr, wi = cc - 2;
+        if (hi >= 0 && hi < T && wi >= 0 && wi < F) v = __ldg(img + hi * F + wi);
+      }
+      pre[u] = v;
     }
-    __syncthreads();
-    const int rows = min(RB, H1 - r0), npx = rows * W1;
-    for (int item = tid; item < npx * ng; item += 256) {
-      const int g = item / npx, px = item - g * npx;
-      const int rl = px / W1, wo = px - rl * W1;
-      V acc[8];
+  };
+  auto stash = [&](int buf) {
+#pragma unroll
+    for (int u = 0; u < kMaxPre; ++u) {
+      const int i = tid + u * kC1Threads;
+      if (i < npatch) s_in[buf * pstride + i] = pre[u];
+    }
+  };
+  __syncthreads();
+  if ((long long)blockIdx.x < ntiles) {
+    fetch(blockIdx.x);
+    stash(0);
+  }
+  __syncthreads();
+  int buf = 0;
+  for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, buf ^= 1) {
+    const long long b = tile / nrb;
+    const int r0 = (int)(tile - b * nrb) * RB;
+    const bool more = tile + gridDim.x < ntiles;
+    if (more) fetch(tile + gridDim.x);
+    const float* patch = s_in + buf * pstride;
+    const int rows = min(RB, H1 - r0), nper = rows * wg;
+    for (int item = tid; item < nper * ng; item += kC1Threads) {
+      const int g = item / nper, pp = item - g * nper;
+      const int rl = pp / wg, wo = 2 * (pp - rl * wg);
+      V acc[2][8];
       {
         const float4* bq = reinterpret_cast<const float4*>(bias + 16 * g);
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
           const float4 bv = __ldg(bq + i);
-          acc[2 * i] = make_float2(bv.x, bv.y);
-          acc[2 * i + 1] = make_float2(bv.z, bv.w);
+          acc[0][2 * i] = acc[1][2 * i] = make_float2(bv.x, bv.y);
+          acc[0][2 * i + 1] = acc[1][2 * i + 1] = make_float2(bv.z, bv.w);
         }
       }
-      const float* xp = s_in + (2 * rl) * FP + 2 * wo;
+      const float* xp = patch + (2 * rl) * FP + 2 * wo;
       const float* wp = s_w + 16 * g;
 #pragma unroll 1
       for (int ki = 0; ki < 10; ++ki) {
 #pragma unroll
         for (int kj = 0; kj < 10; ++kj) {
-          const V x2 = fsplat(xp[ki * FP + kj]);
+          const V xa = fsplat(xp[ki * FP + kj]), xb = fsplat(xp[ki * FP + kj + 2]);
           const float4* wq = reinterpret_cast<const float4*>(wp + (ki * 10 + kj) * C);
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
             const float4 wv = wq[i];
-            acc[2 * i] = ffma(x2, make_float2(wv.x, wv.y), acc[2 * i]);
-            acc[2 * i + 1] = ffma(x2, make_float2(wv.z, wv.w), acc[2 * i + 1]);
+            const V w0 = make_float2(wv.x, wv.y), w1 = make_float2(wv.z, wv.w);
+            acc[0][2 * i] = ffma(xa, w0, acc[0][2 * i]);
+            acc[0][2 * i + 1] = ffma(xa, w1, acc[0][2 * i + 1]);
+            acc[1][2 * i] = ffma(xb, w0, acc[1][2 * i]);
+            acc[1][2 * i + 1] = ffma(xb, w1, acc[1][2 * i + 1]);
           }
         }
       }
-      float4* dst = reinterpret_cast<float4*>(out + ((b * H1 + r0 + rl) * W1 + wo) * (long long)C + 16 * g);
 #pragma unroll
-      for (int i = 0; i < 4; ++i)
-        dst[i] = make_float4(fmaxf(acc[2 * i].x, 0.f), fmaxf(acc[2 * i].y, 0.f), fmaxf(acc[2 * i + 1].x, 0.f),
-                             fmaxf(acc[2 * i + 1].y, 0.f));
+      for (int e = 0; e < 2; ++e) {
+        if (wo + e < W1) {
+          float4* dst = reinterpret_cast<float4*>(out + ((b * H1 + r0 + rl) * W1 + wo + e) * (long long)C + 16 * g);
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            dst[i] = make_float4(fmaxf(acc[e][2 * i].x, 0.f), fmaxf(acc[e][2 * i].y, 0.f), fmaxf(acc[e][2 * i + 1].x, 0.f),
+                                 fmaxf(acc[e][2 * i + 1].y, 0.f));
+        }
+      }
     }
+    if (more) stash(buf ^ 1);   // the other buffer was last read one tile ago, behind the barrier below
+    __syncthreads();
   }
 }
 
 int launch_conv1_relu(kws_handle_t h, const float* in, float* out, const float* w_packed, const float* bias, int64_t B,
                       int T, int F, int H1, int W1, int C, cudaStream_t st) {
   if (C % 16 == 0) {
-    // rows per tile: about one work item (pixel x 16 channels) per thread, at most the whole map
-    int RB = (256 + W1 * (C / 16) - 1) / (W1 * (C / 16));
-    if (RB > H1) RB = H1;
-    if (RB < 1) RB = 1;
-    const size_t smem = ((size_t)100 * C + (size_t)(2 * RB + 8) * (F + 4)) * 4;
-    if (smem <= 200 * 1024) {
+    // rows per tile: about one work item (pixel pair x 16 channels) per thread, tiles of a clip equally tall
+    const int per_row = ((W1 + 1) / 2) * (C / 16);
+    int nrb = (H1 * per_row + kC1Threads - 1) / kC1Threads;
+    if (nrb < 1) nrb = 1;
+    if (nrb > H1) nrb = H1;
+    const int RB = (H1 + nrb - 1) / nrb;
+    const size_t npatch = (size_t)(2 * RB + 8) * (F + 4);
+    const size_t smem = ((size_t)100 * C + 2 * (npatch + kC1Slack)) * 4;
+    if (smem <= 100 * 1024 && npatch <= (size_t)16 * kC1Threads) {
       const long long ntiles = B * ((H1 + RB - 1) / RB);
-      long long g = ntiles < h->sm_count * 8LL ? ntiles : h->sm_count * 8LL;
+      long long g = ntiles < h->sm_count * 12LL ? ntiles : h->sm_count * 12LL;
       KWS_CUDA(cudaFuncSetAttribute(conv1_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      conv1_tile_kernel<<<(unsigned)g, 256, smem, st>>>(in, out, w_packed, bias, B, T, F, H1, W1, C, RB);
+      conv1_tile_kernel<<<(unsigned)g, kC1Threads, smem, st>>>(in, out, w_packed, bias, B, T, F, H1, W1, C, RB);
       KWS_CHECK_LAUNCH(h);
       return KWS_OK;
     }
