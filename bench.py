@@ -136,6 +136,32 @@ class ClockSampler(threading.Thread):
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def _bind_to_gpu_numa_node(gpu_index):
+    """Multi-GPU host-buffer path: pin this rank to the CPUs NVML lists as local to its GPU before the pinned
+    buffers are allocated, so that first-touch places them on the GPU's own NUMA node (the e2e copy otherwise
+    crosses the socket link for half of the ranks).  Best effort: returns the CPU count bound to, or None."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        try:   # CUDA and NVML may enumerate differently: go through the PCI address
+            import torch
+            pr = torch.cuda.get_device_properties(gpu_index)
+            hnd = pynvml.nvmlDeviceGetHandleByPciBusId(
+                ("%08x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)).encode())
+        except Exception:
+            hnd = pynvml.nvmlDeviceGetHandleByIndex(gpu_index)
+        ncpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(hnd, (ncpu + 63) // 64)
+        cpus = {64 * wi + b for wi, wd in enumerate(words) for b in range(64) if (wd >> b) & 1}
+        cpus &= set(os.sched_getaffinity(0))
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return len(cpus)
+    except Exception:
+        pass
+    return None
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -155,6 +181,7 @@ def run_ours(args):
 
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa = _bind_to_gpu_numa_node(local) if world > 1 else None
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
@@ -311,7 +338,7 @@ def run_ours(args):
             "config": {"workload": "mfcc40_b65536", "clips_per_gpu": B, "samples": N_SAMPLES,
                        "numcep": NUMCEP, "nfilt": NFILT, "nfft": 512, "parallelism": f"batch-sharded x{world}",
                        "l2": "inputs (4.2 GB/step) larger than L2, no flush needed",
-                       "e2e_clips_per_step": Be},
+                       "e2e_clips_per_step": Be, "numa_bound_cpus": numa},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": BYTES_PER_CLIP * B, "kernel": "mfcc512_ws_kernel",
