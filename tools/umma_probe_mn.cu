@@ -1,4 +1,8 @@
-// Probe: does tcgen05.mma kind::tf32 accept MN-major (transposed) operands?  One smem tile stored as
+// Probe: does tcgen05.mma kind::tf32 accept MN-major (transposed) operands?
+// RESULT on B200 (round 1): no -- with the a_major/b_major bits set the MMA writes zeros for every LBO/SBO
+// combination, in this interleaved layout and in the 128-byte-swizzle layout of umma_probe_mn2.cu, while the
+// K-major reads of the same tiles (form (b)) are exact.  The weight-gradient GEMM of the training step would
+// therefore need transposed staging; see DESIGN.md 4.6.  One smem tile stored as
 // [channel/4][pixel][4 channels] (16-byte units) is read
 //   (a) MN-major as A (M = 64 channels, K = 128 pixels) and MN-major as B (N = 64 channels, K = 128 pixels):
 //       D1[co, ci] = sum_px G[px, co] X[px, ci]                       (the weight-gradient GEMM)
