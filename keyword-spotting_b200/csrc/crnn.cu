@@ -32,6 +32,7 @@ struct CrnnWeights {
   float* d_conv_w = nullptr;   // [100][Cc]
   float* d_conv_b = nullptr;   // [Cc]
   float* d_wih[2] = {};        // [I][3H]  (k-major; layer 0 columns in [w][c] order)
+  float* d_wimg[2] = {};       // tensor-core projection: per 32-wide K chunk [tf32 hi tile | tf32 lo tile] of W_ih, UMMA K-major
   float* d_whh[2] = {};        // [H][3H]  (k-major)
   float* d_bih[2] = {};        // [3H]
   float* d_bhh[2] = {};        // [3H]
@@ -161,6 +162,159 @@ __global__ void __launch_bounds__(256) gru_inproj_tiled_kernel(const float* __re
   }
 }
 
+// The time-parallel half on the tensor core: C[M, N] = A[M, K] . W[N, K]^T + bias, fp32-grade through a 3-term
+// tf32 split (A_hi W_hi + A_lo W_hi + A_hi W_lo, operands rounded with cvt.rna; error ~2^-21 like the MFCC's DCT).
+// Both operands are K-major as they lie in memory (activations [row][feature], weights [gate][feature]), so no
+// transposition is needed.  Persistent CTAs, tile = 128 rows x N (<= 256) columns, K streamed in chunks of 32
+// through two stages, no CTA-wide barrier in the main loop:
+//   warps 0..6  producers: read the A chunk (coalesced float4), split hi/lo, store both K-major tiles
+//               (144-byte K-chunk pitch: the 8 lanes of a quarter warp hit 32 different banks), arrive on fullA
+//   warp  7     issue warp (converged, elected lane): requests the chunk's pre-split weight tiles by TMA bulk
+//               copy as soon as the stage is free, waits fullA / fullB, issues the 12 tcgen05.mma of the chunk,
+//               tcgen05.commit -> empty[stage] (and -> acc_done after the last chunk of a tile)
+//   warps 0..3  epilogue: TMEM -> registers -> + bias -> global, then arrive on acc_free so that the next tile's
+//               first MMA may overwrite the accumulator; warps 4..6 already produce the next tile meanwhile.
+constexpr int kDK = 32, kDLboA = 144, kDSboA = (kDK / 4) * kDLboA, kDATile = 16 * kDSboA;   // A: 128 rows x 32 K
+constexpr int kDProd = 7;                                                                    // producer warps
+struct DenseParams {
+  const float* A;
+  const float* wimg;   // [K/32][2][N/8 * 1024 B]
+  const float* bias;
+  float* C;
+  long long M;
+  int N, K;
+};
+__global__ void __launch_bounds__(256, 1) dense_gemm_tf32x3_kernel(const DenseParams p) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  __shared__ __align__(8) unsigned long long s_bar[8];   // fullA[2], fullB[2], empty[2], acc_done, acc_free
+  __shared__ uint32_t s_tmem;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int N = p.N, K = p.K, nch = K / kDK;
+  const uint32_t btile = (uint32_t)(N / 8) * 1024u;            // one weight tile (hi or lo) of a chunk
+  const uint32_t stage_bytes = 2u * kDATile + 2u * btile;
+  const uint32_t bar0 = smem_u32(&s_bar[0]);
+  auto fullA = [&](int s) { return bar0 + 8u * s; };
+  auto fullB = [&](int s) { return bar0 + 16u + 8u * s; };
+  auto empty = [&](int s) { return bar0 + 32u + 8u * s; };
+  const uint32_t acc_done = bar0 + 48u, acc_free = bar0 + 56u;
+  if (tid == 0) {
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(fullA(s), kDProd);
+      mbar_init(fullB(s), 1);
+      mbar_init(empty(s), 1);
+    }
+    mbar_init(acc_done, 1);
+    mbar_init(acc_free, 4);
+    fence_mbar_init();
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "n"(256));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = s_tmem;
+  const long long ntiles = (p.M + 127) / 128;
+  const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((128u >> 4) << 24);
+
+  if (warp == kDProd) {
+    // ============================ issue warp ============================
+    uint32_t cnt = 0, it = 0;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+      for (int kc = 0; kc < nch; ++kc, ++cnt) {
+        const int s = cnt & 1;
+        const uint32_t sb = smem_u32(smem) + (uint32_t)s * stage_bytes;
+        if (cnt >= 2) mbar_wait(empty(s), ((cnt - 2) >> 1) & 1);     // the MMAs that read this stage have retired
+        if (lane == 0) {
+          mbar_expect_tx(fullB(s), 2u * btile);
+          tma_load_1d(sb + 2u * kDATile, reinterpret_cast<const unsigned char*>(p.wimg) + (size_t)kc * 2u * btile, 2u * btile,
+                      fullB(s));
+        }
+        __syncwarp();
+        mbar_wait(fullA(s), (cnt >> 1) & 1);
+        mbar_wait(fullB(s), (cnt >> 1) & 1);
+        if (kc == 0 && it > 0) mbar_wait(acc_free, (it - 1) & 1);    // the previous tile's epilogue has read TMEM
+        tc_fence_after();
+        const uint32_t a_hi = sb, a_lo = sb + kDATile, b_hi = sb + 2u * kDATile, b_lo = b_hi + btile;
+#pragma unroll
+        for (int term = 0; term < 3; ++term) {
+          const uint32_t ab = term == 1 ? a_lo : a_hi, bb = term == 2 ? b_lo : b_hi;
+#pragma unroll
+          for (int ks = 0; ks < kDK / 8; ++ks)
+            tc_mma_tf32_elect(tmem, umma_desc(ab + ks * 2u * kDLboA, kDLboA, kDSboA), umma_desc(bb + ks * 256u, 128u, 1024u),
+                              idesc, (kc > 0 || term > 0 || ks > 0) ? 1u : 0u);
+        }
+        tc_commit_elect(empty(s));
+        if (kc == nch - 1) tc_commit_elect(acc_done);
+      }
+    }
+  } else {
+    // ============================ producers (+ epilogue on warps 0..3) ============================
+    uint32_t cnt = 0, it = 0;
+    const int ptid = tid;                       // 0 .. 223
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+      const long long m0 = tile * 128;
+      for (int kc = 0; kc < nch; ++kc, ++cnt) {
+        const int s = cnt & 1;
+        unsigned char* sa = smem + (size_t)s * stage_bytes;
+        // all of this thread's loads of the chunk go out first (and before the wait for the stage): the global
+        // latency is paid once per chunk, overlapped with the MMAs still reading the stage
+        constexpr int kIt = (128 * (kDK / 4) + kDProd * 32 - 1) / (kDProd * 32);
+        float4 v[kIt];
+#pragma unroll
+        for (int u = 0; u < kIt; ++u) {
+          const int i = ptid + u * kDProd * 32, r = i >> 3, c = i & 7;   // row of the tile, 16-byte K chunk
+          const long long m = m0 + r;
+          v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (i < 128 * (kDK / 4) && m < p.M) v[u] = __ldg(reinterpret_cast<const float4*>(p.A + m * K + kc * kDK) + c);
+        }
+        if (cnt >= 2) mbar_wait(empty(s), ((cnt - 2) >> 1) & 1);
+#pragma unroll
+        for (int u = 0; u < kIt; ++u) {
+          const int i = ptid + u * kDProd * 32, r = i >> 3, c = i & 7;
+          if (i < 128 * (kDK / 4)) {
+            const float4 hi = make_float4(to_tf32(v[u].x), to_tf32(v[u].y), to_tf32(v[u].z), to_tf32(v[u].w));
+            const float4 lo = make_float4(to_tf32(v[u].x - hi.x), to_tf32(v[u].y - hi.y), to_tf32(v[u].z - hi.z),
+                                          to_tf32(v[u].w - hi.w));
+            const uint32_t off = (uint32_t)(r >> 3) * kDSboA + (uint32_t)c * kDLboA + (uint32_t)(r & 7) * 16u;
+            *reinterpret_cast<float4*>(sa + off) = hi;
+            *reinterpret_cast<float4*>(sa + kDATile + off) = lo;
+          }
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(fullA(s));
+      }
+      if (warp < 4) {  // epilogue: lane = accumulator row
+        mbar_wait(acc_done, it & 1);
+        tc_fence_after();
+        const long long m = m0 + warp * 32 + lane;
+        float* crow = p.C + m * N;
+        for (int c0 = 0; c0 < N; c0 += 16) {
+          float q[16];
+          tc_ld16(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, q);
+          tc_wait_ld();
+          if (m < p.M) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const float4 bv = __ldg(reinterpret_cast<const float4*>(p.bias + c0) + j);
+              *reinterpret_cast<float4*>(crow + c0 + 4 * j) =
+                  make_float4(q[4 * j] + bv.x, q[4 * j + 1] + bv.y, q[4 * j + 2] + bv.z, q[4 * j + 3] + bv.w);
+            }
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(acc_free);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(256));
+}
+
 // Sequential half of one GRU layer.  xp [B, T, 3H] = W_ih x_t + b_ih (gate order r, z, n like torch).
 // CTA = kGruNB clips; W_hh [H][3H] and the hidden state (transposed, [H][NB], double-buffered) live in shared
 // memory.  Thread = (hidden unit j, group of 8 clips): per k it reads its three gate weights once and eight
@@ -280,7 +434,7 @@ static CrnnWeights* crnn_of(kws_handle_t h) { return reinterpret_cast<CrnnWeight
 
 static void crnn_free(CrnnWeights* m) {
   if (!m) return;
-  void* ptrs[] = {m->d_conv_w, m->d_conv_b, m->d_wih[0], m->d_wih[1], m->d_whh[0], m->d_whh[1], m->d_bih[0],
+  void* ptrs[] = {m->d_wimg[0], m->d_wimg[1], m->d_conv_w, m->d_conv_b, m->d_wih[0], m->d_wih[1], m->d_whh[0], m->d_whh[1], m->d_bih[0],
                   m->d_bih[1],  m->d_bhh[0], m->d_bhh[1], m->d_fc_w,   m->d_fc_b,   m->d_ws};
   for (void* p : ptrs)
     if (p) cudaFree(p);
@@ -404,6 +558,27 @@ int kws_crnn_finalize(kws_handle_t h) {
         p[(size_t)dst * 3 * H + g] = wih[(size_t)g * I + i];
       }
     if ((rc = up(&m.d_wih[l], p))) return rc;
+    if (I % kDK == 0 && (3 * H) % 16 == 0 && 3 * H <= 256) {  // weight tiles of the tensor-core projection
+      const int N = 3 * H;
+      const size_t tile = (size_t)(N / 8) * 1024 / 4;   // floats per tile
+      std::vector<float> img((size_t)(I / kDK) * 2 * tile, 0.f);
+      auto rn = [](float x) {  // cvt.rna.tf32.f32
+        uint32_t u;
+        memcpy(&u, &x, 4);
+        if ((u & 0x7f800000u) != 0x7f800000u) u = (u + 0x1000u) & ~0x1fffu;
+        memcpy(&x, &u, 4);
+        return x;
+      };
+      for (int n = 0; n < N; ++n)
+        for (int k = 0; k < I; ++k) {
+          const float v = p[(size_t)k * N + n], hi = rn(v), lo = rn(v - hi);
+          const int kc = k / kDK, kk = k % kDK;
+          const size_t off = ((size_t)(n >> 3) * 1024 + (size_t)(kk >> 2) * 128 + (size_t)(n & 7) * 16 + (size_t)(kk & 3) * 4) / 4;
+          img[(size_t)kc * 2 * tile + off] = hi;
+          img[(size_t)kc * 2 * tile + tile + off] = lo;
+        }
+      if ((rc = up(&m.d_wimg[l], img))) return rc;
+    }
     const std::vector<float>& whh = m.host[crnn_slot(m, "gru.weight_hh" + s)];  // [3H][H]
     std::vector<float> q((size_t)H * 3 * H);
     for (int g = 0; g < 3 * H; ++g)
@@ -467,7 +642,13 @@ int kws_crnn_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t 
     int I = I0;
     for (int l = 0; l < m.layers; ++l) {
       const long long M = nb * H1;
-      if (I % 16 == 0 && (3 * H) % 64 == 0) {
+      const size_t dsmem = 2 * (2 * (size_t)kDATile + 2 * (size_t)(3 * H / 8) * 1024);
+      if (m.d_wimg[l] && dsmem <= 227 * 1024) {
+        DenseParams dp{x, m.d_wimg[l], m.d_bih[l], d_xp, M, 3 * H, I};
+        KWS_CUDA(cudaFuncSetAttribute(dense_gemm_tf32x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dsmem));
+        const long long nt = (M + 127) / 128;
+        dense_gemm_tf32x3_kernel<<<(unsigned)(nt < h->sm_count ? nt : h->sm_count), 256, dsmem, st>>>(dp);
+      } else if (I % 16 == 0 && (3 * H) % 64 == 0) {
         dim3 grid((unsigned)((M + 127) / 128), (unsigned)(3 * H / 64));
         gru_inproj_tiled_kernel<<<grid, 256, 0, st>>>(x, m.d_wih[l], m.d_bih[l], d_xp, M, 3 * H, I);
       } else {

@@ -45,9 +45,6 @@ constexpr int kWsThreads = (kCWarps + 1) * 32;     // + service warp
 constexpr int kWarpScratch = 2 * 16 * 17 * 16;     // bytes: two half-warp transposes (also holds S2)
 constexpr float kFEps = 2.220446049250313e-16f;
 
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
 
 template <int LOAD_LEN, int ROUNDS>
 __global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastParams p) {
