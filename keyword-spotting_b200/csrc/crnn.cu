@@ -34,6 +34,7 @@ struct CrnnWeights {
   float* d_wih[2] = {};        // [I][3H]  (k-major; layer 0 columns in [w][c] order)
   float* d_wimg[2] = {};       // tensor-core projection: per 32-wide K chunk [tf32 hi tile | tf32 lo tile] of W_ih, UMMA K-major
   float* d_whh[2] = {};        // [H][3H]  (k-major)
+  float* d_whimg[2] = {};      // tensor-core recurrence (H == 64): W_hh in the same tile format
   float* d_bih[2] = {};        // [3H]
   float* d_bhh[2] = {};        // [3H]
   float* d_fc_w = nullptr;     // [H][K]
@@ -183,6 +184,8 @@ struct DenseParams {
   float* C;
   long long M;
   int N, K;
+  int T;   // 0: rows as they lie, C row-major.  > 0: "step-major" tiles for the tensor-core recurrence: A rows are
+           // (clip, step) pairs, tile = (group of 128 clips, step), C = [group][step][column][128 clips]
 };
 __global__ void __launch_bounds__(256, 1) dense_gemm_tf32x3_kernel(const DenseParams p) {
   extern __shared__ __align__(128) unsigned char smem[];
@@ -215,7 +218,9 @@ __global__ void __launch_bounds__(256, 1) dense_gemm_tf32x3_kernel(const DensePa
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = s_tmem;
-  const long long ntiles = (p.M + 127) / 128;
+  const int Tm = p.T;
+  const long long nrows = Tm > 0 ? p.M / Tm : p.M;            // step-major: clips
+  const long long ntiles = Tm > 0 ? ((nrows + 127) / 128) * Tm : (p.M + 127) / 128;
   const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((128u >> 4) << 24);
 
   if (warp == kDProd) {
@@ -254,7 +259,9 @@ __global__ void __launch_bounds__(256, 1) dense_gemm_tf32x3_kernel(const DensePa
     uint32_t cnt = 0, it = 0;
     const int ptid = tid;                       // 0 .. 223
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
-      const long long m0 = tile * 128;
+      // row r of the tile is A row (m0 + r) * mstride + moff
+      const long long m0 = Tm > 0 ? (tile / Tm) * 128 : tile * 128;
+      const long long mstride = Tm > 0 ? Tm : 1, moff = Tm > 0 ? tile % Tm : 0;
       for (int kc = 0; kc < nch; ++kc, ++cnt) {
         const int s = cnt & 1;
         unsigned char* sa = smem + (size_t)s * stage_bytes;
@@ -267,7 +274,8 @@ __global__ void __launch_bounds__(256, 1) dense_gemm_tf32x3_kernel(const DensePa
           const int i = ptid + u * kDProd * 32, r = i >> 3, c = i & 7;   // row of the tile, 16-byte K chunk
           const long long m = m0 + r;
           v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (i < 128 * (kDK / 4) && m < p.M) v[u] = __ldg(reinterpret_cast<const float4*>(p.A + m * K + kc * kDK) + c);
+          if (i < 128 * (kDK / 4) && m < nrows)
+            v[u] = __ldg(reinterpret_cast<const float4*>(p.A + (m * mstride + moff) * K + kc * kDK) + c);
         }
         if (cnt >= 2) mbar_wait(empty(s), ((cnt - 2) >> 1) & 1);
 #pragma unroll
@@ -291,11 +299,15 @@ __global__ void __launch_bounds__(256, 1) dense_gemm_tf32x3_kernel(const DensePa
         tc_fence_after();
         const long long m = m0 + warp * 32 + lane;
         float* crow = p.C + m * N;
+        float* ccol = p.C + tile * N * 128 + warp * 32 + lane;   // step-major: column pitch 128 floats, lanes contiguous
         for (int c0 = 0; c0 < N; c0 += 16) {
           float q[16];
           tc_ld16(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, q);
           tc_wait_ld();
-          if (m < p.M) {
+          if (Tm > 0) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) ccol[(size_t)(c0 + j) * 128] = q[j] + __ldg(p.bias + c0 + j);
+          } else if (m < nrows) {
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
               const float4 bv = __ldg(reinterpret_cast<const float4*>(p.bias + c0) + j);
@@ -375,6 +387,158 @@ __global__ void __launch_bounds__(256) gru_recurrent_kernel(const float* __restr
   }
 }
 
+// The sequential half on the tensor core (H == 64).  CTA = 128 clips = the 128 rows of one accumulator.  Per step
+// D[128 x 192] = h_{t-1} . W_hh^T (3-term tf32 split like the projection, K = 64: 24 tcgen05.mma from the issue
+// warp); the 8 gate warps (lane = clip row, warp / 4 = which 32 units) then read the r/z/n pre-activations from
+// TMEM, add the step-major input projection (lanes = clips: coalesced), apply the gates, keep h in fp32 registers
+// and write its tf32 hi/lo split into the K-major A tiles of the next step.  W_hh hi/lo tiles arrive once by TMA.
+// sigmoid/tanh through ex2 + fast division (abs error ~1e-7, far inside the 1e-4 logit tolerance).
+constexpr int kGtBTile = (192 / 8) * 1024;                     // one W_hh tile (hi or lo) of a 32-wide K chunk
+constexpr int kGtSmem = 4 * kGtBTile + 4 * kDATile;            // W_hh: 2 chunks x (hi|lo); h: 2 chunks x (hi|lo)
+struct GruTcParams {
+  const float* xg;     // [group][T][192][128]  (dense_gemm_tf32x3_kernel, step-major)
+  const float* wimg;   // [2][hi tile | lo tile]
+  const float* bhh;
+  float* hseq;         // nullable, [B][T][64]
+  float* hlast;        // [B][64]
+  long long B;
+  int T;
+};
+__device__ __forceinline__ float fast_sigmoid(float a) { return __fdividef(1.f, 1.f + __expf(-a)); }
+__device__ __forceinline__ float fast_tanh(float a) { return 1.f - __fdividef(2.f, 1.f + __expf(2.f * a)); }
+
+__global__ void __launch_bounds__(288, 1) gru_recurrent_tc_kernel(const GruTcParams p) {
+  constexpr int H = 64, N = 3 * H;
+  extern __shared__ __align__(128) unsigned char smem[];
+  __shared__ __align__(8) unsigned long long s_bar[3];   // wfull, h_ready, acc_done
+  __shared__ uint32_t s_tmem;
+  __shared__ float s_b[N];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, T = p.T;
+  const uint32_t bar0 = smem_u32(&s_bar[0]), wfull = bar0, h_ready = bar0 + 8u, acc_done = bar0 + 16u;
+  unsigned char* s_a = smem + 4 * kGtBTile;
+  if (tid == 0) {
+    mbar_init(wfull, 1);
+    mbar_init(h_ready, 8);
+    mbar_init(acc_done, 1);
+    fence_mbar_init();
+  }
+  for (int i = tid; i < 4 * kDATile / 16; i += 288) reinterpret_cast<float4*>(s_a)[i] = make_float4(0.f, 0.f, 0.f, 0.f);  // h_0 = 0
+  for (int i = tid; i < N; i += 288) s_b[i] = p.bhh[i];
+  fence_proxy_async();
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "n"(256));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = s_tmem;
+
+  if (warp == 8) {
+    // ============================ issue warp ============================
+    if (lane == 0) {
+      mbar_expect_tx(wfull, 4u * kGtBTile);
+      tma_load_1d(smem_u32(smem), p.wimg, 2u * kGtBTile, wfull);
+      tma_load_1d(smem_u32(smem) + 2u * kGtBTile, reinterpret_cast<const unsigned char*>(p.wimg) + 2u * kGtBTile, 2u * kGtBTile,
+                  wfull);
+    }
+    __syncwarp();
+    mbar_wait(wfull, 0);
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((128u >> 4) << 24);
+    for (int t = 0; t < T; ++t) {
+      if (t > 0) mbar_wait(h_ready, (t - 1) & 1);      // h_{t-1} is in the A tiles and the gates have read D
+      tc_fence_after();
+#pragma unroll
+      for (int kc = 0; kc < 2; ++kc) {
+        const uint32_t a_hi = smem_u32(s_a) + kc * 2u * kDATile, a_lo = a_hi + kDATile;
+        const uint32_t b_hi = smem_u32(smem) + kc * 2u * kGtBTile, b_lo = b_hi + kGtBTile;
+#pragma unroll
+        for (int term = 0; term < 3; ++term) {
+          const uint32_t ab = term == 1 ? a_lo : a_hi, bb = term == 2 ? b_lo : b_hi;
+#pragma unroll
+          for (int ks = 0; ks < kDK / 8; ++ks)
+            tc_mma_tf32_elect(tmem, umma_desc(ab + ks * 2u * kDLboA, kDLboA, kDSboA), umma_desc(bb + ks * 256u, 128u, 1024u),
+                              idesc, (kc > 0 || term > 0 || ks > 0) ? 1u : 0u);
+        }
+      }
+      tc_commit_elect(acc_done);
+    }
+  } else {
+    // ============================ gate warps ============================
+    const int rg = warp & 3, uh = warp >> 2, row = rg * 32 + lane;
+    const long long clip = (long long)blockIdx.x * 128 + row;
+    const bool valid = clip < p.B;
+    const float* xg = p.xg + (size_t)blockIdx.x * T * N * 128 + row;
+    const uint32_t trow = tmem + ((uint32_t)(rg * 32) << 16);
+    unsigned char* arow = s_a + uh * 2 * kDATile + (row >> 3) * kDSboA + (row & 7) * 16;
+    float h[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) h[j] = 0.f;
+    for (int t = 0; t < T; ++t) {
+      const float* xt = xg + (size_t)t * N * 128;
+      float x[2][24];
+      auto fetch = [&](int g, float (&d)[24]) {
+        const int u0 = uh * 32 + g * 8;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          d[j] = __ldg(xt + (size_t)(u0 + j) * 128);
+          d[8 + j] = __ldg(xt + (size_t)(H + u0 + j) * 128);
+          d[16 + j] = __ldg(xt + (size_t)(2 * H + u0 + j) * 128);
+        }
+      };
+      fetch(0, x[0]);                        // in flight while the step's MMAs run
+      mbar_wait(acc_done, t & 1);
+      tc_fence_after();
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        if (g < 3) fetch(g + 1, x[(g + 1) & 1]);
+        const int u0 = uh * 32 + g * 8;
+        float dr[8], dz[8], dn[8];
+        tc_ld8(trow + (uint32_t)u0, dr);
+        tc_ld8(trow + (uint32_t)(H + u0), dz);
+        tc_ld8(trow + (uint32_t)(2 * H + u0), dn);
+        tc_wait_ld();
+        float hi[8], lo[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float r = fast_sigmoid(x[g & 1][j] + dr[j] + s_b[u0 + j]);
+          const float z = fast_sigmoid(x[g & 1][8 + j] + dz[j] + s_b[H + u0 + j]);
+          const float n = fast_tanh(x[g & 1][16 + j] + r * (dn[j] + s_b[2 * H + u0 + j]));
+          const float hn = (1.f - z) * n + z * h[g * 8 + j];
+          h[g * 8 + j] = hn;
+          hi[j] = to_tf32(hn);
+          lo[j] = to_tf32(hn - hi[j]);
+        }
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+          unsigned char* dst = arow + (2 * g + q) * kDLboA;
+          *reinterpret_cast<float4*>(dst) = make_float4(hi[4 * q], hi[4 * q + 1], hi[4 * q + 2], hi[4 * q + 3]);
+          *reinterpret_cast<float4*>(dst + kDATile) = make_float4(lo[4 * q], lo[4 * q + 1], lo[4 * q + 2], lo[4 * q + 3]);
+        }
+        if (valid) {
+          if (p.hseq) {
+            float4* o = reinterpret_cast<float4*>(p.hseq + (clip * T + t) * H + u0);
+            o[0] = make_float4(h[g * 8], h[g * 8 + 1], h[g * 8 + 2], h[g * 8 + 3]);
+            o[1] = make_float4(h[g * 8 + 4], h[g * 8 + 5], h[g * 8 + 6], h[g * 8 + 7]);
+          }
+          if (t == T - 1) {
+            float4* o = reinterpret_cast<float4*>(p.hlast + clip * H + u0);
+            o[0] = make_float4(h[g * 8], h[g * 8 + 1], h[g * 8 + 2], h[g * 8 + 3]);
+            o[1] = make_float4(h[g * 8 + 4], h[g * 8 + 5], h[g * 8 + 6], h[g * 8 + 7]);
+          }
+        }
+      }
+      tc_fence_before();
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(h_ready);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(256));
+}
+
 // Any hidden size: thread = (clip, unit) items strided over the CTA, 16 clips per CTA.
 constexpr int kGruNBg = 16;
 __global__ void __launch_bounds__(256) gru_recurrent_generic_kernel(const float* __restrict__ xp, const float* __restrict__ whh,
@@ -434,7 +598,7 @@ static CrnnWeights* crnn_of(kws_handle_t h) { return reinterpret_cast<CrnnWeight
 
 static void crnn_free(CrnnWeights* m) {
   if (!m) return;
-  void* ptrs[] = {m->d_wimg[0], m->d_wimg[1], m->d_conv_w, m->d_conv_b, m->d_wih[0], m->d_wih[1], m->d_whh[0], m->d_whh[1], m->d_bih[0],
+  void* ptrs[] = {m->d_wimg[0], m->d_wimg[1], m->d_whimg[0], m->d_whimg[1], m->d_conv_w, m->d_conv_b, m->d_wih[0], m->d_wih[1], m->d_whh[0], m->d_whh[1], m->d_bih[0],
                   m->d_bih[1],  m->d_bhh[0], m->d_bhh[1], m->d_fc_w,   m->d_fc_b,   m->d_ws};
   for (void* p : ptrs)
     if (p) cudaFree(p);
@@ -558,10 +722,10 @@ int kws_crnn_finalize(kws_handle_t h) {
         p[(size_t)dst * 3 * H + g] = wih[(size_t)g * I + i];
       }
     if ((rc = up(&m.d_wih[l], p))) return rc;
-    if (I % kDK == 0 && (3 * H) % 16 == 0 && 3 * H <= 256) {  // weight tiles of the tensor-core projection
-      const int N = 3 * H;
+    // tf32 hi/lo weight tiles for the tensor-core kernels, from a k-major [K][N] matrix
+    auto wimg_of = [](const std::vector<float>& km, int Kd, int N) {
       const size_t tile = (size_t)(N / 8) * 1024 / 4;   // floats per tile
-      std::vector<float> img((size_t)(I / kDK) * 2 * tile, 0.f);
+      std::vector<float> img((size_t)(Kd / kDK) * 2 * tile, 0.f);
       auto rn = [](float x) {  // cvt.rna.tf32.f32
         uint32_t u;
         memcpy(&u, &x, 4);
@@ -570,20 +734,24 @@ int kws_crnn_finalize(kws_handle_t h) {
         return x;
       };
       for (int n = 0; n < N; ++n)
-        for (int k = 0; k < I; ++k) {
-          const float v = p[(size_t)k * N + n], hi = rn(v), lo = rn(v - hi);
+        for (int k = 0; k < Kd; ++k) {
+          const float v = km[(size_t)k * N + n], hi = rn(v), lo = rn(v - hi);
           const int kc = k / kDK, kk = k % kDK;
           const size_t off = ((size_t)(n >> 3) * 1024 + (size_t)(kk >> 2) * 128 + (size_t)(n & 7) * 16 + (size_t)(kk & 3) * 4) / 4;
           img[(size_t)kc * 2 * tile + off] = hi;
           img[(size_t)kc * 2 * tile + tile + off] = lo;
         }
-      if ((rc = up(&m.d_wimg[l], img))) return rc;
-    }
+      return img;
+    };
+    if (I % kDK == 0 && (3 * H) % 16 == 0 && 3 * H <= 256)
+      if ((rc = up(&m.d_wimg[l], wimg_of(p, I, 3 * H)))) return rc;
     const std::vector<float>& whh = m.host[crnn_slot(m, "gru.weight_hh" + s)];  // [3H][H]
     std::vector<float> q((size_t)H * 3 * H);
     for (int g = 0; g < 3 * H; ++g)
       for (int k = 0; k < H; ++k) q[(size_t)k * 3 * H + g] = whh[(size_t)g * H + k];
     if ((rc = up(&m.d_whh[l], q))) return rc;
+    if (H == 64)
+      if ((rc = up(&m.d_whimg[l], wimg_of(q, H, 3 * H)))) return rc;
     if ((rc = up(&m.d_bih[l], m.host[crnn_slot(m, "gru.bias_ih" + s)]))) return rc;
     if ((rc = up(&m.d_bhh[l], m.host[crnn_slot(m, "gru.bias_hh" + s)]))) return rc;
   }
@@ -612,11 +780,11 @@ int kws_crnn_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t 
   KWS_CUDA(cudaSetDevice(h->device));
   cudaStream_t st = (cudaStream_t)stream;
   const int Cc = m.cc, H = m.hidden, K = m.num_classes, I0 = Cc * W1;
-  const int64_t chunk = B < 8192 ? B : 8192;
+  const int64_t chunk = B < 16384 ? B : 16384;
   // workspace per chunk: conv output [chunk, H1, I0], projections [chunk, H1, 3H], hidden sequence, last state
   size_t need = 0;
   auto take = [&](size_t floats) { size_t o = need; need += (floats * 4 + 255) & ~(size_t)255; return o; };
-  const size_t o_conv = take((size_t)chunk * H1 * I0), o_xp = take((size_t)chunk * H1 * 3 * H),
+  const size_t o_conv = take((size_t)chunk * H1 * I0), o_xp = take((size_t)((chunk + 127) / 128 * 128) * H1 * 3 * H),
                o_seq = take((size_t)chunk * H1 * H), o_last = take((size_t)chunk * H);
   if (need > m.ws_bytes) {
     if (m.d_ws) KWS_CUDA(cudaFree(m.d_ws));
@@ -643,10 +811,11 @@ int kws_crnn_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t 
     for (int l = 0; l < m.layers; ++l) {
       const long long M = nb * H1;
       const size_t dsmem = 2 * (2 * (size_t)kDATile + 2 * (size_t)(3 * H / 8) * 1024);
+      const bool tc_rec = H == 64 && m.d_wimg[l] && m.d_whimg[l];   // both halves of the layer on the tensor core
       if (m.d_wimg[l] && dsmem <= 227 * 1024) {
-        DenseParams dp{x, m.d_wimg[l], m.d_bih[l], d_xp, M, 3 * H, I};
+        DenseParams dp{x, m.d_wimg[l], m.d_bih[l], d_xp, M, 3 * H, I, tc_rec ? H1 : 0};
         KWS_CUDA(cudaFuncSetAttribute(dense_gemm_tf32x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dsmem));
-        const long long nt = (M + 127) / 128;
+        const long long nt = tc_rec ? (nb + 127) / 128 * H1 : (M + 127) / 128;
         dense_gemm_tf32x3_kernel<<<(unsigned)(nt < h->sm_count ? nt : h->sm_count), 256, dsmem, st>>>(dp);
       } else if (I % 16 == 0 && (3 * H) % 64 == 0) {
         dim3 grid((unsigned)((M + 127) / 128), (unsigned)(3 * H / 64));
@@ -657,7 +826,11 @@ int kws_crnn_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t 
       }
       KWS_CHECK_LAUNCH(h);
       const bool more = l + 1 < m.layers;
-      if (H == 64)
+      if (tc_rec) {
+        GruTcParams gp{d_xp, m.d_whimg[l], m.d_bhh[l], more ? d_seq : nullptr, d_last, nb, H1};
+        KWS_CUDA(cudaFuncSetAttribute(gru_recurrent_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kGtSmem));
+        gru_recurrent_tc_kernel<<<(unsigned)((nb + 127) / 128), 288, kGtSmem, st>>>(gp);
+      } else if (H == 64)
         gru_recurrent_kernel<<<(unsigned)((nb + kGruNB - 1) / kGruNB), 256, gru_smem, st>>>(
             d_xp, m.d_whh[l], m.d_bhh[l], more ? d_seq : nullptr, d_last, nb, H1);
       else

@@ -14,7 +14,7 @@ pytestmark = pytest.mark.gpu
 
 
 @pytest.mark.parametrize("F,Cc,H,L,B,T", [(40, 16, 64, 1, 19, 99), (40, 8, 32, 2, 5, 99), (10, 16, 64, 2, 33, 49),
-                                          (26, 4, 128, 1, 3, 31)])
+                                          (26, 4, 128, 1, 3, 31), (40, 16, 64, 2, 150, 31), (40, 16, 64, 1, 257, 20)])
 def test_crnn_matches_oracle(F, Cc, H, L, B, T):
     torch.manual_seed(F + Cc + H + L)
     m = CRNN(num_classes=12, n_features=F, conv_channels=Cc, hidden=H, num_layers=L)
