@@ -31,6 +31,7 @@ struct CrnnWeights {
   std::vector<bool> loaded;
   float* d_conv_w = nullptr;   // [100][Cc]
   float* d_conv_b = nullptr;   // [Cc]
+  float* d_c1img = nullptr;    // tensor-core conv1 (Cc == 16, 18 output columns): [dy][hi|lo][32 x 16] UMMA K-major tiles
   float* d_wih[2] = {};        // [I][3H]  (k-major; layer 0 columns in [w][c] order)
   float* d_wimg[2] = {};       // tensor-core projection: per 32-wide K chunk [tf32 hi tile | tf32 lo tile] of W_ih, UMMA K-major
   float* d_whh[2] = {};        // [H][3H]  (k-major)
@@ -327,6 +328,168 @@ __global__ void __launch_bounds__(256, 1) dense_gemm_tf32x3_kernel(const DensePa
   if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(256));
 }
 
+// conv1 (10 x 10, stride 2, padding 2, + bias, ReLU) of the reference-idiom CRNN (16 channels, 40 features) on the
+// tensor core, fp32-grade through the same 3-term tf32 split.  Tile = 128 clips at one output step t; per kernel row
+// dy the A operand is the feature row 2t-2+dy of those clips, stored K-major with two zero columns in front (the
+// conv's own left padding), so that the 10-wide window of output column w starts at stored column 2w.  Output
+// columns are taken in pairs (w0 = 2g, w0+1): their windows cover stored columns 4g .. 4g+11, i.e. they start on a
+// 16-byte K chunk - the SAME small weight tile [16 window columns x (2 x 16 channels)] serves all nine pairs, only
+// the A descriptor's start moves (a Toeplitz matrix never materialised).  Rows outside the clip (top/bottom
+// padding) are simply not issued: a tile is one step, so they are the same for all its rows.
+//   warps 0..6  producers: feature row -> tf32 hi/lo K-major tiles (3 stages), arrive on fullA
+//   warp  7     issue warp: 54 tcgen05.mma (N = 32) per kernel row, commit -> empty[stage] / acc_done
+//   warps 0..3  epilogue: TMEM -> + bias -> ReLU -> conv output [clip][t][w*16 + c]
+constexpr int kC1Lbo = 144, kC1Sbo = 12 * kC1Lbo, kC1ATile = 16 * kC1Sbo;   // A: 128 rows x 48 stored columns
+constexpr int kC1Stages = 3, kC1WBytes = 10 * 2 * 2048;                     // weights: [dy][hi|lo][32 n x 16 k]
+constexpr int kC1Smem = kC1WBytes + kC1Stages * 2 * kC1ATile;
+struct Conv1TcParams {
+  const float* feats;   // [B][T][40]
+  const float* wimg;    // kC1WBytes
+  const float* bias;    // [16]
+  float* out;           // [B][H1][288]
+  long long B;
+  int T, H1;
+};
+__global__ void __launch_bounds__(256, 1) conv1_tc_kernel(const Conv1TcParams p) {
+  constexpr int F = 40, NC = 288;
+  extern __shared__ __align__(128) unsigned char smem[];
+  __shared__ __align__(8) unsigned long long s_bar[2 * kC1Stages + 3];   // fullA[3], empty[3], wfull, acc_done, acc_free
+  __shared__ uint32_t s_tmem;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, T = p.T, H1 = p.H1;
+  const uint32_t bar0 = smem_u32(&s_bar[0]);
+  auto fullA = [&](int s) { return bar0 + 8u * s; };
+  auto empty = [&](int s) { return bar0 + 8u * (kC1Stages + s); };
+  const uint32_t wfull = bar0 + 8u * (2 * kC1Stages), acc_done = wfull + 8u, acc_free = wfull + 16u;
+  unsigned char* s_a = smem + kC1WBytes;
+  if (tid == 0) {
+    for (int s = 0; s < kC1Stages; ++s) {
+      mbar_init(fullA(s), kDProd);
+      mbar_init(empty(s), 1);
+    }
+    mbar_init(wfull, 1);
+    mbar_init(acc_done, 1);
+    mbar_init(acc_free, 4);
+    fence_mbar_init();
+  }
+  // stored columns 0, 1 and 42..47 stay zero for the whole kernel (padding / K round-up)
+  for (int i = tid; i < kC1Stages * 2 * kC1ATile / 16; i += 256) reinterpret_cast<float4*>(s_a)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  fence_proxy_async();
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "n"(512));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = s_tmem;
+  const long long ngroups = (p.B + 127) / 128, ntiles = ngroups * H1;
+
+  if (warp == kDProd) {
+    // ============================ issue warp ============================
+    if (lane == 0) {
+      mbar_expect_tx(wfull, kC1WBytes);
+      tma_load_1d(smem_u32(smem), p.wimg, kC1WBytes, wfull);
+    }
+    __syncwarp();
+    mbar_wait(wfull, 0);
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((32u >> 3) << 17) | ((128u >> 4) << 24);
+    uint32_t cnt = 0, it = 0;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+      const int t = (int)(tile % H1);
+      const int dy_lo = 2 - 2 * t > 0 ? 2 - 2 * t : 0, dy_hi = T + 1 - 2 * t < 9 ? T + 1 - 2 * t : 9;
+      for (int dy = dy_lo; dy <= dy_hi; ++dy, ++cnt) {
+        const int s = cnt % kC1Stages;
+        mbar_wait(fullA(s), (cnt / kC1Stages) & 1);
+        if (dy == dy_lo && it > 0) mbar_wait(acc_free, (it - 1) & 1);
+        tc_fence_after();
+        const uint32_t a_hi = smem_u32(s_a) + (uint32_t)s * 2u * kC1ATile, a_lo = a_hi + kC1ATile;
+        const uint32_t b_hi = smem_u32(smem) + (uint32_t)dy * 4096u, b_lo = b_hi + 2048u;
+#pragma unroll 1
+        for (int g = 0; g < 9; ++g) {
+#pragma unroll
+          for (int term = 0; term < 3; ++term) {
+            const uint32_t ab = (term == 1 ? a_lo : a_hi) + (uint32_t)g * kC1Lbo, bb = term == 2 ? b_lo : b_hi;
+#pragma unroll
+            for (int kk = 0; kk < 2; ++kk)
+              tc_mma_tf32_elect(tmem + 32u * g, umma_desc(ab + kk * 2u * kC1Lbo, kC1Lbo, kC1Sbo), umma_desc(bb + kk * 256u, 128u, 512u),
+                                idesc, (dy > dy_lo || term > 0 || kk > 0) ? 1u : 0u);
+          }
+        }
+        tc_commit_elect(empty(s));
+        if (dy == dy_hi) tc_commit_elect(acc_done);
+      }
+    }
+  } else {
+    // ============================ producers (+ epilogue on warps 0..3) ============================
+    uint32_t cnt = 0, it = 0;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+      const int t = (int)(tile % H1);
+      const long long c0 = (tile / H1) * 128;
+      const int dy_lo = 2 - 2 * t > 0 ? 2 - 2 * t : 0, dy_hi = T + 1 - 2 * t < 9 ? T + 1 - 2 * t : 9;
+      for (int dy = dy_lo; dy <= dy_hi; ++dy, ++cnt) {
+        const int s = cnt % kC1Stages;
+        unsigned char* sa = s_a + (size_t)s * 2 * kC1ATile;
+        const int y = 2 * t - 2 + dy;
+        constexpr int kItems = 128 * (F / 4), kIt = (kItems + kDProd * 32 - 1) / (kDProd * 32);
+        float4 v[kIt];
+#pragma unroll
+        for (int u = 0; u < kIt; ++u) {
+          const int i = tid + u * kDProd * 32, r = i / (F / 4), c = i - r * (F / 4);
+          v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (i < kItems && c0 + r < p.B) v[u] = __ldg(reinterpret_cast<const float4*>(p.feats + ((c0 + r) * T + y) * F) + c);
+        }
+        if (cnt >= kC1Stages) mbar_wait(empty(s), (cnt / kC1Stages - 1) & 1);
+#pragma unroll
+        for (int u = 0; u < kIt; ++u) {
+          const int i = tid + u * kDProd * 32, r = i / (F / 4), c = i - r * (F / 4);
+          if (i < kItems) {
+            const float2 h0 = make_float2(to_tf32(v[u].x), to_tf32(v[u].y)), h1 = make_float2(to_tf32(v[u].z), to_tf32(v[u].w));
+            const float2 l0 = make_float2(to_tf32(v[u].x - h0.x), to_tf32(v[u].y - h0.y));
+            const float2 l1 = make_float2(to_tf32(v[u].z - h1.x), to_tf32(v[u].w - h1.y));
+            // feature columns 4c .. 4c+3 are stored columns 4c+2 .. 4c+5: the upper half of K chunk c, the lower of c+1
+            unsigned char* d = sa + (r >> 3) * kC1Sbo + c * kC1Lbo + (r & 7) * 16;
+            *reinterpret_cast<float2*>(d + 8) = h0;
+            *reinterpret_cast<float2*>(d + kC1Lbo) = h1;
+            *reinterpret_cast<float2*>(d + kC1ATile + 8) = l0;
+            *reinterpret_cast<float2*>(d + kC1ATile + kC1Lbo) = l1;
+          }
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(fullA(s));
+      }
+      if (warp < 4) {  // epilogue: lane = accumulator row = clip of the group
+        mbar_wait(acc_done, it & 1);
+        tc_fence_after();
+        const long long clip = c0 + warp * 32 + lane;
+        float* orow = p.out + (clip * H1 + t) * NC;
+        float bv[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) bv[j] = __ldg(p.bias + j);
+#pragma unroll 2
+        for (int w = 0; w < NC / 16; ++w) {
+          float q[16];
+          tc_ld16(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)(16 * w), q);
+          tc_wait_ld();
+          if (clip < p.B) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              *reinterpret_cast<float4*>(orow + 16 * w + 4 * j) =
+                  make_float4(fmaxf(q[4 * j] + bv[4 * j], 0.f), fmaxf(q[4 * j + 1] + bv[4 * j + 1], 0.f),
+                              fmaxf(q[4 * j + 2] + bv[4 * j + 2], 0.f), fmaxf(q[4 * j + 3] + bv[4 * j + 3], 0.f));
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(acc_free);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(512));
+}
+
 // Sequential half of one GRU layer.  xp [B, T, 3H] = W_ih x_t + b_ih (gate order r, z, n like torch).
 // CTA = kGruNB clips; W_hh [H][3H] and the hidden state (transposed, [H][NB], double-buffered) live in shared
 // memory.  Thread = (hidden unit j, group of 8 clips): per k it reads its three gate weights once and eight
@@ -598,7 +761,7 @@ static CrnnWeights* crnn_of(kws_handle_t h) { return reinterpret_cast<CrnnWeight
 
 static void crnn_free(CrnnWeights* m) {
   if (!m) return;
-  void* ptrs[] = {m->d_wimg[0], m->d_wimg[1], m->d_whimg[0], m->d_whimg[1], m->d_conv_w, m->d_conv_b, m->d_wih[0], m->d_wih[1], m->d_whh[0], m->d_whh[1], m->d_bih[0],
+  void* ptrs[] = {m->d_c1img, m->d_wimg[0], m->d_wimg[1], m->d_whimg[0], m->d_whimg[1], m->d_conv_w, m->d_conv_b, m->d_wih[0], m->d_wih[1], m->d_whh[0], m->d_whh[1], m->d_bih[0],
                   m->d_bih[1],  m->d_bhh[0], m->d_bhh[1], m->d_fc_w,   m->d_fc_b,   m->d_ws};
   for (void* p : ptrs)
     if (p) cudaFree(p);
@@ -706,6 +869,27 @@ int kws_crnn_finalize(kws_handle_t h) {
       for (int t = 0; t < 100; ++t) p[(size_t)t * Cc + c] = w[(size_t)c * 100 + t];
     if ((rc = up(&m.d_conv_w, p))) return rc;
     if ((rc = up(&m.d_conv_b, m.host[crnn_slot(m, "conv1.bias")]))) return rc;
+    if (Cc == 16 && W1 == 18) {
+      auto rn = [](float x) {  // cvt.rna.tf32.f32
+        uint32_t u;
+        memcpy(&u, &x, 4);
+        if ((u & 0x7f800000u) != 0x7f800000u) u = (u + 0x1000u) & ~0x1fffu;
+        memcpy(&x, &u, 4);
+        return x;
+      };
+      std::vector<float> img(kC1WBytes / 4, 0.f);
+      for (int dy = 0; dy < 10; ++dy)
+        for (int n = 0; n < 32; ++n)        // n = wl * 16 + c: the pair's second column sees the window two to the right
+          for (int j = 0; j < 16; ++j) {
+            const int wl = n >> 4, c = n & 15, dx = j - 2 * wl;
+            const float v = (dx >= 0 && dx < 10) ? w[(size_t)c * 100 + dy * 10 + dx] : 0.f;
+            const float hi = rn(v), lo = rn(v - hi);
+            const size_t off = ((size_t)(n >> 3) * 512 + (size_t)(j >> 2) * 128 + (size_t)(n & 7) * 16 + (size_t)(j & 3) * 4) / 4;
+            img[(size_t)dy * 1024 + off] = hi;
+            img[(size_t)dy * 1024 + 512 + off] = lo;
+          }
+      if ((rc = up(&m.d_c1img, img))) return rc;
+    }
   }
   for (int l = 0; l < m.layers; ++l) {
     const std::string s = "_l" + std::to_string(l);
@@ -804,8 +988,16 @@ int kws_crnn_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t 
     KWS_CUDA(cudaFuncSetAttribute(gru_recurrent_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gru_smem));
   for (int64_t b0 = 0; b0 < B; b0 += chunk) {
     const int64_t nb = (B - b0 < chunk) ? B - b0 : chunk;
-    int rc = launch_conv1_relu(h, feats_dev + b0 * T * F, d_conv, m.d_conv_w, m.d_conv_b, nb, (int)T, (int)F, H1, W1, Cc, st);
-    if (rc) return rc;
+    if (m.d_c1img && F == 40 && Cc == 16) {
+      Conv1TcParams cp{feats_dev + b0 * T * F, m.d_c1img, m.d_conv_b, d_conv, nb, (int)T, H1};
+      KWS_CUDA(cudaFuncSetAttribute(conv1_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kC1Smem));
+      const long long nt = (nb + 127) / 128 * H1;
+      conv1_tc_kernel<<<(unsigned)(nt < h->sm_count ? nt : h->sm_count), 256, kC1Smem, st>>>(cp);
+      KWS_CHECK_LAUNCH(h);
+    } else {
+      int rc = launch_conv1_relu(h, feats_dev + b0 * T * F, d_conv, m.d_conv_w, m.d_conv_b, nb, (int)T, (int)F, H1, W1, Cc, st);
+      if (rc) return rc;
+    }
     const float* x = d_conv;
     int I = I0;
     for (int l = 0; l < m.layers; ++l) {
