@@ -192,7 +192,7 @@ __global__ void __launch_bounds__(256, 1) dense_gemm_tf32x3_kernel(const DensePa
   extern __shared__ __align__(128) unsigned char smem[];
   __shared__ __align__(8) unsigned long long s_bar[8];   // fullA[2], fullB[2], empty[2], acc_done, acc_free
   __shared__ uint32_t s_tmem;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
   const int N = p.N, K = p.K, nch = K / kDK;
   const uint32_t btile = (uint32_t)(N / 8) * 1024u;            // one weight tile (hi or lo) of a chunk
   const uint32_t stage_bytes = 2u * kDATile + 2u * btile;
@@ -355,7 +355,7 @@ __global__ void __launch_bounds__(256, 1) conv1_tc_kernel(const Conv1TcParams p)
   extern __shared__ __align__(128) unsigned char smem[];
   __shared__ __align__(8) unsigned long long s_bar[2 * kC1Stages + 3];   // fullA[3], empty[3], wfull, acc_done, acc_free
   __shared__ uint32_t s_tmem;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, T = p.T, H1 = p.H1;
+  const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31, T = p.T, H1 = p.H1;
   const uint32_t bar0 = smem_u32(&s_bar[0]);
   auto fullA = [&](int s) { return bar0 + 8u * s; };
   auto empty = [&](int s) { return bar0 + 8u * (kC1Stages + s); };
@@ -576,7 +576,7 @@ __global__ void __launch_bounds__(288, 1) gru_recurrent_tc_kernel(const GruTcPar
   __shared__ __align__(8) unsigned long long s_bar[3];   // wfull, h_ready, acc_done
   __shared__ uint32_t s_tmem;
   __shared__ float s_b[N];
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, T = p.T;
+  const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31, T = p.T;
   const uint32_t bar0 = smem_u32(&s_bar[0]), wfull = bar0, h_ready = bar0 + 8u, acc_done = bar0 + 16u;
   unsigned char* s_a = smem + 4 * kGtBTile;
   if (tid == 0) {

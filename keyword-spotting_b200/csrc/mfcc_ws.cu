@@ -57,7 +57,7 @@ __global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastPar
   const float2* s_twp = reinterpret_cast<const float2*>(smem + p.off_twp);
   float* s_c0 = reinterpret_cast<float*>(smem + p.off_c0);  // [2][20]
 
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
   const bool do_dct = (p.mode == kModeMfcc);
   const uint32_t bar_full = smem_u32(&s_bar[0]), bar_empty = smem_u32(&s_bar[2]);
   const uint32_t bar_afull = smem_u32(&s_bar[4]), bar_mma = smem_u32(&s_bar[5]);

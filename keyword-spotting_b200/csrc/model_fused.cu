@@ -289,7 +289,7 @@ __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedPa
   float* s_pool = reinterpret_cast<float*>(smem + L::off_pool);  // [3][2][PACK][64]
   float* s_par = reinterpret_cast<float*>(smem + L::off_par);    // [4][64][12]
 
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
   const uint32_t barO = smem_u32(&s_bar[0]), barE = smem_u32(&s_bar[1]);
   const int T = p.T, H0 = p.H0, TF = T * F;
   const int feat_stride = (int)L::feat_floats(T);

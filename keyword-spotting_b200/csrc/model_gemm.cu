@@ -45,7 +45,7 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_gemm_kernel(const GemmParams p) 
   extern __shared__ __align__(128) unsigned char smem[];
   __shared__ __align__(8) unsigned long long s_bar[4];  // [0,1] MMAs of buffer retired, [2,3] weight chunk landed
   __shared__ uint32_t s_tmem;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
   const int bbytes = (p.npad / 8) * kGSbo;
   unsigned char* sA = smem;                      // [2][kGABytes]
   unsigned char* sB = smem + 2 * kGABytes;       // [2][bbytes]
