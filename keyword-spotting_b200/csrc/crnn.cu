@@ -185,6 +185,7 @@ struct DenseParams {
   float* C;
   long long M;
   int N, K;
+  int atile;   // 1 (needs T > 0): A is tile-major [tile][K][128 rows] as conv1_tc_kernel writes it
   int T;   // 0: rows as they lie, C row-major.  > 0: "step-major" tiles for the tensor-core recurrence: A rows are
            // (clip, step) pairs, tile = (group of 128 clips, step), C = [group][step][column][128 clips]
 };
@@ -257,70 +258,94 @@ __global__ void __launch_bounds__(256, 1) dense_gemm_tf32x3_kernel(const DensePa
     }
   } else {
     // ============================ producers (+ epilogue on warps 0..3) ============================
-    uint32_t cnt = 0, it = 0;
-    const int ptid = tid;                       // 0 .. 223
-    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
-      // row r of the tile is A row (m0 + r) * mstride + moff
-      const long long m0 = Tm > 0 ? (tile / Tm) * 128 : tile * 128;
+    // The loads of stage c+1 are issued before stage c is converted: two chunks per thread in flight, the global
+    // latency is hidden behind the conversion, the stage wait and (warps 0..3) the epilogue.
+    constexpr int kIt = (128 * (kDK / 4) + kDProd * 32 - 1) / (kDProd * 32);
+    auto load = [&](long long tile, int kc, float4 (&v)[kIt]) {
+      const long long m0 = Tm > 0 ? (tile / Tm) * 128 : tile * 128;      // row r of the tile is A row (m0 + r) * mstride + moff
       const long long mstride = Tm > 0 ? Tm : 1, moff = Tm > 0 ? tile % Tm : 0;
-      for (int kc = 0; kc < nch; ++kc, ++cnt) {
-        const int s = cnt & 1;
-        unsigned char* sa = smem + (size_t)s * stage_bytes;
-        // all of this thread's loads of the chunk go out first (and before the wait for the stage): the global
-        // latency is paid once per chunk, overlapped with the MMAs still reading the stage
-        constexpr int kIt = (128 * (kDK / 4) + kDProd * 32 - 1) / (kDProd * 32);
-        float4 v[kIt];
+      if (p.atile) {   // lanes = rows: four coalesced scalar loads per item
+        const float* at = p.A + ((size_t)tile * K + (size_t)kc * kDK) * 128;
 #pragma unroll
         for (int u = 0; u < kIt; ++u) {
-          const int i = ptid + u * kDProd * 32, r = i >> 3, c = i & 7;   // row of the tile, 16-byte K chunk
-          const long long m = m0 + r;
+          const int i = tid + u * kDProd * 32, r = i & 127, c = i >> 7;
           v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (i < 128 * (kDK / 4) && m < nrows)
-            v[u] = __ldg(reinterpret_cast<const float4*>(p.A + (m * mstride + moff) * K + kc * kDK) + c);
-        }
-        if (cnt >= 2) mbar_wait(empty(s), ((cnt - 2) >> 1) & 1);
-#pragma unroll
-        for (int u = 0; u < kIt; ++u) {
-          const int i = ptid + u * kDProd * 32, r = i >> 3, c = i & 7;
           if (i < 128 * (kDK / 4)) {
-            const float4 hi = make_float4(to_tf32(v[u].x), to_tf32(v[u].y), to_tf32(v[u].z), to_tf32(v[u].w));
-            const float4 lo = make_float4(to_tf32(v[u].x - hi.x), to_tf32(v[u].y - hi.y), to_tf32(v[u].z - hi.z),
-                                          to_tf32(v[u].w - hi.w));
-            const uint32_t off = (uint32_t)(r >> 3) * kDSboA + (uint32_t)c * kDLboA + (uint32_t)(r & 7) * 16u;
-            *reinterpret_cast<float4*>(sa + off) = hi;
-            *reinterpret_cast<float4*>(sa + kDATile + off) = lo;
+            const float* a = at + (size_t)(4 * c) * 128 + r;
+            v[u] = make_float4(__ldg(a), __ldg(a + 128), __ldg(a + 256), __ldg(a + 384));
           }
         }
-        fence_proxy_async();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(fullA(s));
+        return;
       }
-      if (warp < 4) {  // epilogue: lane = accumulator row
-        mbar_wait(acc_done, it & 1);
-        tc_fence_after();
-        const long long m = m0 + warp * 32 + lane;
-        float* crow = p.C + m * N;
-        float* ccol = p.C + tile * N * 128 + warp * 32 + lane;   // step-major: column pitch 128 floats, lanes contiguous
-        for (int c0 = 0; c0 < N; c0 += 16) {
-          float q[16];
-          tc_ld16(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, q);
-          tc_wait_ld();
-          if (Tm > 0) {
 #pragma unroll
-            for (int j = 0; j < 16; ++j) ccol[(size_t)(c0 + j) * 128] = q[j] + __ldg(p.bias + c0 + j);
-          } else if (m < nrows) {
+      for (int u = 0; u < kIt; ++u) {
+        const int i = tid + u * kDProd * 32, r = i >> 3, c = i & 7;   // row of the tile, 16-byte K chunk
+        const long long m = m0 + r;
+        v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (i < 128 * (kDK / 4) && m < nrows)
+          v[u] = __ldg(reinterpret_cast<const float4*>(p.A + (m * mstride + moff) * K + kc * kDK) + c);
+      }
+    };
+    uint32_t cnt = 0, it = 0;
+    long long tile = blockIdx.x;
+    int kc = 0;
+    float4 v[kIt], vn[kIt];
+    if (tile < ntiles) load(tile, 0, v);
+    while (tile < ntiles) {
+      long long ntile = tile;
+      int nkc = kc + 1;
+      if (nkc == nch) nkc = 0, ntile += gridDim.x;
+      if (ntile < ntiles) load(ntile, nkc, vn);
+      const int s = cnt & 1;
+      unsigned char* sa = smem + (size_t)s * stage_bytes;
+      if (cnt >= 2) mbar_wait(empty(s), ((cnt - 2) >> 1) & 1);
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const float4 bv = __ldg(reinterpret_cast<const float4*>(p.bias + c0) + j);
-              *reinterpret_cast<float4*>(crow + c0 + 4 * j) =
-                  make_float4(q[4 * j] + bv.x, q[4 * j + 1] + bv.y, q[4 * j + 2] + bv.z, q[4 * j + 3] + bv.w);
+      for (int u = 0; u < kIt; ++u) {
+        const int i = tid + u * kDProd * 32, r = p.atile ? (i & 127) : (i >> 3), c = p.atile ? (i >> 7) : (i & 7);
+        if (i < 128 * (kDK / 4)) {
+          const float4 hi = make_float4(to_tf32(v[u].x), to_tf32(v[u].y), to_tf32(v[u].z), to_tf32(v[u].w));
+          const float4 lo = make_float4(to_tf32(v[u].x - hi.x), to_tf32(v[u].y - hi.y), to_tf32(v[u].z - hi.z),
+                                        to_tf32(v[u].w - hi.w));
+          const uint32_t off = (uint32_t)(r >> 3) * kDSboA + (uint32_t)c * kDLboA + (uint32_t)(r & 7) * 16u;
+          *reinterpret_cast<float4*>(sa + off) = hi;
+          *reinterpret_cast<float4*>(sa + kDATile + off) = lo;
+        }
+      }
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(fullA(s));
+      if (kc == nch - 1) {
+        if (warp < 4) {  // epilogue: lane = accumulator row
+          mbar_wait(acc_done, it & 1);
+          tc_fence_after();
+          const long long m = (Tm > 0 ? (tile / Tm) * 128 : tile * 128) + warp * 32 + lane;
+          float* crow = p.C + m * N;
+          float* ccol = p.C + tile * N * 128 + warp * 32 + lane;   // step-major: column pitch 128 floats, lanes contiguous
+          for (int c0 = 0; c0 < N; c0 += 16) {
+            float q[16];
+            tc_ld16(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, q);
+            tc_wait_ld();
+            if (Tm > 0) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) ccol[(size_t)(c0 + j) * 128] = q[j] + __ldg(p.bias + c0 + j);
+            } else if (m < nrows) {
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const float4 bv = __ldg(reinterpret_cast<const float4*>(p.bias + c0) + j);
+                *reinterpret_cast<float4*>(crow + c0 + 4 * j) =
+                    make_float4(q[4 * j] + bv.x, q[4 * j + 1] + bv.y, q[4 * j + 2] + bv.z, q[4 * j + 3] + bv.w);
+              }
             }
           }
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(acc_free);
         }
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(acc_free);
+        ++it;
       }
+#pragma unroll
+      for (int u = 0; u < kIt; ++u) v[u] = vn[u];
+      tile = ntile, kc = nkc, ++cnt;
     }
   }
   tc_fence_before();
@@ -340,13 +365,13 @@ __global__ void __launch_bounds__(256, 1) dense_gemm_tf32x3_kernel(const DensePa
 //   warp  7     issue warp: 54 tcgen05.mma (N = 32) per kernel row, commit -> empty[stage] / acc_done
 //   warps 0..3  epilogue: TMEM -> + bias -> ReLU -> conv output [clip][t][w*16 + c]
 constexpr int kC1Lbo = 144, kC1Sbo = 12 * kC1Lbo, kC1ATile = 16 * kC1Sbo;   // A: 128 rows x 48 stored columns
-constexpr int kC1Stages = 3, kC1WBytes = 10 * 2 * 2048;                     // weights: [dy][hi|lo][32 n x 16 k]
+constexpr int kC1Stages = 2, kC1WBytes = 10 * 2 * 4096;                     // weights: [dy][hi|lo][64 n x 16 k]
 constexpr int kC1Smem = kC1WBytes + kC1Stages * 2 * kC1ATile;
 struct Conv1TcParams {
   const float* feats;   // [B][T][40]
   const float* wimg;    // kC1WBytes
   const float* bias;    // [16]
-  float* out;           // [B][H1][288]
+  float* out;           // [group * H1 + t][288][128 clips]  (tile-major: what dense_gemm_tf32x3_kernel reads with atile = 1)
   long long B;
   int T, H1;
 };
@@ -392,7 +417,7 @@ __global__ void __launch_bounds__(256, 1) conv1_tc_kernel(const Conv1TcParams p)
     }
     __syncwarp();
     mbar_wait(wfull, 0);
-    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((32u >> 3) << 17) | ((128u >> 4) << 24);
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((64u >> 3) << 17) | ((128u >> 4) << 24);
     uint32_t cnt = 0, it = 0;
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
       const int t = (int)(tile % H1);
@@ -403,15 +428,15 @@ __global__ void __launch_bounds__(256, 1) conv1_tc_kernel(const Conv1TcParams p)
         if (dy == dy_lo && it > 0) mbar_wait(acc_free, (it - 1) & 1);
         tc_fence_after();
         const uint32_t a_hi = smem_u32(s_a) + (uint32_t)s * 2u * kC1ATile, a_lo = a_hi + kC1ATile;
-        const uint32_t b_hi = smem_u32(smem) + (uint32_t)dy * 4096u, b_lo = b_hi + 2048u;
-#pragma unroll 1
-        for (int g = 0; g < 9; ++g) {
+        const uint32_t b_hi = smem_u32(smem) + (uint32_t)dy * 8192u, b_lo = b_hi + 4096u;
+#pragma unroll
+        for (int g = 0; g < 5; ++g) {
 #pragma unroll
           for (int term = 0; term < 3; ++term) {
-            const uint32_t ab = (term == 1 ? a_lo : a_hi) + (uint32_t)g * kC1Lbo, bb = term == 2 ? b_lo : b_hi;
+            const uint32_t ab = (term == 1 ? a_lo : a_hi) + (uint32_t)g * 2u * kC1Lbo, bb = term == 2 ? b_lo : b_hi;
 #pragma unroll
             for (int kk = 0; kk < 2; ++kk)
-              tc_mma_tf32_elect(tmem + 32u * g, umma_desc(ab + kk * 2u * kC1Lbo, kC1Lbo, kC1Sbo), umma_desc(bb + kk * 256u, 128u, 512u),
+              tc_mma_tf32_elect(tmem + 64u * g, umma_desc(ab + kk * 2u * kC1Lbo, kC1Lbo, kC1Sbo), umma_desc(bb + kk * 256u, 128u, 512u),
                                 idesc, (dy > dy_lo || term > 0 || kk > 0) ? 1u : 0u);
           }
         }
@@ -421,68 +446,82 @@ __global__ void __launch_bounds__(256, 1) conv1_tc_kernel(const Conv1TcParams p)
     }
   } else {
     // ============================ producers (+ epilogue on warps 0..3) ============================
-    uint32_t cnt = 0, it = 0;
-    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
-      const int t = (int)(tile % H1);
+    // Stages are (tile, kernel row) pairs walked in one flat sequence; the loads of the next stage are issued
+    // before the current one is converted (two feature rows per thread in flight, also across tile boundaries).
+    constexpr int kItems = 128 * (F / 4), kIt = (kItems + kDProd * 32 - 1) / (kDProd * 32);
+    auto dy_first = [&](long long tile) { const int t = (int)(tile % H1); return 2 - 2 * t > 0 ? 2 - 2 * t : 0; };
+    auto dy_last = [&](long long tile) { const int t = (int)(tile % H1); return T + 1 - 2 * t < 9 ? T + 1 - 2 * t : 9; };
+    auto load = [&](long long tile, int dy, float4 (&v)[kIt]) {
       const long long c0 = (tile / H1) * 128;
-      const int dy_lo = 2 - 2 * t > 0 ? 2 - 2 * t : 0, dy_hi = T + 1 - 2 * t < 9 ? T + 1 - 2 * t : 9;
-      for (int dy = dy_lo; dy <= dy_hi; ++dy, ++cnt) {
-        const int s = cnt % kC1Stages;
-        unsigned char* sa = s_a + (size_t)s * 2 * kC1ATile;
-        const int y = 2 * t - 2 + dy;
-        constexpr int kItems = 128 * (F / 4), kIt = (kItems + kDProd * 32 - 1) / (kDProd * 32);
-        float4 v[kIt];
+      const int y = 2 * (int)(tile % H1) - 2 + dy;
 #pragma unroll
-        for (int u = 0; u < kIt; ++u) {
-          const int i = tid + u * kDProd * 32, r = i / (F / 4), c = i - r * (F / 4);
-          v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (i < kItems && c0 + r < p.B) v[u] = __ldg(reinterpret_cast<const float4*>(p.feats + ((c0 + r) * T + y) * F) + c);
-        }
-        if (cnt >= kC1Stages) mbar_wait(empty(s), (cnt / kC1Stages - 1) & 1);
-#pragma unroll
-        for (int u = 0; u < kIt; ++u) {
-          const int i = tid + u * kDProd * 32, r = i / (F / 4), c = i - r * (F / 4);
-          if (i < kItems) {
-            const float2 h0 = make_float2(to_tf32(v[u].x), to_tf32(v[u].y)), h1 = make_float2(to_tf32(v[u].z), to_tf32(v[u].w));
-            const float2 l0 = make_float2(to_tf32(v[u].x - h0.x), to_tf32(v[u].y - h0.y));
-            const float2 l1 = make_float2(to_tf32(v[u].z - h1.x), to_tf32(v[u].w - h1.y));
-            // feature columns 4c .. 4c+3 are stored columns 4c+2 .. 4c+5: the upper half of K chunk c, the lower of c+1
-            unsigned char* d = sa + (r >> 3) * kC1Sbo + c * kC1Lbo + (r & 7) * 16;
-            *reinterpret_cast<float2*>(d + 8) = h0;
-            *reinterpret_cast<float2*>(d + kC1Lbo) = h1;
-            *reinterpret_cast<float2*>(d + kC1ATile + 8) = l0;
-            *reinterpret_cast<float2*>(d + kC1ATile + kC1Lbo) = l1;
-          }
-        }
-        fence_proxy_async();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(fullA(s));
+      for (int u = 0; u < kIt; ++u) {
+        const int i = tid + u * kDProd * 32, r = i / (F / 4), c = i - r * (F / 4);
+        v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (i < kItems && c0 + r < p.B) v[u] = __ldg(reinterpret_cast<const float4*>(p.feats + ((c0 + r) * T + y) * F) + c);
       }
-      if (warp < 4) {  // epilogue: lane = accumulator row = clip of the group
-        mbar_wait(acc_done, it & 1);
-        tc_fence_after();
-        const long long clip = c0 + warp * 32 + lane;
-        float* orow = p.out + (clip * H1 + t) * NC;
-        float bv[16];
+    };
+    uint32_t cnt = 0, it = 0;
+    long long tile = blockIdx.x;
+    int dy = tile < ntiles ? dy_first(tile) : 0;
+    float4 v[kIt], vn[kIt];
+    if (tile < ntiles) load(tile, dy, v);
+    while (tile < ntiles) {
+      const bool last = dy == dy_last(tile);
+      long long ntile = tile;
+      int ndy = dy + 1;
+      if (last) {
+        ntile += gridDim.x;
+        ndy = ntile < ntiles ? dy_first(ntile) : 0;
+      }
+      if (ntile < ntiles) load(ntile, ndy, vn);
+      const int s = cnt % kC1Stages;
+      unsigned char* sa = s_a + (size_t)s * 2 * kC1ATile;
+      if (cnt >= kC1Stages) mbar_wait(empty(s), (cnt / kC1Stages - 1) & 1);
 #pragma unroll
-        for (int j = 0; j < 16; ++j) bv[j] = __ldg(p.bias + j);
+      for (int u = 0; u < kIt; ++u) {
+        const int i = tid + u * kDProd * 32, r = i / (F / 4), c = i - r * (F / 4);
+        if (i < kItems) {
+          const float2 h0 = make_float2(to_tf32(v[u].x), to_tf32(v[u].y)), h1 = make_float2(to_tf32(v[u].z), to_tf32(v[u].w));
+          const float2 l0 = make_float2(to_tf32(v[u].x - h0.x), to_tf32(v[u].y - h0.y));
+          const float2 l1 = make_float2(to_tf32(v[u].z - h1.x), to_tf32(v[u].w - h1.y));
+          // feature columns 4c .. 4c+3 are stored columns 4c+2 .. 4c+5: the upper half of K chunk c, the lower of c+1
+          unsigned char* d = sa + (r >> 3) * kC1Sbo + c * kC1Lbo + (r & 7) * 16;
+          *reinterpret_cast<float2*>(d + 8) = h0;
+          *reinterpret_cast<float2*>(d + kC1Lbo) = h1;
+          *reinterpret_cast<float2*>(d + kC1ATile + 8) = l0;
+          *reinterpret_cast<float2*>(d + kC1ATile + kC1Lbo) = l1;
+        }
+      }
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(fullA(s));
+      if (last) {
+        if (warp < 4) {  // epilogue: lane = accumulator row = clip of the group
+          mbar_wait(acc_done, it & 1);
+          tc_fence_after();
+          // tile-major output [tile][w*16 + c][128 clips]: lanes = clips, every store a full 128-byte line
+          float* ocol = p.out + (size_t)tile * NC * 128 + warp * 32 + lane;
+          float bv[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) bv[j] = __ldg(p.bias + j);
 #pragma unroll 2
-        for (int w = 0; w < NC / 16; ++w) {
-          float q[16];
-          tc_ld16(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)(16 * w), q);
-          tc_wait_ld();
-          if (clip < p.B) {
+          for (int w = 0; w < NC / 16; ++w) {
+            float q[16];
+            tc_ld16(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)(16 * w), q);
+            tc_wait_ld();
 #pragma unroll
-            for (int j = 0; j < 4; ++j)
-              *reinterpret_cast<float4*>(orow + 16 * w + 4 * j) =
-                  make_float4(fmaxf(q[4 * j] + bv[4 * j], 0.f), fmaxf(q[4 * j + 1] + bv[4 * j + 1], 0.f),
-                              fmaxf(q[4 * j + 2] + bv[4 * j + 2], 0.f), fmaxf(q[4 * j + 3] + bv[4 * j + 3], 0.f));
+            for (int j = 0; j < 16; ++j) ocol[(size_t)(16 * w + j) * 128] = fmaxf(q[j] + bv[j], 0.f);
           }
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(acc_free);
         }
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(acc_free);
+        ++it;
       }
+#pragma unroll
+      for (int u = 0; u < kIt; ++u) v[u] = vn[u];
+      tile = ntile, dy = ndy, ++cnt;
     }
   }
   tc_fence_before();
@@ -879,14 +918,14 @@ int kws_crnn_finalize(kws_handle_t h) {
       };
       std::vector<float> img(kC1WBytes / 4, 0.f);
       for (int dy = 0; dy < 10; ++dy)
-        for (int n = 0; n < 32; ++n)        // n = wl * 16 + c: the pair's second column sees the window two to the right
+        for (int n = 0; n < 64; ++n)        // n = wl * 16 + c: column wl of the group sees the window 2 * wl to the right
           for (int j = 0; j < 16; ++j) {
             const int wl = n >> 4, c = n & 15, dx = j - 2 * wl;
             const float v = (dx >= 0 && dx < 10) ? w[(size_t)c * 100 + dy * 10 + dx] : 0.f;
             const float hi = rn(v), lo = rn(v - hi);
             const size_t off = ((size_t)(n >> 3) * 512 + (size_t)(j >> 2) * 128 + (size_t)(n & 7) * 16 + (size_t)(j & 3) * 4) / 4;
-            img[(size_t)dy * 1024 + off] = hi;
-            img[(size_t)dy * 1024 + 512 + off] = lo;
+            img[(size_t)dy * 2048 + off] = hi;
+            img[(size_t)dy * 2048 + 1024 + off] = lo;
           }
       if ((rc = up(&m.d_c1img, img))) return rc;
     }
@@ -968,7 +1007,7 @@ int kws_crnn_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t 
   // workspace per chunk: conv output [chunk, H1, I0], projections [chunk, H1, 3H], hidden sequence, last state
   size_t need = 0;
   auto take = [&](size_t floats) { size_t o = need; need += (floats * 4 + 255) & ~(size_t)255; return o; };
-  const size_t o_conv = take((size_t)chunk * H1 * I0), o_xp = take((size_t)((chunk + 127) / 128 * 128) * H1 * 3 * H),
+  const size_t o_conv = take((size_t)((chunk + 127) / 128 * 128) * H1 * I0), o_xp = take((size_t)((chunk + 127) / 128 * 128) * H1 * 3 * H),
                o_seq = take((size_t)chunk * H1 * H), o_last = take((size_t)chunk * H);
   if (need > m.ws_bytes) {
     if (m.d_ws) KWS_CUDA(cudaFree(m.d_ws));
@@ -988,7 +1027,9 @@ int kws_crnn_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t 
     KWS_CUDA(cudaFuncSetAttribute(gru_recurrent_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gru_smem));
   for (int64_t b0 = 0; b0 < B; b0 += chunk) {
     const int64_t nb = (B - b0 < chunk) ? B - b0 : chunk;
-    if (m.d_c1img && F == 40 && Cc == 16) {
+    // tensor-core conv1 writes tile-major, which only the step-major tensor-core projection reads
+    const bool conv_tc = m.d_c1img && F == 40 && Cc == 16 && H == 64 && m.d_wimg[0] && m.d_whimg[0];
+    if (conv_tc) {
       Conv1TcParams cp{feats_dev + b0 * T * F, m.d_c1img, m.d_conv_b, d_conv, nb, (int)T, H1};
       KWS_CUDA(cudaFuncSetAttribute(conv1_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kC1Smem));
       const long long nt = (nb + 127) / 128 * H1;
@@ -1005,7 +1046,7 @@ int kws_crnn_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t 
       const size_t dsmem = 2 * (2 * (size_t)kDATile + 2 * (size_t)(3 * H / 8) * 1024);
       const bool tc_rec = H == 64 && m.d_wimg[l] && m.d_whimg[l];   // both halves of the layer on the tensor core
       if (m.d_wimg[l] && dsmem <= 227 * 1024) {
-        DenseParams dp{x, m.d_wimg[l], m.d_bih[l], d_xp, M, 3 * H, I, tc_rec ? H1 : 0};
+        DenseParams dp{x, m.d_wimg[l], m.d_bih[l], d_xp, M, 3 * H, I, (l == 0 && conv_tc) ? 1 : 0, tc_rec ? H1 : 0};
         KWS_CUDA(cudaFuncSetAttribute(dense_gemm_tf32x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dsmem));
         const long long nt = tc_rec ? (nb + 127) / 128 * H1 : (M + 127) / 128;
         dense_gemm_tf32x3_kernel<<<(unsigned)(nt < h->sm_count ? nt : h->sm_count), 256, dsmem, st>>>(dp);
