@@ -176,8 +176,22 @@ __global__ void __launch_bounds__(256) gru_inproj_tiled_kernel(const float* __re
 //               tcgen05.commit -> empty[stage] (and -> acc_done after the last chunk of a tile)
 //   warps 0..3  epilogue: TMEM -> registers -> + bias -> global, then arrive on acc_free so that the next tile's
 //               first MMA may overwrite the accumulator; warps 4..6 already produce the next tile meanwhile.
+
+// Loads the compiler may not sink below a later asm volatile (the stage waits): the next stage's data is
+// requested BEFORE the current stage is converted.
+__device__ __forceinline__ float4 ldg_early4(const float4* ptr) {
+  float4 v;
+  asm volatile("ld.global.nc.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(ptr));
+  return v;
+}
+__device__ __forceinline__ float ldg_early(const float* ptr) {
+  float v;
+  asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(v) : "l"(ptr));
+  return v;
+}
 constexpr int kDK = 32, kDLboA = 144, kDSboA = (kDK / 4) * kDLboA, kDATile = 16 * kDSboA;   // A: 128 rows x 32 K
 constexpr int kDProd = 7;                                                                    // producer warps
+constexpr int kDBStages = 3;                                                                 // weight-tile ring of the projection
 struct DenseParams {
   const float* A;
   const float* wimg;   // [K/32][2][N/8 * 1024 B]
@@ -191,22 +205,27 @@ struct DenseParams {
 };
 __global__ void __launch_bounds__(256, 1) dense_gemm_tf32x3_kernel(const DenseParams p) {
   extern __shared__ __align__(128) unsigned char smem[];
-  __shared__ __align__(8) unsigned long long s_bar[8];   // fullA[2], fullB[2], empty[2], acc_done, acc_free
+  __shared__ __align__(8) unsigned long long s_bar[12];   // fullA[2], empty[2], fullB[3], emptyB[3], acc_done, acc_free
   __shared__ uint32_t s_tmem;
   const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
   const int N = p.N, K = p.K, nch = K / kDK;
   const uint32_t btile = (uint32_t)(N / 8) * 1024u;            // one weight tile (hi or lo) of a chunk
-  const uint32_t stage_bytes = 2u * kDATile + 2u * btile;
+  // shared memory: two A stages (hi|lo tiles written by the producers), then kDBStages weight stages (TMA)
+  const uint32_t boff = 2u * 2u * kDATile;
   const uint32_t bar0 = smem_u32(&s_bar[0]);
   auto fullA = [&](int s) { return bar0 + 8u * s; };
-  auto fullB = [&](int s) { return bar0 + 16u + 8u * s; };
-  auto empty = [&](int s) { return bar0 + 32u + 8u * s; };
-  const uint32_t acc_done = bar0 + 48u, acc_free = bar0 + 56u;
+  auto empty = [&](int s) { return bar0 + 16u + 8u * s; };
+  auto fullB = [&](int s) { return bar0 + 32u + 8u * s; };
+  auto emptyB = [&](int s) { return bar0 + 56u + 8u * s; };
+  const uint32_t acc_done = bar0 + 80u, acc_free = bar0 + 88u;
   if (tid == 0) {
     for (int s = 0; s < 2; ++s) {
       mbar_init(fullA(s), kDProd);
-      mbar_init(fullB(s), 1);
       mbar_init(empty(s), 1);
+    }
+    for (int s = 0; s < kDBStages; ++s) {
+      mbar_init(fullB(s), 1);
+      mbar_init(emptyB(s), 1);
     }
     mbar_init(acc_done, 1);
     mbar_init(acc_free, 4);
@@ -227,23 +246,32 @@ __global__ void __launch_bounds__(256, 1) dense_gemm_tf32x3_kernel(const DensePa
 
   if (warp == kDProd) {
     // ============================ issue warp ============================
+    // The weight tiles run kDBStages - 1 chunks ahead of the MMAs in their own ring: a stage is refilled as soon as
+    // the chunk before the current one has retired, so the copy has two chunks of MMA time to land.
+    const long long mine = blockIdx.x < ntiles ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    const uint32_t total = (uint32_t)(mine * nch);
+    auto fetchB = [&](uint32_t c) {   // chunk c of this CTA's flat sequence
+      const int sb = c % kDBStages;
+      if (c >= (uint32_t)kDBStages) mbar_wait(emptyB(sb), (c / kDBStages - 1) & 1);
+      if (lane == 0) {
+        mbar_expect_tx(fullB(sb), 2u * btile);
+        tma_load_1d(smem_u32(smem) + boff + (uint32_t)sb * 2u * btile,
+                    reinterpret_cast<const unsigned char*>(p.wimg) + (size_t)(c % nch) * 2u * btile, 2u * btile, fullB(sb));
+      }
+      __syncwarp();
+    };
+    for (uint32_t c = 0; c < (uint32_t)(kDBStages - 1) && c < total; ++c) fetchB(c);
     uint32_t cnt = 0, it = 0;
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
       for (int kc = 0; kc < nch; ++kc, ++cnt) {
-        const int s = cnt & 1;
-        const uint32_t sb = smem_u32(smem) + (uint32_t)s * stage_bytes;
-        if (cnt >= 2) mbar_wait(empty(s), ((cnt - 2) >> 1) & 1);     // the MMAs that read this stage have retired
-        if (lane == 0) {
-          mbar_expect_tx(fullB(s), 2u * btile);
-          tma_load_1d(sb + 2u * kDATile, reinterpret_cast<const unsigned char*>(p.wimg) + (size_t)kc * 2u * btile, 2u * btile,
-                      fullB(s));
-        }
-        __syncwarp();
+        const int s = cnt & 1, sb = cnt % kDBStages;
+        if (cnt + kDBStages - 1 < total) fetchB(cnt + kDBStages - 1);
+        const uint32_t sa = smem_u32(smem) + (uint32_t)s * 2u * kDATile;
         mbar_wait(fullA(s), (cnt >> 1) & 1);
-        mbar_wait(fullB(s), (cnt >> 1) & 1);
+        mbar_wait(fullB(sb), (cnt / kDBStages) & 1);
         if (kc == 0 && it > 0) mbar_wait(acc_free, (it - 1) & 1);    // the previous tile's epilogue has read TMEM
         tc_fence_after();
-        const uint32_t a_hi = sb, a_lo = sb + kDATile, b_hi = sb + 2u * kDATile, b_lo = b_hi + btile;
+        const uint32_t a_hi = sa, a_lo = sa + kDATile, b_hi = smem_u32(smem) + boff + (uint32_t)sb * 2u * btile, b_lo = b_hi + btile;
 #pragma unroll
         for (int term = 0; term < 3; ++term) {
           const uint32_t ab = term == 1 ? a_lo : a_hi, bb = term == 2 ? b_lo : b_hi;
@@ -253,6 +281,7 @@ __global__ void __launch_bounds__(256, 1) dense_gemm_tf32x3_kernel(const DensePa
                               idesc, (kc > 0 || term > 0 || ks > 0) ? 1u : 0u);
         }
         tc_commit_elect(empty(s));
+        tc_commit_elect(emptyB(sb));
         if (kc == nch - 1) tc_commit_elect(acc_done);
       }
     }
@@ -272,7 +301,7 @@ __global__ void __launch_bounds__(256, 1) dense_gemm_tf32x3_kernel(const DensePa
           v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
           if (i < 128 * (kDK / 4)) {
             const float* a = at + (size_t)(4 * c) * 128 + r;
-            v[u] = make_float4(__ldg(a), __ldg(a + 128), __ldg(a + 256), __ldg(a + 384));
+            v[u] = make_float4(ldg_early(a), ldg_early(a + 128), ldg_early(a + 256), ldg_early(a + 384));
           }
         }
         return;
@@ -283,7 +312,7 @@ __global__ void __launch_bounds__(256, 1) dense_gemm_tf32x3_kernel(const DensePa
         const long long m = m0 + r;
         v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (i < 128 * (kDK / 4) && m < nrows)
-          v[u] = __ldg(reinterpret_cast<const float4*>(p.A + (m * mstride + moff) * K + kc * kDK) + c);
+          v[u] = ldg_early4(reinterpret_cast<const float4*>(p.A + (m * mstride + moff) * K + kc * kDK) + c);
       }
     };
     uint32_t cnt = 0, it = 0;
@@ -297,7 +326,7 @@ __global__ void __launch_bounds__(256, 1) dense_gemm_tf32x3_kernel(const DensePa
       if (nkc == nch) nkc = 0, ntile += gridDim.x;
       if (ntile < ntiles) load(ntile, nkc, vn);
       const int s = cnt & 1;
-      unsigned char* sa = smem + (size_t)s * stage_bytes;
+      unsigned char* sa = smem + (size_t)s * 2 * kDATile;
       if (cnt >= 2) mbar_wait(empty(s), ((cnt - 2) >> 1) & 1);
 #pragma unroll
       for (int u = 0; u < kIt; ++u) {
@@ -361,12 +390,13 @@ __global__ void __launch_bounds__(256, 1) dense_gemm_tf32x3_kernel(const DensePa
 // 16-byte K chunk - the SAME small weight tile [16 window columns x (2 x 16 channels)] serves all nine pairs, only
 // the A descriptor's start moves (a Toeplitz matrix never materialised).  Rows outside the clip (top/bottom
 // padding) are simply not issued: a tile is one step, so they are the same for all its rows.
-//   warps 0..6  producers: feature row -> tf32 hi/lo K-major tiles (3 stages), arrive on fullA
-//   warp  7     issue warp: 54 tcgen05.mma (N = 32) per kernel row, commit -> empty[stage] / acc_done
+//   warps 0..14 producers: feature row -> tf32 hi/lo K-major tiles (2 stages), arrive on fullA
+//   warp  15    issue warp: 30 tcgen05.mma (N = 64) per kernel row, commit -> empty[stage] / acc_done
 //   warps 0..3  epilogue: TMEM -> + bias -> ReLU -> conv output [clip][t][w*16 + c]
 constexpr int kC1Lbo = 144, kC1Sbo = 12 * kC1Lbo, kC1ATile = 16 * kC1Sbo;   // A: 128 rows x 48 stored columns
 constexpr int kC1Stages = 2, kC1WBytes = 10 * 2 * 4096;                     // weights: [dy][hi|lo][64 n x 16 k]
 constexpr int kC1Smem = kC1WBytes + kC1Stages * 2 * kC1ATile;
+constexpr int kC1Prod = 15, kC1Threads = (kC1Prod + 1) * 32;              // producer warps + the issue warp
 struct Conv1TcParams {
   const float* feats;   // [B][T][40]
   const float* wimg;    // kC1WBytes
@@ -375,7 +405,7 @@ struct Conv1TcParams {
   long long B;
   int T, H1;
 };
-__global__ void __launch_bounds__(256, 1) conv1_tc_kernel(const Conv1TcParams p) {
+__global__ void __launch_bounds__(kC1Threads, 1) conv1_tc_kernel(const Conv1TcParams p) {
   constexpr int F = 40, NC = 288;
   extern __shared__ __align__(128) unsigned char smem[];
   __shared__ __align__(8) unsigned long long s_bar[2 * kC1Stages + 3];   // fullA[3], empty[3], wfull, acc_done, acc_free
@@ -388,7 +418,7 @@ __global__ void __launch_bounds__(256, 1) conv1_tc_kernel(const Conv1TcParams p)
   unsigned char* s_a = smem + kC1WBytes;
   if (tid == 0) {
     for (int s = 0; s < kC1Stages; ++s) {
-      mbar_init(fullA(s), kDProd);
+      mbar_init(fullA(s), kC1Prod);
       mbar_init(empty(s), 1);
     }
     mbar_init(wfull, 1);
@@ -397,7 +427,7 @@ __global__ void __launch_bounds__(256, 1) conv1_tc_kernel(const Conv1TcParams p)
     fence_mbar_init();
   }
   // stored columns 0, 1 and 42..47 stay zero for the whole kernel (padding / K round-up)
-  for (int i = tid; i < kC1Stages * 2 * kC1ATile / 16; i += 256) reinterpret_cast<float4*>(s_a)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int i = tid; i < kC1Stages * 2 * kC1ATile / 16; i += kC1Threads) reinterpret_cast<float4*>(s_a)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   fence_proxy_async();
   if (warp == 0) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "n"(512));
@@ -409,7 +439,7 @@ __global__ void __launch_bounds__(256, 1) conv1_tc_kernel(const Conv1TcParams p)
   const uint32_t tmem = s_tmem;
   const long long ngroups = (p.B + 127) / 128, ntiles = ngroups * H1;
 
-  if (warp == kDProd) {
+  if (warp == kC1Prod) {
     // ============================ issue warp ============================
     if (lane == 0) {
       mbar_expect_tx(wfull, kC1WBytes);
@@ -446,9 +476,9 @@ __global__ void __launch_bounds__(256, 1) conv1_tc_kernel(const Conv1TcParams p)
     }
   } else {
     // ============================ producers (+ epilogue on warps 0..3) ============================
-    // Stages are (tile, kernel row) pairs walked in one flat sequence; the loads of the next stage are issued
-    // before the current one is converted (two feature rows per thread in flight, also across tile boundaries).
-    constexpr int kItems = 128 * (F / 4), kIt = (kItems + kDProd * 32 - 1) / (kDProd * 32);
+    // Stages are (tile, kernel row) pairs walked in one flat sequence; a stage's loads are issued before the wait
+    // for its shared-memory slot.  15 producer warps: the conversion is issue-latency bound with fewer.
+    constexpr int kItems = 128 * (F / 4), kIt = (kItems + kC1Prod * 32 - 1) / (kC1Prod * 32);
     auto dy_first = [&](long long tile) { const int t = (int)(tile % H1); return 2 - 2 * t > 0 ? 2 - 2 * t : 0; };
     auto dy_last = [&](long long tile) { const int t = (int)(tile % H1); return T + 1 - 2 * t < 9 ? T + 1 - 2 * t : 9; };
     auto load = [&](long long tile, int dy, float4 (&v)[kIt]) {
@@ -456,17 +486,17 @@ __global__ void __launch_bounds__(256, 1) conv1_tc_kernel(const Conv1TcParams p)
       const int y = 2 * (int)(tile % H1) - 2 + dy;
 #pragma unroll
       for (int u = 0; u < kIt; ++u) {
-        const int i = tid + u * kDProd * 32, r = i / (F / 4), c = i - r * (F / 4);
+        const int i = tid + u * kC1Prod * 32, r = i / (F / 4), c = i - r * (F / 4);
         v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (i < kItems && c0 + r < p.B) v[u] = __ldg(reinterpret_cast<const float4*>(p.feats + ((c0 + r) * T + y) * F) + c);
+        if (i < kItems && c0 + r < p.B) v[u] = ldg_early4(reinterpret_cast<const float4*>(p.feats + ((c0 + r) * T + y) * F) + c);
       }
     };
     uint32_t cnt = 0, it = 0;
     long long tile = blockIdx.x;
     int dy = tile < ntiles ? dy_first(tile) : 0;
-    float4 v[kIt], vn[kIt];
-    if (tile < ntiles) load(tile, dy, v);
+    float4 v[kIt];
     while (tile < ntiles) {
+      load(tile, dy, v);
       const bool last = dy == dy_last(tile);
       long long ntile = tile;
       int ndy = dy + 1;
@@ -474,13 +504,12 @@ __global__ void __launch_bounds__(256, 1) conv1_tc_kernel(const Conv1TcParams p)
         ntile += gridDim.x;
         ndy = ntile < ntiles ? dy_first(ntile) : 0;
       }
-      if (ntile < ntiles) load(ntile, ndy, vn);
       const int s = cnt % kC1Stages;
       unsigned char* sa = s_a + (size_t)s * 2 * kC1ATile;
       if (cnt >= kC1Stages) mbar_wait(empty(s), (cnt / kC1Stages - 1) & 1);
 #pragma unroll
       for (int u = 0; u < kIt; ++u) {
-        const int i = tid + u * kDProd * 32, r = i / (F / 4), c = i - r * (F / 4);
+        const int i = tid + u * kC1Prod * 32, r = i / (F / 4), c = i - r * (F / 4);
         if (i < kItems) {
           const float2 h0 = make_float2(to_tf32(v[u].x), to_tf32(v[u].y)), h1 = make_float2(to_tf32(v[u].z), to_tf32(v[u].w));
           const float2 l0 = make_float2(to_tf32(v[u].x - h0.x), to_tf32(v[u].y - h0.y));
@@ -519,8 +548,6 @@ __global__ void __launch_bounds__(256, 1) conv1_tc_kernel(const Conv1TcParams p)
         }
         ++it;
       }
-#pragma unroll
-      for (int u = 0; u < kIt; ++u) v[u] = vn[u];
       tile = ntile, dy = ndy, ++cnt;
     }
   }
@@ -1033,7 +1060,7 @@ int kws_crnn_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t 
       Conv1TcParams cp{feats_dev + b0 * T * F, m.d_c1img, m.d_conv_b, d_conv, nb, (int)T, H1};
       KWS_CUDA(cudaFuncSetAttribute(conv1_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kC1Smem));
       const long long nt = (nb + 127) / 128 * H1;
-      conv1_tc_kernel<<<(unsigned)(nt < h->sm_count ? nt : h->sm_count), 256, kC1Smem, st>>>(cp);
+      conv1_tc_kernel<<<(unsigned)(nt < h->sm_count ? nt : h->sm_count), kC1Threads, kC1Smem, st>>>(cp);
       KWS_CHECK_LAUNCH(h);
     } else {
       int rc = launch_conv1_relu(h, feats_dev + b0 * T * F, d_conv, m.d_conv_w, m.d_conv_b, nb, (int)T, (int)F, H1, W1, Cc, st);
@@ -1043,7 +1070,7 @@ int kws_crnn_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t 
     int I = I0;
     for (int l = 0; l < m.layers; ++l) {
       const long long M = nb * H1;
-      const size_t dsmem = 2 * (2 * (size_t)kDATile + 2 * (size_t)(3 * H / 8) * 1024);
+      const size_t dsmem = 2 * 2 * (size_t)kDATile + kDBStages * 2 * (size_t)(3 * H / 8) * 1024;
       const bool tc_rec = H == 64 && m.d_wimg[l] && m.d_whimg[l];   // both halves of the layer on the tensor core
       if (m.d_wimg[l] && dsmem <= 227 * 1024) {
         DenseParams dp{x, m.d_wimg[l], m.d_bih[l], d_xp, M, 3 * H, I, (l == 0 && conv_tc) ? 1 : 0, tc_rec ? H1 : 0};
