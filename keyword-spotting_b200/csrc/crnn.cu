@@ -169,9 +169,9 @@ __global__ void __launch_bounds__(256) gru_inproj_tiled_kernel(const float* __re
 // Both operands are K-major as they lie in memory (activations [row][feature], weights [gate][feature]), so no
 // transposition is needed.  Persistent CTAs, tile = 128 rows x N (<= 256) columns, K streamed in chunks of 32
 // through two stages, no CTA-wide barrier in the main loop:
-//   warps 0..6  producers: read the A chunk (coalesced float4), split hi/lo, store both K-major tiles
+//   warps 0..14 producers: read the A chunk (coalesced float4), split hi/lo, store both K-major tiles
 //               (144-byte K-chunk pitch: the 8 lanes of a quarter warp hit 32 different banks), arrive on fullA
-//   warp  7     issue warp (converged, elected lane): requests the chunk's pre-split weight tiles by TMA bulk
+//   warp  15    issue warp (converged, elected lane): requests the chunk's pre-split weight tiles by TMA bulk
 //               copy as soon as the stage is free, waits fullA / fullB, issues the 12 tcgen05.mma of the chunk,
 //               tcgen05.commit -> empty[stage] (and -> acc_done after the last chunk of a tile)
 //   warps 0..3  epilogue: TMEM -> registers -> + bias -> global, then arrive on acc_free so that the next tile's
@@ -190,7 +190,7 @@ __device__ __forceinline__ float ldg_early(const float* ptr) {
   return v;
 }
 constexpr int kDK = 32, kDLboA = 144, kDSboA = (kDK / 4) * kDLboA, kDATile = 16 * kDSboA;   // A: 128 rows x 32 K
-constexpr int kDProd = 7;                                                                    // producer warps
+constexpr int kDProd = 15;                                                                   // producer warps
 constexpr int kDBStages = 3;                                                                 // weight-tile ring of the projection
 struct DenseParams {
   const float* A;
@@ -203,7 +203,7 @@ struct DenseParams {
   int T;   // 0: rows as they lie, C row-major.  > 0: "step-major" tiles for the tensor-core recurrence: A rows are
            // (clip, step) pairs, tile = (group of 128 clips, step), C = [group][step][column][128 clips]
 };
-__global__ void __launch_bounds__(256, 1) dense_gemm_tf32x3_kernel(const DenseParams p) {
+__global__ void __launch_bounds__((kDProd + 1) * 32, 1) dense_gemm_tf32x3_kernel(const DenseParams p) {
   extern __shared__ __align__(128) unsigned char smem[];
   __shared__ __align__(8) unsigned long long s_bar[12];   // fullA[2], empty[2], fullB[3], emptyB[3], acc_done, acc_free
   __shared__ uint32_t s_tmem;
@@ -1076,7 +1076,7 @@ int kws_crnn_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t 
         DenseParams dp{x, m.d_wimg[l], m.d_bih[l], d_xp, M, 3 * H, I, (l == 0 && conv_tc) ? 1 : 0, tc_rec ? H1 : 0};
         KWS_CUDA(cudaFuncSetAttribute(dense_gemm_tf32x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dsmem));
         const long long nt = tc_rec ? (nb + 127) / 128 * H1 : (M + 127) / 128;
-        dense_gemm_tf32x3_kernel<<<(unsigned)(nt < h->sm_count ? nt : h->sm_count), 256, dsmem, st>>>(dp);
+        dense_gemm_tf32x3_kernel<<<(unsigned)(nt < h->sm_count ? nt : h->sm_count), (kDProd + 1) * 32, dsmem, st>>>(dp);
       } else if (I % 16 == 0 && (3 * H) % 64 == 0) {
         dim3 grid((unsigned)((M + 127) / 128), (unsigned)(3 * H / 64));
         gru_inproj_tiled_kernel<<<grid, 256, 0, st>>>(x, m.d_wih[l], m.d_bih[l], d_xp, M, 3 * H, I);
