@@ -9,5 +9,6 @@ run python tools/bench_crnn.py 16384 3
 run python tools/bench_dscnn_l.py 1024 2
 run python tools/bench_eager.py 16384 40
 run python tools/bench_eager_l.py 1024
+run python tools/bench_eager_crnn.py 16384
 for F in 40 10; do echo "== python tools/bench_model.py 16384 $F 5" >> $txt; timeout 300 python tools/bench_model.py 16384 $F 5 2>&1 | tail -4 >> $txt; done
 echo "== python tools/bench_model.py 256 40 20 auto (BASELINE configs[0] batch)" >> $txt; timeout 100 python tools/bench_model.py 256 40 20 auto 2>&1 | tail -3 >> $txt
