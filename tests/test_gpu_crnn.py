@@ -14,7 +14,9 @@ pytestmark = pytest.mark.gpu
 
 
 @pytest.mark.parametrize("F,Cc,H,L,B,T", [(40, 16, 64, 1, 19, 99), (40, 8, 32, 2, 5, 99), (10, 16, 64, 2, 33, 49),
-                                          (26, 4, 128, 1, 3, 31), (40, 16, 64, 2, 150, 31), (40, 16, 64, 1, 257, 20)])
+                                          (26, 4, 128, 1, 3, 31), (40, 16, 64, 2, 150, 31), (40, 16, 64, 1, 257, 20),
+                                          # tensor-core path edges: one output step, exactly one / one-plus-one clip groups
+                                          (40, 16, 64, 1, 1, 6), (40, 16, 64, 1, 128, 11), (40, 16, 64, 2, 129, 13)])
 def test_crnn_matches_oracle(F, Cc, H, L, B, T):
     torch.manual_seed(F + Cc + H + L)
     m = CRNN(num_classes=12, n_features=F, conv_channels=Cc, hidden=H, num_layers=L)
