@@ -1055,7 +1055,8 @@ int kws_crnn_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t 
   for (int64_t b0 = 0; b0 < B; b0 += chunk) {
     const int64_t nb = (B - b0 < chunk) ? B - b0 : chunk;
     // tensor-core conv1 writes tile-major, which only the step-major tensor-core projection reads
-    const bool conv_tc = m.d_c1img && F == 40 && Cc == 16 && H == 64 && m.d_wimg[0] && m.d_whimg[0];
+    const bool conv_tc = m.d_c1img && F == 40 && Cc == 16 && H == 64 && m.d_wimg[0] && m.d_whimg[0] &&
+                         (reinterpret_cast<uintptr_t>(feats_dev) & 15) == 0;   // 16-byte feature loads
     if (conv_tc) {
       Conv1TcParams cp{feats_dev + b0 * T * F, m.d_c1img, m.d_conv_b, d_conv, nb, (int)T, H1};
       KWS_CUDA(cudaFuncSetAttribute(conv1_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kC1Smem));
