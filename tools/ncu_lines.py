@@ -8,6 +8,8 @@ import sys
 import tempfile
 
 rep, so, kname = sys.argv[1:4]
+import os
+so = os.path.abspath(so)
 top = int(sys.argv[4]) if len(sys.argv) > 4 else 40
 tmp = tempfile.mkdtemp()
 subprocess.run(["cuobjdump", "-xelf", "all", so], cwd=tmp, check=True, capture_output=True)
