@@ -140,7 +140,7 @@ enum FeatureMode { kModeMfcc = 0, kModeLogMel = 1 };
 int launch_mfcc(kws_handle_t h, const void* pcm_dev, bool is_i16, int64_t B, int64_t N,
                 int64_t pcm_stride, float* out_dev, int mode, cudaStream_t stream);
 // mfcc_fast.cu: 1 = handled, 0 = configuration needs the generic kernel, <0 = error
-int launch_mfcc_fast(kws_handle_t h, const float* pcm_dev, int64_t B, int64_t N, int64_t pcm_stride,
+int launch_mfcc_fast(kws_handle_t h, const void* pcm_dev, bool is_i16, int64_t B, int64_t N, int64_t pcm_stride,
                      float* out_dev, int mode, cudaStream_t stream);
 // model_fused.cu: 1 = handled, 0 = configuration outside the fused kernel, <0 = error
 int launch_dscnn_fused(kws_handle_t h, const float* feats_dev, int64_t B, int64_t T, int64_t F, float* logits_dev,

@@ -378,8 +378,8 @@ int launch_mfcc(kws_handle_t h, const void* pcm_dev, bool is_i16, int64_t B, int
   if (B == 0) return KWS_OK;
   if (!pcm_dev || !out_dev) return fail(KWS_ERR_INVALID, "null device pointer");
 
-  if (!is_i16) {
-    const int rc = launch_mfcc_fast(h, (const float*)pcm_dev, B, N, pcm_stride, out_dev, mode, stream);
+  {
+    const int rc = launch_mfcc_fast(h, pcm_dev, is_i16, B, N, pcm_stride, out_dev, mode, stream);
     if (rc != 0) return rc < 0 ? rc : KWS_OK;
   }
   MfccParams p{};

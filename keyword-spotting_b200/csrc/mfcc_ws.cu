@@ -26,7 +26,7 @@
 namespace kws {
 
 struct FastParams {
-  const float* pcm;
+  const void* pcm;      // float32, or int16 (scaled by 1/32768 = librosa.load) when the kernel is the int16 variant
   float* out;
   long long B, N, stride, total_tiles;
   int nframes, tiles_per_clip, hop, M, ncep, mode, append_energy;
@@ -46,8 +46,21 @@ constexpr int kWarpScratch = 2 * 16 * 17 * 16;     // bytes: two half-warp trans
 constexpr float kFEps = 2.220446049250313e-16f;
 
 
-template <int LOAD_LEN, int ROUNDS>
+// raw-sample access: the raw stage holds the clip's own sample type; int16 is scaled exactly like
+// librosa.load (x / 32768, audio_processor.py:145) when it is read
+__device__ __forceinline__ float2 ld_pair(const float* q) { return *reinterpret_cast<const float2*>(q); }
+__device__ __forceinline__ float ld_one(const float* q) { return *q; }
+__device__ __forceinline__ float2 ld_pair(const short* q) {
+  const short2 s = *reinterpret_cast<const short2*>(q);
+  return make_float2((float)s.x * (1.0f / 32768.0f), (float)s.y * (1.0f / 32768.0f));
+}
+__device__ __forceinline__ float ld_one(const short* q) { return (float)*q * (1.0f / 32768.0f); }
+
+// T = float or short.  kLead = samples kept in front of a tile (16 bytes, so that the TMA destination of a
+// tile that starts inside the clip stays 16-byte aligned while sample s0 - 1 is available)
+template <int LOAD_LEN, int ROUNDS, typename T>
 __global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastParams p) {
+  constexpr int kLead = 16 / (int)sizeof(T);
   extern __shared__ __align__(128) unsigned char smem[];
   // [0,1] raw stage full, [2,3] raw stage empty, [4] A rows of the tile written, [5] tile MMAs retired
   __shared__ __align__(8) unsigned long long s_bar[6];
@@ -102,19 +115,20 @@ __global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastPar
 
   if (warp == 0) {
     // =========================== service warp ===========================
-    auto issue_tma = [&](int it) {  // one thread: raw[stage][j] = x[s0 - 4 + j]
+    auto issue_tma = [&](int it) {  // one thread: raw[stage][j] = x[s0 - kLead + j]
       const unsigned tile_id = blockIdx.x + (unsigned)it * gridDim.x;  // launcher: total_tiles < 2^31
       const unsigned clip = tile_id / (unsigned)p.tiles_per_clip;
       const int t = (int)(tile_id - clip * (unsigned)p.tiles_per_clip);
       const long long s0 = (long long)t * kFramesPerTile * hop;
-      const long long first = s0 >= 4 ? s0 - 4 : 0;
+      const long long first = s0 >= kLead ? s0 - kLead : 0;
       long long end = s0 + p.tile_len;
       if (end > p.N) end = p.N;
-      const uint32_t bytes = (uint32_t)(end - first) * 4u;
+      const uint32_t bytes = (uint32_t)(end - first) * (uint32_t)sizeof(T);
       const uint32_t bar = bar_full + 8u * (it & 1);
-      float* raw = reinterpret_cast<float*>(smem + (size_t)(it & 1) * p.raw_stride);
+      T* raw = reinterpret_cast<T*>(smem + (size_t)(it & 1) * p.raw_stride);
       mbar_expect_tx(bar, bytes);
-      tma_load_1d(smem_u32(raw + (s0 >= 4 ? 0 : 4)), p.pcm + (size_t)clip * p.stride + first, bytes, bar);
+      tma_load_1d(smem_u32(raw + (s0 >= kLead ? 0 : kLead)),
+                  reinterpret_cast<const T*>(p.pcm) + (size_t)clip * p.stride + first, bytes, bar);
     };
     auto issue_mma = [&]() {  // converged warp, elected lane: D[128 x 48] = Ahi*Bhi + Alo*Bhi + Ahi*Blo over Kpad
       tc_fence_after();
@@ -207,12 +221,12 @@ __global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastPar
       const unsigned clip = tile_id / (unsigned)p.tiles_per_clip;
       const int t = (int)(tile_id - clip * (unsigned)p.tiles_per_clip);
       const int s0 = t * kFramesPerTile * hop;
-      float* raw_w = reinterpret_cast<float*>(smem + (size_t)(it & 1) * p.raw_stride);
-      const float* raw = raw_w;
+      T* raw_w = reinterpret_cast<T*>(smem + (size_t)(it & 1) * p.raw_stride);
+      const T* raw = raw_w;
       __syncwarp();  // previous tile: every lane is done with the scratch this conversion overwrites
       mbar_wait(bar_full + 8u * (it & 1), (it >> 1) & 1);
       if (s0 == 0 && cw == 0) {  // y[0] = x[0] - pre * 0: give the clip's first sample a zero predecessor
-        if (lane == 0) raw_w[3] = 0.f;
+        if (lane == 0) raw_w[kLead - 1] = (T)0;
         __syncwarp();
       }
 
@@ -226,7 +240,7 @@ __global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastPar
         // ---- pass-1 loads straight from the raw stage with pre-emphasis on the fly:
         //      z[16 m + l] = (y[32m + 2l], y[32m + 2l + 1]),  y[i] = x[i] - pre * x[i-1]  (fp32, the
         //      product rounded before the subtraction = psf's float32 step); frame A in .x, B in .y
-        const float* qa = raw + 4 + fa_local * hop + 2 * l;
+        const T* qa = raw + kLead + fa_local * hop + 2 * l;
         const int gA = s0 + fa_local * hop + 2 * l;  // clip sample index of this lane's first sample
         CF x16[16];
         if (gA - 2 * l + hop + LOAD_LEN <= n) {      // both frames entirely inside the clip (half-warp uniform)
@@ -235,9 +249,9 @@ __global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastPar
             x16[m].re = fsplat(0.f);
             x16[m].im = fsplat(0.f);
             if (32 * m + 31 < LOAD_LEN || (32 * m < LOAD_LEN && 32 * m + 2 * l + 1 < LOAD_LEN)) {
-              const float2 a = *reinterpret_cast<const float2*>(qa + 32 * m);
-              const float2 b = *reinterpret_cast<const float2*>(qa + 32 * m + hop);
-              const float am = qa[32 * m - 1], bm = qa[32 * m + hop - 1];
+              const float2 a = ld_pair(qa + 32 * m);
+              const float2 b = ld_pair(qa + 32 * m + hop);
+              const float am = ld_one(qa + 32 * m - 1), bm = ld_one(qa + 32 * m + hop - 1);
               x16[m].re.x = __fsub_rn(a.x, __fmul_rn(pre, am));
               x16[m].im.x = __fsub_rn(a.y, __fmul_rn(pre, a.x));
               x16[m].re.y = __fsub_rn(b.x, __fmul_rn(pre, bm));
@@ -251,9 +265,9 @@ __global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastPar
             x16[m].im = fsplat(0.f);
             if (32 * m + 31 < LOAD_LEN || (32 * m < LOAD_LEN && 32 * m + 2 * l + 1 < LOAD_LEN)) {
               const int g = gA + 32 * m;
-              const float2 a = *reinterpret_cast<const float2*>(qa + 32 * m);
-              const float2 b = *reinterpret_cast<const float2*>(qa + 32 * m + hop);
-              const float am = qa[32 * m - 1], bm = qa[32 * m + hop - 1];
+              const float2 a = ld_pair(qa + 32 * m);
+              const float2 b = ld_pair(qa + 32 * m + hop);
+              const float am = ld_one(qa + 32 * m - 1), bm = ld_one(qa + 32 * m + hop - 1);
               x16[m].re.x = (g < n) ? __fsub_rn(a.x, __fmul_rn(pre, am)) : 0.f;
               x16[m].im.x = (g + 1 < n) ? __fsub_rn(a.y, __fmul_rn(pre, a.x)) : 0.f;
               x16[m].re.y = (g + hop < n) ? __fsub_rn(b.x, __fmul_rn(pre, bm)) : 0.f;
@@ -429,13 +443,17 @@ __global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastPar
 
 // returns 1 when the fast kernel handled the launch, 0 when the configuration needs the generic
 // kernel, negative on error
-int launch_mfcc_fast(kws_handle_t h, const float* pcm_dev, int64_t B, int64_t N, int64_t pcm_stride,
+int launch_mfcc_fast(kws_handle_t h, const void* pcm_dev, bool is_i16, int64_t B, int64_t N, int64_t pcm_stride,
                      float* out_dev, int mode, cudaStream_t stream) {
   const FeatureTables& t = h->feat;
   const int M = t.cfg.nfilt, hop = t.cfg.frame_step;
   if (t.d_window != nullptr || t.load_len != 400 || M > 48 || t.d_dctB == nullptr) return 0;
-  // TMA bulk copies need 16-byte aligned sources and sizes; the interleaved tile needs an even hop
-  if ((hop & 3) != 0 || (N & 3) != 0 || (pcm_stride & 3) != 0 || (reinterpret_cast<size_t>(pcm_dev) & 15) != 0)
+  // TMA bulk copies need 16-byte aligned sources and sizes (4 float or 8 int16 samples); the interleaved
+  // tile needs an even hop
+  const int64_t amask = is_i16 ? 7 : 3;
+  const size_t esz = is_i16 ? 2 : 4;
+  if ((hop & amask) != 0 || (N & amask) != 0 || (pcm_stride & amask) != 0 ||
+      (reinterpret_cast<size_t>(pcm_dev) & 15) != 0)
     return 0;
   if (N >= (1ll << 30)) return 0;
   constexpr int ROUNDS = 3;
@@ -463,7 +481,7 @@ int launch_mfcc_fast(kws_handle_t h, const float* pcm_dev, int64_t B, int64_t N,
   p.kpad = t.dct_kpad;
   p.tile_len = (kFramesPerTile - 1) * hop + 400;  // samples a tile's 20 frames span
   const uint32_t sbo = (uint32_t)(p.kpad / 4) * 128u;
-  p.raw_stride = (int)(((size_t)(p.tile_len + 4) * 4 + 127) & ~(size_t)127);
+  p.raw_stride = (int)(((size_t)p.tile_len * esz + 16 + 127) & ~(size_t)127);
   size_t off = (size_t)2 * p.raw_stride;           // two raw stages at offset 0
   p.off_a = (int)off;                              // A hi rows 0..23, then A lo rows 0..23
   off += (size_t)6 * sbo;
@@ -485,7 +503,7 @@ int launch_mfcc_fast(kws_handle_t h, const float* pcm_dev, int64_t B, int64_t N,
   // shared memory (rows >= 24 are don't-care values that only reach accumulator rows we never read)
   if ((size_t)p.off_a + (size_t)(3 + 16) * sbo > smem_bytes || smem_bytes > 112 * 1024) return 0;
 
-  auto kern = mfcc512_ws_kernel<400, ROUNDS>;
+  auto kern = is_i16 ? mfcc512_ws_kernel<400, ROUNDS, short> : mfcc512_ws_kernel<400, ROUNDS, float>;
   KWS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
   // two CTAs per SM by construction (<= 112 KB shared memory and <= 168 registers each); ask for
   // the full shared-memory carve-out so the second CTA is not refused

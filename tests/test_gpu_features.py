@@ -108,9 +108,32 @@ def test_int16_ingest(proc):
     got = proc.extract_features(i16.cuda()).cpu().numpy()
     as_float = (i16.numpy().astype(np.float32) / 32768.0)       # librosa.load scaling
     _close(got, psf_mfcc.extract_features_batch(as_float), "int16")
-    # int16 ingest runs the generic kernel, float32 input the fast one: same features within fp32 noise
-    torch.testing.assert_close(proc.extract_features(i16.cuda()),
-                               proc.extract_features(torch.from_numpy(as_float).cuda()), rtol=1e-3, atol=1e-4)
+    # aligned int16 rows take the warp-specialised kernel like float32 rows do; x/32768 is exact, so the
+    # two sample formats give the same bits
+    f32_feats = proc.extract_features(torch.from_numpy(as_float).cuda())
+    assert torch.equal(proc.extract_features(i16.cuda()), f32_feats)
+    for numcep, nfilt in [(40, 40), (13, 26)]:
+        assert torch.equal(proc.extract_features(i16.cuda(), numcep=numcep, nfilt=nfilt),
+                           proc.extract_features(torch.from_numpy(as_float).cuda(), numcep=numcep, nfilt=nfilt))
+    assert torch.equal(proc.extract_logfbank(i16.cuda(), nfilt=40),
+                       proc.extract_logfbank(torch.from_numpy(as_float).cuda(), nfilt=40))
+    # a clip length that is not a multiple of 8 samples (TMA alignment of 2-byte samples) falls back to the
+    # generic kernel while float32 stays on the fast one: same features within fp32 noise
+    odd = torch.randint(-32768, 32767, (4, 16004), generator=g, dtype=torch.int16)
+    torch.testing.assert_close(proc.extract_features(odd.cuda()),
+                               proc.extract_features((odd.float() / 32768.0).cuda()), rtol=1e-3, atol=1e-4)
+
+
+def test_int16_ragged_lengths(proc):
+    """int16 clips whose last frames run past the end (zero padding after pre-emphasis), fast kernel."""
+    g = torch.Generator().manual_seed(3)
+    for n in (16000, 15992, 8000, 408):
+        i16 = torch.randint(-32768, 32767, (3, n), generator=g, dtype=torch.int16)
+        as_float = i16.float() / 32768.0
+        assert torch.equal(proc.extract_features(i16.cuda(), numcep=40, nfilt=40),
+                           proc.extract_features(as_float.cuda(), numcep=40, nfilt=40)), n
+        _close(proc.extract_features(i16.cuda(), numcep=40, nfilt=40).cpu().numpy(),
+               psf_mfcc.extract_features_batch(as_float.numpy(), numcep=40, nfilt=40), f"int16 n={n}")
 
 
 def test_strided_rows_and_host_path(proc):
