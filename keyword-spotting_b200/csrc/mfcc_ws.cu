@@ -40,8 +40,15 @@ struct FastParams {
   int off_a, off_scratch, off_b, off_melw, off_edges, off_twp, off_c0;
 };
 
-constexpr int kCWarps = kFramesPerTile / 4;        // 5 compute warps
-constexpr int kWsThreads = (kCWarps + 1) * 32;     // + service warp
+// One CTA per SM: the kernel is bound by exposed latency, not by issue slots or HBM, so what counts is the
+// number of resident compute warps.  ptxas needs 128 registers for the compute path, i.e. 16 warps per SM:
+// 13 compute warps (tile = 52 frames, two tiles per 99-frame clip, 25 of 26 warp slots busy) + 2 service
+// warps.  (Two CTAs of 5 + 1 warps, the previous layout, kept 10 compute warps resident: 10.8 M clips/s.)
+constexpr int kCWarps = 13;                        // compute warps
+constexpr int kSvcWarps = 2;                       // service warps: TMEM lanes 0..31 and 32..63
+constexpr int kTileFrames = kCWarps * 4;           // 52 frames per tile = rows of the DCT GEMM
+constexpr int kAGroups = (kTileFrames + 7) / 8;    // 8-row groups of the A operand
+constexpr int kWsThreads = (kCWarps + kSvcWarps) * 32;
 constexpr int kWarpScratch = 2 * 16 * 17 * 16;     // bytes: two half-warp transposes (also holds S2)
 constexpr float kFEps = 2.220446049250313e-16f;
 
@@ -59,21 +66,22 @@ __device__ __forceinline__ float ld_one(const short* q) { return (float)*q * (1.
 // T = float or short.  kLead = samples kept in front of a tile (16 bytes, so that the TMA destination of a
 // tile that starts inside the clip stays 16-byte aligned while sample s0 - 1 is available)
 template <int LOAD_LEN, int ROUNDS, typename T>
-__global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastParams p) {
+__global__ void __launch_bounds__(kWsThreads, 1) mfcc512_ws_kernel(const FastParams p) {
   constexpr int kLead = 16 / (int)sizeof(T);
   extern __shared__ __align__(128) unsigned char smem[];
-  // [0,1] raw stage full, [2,3] raw stage empty, [4] A rows of the tile written, [5] tile MMAs retired
-  __shared__ __align__(8) unsigned long long s_bar[6];
+  // [0,1] raw stage full, [2,3] raw stage empty, [4] A rows of the tile written, [5] tile MMAs retired,
+  // [6] second service warp has drained its accumulator rows
+  __shared__ __align__(8) unsigned long long s_bar[7];
   __shared__ uint32_t s_tmem;
   const float* s_inv = reinterpret_cast<const float*>(smem + p.off_melw);  // [M+1] 1 / segment length
   const int* s_edges = reinterpret_cast<const int*>(smem + p.off_edges);
   const float2* s_twp = reinterpret_cast<const float2*>(smem + p.off_twp);
-  float* s_c0 = reinterpret_cast<float*>(smem + p.off_c0);  // [2][20]
+  float* s_c0 = reinterpret_cast<float*>(smem + p.off_c0);  // [2][kTileFrames]
 
   const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
   const bool do_dct = (p.mode == kModeMfcc);
   const uint32_t bar_full = smem_u32(&s_bar[0]), bar_empty = smem_u32(&s_bar[2]);
-  const uint32_t bar_afull = smem_u32(&s_bar[4]), bar_mma = smem_u32(&s_bar[5]);
+  const uint32_t bar_afull = smem_u32(&s_bar[4]), bar_mma = smem_u32(&s_bar[5]), bar_epi = smem_u32(&s_bar[6]);
   const int hop = p.hop;
   const uint32_t sbo = (uint32_t)(p.kpad / 4) * 128u;  // bytes between 8-row groups of A and B
 
@@ -84,6 +92,7 @@ __global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastPar
     mbar_init(bar_empty + 8, kCWarps);
     mbar_init(bar_afull, kCWarps);
     mbar_init(bar_mma, 1);
+    mbar_init(bar_epi, 1);
     fence_mbar_init();
   }
   if (warp == 0 && do_dct) {
@@ -101,7 +110,7 @@ __global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastPar
     float* b = reinterpret_cast<float*>(smem + p.off_b);
     for (int i = tid; i < 2 * kDctN * p.kpad; i += kWsThreads) b[i] = p.dctB[i];
     float* a = reinterpret_cast<float*>(smem + p.off_a);
-    for (int i = tid; i < 2 * 24 * p.kpad; i += kWsThreads) a[i] = 0.f;
+    for (int i = tid; i < 2 * kAGroups * 8 * p.kpad; i += kWsThreads) a[i] = 0.f;
   }
   fence_proxy_async();  // B (and the zeroed A) were written through the generic proxy
   tc_fence_before();
@@ -113,13 +122,15 @@ __global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastPar
                        ? (int)((p.total_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x)
                        : 0;
 
-  if (warp == 0) {
-    // =========================== service warp ===========================
+  if (warp < kSvcWarps) {
+    // =========================== service warps ===========================
+    // warp 0: TMA ring producer, MMA issue, epilogue of accumulator rows 0..31; warp 1: epilogue of rows 32..63
+    // (a warp reads the TMEM lane quarter of its index)
     auto issue_tma = [&](int it) {  // one thread: raw[stage][j] = x[s0 - kLead + j]
       const unsigned tile_id = blockIdx.x + (unsigned)it * gridDim.x;  // launcher: total_tiles < 2^31
       const unsigned clip = tile_id / (unsigned)p.tiles_per_clip;
       const int t = (int)(tile_id - clip * (unsigned)p.tiles_per_clip);
-      const long long s0 = (long long)t * kFramesPerTile * hop;
+      const long long s0 = (long long)t * kTileFrames * hop;
       const long long first = s0 >= kLead ? s0 - kLead : 0;
       long long end = s0 + p.tile_len;
       if (end > p.N) end = p.N;
@@ -132,7 +143,7 @@ __global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastPar
     };
     auto issue_mma = [&]() {  // converged warp, elected lane: D[128 x 48] = Ahi*Bhi + Alo*Bhi + Ahi*Blo over Kpad
       tc_fence_after();
-      const uint32_t a_hi = smem_u32(smem + p.off_a), a_lo = a_hi + 3u * sbo;
+      const uint32_t a_hi = smem_u32(smem + p.off_a), a_lo = a_hi + (uint32_t)kAGroups * sbo;
       const uint32_t b_hi = smem_u32(smem + p.off_b), b_lo = b_hi + (uint32_t)(kDctN / 8) * sbo;
       const int ksteps = p.kpad / 8;
       uint32_t acc = 0;
@@ -146,7 +157,7 @@ __global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastPar
       }
       tc_commit_elect(bar_mma);
     };
-    if (lane == 0) {
+    if (warp == 0 && lane == 0) {
       if (n_it > 0) issue_tma(0);
       if (n_it > 1) issue_tma(1);
     }
@@ -154,7 +165,7 @@ __global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastPar
       const unsigned tile_id = blockIdx.x + (unsigned)it * gridDim.x;  // launcher: total_tiles < 2^31
       const unsigned clip = tile_id / (unsigned)p.tiles_per_clip;
       const int t = (int)(tile_id - clip * (unsigned)p.tiles_per_clip);
-      if (it + 2 < n_it) {  // refill this stage as soon as every compute warp has converted tile `it`
+      if (warp == 0 && it + 2 < n_it) {  // refill this stage as soon as every compute warp has converted tile `it`
         mbar_wait_idle(bar_empty + 8u * (it & 1), (it >> 1) & 1);
         if (lane == 0) {
           fence_proxy_async();
@@ -163,9 +174,14 @@ __global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastPar
         __syncwarp();
       }
       if (do_dct) {
-        mbar_wait_idle(bar_afull, it & 1);
-        issue_mma();
-        mbar_wait(bar_mma, it & 1);
+        if (warp == 0) {
+          mbar_wait_idle(bar_afull, it & 1);
+          if (it > 0) mbar_wait(bar_epi, (it - 1) & 1);  // warp 1 has read the previous tile's rows
+          issue_mma();
+          mbar_wait(bar_mma, it & 1);
+        } else {
+          mbar_wait_idle(bar_mma, it & 1);
+        }
         // ---- epilogue (lane = frame row of the tile): TMEM -> registers -> global ----
         float v[kDctN];
         tc_fence_after();
@@ -173,16 +189,21 @@ __global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastPar
           float q[16];
 #pragma unroll
           for (int c = 0; c < kDctN / 16; ++c) {
-            tc_ld16(tmem + c * 16, q);
+            tc_ld16(tmem + ((uint32_t)(warp * 32) << 16) + c * 16, q);
 #pragma unroll
             for (int i = 0; i < 16; ++i) v[c * 16 + i] = q[i];
           }
         }
         tc_wait_ld();
         tc_fence_before();
-        const int f = t * kFramesPerTile + lane;
-        if (lane < kFramesPerTile && f < p.nframes) {
-          const float c0 = s_c0[(it & 1) * kFramesPerTile + lane];
+        if (warp != 0) {
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar_epi);
+        }
+        const int row = warp * 32 + lane;
+        const int f = t * kTileFrames + row;
+        if (row < kTileFrames && f < p.nframes) {
+          const float c0 = s_c0[(it & 1) * kTileFrames + row];
           v[0] = p.append_energy ? c0 : v[0] + c0;
           float* o = p.out + ((size_t)clip * p.nframes + f) * p.ncep;
           if ((p.ncep & 3) == 0) {
@@ -199,7 +220,7 @@ __global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastPar
     }
   } else {
     // =========================== compute warps ===========================
-    const int cw = warp - 1, half = lane >> 4, l = lane & 15;
+    const int cw = warp - kSvcWarps, half = lane >> 4, l = lane & 15;
     unsigned char* wscratch = smem + p.off_scratch + cw * kWarpScratch;
     unsigned char* scratch = wscratch + half * (kWarpScratch / 2);  // this half-warp's transpose area
     float4* s_tr = reinterpret_cast<float4*>(scratch);
@@ -220,7 +241,7 @@ __global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastPar
       const unsigned tile_id = blockIdx.x + (unsigned)it * gridDim.x;  // launcher: total_tiles < 2^31
       const unsigned clip = tile_id / (unsigned)p.tiles_per_clip;
       const int t = (int)(tile_id - clip * (unsigned)p.tiles_per_clip);
-      const int s0 = t * kFramesPerTile * hop;
+      const int s0 = t * kTileFrames * hop;
       T* raw_w = reinterpret_cast<T*>(smem + (size_t)(it & 1) * p.raw_stride);
       const T* raw = raw_w;
       __syncwarp();  // previous tile: every lane is done with the scratch this conversion overwrites
@@ -231,8 +252,8 @@ __global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastPar
       }
 
       const int fa_local = cw * 4 + half * 2;
-      const int fA = t * kFramesPerTile + fa_local, fB = fA + 1;
-      const bool active = (t * kFramesPerTile + cw * 4) < p.nframes;  // warp-uniform
+      const int fA = t * kTileFrames + fa_local, fB = fA + 1;
+      const bool active = (t * kTileFrames + cw * 4) < p.nframes;  // warp-uniform
       if (!active && lane == 0) mbar_arrive(bar_empty + 8u * (it & 1));
       V lm[ROUNDS];
       V mean = fsplat(0.f), esum = fsplat(0.f);
@@ -418,14 +439,14 @@ __global__ void __launch_bounds__(kWsThreads, 2) mfcc512_ws_kernel(const FastPar
               const uint32_t ob = (uint32_t)((fa_local + 1) >> 3) * sbo + (uint32_t)((fa_local + 1) & 7) * 16u + col;
               *reinterpret_cast<float*>(abase + oa) = hx;
               *reinterpret_cast<float*>(abase + ob) = hy;
-              *reinterpret_cast<float*>(abase + 3u * sbo + oa) = lx;
-              *reinterpret_cast<float*>(abase + 3u * sbo + ob) = ly;
+              *reinterpret_cast<float*>(abase + (uint32_t)kAGroups * sbo + oa) = lx;
+              *reinterpret_cast<float*>(abase + (uint32_t)kAGroups * sbo + ob) = ly;
             }
           }
           if (l == 0) {
             const float eA = (esum.x == 0.f) ? kFEps : esum.x, eB = (esum.y == 0.f) ? kFEps : esum.y;
             const float sq = sqrtf((float)p.M);
-            float* c0 = s_c0 + (it & 1) * kFramesPerTile + fa_local;
+            float* c0 = s_c0 + (it & 1) * kTileFrames + fa_local;
             c0[0] = p.append_energy ? fast_log(eA) : sq * mean.x;  // else: the removed mean only moves c0
             c0[1] = p.append_energy ? fast_log(eB) : sq * mean.y;
           }
@@ -464,7 +485,7 @@ int launch_mfcc_fast(kws_handle_t h, const void* pcm_dev, bool is_i16, int64_t B
   p.N = N;
   p.stride = pcm_stride;
   p.nframes = (int)kws_num_frames(N, t.cfg.frame_len, t.cfg.frame_step);
-  p.tiles_per_clip = (p.nframes + kFramesPerTile - 1) / kFramesPerTile;
+  p.tiles_per_clip = (p.nframes + kTileFrames - 1) / kTileFrames;
   p.total_tiles = (long long)B * p.tiles_per_clip;
   if (p.total_tiles >= (1ll << 31) - 4096) return 0;
   p.hop = hop;
@@ -479,12 +500,12 @@ int launch_mfcc_fast(kws_handle_t h, const void* pcm_dev, bool is_i16, int64_t B
   p.edges = t.d_segedge;
   p.dctB = t.d_dctB;
   p.kpad = t.dct_kpad;
-  p.tile_len = (kFramesPerTile - 1) * hop + 400;  // samples a tile's 20 frames span
+  p.tile_len = (kTileFrames - 1) * hop + 400;  // samples a tile's frames span
   const uint32_t sbo = (uint32_t)(p.kpad / 4) * 128u;
   p.raw_stride = (int)(((size_t)p.tile_len * esz + 16 + 127) & ~(size_t)127);
   size_t off = (size_t)2 * p.raw_stride;           // two raw stages at offset 0
-  p.off_a = (int)off;                              // A hi rows 0..23, then A lo rows 0..23
-  off += (size_t)6 * sbo;
+  p.off_a = (int)off;                              // A hi row groups, then A lo row groups
+  off += (size_t)2 * kAGroups * sbo;
   p.off_scratch = (int)off;
   off += (size_t)kCWarps * kWarpScratch;
   p.off_b = (int)off;                              // B hi [48 x kpad], then B lo
@@ -496,19 +517,17 @@ int launch_mfcc_fast(kws_handle_t h, const void* pcm_dev, bool is_i16, int64_t B
   p.off_twp = (int)off;
   off += 128 * 8;
   p.off_c0 = (int)off;
-  off += 2 * kFramesPerTile * 4;
+  off += 2 * kTileFrames * 4;
   const size_t smem_bytes = off;
   static_assert(2064 + 2 * (16 * ROUNDS + 1) * 8 <= kWarpScratch / 2, "scratch layout overflow");
   // the tensor core reads 128 rows of A: 16 row groups past each base must stay inside the CTA's
   // shared memory (rows >= 24 are don't-care values that only reach accumulator rows we never read)
-  if ((size_t)p.off_a + (size_t)(3 + 16) * sbo > smem_bytes || smem_bytes > 112 * 1024) return 0;
+  if ((size_t)p.off_a + (size_t)(kAGroups + 16) * sbo > smem_bytes || smem_bytes > 227 * 1024 - 256) return 0;
 
   auto kern = is_i16 ? mfcc512_ws_kernel<400, ROUNDS, short> : mfcc512_ws_kernel<400, ROUNDS, float>;
   KWS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
-  // two CTAs per SM by construction (<= 112 KB shared memory and <= 168 registers each); ask for
-  // the full shared-memory carve-out so the second CTA is not refused
   KWS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-  long long grid = (long long)h->sm_count * 2;
+  long long grid = (long long)h->sm_count;  // one persistent CTA per SM
   if (grid > p.total_tiles) grid = p.total_tiles;
   kern<<<(unsigned)grid, kWsThreads, smem_bytes, stream>>>(p);
   KWS_CHECK_LAUNCH(h);
