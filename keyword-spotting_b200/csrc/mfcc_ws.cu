@@ -122,12 +122,22 @@ __global__ void __launch_bounds__(kWsThreads, 1) mfcc512_ws_kernel(const FastPar
                        ? (int)((p.total_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x)
                        : 0;
 
+  // Tile `it` of this CTA.  A clip's first tile keeps all 13 compute warps busy, its second one 12, so a CTA
+  // that always got the same half (even grid, two tiles per clip) would be the slow or the fast one of its
+  // pair: neighbouring CTAs swap tiles every other iteration.
+  const bool swap_ok = (gridDim.x & 1u) == 0u;
+  auto tile_of = [&](int it) -> unsigned {
+    unsigned id = blockIdx.x + (unsigned)it * gridDim.x;  // launcher: total_tiles < 2^31
+    if (swap_ok && (it & 1) && (long long)(id | 1u) < p.total_tiles) id ^= 1u;
+    return id;
+  };
+
   if (warp < kSvcWarps) {
     // =========================== service warps ===========================
     // warp 0: TMA ring producer, MMA issue, epilogue of accumulator rows 0..31; warp 1: epilogue of rows 32..63
     // (a warp reads the TMEM lane quarter of its index)
     auto issue_tma = [&](int it) {  // one thread: raw[stage][j] = x[s0 - kLead + j]
-      const unsigned tile_id = blockIdx.x + (unsigned)it * gridDim.x;  // launcher: total_tiles < 2^31
+      const unsigned tile_id = tile_of(it);
       const unsigned clip = tile_id / (unsigned)p.tiles_per_clip;
       const int t = (int)(tile_id - clip * (unsigned)p.tiles_per_clip);
       const long long s0 = (long long)t * kTileFrames * hop;
@@ -162,7 +172,7 @@ __global__ void __launch_bounds__(kWsThreads, 1) mfcc512_ws_kernel(const FastPar
       if (n_it > 1) issue_tma(1);
     }
     for (int it = 0; it < n_it; ++it) {
-      const unsigned tile_id = blockIdx.x + (unsigned)it * gridDim.x;  // launcher: total_tiles < 2^31
+      const unsigned tile_id = tile_of(it);
       const unsigned clip = tile_id / (unsigned)p.tiles_per_clip;
       const int t = (int)(tile_id - clip * (unsigned)p.tiles_per_clip);
       if (warp == 0 && it + 2 < n_it) {  // refill this stage as soon as every compute warp has converted tile `it`
@@ -238,7 +248,7 @@ __global__ void __launch_bounds__(kWsThreads, 1) mfcc512_ws_kernel(const FastPar
     const int n = (int)p.N;
 
     for (int it = 0; it < n_it; ++it) {
-      const unsigned tile_id = blockIdx.x + (unsigned)it * gridDim.x;  // launcher: total_tiles < 2^31
+      const unsigned tile_id = tile_of(it);
       const unsigned clip = tile_id / (unsigned)p.tiles_per_clip;
       const int t = (int)(tile_id - clip * (unsigned)p.tiles_per_clip);
       const int s0 = t * kTileFrames * hop;
