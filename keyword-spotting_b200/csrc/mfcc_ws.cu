@@ -1,26 +1,27 @@
 // Fast, warp-specialised variant of the fused PCM -> MFCC kernel (see mfcc.cu for the algorithm
 // and the reference call chain it replaces: kws/libs/audio_processor.py:235-278 -> psf.mfcc).
 //
-// Same decomposition as mfcc.cu (tile = 20 frames of one clip, warp = 4 frames, half-warp =
-// 2 frames packed in f32x2 registers, 256-point complex FFT = 16 lanes x radix-16 twice).  The
-// kernel is bound by instruction issue and shared-memory bandwidth, not HBM, so
-// this variant removes instructions, exposed latency and every CTA-wide barrier:
-//   * 6 warps per CTA, 2 CTAs per SM.  Warp 0 is a SERVICE warp: it streams raw PCM tiles into a
-//     2-stage shared-memory ring with TMA bulk copies (cp.async.bulk + mbarrier full/empty pairs),
-//     issues the tensor-core DCT of each finished tile and drains its accumulator from TMEM to
-//     global memory.  Warps 1..5 are COMPUTE warps that never wait for each other: they only meet
-//     at mbarriers (tile landed / A rows written / previous MMA retired).
-//   * each compute warp pre-emphasises (fp32, two roundings = psf's float32 step) exactly the
-//     880 samples its 4 frames span and stores them interleaved, S2[i] = (y[i], y[i+hop]), in its
-//     private scratch, so one LDS.128 yields the packed (re, im) pair of both frames;
+// Same arithmetic as mfcc.cu (warp = 4 frames, half-warp = 2 frames packed in f32x2 registers,
+// 256-point complex FFT = 16 lanes x radix-16 twice).  The kernel is bound by exposed latency,
+// instruction issue and shared-memory bandwidth, not HBM, so this variant removes
+// instructions and every CTA-wide barrier and keeps as many compute warps resident as fit:
+//   * one persistent CTA per SM, 15 warps (128 registers): 13 COMPUTE warps that never wait for each
+//     other - they only meet at mbarriers (tile landed / A rows written / previous MMA retired) - and
+//     2 SERVICE warps.  Service warp 0 streams raw PCM tiles (52 frames of one clip; float32 or int16
+//     samples) into a 2-stage shared-memory ring with TMA bulk copies (cp.async.bulk + mbarrier
+//     full/empty pairs) and issues the tensor-core DCT of each finished tile; both service warps drain
+//     the accumulator from TMEM to global memory (rows 0..31 and 32..51: a warp reads the TMEM lane
+//     quarter of its index);
+//   * pre-emphasis (fp32, two roundings = psf's float32 step) on the fly when a warp reads its samples
+//     from the raw stage;
 //   * FADD2/FFMA2 operand modifiers (negate, scalar broadcast) keep twiddles and weights scalar;
 //   * the real-FFT split computes X[k] and X[256-k] together from one shuffled mirror value;
-//   * DCT-II (+lifter) of the tile, [20 x M] x [M x C], on the tensor core: tcgen05.mma kind::tf32
+//   * DCT-II (+lifter) of the tile, [52 x M] x [M x C], on the tensor core: tcgen05.mma kind::tf32
 //     with a 3-term hi/lo split (fp32-grade), K-major no-swizzle operands, accumulator in TMEM,
-//     tcgen05.commit -> mbarrier, tcgen05.ld epilogue in the service warp;
+//     tcgen05.commit -> mbarrier, tcgen05.ld epilogue in the service warps;
 //   * log is a range-reduced MUFU.LG2.
 // Configurations it does not cover (window function, frame_len != 400, nfilt > 48, unaligned
-// input, hop > 344) fall back to the generic kernel in mfcc.cu.
+// input, a hop too long for the shared-memory tile) fall back to the generic kernel in mfcc.cu.
 #include "mfcc_dev.cuh"
 
 namespace kws {
