@@ -185,6 +185,12 @@ int kws_pcm_to_logits(kws_handle_t h, const float* pcm_dev, int64_t B, int64_t N
                       int64_t pcm_stride, float* logits_dev, void* stream);
 int kws_pcm_to_logits_host(kws_handle_t h, const float* pcm_host, int64_t B, int64_t N,
                            float* logits_host);
+/* the same two calls fed 16-bit PCM (x/32768 = librosa.load, audio_processor.py:145, happens inside the
+ * MFCC kernel; logits are bit-equal to the float32 calls on x/32768) */
+int kws_pcm_to_logits_i16(kws_handle_t h, const int16_t* pcm_dev, int64_t B, int64_t N,
+                          int64_t pcm_stride, float* logits_dev, void* stream);
+int kws_pcm_to_logits_host_i16(kws_handle_t h, const int16_t* pcm_host, int64_t B, int64_t N,
+                               float* logits_host);
 
 #ifdef __cplusplus
 }

@@ -154,8 +154,8 @@ int kws_mfcc_host_i16(kws_handle_t h, const int16_t* pcm_host, int64_t B, int64_
 }
 
 
-int kws_pcm_to_logits(kws_handle_t h, const float* pcm_dev, int64_t B, int64_t N, int64_t pcm_stride,
-                      float* logits_dev, void* stream) {
+static int pcm_to_logits_impl(kws_handle_t h, const void* pcm_dev, bool is_i16, int64_t B, int64_t N,
+                             int64_t pcm_stride, float* logits_dev, void* stream) {
   if (!h) return fail(KWS_ERR_INVALID, "null handle");
   if (!h->feat.ready) return fail(KWS_ERR_STATE, "features not configured");
   if (!h->model.finalized) return fail(KWS_ERR_STATE, "model weights not finalized");
@@ -172,13 +172,24 @@ int kws_pcm_to_logits(kws_handle_t h, const float* pcm_dev, int64_t B, int64_t N
     KWS_CUDA(cudaMalloc((void**)&h->d_feat_tmp, need));
     h->feat_tmp_bytes = need;
   }
-  int rc = launch_mfcc(h, pcm_dev, false, B, N, pcm_stride, h->d_feat_tmp, kModeMfcc, (cudaStream_t)stream);
+  int rc = launch_mfcc(h, pcm_dev, is_i16, B, N, pcm_stride, h->d_feat_tmp, kModeMfcc, (cudaStream_t)stream);
   if (rc) return rc;
   return kws_model_forward(h, h->d_feat_tmp, B, nframes, F, logits_dev, stream);
 }
 
-int kws_pcm_to_logits_host(kws_handle_t h, const float* pcm_host, int64_t B, int64_t N,
-                           float* logits_host) {
+int kws_pcm_to_logits(kws_handle_t h, const float* pcm_dev, int64_t B, int64_t N, int64_t pcm_stride,
+                      float* logits_dev, void* stream) {
+  return pcm_to_logits_impl(h, pcm_dev, false, B, N, pcm_stride, logits_dev, stream);
+}
+
+int kws_pcm_to_logits_i16(kws_handle_t h, const int16_t* pcm_dev, int64_t B, int64_t N, int64_t pcm_stride,
+                          float* logits_dev, void* stream) {
+  return pcm_to_logits_impl(h, pcm_dev, true, B, N, pcm_stride, logits_dev, stream);
+}
+
+static int pcm_to_logits_host_impl(kws_handle_t h, const void* pcm_host, bool is_i16, int64_t B, int64_t N,
+                                   float* logits_host) {
+  const size_t esz = is_i16 ? 2 : 4;
   if (!h) return fail(KWS_ERR_INVALID, "null handle");
   if (!h->feat.ready) return fail(KWS_ERR_STATE, "features not configured");
   if (!h->model.finalized) return fail(KWS_ERR_STATE, "model weights not finalized");
@@ -201,9 +212,10 @@ int kws_pcm_to_logits_host(kws_handle_t h, const float* pcm_host, int64_t B, int
     const int64_t nb = std::min<int64_t>(chunk, B - b0);
     const int s = i & 1;
     cudaStream_t st = h->s_copy[s];
-    KWS_CUDA(cudaMemcpyAsync(h->d_stage_in[s], pcm_host + b0 * N, (size_t)nb * N * 4, cudaMemcpyHostToDevice, st));
+    KWS_CUDA(cudaMemcpyAsync(h->d_stage_in[s], (const char*)pcm_host + (size_t)b0 * N * esz, (size_t)nb * N * esz,
+                             cudaMemcpyHostToDevice, st));
     if (i > 0) KWS_CUDA(cudaStreamWaitEvent(st, done, 0));
-    rc = kws_pcm_to_logits(h, (const float*)h->d_stage_in[s], nb, N, N, (float*)h->d_stage_out[s], st);
+    rc = pcm_to_logits_impl(h, h->d_stage_in[s], is_i16, nb, N, N, (float*)h->d_stage_out[s], st);
     if (rc) { cudaEventDestroy(done); return rc; }
     KWS_CUDA(cudaEventRecord(done, st));
     KWS_CUDA(cudaMemcpyAsync(logits_host + b0 * K, h->d_stage_out[s], (size_t)nb * K * 4, cudaMemcpyDeviceToHost, st));
@@ -212,6 +224,14 @@ int kws_pcm_to_logits_host(kws_handle_t h, const float* pcm_host, int64_t B, int
   KWS_CUDA(cudaStreamSynchronize(h->s_copy[1]));
   cudaEventDestroy(done);
   return KWS_OK;
+}
+
+int kws_pcm_to_logits_host(kws_handle_t h, const float* pcm_host, int64_t B, int64_t N, float* logits_host) {
+  return pcm_to_logits_host_impl(h, pcm_host, false, B, N, logits_host);
+}
+
+int kws_pcm_to_logits_host_i16(kws_handle_t h, const int16_t* pcm_host, int64_t B, int64_t N, float* logits_host) {
+  return pcm_to_logits_host_impl(h, pcm_host, true, B, N, logits_host);
 }
 
 }  // extern "C"

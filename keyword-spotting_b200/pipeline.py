@@ -50,17 +50,19 @@ class KeywordSpotter:
             self._bound_h = self._h
 
     def __call__(self, pcm: torch.Tensor) -> torch.Tensor:
-        """``pcm[B, N]`` float32 on the device -> logits ``[B, num_classes]``."""
+        """``pcm[B, N]`` float32 (or int16 PCM, scaled by 1/32768 like ``librosa.load``) -> logits
+        ``[B, num_classes]`` on the device."""
         lib = _native.lib()
         self._bind()
-        x = pcm.to(self.device, torch.float32).contiguous()
+        i16 = pcm.dtype == torch.int16
+        x = pcm.to(self.device, torch.int16 if i16 else torch.float32).contiguous()
         if x.dim() == 1:
             x = x.unsqueeze(0)
         B, N = x.shape
         out = torch.empty((B, self.model.num_classes), dtype=torch.float32, device=self.device)
         if B:
             with torch.cuda.device(self.device):
-                _native.check(lib.kws_pcm_to_logits(
+                _native.check((lib.kws_pcm_to_logits_i16 if i16 else lib.kws_pcm_to_logits)(
                     self._h.ptr, C.c_void_p(x.data_ptr()), B, N, x.stride(0), C.c_void_p(out.data_ptr()),
                     _native.current_stream_ptr(self._idx)), ModelError)
         return out
@@ -99,14 +101,17 @@ class KeywordSpotter:
         return out[0] if single else out
 
     def infer_host(self, pcm: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
-        """HOST float32 ``[B, N]`` (ideally pinned) -> HOST logits; copies pipelined in the library."""
+        """HOST float32 or int16 ``[B, N]`` (ideally pinned) -> HOST logits; copies pipelined in the library.
+        16-bit PCM (the wav sample format) halves the PCIe bytes, which is what bounds this call."""
         lib = _native.lib()
         self._bind()
+        if pcm.device.type != "cpu" or pcm.dtype not in (torch.float32, torch.int16) or pcm.dim() != 2:
+            raise AudioProcessingError("infer_host expects a float32 (or int16 PCM) [B, N] CPU tensor")
         pcm = pcm.contiguous()
         B, N = pcm.shape
         if out is None:
             out = torch.empty((B, self.model.num_classes), dtype=torch.float32, pin_memory=True)
         with torch.cuda.device(self.device):
-            _native.check(lib.kws_pcm_to_logits_host(self._h.ptr, C.c_void_p(pcm.data_ptr()), B, N,
-                                                     C.c_void_p(out.data_ptr())), ModelError)
+            fn = lib.kws_pcm_to_logits_host_i16 if pcm.dtype == torch.int16 else lib.kws_pcm_to_logits_host
+            _native.check(fn(self._h.ptr, C.c_void_p(pcm.data_ptr()), B, N, C.c_void_p(out.data_ptr())), ModelError)
         return out

@@ -185,6 +185,11 @@ def test_pcm_to_logits(numcep, nfilt):
     np.testing.assert_allclose(got, two_step.cpu().numpy(), rtol=0, atol=1e-5)
     host = ks.infer_host(pcm.pin_memory())
     np.testing.assert_allclose(host.numpy(), got, rtol=0, atol=1e-6)
+    # 16-bit PCM: x/32768 happens inside the MFCC kernel, same bits as the float32 call
+    i16 = (pcm * 32767).round().to(torch.int16)
+    from_float = ks((i16.float() / 32768.0).cuda())
+    assert torch.equal(ks(i16.cuda()), from_float)
+    assert torch.equal(ks.infer_host(i16.pin_memory()), from_float.cpu())
 
 
 def test_two_spotters_share_one_model():
