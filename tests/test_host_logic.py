@@ -153,3 +153,26 @@ def test_batchnorm_folding_matches_torch_eval():
     want = bn(conv(x))
     got = torch.nn.functional.conv2d(x, folded["c.weight"], folded["c.bias"], padding=1, groups=8)
     assert torch.allclose(got, want, atol=1e-5, rtol=1e-5)
+
+
+def test_bench_reference_arm_prints_one_json_line():
+    """bench.py contract: stdout carries exactly ONE JSON line (library chatter is routed to stderr); the
+    reference arm is the CPU port on the host cores and needs no GPU."""
+    import json
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "1",
+                        "--warmup", "0"], capture_output=True, text=True, timeout=300, cwd=root)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [ln for ln in r.stdout.splitlines() if ln.strip()]
+    assert len(lines) == 1, r.stdout
+    line = json.loads(lines[0])
+    assert line["impl"] == "reference" and line["unit"] == "clips/s" and line["value"] > 0
+    assert line["cpu_baseline"]["kind"] == "port" and line["cpu_baseline"]["cores"] >= 1
+    assert line["e2e"] == {"value": line["value"], "unit": "clips/s", "h2d_bytes_per_step": 0,
+                           "d2h_bytes_per_step": 0}
+    for key in ("metric", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling", "dtype",
+                "data", "config"):
+        assert key in line, key
