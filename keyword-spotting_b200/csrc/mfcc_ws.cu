@@ -54,15 +54,20 @@ constexpr int kWarpScratch = 2 * 16 * 17 * 16;     // bytes: two half-warp trans
 constexpr float kFEps = 2.220446049250313e-16f;
 
 
-// raw-sample access: the raw stage holds the clip's own sample type; int16 is scaled exactly like
-// librosa.load (x / 32768, audio_processor.py:145) when it is read
+// raw-sample access: the raw stage holds the clip's own sample type.  int16 samples are used as integers-in-
+// float: librosa.load's x / 32768 (audio_processor.py:145) is a power of two, so it commutes with every fp32
+// rounding of the pre-emphasis and the FFT (nothing here comes near the under/overflow range: |X| < 2^26) and
+// is applied once, as 2^-30, to the power spectrum - the same bits as converting first, 6 multiplies per
+// sample pair cheaper.
 __device__ __forceinline__ float2 ld_pair(const float* q) { return *reinterpret_cast<const float2*>(q); }
 __device__ __forceinline__ float ld_one(const float* q) { return *q; }
 __device__ __forceinline__ float2 ld_pair(const short* q) {
   const short2 s = *reinterpret_cast<const short2*>(q);
-  return make_float2((float)s.x * (1.0f / 32768.0f), (float)s.y * (1.0f / 32768.0f));
+  return make_float2((float)s.x, (float)s.y);
 }
-__device__ __forceinline__ float ld_one(const short* q) { return (float)*q * (1.0f / 32768.0f); }
+__device__ __forceinline__ float ld_one(const short* q) { return (float)*q; }
+template <typename T> __device__ __forceinline__ constexpr float power_scale() { return 1.0f; }
+template <> __device__ __forceinline__ constexpr float power_scale<short>() { return 1.0f / 1073741824.0f; }
 
 // T = float or short.  kLead = samples kept in front of a tile (16 bytes, so that the TMA destination of a
 // tile that starts inside the clip stays 16-byte aligned while sample s0 - 1 is available)
@@ -334,7 +339,7 @@ __global__ void __launch_bounds__(kWsThreads, 1) mfcc512_ws_kernel(const FastPar
         // ---- real-FFT split, two bins per step: k = l + 16 k2 and 256 - k ----
         const int partner = (lane & 16) | ((16 - l) & 15);
         const bool l0 = (l == 0);
-        const V sc = fsplat(1.0f / 2048.0f);
+        const V sc = fsplat(power_scale<T>() / 2048.0f);
 #pragma unroll
         for (int k2 = 0; k2 < 8; ++k2) {
           const CF zk = x16[Q16(k2)];
@@ -361,7 +366,7 @@ __global__ void __launch_bounds__(kWsThreads, 1) mfcc512_ws_kernel(const FastPar
         }
         if (l0) {  // bin 128 is its own mirror: |X[128]|^2 = |Z[128]|^2
           const CF z8 = x16[Q16(8)];
-          const V p8 = fmul(ffma(z8.im, z8.im, fmul(z8.re, z8.re)), fsplat(1.0f / 512.0f));
+          const V p8 = fmul(ffma(z8.im, z8.im, fmul(z8.re, z8.re)), fsplat(power_scale<T>() / 512.0f));
           s_P[128] = p8;
           esum = fadd(esum, p8);
         }
