@@ -169,6 +169,19 @@ def test_full_size_properties(proc):
     out = proc.extract_features(pcm, numcep=40, nfilt=40)
     assert tuple(out.shape) == (B, 99, 40) and bool(torch.isfinite(out).all())
     assert torch.equal(out[:1024], out[-1024:]) and torch.equal(out[1024:2048], out[:1024])
+    # every copy of the 1024 clips, wherever its tiles landed in the persistent grid (tile swap between
+    # neighbouring CTAs, both halves of a clip, first and last iteration), gives the same bits
+    assert bool((out.view(B // 1024, 1024, 99, 40) == out[:1024].unsqueeze(0)).all())
+    del out
+    # an odd clip count leaves the last CTA pair without a partner tile to swap
+    odd = proc.extract_features(pcm[:4097], numcep=40, nfilt=40)
+    ref = proc.extract_features(base, numcep=40, nfilt=40)
+    assert torch.equal(odd[:4096].view(4, 1024, 99, 40), ref.unsqueeze(0).expand(4, -1, -1, -1))
+    assert torch.equal(odd[4096], ref[0])
+    i16 = (base * 32767).round().to(torch.int16)
+    out16 = proc.extract_features(i16.repeat(8, 1), numcep=40, nfilt=40)
+    assert torch.equal(out16.view(8, 1024, 99, 40), proc.extract_features(i16, numcep=40, nfilt=40).unsqueeze(0).expand(8, -1, -1, -1))
+    out = proc.extract_features(pcm[:2048], numcep=40, nfilt=40)
     idx = [0, 511, 1023]
     want = psf_mfcc.extract_features_batch(base[idx].cpu().numpy(), numcep=40, nfilt=40)
     _close(out[idx].cpu().numpy(), want, "full-size sample")
