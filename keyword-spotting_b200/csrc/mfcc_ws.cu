@@ -45,6 +45,10 @@ struct FastParams {
 // number of resident compute warps.  ptxas needs 128 registers for the compute path, i.e. 16 warps per SM:
 // 13 compute warps (tile = 52 frames, two tiles per 99-frame clip, 25 of 26 warp slots busy) + 2 service
 // warps.  (Two CTAs of 5 + 1 warps, the previous layout, kept 10 compute warps resident: 10.8 M clips/s.)
+// Warp slots are handed out consecutively (tools/warpslot_probe.cu) and slot % 4 is the scheduler: 12 compute
+// warps are three per scheduler, the 13th is a fourth one on one scheduler and makes its tile 19 % slower
+// for 8 % more work - at this occupancy the kernel is at a throughput plateau, so a 14th
+// compute warp or tiles that ignore clip ends would not help (both measured).
 constexpr int kCWarps = 13;                        // compute warps
 constexpr int kSvcWarps = 2;                       // service warps: TMEM lanes 0..31 and 32..63
 constexpr int kTileFrames = kCWarps * 4;           // 52 frames per tile = rows of the DCT GEMM
