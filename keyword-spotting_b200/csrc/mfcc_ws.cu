@@ -47,8 +47,8 @@ struct FastParams {
 // warps.  (Two CTAs of 5 + 1 warps, the previous layout, kept 10 compute warps resident: 10.8 M clips/s.)
 // Warp slots are handed out consecutively (tools/warpslot_probe.cu) and slot % 4 is the scheduler: 12 compute
 // warps are three per scheduler, the 13th is a fourth one on one scheduler and makes its tile 19 % slower
-// for 8 % more work - at this occupancy the kernel is at a throughput plateau, so a 14th
-// compute warp or tiles that ignore clip ends would not help (both measured).
+// for 8 % more work - at this occupancy the kernel is at a throughput plateau: tiles that
+// ignore clip ends, with 12 or 13 always-busy warps, were measured and are no faster.
 constexpr int kCWarps = 13;                        // compute warps
 constexpr int kSvcWarps = 2;                       // service warps: TMEM lanes 0..31 and 32..63
 constexpr int kTileFrames = kCWarps * 4;           // 52 frames per tile = rows of the DCT GEMM
