@@ -87,6 +87,7 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
 // bounded wait: a protocol bug traps instead of hanging the GPU
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   uint32_t done = 0;
+#pragma unroll 1
   for (int spin = 0; spin < (1 << 24); ++spin) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
@@ -103,6 +104,7 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
 // polling does not take issue slots from the compute warps
 __device__ __forceinline__ void mbar_wait_idle(uint32_t bar, uint32_t parity) {
   uint32_t done = 0;
+#pragma unroll 1
   for (int spin = 0; spin < (1 << 22); ++spin) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
