@@ -216,14 +216,16 @@ __global__ void __launch_bounds__(kWsThreads, 1) mfcc512_ws_kernel(const FastPar
         }
         tc_wait_ld();
         tc_fence_before();
+        const int row = warp * 32 + lane;
+        const int f = t * kTileFrames + row;
+        // c0 of this tile is read BEFORE warp 1 releases the accumulator: its release lets the next tile's MMAs
+        // go, and their completion lets the compute warps overwrite this half of s_c0 two tiles on
+        const float c0 = (row < kTileFrames) ? s_c0[(it & 1) * kTileFrames + row] : 0.f;
         if (warp != 0) {
           __syncwarp();
           if (lane == 0) mbar_arrive(bar_epi);
         }
-        const int row = warp * 32 + lane;
-        const int f = t * kTileFrames + row;
         if (row < kTileFrames && f < p.nframes) {
-          const float c0 = s_c0[(it & 1) * kTileFrames + row];
           v[0] = p.append_energy ? c0 : v[0] + c0;
           float* o = p.out + ((size_t)clip * p.nframes + f) * p.ncep;
           if ((p.ncep & 3) == 0) {
