@@ -72,6 +72,10 @@ int kws_destroy(kws_handle_t h);
 /* number of this library's kernels launched through the handle since creation */
 int64_t kws_launch_count(kws_handle_t h);
 
+/* measurement aid (bench.py roofline): fp32 FMA throughput of the handle's device in TFLOP/s, scalar FFMA
+ * and packed FFMA2 chains, best of four timed launches.  No reference counterpart. */
+int kws_probe_fp32_tflops(kws_handle_t h, double* ffma_tflops, double* ffma2_tflops);
+
 /* ---- host-side helpers (pure CPU arithmetic, usable without a GPU) ------------------ */
 /* psf sigproc.round_half_up (decimal ROUND_HALF_UP) */
 int64_t kws_round_half_up(double v);

@@ -48,6 +48,7 @@ SIGNATURES = {
     "kws_create": (_i32, [_i32, C.POINTER(_vp)]),
     "kws_destroy": (_i32, [_vp]),
     "kws_launch_count": (_i64, [_vp]),
+    "kws_probe_fp32_tflops": (_i32, [_vp, C.POINTER(_dbl), C.POINTER(_dbl)]),
     "kws_feature_config_default": (None, [C.POINTER(FeatureConfig)]),
     "kws_round_half_up": (_i64, [_dbl]),
     "kws_num_frames": (_i64, [_i64, _i64, _i64]),

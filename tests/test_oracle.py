@@ -146,3 +146,75 @@ def test_crnn_oracle_matches_torch_gru():
     want = fc(gru(seq)[0][:, -1])
     got = crnn_ref.forward(sd, x)
     assert torch.allclose(got, want, atol=1e-10)
+
+
+def test_psf_front_stages_pinned_by_reference_sigproc(golden_dir):
+    """psf stages 1-5 (float32 pre-emphasis, float64 framing with a rectangular window, |rFFT|^2/512,
+    frame energy) of the restatement against vectors produced by RUNNING the reference's own torch
+    sigproc helpers on the parity set (tests/golden/make_golden.py::golden_psf_front)."""
+    from kws_b200.utils import synth  # noqa: F401  (pure numpy/torch-CPU generator)
+    g = np.load(os.path.join(golden_dir, "psf_front_parity8.npz"))
+    pcm = synth.parity_pcm(8).numpy()
+    rows = g["frame_rows"]
+    for b, x in enumerate(pcm):
+        y = psf_mfcc.preemphasis(x, 0.97)
+        assert y.dtype == np.float32
+        np.testing.assert_allclose(y.astype(np.float64).sum(), g["preemph_sum"][b], rtol=1e-12, atol=1e-12)
+        ps = psf_mfcc.powspec(psf_mfcc.framesig(y, 400, 160), 512)
+        scale = max(float(g["energy"][b].max()), 1e-30)
+        np.testing.assert_allclose(ps[rows], g["pspec_rows"][b], rtol=1e-9, atol=1e-12 * scale)
+        np.testing.assert_allclose(ps.sum(axis=1), g["energy"][b], rtol=1e-10, atol=1e-12 * scale)
+        # ... and through the restated fbank(): its energy output is that row sum with 0 -> eps
+        _, energy = psf_mfcc.fbank(x, nfilt=40)
+        want = np.where(g["energy"][b] == 0, psf_mfcc.EPS, g["energy"][b])
+        np.testing.assert_allclose(energy, want, rtol=1e-10, atol=1e-12 * scale)
+
+
+def test_train_step_oracle_is_torch_adam():
+    """oracle/dscnn_ref.cross_entropy_train_step re-implements Adam by hand; three of its steps must
+    equal three steps of torch.optim.Adam(lr=1e-3) + CrossEntropyLoss, which is what the reference builds
+    (kws/libs/training.py:112-123)."""
+    sd = dscnn_ref.init_state_dict(seed=4, dtype=torch.float64)
+    g = torch.Generator().manual_seed(5)
+    xs = torch.randn(3, 6, 1, 99, 10, generator=g, dtype=torch.float64)
+    ys = torch.randint(0, 12, (3, 6), generator=g)
+    params = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+    opt = torch.optim.Adam(list(params.values()), lr=1e-3)
+    crit = torch.nn.CrossEntropyLoss()
+    cur, state = sd, None
+    for i in range(3):
+        opt.zero_grad()
+        loss_t = crit(dscnn_ref.forward(params, xs[i]), ys[i])
+        loss_t.backward()
+        opt.step()
+        loss_o, _, cur, state = dscnn_ref.cross_entropy_train_step(cur, xs[i], ys[i], state)
+        assert abs(float(loss_t) - float(loss_o)) < 1e-12
+    for k in sd:
+        np.testing.assert_allclose(cur[k].numpy(), params[k].detach().numpy(), rtol=1e-9, atol=1e-12)
+
+
+def test_train_step_oracle_matches_reference_trainer(golden_dir):
+    """The same oracle against one epoch (four batches) of the REFERENCE's own KWSTrainer.train_epoch
+    (kws/libs/training.py:266-345), run on CPU by tests/golden/make_golden.py::golden_trainer."""
+    g = np.load(os.path.join(golden_dir, "ref_trainer_epoch.npz"))
+    sd = {k[4:]: torch.from_numpy(g[k]) for k in g.files if k.startswith("sd0.")}
+    want = {k[4:]: g[k] for k in g.files if k.startswith("sd1.")}
+    xs, ys = torch.from_numpy(g["x"]), torch.from_numpy(g["y"])
+    cur, state, losses = sd, None, []
+    for i in range(xs.shape[0]):
+        loss, _, cur, state = dscnn_ref.cross_entropy_train_step(cur, xs[i], ys[i], state)
+        losses.append(float(loss))
+    assert abs(np.mean(losses) - float(g["epoch_loss"])) < 1e-5
+    for k in want:   # fp32 CPU training: thread-order rounding only
+        np.testing.assert_allclose(cur[k].numpy(), want[k], rtol=2e-4, atol=2e-6)
+
+
+def test_reference_checkpoint_golden_layout(golden_dir):
+    """The checkpoint written by the reference's Trainer.save_checkpoint (training.py:199-216) has the
+    layout load_reference_checkpoint() expects and holds the post-epoch parameters."""
+    ck = torch.load(os.path.join(golden_dir, "ref_trainer_checkpoint.pth"), map_location="cpu", weights_only=False)
+    assert set(ck) == {"model_state_dict", "optimizer_state_dict", "metrics", "config", "epoch"}
+    g = np.load(os.path.join(golden_dir, "ref_trainer_epoch.npz"))
+    for k, v in ck["model_state_dict"].items():
+        np.testing.assert_array_equal(v.numpy(), g["sd1." + k])
+    assert ck["optimizer_state_dict"]["param_groups"][0]["lr"] == 1e-3
