@@ -95,6 +95,8 @@ int kws_features_configure(kws_handle_t h, const kws_feature_config* cfg);
 /* output columns = min(numcep, nfilt) */
 int kws_features_ncep(kws_handle_t h);
 /* pcm_dev: [B, N] float32 rows `pcm_stride` floats apart; out_dev: [B, nframes, ncep] float32.
+ * Alignment: none required.  16-byte aligned pcm_dev / out_dev with pcm_stride, N and the hop multiples of
+ * 4 samples (8 for int16) run on the TMA-fed tensor-core kernel; anything else takes the generic kernel.
  * Rows may overlap (1 <= pcm_stride < N): B sliding windows of one long recording, hop = pcm_stride, are
  * read in place -- the batch form of the reference's 1 s sliding-window inference concept
  * (kws/inference/inference_local.py:114-188).  The same holds for kws_pcm_to_logits. */
@@ -104,6 +106,8 @@ int kws_mfcc(kws_handle_t h, const float* pcm_dev, int64_t B, int64_t N, int64_t
 int kws_logfbank(kws_handle_t h, const float* pcm_dev, int64_t B, int64_t N, int64_t pcm_stride,
                  float* out_dev, void* stream);
 /* int16 PCM ingest (librosa.load scaling x/32768, audio_processor.py:145) fused in front */
+int kws_logfbank_i16(kws_handle_t h, const int16_t* pcm_dev, int64_t B, int64_t N, int64_t pcm_stride,
+                     float* out_dev, void* stream);
 int kws_mfcc_i16(kws_handle_t h, const int16_t* pcm_dev, int64_t B, int64_t N, int64_t pcm_stride,
                  float* out_dev, void* stream);
 /* end-to-end with HOST buffers: chunked H2D -> kernel -> D2H, double-buffered on two streams.
@@ -176,7 +180,8 @@ int kws_crnn_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t 
  * the caller between the two calls (grad_scale = 1/world_size folds the mean into Adam). ------- */
 int64_t kws_train_num_params(kws_handle_t h);
 /* feats_dev [B,1,T,F] float32, labels_dev [B] int64 -> grads_dev (overwritten), loss_dev[1] (mean CE),
- * logits_out_dev [B,num_classes] or NULL */
+ * logits_out_dev [B,num_classes] or NULL.  A label outside [0, num_classes) (torch raises there) contributes no
+ * gradient and makes loss_dev NaN. */
 int kws_train_forward_backward(kws_handle_t h, const float* params_dev, const float* feats_dev,
                                const int64_t* labels_dev, int64_t B, int64_t T, int64_t F, float* grads_dev,
                                float* loss_dev, float* logits_out_dev, void* stream);

@@ -59,6 +59,7 @@ SIGNATURES = {
     "kws_features_ncep": (_i32, [_vp]),
     "kws_mfcc": (_i32, [_vp, _vp, _i64, _i64, _i64, _vp, _vp]),
     "kws_logfbank": (_i32, [_vp, _vp, _i64, _i64, _i64, _vp, _vp]),
+    "kws_logfbank_i16": (_i32, [_vp, _vp, _i64, _i64, _i64, _vp, _vp]),
     "kws_mfcc_i16": (_i32, [_vp, _vp, _i64, _i64, _i64, _vp, _vp]),
     "kws_mfcc_host": (_i32, [_vp, _vp, _i64, _i64, _vp]),
     "kws_sigproc_preemphasis": (_i32, [_i32, _vp, _vp, _i64, _i64, _dbl, _vp]),

@@ -122,9 +122,7 @@ class AudioProcessor:
         if B > 0:
             stream = _native.current_stream_ptr(self._dev_index())
             if logmel:
-                if i16:
-                    x = x.to(torch.float32) / 32768.0
-                fn = lib.kws_logfbank
+                fn = lib.kws_logfbank_i16 if i16 else lib.kws_logfbank
             else:
                 fn = lib.kws_mfcc_i16 if i16 else lib.kws_mfcc
             with torch.cuda.device(self.device):

@@ -5,9 +5,30 @@
 #include <algorithm>
 #include <cstring>
 
+#include <map>
+#include <mutex>
+#include <utility>
+
 #include "common.cuh"
 
 using namespace kws;
+
+namespace kws {
+int ensure_dyn_smem_impl(const void* func, size_t bytes, bool max_carveout) {
+  static std::mutex mu;
+  static std::map<std::pair<const void*, int>, size_t> granted;
+  int dev = 0;
+  KWS_CUDA(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> lock(mu);
+  size_t& g = granted[{func, dev}];
+  if (bytes <= g) return KWS_OK;
+  KWS_CUDA(cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  if (max_carveout)
+    KWS_CUDA(cudaFuncSetAttribute(func, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+  g = bytes;
+  return KWS_OK;
+}
+}  // namespace kws
 
 namespace {
 
@@ -91,6 +112,8 @@ int kws_destroy(kws_handle_t h) {
     if (h->d_stage_in[i]) cudaFree(h->d_stage_in[i]);
     if (h->d_stage_out[i]) cudaFree(h->d_stage_out[i]);
   }
+  for (int i = 0; i < 4; ++i)
+    if (h->ev[i]) cudaEventDestroy(h->ev[i]);
   if (h->d_feat_tmp) cudaFree(h->d_feat_tmp);
   if (h->train.base) cudaFree(h->train.base);
   delete h;
@@ -118,6 +141,11 @@ int kws_mfcc(kws_handle_t h, const float* pcm_dev, int64_t B, int64_t N, int64_t
 int kws_logfbank(kws_handle_t h, const float* pcm_dev, int64_t B, int64_t N, int64_t pcm_stride,
                  float* out_dev, void* stream) {
   return launch_mfcc(h, pcm_dev, false, B, N, pcm_stride, out_dev, kModeLogMel, (cudaStream_t)stream);
+}
+
+int kws_logfbank_i16(kws_handle_t h, const int16_t* pcm_dev, int64_t B, int64_t N, int64_t pcm_stride,
+                     float* out_dev, void* stream) {
+  return launch_mfcc(h, pcm_dev, true, B, N, pcm_stride, out_dev, kModeLogMel, (cudaStream_t)stream);
 }
 
 int kws_mfcc_i16(kws_handle_t h, const int16_t* pcm_dev, int64_t B, int64_t N, int64_t pcm_stride,
@@ -177,12 +205,13 @@ static int pcm_to_logits_impl(kws_handle_t h, const void* pcm_dev, bool is_i16, 
   const int64_t nframes = kws_num_frames(N, h->feat.cfg.frame_len, h->feat.cfg.frame_step);
   const int64_t F = h->feat.ncep;
   const size_t need = (size_t)B * nframes * F * 4;
-  if (need > h->feat_tmp_bytes) {
+  if (need > h->feat_tmp_bytes) {  // grows geometrically: a sweep of growing batches reallocates O(log) times
+    const size_t want = h->feat_tmp_bytes ? std::max(need, std::min<size_t>(h->feat_tmp_bytes * 2, need + (need >> 1))) : need;
     if (h->d_feat_tmp) KWS_CUDA(cudaFree(h->d_feat_tmp));
     h->d_feat_tmp = nullptr;
     h->feat_tmp_bytes = 0;
-    KWS_CUDA(cudaMalloc((void**)&h->d_feat_tmp, need));
-    h->feat_tmp_bytes = need;
+    KWS_CUDA(cudaMalloc((void**)&h->d_feat_tmp, want));
+    h->feat_tmp_bytes = want;
   }
   int rc = launch_mfcc(h, pcm_dev, is_i16, B, N, pcm_stride, h->d_feat_tmp, kModeMfcc, (cudaStream_t)stream);
   if (rc) return rc;
@@ -217,8 +246,8 @@ static int pcm_to_logits_host_impl(kws_handle_t h, const void* pcm_host, bool is
   if (rc) return rc;
   // the feature scratch and the model workspace are shared, so the two streams only overlap
   // copies with compute: compute of chunk i+1 waits for compute of chunk i.
-  cudaEvent_t done = nullptr;
-  KWS_CUDA(cudaEventCreateWithFlags(&done, cudaEventDisableTiming));
+  if (!h->ev[0]) KWS_CUDA(cudaEventCreateWithFlags(&h->ev[0], cudaEventDisableTiming));  // cached on the handle
+  cudaEvent_t done = h->ev[0];
   int i = 0;
   for (int64_t b0 = 0; b0 < B; b0 += chunk, ++i) {
     const int64_t nb = std::min<int64_t>(chunk, B - b0);
@@ -228,13 +257,12 @@ static int pcm_to_logits_host_impl(kws_handle_t h, const void* pcm_host, bool is
                              cudaMemcpyHostToDevice, st));
     if (i > 0) KWS_CUDA(cudaStreamWaitEvent(st, done, 0));
     rc = pcm_to_logits_impl(h, h->d_stage_in[s], is_i16, nb, N, N, (float*)h->d_stage_out[s], st);
-    if (rc) { cudaEventDestroy(done); return rc; }
+    if (rc) return rc;
     KWS_CUDA(cudaEventRecord(done, st));
     KWS_CUDA(cudaMemcpyAsync(logits_host + b0 * K, h->d_stage_out[s], (size_t)nb * K * 4, cudaMemcpyDeviceToHost, st));
   }
   KWS_CUDA(cudaStreamSynchronize(h->s_copy[0]));
   KWS_CUDA(cudaStreamSynchronize(h->s_copy[1]));
-  cudaEventDestroy(done);
   return KWS_OK;
 }
 

@@ -40,6 +40,14 @@ int fail(int code, const char* fmt, ...);
                          __FILE__, __LINE__);                                               \
   } while (0)
 
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is sticky per (function, device): issue it only the first
+// time, or when a launch needs more than was granted before (capi.cu keeps the table)
+int ensure_dyn_smem_impl(const void* func, size_t bytes, bool max_carveout);
+template <typename K>
+inline int ensure_dyn_smem(K kern, size_t bytes, bool max_carveout = false) {
+  return ensure_dyn_smem_impl(reinterpret_cast<const void*>(kern), bytes, max_carveout);
+}
+
 #define KWS_CHECK_LAUNCH(h)                                                       \
   do {                                                                            \
     cudaError_t _e = cudaGetLastError();                                          \

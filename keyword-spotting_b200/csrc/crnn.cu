@@ -1049,9 +1049,9 @@ int kws_crnn_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t 
   const int gnb = H == 64 ? kGruNB : kGruNBg;
   const size_t gru_smem = ((size_t)H * 3 * H + 2 * (size_t)gnb * H) * 4;
   if (H == 64)
-    KWS_CUDA(cudaFuncSetAttribute(gru_recurrent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gru_smem));
+    if (int rc_ = ensure_dyn_smem(gru_recurrent_kernel, (size_t)gru_smem)) return rc_;
   else
-    KWS_CUDA(cudaFuncSetAttribute(gru_recurrent_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gru_smem));
+    if (int rc_ = ensure_dyn_smem(gru_recurrent_generic_kernel, (size_t)gru_smem)) return rc_;
   for (int64_t b0 = 0; b0 < B; b0 += chunk) {
     const int64_t nb = (B - b0 < chunk) ? B - b0 : chunk;
     // tensor-core conv1 writes tile-major, which only the step-major tensor-core projection reads
@@ -1059,7 +1059,7 @@ int kws_crnn_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t 
                          (reinterpret_cast<uintptr_t>(feats_dev) & 15) == 0;   // 16-byte feature loads
     if (conv_tc) {
       Conv1TcParams cp{feats_dev + b0 * T * F, m.d_c1img, m.d_conv_b, d_conv, nb, (int)T, H1};
-      KWS_CUDA(cudaFuncSetAttribute(conv1_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kC1Smem));
+      if (int rc_ = ensure_dyn_smem(conv1_tc_kernel, (size_t)kC1Smem)) return rc_;
       const long long nt = (nb + 127) / 128 * H1;
       conv1_tc_kernel<<<(unsigned)(nt < h->sm_count ? nt : h->sm_count), kC1Threads, kC1Smem, st>>>(cp);
       KWS_CHECK_LAUNCH(h);
@@ -1075,7 +1075,7 @@ int kws_crnn_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t 
       const bool tc_rec = H == 64 && m.d_wimg[l] && m.d_whimg[l];   // both halves of the layer on the tensor core
       if (m.d_wimg[l] && dsmem <= 227 * 1024) {
         DenseParams dp{x, m.d_wimg[l], m.d_bih[l], d_xp, M, 3 * H, I, (l == 0 && conv_tc) ? 1 : 0, tc_rec ? H1 : 0};
-        KWS_CUDA(cudaFuncSetAttribute(dense_gemm_tf32x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dsmem));
+        if (int rc_ = ensure_dyn_smem(dense_gemm_tf32x3_kernel, (size_t)dsmem)) return rc_;
         const long long nt = tc_rec ? (nb + 127) / 128 * H1 : (M + 127) / 128;
         dense_gemm_tf32x3_kernel<<<(unsigned)(nt < h->sm_count ? nt : h->sm_count), (kDProd + 1) * 32, dsmem, st>>>(dp);
       } else if (I % 16 == 0 && (3 * H) % 64 == 0) {
@@ -1089,7 +1089,7 @@ int kws_crnn_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t 
       const bool more = l + 1 < m.layers;
       if (tc_rec) {
         GruTcParams gp{d_xp, m.d_whimg[l], m.d_bhh[l], more ? d_seq : nullptr, d_last, nb, H1};
-        KWS_CUDA(cudaFuncSetAttribute(gru_recurrent_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kGtSmem));
+        if (int rc_ = ensure_dyn_smem(gru_recurrent_tc_kernel, (size_t)kGtSmem)) return rc_;
         gru_recurrent_tc_kernel<<<(unsigned)((nb + 127) / 128), 288, kGtSmem, st>>>(gp);
       } else if (H == 64)
         gru_recurrent_kernel<<<(unsigned)((nb + kGruNB - 1) / kGruNB), 256, gru_smem, st>>>(

@@ -426,7 +426,7 @@ int launch_mfcc(kws_handle_t h, const void* pcm_dev, bool is_i16, int64_t B, int
   static_assert(2064 + (2 * (kMaxFilt + 1) + kMaxFilt) * 8 <= kScratchHalf, "scratch layout overflow");
 
   auto kern = is_i16 ? mfcc512_kernel<true> : mfcc512_kernel<false>;
-  KWS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+  if (int rc = ensure_dyn_smem(kern, smem_bytes)) return rc;
   int occ = 0;
   KWS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kThreads, smem_bytes));
   if (occ < 1) return fail(KWS_ERR_CUDA, "mfcc kernel does not fit on an SM");

@@ -498,6 +498,9 @@ int launch_mfcc_fast(kws_handle_t h, const void* pcm_dev, bool is_i16, int64_t B
   if ((hop & amask) != 0 || (N & amask) != 0 || (pcm_stride & amask) != 0 ||
       (reinterpret_cast<size_t>(pcm_dev) & 15) != 0)
     return 0;
+  // the epilogue writes rows with float4 stores when ncep % 4 == 0: the output must then be 16-byte aligned
+  // (an offset into a larger feature buffer need not be) - otherwise the generic kernel's scalar stores
+  if ((t.ncep & 3) == 0 && mode == kModeMfcc && (reinterpret_cast<size_t>(out_dev) & 15) != 0) return 0;
   if (N >= (1ll << 30)) return 0;
   constexpr int ROUNDS = 3;
   FastParams p{};
@@ -547,8 +550,7 @@ int launch_mfcc_fast(kws_handle_t h, const void* pcm_dev, bool is_i16, int64_t B
   if ((size_t)p.off_a + (size_t)(kAGroups + 16) * sbo > smem_bytes || smem_bytes > 227 * 1024 - 256) return 0;
 
   auto kern = is_i16 ? mfcc512_ws_kernel<400, ROUNDS, short> : mfcc512_ws_kernel<400, ROUNDS, float>;
-  KWS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
-  KWS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+  if (int rc = ensure_dyn_smem(kern, smem_bytes, true)) return rc;
   long long grid = (long long)h->sm_count;  // one persistent CTA per SM
   if (grid > p.total_tiles) grid = p.total_tiles;
   kern<<<(unsigned)grid, kWsThreads, smem_bytes, stream>>>(p);

@@ -427,7 +427,7 @@ int launch_conv1_relu(kws_handle_t h, const float* in, float* out, const float* 
     if (smem <= 100 * 1024 && npatch <= (size_t)16 * kC1Threads) {
       const long long ntiles = B * ((H1 + RB - 1) / RB);
       long long g = ntiles < h->sm_count * 12LL ? ntiles : h->sm_count * 12LL;
-      KWS_CUDA(cudaFuncSetAttribute(conv1_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      if (int rc_ = ensure_dyn_smem(conv1_tile_kernel, (size_t)smem)) return rc_;
       conv1_tile_kernel<<<(unsigned)g, kC1Threads, smem, st>>>(in, out, w_packed, bias, B, T, F, H1, W1, C, RB);
       KWS_CHECK_LAUNCH(h);
       return KWS_OK;
@@ -459,7 +459,7 @@ int train_forward_layers(kws_handle_t h, const float* feats_dev, int64_t B, int 
     if (C == 64) {
       const long long nt = (npix + kB64Pix - 1) / kB64Pix;
       const long long g64 = nt < h->sm_count * 3LL ? nt : h->sm_count * 3LL;
-      KWS_CUDA(cudaFuncSetAttribute(dsblock64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kB64Smem));
+      if (int rc_ = ensure_dyn_smem(dsblock64_kernel, (size_t)kB64Smem)) return rc_;
       dsblock64_kernel<<<(unsigned)g64, 256, kB64Smem, st>>>(w.L[i], w.L[i + 1], m.d_dw_w + (size_t)i * 9 * C,
                                                             m.d_dw_b + (size_t)i * C, m.d_pw_w + (size_t)i * C * C,
                                                             m.d_pw_b + (size_t)i * C, B, H, W, w.D[i]);

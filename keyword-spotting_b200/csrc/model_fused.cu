@@ -638,7 +638,7 @@ static int launch_fused_t(kws_handle_t h, const FusedParams& p, cudaStream_t str
   const size_t smem_bytes = (size_t)L::off_feat + L::CL * L::feat_floats(p.T) * 4;
   if (smem_bytes > 227 * 1024) return 0;
   auto kern = dscnn_fused_kernel<F, NPIX, PACK>;
-  KWS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+  if (int rc = ensure_dyn_smem(kern, smem_bytes)) return rc;
   const long long ngroups = (p.B + L::CL - 1) / L::CL;
   if (ngroups > 0x7fffffffLL / 64) return 0;
   long long grid = h->sm_count;

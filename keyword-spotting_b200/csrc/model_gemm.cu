@@ -425,8 +425,8 @@ int launch_dscnn_gemm(kws_handle_t h, const float* feats_dev, int64_t B, int T, 
   const size_t smem_bytes = 2 * kGABytes + 2 * (size_t)(g->npad / 8) * kGSbo + (size_t)9 * ((C + kGKC - 1) / kGKC * kGKC) * 4 +
                             (size_t)3 * patch_bytes;
   if (smem_bytes > 227 * 1024) return 0;
-  KWS_CUDA(cudaFuncSetAttribute(dscnn_gemm_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
-  KWS_CUDA(cudaFuncSetAttribute(dscnn_gemm_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+  if (int rc = ensure_dyn_smem(dscnn_gemm_kernel<0>, smem_bytes)) return rc;
+  if (int rc = ensure_dyn_smem(dscnn_gemm_kernel<1>, smem_bytes)) return rc;
   const int ctas_per_sm = (g->tmem_cols <= 256 && smem_bytes <= 100 * 1024) ? 2 : 1;
   GemmParams p{};
   p.C = C;

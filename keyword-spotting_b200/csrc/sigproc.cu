@@ -197,11 +197,11 @@ int kws_sigproc_spec(int dtype, const void* frames_dev, int64_t R, int64_t L, in
     const size_t sm = (size_t)nfft * 2 * es;
     const int threads = nfft / 2 < 64 ? 64 : (nfft / 2 > 512 ? 512 : (int)nfft / 2);
     if (dtype == 0) {
-      KWS_CUDA(cudaFuncSetAttribute(spec_pow2_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+      if (int rc_ = ensure_dyn_smem(spec_pow2_kernel<float>, (size_t)sm)) return rc_;
       spec_pow2_kernel<float><<<grid, threads, sm, st>>>((const float*)frames_dev, (float*)out_dev, R, (int)L,
                                                          (int)nfft, lg, power);
     } else {
-      KWS_CUDA(cudaFuncSetAttribute(spec_pow2_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+      if (int rc_ = ensure_dyn_smem(spec_pow2_kernel<double>, (size_t)sm)) return rc_;
       spec_pow2_kernel<double><<<grid, threads, sm, st>>>((const double*)frames_dev, (double*)out_dev, R, (int)L,
                                                           (int)nfft, lg, power);
     }
@@ -209,10 +209,10 @@ int kws_sigproc_spec(int dtype, const void* frames_dev, int64_t R, int64_t L, in
     const size_t sm = (size_t)(L < nfft ? L : nfft) * es;
     if (sm > 200 * 1024) return fail(KWS_ERR_INVALID, "frame too long for the DFT kernel");
     if (dtype == 0) {
-      KWS_CUDA(cudaFuncSetAttribute(spec_dft_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+      if (int rc_ = ensure_dyn_smem(spec_dft_kernel<float>, (size_t)sm)) return rc_;
       spec_dft_kernel<float><<<grid, 256, sm, st>>>((const float*)frames_dev, (float*)out_dev, R, (int)L, (int)nfft, power);
     } else {
-      KWS_CUDA(cudaFuncSetAttribute(spec_dft_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+      if (int rc_ = ensure_dyn_smem(spec_dft_kernel<double>, (size_t)sm)) return rc_;
       spec_dft_kernel<double><<<grid, 256, sm, st>>>((const double*)frames_dev, (double*)out_dev, R, (int)L, (int)nfft, power);
     }
   }

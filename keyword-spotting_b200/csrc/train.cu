@@ -92,10 +92,18 @@ __global__ void ce_fc_bwd_kernel(const float* __restrict__ logits, const long lo
       for (int k = 1; k < K; ++k) mx = fmaxf(mx, lg[k]);
       float se = 0.f;
       for (int k = 0; k < K; ++k) se += expf(lg[k] - mx);
-      const int y = (int)labels[b];
+      const long long yl = labels[b];
       const float lse = mx + logf(se);
-      for (int k = 0; k < K; ++k) s_dl[k] = (expf(lg[k] - lse) - (k == y ? 1.f : 0.f)) * invB;
-      lsum += (lse - lg[y]) * invB;
+      if (yl < 0 || yl >= K) {
+        // torch's CrossEntropyLoss raises on a label outside [0, K) (ignore_index is not part of the reference
+        // step, training.py:115); a kernel cannot: the sample contributes no gradient and the loss turns NaN
+        for (int k = 0; k < K; ++k) s_dl[k] = 0.f;
+        lsum = __int_as_float(0x7fc00000);
+      } else {
+        const int y = (int)yl;
+        for (int k = 0; k < K; ++k) s_dl[k] = (expf(lg[k] - lse) - (k == y ? 1.f : 0.f)) * invB;
+        lsum += (lse - lg[y]) * invB;
+      }
     }
     __syncthreads();
     const float pv = pooled[b * C + c];
@@ -456,7 +464,7 @@ int kws_train_forward_backward(kws_handle_t h, const float* params_dev, const fl
     KWS_CHECK_LAUNCH(h);
   }
   const size_t pw_smem = kPwSmem;
-  KWS_CUDA(cudaFuncSetAttribute(pw_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pw_smem));
+  if (int rc_ = ensure_dyn_smem(pw_bwd_kernel, (size_t)pw_smem)) return rc_;
   const float* dout = nullptr;
   for (int l = nb - 1; l >= 0; --l) {
     const int H = H1 + 2 * l, W = W1 + 2 * l;  // block input size; output is (H+2) x (W+2)

@@ -186,3 +186,35 @@ def test_full_size_properties(proc):
     want = psf_mfcc.extract_features_batch(base[idx].cpu().numpy(), numcep=40, nfilt=40)
     _close(out[idx].cpu().numpy(), want, "full-size sample")
     assert proc.launch_count() > 0
+
+
+def test_int16_logfbank_against_oracle(proc):
+    """kws_logfbank_i16 (no eager int16 -> float32 detour in the Python layer any more) against the float64
+    oracle on x/32768, not against the float kernel alone."""
+    g = torch.Generator().manual_seed(5)
+    i16 = torch.randint(-20000, 20000, (3, 16000), generator=g, dtype=torch.int16)
+    l0 = proc.launch_count()
+    got = proc.extract_logfbank(i16.cuda(), nfilt=40).cpu().numpy()
+    assert proc.launch_count() - l0 == 1                  # one kernel, no conversion pass
+    as_float = i16.numpy().astype(np.float32) / 32768.0
+    want = np.stack([psf_mfcc.logfbank(x, nfilt=40) for x in as_float])
+    _close(got, want, "int16 log-mel")
+
+
+def test_c_abi_unaligned_output_pointer(proc):
+    """ADVICE r1: a C-ABI caller may pass a 4-byte aligned output (an offset into a larger feature buffer);
+    the TMA-fed kernel's float4 row stores must not be used then."""
+    import ctypes as C
+
+    from kws_b200 import _native
+    pcm = synth.uniform_pcm(5, seed=9).cuda()
+    ref = proc.extract_features(pcm, numcep=40, nfilt=40)
+    plan = proc._plan(16000, 40, 0.025, 0.01, 40)
+    buf = torch.zeros(5 * 99 * 40 + 8, dtype=torch.float32, device="cuda")
+    for off in (1, 2, 3):
+        out = buf[off:off + 5 * 99 * 40]
+        assert out.data_ptr() % 16 != 0
+        _native.check(_native.lib().kws_mfcc(plan.handle.ptr, C.c_void_p(pcm.data_ptr()), 5, 16000, 16000,
+                                             C.c_void_p(out.data_ptr()), _native.current_stream_ptr(0)))
+        torch.cuda.synchronize()
+        torch.testing.assert_close(out.view(5, 99, 40), ref, rtol=1e-3, atol=1e-4)

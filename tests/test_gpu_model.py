@@ -209,3 +209,64 @@ def test_two_spotters_share_one_model():
     two_step = m(proc.extract_features(pcm, numcep=10, nfilt=26).unsqueeze(1))
     np.testing.assert_allclose(a10.cpu().numpy(), two_step.cpu().numpy(), rtol=0, atol=1e-5)
     assert (a10 - a40).abs().max() > 1e-4
+
+
+def test_weight_updates_through_data_need_invalidate_or_strict_tracking():
+    """`p.data.copy_()` does not bump `p._version`, so the packed device images are stale until
+    `invalidate_packed()` is called (or `strict_weight_tracking` keys the cache on the contents);
+    `load_state_dict` invalidates by itself."""
+    sd = dscnn_ref.init_state_dict(seed=11)
+    m = DepthwiseSeparableConv()
+    m.load_state_dict(sd)
+    m = m.cuda()
+    x = torch.randn(4, 1, 99, 40, generator=torch.Generator().manual_seed(2)).cuda()
+    before = m(x).clone()
+    new_w = torch.randn_like(m.fc.weight) * 0.3
+    m.fc.weight.data.copy_(new_w)
+    m.invalidate_packed()
+    after = m(x)
+    assert (after - before).abs().max().item() > 1e-2
+    sd2 = {k: v.clone() for k, v in sd.items()}
+    sd2["fc.weight"] = new_w.cpu()
+    want = dscnn_ref.forward({k: v.double() for k, v in sd2.items()}, x.cpu().double()).numpy()
+    np.testing.assert_allclose(after.cpu().numpy(), want, rtol=1e-3, atol=1e-3)
+    # content-keyed cache: no explicit call needed
+    m.strict_weight_tracking = True
+    m(x)
+    m.fc.bias.data.add_(1.0)
+    np.testing.assert_allclose(m(x).cpu().numpy(), want + 1.0, rtol=1e-3, atol=1e-3)
+    # load_state_dict always invalidates (post-hook), even with tracking off
+    m.strict_weight_tracking = False
+    m.load_state_dict(sd)
+    np.testing.assert_allclose(m(x).cpu().numpy(), before.cpu().numpy(), rtol=0, atol=1e-6)
+
+
+@pytest.mark.parametrize("F", [40, 10])
+def test_trained_scale_weights(F):
+    """every other precision test uses the reference initialiser (fc ~ N(0, 0.01), |logit| < 0.2),
+    which shrinks absolute logit errors ~100x.  With trained-scale weights (fc std 0.5, |logit| ~ 10) the
+    single-pass tf32 GEMMs of the default path must hold a scale-relative bound and the argmax on safe margins;
+    the layered fp32 path must be fp32-grade."""
+    sd = dscnn_ref.init_state_dict(seed=77)
+    g = torch.Generator().manual_seed(78)
+    sd["fc.weight"] = torch.randn(12, 64, generator=g) * 0.5
+    sd["fc.bias"] = torch.randn(12, generator=g)
+    for i in range(1, 5):   # conv weights drift from their initial scale while training
+        sd[f"dsconv{i}.pointwise.weight"] = sd[f"dsconv{i}.pointwise.weight"] * 1.5
+    m = DepthwiseSeparableConv()
+    m.load_state_dict(sd)
+    m = m.cuda()
+    x = torch.randn(256, 1, 99, F, generator=g) * 4.0
+    want = dscnn_ref.forward({k: v.double() for k, v in sd.items()}, x.double()).numpy()
+    scale = np.abs(want).max()
+    assert scale > 3.0                                    # really a trained-scale case
+    fused = m(x.cuda()).cpu().numpy()
+    rel = np.abs(fused - want).max() / scale
+    assert rel < 1e-3, rel                                # north_star: logits within 1e-3 (scale-relative here)
+    srt = np.sort(want, axis=1)
+    safe = (srt[:, -1] - srt[:, -2]) > 4e-3 * scale
+    assert safe.mean() > 0.9
+    assert (fused.argmax(1)[safe] == want.argmax(1)[safe]).all()
+    m.set_kernel_path("layered")
+    layered = m(x.cuda()).cpu().numpy()
+    assert np.abs(layered - want).max() / scale < 2e-5
