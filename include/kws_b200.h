@@ -189,9 +189,16 @@ int kws_train_forward_backward(kws_handle_t h, const float* params_dev, const fl
 int kws_train_adam(kws_handle_t h, float* params_dev, const float* grads_dev, float* m_dev, float* v_dev, int64_t n,
                    int64_t step, float lr, float beta1, float beta2, float eps, float grad_scale, void* stream);
 
-/* ---- fused path: PCM -> logits ------------------------------------------------------ */
+/* ---- fused path: PCM -> logits ------------------------------------------------------
+ * Replaces extract_features (audio_processor.py:235-278) + DepthwiseSeparableConv.forward (models.py:160-183)
+ * back to back.  Batches of at least `min_clips` (default 1024) run as ONE kernel launch: MFCC CTAs and network
+ * CTAs of the same grid exchange features through an L2-resident ring (HBM sees PCM in, logits out); smaller
+ * batches run the MFCC kernel and the network kernel back to back.  Both give the same logits bit for bit. */
 int kws_pcm_to_logits(kws_handle_t h, const float* pcm_dev, int64_t B, int64_t N,
                       int64_t pcm_stride, float* logits_dev, void* stream);
+/* min_clips: smallest batch that takes the single launch (>= 1; < 1 disables it); mfcc_share: share of the SMs
+ * running the MFCC role, 0 = default for the feature width (0.17 at 40 coefficients, 0.285 at 10) */
+int kws_pcm_to_logits_configure(kws_handle_t h, int64_t min_clips, double mfcc_share);
 int kws_pcm_to_logits_host(kws_handle_t h, const float* pcm_host, int64_t B, int64_t N,
                            float* logits_host);
 /* the same two calls fed 16-bit PCM (x/32768 = librosa.load, audio_processor.py:145, happens inside the

@@ -14,7 +14,8 @@ import threading
 from .common.errors import NativeLibraryError
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libkws_b200.so")
+# KWS_LIB: an experiment build of the same sources (build.py --out=...), for A/B timing runs only
+LIB_PATH = os.path.join(_HERE, os.environ.get("KWS_LIB", "libkws_b200.so"))
 
 _lib = None
 _lock = threading.Lock()
@@ -82,6 +83,7 @@ SIGNATURES = {
     "kws_train_adam": (_i32, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _f32, _f32, _f32, _f32, _f32, _vp]),
     "kws_model_forward": (_i32, [_vp, _vp, _i64, _i64, _i64, _vp, _vp]),
     "kws_model_workspace_bytes": (_i64, [_vp, _i64, _i64, _i64]),
+    "kws_pcm_to_logits_configure": (_i32, [_vp, _i64, _dbl]),
     "kws_pcm_to_logits": (_i32, [_vp, _vp, _i64, _i64, _i64, _vp, _vp]),
     "kws_pcm_to_logits_host": (_i32, [_vp, _vp, _i64, _i64, _vp]),
     "kws_pcm_to_logits_i16": (_i32, [_vp, _vp, _i64, _i64, _i64, _vp, _vp]),

@@ -115,6 +115,8 @@ int kws_destroy(kws_handle_t h) {
   for (int i = 0; i < 4; ++i)
     if (h->ev[i]) cudaEventDestroy(h->ev[i]);
   if (h->d_feat_tmp) cudaFree(h->d_feat_tmp);
+  if (h->d_ring) cudaFree(h->d_ring);
+  if (h->d_ring_cnt) cudaFree(h->d_ring_cnt);
   if (h->train.base) cudaFree(h->train.base);
   delete h;
   return KWS_OK;
@@ -202,6 +204,14 @@ static int pcm_to_logits_impl(kws_handle_t h, const void* pcm_dev, bool is_i16, 
   if (B < 0 || N < 1) return fail(KWS_ERR_INVALID, "bad B/N");
   if (B == 0) return KWS_OK;
   KWS_CUDA(cudaSetDevice(h->device));
+  if (!pcm_dev || !logits_dev) return fail(KWS_ERR_INVALID, "null device pointer");
+  if (pcm_stride < 1) return fail(KWS_ERR_INVALID, "bad stride");
+  // one launch, features through the L2-resident ring (pcm_logits_fused.cu).  Small batches cannot fill both
+  // roles' CTAs (a 256-clip batch is one wave of the model alone), so they run the two kernels back to back.
+  if (B >= h->pipe_min_clips) {
+    const int rc = launch_pcm_logits_fused(h, pcm_dev, is_i16, B, N, pcm_stride, logits_dev, (cudaStream_t)stream);
+    if (rc != 0) return rc < 0 ? rc : KWS_OK;
+  }
   const int64_t nframes = kws_num_frames(N, h->feat.cfg.frame_len, h->feat.cfg.frame_step);
   const int64_t F = h->feat.ncep;
   const size_t need = (size_t)B * nframes * F * 4;
@@ -216,6 +226,14 @@ static int pcm_to_logits_impl(kws_handle_t h, const void* pcm_dev, bool is_i16, 
   int rc = launch_mfcc(h, pcm_dev, is_i16, B, N, pcm_stride, h->d_feat_tmp, kModeMfcc, (cudaStream_t)stream);
   if (rc) return rc;
   return kws_model_forward(h, h->d_feat_tmp, B, nframes, F, logits_dev, stream);
+}
+
+int kws_pcm_to_logits_configure(kws_handle_t h, int64_t min_clips, double mfcc_share) {
+  if (!h) return fail(KWS_ERR_INVALID, "null handle");
+  if (mfcc_share < 0.0 || mfcc_share >= 1.0) return fail(KWS_ERR_INVALID, "mfcc_share must be in [0, 1)");
+  h->pipe_min_clips = min_clips < 1 ? (int64_t)1 << 62 : min_clips;   // < 1: never use the single-launch kernel
+  h->pipe_mfcc_share = mfcc_share;
+  return KWS_OK;
 }
 
 int kws_pcm_to_logits(kws_handle_t h, const float* pcm_dev, int64_t B, int64_t N, int64_t pcm_stride,

@@ -136,8 +136,15 @@ struct kws_handle_s {
   void* d_stage_in[2] = {nullptr, nullptr};
   void* d_stage_out[2] = {nullptr, nullptr};
   size_t stage_in_bytes = 0, stage_out_bytes = 0;
-  float* d_feat_tmp = nullptr;   // features scratch for the unfused pcm->logits path
+  float* d_feat_tmp = nullptr;   // features scratch of the two-kernel pcm->logits path (small batches)
   size_t feat_tmp_bytes = 0;
+  // single-launch pcm->logits (pcm_logits_fused.cu): L2-resident feature ring + its two counters per slot
+  float* d_ring = nullptr;
+  unsigned* d_ring_cnt = nullptr;
+  size_t ring_bytes = 0;
+  unsigned ring_slots = 0;
+  double pipe_mfcc_share = 0.0;  // share of the SMs given to the MFCC role (0 = default for the feature width)
+  int64_t pipe_min_clips = 1024; // below this batch the two kernels run back to back (see capi.cu)
   kws::TrainWorkspace train;
   void* crnn = nullptr;          // kws::CrnnWeights, owned by crnn.cu
 };
@@ -156,6 +163,9 @@ int launch_dscnn_fused(kws_handle_t h, const float* feats_dev, int64_t B, int64_
 int build_fused_model(ModelWeights& m, const std::vector<float>& conv1_w, const std::vector<float>& conv1_b,
                       const std::vector<const float*>& dw_w, const std::vector<const float*>& dw_b,
                       const std::vector<const float*>& pw_w, const std::vector<const float*>& pw_b);
+// pcm_logits_fused.cu: PCM -> logits in one launch (1 = handled, 0 = n/a, <0 = error)
+int launch_pcm_logits_fused(kws_handle_t h, const void* pcm_dev, bool is_i16, int64_t B, int64_t N, int64_t pcm_stride,
+                            float* logits_dev, cudaStream_t stream);
 // model.cu: layered forward that keeps every activation (training), logits/pooled into the workspace
 int train_forward_layers(kws_handle_t h, const float* feats_dev, int64_t B, int T, int F, TrainWorkspace& w,
                          cudaStream_t st);

@@ -1048,10 +1048,11 @@ int kws_crnn_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t 
         *d_last = (float*)(ws + o_last);
   const int gnb = H == 64 ? kGruNB : kGruNBg;
   const size_t gru_smem = ((size_t)H * 3 * H + 2 * (size_t)gnb * H) * 4;
-  if (H == 64)
+  if (H == 64) {
     if (int rc_ = ensure_dyn_smem(gru_recurrent_kernel, (size_t)gru_smem)) return rc_;
-  else
+  } else {
     if (int rc_ = ensure_dyn_smem(gru_recurrent_generic_kernel, (size_t)gru_smem)) return rc_;
+  }
   for (int64_t b0 = 0; b0 < B; b0 += chunk) {
     const int64_t nb = (B - b0 < chunk) ? B - b0 : chunk;
     // tensor-core conv1 writes tile-major, which only the step-major tensor-core projection reads

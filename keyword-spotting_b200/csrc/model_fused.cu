@@ -1,576 +1,12 @@
-// Fused forward of the reference KWS network (kws/libs/models.py:122-183) for channels = 64,
-// four blocks: features [B, T, F] -> logits [B, num_classes] in ONE kernel, every activation
-// on-chip (tensor memory + registers + shared memory), HBM sees only the features and the logits.
-//
-// Formulation.  Every GEMM-able layer (conv1 10x10 s2 p2 as an im2col GEMM with K = 100, the
-// four pointwise 1x1 convs with K = 64) is computed TRANSPOSED on the tensor core:
-//     D[c_out, pixel] = W[c_out, k] . X[pixel, k]^T      tcgen05.mma kind::tf32, M = 64, N = one
-// output row of pixels (padded to 24, or 16 for F = 10), accumulator in TMEM.  With M = 64 the
-// accumulator row c_out lives in TMEM lane 32*(c/16) + c%16 and a second, independent M = 64 tile
-// sits at lane offset 16 (tools/umma_probe.cu pins both facts on the device), so a CTA works on a
-// PAIR of clips ("slots") and thread (warp quarter q, lane) of every warp owns
-//     slot = lane / 16,  channel = 16 q + lane % 16
-// -- the depthwise 3x3 is per channel, so the thread that reads a channel's accumulator row from
-// TMEM (tcgen05.ld 32x32b: one lane per thread) applies bias + ReLU and runs the 3x3 stencil on
-// rows it holds in registers, with no inter-thread exchange at all, then stores the depthwise
-// result as the K-major B operand of the next pointwise GEMM (one 4-byte store per pixel, the
-// 144-byte K-chunk pitch puts the 16 channels of a quarter on 16 different banks).
-//
-// Schedule.  The network is streamed row by row through all layers (a skewed wavefront, see the
-// stage table above fused_mma_warp): a step has two phases, each = depthwise stencils of two
-// blocks by the twelve compute warps, one CTA barrier, and the GEMMs of the rows just finished,
-// issued by the two MMA warps (one per clip slot) and retired while the other phase computes.
-// TMEM holds, per layer, a ring of the last two raw accumulator rows; the last layer's row is
-// pooled as soon as it retires.
-//
-// Bias, ReLU and the padding=1 quirk.  The pointwise padding=1 quirk (models.py:104-106: each block
-// grows H and W by 2 and the new border pixels are ReLU(bias)) and every bias are folded INTO the
-// GEMMs, so the depthwise stage reads a finished padded layer row from TMEM and its activation is
-// a bare max(raw, 0) -- no bias add, no border patching, no column masks in the CUDA-core code:
-//   * each pointwise GEMM has K = 64 + 8: B-tile K-slots 64..67 hold the indicators
-//     (interior, border, interior, border) of the output pixel and the A image holds
-//     (folded bias hi, border bias hi, folded bias lo, border bias lo) there (hi + lo = the fp32
-//     bias as two tf32 terms; "folded" = pointwise bias + W_pw . depthwise bias, on the host);
-//   * the depthwise result of pixel x is stored as B-tile pixel row x + 1; rows 0 and W + 1 carry
-//     only the border indicator, rows past the layer carry nothing, so the GEMM row IS the padded
-//     layer row: [ReLU-able border bias | W interior pixels | border bias | zeros];
-//   * conv1 uses its four spare K slots (100..103) the same way; the margin column left of a ring
-//     row is never written and stays zero = the depthwise conv's own zero padding;
-//   * the constant top/bottom border rows and the all-zero row that flushes the stencil are
-//     constant TMEM rows written once at kernel start; a stage just picks the row address.
-//
-// Precision: tf32 operands (cvt.rna), fp32 accumulate; logits agree with the fp32 reference to
-// ~3e-6 absolute / 2e-4 relative (tests/test_gpu_model.py; north_star tolerance 1e-3).
-#include <cstring>
-#include <vector>
-
-#include "mfcc_dev.cuh"
+// Fused forward of the reference KWS network: stand-alone launch + host-side packing (body in model_fused_body.cuh).
+#include "model_fused_body.cuh"
 
 namespace kws {
 
-constexpr int kFC = 64;                      // channels of the reference network
-constexpr int kLboB = 144;                   // K-chunk pitch of the B tiles (bank spreading)
-constexpr int kKC1 = 104;                    // conv1 K: 100 taps + (bias hi, 0, bias lo, 0)
-constexpr int kKCp = 72;                     // pointwise K: 64 channels + 4 bias/indicator slots + 4 zero slots
-constexpr int kSboA1 = (kKC1 / 4) * 128;     // 8-row group pitch: conv1 weights
-// pointwise weights: 17 stored K-chunks; the 18th (K slots 68..71) aliases the next group's first
-// chunk -- finite numbers that meet the B tile's real zeros there
-constexpr int kSboAp = (kKCp / 4 - 1) * 128;
-constexpr int kSboB1 = (kKC1 / 4) * kLboB;   //                    conv1 im2col tile
-constexpr int kSboBp = (kKCp / 4) * kLboB;   //                    depthwise-output tile
-constexpr int kAImgBytes = 8 * kSboA1 + 4 * 8 * kSboAp;
-
-struct FusedParams {
-  const float* feats;     // [B, T, F]
-  float* logits;          // [B, ncls]
-  long long B;
-  int T, H0, ncls;
-  const float* a_img;     // tf32 A-operand images: conv1 then 4 pointwise, K-major no-swizzle, biases in the K tail
-  const float* dw_w;      // [4][9][64]
-  const float* border;    // [5][64] row 0 unused; ReLU(pointwise bias) of block l
-  const float* fc_w;      // [64][ncls]
-  const float* fc_b;      // [ncls]
-};
-
-// One step of the depthwise 3x3 (zero padding 1) of a block for this thread's (slot, channel) on
-// its warp's 8-pixel column segment [8j, 8j+8): consume one INPUT row of the block's input layer
-// and finish the OUTPUT row above it.  The stencil is accumulated per input row: with v = the
-// activated row,
-//     out[x]  = P[x] + sum_dx w[2][dx] v[x+dx]     (output row i-1 complete -> B tile of the pointwise GEMM)
-//     P'[x]   = R[x] + sum_dx w[1][dx] v[x+dx]     (output row i, two of three rows in)
-//     R'[x]   =        sum_dx w[0][dx] v[x+dx]     (output row i+1, one row in)
-// so every input row is read from TMEM and activated exactly once and nothing is ever moved.
-// `taddr` is the TMEM address of layer column 8j - 1 of the input row (a ring row, a constant border
-// row or the zero row -- the caller picks); layer column = TMEM column for every layer, the bias is
-// already in the accumulator, so v = max(raw, 0).  The stencil runs on packed f32x2 pairs of
-// adjacent pixels: E[p] = (v[2p], v[2p+1]) and the odd-aligned O[p] = (v[2p+1], v[2p+2]) are both
-// produced straight by the max, so no register pair is ever re-assembled.
-// W = width of the layer (= number of valid output pixels), SHIFT = pixel offset of the result in the
-// B tile (1 where the following pointwise output carries a border column).  `par` points at this
-// channel's [w0..w8] column.
-// Clips per slot: with PACK = 2 (narrow feature maps, F = 10) two clips sit side by side in one GEMM row, the
-// second at column kPackOff; the indicator scheme leaves the columns between them zero, which is each clip's
-// own zero padding, so the stencil needs no change -- only "which pixels are real" does.
-constexpr int kPackOff = 12;
-template <int W, int PACK>
-__host__ __device__ constexpr bool px_valid(int px) {
-  return PACK == 1 ? px < W : (px < W || (px >= kPackOff && px < kPackOff + W));
-}
-
-template <int W, int SHIFT, int PACK>
-__device__ __forceinline__ void dw_seg(uint32_t taddr, int j, bool st, const float4* par, unsigned char* dst,
-                                       V (&P)[4], V (&R)[4]) {
-  const float4 w0 = par[0], w1 = par[1];
-  const float w8 = reinterpret_cast<const float*>(par)[8];
-  // E pairs from a load at column 8j-1, O pairs from a second load one column to the right; the max is
-  // done in place on the load's registers so that each pair stays the aligned register pair it arrived as
-  float ra[16], rb[8];
-  tc_ld16(taddr, ra);
-  tc_ld8(taddr + 1u, rb);
-  tc_wait_ld();
-#pragma unroll
-  for (int k = 0; k < 10; ++k) asm("max.f32 %0, %0, 0f00000000;" : "+f"(ra[k]));
-#pragma unroll
-  for (int k = 0; k < 8; ++k) asm("max.f32 %0, %0, 0f00000000;" : "+f"(rb[k]));
-  V E[5], O[4];
-#pragma unroll
-  for (int pp = 0; pp < 5; ++pp) E[pp] = make_float2(ra[2 * pp], ra[2 * pp + 1]);
-#pragma unroll
-  for (int pp = 0; pp < 4; ++pp) O[pp] = make_float2(rb[2 * pp], rb[2 * pp + 1]);
-  // warp-uniform store predicates.  PACK = 1: pixels x < KL of the last valid segment JL, all pixels of the
-  // segments before it; PACK = 2: per segment, from the compile-time validity of its eight columns
-  constexpr int JL = (W - 1) / 8, KL = W - 8 * JL;
-  const bool st_lo = st && j <= JL, st_hi = st && j < JL;
-  const bool s0 = st && j == 0, s1 = st && j == 1, s2 = st && j == 2;
-#pragma unroll
-  for (int pp = 0; pp < 4; ++pp) {  // output pixels 2pp, 2pp+1 of the segment, packed f32x2
-    const V o = ffma(fsplat(w8), E[pp + 1], ffma(fsplat(w1.w), O[pp], ffma(fsplat(w1.z), E[pp], P[pp])));
-    P[pp] = ffma(fsplat(w1.y), E[pp + 1], ffma(fsplat(w1.x), O[pp], ffma(fsplat(w0.w), E[pp], R[pp])));
-    R[pp] = ffma(fsplat(w0.z), E[pp + 1], ffma(fsplat(w0.y), O[pp], fmul(fsplat(w0.x), E[pp])));
-    // tf32 round-to-nearest (ties away) = add half an ulp of the 10-bit mantissa; the MMA drops the low 13 bits
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-      const int x = 2 * pp + h;
-      // pixels past the layer are never stored: their B-tile rows stay zero (or hold the border indicator)
-      const bool on = PACK == 1 ? (x < KL ? st_lo : st_hi)
-                                : ((px_valid<W, PACK>(x) && s0) || (px_valid<W, PACK>(8 + x) && s1) || (px_valid<W, PACK>(16 + x) && s2));
-      if (on)
-        *reinterpret_cast<uint32_t*>(dst + ((x + SHIFT) >> 3) * kSboBp + ((x + SHIFT) & 7) * 16) =
-            __float_as_uint(h ? o.y : o.x) + 0x1000u;
-    }
-  }
-}
-
-constexpr int kCWarps = 12;                       // compute warps: 3 column segments x 4 lane quarters
-constexpr int kCThreads = kCWarps * 32;
-constexpr int kFThreads = (kCWarps + 2) * 32;     // + one MMA-issue warp per clip slot
-constexpr int kRingCols = 64;                     // per layer: 2 row slots x (8 margin + 24) columns
-// last pointwise layer's row (pooled at once): 8-column margin + 24, like a ring slot.  The margin is load-bearing:
-// the right halo of ring 3's second slot (layer column 24 of the widest layer) falls on it and must read zero.
-constexpr int kAcc4Col = 4 * kRingCols;
-constexpr int kConstCol = kAcc4Col + 32;          // constant border rows of the three padded layers, 32 columns each
-constexpr int kZeroCol = kConstCol + 3 * 32;      // the all-zero row that flushes a stencil
-
-template <int F, int NPIX, int PACK>
-struct FusedLayout {
-  static constexpr int FP = F + 4;  // feature row pitch: 2 zero columns left, >= 2 right (conv1 padding 2)
-  static constexpr int CL = 2 * PACK;  // clips per CTA step: 2 slots x PACK side by side
-  static constexpr int b1_tile = (NPIX / 8) * kSboB1, b1_stride = b1_tile + 64;
-  static constexpr int bp_tile = (NPIX / 8) * kSboBp, bp_stride = bp_tile + 64;
-  static constexpr int off_a1 = 0;
-  static constexpr int off_ap = 8 * kSboA1;
-  static constexpr int off_b1 = kAImgBytes;
-  static constexpr int off_bp = off_b1 + 2 * b1_stride;
-  static constexpr int off_par = off_bp + 8 * bp_stride;          // [4][64][12] depthwise taps (9 used)
-  static constexpr int off_pool = off_par + 4 * kFC * 12 * 4;     // [3][2][PACK][64] pooling partials
-  static constexpr int off_feat = off_pool + 3 * CL * kFC * 4;
-  // zero-padded feature map of one clip: rows -2 .. T+1
-  static constexpr size_t feat_floats(int T) { return (size_t)(T + 4) * FP; }
-};
-
-// The MMA warps run their issue code CONVERGED and every tcgen05 instruction is predicated on an elected lane
-// (see tc_mma_tf32_elect in mfcc_dev.cuh): issued from inside `if (lane == 0)`, MMA issue was the critical
-// path of a step.  ACC is an immediate here.
-template <bool ACC>
-__device__ __forceinline__ void tc_mma_tf32_c(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc) {
-  asm volatile(
-      "{\n\t.reg .pred p, pe;\n\t"
-      "elect.sync _|pe, 0xffffffff;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "@pe tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
-      "l"(adesc), "l"(bdesc), "r"(idesc), "n"(ACC ? 1 : 0)
-      : "memory");
-}
-// one GEMM: NK k-steps of 8; the descriptors' address fields advance by 256 B (A) / 2 * 144 B (B)
-template <int NK>
-__device__ __forceinline__ void issue_gemm(uint32_t d, uint64_t adesc, uint64_t bdesc, uint32_t idesc) {
-  tc_mma_tf32_c<false>(d, adesc, bdesc, idesc);
-#pragma unroll
-  for (int ks = 1; ks < NK; ++ks)
-    tc_mma_tf32_c<true>(d, adesc + (uint64_t)(ks * (256 >> 4)), bdesc + (uint64_t)(ks * ((2 * kLboB) >> 4)), idesc);
-}
-
-// Stage schedule (local step t of a clip pair; phase A then phase B inside a step):
-//   conv1 im2col + GEMM row t                    (B)      | dw1: input row t-2 (A), pw1 GEMM row t-3 (end of A)
-//   dw2: input row t-3 (B), pw2 GEMM row t-4 (end of B)    | dw3: input row t-5 (A), pw3 GEMM row t-6 (end of A)
-//   dw4: input row t-6 (B), pw4 GEMM row t-7 (end of B)    | pooling of pw4 row t-8 (B)
-// GEMMs issued at the end of a phase run on the tensor core while the compute warps execute the
-// next phase, whose stages never touch what those GEMMs read or write.
-//
-// The clip pairs of a CTA are streamed back to back with period PER = H0 + 7 steps (the longest stage,
-// dw4, has exactly PER rows), so the pipeline never drains between pairs: with tl = global step mod PER
-// and n = global step / PER, a stage with lag g works on row i = tl - g of pair n, or, while that is
-// negative, on row i + PER of pair n - 1.  Every stage resets itself (the zero flush row clears the
-// stencil state), so nothing else marks the boundary between two pairs.
-struct StageRow {
-  int i;      // row index inside the stage's pair (valid when on)
-  bool on;
-};
-__device__ __forceinline__ StageRow stage_row(int tl, int n, int npair, int per, int g, int len) {
-  int i = tl - g, cn = n;
-  if (i < 0) {
-    i += per;
-    cn = n - 1;
-  }
-  return StageRow{i, cn >= 0 && cn < npair && i < len};
-}
-
-template <int F, int NPIX, int PACK, int SLOT>
-__device__ __forceinline__ void fused_mma_warp(unsigned char* smem, uint32_t tmem, uint32_t barO, uint32_t barE, int H0,
-                                               int my_pairs) {
-  using L = FusedLayout<F, NPIX, PACK>;
-  constexpr uint32_t kIdescF = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(NPIX >> 3) << 17) | ((64u >> 4) << 24);
-  const uint32_t sbase = smem_u32(smem);
-  const uint64_t a1 = umma_desc(sbase + L::off_a1, 128u, kSboA1);
-  const uint64_t b1 = umma_desc(sbase + L::off_b1 + SLOT * L::b1_stride, kLboB, kSboB1);
-  uint64_t ap[4], bp[4];
-#pragma unroll
-  for (int l = 0; l < 4; ++l) {
-    ap[l] = umma_desc(sbase + L::off_ap + l * 8 * kSboAp, 128u, kSboAp);
-    bp[l] = umma_desc(sbase + L::off_bp + (l * 2 + SLOT) * L::bp_stride, kLboB, kSboBp);
-  }
-  const uint32_t d0 = tmem + ((uint32_t)(SLOT * 16) << 16) + 8u;  // ring rows start after an 8-column margin
-  const int per = H0 + 7, total = my_pairs * per + 7;
-  __syncthreads();  // features of the first pair loaded
-  int tl = 0, n = 0;
-  for (int tg = 0; tg < total; ++tg) {
-    __syncthreads();  // phase A written
-    tc_fence_after();
-    {
-      StageRow r = stage_row(tl, n, my_pairs, per, 3, H0);
-      if (r.on) issue_gemm<kKCp / 8>(d0 + 1 * kRingCols + (r.i & 1) * 32, ap[0], bp[0], kIdescF);
-      r = stage_row(tl, n, my_pairs, per, 6, H0 + 4);
-      if (r.on) issue_gemm<kKCp / 8>(d0 + 3 * kRingCols + (r.i & 1) * 32, ap[2], bp[2], kIdescF);
-      tc_commit_elect(barO);
-    }
-    __syncthreads();  // phase B written
-    tc_fence_after();
-    {
-      StageRow r = stage_row(tl, n, my_pairs, per, 0, H0);
-      if (r.on) issue_gemm<kKC1 / 8>(d0 + (r.i & 1) * 32, a1, b1, kIdescF);
-      r = stage_row(tl, n, my_pairs, per, 4, H0 + 2);
-      if (r.on) issue_gemm<kKCp / 8>(d0 + 2 * kRingCols + (r.i & 1) * 32, ap[1], bp[1], kIdescF);
-      r = stage_row(tl, n, my_pairs, per, 7, H0 + 6);
-      if (r.on) issue_gemm<kKCp / 8>(d0 + kAcc4Col, ap[3], bp[3], kIdescF);
-      tc_commit_elect(barE);
-    }
-    if (++tl == per) {
-      tl = 0;
-      ++n;
-    }
-  }
-}
-
-// TMEM column (relative to the lane quarter's base) of input row i of a depthwise stage: `ring` is the
-// input layer's ring; BORDER layers have HIN + 2 rows whose first and last are the constant row `cst`;
-// row HL (one past the end) is the zero row that flushes the last output row.
-template <bool BORDER>
-__device__ __forceinline__ uint32_t dw_row_col(int i, int HIN, uint32_t ring, uint32_t cst) {
-  const int HL = BORDER ? HIN + 2 : HIN;
-  if (i >= HL) return (uint32_t)kZeroCol;
-  if (BORDER) {
-    if (i == 0 || i == HL - 1) return cst;
-    return ring + (uint32_t)(((i - 1) & 1) * 32);
-  }
-  return ring + (uint32_t)((i & 1) * 32);
-}
-
 template <int F, int NPIX, int PACK>
 __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedParams p) {
-  constexpr int W0 = (F - 6) / 2 + 1, W3 = W0 + 6, NSEG = NPIX / 8;
-  static_assert(W3 <= NPIX && NPIX % 8 == 0 && NSEG <= 3, "row of the widest layer must fit the MMA N");
-  static_assert(PACK == 1 || (PACK == 2 && W3 + 2 < kPackOff && kPackOff + W3 <= NPIX), "two clips per slot need a zero gap");
-  using L = FusedLayout<F, NPIX, PACK>;
-  constexpr int FP = L::FP, CL = L::CL;
   extern __shared__ __align__(128) unsigned char smem[];
-  __shared__ __align__(8) unsigned long long s_bar[2];
-  __shared__ uint32_t s_tmem;
-  float* s_feat = reinterpret_cast<float*>(smem + L::off_feat);  // [CL][(T + 4) * FP], zero padded, tf32-rounded
-  float* s_pool = reinterpret_cast<float*>(smem + L::off_pool);  // [3][2][PACK][64]
-  float* s_par = reinterpret_cast<float*>(smem + L::off_par);    // [4][64][12]
-
-  const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
-  const uint32_t barO = smem_u32(&s_bar[0]), barE = smem_u32(&s_bar[1]);
-  const int T = p.T, H0 = p.H0, TF = T * F;
-  const int feat_stride = (int)L::feat_floats(T);
-  const long long npairs = (p.B + CL - 1) / CL;  // groups of CL clips ("pairs" when PACK = 1)
-
-  if (tid == 0) {
-    mbar_init(barO, 2);
-    mbar_init(barE, 2);
-    fence_mbar_init();
-  }
-  if (warp == 0) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "n"(512));
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
-  }
-  {
-    const uint4* src = reinterpret_cast<const uint4*>(p.a_img);
-    uint4* dst = reinterpret_cast<uint4*>(smem);
-    for (int i = tid; i < kAImgBytes / 16; i += kFThreads) dst[i] = src[i];
-    uint4* z = reinterpret_cast<uint4*>(smem + L::off_b1);
-    const int nz = (L::off_feat - L::off_b1) / 16 + (CL * feat_stride * 4 + 15) / 16;  // B tiles, pool, feature pads
-    for (int i = tid; i < nz; i += kFThreads) z[i] = make_uint4(0, 0, 0, 0);
-  }
-  __syncthreads();
-  for (int i = tid; i < 4 * kFC * 12; i += kFThreads) {
-    const int l = i / (12 * kFC), ch = (i / 12) % kFC, k = i % 12;
-    s_par[i] = k < 9 ? p.dw_w[(l * 9 + k) * kFC + ch] : 0.f;
-  }
-  // constant K tail of the B tiles: (interior, border, interior, border) indicators of every pixel row
-  for (int i = tid; i < 2 * 5 * NPIX; i += kFThreads) {
-    const int s = i / (5 * NPIX), l = (i / NPIX) % 5, px = i % NPIX;  // l = 0: conv1 tile, 1..4: tile of pointwise l
-    const int pl = (PACK == 2 && px >= kPackOff) ? px - kPackOff : px;  // column inside its clip
-    float in = 0.f, bo = 0.f;
-    unsigned char* tile;
-    int chunk, sbo;
-    if (l == 0) {
-      tile = smem + L::off_b1 + s * L::b1_stride, chunk = 25, sbo = kSboB1;
-      in = pl < W0 ? 1.f : 0.f;
-    } else {
-      tile = smem + L::off_bp + ((l - 1) * 2 + s) * L::bp_stride, chunk = 16, sbo = kSboBp;
-      const int Wl = W0 + 2 * (l - 1);  // width of the depthwise output feeding pointwise l
-      if (l < 4) {
-        in = (pl >= 1 && pl <= Wl) ? 1.f : 0.f;
-        bo = (pl == 0 || pl == Wl + 1) ? 1.f : 0.f;
-      } else {
-        in = pl < Wl ? 1.f : 0.f;
-      }
-    }
-    *reinterpret_cast<float4*>(tile + (px >> 3) * sbo + chunk * kLboB + (px & 7) * 16) = make_float4(in, bo, in, bo);
-  }
-  fence_proxy_async();
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem = s_tmem;
-  if (warp < 4) {  // zero all of tensor memory once, then the constant border rows of the three padded layers
-    for (int col = 0; col < 512; col += 16) {
-      asm volatile(
-          "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1};" ::"r"(
-              tmem + ((uint32_t)(warp * 32) << 16) + col),
-          "r"(0)
-          : "memory");
-    }
-    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
-    const int ch = warp * 16 + (lane & 15);
-    for (int l = 1; l < 4; ++l) {
-      const uint32_t bv = __float_as_uint(p.border[l * kFC + ch]);
-      const int WL = W0 + 2 * l;
-      for (int x0 = 0; x0 < NPIX; x0 += 8) {
-        uint32_t v[8];
-#pragma unroll
-        for (int x = 0; x < 8; ++x) v[x] = (x0 + x < WL || (PACK == 2 && x0 + x >= kPackOff && x0 + x < kPackOff + WL)) ? bv : 0u;
-        asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"r"(
-                         tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)(kConstCol + (l - 1) * 32 + 8 + x0)),
-                     "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
-                     : "memory");
-      }
-    }
-    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
-  }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-
-  // pairs of this CTA: blockIdx.x, + gridDim.x, ... (the launcher keeps gridDim.x <= npairs)
-  const int my_pairs = (int)((npairs - blockIdx.x + gridDim.x - 1) / gridDim.x);
-  if (warp == kCWarps) {
-    fused_mma_warp<F, NPIX, PACK, 0>(smem, tmem, barO, barE, H0, my_pairs);
-  } else if (warp == kCWarps + 1) {
-    fused_mma_warp<F, NPIX, PACK, 1>(smem, tmem, barO, barE, H0, my_pairs);
-  } else {
-    // =========================== compute warps ===========================
-    const int j = warp >> 2, q = warp & 3, sl = lane >> 4, c = q * 16 + (lane & 15);
-    const bool seg_on = j < NSEG;
-    // TMEM: this warp's lane quarter; ring row slot s of layer l starts at column l*64 + s*32, its data
-    // after an 8-column margin; a 16-column load from (segment start - 1) covers the segment and its halo
-    const uint32_t my_tmem = tmem + ((uint32_t)(q * 32) << 16);
-    const uint32_t my_ld = my_tmem + 7u + (uint32_t)(8 * j);
-    unsigned char* my_dst = smem + L::off_bp + sl * L::bp_stride + j * kSboBp + (c >> 2) * kLboB + (c & 3) * 4;
-    const float4* my_par = reinterpret_cast<const float4*>(s_par) + c * 3;
-    // conv1 im2col item of this thread: clip, 16-byte K-chunk (4 taps), pixel column(s).
-    //   PACK = 1: 2 clips x 25 chunks x 7 column groups (columns xg, xg+7, xg+14)
-    //   PACK = 2: 4 clips x 25 chunks x W0 columns, one item per thread; clip u of a slot sits at row u * kPackOff
-    constexpr int kImItems = PACK == 1 ? 350 : CL * 25 * W0;
-    static_assert(kImItems <= kCThreads, "im2col items must fit the compute threads");
-    const bool im_on = tid < kImItems;
-    const int im_kc = tid % 25;
-    const int im_r = tid / 25;                                   // PACK 1: slot * 7 + xg;  PACK 2: clip * W0 + x
-    const int im_sc = PACK == 1 ? im_r / 7 : im_r / W0;          // clip of the CTA step (slot * PACK + u)
-    const int im_x0 = PACK == 1 ? im_r % 7 : im_r % W0;
-    const int im_row0 = PACK == 1 ? 0 : (im_sc % PACK) * kPackOff;
-    // taps 4kc .. 4kc+3 are two pairs of horizontally adjacent taps (a window row has 10 taps and 4kc is even),
-    // each pair one aligned 8-byte read of the padded feature row
-    int im_off[2];
-#pragma unroll
-    for (int e = 0; e < 2; ++e) {
-      const int k = 4 * im_kc + 2 * e, ki = k / 10, kj = k - 10 * ki;
-      im_off[e] = ki * FP + kj;
-    }
-    const float* im_src = s_feat + im_sc * feat_stride;
-    unsigned char* im_dst = smem + L::off_b1 + (im_sc / PACK) * L::b1_stride + im_kc * kLboB;
-    // rolling feature load: while pair n runs, the two feature-map rows conv1 has just left behind are
-    // refilled with rows 2tl-4, 2tl-3 of pair n+1 (thread = clip, row parity, column)
-    const bool fl_on = tid < CL * 2 * F;
-    const int fl_s = tid / (2 * F), fl_r = (tid / F) & 1, fl_c = tid % F;
-
-    const int per = H0 + 7, total = my_pairs * per + 7;
-    const int H3 = H0 + 6;
-    const float nborder = (float)((H3 + 2) * (W3 + 2) - H3 * W3);
-    const float inv_area = 1.0f / (float)((H3 + 2) * (W3 + 2));
-    uint32_t nO = 0, nE = 0;  // completed waits on the two MMA-group barriers
-
-    // global average pool (interior sum + border constant) and fc of the group whose pooling has finished:
-    // warp w takes outputs w, w + 12, ...; a lane sums two channels, the warp reduces
-    auto pool_fc = [&](long long pair) {
-      for (int o = warp; o < CL * p.ncls; o += kCWarps) {
-        const int sc = o / p.ncls, k = o - sc * p.ncls;   // sc = slot * PACK + u
-        float acc = 0.f;
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          const int ch = lane + 32 * h;
-          const float pooled = (s_pool[sc * kFC + ch] + s_pool[(CL + sc) * kFC + ch] + s_pool[(2 * CL + sc) * kFC + ch] +
-                                nborder * p.border[4 * kFC + ch]) * inv_area;
-          acc = fmaf(pooled, p.fc_w[ch * p.ncls + k], acc);
-        }
-#pragma unroll
-        for (int d = 16; d >= 1; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
-        const long long b = CL * pair + sc;
-        if (lane == 0 && b < p.B) p.logits[b * p.ncls + k] = acc + p.fc_b[k];
-      }
-    };
-
-    {  // features of the first group -> zero-padded, tf32-rounded maps in shared memory
-      const long long first = (long long)CL * blockIdx.x;
-      const float* src = p.feats + first * TF;
-      for (int i = tid; i < CL * TF; i += kCThreads) {
-        const int sc = i / TF, rem = i - sc * TF, fr = rem / F, fc = rem - fr * F;
-        s_feat[sc * feat_stride + (fr + 2) * FP + fc + 2] = (first + sc < p.B) ? to_tf32(__ldg(src + i)) : 0.f;
-      }
-    }
-    float psum[PACK];
-#pragma unroll
-    for (int u = 0; u < PACK; ++u) psum[u] = 0.f;
-    V P[4][4], R[4][4];
-#pragma unroll
-    for (int l = 0; l < 4; ++l)
-#pragma unroll
-      for (int x = 0; x < 4; ++x) P[l][x] = R[l][x] = fsplat(0.f);
-    __syncthreads();
-
-    int tl = 0, n = 0, fc_n = -1;  // fc_n: group (CTA-local index) whose pooled sums wait in s_pool
-    for (int tg = 0; tg < total; ++tg) {
-      // ================= phase A: depthwise of blocks 1 and 3 =================
-      float fl_v = 0.f;
-      const int fl_fr = 2 * tl - 4 + fl_r;
-      const bool fl_do = fl_on && n + 1 < my_pairs && fl_fr >= 0 && fl_fr < T;
-      if (fl_do) {
-        const long long clip = CL * ((long long)blockIdx.x + (long long)(n + 1) * gridDim.x) + fl_s;
-        if (clip < p.B) fl_v = __ldg(p.feats + clip * TF + fl_fr * F + fl_c);
-      }
-      if (tg > 0) {  // the GEMMs issued after the previous phase A (pw1, pw3) have retired
-        mbar_wait(barO, nO & 1);
-        ++nO;
-        tc_fence_after();
-      }
-      if (seg_on) {
-        StageRow r = stage_row(tl, n, my_pairs, per, 2, H0 + 1);
-        if (r.on)
-          dw_seg<W0, 1, PACK>(my_ld + dw_row_col<false>(r.i, H0, 0 * kRingCols, 0), j, r.i >= 1, my_par + 0 * 3 * kFC,
-                              my_dst + 0 * 2 * L::bp_stride, P[0], R[0]);
-        r = stage_row(tl, n, my_pairs, per, 5, H0 + 5);
-        if (r.on)
-          dw_seg<W0 + 4, 1, PACK>(my_ld + dw_row_col<true>(r.i, H0 + 2, 2 * kRingCols, kConstCol + 32), j, r.i >= 1,
-                                  my_par + 2 * 3 * kFC, my_dst + 2 * 2 * L::bp_stride, P[2], R[2]);
-      }
-      if (fc_n >= 0) {
-        pool_fc((long long)blockIdx.x + (long long)fc_n * gridDim.x);
-        fc_n = -1;
-      }
-      if (fl_do) s_feat[fl_s * feat_stride + (fl_fr + 2) * FP + fl_c + 2] = to_tf32(fl_v);
-      fence_proxy_async();
-      tc_fence_before();
-      __syncthreads();
-      // ================= phase B: conv1 im2col, depthwise of blocks 2 and 4, pooling =================
-      if (tg > 0) {  // the GEMMs issued after the previous phase B (conv1, pw2, pw4) have retired
-        mbar_wait(barE, nE & 1);
-        ++nE;
-        tc_fence_after();
-      }
-      if (tl < H0 && n < my_pairs && im_on) {
-        const float* rowp = im_src + 2 * tl * FP;
-        if (PACK == 1) {
-          for (int x = im_x0; x < W0; x += 7) {
-            const float* q4 = rowp + 2 * x;
-            const float2 lo = *reinterpret_cast<const float2*>(q4 + im_off[0]);
-            const float2 hi = *reinterpret_cast<const float2*>(q4 + im_off[1]);
-            *reinterpret_cast<float4*>(im_dst + (x >> 3) * kSboB1 + (x & 7) * 16) = make_float4(lo.x, lo.y, hi.x, hi.y);
-          }
-        } else {
-          const float* q4 = rowp + 2 * im_x0;
-          const float2 lo = *reinterpret_cast<const float2*>(q4 + im_off[0]);
-          const float2 hi = *reinterpret_cast<const float2*>(q4 + im_off[1]);
-          const int row = im_row0 + im_x0;
-          *reinterpret_cast<float4*>(im_dst + (row >> 3) * kSboB1 + (row & 7) * 16) = make_float4(lo.x, lo.y, hi.x, hi.y);
-        }
-      }
-      {
-        StageRow r = stage_row(tl, n, my_pairs, per, 3, H0 + 3);
-        if (seg_on && r.on)
-          dw_seg<W0 + 2, 1, PACK>(my_ld + dw_row_col<true>(r.i, H0, 1 * kRingCols, kConstCol), j, r.i >= 1,
-                                  my_par + 1 * 3 * kFC, my_dst + 1 * 2 * L::bp_stride, P[1], R[1]);
-        r = stage_row(tl, n, my_pairs, per, 6, H0 + 7);
-        if (seg_on && r.on)
-          dw_seg<W0 + 6, 0, PACK>(my_ld + dw_row_col<true>(r.i, H0 + 4, 3 * kRingCols, kConstCol + 64), j, r.i >= 1,
-                                  my_par + 3 * 3 * kFC, my_dst + 3 * 2 * L::bp_stride, P[3], R[3]);
-        r = stage_row(tl, n, my_pairs, per, 8, H3);
-        if (r.on) {  // pooling of the last block's row (interior pixels; the border is added in pool_fc)
-          if (seg_on) {
-            float raw[8];
-            tc_ld8(my_tmem + (uint32_t)kAcc4Col + 8u + (uint32_t)(8 * j), raw);
-            tc_wait_ld();
-            // columns past a clip's layer are 0; with two clips per slot columns < kPackOff belong to the first
-            float lo4 = 0.f, hi4 = 0.f;
-#pragma unroll
-            for (int x = 0; x < 4; ++x) {
-              lo4 += fmaxf(raw[x], 0.f);
-              hi4 += fmaxf(raw[4 + x], 0.f);
-            }
-            if (PACK == 1) {
-              psum[0] += lo4 + hi4;
-            } else {
-              psum[0] += (j < 2 ? lo4 : 0.f) + (j < 1 ? hi4 : 0.f);
-              psum[PACK - 1] += (j >= 2 ? lo4 : 0.f) + (j >= 1 ? hi4 : 0.f);
-            }
-          }
-          if (r.i == H3 - 1) {  // last row of the group: hand the sums to pool_fc (next phase A)
-#pragma unroll
-            for (int u = 0; u < PACK; ++u) {
-              s_pool[((j * 2 + sl) * PACK + u) * kFC + c] = psum[u];
-              psum[u] = 0.f;
-            }
-            fc_n = tl >= 8 ? n : n - 1;
-          }
-        }
-      }
-      fence_proxy_async();
-      tc_fence_before();
-      __syncthreads();
-      if (++tl == per) {
-        tl = 0;
-        ++n;
-      }
-    }
-    // the last step's GEMM groups are empty; wait for them so that nothing is in flight at dealloc
-    mbar_wait(barO, nO & 1);
-    mbar_wait(barE, nE & 1);
-    tc_fence_after();
-    if (fc_n >= 0) pool_fc((long long)blockIdx.x + (long long)fc_n * gridDim.x);
-  }
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(512));
+  dscnn_fused_body<F, NPIX, PACK, false>(p, smem, blockIdx.x, gridDim.x);
 }
 
 // ---- host side ------------------------------------------------------------------------------
@@ -648,13 +84,14 @@ static int launch_fused_t(kws_handle_t h, const FusedParams& p, cudaStream_t str
   return 1;
 }
 
-// 1 = handled, 0 = shape/configuration outside the fused kernel (caller uses the layered path), < 0 = error
-int launch_dscnn_fused(kws_handle_t h, const float* feats_dev, int64_t B, int64_t T, int64_t F, float* logits_dev,
-                       cudaStream_t stream) {
+// 1 = the fused kernel covers this shape (parameters filled), 0 = not
+int fill_fused_params(kws_handle_t h, const float* feats_dev, int64_t B, int64_t T, int64_t F, float* logits_dev,
+                      FusedParams* pp) {
   const ModelWeights& m = h->model;
   if (m.channels != kFC || m.num_blocks != 4 || m.d_fused_a == nullptr) return 0;
   if (T < 6 || T > 4096 || (F != 40 && F != 10)) return 0;
-  FusedParams p{};
+  FusedParams& p = *pp;
+  p = FusedParams{};
   p.feats = feats_dev;
   p.logits = logits_dev;
   p.B = B;
@@ -666,6 +103,14 @@ int launch_dscnn_fused(kws_handle_t h, const float* feats_dev, int64_t B, int64_
   p.border = m.d_fused_border;
   p.fc_w = m.d_fc_w;
   p.fc_b = m.d_fc_b;
+  return 1;
+}
+
+// 1 = handled, 0 = shape/configuration outside the fused kernel (caller uses the layered path), < 0 = error
+int launch_dscnn_fused(kws_handle_t h, const float* feats_dev, int64_t B, int64_t T, int64_t F, float* logits_dev,
+                       cudaStream_t stream) {
+  FusedParams p;
+  if (!fill_fused_params(h, feats_dev, B, T, F, logits_dev, &p)) return 0;
   if (F == 40) return launch_fused_t<40, 24, 1>(h, p, stream);
   // 99x10 features (the reference's default): the widest layer is 9 columns, two clips share a slot's 24-column row
   const int rc = launch_fused_t<10, 24, 2>(h, p, stream);

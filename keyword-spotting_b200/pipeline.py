@@ -49,6 +49,13 @@ class KeywordSpotter:
             self.model._feature_cfg_owner = self
             self._bound_h = self._h
 
+    def configure_single_launch(self, min_clips: int = 1024, mfcc_share: float = 0.0) -> None:
+        """Batches of at least ``min_clips`` run as ONE kernel launch (MFCC CTAs feeding network CTAs through an
+        L2-resident feature ring, ``csrc/pcm_logits_fused.cu``); ``min_clips < 1`` always runs the two kernels back
+        to back.  ``mfcc_share``: share of the SMs given to the MFCC role (0 = default)."""
+        self._bind()
+        _native.check(_native.lib().kws_pcm_to_logits_configure(self._h.ptr, int(min_clips), float(mfcc_share)), ModelError)
+
     def __call__(self, pcm: torch.Tensor) -> torch.Tensor:
         """``pcm[B, N]`` float32 (or int16 PCM, scaled by 1/32768 like ``librosa.load``) -> logits
         ``[B, num_classes]`` on the device."""
