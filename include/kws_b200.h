@@ -126,6 +126,18 @@ int kws_augment(kws_handle_t h, const float* pcm_dev, int64_t B, int64_t N, int6
                 const int64_t* noise_start_dev, const int64_t* noise_len_dev, const int64_t* noise_offset_dev,
                 const float* noise_volume_dev, float* out_dev, void* stream);
 
+/* ---- incremental features for sliding windows (kws/inference/inference_local.py:114-188).
+ * Windows of N samples every `hop` samples (hop a multiple of frame_step) share frames 1..T-2 with the recording's
+ * own frame grid; only a window's first frame (no pre-emphasis predecessor) and last frame (zero tail after the
+ * window end) are its own.  kws_stream_edge_frames writes those 2*nwin frames, pre-emphasised exactly like psf's
+ * float32 step, as rows of frame_len floats (row 2w = first, 2w+1 = last frame of window w) for a feature plan with
+ * frame_step = frame_len and preemph = 0; kws_stream_gather_windows assembles [nwin, T, F] feature maps from the
+ * recording's features [rec_frames, F] (kws_mfcc on the whole recording) and the edge features [2*nwin, F]. */
+int kws_stream_edge_frames(kws_handle_t h, const float* rec_dev, int64_t L, int64_t nwin, int64_t hop, int64_t N,
+                           int64_t frame_len, int64_t frame_step, float preemph, float* out_dev, void* stream);
+int kws_stream_gather_windows(kws_handle_t h, const float* rec_feats_dev, int64_t rec_frames, const float* edge_feats_dev,
+                              int64_t nwin, int64_t T, int64_t F, int64_t hop_frames, float* win_dev, void* stream);
+
 /* ---- sigproc: replaces kws/libs/speech_features/sigproc.py -------------------------- */
 /* dtype: 0 = float32, 1 = float64 (the torch helpers follow the input dtype) */
 int kws_sigproc_preemphasis(int dtype, const void* in_dev, void* out_dev, int64_t B, int64_t N,
@@ -191,13 +203,13 @@ int kws_train_adam(kws_handle_t h, float* params_dev, const float* grads_dev, fl
 
 /* ---- fused path: PCM -> logits ------------------------------------------------------
  * Replaces extract_features (audio_processor.py:235-278) + DepthwiseSeparableConv.forward (models.py:160-183)
- * back to back.  Batches of at least `min_clips` (default 1024) run as ONE kernel launch: MFCC CTAs and network
+ * back to back.  Batches of at least `min_clips` (default 8192) run as ONE kernel launch: MFCC CTAs and network
  * CTAs of the same grid exchange features through an L2-resident ring (HBM sees PCM in, logits out); smaller
  * batches run the MFCC kernel and the network kernel back to back.  Both give the same logits bit for bit. */
 int kws_pcm_to_logits(kws_handle_t h, const float* pcm_dev, int64_t B, int64_t N,
                       int64_t pcm_stride, float* logits_dev, void* stream);
 /* min_clips: smallest batch that takes the single launch (>= 1; < 1 disables it); mfcc_share: share of the SMs
- * running the MFCC role, 0 = default for the feature width (0.17 at 40 coefficients, 0.285 at 10) */
+ * running the MFCC role, 0 = default for the feature width (0.207 at 40 coefficients, 0.355 at 10: the measured cost ratio of the two roles) */
 int kws_pcm_to_logits_configure(kws_handle_t h, int64_t min_clips, double mfcc_share);
 int kws_pcm_to_logits_host(kws_handle_t h, const float* pcm_host, int64_t B, int64_t N,
                            float* logits_host);

@@ -73,6 +73,8 @@ SIGNATURES = {
     "kws_model_set_path": (_i32, [_vp, _i32]),
     "kws_mfcc_host_i16": (_i32, [_vp, _vp, _i64, _i64, _vp]),
     "kws_augment": (_i32, [_vp, _vp, _i64, _i64, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "kws_stream_edge_frames": (_i32, [_vp, _vp, _i64, _i64, _i64, _i64, _i64, _i64, _f32, _vp, _vp]),
+    "kws_stream_gather_windows": (_i32, [_vp, _vp, _i64, _vp, _i64, _i64, _i64, _i64, _vp, _vp]),
     "kws_crnn_create": (_i32, [_vp, _i32, _i32, _i32, _i32, _i32]),
     "kws_crnn_load_tensor": (_i32, [_vp, C.c_char_p, _vp, C.POINTER(_i64), _i32]),
     "kws_crnn_finalize": (_i32, [_vp]),

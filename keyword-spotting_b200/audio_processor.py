@@ -62,14 +62,17 @@ class AudioConfig:
 class _FeaturePlan:
     """One native handle configured for one (sr, frame_len, hop, nfft, nfilt, numcep) tuple."""
 
-    def __init__(self, device_index: int, key):
+    def __init__(self, device_index: int, key, preemph: Optional[float] = None):
         lib = _native.lib()
         self.handle = _native.Handle(device_index)
         cfg = _native.FeatureConfig()
         lib.kws_feature_config_default(C.byref(cfg))
         (cfg.sample_rate, cfg.frame_len, cfg.frame_step, cfg.nfft, cfg.nfilt, cfg.numcep) = key
+        if preemph is not None:
+            cfg.preemph = preemph
+        self.preemph = float(cfg.preemph)
         _native.check(lib.kws_features_configure(self.handle.ptr, C.byref(cfg)), AudioProcessingError)
-        self.frame_len, self.frame_step, self.nfilt = cfg.frame_len, cfg.frame_step, cfg.nfilt
+        self.frame_len, self.frame_step, self.nfilt = int(cfg.frame_len), int(cfg.frame_step), int(cfg.nfilt)
         self.ncep = int(lib.kws_features_ncep(self.handle.ptr))
 
 
@@ -132,6 +135,56 @@ class AudioProcessor:
             out = out[0]
         if is_numpy:
             return out.cpu().numpy().astype(np.float64)
+        return out
+
+    def sliding_features_incremental(self, recording: torch.Tensor, hop_samples: int,
+                                     window_samples: Optional[int] = None, **kw) -> torch.Tensor:
+        """Same result as :meth:`sliding_features` (``[nwin, nframes, numcep]``) with the frames consecutive windows
+        share computed ONCE: the recording is transformed as one long clip, the two frames per
+        window that differ from the recording's frame grid (first: no pre-emphasis predecessor; last: zero tail past
+        the window end) are transformed separately, and the windows are assembled by a gather.  Needs
+        ``hop_samples`` to be a multiple of the frame step.  Frames 1..T-2 equal the per-window call bit for bit;
+        the two edge frames come from the generic kernel and agree within fp32 rounding (north_star tolerance)."""
+        lib = _native.lib()
+        sr = kw.get("samplerate") or self.config.sample_rate
+        numcep = kw.get("numcep") or self.config.num_cepstral_coeffs
+        winlen = kw.get("winlen") or self.config.frame_length
+        winstep = kw.get("winstep") or self.config.frame_step
+        nfilt = kw.get("nfilt") or self.config.num_mel_filters
+        plan = self._plan(sr, numcep, winlen, winstep, nfilt)
+        fl, fs = plan.frame_len, plan.frame_step
+        N, hop = int(window_samples or self.config.desired_samples), int(hop_samples)
+        x = recording.to(self.device, torch.float32).contiguous()
+        if x.dim() != 1 or x.shape[0] < N or hop < 1 or N < fl:
+            raise AudioProcessingError(f"expected a [L] recording with L >= {N} >= frame length and hop >= 1")
+        if hop % fs != 0:
+            raise AudioProcessingError(f"incremental features need hop_samples to be a multiple of the frame step ({fs})")
+        L = x.shape[0]
+        nwin = (L - N) // hop + 1
+        T = int(lib.kws_num_frames(N, fl, fs))
+        if T < 3:
+            return self.sliding_features(recording, hop_samples, window_samples, **kw)
+        nfft = max(self.config.fft_size, int(winlen * sr))
+        ekey = (int(sr), fl, fl, int(nfft), int(nfilt), int(numcep), 0.0)     # one frame per row, no pre-emphasis
+        eplan = self._plans.get(ekey)
+        if eplan is None:
+            eplan = self._plans[ekey] = _FeaturePlan(self._dev_index(), ekey[:6], preemph=0.0)
+        stream = _native.current_stream_ptr(self._dev_index())
+        # the recording is only needed up to the last window's end
+        Lr = (nwin - 1) * hop + N
+        rec_frames = int(lib.kws_num_frames(Lr, fl, fs))
+        rec_feats = torch.empty((rec_frames, plan.ncep), dtype=torch.float32, device=self.device)
+        edge_pcm = torch.empty((2 * nwin, fl), dtype=torch.float32, device=self.device)
+        edge_feats = torch.empty((2 * nwin, plan.ncep), dtype=torch.float32, device=self.device)
+        out = torch.empty((nwin, T, plan.ncep), dtype=torch.float32, device=self.device)
+        vp = lambda t: C.c_void_p(t.data_ptr())  # noqa: E731
+        with torch.cuda.device(self.device):
+            chk = lambda rc: _native.check(rc, AudioProcessingError)  # noqa: E731
+            chk(lib.kws_mfcc(plan.handle.ptr, vp(x), 1, Lr, Lr, vp(rec_feats), stream))
+            chk(lib.kws_stream_edge_frames(plan.handle.ptr, vp(x), L, nwin, hop, N, fl, fs, plan.preemph, vp(edge_pcm), stream))
+            chk(lib.kws_mfcc(eplan.handle.ptr, vp(edge_pcm), 1, 2 * nwin * fl, 2 * nwin * fl, vp(edge_feats), stream))
+            chk(lib.kws_stream_gather_windows(plan.handle.ptr, vp(rec_feats), rec_frames, vp(edge_feats), nwin, T, plan.ncep,
+                                              hop // fs, vp(out), stream))
         return out
 
     def sliding_features(self, recording: torch.Tensor, hop_samples: int, window_samples: Optional[int] = None,

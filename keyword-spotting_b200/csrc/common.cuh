@@ -144,7 +144,7 @@ struct kws_handle_s {
   size_t ring_bytes = 0;
   unsigned ring_slots = 0;
   double pipe_mfcc_share = 0.0;  // share of the SMs given to the MFCC role (0 = default for the feature width)
-  int64_t pipe_min_clips = 1024; // below this batch the two kernels run back to back (see capi.cu)
+  int64_t pipe_min_clips = 8192; // below this batch the two kernels run back to back (see capi.cu)
   kws::TrainWorkspace train;
   void* crnn = nullptr;          // kws::CrnnWeights, owned by crnn.cu
 };

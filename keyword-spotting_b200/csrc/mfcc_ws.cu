@@ -1,4 +1,6 @@
 // Fast, warp-specialised PCM -> MFCC kernel: stand-alone launch (body in mfcc_ws_body.cuh).
+#include <cstdlib>
+
 #include "mfcc_ws_body.cuh"
 
 namespace kws {
@@ -69,7 +71,18 @@ int fill_fast_params(kws_handle_t h, const void* pcm_dev, bool is_i16, int64_t B
   off += 128 * 8;
   p.off_c0 = (int)off;
   off += 2 * kTileFrames * 4;
+  off = (off + 15) & ~(size_t)15;
+  p.off_lows = (int)off;                           // low bins: float64 block sums, B fragments, frame phases
+  off += kLowSBytes;
+  p.off_lowbw = (int)off;
+  off += kLowBwBytes;
+  p.off_lowfw = (int)off;
+  off += kLowFwBytes;
   const size_t smem_bytes = off;
+  // the low-bin warp's block decomposition is specific to hop 160 / frame 400 (blocks of gcd = 80 samples);
+  // KWS_LOW_BINS=0 switches it off (A/B timing, and the tail measurement of tools/mfcc_tail.py)
+  static const bool low_env = [] { const char* e = std::getenv("KWS_LOW_BINS"); return !(e && e[0] == '0'); }();
+  p.low_bins = (hop == 2 * kLowBlock && low_env) ? 1 : 0;
   static_assert(2064 + 2 * (16 * ROUNDS + 1) * 8 <= kWarpScratch / 2, "scratch layout overflow");
   // the tensor core reads 128 rows of A: 16 row groups past each base must stay inside the CTA's
   // shared memory (rows >= 24 are don't-care values that only reach accumulator rows we never read)

@@ -40,6 +40,8 @@ struct FastParams {
   const float* dctB;    // B operand image: hi then lo, canonical K-major layout [48 x Kpad] each
   int kpad, tile_len, raw_stride;  // raw_stride: bytes between the two raw stages
   int off_a, off_scratch, off_b, off_melw, off_edges, off_twp, off_c0;
+  int off_lows, off_lowbw, off_lowfw;   // low bins: block sums, DMMA B fragments, frame-assembly phases
+  int low_bins;             // 1: bins 1..4 in float64 on the fp64 tensor core (hop 160 / frame 400 only), 0: fp32 FFT only
   // PIPE only: `out` is a ring of 2^ring_shift clip slots; prod_cnt[slot] counts published tile halves (4 per
   // clip: 2 tiles x 2 epilogue warps), cons_cnt[slot] counts clips the model role has finished reading
   unsigned ring_shift;
@@ -79,6 +81,13 @@ constexpr int kSvcWarps = 2;                       // service warps: TMEM lanes 
 constexpr int kTileFrames = kWsCWarps * 4;           // 52 frames per tile = rows of the DCT GEMM
 constexpr int kAGroups = (kTileFrames + 7) / 8;    // 8-row groups of the A operand
 constexpr int kWsThreads = (kWsCWarps + kSvcWarps) * 32;
+// ---- bins 1..4 in float64 (see low_block_sums below) ----
+constexpr int kLowBins = 4;                        // bins 1..4
+constexpr int kLowBlock = 80;                      // gcd(hop 160, frame 400): block sums are shared between frames
+constexpr int kLowMTiles = kWsCWarps + 1;            // 8-block row tiles of a 52-frame tile (107 blocks): one per compute warp + 1
+constexpr int kLowSBytes = kLowMTiles * 8 * kLowBins * 16;   // block sums (re, im) float64
+constexpr int kLowBwBytes = 5 * 2 * 32 * 16;       // DMMA B fragments [q][half][lane][2] float64
+constexpr int kLowFwBytes = kLowBins * 5 * 16;     // frame-assembly phases [bin][j](re, im) float64
 constexpr int kWarpScratch = 2 * 16 * 17 * 16;     // bytes: two half-warp transposes (also holds S2)
 constexpr float kFEps = 2.220446049250313e-16f;
 constexpr int kWsRounds = 3;                       // mel filters per lane: nfilt <= 16 * kWsRounds
@@ -96,6 +105,21 @@ __device__ __forceinline__ float2 ld_pair(const short* q) {
   return make_float2((float)s.x, (float)s.y);
 }
 __device__ __forceinline__ float ld_one(const short* q) { return (float)*q; }
+__device__ __forceinline__ void ld_quad(const float* q, float (&x)[4]) {
+  const float4 v = *reinterpret_cast<const float4*>(q);
+  x[0] = v.x; x[1] = v.y; x[2] = v.z; x[3] = v.w;
+}
+__device__ __forceinline__ void ld_quad(const short* q, float (&x)[4]) {
+  const short4 v = *reinterpret_cast<const short4*>(q);
+  x[0] = (float)v.x; x[1] = (float)v.y; x[2] = (float)v.z; x[3] = (float)v.w;
+}
+// D[8x8] += A[8x4] . B[4x8] in float64 on the tensor core (DMMA): lane holds A[lane/4][lane%4], B[lane%4][lane/4],
+// C/D[lane/4][2 (lane%4) + {0, 1}]
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
+  asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0, %1}, {%2}, {%3}, {%0, %1};"
+               : "+d"(c0), "+d"(c1)
+               : "d"(a), "d"(b));
+}
 template <typename T> __device__ __forceinline__ constexpr float power_scale() { return 1.0f; }
 template <> __device__ __forceinline__ constexpr float power_scale<short>() { return 1.0f / 1073741824.0f; }
 
@@ -110,8 +134,9 @@ __device__ __forceinline__ void mfcc512_ws_body(const FastParams& p, unsigned ch
                                                 const unsigned nblk) {
   constexpr int kLead = 16 / (int)sizeof(T);
   // [0,1] raw stage full, [2,3] raw stage empty, [4] A rows of the tile written, [5] tile MMAs retired,
-  // [6] second service warp has drained its accumulator rows
-  __shared__ __align__(8) unsigned long long s_bar[7];
+  // [6] second service warp has drained its accumulator rows, [7] low-bin block sums of the tile written by every
+  // compute warp, [8] ... and read by every compute warp
+  __shared__ __align__(8) unsigned long long s_bar[9];
   __shared__ uint32_t s_tmem;
   const float* s_inv = reinterpret_cast<const float*>(smem + p.off_melw);  // [M+1] 1 / segment length
   const int* s_edges = reinterpret_cast<const int*>(smem + p.off_edges);
@@ -122,6 +147,7 @@ __device__ __forceinline__ void mfcc512_ws_body(const FastParams& p, unsigned ch
   const bool do_dct = (p.mode == kModeMfcc);
   const uint32_t bar_full = smem_u32(&s_bar[0]), bar_empty = smem_u32(&s_bar[2]);
   const uint32_t bar_afull = smem_u32(&s_bar[4]), bar_mma = smem_u32(&s_bar[5]), bar_epi = smem_u32(&s_bar[6]);
+  const uint32_t bar_sfull = smem_u32(&s_bar[7]), bar_sfree = smem_u32(&s_bar[8]);
   const int hop = p.hop;
   const uint32_t sbo = (uint32_t)(p.kpad / 4) * 128u;  // bytes between 8-row groups of A and B
 
@@ -130,6 +156,8 @@ __device__ __forceinline__ void mfcc512_ws_body(const FastParams& p, unsigned ch
     mbar_init(bar_full + 8, 1);
     mbar_init(bar_empty, kWsCWarps);
     mbar_init(bar_empty + 8, kWsCWarps);
+    mbar_init(bar_sfull, kWsCWarps);
+    mbar_init(bar_sfree, kWsCWarps);
     mbar_init(bar_afull, kWsCWarps);
     mbar_init(bar_mma, 1);
     mbar_init(bar_epi, 1);
@@ -151,6 +179,26 @@ __device__ __forceinline__ void mfcc512_ws_body(const FastParams& p, unsigned ch
     for (int i = tid; i < 2 * kDctN * p.kpad; i += kWsThreads) b[i] = p.dctB[i];
     float* a = reinterpret_cast<float*>(smem + p.off_a);
     for (int i = tid; i < 2 * kAGroups * 8 * p.kpad; i += kWsThreads) a[i] = 0.f;
+    if (p.low_bins) {
+      // DMMA B fragments of the block-sum GEMM, [q][half][lane][2]: lane (r = lane/4, c = lane%4) holds, for k-step
+      // 4 q + j, the twiddle of sample i = 16 q + 4 c + j and column n = r: bin r/2 + 1, cos for even n, -sin for odd
+      double* bwt = reinterpret_cast<double*>(smem + p.off_lowbw);
+      for (int i = tid; i < 5 * 2 * 32 * 2; i += kWsThreads) {
+        const int e = i & 1, ln = (i >> 1) & 31, hh = (i >> 6) & 1, q = i >> 7;
+        const int j = 2 * hh + e, r = ln >> 2, c = ln & 3;
+        double sn, cs;
+        sincospi((double)((16 * q + 4 * c + j) * ((r >> 1) + 1)) / 256.0, &sn, &cs);
+        bwt[i] = (r & 1) ? -sn : cs;
+      }
+      // phase of block j of a frame for bin b + 1: e^{-2 pi i 80 j (b + 1) / 512}
+      double* fwt = reinterpret_cast<double*>(smem + p.off_lowfw);
+      for (int i = tid; i < kLowBins * 5; i += kWsThreads) {
+        double sn, cs;
+        sincospi((double)(kLowBlock * (i % 5) * (i / 5 + 1)) / 256.0, &sn, &cs);
+        fwt[2 * i] = cs;
+        fwt[2 * i + 1] = -sn;
+      }
+    }
   }
   fence_proxy_async();  // B (and the zeroed A) were written through the generic proxy
   tc_fence_before();
@@ -282,6 +330,7 @@ __device__ __forceinline__ void mfcc512_ws_body(const FastParams& p, unsigned ch
   } else {
     // =========================== compute warps ===========================
     const int cw = warp - kSvcWarps, half = lane >> 4, l = lane & 15;
+    double* s_S = reinterpret_cast<double*>(smem + p.off_lows);  // [blocks][4 bins][re, im]
     unsigned char* wscratch = smem + p.off_scratch + cw * kWarpScratch;
     unsigned char* scratch = wscratch + half * (kWarpScratch / 2);  // this half-warp's transpose area
     float4* s_tr = reinterpret_cast<float4*>(scratch);
@@ -315,7 +364,64 @@ __device__ __forceinline__ void mfcc512_ws_body(const FastParams& p, unsigned ch
       const int fa_local = cw * 4 + half * 2;
       const int fA = t * kTileFrames + fa_local, fB = fA + 1;
       const bool active = (t * kTileFrames + cw * 4) < p.nframes;  // warp-uniform
-      if (!active && lane == 0) mbar_arrive(bar_empty + 8u * (it & 1));
+
+      // ---- bins 1..4 in float64, part 1: block sums on the fp64 tensor core ----
+      // Why: pre-emphasised broadband audio leaves bins 1..2 about 30 dB under the rest of the spectrum, so the
+      // ~3e-7 * ||frame|| rounding floor of ANY fp32 FFT is a 1e-5 relative error of the lowest mel filters, which
+      // the log, the DCT and the x11.5 lifter turn into MFCC errors of up to 7x the north_star bound on white noise
+      // (22 of 3.2e7 values outside it).  Frames overlap (hop 160, length 400), so the DFT of the four bins is taken
+      // once per 80-sample BLOCK,  S_b[k] = sum_{i<80} y[80 b + i] e^{-2 pi i k / 512}  -- a GEMM [blocks x 80] . [80 x 8]
+      // in DMMA m8n8k4 steps, one 8-block row tile per compute warp (the warp's own 640 samples; warp 0 also
+      // takes the 14th tile) -- and a frame is five phase-shifted blocks (part 2, below).  The GEMM's K index is
+      // permuted (sample 16 q + 4 c + j <-> k-step 4 q + j, column c) so that a lane's four A values of a k-step group
+      // are one 16-byte (8-byte for int16) shared-memory read.  On B200 a DMMA issues every 16 cycles per SM
+      // sub-core and holds that sub-core's FMA datapath meanwhile (tools/dmma_probe.cu), which is why the work is
+      // spread over all compute warps instead of one dedicated warp (measured: 9.1 M -> see DESIGN 4.1).
+      if (p.low_bins) {
+        int nfr = p.nframes - t * kTileFrames;
+        if (nfr > kTileFrames) nfr = kTileFrames;
+        const int nmt = (2 * (nfr - 1) + 5 + 7) >> 3;  // row tiles that hold the blocks this tile's frames use
+        if (it > 0) mbar_wait(bar_sfree, (it - 1) & 1);  // every warp has assembled the previous tile's frames
+        const int r = lane >> 2, c = lane & 3;
+        const double2* bwt = reinterpret_cast<const double2*>(smem + p.off_lowbw) + lane;
+#pragma unroll 1
+        for (int mt = cw; mt < nmt; mt += kWsCWarps) {
+          double a00 = 0.0, a01 = 0.0, a10 = 0.0, a11 = 0.0;  // two accumulators: even / odd k-steps
+          const int loc = kLowBlock * (8 * mt + r) + 4 * c;  // tile-local index of this lane's first sample
+          const T* q0 = raw + kLead + loc;
+          const bool inside = s0 + kLowBlock * 8 * (mt + 1) <= n;  // warp-uniform: the row tile ends inside the clip
+#pragma unroll
+          for (int q = 0; q < 5; ++q) {
+            float x[4];
+            ld_quad(q0 + 16 * q, x);
+            const float xm = ld_one(q0 + 16 * q - 1);
+            float y[4];
+            y[0] = __fsub_rn(x[0], __fmul_rn(pre, xm));
+            y[1] = __fsub_rn(x[1], __fmul_rn(pre, x[0]));
+            y[2] = __fsub_rn(x[2], __fmul_rn(pre, x[1]));
+            y[3] = __fsub_rn(x[3], __fmul_rn(pre, x[2]));
+            if (!inside) {  // samples >= N are zero AFTER pre-emphasis (psf pads y)
+              const int g = s0 + loc + 16 * q;
+#pragma unroll
+              for (int j = 0; j < 4; ++j) y[j] = (g + j < n) ? y[j] : 0.f;
+            }
+            const double2 b01 = bwt[(2 * q) * 32], b23 = bwt[(2 * q + 1) * 32];
+            dmma884(a00, a01, (double)y[0], b01.x);
+            dmma884(a10, a11, (double)y[1], b01.y);
+            dmma884(a00, a01, (double)y[2], b23.x);
+            dmma884(a10, a11, (double)y[3], b23.y);
+          }
+          *reinterpret_cast<double2*>(s_S + ((8 * mt + r) * kLowBins + c) * 2) = make_double2(a00 + a10, a01 + a11);
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_sfull);
+      }
+      if (!active) {
+        if (lane == 0) {
+          mbar_arrive(bar_empty + 8u * (it & 1));
+          if (p.low_bins) mbar_arrive(bar_sfree);
+        }
+      }
       V lm[ROUNDS];
       V mean = fsplat(0.f), esum = fsplat(0.f);
       if (active) {
@@ -385,6 +491,32 @@ __device__ __forceinline__ void mfcc512_ws_body(const FastParams& p, unsigned ch
         const int partner = (lane & 16) | ((16 - l) & 15);
         const bool l0 = (l == 0);
         const V sc = fsplat(power_scale<T>() / 2048.0f);
+        // bins 1..4 come from the low-bin warp (float64 DFT): lane l = 1..4 of the first step owns them
+        // ---- bins 1..4 in float64, part 2: X_f[k] = sum_{j<5} e^{-2 pi i 80 j k / 512} S_{2f+j}[k]; lanes 0..15 take
+        //      (frame lane/4 of this warp, bin lane%4 + 1), the powers are shuffled to the lanes that own those bins ----
+        V lowp = fsplat(0.f);
+        const bool use_low = p.low_bins && l >= 1 && l <= kLowBins;
+        if (p.low_bins) {
+          mbar_wait(bar_sfull, it & 1);
+          float pw = 0.f;
+          if (lane < 16) {
+            const int f = cw * 4 + (lane >> 2), b = lane & 3;
+            const double2* fw = reinterpret_cast<const double2*>(smem + p.off_lowfw) + b * 5;
+            double xr = 0.0, xi = 0.0;
+#pragma unroll
+            for (int j = 0; j < 5; ++j) {
+              const double2 sv = *reinterpret_cast<const double2*>(s_S + ((2 * f + j) * kLowBins + b) * 2);
+              const double2 w = fw[j];
+              xr = fma(sv.x, w.x, fma(-sv.y, w.y, xr));
+              xi = fma(sv.x, w.y, fma(sv.y, w.x, xi));
+            }
+            pw = (float)((xr * xr + xi * xi) * ((double)power_scale<T>() / 512.0));
+          }
+          const int src = ((2 * half) << 2) | ((l - 1) & 3);
+          lowp.x = __shfl_sync(0xffffffffu, pw, src);
+          lowp.y = __shfl_sync(0xffffffffu, pw, src + 4);
+          if (lane == 0) mbar_arrive(bar_sfree);
+        }
 #pragma unroll
         for (int k2 = 0; k2 < 8; ++k2) {
           const CF zk = x16[Q16(k2)];
@@ -403,8 +535,9 @@ __device__ __forceinline__ void mfcc512_ws_body(const FastParams& p, unsigned ch
           const V ti = ffma(di, wi, fneg(fmul(dr, wr)));
           const V ar = fadd(sr, tr), ai = fadd(si, ti);     // 2 X[k]
           const V br = fsub(sr, tr), bi = fsub(si, ti);     // conj(2 X[256-k])
-          const V pk = fmul(ffma(ai, ai, fmul(ar, ar)), sc);
+          V pk = fmul(ffma(ai, ai, fmul(ar, ar)), sc);
           const V pm = fmul(ffma(bi, bi, fmul(br, br)), sc);
+          if (k2 == 0 && use_low) pk = lowp;
           s_P[l + 16 * k2] = pk;
           s_P[256 - l - 16 * k2] = pm;
           esum = fadd(esum, fadd(pk, pm));

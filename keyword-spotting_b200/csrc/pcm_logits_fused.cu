@@ -46,7 +46,7 @@ static int launch_t(kws_handle_t h, FastParams& mp, FusedParams& fp, size_t mfcc
   const long long ngroups = (fp.B + L::CL - 1) / L::CL;
   if (ngroups > 0x7fffffffLL / 64) return 0;
   // role split: share of the SMs the MFCC role needs so that both roles run at the same clips/s
-  const double share = h->pipe_mfcc_share > 0.0 ? h->pipe_mfcc_share : (F == 40 ? 0.170 : 0.285);
+  const double share = h->pipe_mfcc_share > 0.0 ? h->pipe_mfcc_share : (F == 40 ? 0.207 : 0.355);
   long long grid = h->sm_count;
   long long n_mfcc = (long long)(grid * share + 0.5);
   if (n_mfcc < 1) n_mfcc = 1;

@@ -49,7 +49,7 @@ class KeywordSpotter:
             self.model._feature_cfg_owner = self
             self._bound_h = self._h
 
-    def configure_single_launch(self, min_clips: int = 1024, mfcc_share: float = 0.0) -> None:
+    def configure_single_launch(self, min_clips: int = 8192, mfcc_share: float = 0.0) -> None:
         """Batches of at least ``min_clips`` run as ONE kernel launch (MFCC CTAs feeding network CTAs through an
         L2-resident feature ring, ``csrc/pcm_logits_fused.cu``); ``min_clips < 1`` always runs the two kernels back
         to back.  ``mfcc_share``: share of the SMs given to the MFCC role (0 = default)."""
@@ -73,6 +73,18 @@ class KeywordSpotter:
                     self._h.ptr, C.c_void_p(x.data_ptr()), B, N, x.stride(0), C.c_void_p(out.data_ptr()),
                     _native.current_stream_ptr(self._idx)), ModelError)
         return out
+
+    def sliding_logits_incremental(self, recording: torch.Tensor, hop_samples: int,
+                                   window_samples: Optional[int] = None) -> torch.Tensor:
+        """:meth:`sliding_logits` with incremental features: the frames overlapping windows share
+        are computed once (``AudioProcessor.sliding_features_incremental``; ``hop_samples`` must be a multiple of the
+        frame step), then every window's feature map goes through the network.  ``recording`` is ``[L]``."""
+        from .audio_processor import AudioProcessor
+        if getattr(self, "_proc", None) is None:
+            self._proc = AudioProcessor(None, self.config, device=self.device)
+        feats = self._proc.sliding_features_incremental(recording, hop_samples, window_samples,
+                                                        numcep=int(self._cfg.numcep), nfilt=int(self._cfg.nfilt))
+        return self.model(feats.unsqueeze(1))
 
     def sliding_logits(self, recording: torch.Tensor, hop_samples: int,
                        window_samples: Optional[int] = None) -> torch.Tensor:

@@ -70,14 +70,14 @@ def test_single_launch_int16_and_role_split(ring_env):
 
 
 def test_single_launch_against_oracle_default_threshold():
-    """Default configuration: a 2048-clip batch takes the single launch; parity set inside it vs the float64 oracle."""
+    """Default configuration: an 8192-clip batch takes the single launch; parity set inside it vs the float64 oracle."""
     sd, ks = _spotter(40, 40, seed=5)
-    pcm = synth.uniform_pcm(2048, seed=6)
+    pcm = synth.uniform_pcm(8192, seed=6)
     pcm[:8] = synth.parity_pcm(8)
     l0 = ks.model.launch_count()
     got = ks(pcm.cuda()).cpu().numpy()
     assert ks.model.launch_count() - l0 == 1
-    idx = list(range(8)) + [100, 1023, 1024, 2047]
+    idx = list(range(8)) + [100, 1023, 1024, 8191]
     feats = psf_mfcc.extract_features_batch(pcm[idx].numpy(), numcep=40, nfilt=40)
     want = dscnn_ref.forward({k: v.double() for k, v in sd.items()}, torch.from_numpy(feats).unsqueeze(1)).numpy()
     np.testing.assert_allclose(got[idx], want, rtol=0, atol=1e-3)

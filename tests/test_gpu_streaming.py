@@ -72,3 +72,41 @@ def test_sliding_rejects_short_recordings():
         proc.sliding_features(torch.zeros(N - 1).cuda(), 160)
     with pytest.raises(AudioProcessingError):
         proc.sliding_features(torch.zeros(2 * N).cuda(), 0)
+
+
+@pytest.mark.parametrize("hop,extra", [(160, 123), (320, 0), (1600, 77), (16000, 5)])
+def test_incremental_features_share_frames(hop, extra):
+    """f4: frames shared by consecutive windows are computed once (the recording as one long clip + two edge frames
+    per window + a gather).  Interior frames equal the per-window result bit for bit (same kernel, same frame
+    samples); the two edge frames come from a second plan (frame step = frame length, pre-emphasised by
+    kws_stream_edge_frames) and hold the parity tolerance; the whole map holds it against the float64 oracle."""
+    proc = AudioProcessor(None, AudioConfig(), device="cuda:0")
+    rec = _recording(N + 23 * hop + extra, seed=hop + 1).cuda()
+    full = proc.sliding_features(rec, hop, numcep=40, nfilt=40)
+    l0 = proc.launch_count()
+    inc = proc.sliding_features_incremental(rec, hop, numcep=40, nfilt=40)
+    assert proc.launch_count() - l0 == 4           # recording MFCC, edge frames, edge MFCC, gather
+    assert inc.shape == full.shape == (24, 99, 40)
+    assert torch.equal(inc[:, 1:98], full[:, 1:98])
+    edge_err = (inc - full).abs()
+    assert (edge_err <= 1e-4 + 1e-3 * full.abs()).all(), edge_err.max().item()
+    for k in (0, 11, 23):
+        ref = psf_mfcc.extract_features_batch(rec[k * hop:k * hop + N].cpu().numpy()[None], numcep=40, nfilt=40)[0]
+        err = np.abs(inc[k].cpu().numpy().astype(np.float64) - ref)
+        assert (err <= 1e-4 + 1e-3 * np.abs(ref)).all(), (k, err.max())
+
+
+def test_incremental_logits_and_default_shape():
+    sd = dscnn_ref.init_state_dict(seed=13)
+    m = DepthwiseSeparableConv()
+    m.load_state_dict(sd)
+    ks = KeywordSpotter(m.cuda(), AudioConfig(), device="cuda:0")     # the reference's default 10 x 26 features
+    rec = _recording(N + 40 * 480, seed=3).cuda()
+    want = ks.sliding_logits(rec, 480)
+    got = ks.sliding_logits_incremental(rec, 480)
+    assert got.shape == want.shape == (41, 12)
+    np.testing.assert_allclose(got.cpu().numpy(), want.cpu().numpy(), rtol=0, atol=1e-4)
+    assert (got.argmax(1) == want.argmax(1)).all()
+    proc = AudioProcessor(None, AudioConfig(), device="cuda:0")
+    with pytest.raises(AudioProcessingError):
+        proc.sliding_features_incremental(rec, 250)       # not a multiple of the frame step
