@@ -209,7 +209,7 @@ int kws_train_adam(kws_handle_t h, float* params_dev, const float* grads_dev, fl
 int kws_pcm_to_logits(kws_handle_t h, const float* pcm_dev, int64_t B, int64_t N,
                       int64_t pcm_stride, float* logits_dev, void* stream);
 /* min_clips: smallest batch that takes the single launch (>= 1; < 1 disables it); mfcc_share: share of the SMs
- * running the MFCC role, 0 = default for the feature width (0.207 at 40 coefficients, 0.355 at 10: the measured cost ratio of the two roles) */
+ * running the MFCC role, 0 = default for the feature width (0.218 at 40 coefficients, 0.371 at 10: the measured cost ratio of the two roles) */
 int kws_pcm_to_logits_configure(kws_handle_t h, int64_t min_clips, double mfcc_share);
 int kws_pcm_to_logits_host(kws_handle_t h, const float* pcm_host, int64_t B, int64_t N,
                            float* logits_host);

@@ -71,7 +71,7 @@ int build_fused_model(ModelWeights& m, const std::vector<float>& conv1_w, const 
 template <int F, int NPIX, int PACK>
 static int launch_fused_t(kws_handle_t h, const FusedParams& p, cudaStream_t stream) {
   using L = FusedLayout<F, NPIX, PACK>;
-  const size_t smem_bytes = (size_t)L::off_feat + L::CL * L::feat_floats(p.T) * 4;
+  const size_t smem_bytes = L::smem_bytes(p.T);
   if (smem_bytes > 227 * 1024) return 0;
   auto kern = dscnn_fused_kernel<F, NPIX, PACK>;
   if (int rc = ensure_dyn_smem(kern, smem_bytes)) return rc;

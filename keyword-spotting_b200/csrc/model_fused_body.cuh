@@ -108,11 +108,37 @@ __host__ __device__ constexpr bool px_valid(int px) {
   return PACK == 1 ? px < W : (px < W || (px >= kPackOff && px < kPackOff + W));
 }
 
+// Shared memory through explicit 32-bit shared-window addresses: with generic pointers ptxas rebuilt the shared
+// base (S2R CgaCtaId + LEA) and the per-thread offsets (S2R TID + IMADs) in front of every stencil call -- ~28 of the
+// ~110 instructions of a call (ncu r2a, SASS view).  keep_u32() makes a value opaque to the optimiser so that it is
+// kept in its register instead of being rematerialised from the thread index.
+__device__ __forceinline__ uint32_t keep_u32(uint32_t v) {
+  asm volatile("" : "+r"(v));
+  return v;
+}
+__device__ __forceinline__ float4 lds128(uint32_t a) {
+  float4 v;
+  asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ uint2 lds64(uint32_t a) {
+  uint2 v;
+  asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ float lds32(uint32_t a) {
+  float v;
+  asm("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ void sts32(uint32_t a, uint32_t v) {  // a = base + constant: ptxas folds it into the STS offset
+  asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory");
+}
+
 template <int W, int SHIFT, int PACK>
-__device__ __forceinline__ void dw_seg(uint32_t taddr, int j, bool st, const float4* par, unsigned char* dst,
-                                       V (&P)[4], V (&R)[4]) {
-  const float4 w0 = par[0], w1 = par[1];
-  const float w8 = reinterpret_cast<const float*>(par)[8];
+__device__ __forceinline__ void dw_seg(uint32_t taddr, int j, bool st, uint32_t par, uint32_t dst, V (&P)[4], V (&R)[4]) {
+  const float4 w0 = lds128(par), w1 = lds128(par + 16u);
+  const float w8 = lds32(par + 32u);
   // E pairs from a load at column 8j-1, O pairs from a second load one column to the right; the max is
   // done in place on the load's registers so that each pair stays the aligned register pair it arrived as
   float ra[16], rb[8];
@@ -145,9 +171,7 @@ __device__ __forceinline__ void dw_seg(uint32_t taddr, int j, bool st, const flo
       // pixels past the layer are never stored: their B-tile rows stay zero (or hold the border indicator)
       const bool on = PACK == 1 ? (x < KL ? st_lo : st_hi)
                                 : ((px_valid<W, PACK>(x) && s0) || (px_valid<W, PACK>(8 + x) && s1) || (px_valid<W, PACK>(16 + x) && s2));
-      if (on)
-        *reinterpret_cast<uint32_t*>(dst + ((x + SHIFT) >> 3) * kSboBp + ((x + SHIFT) & 7) * 16) =
-            __float_as_uint(h ? o.y : o.x) + 0x1000u;
+      if (on) sts32(dst + (uint32_t)(((x + SHIFT) >> 3) * kSboBp + ((x + SHIFT) & 7) * 16), __float_as_uint(h ? o.y : o.x) + 0x1000u);
     }
   }
 }
@@ -171,16 +195,10 @@ struct FusedLayout {
   static constexpr int FP = F + 4;  // feature row pitch: 2 zero columns left, >= 2 right (conv1 padding 2)
   static constexpr int CL = 2 * PACK;  // clips per CTA step: 2 slots x PACK side by side
   static constexpr int b1_tile = (NPIX / 8) * kSboB1, b1_stride = b1_tile + 64;
-  // slot stride of the depthwise-output tiles: a warp's store covers both clip slots (lanes 0..15 / 16..31), each
-  // slot's 16 channels on 16 consecutive banks, so the two slots must sit 16 banks apart: stride = 16 words mod 32
-  // (with the former +64 B pad they overlapped on 8 banks: every store was two wavefronts)
-  static constexpr int bp_tile = (NPIX / 8) * kSboBp;
-#ifdef KWS_BP_PAD
-  static constexpr int bp_stride = bp_tile + KWS_BP_PAD;   // A/B builds only
-#else
-  static constexpr int bp_stride = bp_tile + 64 + ((64 + 128 - (bp_tile + 64) % 128) % 128);
-  static_assert(bp_stride % 128 == 64 && bp_stride - bp_tile >= 64, "slot stride must be 16 banks mod 32");
-#endif
+  // slot stride of the depthwise-output tiles.  (A stride of 16 banks mod 32 makes the two clip slots of a warp's store
+  // conflict-free -- measured in round 2: shared-memory conflicts halve, run time unchanged -- but costs 256 bytes
+  // that the stage-schedule table needs.)
+  static constexpr int bp_tile = (NPIX / 8) * kSboBp, bp_stride = bp_tile + 64;
   static constexpr int off_a1 = 0;
   static constexpr int off_ap = 8 * kSboA1;
   static constexpr int off_b1 = kAImgBytes;
@@ -190,6 +208,11 @@ struct FusedLayout {
   static constexpr int off_feat = off_pool + 3 * CL * kFC * 4;
   // zero-padded feature map of one clip: rows -2 .. T+1
   static constexpr size_t feat_floats(int T) { return (size_t)(T + 4) * FP; }
+  // bytes of dynamic shared memory for T frames: ... + feature maps + the per-step stage schedule (uint2 per local step)
+  static constexpr size_t smem_bytes(int T) {
+    return (((size_t)off_feat + CL * feat_floats(T) * 4 + 7) & ~(size_t)7) + (size_t)((T + 4 - 10) / 2 + 1 + 7) * 8;
+  }
+  static constexpr size_t off_sched(int T) { return ((size_t)off_feat + CL * feat_floats(T) * 4 + 7) & ~(size_t)7; }
 };
 
 // The MMA warps run their issue code CONVERGED and every tcgen05 instruction is predicated on an elected lane
@@ -299,6 +322,26 @@ __device__ __forceinline__ uint32_t dw_row_col(int i, int HIN, uint32_t ring, ui
   return ring + (uint32_t)((i & 1) * 32);
 }
 
+// Stage schedule of the compute warps, one uint2 per local step tl, built once per kernel: which row of which pair
+// each stencil stage works on is a function of tl alone (except "does that pair exist", which depends on the pair
+// counter n).  12 bits per stencil stage: [8:0] TMEM column of the input row relative to the lane quarter's base
+// (ring slot, constant border row or the zero row), [9] the finished output row is stored, [10] the row belongs to the
+// PREVIOUS pair (tl < lag), [11] the stage has a row at this step.  Computing this per step cost ~20 instructions per
+// stage and step (stage_row + dw_row_col: 16 % of the executed instructions, ncu r2a).
+//   .x: dw1 [0:12), dw3 [12:24), pooling [24:28) = (valid, prev, last row, -)      .y: dw2 [0:12), dw4 [12:24)
+constexpr uint32_t kSchSt = 1u << 9, kSchPrev = 1u << 10, kSchOn = 1u << 11;
+template <bool BORDER>
+__device__ __forceinline__ uint32_t sched_entry(int tl, int per, int g, int len, int HIN, uint32_t ring, uint32_t cst) {
+  int i = tl - g;
+  uint32_t e = 0;
+  if (i < 0) {
+    i += per;
+    e |= kSchPrev;
+  }
+  if (i < len) e |= kSchOn | dw_row_col<BORDER>(i, HIN, ring, cst) | (i >= 1 ? kSchSt : 0u);
+  return e;
+}
+
 // PIPE = false: the stand-alone kernel (features [B, T, F] in global memory).  PIPE = true: the consumer role of
 // the single-launch PCM -> logits kernel (pcm_logits_fused.cu): a clip's features are read from slot clip % ring of
 // the L2-resident ring once the MFCC role has published them (prod_cnt), with L2-coherent loads, and the slot is
@@ -345,6 +388,24 @@ __device__ __forceinline__ void dscnn_fused_body(const FusedParams& p, unsigned 
   for (int i = tid; i < 4 * kFC * 12; i += kFThreads) {
     const int l = i / (12 * kFC), ch = (i / 12) % kFC, k = i % 12;
     s_par[i] = k < 9 ? p.dw_w[(l * 9 + k) * kFC + ch] : 0.f;
+  }
+  uint2* s_sched = reinterpret_cast<uint2*>(smem + L::off_sched(T));
+  for (int tl = tid; tl < H0 + 7; tl += kFThreads) {
+    const int per = H0 + 7;
+    uint2 e;
+    e.x = sched_entry<false>(tl, per, 2, H0 + 1, H0, 0 * kRingCols, 0) |
+          (sched_entry<true>(tl, per, 5, H0 + 5, H0 + 2, 2 * kRingCols, kConstCol + 32) << 12);
+    int ip = tl - 8;
+    uint32_t pe = 0;
+    if (ip < 0) {
+      ip += per;
+      pe |= 2u;
+    }
+    if (ip < H0 + 6) pe |= 1u | (ip == H0 + 5 ? 4u : 0u);
+    e.x |= pe << 24;
+    e.y = sched_entry<true>(tl, per, 3, H0 + 3, H0, 1 * kRingCols, kConstCol) |
+          (sched_entry<true>(tl, per, 6, H0 + 7, H0 + 4, 3 * kRingCols, kConstCol + 64) << 12);
+    s_sched[tl] = e;
   }
   // constant K tail of the B tiles: (interior, border, interior, border) indicators of every pixel row
   for (int i = tid; i < 2 * 5 * NPIX; i += kFThreads) {
@@ -415,9 +476,10 @@ __device__ __forceinline__ void dscnn_fused_body(const FusedParams& p, unsigned 
     // TMEM: this warp's lane quarter; ring row slot s of layer l starts at column l*64 + s*32, its data
     // after an 8-column margin; a 16-column load from (segment start - 1) covers the segment and its halo
     const uint32_t my_tmem = tmem + ((uint32_t)(q * 32) << 16);
-    const uint32_t my_ld = my_tmem + 7u + (uint32_t)(8 * j);
-    unsigned char* my_dst = smem + L::off_bp + sl * L::bp_stride + j * kSboBp + (c >> 2) * kLboB + (c & 3) * 4;
-    const float4* my_par = reinterpret_cast<const float4*>(s_par) + c * 3;
+    const uint32_t my_ld = keep_u32(my_tmem + 7u + (uint32_t)(8 * j));
+    const uint32_t my_dst = keep_u32(smem_u32(smem) + (uint32_t)(L::off_bp + sl * L::bp_stride + j * kSboBp + (c >> 2) * kLboB + (c & 3) * 4));
+    const uint32_t sched_s = keep_u32(smem_u32(s_sched));
+    const uint32_t my_par = keep_u32(smem_u32(s_par) + (uint32_t)(c * 48));
     // conv1 im2col item of this thread: clip, 16-byte K-chunk (4 taps), pixel column(s).
     //   PACK = 1: 2 clips x 25 chunks x 7 column groups (columns xg, xg+7, xg+14)
     //   PACK = 2: 4 clips x 25 chunks x W0 columns, one item per thread; clip u of a slot sits at row u * kPackOff
@@ -532,15 +594,18 @@ __device__ __forceinline__ void dscnn_fused_body(const FusedParams& p, unsigned 
         ++nO;
         tc_fence_after();
       }
+      const uint2 sch = lds64(sched_s + 8u * (uint32_t)tl);
+      // a stage's row exists if its pair does: the current pair n, or pair n - 1 for rows that lag past the period end
+      const uint32_t pair_ok = (n < my_pairs ? kSchOn : 0u) | (n >= 1 ? (kSchOn << 16) : 0u);
+      auto stage_on = [&](uint32_t e) { return (e & ((e & kSchPrev) ? (pair_ok >> 16) : pair_ok)) != 0u; };
       if (seg_on) {
-        StageRow r = stage_row(tl, n, my_pairs, per, 2, H0 + 1);
-        if (r.on)
-          dw_seg<W0, 1, PACK>(my_ld + dw_row_col<false>(r.i, H0, 0 * kRingCols, 0), j, r.i >= 1, my_par + 0 * 3 * kFC,
-                              my_dst + 0 * 2 * L::bp_stride, P[0], R[0]);
-        r = stage_row(tl, n, my_pairs, per, 5, H0 + 5);
-        if (r.on)
-          dw_seg<W0 + 4, 1, PACK>(my_ld + dw_row_col<true>(r.i, H0 + 2, 2 * kRingCols, kConstCol + 32), j, r.i >= 1,
-                                  my_par + 2 * 3 * kFC, my_dst + 2 * 2 * L::bp_stride, P[2], R[2]);
+        const uint32_t e1 = sch.x & 0xfffu, e3 = (sch.x >> 12) & 0xfffu;
+        if (stage_on(e1))
+          dw_seg<W0, 1, PACK>(my_ld + (e1 & 0x1ffu), j, (e1 & kSchSt) != 0u, my_par + 0u * 48u * kFC,
+                              my_dst + (uint32_t)(0 * 2 * L::bp_stride), P[0], R[0]);
+        if (stage_on(e3))
+          dw_seg<W0 + 4, 1, PACK>(my_ld + (e3 & 0x1ffu), j, (e3 & kSchSt) != 0u, my_par + 2u * 48u * kFC,
+                                  my_dst + (uint32_t)(2 * 2 * L::bp_stride), P[2], R[2]);
       }
       if (fc_n >= 0) {
         pool_fc((long long)bid + (long long)fc_n * nblk);
@@ -574,16 +639,15 @@ __device__ __forceinline__ void dscnn_fused_body(const FusedParams& p, unsigned 
         }
       }
       {
-        StageRow r = stage_row(tl, n, my_pairs, per, 3, H0 + 3);
-        if (seg_on && r.on)
-          dw_seg<W0 + 2, 1, PACK>(my_ld + dw_row_col<true>(r.i, H0, 1 * kRingCols, kConstCol), j, r.i >= 1,
-                                  my_par + 1 * 3 * kFC, my_dst + 1 * 2 * L::bp_stride, P[1], R[1]);
-        r = stage_row(tl, n, my_pairs, per, 6, H0 + 7);
-        if (seg_on && r.on)
-          dw_seg<W0 + 6, 0, PACK>(my_ld + dw_row_col<true>(r.i, H0 + 4, 3 * kRingCols, kConstCol + 64), j, r.i >= 1,
-                                  my_par + 3 * 3 * kFC, my_dst + 3 * 2 * L::bp_stride, P[3], R[3]);
-        r = stage_row(tl, n, my_pairs, per, 8, H3);
-        if (r.on) {  // pooling of the last block's row (interior pixels; the border is added in pool_fc)
+        const uint32_t e2 = sch.y & 0xfffu, e4 = (sch.y >> 12) & 0xfffu;
+        if (seg_on && stage_on(e2))
+          dw_seg<W0 + 2, 1, PACK>(my_ld + (e2 & 0x1ffu), j, (e2 & kSchSt) != 0u, my_par + 1u * 48u * kFC,
+                                  my_dst + (uint32_t)(1 * 2 * L::bp_stride), P[1], R[1]);
+        if (seg_on && stage_on(e4))
+          dw_seg<W0 + 6, 0, PACK>(my_ld + (e4 & 0x1ffu), j, (e4 & kSchSt) != 0u, my_par + 3u * 48u * kFC,
+                                  my_dst + (uint32_t)(3 * 2 * L::bp_stride), P[3], R[3]);
+        const uint32_t ep = sch.x >> 24;   // pooling: bit 0 has a row, bit 1 previous pair, bit 2 last row of the group
+        if ((ep & 1u) && ((ep & 2u) ? n >= 1 : n < my_pairs)) {  // pooling of the last block's row (interior pixels; the border is added in pool_fc)
           if (seg_on) {
             float raw[8];
             tc_ld8(my_tmem + (uint32_t)kAcc4Col + 8u + (uint32_t)(8 * j), raw);
@@ -602,13 +666,13 @@ __device__ __forceinline__ void dscnn_fused_body(const FusedParams& p, unsigned 
               psum[PACK - 1] += (j >= 2 ? lo4 : 0.f) + (j >= 1 ? hi4 : 0.f);
             }
           }
-          if (r.i == H3 - 1) {  // last row of the group: hand the sums to pool_fc (next phase A)
+          if (ep & 4u) {  // last row of the group: hand the sums to pool_fc (next phase A)
 #pragma unroll
             for (int u = 0; u < PACK; ++u) {
               s_pool[((j * 2 + sl) * PACK + u) * kFC + c] = psum[u];
               psum[u] = 0.f;
             }
-            fc_n = tl >= 8 ? n : n - 1;
+            fc_n = (ep & 2u) ? n - 1 : n;
           }
         }
       }

@@ -40,13 +40,13 @@ pcm_logits_fused_kernel(const FastParams mp, const FusedParams fp, const unsigne
 template <typename T, int F, int NPIX, int PACK>
 static int launch_t(kws_handle_t h, FastParams& mp, FusedParams& fp, size_t mfcc_smem, cudaStream_t stream) {
   using L = FusedLayout<F, NPIX, PACK>;
-  const size_t model_smem = (size_t)L::off_feat + L::CL * L::feat_floats(fp.T) * 4;
+  const size_t model_smem = L::smem_bytes(fp.T);
   if (model_smem > 227 * 1024) return 0;
   const size_t smem_bytes = mfcc_smem > model_smem ? mfcc_smem : model_smem;
   const long long ngroups = (fp.B + L::CL - 1) / L::CL;
   if (ngroups > 0x7fffffffLL / 64) return 0;
   // role split: share of the SMs the MFCC role needs so that both roles run at the same clips/s
-  const double share = h->pipe_mfcc_share > 0.0 ? h->pipe_mfcc_share : (F == 40 ? 0.207 : 0.355);
+  const double share = h->pipe_mfcc_share > 0.0 ? h->pipe_mfcc_share : (F == 40 ? 0.218 : 0.371);
   long long grid = h->sm_count;
   long long n_mfcc = (long long)(grid * share + 0.5);
   if (n_mfcc < 1) n_mfcc = 1;

@@ -46,7 +46,7 @@ if rank == 0:
         solo.step(x, y)
     d = (solo.params - mine).abs()
     # gradient parity between the sharded and the whole-batch step (same summation, different order)
-    gd = float((solo.grads - ts.grads).abs().max().item() / solo.grads.abs().max().item())
+    gd = float((solo.grads - ts.grads / world).abs().max().item() / solo.grads.abs().max().item())   # the reduced buffer is the SUM; Adam applies 1/world
     json.dump({"world": world, "max_abs_diff_vs_single": float(d.max().item()), "frac_within_2e-5": float((d < 2e-5).float().mean().item()),
                "grad_rel_diff": gd, "ranks_equal": ranks_equal}, open(sys.argv[1], "w"))
 dist.barrier()
