@@ -203,14 +203,15 @@ int kws_train_adam(kws_handle_t h, float* params_dev, const float* grads_dev, fl
 
 /* ---- fused path: PCM -> logits ------------------------------------------------------
  * Replaces extract_features (audio_processor.py:235-278) + DepthwiseSeparableConv.forward (models.py:160-183)
- * back to back.  Batches of at least `min_clips` (default 8192) run as ONE kernel launch: MFCC CTAs and network
- * CTAs of the same grid exchange features through an L2-resident ring (HBM sees PCM in, logits out); smaller
- * batches run the MFCC kernel and the network kernel back to back.  Both give the same logits bit for bit. */
+ * back to back, as ONE kernel launch: every CTA alternates between the MFCC of its next chunk of clips (features into
+ * the CTA's own L2-resident scratch) and the network on that chunk; HBM sees PCM in and logits out.  Configurations
+ * the single-launch kernel does not cover (other channel counts, unaligned PCM, window functions ...) run the MFCC
+ * kernel and the network kernel back to back.  Both give the same logits bit for bit. */
 int kws_pcm_to_logits(kws_handle_t h, const float* pcm_dev, int64_t B, int64_t N,
                       int64_t pcm_stride, float* logits_dev, void* stream);
-/* min_clips: smallest batch that takes the single launch (>= 1; < 1 disables it); mfcc_share: share of the SMs
- * running the MFCC role, 0 = default for the feature width (0.218 at 40 coefficients, 0.371 at 10: the measured cost ratio of the two roles) */
-int kws_pcm_to_logits_configure(kws_handle_t h, int64_t min_clips, double mfcc_share);
+/* min_clips: smallest batch that takes the single launch (default 1; < 1 disables it: always two kernels);
+ * chunk_clips: clips per CTA and phase (default 32; 0 keeps the current value) */
+int kws_pcm_to_logits_configure(kws_handle_t h, int64_t min_clips, int chunk_clips);
 int kws_pcm_to_logits_host(kws_handle_t h, const float* pcm_host, int64_t B, int64_t N,
                            float* logits_host);
 /* the same two calls fed 16-bit PCM (x/32768 = librosa.load, audio_processor.py:145, happens inside the

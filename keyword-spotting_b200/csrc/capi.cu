@@ -116,7 +116,6 @@ int kws_destroy(kws_handle_t h) {
     if (h->ev[i]) cudaEventDestroy(h->ev[i]);
   if (h->d_feat_tmp) cudaFree(h->d_feat_tmp);
   if (h->d_ring) cudaFree(h->d_ring);
-  if (h->d_ring_cnt) cudaFree(h->d_ring_cnt);
   if (h->train.base) cudaFree(h->train.base);
   delete h;
   return KWS_OK;
@@ -206,8 +205,8 @@ static int pcm_to_logits_impl(kws_handle_t h, const void* pcm_dev, bool is_i16, 
   KWS_CUDA(cudaSetDevice(h->device));
   if (!pcm_dev || !logits_dev) return fail(KWS_ERR_INVALID, "null device pointer");
   if (pcm_stride < 1) return fail(KWS_ERR_INVALID, "bad stride");
-  // one launch, features through the L2-resident ring (pcm_logits_fused.cu).  Small batches cannot fill both
-  // roles' CTAs (a 256-clip batch is one wave of the model alone), so they run the two kernels back to back.
+  // one launch: every CTA alternates between the MFCC of its next chunk of clips and the network on that chunk, the
+  // features stay in the CTA's L2-resident scratch (pcm_logits_fused.cu)
   if (B >= h->pipe_min_clips) {
     const int rc = launch_pcm_logits_fused(h, pcm_dev, is_i16, B, N, pcm_stride, logits_dev, (cudaStream_t)stream);
     if (rc != 0) return rc < 0 ? rc : KWS_OK;
@@ -228,11 +227,11 @@ static int pcm_to_logits_impl(kws_handle_t h, const void* pcm_dev, bool is_i16, 
   return kws_model_forward(h, h->d_feat_tmp, B, nframes, F, logits_dev, stream);
 }
 
-int kws_pcm_to_logits_configure(kws_handle_t h, int64_t min_clips, double mfcc_share) {
+int kws_pcm_to_logits_configure(kws_handle_t h, int64_t min_clips, int chunk_clips) {
   if (!h) return fail(KWS_ERR_INVALID, "null handle");
-  if (mfcc_share < 0.0 || mfcc_share >= 1.0) return fail(KWS_ERR_INVALID, "mfcc_share must be in [0, 1)");
+  if (chunk_clips < 0 || chunk_clips > 4096) return fail(KWS_ERR_INVALID, "chunk_clips must be in [0, 4096]");
   h->pipe_min_clips = min_clips < 1 ? (int64_t)1 << 62 : min_clips;   // < 1: never use the single-launch kernel
-  h->pipe_mfcc_share = mfcc_share;
+  if (chunk_clips > 0) h->pipe_chunk_clips = chunk_clips;
   return KWS_OK;
 }
 

@@ -138,13 +138,11 @@ struct kws_handle_s {
   size_t stage_in_bytes = 0, stage_out_bytes = 0;
   float* d_feat_tmp = nullptr;   // features scratch of the two-kernel pcm->logits path (small batches)
   size_t feat_tmp_bytes = 0;
-  // single-launch pcm->logits (pcm_logits_fused.cu): L2-resident feature ring + its two counters per slot
+  // single-launch pcm->logits (pcm_logits_fused.cu): per-CTA, L2-resident feature scratch (one chunk of clips each)
   float* d_ring = nullptr;
-  unsigned* d_ring_cnt = nullptr;
   size_t ring_bytes = 0;
-  unsigned ring_slots = 0;
-  double pipe_mfcc_share = 0.0;  // share of the SMs given to the MFCC role (0 = default for the feature width)
-  int64_t pipe_min_clips = 8192; // below this batch the two kernels run back to back (see capi.cu)
+  int pipe_chunk_clips = 32;     // clips a CTA transforms before it runs the network on them
+  int64_t pipe_min_clips = 1;    // smaller batches run the two kernels back to back (see capi.cu)
   kws::TrainWorkspace train;
   void* crnn = nullptr;          // kws::CrnnWeights, owned by crnn.cu
 };

@@ -8,7 +8,7 @@ namespace kws {
 template <int LOAD_LEN, int ROUNDS, typename T>
 __global__ void __launch_bounds__(kWsThreads, 1) mfcc512_ws_kernel(const FastParams p) {
   extern __shared__ __align__(128) unsigned char smem[];
-  mfcc512_ws_body<LOAD_LEN, ROUNDS, T, false>(p, smem, blockIdx.x, gridDim.x);
+  mfcc512_ws_body<LOAD_LEN, ROUNDS, T, false>(p, smem, blockIdx.x, gridDim.x, 0, p.B, p.out, 0u);
 }
 
 // Fills the kernel parameters and the dynamic shared-memory size for a configuration the fast kernel covers:

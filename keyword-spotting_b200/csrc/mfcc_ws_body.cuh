@@ -42,31 +42,7 @@ struct FastParams {
   int off_a, off_scratch, off_b, off_melw, off_edges, off_twp, off_c0;
   int off_lows, off_lowbw, off_lowfw;   // low bins: block sums, DMMA B fragments, frame-assembly phases
   int low_bins;             // 1: bins 1..4 in float64 on the fp64 tensor core (hop 160 / frame 400 only), 0: fp32 FFT only
-  // PIPE only: `out` is a ring of 2^ring_shift clip slots; prod_cnt[slot] counts published tile halves (4 per
-  // clip: 2 tiles x 2 epilogue warps), cons_cnt[slot] counts clips the model role has finished reading
-  unsigned ring_shift;
-  unsigned* prod_cnt;
-  const unsigned* cons_cnt;
 };
-
-__device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned* p) {
-  unsigned v;
-  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void red_release_gpu_add(unsigned* p, unsigned v) {
-  asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-// spin until *p >= want.  Bounded (about a second: legitimate waits last micro- to milliseconds, the whole kernel
-// tens of milliseconds) so that a protocol bug traps instead of hanging the GPU.
-__device__ __forceinline__ void wait_counter_ge(const unsigned* p, unsigned want) {
-#pragma unroll 1
-  for (int spin = 0; spin < (1 << 21); ++spin) {
-    if ((int)(ld_acquire_gpu(p) - want) >= 0) return;
-    __nanosleep(128);
-  }
-  __trap();
-}
 
 // One CTA per SM: the kernel is bound by exposed latency, not by issue slots or HBM, so what counts is the
 // number of resident compute warps.  ptxas needs 128 registers for the compute path, i.e. 16 warps per SM:
@@ -125,13 +101,18 @@ template <> __device__ __forceinline__ constexpr float power_scale<short>() { re
 
 // T = float or short.  kLead = samples kept in front of a tile (16 bytes, so that the TMA destination of a
 // tile that starts inside the clip stays 16-byte aligned while sample s0 - 1 is available)
-// PIPE = false: the stand-alone kernel (features to p.out[clip]).  PIPE = true: the producer role of the
-// single-launch PCM -> logits kernel (pcm_logits_fused.cu): features go to slot clip % ring of an L2-resident
-// ring and each finished tile is published through p.prod_cnt (see FeatureRing in common.cuh).
-// bid / nblk: this CTA's index and the CTA count of its role.
-template <int LOAD_LEN, int ROUNDS, typename T, bool PIPE>
+// The body works on the sub-batch of `nclips` clips starting at clip `clip0` of p.pcm and writes the features of its
+// clip c to out_base[c] (c = 0 .. nclips-1); tiles bid, bid + nblk, ... of that sub-batch are this CTA's.
+//   CHUNK = false: the stand-alone kernel (clip0 = 0, nclips = p.B, out_base = p.out, grid-strided tiles).
+//   CHUNK = true : one phase of the single-launch PCM -> logits kernel (pcm_logits_fused.cu): the CTA transforms
+//                  its next chunk of clips into its own L2-resident scratch (bid = 0, nblk = 1) before the network
+//                  phase consumes it; tensor memory is allocated once by the caller (tmem_ext) and the mbarriers
+//                  are invalidated at the end so that the next phase can re-initialise them.
+template <int LOAD_LEN, int ROUNDS, typename T, bool CHUNK>
 __device__ __forceinline__ void mfcc512_ws_body(const FastParams& p, unsigned char* smem, const unsigned bid,
-                                                const unsigned nblk) {
+                                                const unsigned nblk, const long long clip0, const long long nclips,
+                                                float* out_base, const uint32_t tmem_ext) {
+  const long long total_tiles = nclips * p.tiles_per_clip;
   constexpr int kLead = 16 / (int)sizeof(T);
   // [0,1] raw stage full, [2,3] raw stage empty, [4] A rows of the tile written, [5] tile MMAs retired,
   // [6] second service warp has drained its accumulator rows, [7] low-bin block sums of the tile written by every
@@ -163,7 +144,7 @@ __device__ __forceinline__ void mfcc512_ws_body(const FastParams& p, unsigned ch
     mbar_init(bar_epi, 1);
     fence_mbar_init();
   }
-  if (warp == 0 && do_dct) {
+  if (!CHUNK && warp == 0 && do_dct) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)),
                  "n"(kTmemCols));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
@@ -204,10 +185,10 @@ __device__ __forceinline__ void mfcc512_ws_body(const FastParams& p, unsigned ch
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem = do_dct ? s_tmem : 0u;
+  const uint32_t tmem = CHUNK ? tmem_ext : (do_dct ? s_tmem : 0u);
   // tiles of this CTA: bid + it * nblk, it = 0 .. n_it-1
-  const int n_it = (p.total_tiles > (long long)bid)
-                       ? (int)((p.total_tiles - bid + nblk - 1) / nblk)
+  const int n_it = (total_tiles > (long long)bid)
+                       ? (int)((total_tiles - bid + nblk - 1) / nblk)
                        : 0;
 
   // Tile `it` of this CTA.  A clip's first tile keeps all 13 compute warps busy, its second one 12, so a CTA
@@ -216,7 +197,7 @@ __device__ __forceinline__ void mfcc512_ws_body(const FastParams& p, unsigned ch
   const bool swap_ok = (nblk & 1u) == 0u;
   auto tile_of = [&](int it) -> unsigned {
     unsigned id = bid + (unsigned)it * nblk;  // launcher: total_tiles < 2^31
-    if (swap_ok && (it & 1) && (long long)(id | 1u) < p.total_tiles) id ^= 1u;
+    if (swap_ok && (it & 1) && (long long)(id | 1u) < total_tiles) id ^= 1u;
     return id;
   };
 
@@ -237,7 +218,7 @@ __device__ __forceinline__ void mfcc512_ws_body(const FastParams& p, unsigned ch
       T* raw = reinterpret_cast<T*>(smem + (size_t)(it & 1) * p.raw_stride);
       mbar_expect_tx(bar, bytes);
       tma_load_1d(smem_u32(raw + (s0 >= kLead ? 0 : kLead)),
-                  reinterpret_cast<const T*>(p.pcm) + (size_t)clip * p.stride + first, bytes, bar);
+                  reinterpret_cast<const T*>(p.pcm) + (size_t)(clip0 + clip) * p.stride + first, bytes, bar);
     };
     auto issue_mma = [&]() {  // converged warp, elected lane: D[128 x 48] = Ahi*Bhi + Alo*Bhi + Ahi*Blo over Kpad
       tc_fence_after();
@@ -296,11 +277,7 @@ __device__ __forceinline__ void mfcc512_ws_body(const FastParams& p, unsigned ch
         tc_fence_before();
         const int row = warp * 32 + lane;
         const int f = t * kTileFrames + row;
-        const unsigned slot = PIPE ? (clip & ((1u << p.ring_shift) - 1u)) : clip;
-        if (PIPE) {  // the slot's previous clip (one ring generation back) must have been consumed
-          if (lane == 0) wait_counter_ge(p.cons_cnt + slot, clip >> p.ring_shift);
-          __syncwarp();
-        }
+
         // c0 of this tile is read BEFORE warp 1 releases the accumulator: its release lets the next tile's MMAs
         // go, and their completion lets the compute warps overwrite this half of s_c0 two tiles on
         const float c0 = (row < kTileFrames) ? s_c0[(it & 1) * kTileFrames + row] : 0.f;
@@ -310,7 +287,7 @@ __device__ __forceinline__ void mfcc512_ws_body(const FastParams& p, unsigned ch
         }
         if (row < kTileFrames && f < p.nframes) {
           v[0] = p.append_energy ? c0 : v[0] + c0;
-          float* o = p.out + ((size_t)slot * p.nframes + f) * p.ncep;
+          float* o = out_base + ((size_t)clip * p.nframes + f) * p.ncep;
           if ((p.ncep & 3) == 0) {
 #pragma unroll
             for (int c = 0; c < kDctN; c += 4)
@@ -320,10 +297,6 @@ __device__ __forceinline__ void mfcc512_ws_body(const FastParams& p, unsigned ch
             for (int c = 0; c < kDctN; ++c)
               if (c < p.ncep) o[c] = v[c];
           }
-        }
-        if (PIPE) {  // publish this warp's rows of the tile: stores -> warp sync -> cumulative release by lane 0
-          __syncwarp();
-          if (lane == 0) red_release_gpu_add(p.prod_cnt + slot, 1u);
         }
       }
     }
@@ -601,8 +574,8 @@ __device__ __forceinline__ void mfcc512_ws_body(const FastParams& p, unsigned ch
           for (int r = 0; r < ROUNDS; ++r) {
             const int j = l + 16 * r;
             if (j < p.M) {
-              if (fA < p.nframes) p.out[((size_t)clip * p.nframes + fA) * p.M + j] = lm[r].x;
-              if (fB < p.nframes) p.out[((size_t)clip * p.nframes + fB) * p.M + j] = lm[r].y;
+              if (fA < p.nframes) out_base[((size_t)clip * p.nframes + fA) * p.M + j] = lm[r].x;
+              if (fB < p.nframes) out_base[((size_t)clip * p.nframes + fB) * p.M + j] = lm[r].y;
             }
           }
         } else {
@@ -652,8 +625,11 @@ __device__ __forceinline__ void mfcc512_ws_body(const FastParams& p, unsigned ch
     }
   }
   __syncthreads();
-  if (warp == 0 && do_dct)
+  if (CHUNK) {  // the next phase of the caller's loop re-initialises these barriers
+    if (tid < 9) asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(smem_u32(&s_bar[tid])) : "memory");
+  } else if (warp == 0 && do_dct) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(kTmemCols));
+  }
 }
 
 // mfcc_ws.cu

@@ -6,7 +6,7 @@ namespace kws {
 template <int F, int NPIX, int PACK>
 __global__ void __launch_bounds__(kFThreads, 1) dscnn_fused_kernel(const FusedParams p) {
   extern __shared__ __align__(128) unsigned char smem[];
-  dscnn_fused_body<F, NPIX, PACK, false>(p, smem, blockIdx.x, gridDim.x);
+  dscnn_fused_body<F, NPIX, PACK, false>(p, smem, blockIdx.x, gridDim.x, p.B, p.feats, p.logits, 0u);
 }
 
 // ---- host side ------------------------------------------------------------------------------

@@ -63,7 +63,7 @@ constexpr int kSboBp = (kKCp / 4) * kLboB;   //                    depthwise-out
 constexpr int kAImgBytes = 8 * kSboA1 + 4 * 8 * kSboAp;
 
 struct FusedParams {
-  const float* feats;     // [B, T, F]; PIPE: ring of 2^ring_shift clip slots written by the MFCC role
+  const float* feats;     // [B, T, F]
   float* logits;          // [B, ncls]
   long long B;
   int T, H0, ncls;
@@ -72,15 +72,11 @@ struct FusedParams {
   const float* border;    // [5][64] row 0 unused; ReLU(pointwise bias) of block l
   const float* fc_w;      // [64][ncls]
   const float* fc_b;      // [ncls]
-  // PIPE only (single-launch PCM -> logits): see FastParams
-  unsigned ring_shift, prod_per_clip;
-  const unsigned* prod_cnt;
-  unsigned* cons_cnt;
 };
 
-// CTA-wide barrier of the model role.  Stand-alone kernel: all kFThreads threads of the block.  PIPE: the block
+// CTA-wide barrier of the model role.  Stand-alone kernel: all kFThreads threads of the block.  CHUNK: the block
 // has one more (idle, exited) warp than the role uses, so the role's 14 warps meet at named barrier 1.
-template <bool PIPE>
+template <bool CHUNK>
 __device__ __forceinline__ void fused_sync();
 
 // One step of the depthwise 3x3 (zero padding 1) of a block for this thread's (slot, channel) on
@@ -262,7 +258,7 @@ __device__ __forceinline__ StageRow stage_row(int tl, int n, int npair, int per,
   return StageRow{i, cn >= 0 && cn < npair && i < len};
 }
 
-template <int F, int NPIX, int PACK, int SLOT, bool PIPE>
+template <int F, int NPIX, int PACK, int SLOT, bool CHUNK>
 __device__ __forceinline__ void fused_mma_warp(unsigned char* smem, uint32_t tmem, uint32_t barO, uint32_t barE, int H0,
                                                int my_pairs) {
   using L = FusedLayout<F, NPIX, PACK>;
@@ -278,10 +274,10 @@ __device__ __forceinline__ void fused_mma_warp(unsigned char* smem, uint32_t tme
   }
   const uint32_t d0 = tmem + ((uint32_t)(SLOT * 16) << 16) + 8u;  // ring rows start after an 8-column margin
   const int per = H0 + 7, total = my_pairs * per + 7;
-  fused_sync<PIPE>();  // features of the first pair loaded
+  fused_sync<CHUNK>();  // features of the first pair loaded
   int tl = 0, n = 0;
   for (int tg = 0; tg < total; ++tg) {
-    fused_sync<PIPE>();  // phase A written
+    fused_sync<CHUNK>();  // phase A written
     tc_fence_after();
     {
       StageRow r = stage_row(tl, n, my_pairs, per, 3, H0);
@@ -290,7 +286,7 @@ __device__ __forceinline__ void fused_mma_warp(unsigned char* smem, uint32_t tme
       if (r.on) issue_gemm<kKCp / 8>(d0 + 3 * kRingCols + (r.i & 1) * 32, ap[2], bp[2], kIdescF);
       tc_commit_elect(barO);
     }
-    fused_sync<PIPE>();  // phase B written
+    fused_sync<CHUNK>();  // phase B written
     tc_fence_after();
     {
       StageRow r = stage_row(tl, n, my_pairs, per, 0, H0);
@@ -342,13 +338,18 @@ __device__ __forceinline__ uint32_t sched_entry(int tl, int per, int g, int len,
   return e;
 }
 
-// PIPE = false: the stand-alone kernel (features [B, T, F] in global memory).  PIPE = true: the consumer role of
-// the single-launch PCM -> logits kernel (pcm_logits_fused.cu): a clip's features are read from slot clip % ring of
-// the L2-resident ring once the MFCC role has published them (prod_cnt), with L2-coherent loads, and the slot is
-// handed back through cons_cnt after the last read.  bid / nblk: this CTA's index and the CTA count of its role.
-template <int F, int NPIX, int PACK, bool PIPE>
+// The body runs the network on `nclips` clips whose features are feats_base[c] (c = 0 .. nclips-1) and writes
+// logits_base[c]; groups bid, bid + nblk, ... of those clips are this CTA's.
+//   CHUNK = false: the stand-alone kernel (nclips = p.B, feats_base = p.feats, logits_base = p.logits).
+//   CHUNK = true : one phase of the single-launch PCM -> logits kernel (pcm_logits_fused.cu): the features are the
+//                  chunk this CTA's MFCC phase has just written to its L2-resident scratch -- read with L2-coherent
+//                  loads, the same addresses are rewritten every chunk --, the block has one more warp than the
+//                  role uses, tensor memory belongs to the caller (tmem_ext) and the mbarriers are invalidated at
+//                  the end.
+template <int F, int NPIX, int PACK, bool CHUNK>
 __device__ __forceinline__ void dscnn_fused_body(const FusedParams& p, unsigned char* smem, const unsigned bid,
-                                                 const unsigned nblk) {
+                                                 const unsigned nblk, const long long nclips, const float* feats_base,
+                                                 float* logits_base, const uint32_t tmem_ext) {
   constexpr int W0 = (F - 6) / 2 + 1, W3 = W0 + 6, NSEG = NPIX / 8;
   static_assert(W3 <= NPIX && NPIX % 8 == 0 && NSEG <= 3, "row of the widest layer must fit the MMA N");
   static_assert(PACK == 1 || (PACK == 2 && W3 + 2 < kPackOff && kPackOff + W3 <= NPIX), "two clips per slot need a zero gap");
@@ -356,7 +357,7 @@ __device__ __forceinline__ void dscnn_fused_body(const FusedParams& p, unsigned 
   constexpr int FP = L::FP, CL = L::CL;
   __shared__ __align__(8) unsigned long long s_bar[2];
   __shared__ uint32_t s_tmem;
-  if (PIPE && threadIdx.x >= kFThreads) return;  // the block is sized for the MFCC role: one warp more
+  if (CHUNK && threadIdx.x >= kFThreads) return;  // the block is sized for the MFCC role: one warp more
   float* s_feat = reinterpret_cast<float*>(smem + L::off_feat);  // [CL][(T + 4) * FP], zero padded, tf32-rounded
   float* s_pool = reinterpret_cast<float*>(smem + L::off_pool);  // [3][2][PACK][64]
   float* s_par = reinterpret_cast<float*>(smem + L::off_par);    // [4][64][12]
@@ -365,14 +366,14 @@ __device__ __forceinline__ void dscnn_fused_body(const FusedParams& p, unsigned 
   const uint32_t barO = smem_u32(&s_bar[0]), barE = smem_u32(&s_bar[1]);
   const int T = p.T, H0 = p.H0, TF = T * F;
   const int feat_stride = (int)L::feat_floats(T);
-  const long long npairs = (p.B + CL - 1) / CL;  // groups of CL clips ("pairs" when PACK = 1)
+  const long long npairs = (nclips + CL - 1) / CL;  // groups of CL clips ("pairs" when PACK = 1)
 
   if (tid == 0) {
     mbar_init(barO, 2);
     mbar_init(barE, 2);
     fence_mbar_init();
   }
-  if (warp == 0) {
+  if (!CHUNK && warp == 0) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "n"(512));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
   }
@@ -384,7 +385,7 @@ __device__ __forceinline__ void dscnn_fused_body(const FusedParams& p, unsigned 
     const int nz = (L::off_feat - L::off_b1) / 16 + (CL * feat_stride * 4 + 15) / 16;  // B tiles, pool, feature pads
     for (int i = tid; i < nz; i += kFThreads) z[i] = make_uint4(0, 0, 0, 0);
   }
-  fused_sync<PIPE>();
+  fused_sync<CHUNK>();
   for (int i = tid; i < 4 * kFC * 12; i += kFThreads) {
     const int l = i / (12 * kFC), ch = (i / 12) % kFC, k = i % 12;
     s_par[i] = k < 9 ? p.dw_w[(l * 9 + k) * kFC + ch] : 0.f;
@@ -431,9 +432,9 @@ __device__ __forceinline__ void dscnn_fused_body(const FusedParams& p, unsigned 
   }
   fence_proxy_async();
   tc_fence_before();
-  fused_sync<PIPE>();
+  fused_sync<CHUNK>();
   tc_fence_after();
-  const uint32_t tmem = s_tmem;
+  const uint32_t tmem = CHUNK ? tmem_ext : s_tmem;
   if (warp < 4) {  // zero all of tensor memory once, then the constant border rows of the three padded layers
     for (int col = 0; col < 512; col += 16) {
       asm volatile(
@@ -460,15 +461,15 @@ __device__ __forceinline__ void dscnn_fused_body(const FusedParams& p, unsigned 
     asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
   }
   tc_fence_before();
-  fused_sync<PIPE>();
+  fused_sync<CHUNK>();
   tc_fence_after();
 
   // pairs of this CTA: bid, + nblk, ... (the launcher keeps nblk <= npairs)
   const int my_pairs = (int)((npairs - bid + nblk - 1) / nblk);
   if (warp == kFCWarps) {
-    fused_mma_warp<F, NPIX, PACK, 0, PIPE>(smem, tmem, barO, barE, H0, my_pairs);
+    fused_mma_warp<F, NPIX, PACK, 0, CHUNK>(smem, tmem, barO, barE, H0, my_pairs);
   } else if (warp == kFCWarps + 1) {
-    fused_mma_warp<F, NPIX, PACK, 1, PIPE>(smem, tmem, barO, barE, H0, my_pairs);
+    fused_mma_warp<F, NPIX, PACK, 1, CHUNK>(smem, tmem, barO, barE, H0, my_pairs);
   } else {
     // =========================== compute warps ===========================
     const int j = warp >> 2, q = warp & 3, sl = lane >> 4, c = q * 16 + (lane & 15);
@@ -528,34 +529,17 @@ __device__ __forceinline__ void dscnn_fused_body(const FusedParams& p, unsigned 
 #pragma unroll
         for (int d = 16; d >= 1; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
         const long long b = CL * pair + sc;
-        if (lane == 0 && b < p.B) p.logits[b * p.ncls + k] = acc + p.fc_b[k];
+        if (lane == 0 && b < nclips) logits_base[b * p.ncls + k] = acc + p.fc_b[k];
       }
     };
 
-    // PIPE: ring slot of a clip, "all four tile halves of this clip published" and "slot free again"
-    const unsigned ring_mask = PIPE ? ((1u << p.ring_shift) - 1u) : 0u;
-    auto clip_wait = [&](long long clip) {
-      wait_counter_ge(p.prod_cnt + ((unsigned)clip & ring_mask), p.prod_per_clip * ((unsigned)(clip >> p.ring_shift) + 1u));
-    };
-    auto clip_release = [&](long long clip) { red_release_gpu_add(p.cons_cnt + ((unsigned)clip & ring_mask), 1u); };
     {  // features of the first group -> zero-padded, tf32-rounded maps in shared memory
       const long long first = (long long)CL * bid;
-      if (PIPE) {
-        if (tid < CL && first + tid < p.B) clip_wait(first + tid);
-        asm volatile("bar.sync 2, %0;" ::"n"(kCThreads) : "memory");  // compute warps only
-        for (int i = tid; i < CL * TF; i += kCThreads) {
-          const int sc = i / TF, rem = i - sc * TF, fr = rem / F, fc = rem - fr * F;
-          const float* src = p.feats + (size_t)((unsigned)(first + sc) & ring_mask) * TF + rem;
-          s_feat[sc * feat_stride + (fr + 2) * FP + fc + 2] = (first + sc < p.B) ? to_tf32(__ldcg(src)) : 0.f;
-        }
-        asm volatile("bar.sync 2, %0;" ::"n"(kCThreads) : "memory");  // every load has landed
-        if (tid < CL && first + tid < p.B) clip_release(first + tid);
-      } else {
-        const float* src = p.feats + first * TF;
-        for (int i = tid; i < CL * TF; i += kCThreads) {
-          const int sc = i / TF, rem = i - sc * TF, fr = rem / F, fc = rem - fr * F;
-          s_feat[sc * feat_stride + (fr + 2) * FP + fc + 2] = (first + sc < p.B) ? to_tf32(__ldg(src + i)) : 0.f;
-        }
+      const float* src = feats_base + first * TF;
+      for (int i = tid; i < CL * TF; i += kCThreads) {
+        const int sc = i / TF, rem = i - sc * TF, fr = rem / F, fc = rem - fr * F;
+        s_feat[sc * feat_stride + (fr + 2) * FP + fc + 2] =
+            (first + sc < nclips) ? to_tf32(CHUNK ? __ldcg(src + i) : __ldg(src + i)) : 0.f;
       }
     }
     float psum[PACK];
@@ -566,7 +550,7 @@ __device__ __forceinline__ void dscnn_fused_body(const FusedParams& p, unsigned 
     for (int l = 0; l < 4; ++l)
 #pragma unroll
       for (int x = 0; x < 4; ++x) P[l][x] = R[l][x] = fsplat(0.f);
-    fused_sync<PIPE>();
+    fused_sync<CHUNK>();
 
     int tl = 0, n = 0, fc_n = -1;  // fc_n: group (CTA-local index) whose pooled sums wait in s_pool
     for (int tg = 0; tg < total; ++tg) {
@@ -574,20 +558,12 @@ __device__ __forceinline__ void dscnn_fused_body(const FusedParams& p, unsigned 
       float fl_v = 0.f;
       const int fl_fr = 2 * tl - 4 + fl_r;
       const bool fl_do = fl_on && n + 1 < my_pairs && fl_fr >= 0 && fl_fr < T;
-      if (PIPE && tid < CL && n + 1 < my_pairs) {
-        // next group's clips: wait for the MFCC role one step before the refill starts (the barrier that ends this
-        // phase publishes it to the refill threads); hand the slot back one step after the last row was read
-        const long long clip = CL * ((long long)bid + (long long)(n + 1) * nblk) + tid;
-        if (clip < p.B) {
-          if (tl == 1) clip_wait(clip);
-          if (2 * tl - 4 == ((T + 1) & ~1)) clip_release(clip);
-        }
-      }
       if (fl_do) {
         const long long clip = CL * ((long long)bid + (long long)(n + 1) * nblk) + fl_s;
-        if (clip < p.B)
-          fl_v = PIPE ? __ldcg(p.feats + (size_t)((unsigned)clip & ring_mask) * TF + fl_fr * F + fl_c)
-                      : __ldg(p.feats + clip * TF + fl_fr * F + fl_c);
+        if (clip < nclips) {
+          const float* src = feats_base + clip * TF + fl_fr * F + fl_c;
+          fl_v = CHUNK ? __ldcg(src) : __ldg(src);
+        }
       }
       if (tg > 0) {  // the GEMMs issued after the previous phase A (pw1, pw3) have retired
         mbar_wait(barO, nO & 1);
@@ -614,7 +590,7 @@ __device__ __forceinline__ void dscnn_fused_body(const FusedParams& p, unsigned 
       if (fl_do) s_feat[fl_s * feat_stride + (fl_fr + 2) * FP + fl_c + 2] = to_tf32(fl_v);
       fence_proxy_async();
       tc_fence_before();
-      fused_sync<PIPE>();
+      fused_sync<CHUNK>();
       // ================= phase B: conv1 im2col, depthwise of blocks 2 and 4, pooling =================
       if (tg > 0) {  // the GEMMs issued after the previous phase B (conv1, pw2, pw4) have retired
         mbar_wait(barE, nE & 1);
@@ -678,7 +654,7 @@ __device__ __forceinline__ void dscnn_fused_body(const FusedParams& p, unsigned 
       }
       fence_proxy_async();
       tc_fence_before();
-      fused_sync<PIPE>();
+      fused_sync<CHUNK>();
       if (++tl == per) {
         tl = 0;
         ++n;
@@ -691,8 +667,12 @@ __device__ __forceinline__ void dscnn_fused_body(const FusedParams& p, unsigned 
     if (fc_n >= 0) pool_fc((long long)bid + (long long)fc_n * nblk);
   }
   tc_fence_before();
-  fused_sync<PIPE>();
-  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(512));
+  fused_sync<CHUNK>();
+  if (CHUNK) {  // the next phase of the caller's loop re-initialises these barriers
+    if (tid < 2) asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(smem_u32(&s_bar[tid])) : "memory");
+  } else if (warp == 0) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(512));
+  }
 }
 
 // model_fused.cu

@@ -3,62 +3,106 @@
 // Reference chain replaced: AudioProcessor.extract_features (kws/libs/audio_processor.py:235-278 -> psf.mfcc)
 // followed by DepthwiseSeparableConv.forward (kws/libs/models.py:160-183).
 //
-// One persistent CTA per SM, two ROLES in the same grid:
-//   * CTAs [0, n_mfcc): the warp-specialised MFCC pipeline of mfcc_ws_body.cuh (TMA ring -> register FFT ->
-//     mel/log -> tcgen05 DCT), writing each tile of 52 frames into slot `clip % R` of a feature RING;
-//   * CTAs [n_mfcc, grid): the row-streamed tcgen05 network of model_fused_body.cuh, reading a clip's features
-//     from that slot as soon as all of its tiles are published, and handing the slot back after the last read.
-// The ring (R = 1024 clips x 15.8 KB = 16 MB by default) lives in the 126 MB L2: a slot is overwritten ~R clips
-// later, long before its lines would be evicted, so the features never travel to HBM and back -- HBM sees the
-// PCM (64 KB/clip) and the logits (48 B/clip).  Handshake per slot, two monotonic counters in global memory:
-//     prod_cnt[slot] += 1   by each MFCC epilogue warp after its rows of a tile are stored (red.release.gpu)
-//     cons_cnt[slot] += 1   by the model CTA after its last load of the clip                (red.release.gpu)
-//   clip c (generation g = c / R) may be READ  when prod_cnt[slot] >= prod_per_clip * (g + 1)   (ld.acquire.gpu)
-//                                  may be WRITTEN when cons_cnt[slot] >= g
-// Both roles walk their work in increasing clip order with a static round-robin assignment, so the smallest
-// unconsumed clip can always be produced and then consumed: no deadlock for any R >= 1 as long as all CTAs are
-// co-resident (grid <= SM count, one CTA per SM by shared memory).  The split n_mfcc : n_model follows the
-// measured per-clip cost of the two roles (handle setting; default from the rates in DESIGN.md section 4).
+// One persistent CTA per SM.  Every CTA owns a contiguous range of clips and walks it in CHUNKS (32 clips by
+// default), alternating between the two phases it shares its shared memory and tensor memory between:
+//   1. MFCC phase   : the warp-specialised pipeline of mfcc_ws_body.cuh (TMA ring -> register FFT -> float64 low
+//                     bins -> mel/log -> tcgen05 DCT) turns the chunk's PCM into features in the CTA's OWN scratch
+//                     (chunk x 15.8 KB; 148 CTAs x 32 clips = 75 MB, inside the 126 MB L2, rewritten every chunk);
+//   2. network phase: the row-streamed tcgen05 network of model_fused_body.cuh reads those features back with
+//                     L2-coherent loads and writes the chunk's logits.
+// A CTA only ever consumes what it produced itself, so the phases need no handshake beyond the CTA barrier between
+// them: no flags, no inter-CTA ordering, nothing to balance (each CTA does the same work per clip), and a small
+// batch is simply one short chunk per CTA.  HBM sees the PCM (64 KB/clip) and the logits (48 B/clip); the feature
+// scratch lives in L2.  Per chunk the phase switch costs one re-initialisation of each role's shared-memory tables
+// (a few microseconds against ~2 ms of work per 32-clip chunk).
+//
+// Round-2 history, measured on B200 at 65 536 clips: a producer/consumer split of the grid (MFCC CTAs feeding
+// network CTAs through an L2 ring with per-slot counters) reached 2.17 M clips/s against 2.34 M for the two kernels
+// back to back -- the network CTAs ran 5-10 % slower next to polling producers and the two roles had to be balanced
+// to within one CTA; this design replaced it.
+#include <cstdlib>
+
 #include "model_fused_body.cuh"
 
 namespace kws {
 
 constexpr int kPipeThreads = kWsThreads > kFThreads ? kWsThreads : kFThreads;
-static_assert(kPipeThreads == kWsThreads, "the block is sized for the MFCC role; the model role idles the rest");
+static_assert(kPipeThreads == kWsThreads, "the block is sized for the MFCC phase; the network phase idles one warp");
 
-template <typename T, int F, int NPIX, int PACK>
-__global__ void __launch_bounds__(kPipeThreads, 1)
-pcm_logits_fused_kernel(const FastParams mp, const FusedParams fp, const unsigned n_mfcc) {
+// The network phase is a separate (non-inlined) device function: with both phases inlined into one loop body ptxas
+// allocated registers for an 11 K-instruction function and spilled the stencil state and FFT registers inside the
+// hot loops (-45 %).  The MFCC phase stays inline in the kernel so that its parameter record keeps its place in the
+// constant bank (as a function argument it lives in local memory: +26 % instructions, measured); the network reads
+// its few parameters by value (-2 %).  The dynamic shared memory is re-declared inside the function (same array),
+// so that the address space stays known.
+template <int F, int NPIX, int PACK>
+__device__ __noinline__ void network_phase(const FusedParams fp, long long nc, const float* feats, float* logits,
+                                           uint32_t tmem) {
   extern __shared__ __align__(128) unsigned char smem[];
-  if (blockIdx.x < n_mfcc) {
-    mfcc512_ws_body<400, kWsRounds, T, true>(mp, smem, blockIdx.x, n_mfcc);
-  } else {
-    dscnn_fused_body<F, NPIX, PACK, true>(fp, smem, blockIdx.x - n_mfcc, gridDim.x - n_mfcc);
-  }
+  dscnn_fused_body<F, NPIX, PACK, true>(fp, smem, 0u, 1u, nc, feats, logits, tmem);
 }
 
 template <typename T, int F, int NPIX, int PACK>
-static int launch_t(kws_handle_t h, FastParams& mp, FusedParams& fp, size_t mfcc_smem, cudaStream_t stream) {
+__global__ void __launch_bounds__(kPipeThreads, 1)
+pcm_logits_fused_kernel(const FastParams mp, const FusedParams fp, float* scratch, const int chunk_clips, const int skip) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  __shared__ uint32_t s_tmem_all;
+  using L = FusedLayout<F, NPIX, PACK>;
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
+  if (warp == 0) {  // all of tensor memory, once: the MFCC phase uses 64 columns of it, the network all 512
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem_all)), "n"(512));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = s_tmem_all;
+  // this CTA's clips: groups of CL clips split evenly over the grid (a group is the network's unit of work)
+  const long long ngroups = (fp.B + L::CL - 1) / L::CL;
+  const long long lo = L::CL * (ngroups * blockIdx.x / gridDim.x);
+  long long hi = L::CL * (ngroups * (blockIdx.x + 1) / gridDim.x);
+  if (hi > fp.B) hi = fp.B;
+  float* my = scratch + (size_t)blockIdx.x * chunk_clips * fp.T * F;
+  for (long long c0 = lo; c0 < hi; c0 += chunk_clips) {
+    const long long nc = hi - c0 < chunk_clips ? hi - c0 : chunk_clips;
+    if (!(skip & 1)) mfcc512_ws_body<400, kWsRounds, T, true>(mp, smem, 0u, 1u, c0, nc, my, tmem);
+    __threadfence();  // the features were written through L2 by this CTA's epilogue warps
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (!(skip & 2)) network_phase<F, NPIX, PACK>(fp, nc, my, fp.logits + c0 * fp.ncls, tmem);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+  }
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(512));
+}
+
+template <typename T, int F, int NPIX, int PACK>
+static int launch_t(kws_handle_t h, FastParams& mp, FusedParams& fp, size_t mfcc_smem, int chunk, cudaStream_t stream) {
   using L = FusedLayout<F, NPIX, PACK>;
   const size_t model_smem = L::smem_bytes(fp.T);
   if (model_smem > 227 * 1024) return 0;
   const size_t smem_bytes = mfcc_smem > model_smem ? mfcc_smem : model_smem;
   const long long ngroups = (fp.B + L::CL - 1) / L::CL;
   if (ngroups > 0x7fffffffLL / 64) return 0;
-  // role split: share of the SMs the MFCC role needs so that both roles run at the same clips/s
-  const double share = h->pipe_mfcc_share > 0.0 ? h->pipe_mfcc_share : (F == 40 ? 0.218 : 0.371);
   long long grid = h->sm_count;
-  long long n_mfcc = (long long)(grid * share + 0.5);
-  if (n_mfcc < 1) n_mfcc = 1;
-  if (n_mfcc > grid - 1) n_mfcc = grid - 1;
-  if (n_mfcc > mp.total_tiles) n_mfcc = mp.total_tiles;
-  long long n_model = grid - n_mfcc;
-  if (n_model > ngroups) n_model = ngroups;
-  grid = n_mfcc + n_model;
+  if (grid > ngroups) grid = ngroups;
+  chunk = (chunk + L::CL - 1) / L::CL * L::CL;
+  // scratch: one chunk of features per CTA, allocated once per handle (grows with the chunk size / feature shape)
+  const size_t need = (size_t)h->sm_count * chunk * fp.T * F * sizeof(float);
+  if (need > h->ring_bytes) {
+    if (h->d_ring) KWS_CUDA(cudaFree(h->d_ring));
+    h->d_ring = nullptr;
+    h->ring_bytes = 0;
+    KWS_CUDA(cudaMalloc((void**)&h->d_ring, need));
+    h->ring_bytes = need;
+  }
   auto kern = pcm_logits_fused_kernel<T, F, NPIX, PACK>;
   if (int rc = ensure_dyn_smem(kern, smem_bytes, true)) return rc;
-  KWS_CUDA(cudaMemsetAsync(h->d_ring_cnt, 0, (size_t)2 * h->ring_slots * sizeof(unsigned), stream));
-  kern<<<(unsigned)grid, kPipeThreads, smem_bytes, stream>>>(mp, fp, (unsigned)n_mfcc);
+  // KWS_PHASE_SKIP (timing aid only; the logits are then meaningless): 1 = skip the MFCC phase, 2 = skip the network phase
+  static const int skip = [] { const char* e = std::getenv("KWS_PHASE_SKIP"); return e ? std::atoi(e) : 0; }();
+  kern<<<(unsigned)grid, kPipeThreads, smem_bytes, stream>>>(mp, fp, h->d_ring, chunk, skip);
   KWS_CHECK_LAUNCH(h);
   return 1;
 }
@@ -71,49 +115,27 @@ int launch_pcm_logits_fused(kws_handle_t h, const void* pcm_dev, bool is_i16, in
   if (h->model.path != 0) return 0;
   const int64_t nframes = kws_num_frames(N, t.cfg.frame_len, t.cfg.frame_step);
   const int F = t.ncep;
-  // ring: power-of-two slot count, allocated once per handle (re-allocated when the feature shape grows)
-  unsigned shift = 10;
-  if (const char* e = std::getenv("KWS_RING_SLOTS")) {
+  int chunk = h->pipe_chunk_clips;
+  if (const char* e = std::getenv("KWS_CHUNK_CLIPS")) {
     const long v = std::atol(e);
-    if (v >= 2 && v <= (1 << 20)) {
-      shift = 0;
-      while ((1L << (shift + 1)) <= v) ++shift;
-    }
-  }
-  const size_t slot_bytes = (size_t)nframes * F * 4;
-  const size_t need = slot_bytes << shift;
-  if (need > h->ring_bytes || h->ring_slots != (1u << shift)) {
-    if (h->d_ring) KWS_CUDA(cudaFree(h->d_ring));
-    if (h->d_ring_cnt) KWS_CUDA(cudaFree(h->d_ring_cnt));
-    h->d_ring = nullptr;
-    h->d_ring_cnt = nullptr;
-    h->ring_bytes = 0;
-    KWS_CUDA(cudaMalloc((void**)&h->d_ring, need));
-    KWS_CUDA(cudaMalloc((void**)&h->d_ring_cnt, (size_t)2 * sizeof(unsigned) << shift));
-    h->ring_bytes = need;
-    h->ring_slots = 1u << shift;
+    if (v >= 1 && v <= 4096) chunk = (int)v;
   }
   FastParams mp;
   size_t mfcc_smem = 0;
-  if (!fill_fast_params(h, pcm_dev, is_i16, B, N, pcm_stride, h->d_ring, kModeMfcc, &mp, &mfcc_smem)) return 0;
+  // out_dev is replaced by the per-CTA scratch inside the kernel; any aligned non-null pointer passes the checks
+  if (!fill_fast_params(h, pcm_dev, is_i16, B, N, pcm_stride, logits_dev, kModeMfcc, &mp, &mfcc_smem)) return 0;
   FusedParams fp;
-  if (!fill_fused_params(h, h->d_ring, B, nframes, F, logits_dev, &fp)) return 0;
-  mp.ring_shift = fp.ring_shift = shift;
-  mp.prod_cnt = h->d_ring_cnt;
-  mp.cons_cnt = h->d_ring_cnt + h->ring_slots;
-  fp.prod_cnt = h->d_ring_cnt;
-  fp.cons_cnt = h->d_ring_cnt + h->ring_slots;
-  fp.prod_per_clip = 2u * (unsigned)mp.tiles_per_clip;   // two epilogue warps publish each tile
+  if (!fill_fused_params(h, nullptr, B, nframes, F, logits_dev, &fp)) return 0;
   if (F == 40) {
-    return is_i16 ? launch_t<short, 40, 24, 1>(h, mp, fp, mfcc_smem, stream)
-                  : launch_t<float, 40, 24, 1>(h, mp, fp, mfcc_smem, stream);
+    return is_i16 ? launch_t<short, 40, 24, 1>(h, mp, fp, mfcc_smem, chunk, stream)
+                  : launch_t<float, 40, 24, 1>(h, mp, fp, mfcc_smem, chunk, stream);
   }
   if (F == 10) {
-    const int rc = is_i16 ? launch_t<short, 10, 24, 2>(h, mp, fp, mfcc_smem, stream)
-                          : launch_t<float, 10, 24, 2>(h, mp, fp, mfcc_smem, stream);
+    const int rc = is_i16 ? launch_t<short, 10, 24, 2>(h, mp, fp, mfcc_smem, chunk, stream)
+                          : launch_t<float, 10, 24, 2>(h, mp, fp, mfcc_smem, chunk, stream);
     if (rc != 0) return rc;
-    return is_i16 ? launch_t<short, 10, 16, 1>(h, mp, fp, mfcc_smem, stream)
-                  : launch_t<float, 10, 16, 1>(h, mp, fp, mfcc_smem, stream);
+    return is_i16 ? launch_t<short, 10, 16, 1>(h, mp, fp, mfcc_smem, chunk, stream)
+                  : launch_t<float, 10, 16, 1>(h, mp, fp, mfcc_smem, chunk, stream);
   }
   return 0;
 }

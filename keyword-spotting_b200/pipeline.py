@@ -49,12 +49,13 @@ class KeywordSpotter:
             self.model._feature_cfg_owner = self
             self._bound_h = self._h
 
-    def configure_single_launch(self, min_clips: int = 8192, mfcc_share: float = 0.0) -> None:
-        """Batches of at least ``min_clips`` run as ONE kernel launch (MFCC CTAs feeding network CTAs through an
-        L2-resident feature ring, ``csrc/pcm_logits_fused.cu``); ``min_clips < 1`` always runs the two kernels back
-        to back.  ``mfcc_share``: share of the SMs given to the MFCC role (0 = default)."""
+    def configure_single_launch(self, min_clips: int = 1, chunk_clips: int = 0) -> None:
+        """PCM -> logits runs as ONE kernel launch (``csrc/pcm_logits_fused.cu``: every CTA alternates between the
+        MFCC of its next ``chunk_clips`` clips and the network on them, features in an L2-resident scratch) for
+        batches of at least ``min_clips``; ``min_clips < 1`` always runs the MFCC kernel and the network kernel back
+        to back.  ``chunk_clips = 0`` keeps the current chunk size (default 32)."""
         self._bind()
-        _native.check(_native.lib().kws_pcm_to_logits_configure(self._h.ptr, int(min_clips), float(mfcc_share)), ModelError)
+        _native.check(_native.lib().kws_pcm_to_logits_configure(self._h.ptr, int(min_clips), int(chunk_clips)), ModelError)
 
     def __call__(self, pcm: torch.Tensor) -> torch.Tensor:
         """``pcm[B, N]`` float32 (or int16 PCM, scaled by 1/32768 like ``librosa.load``) -> logits

@@ -1,8 +1,9 @@
 """PCM -> logits as ONE kernel launch (csrc/pcm_logits_fused.cu; north_star "the whole clip stays on-chip"):
-MFCC CTAs and network CTAs of one grid exchange features through an L2-resident ring.  The logits must equal the
-two-kernel path (MFCC kernel, then network kernel) bit for bit -- same arithmetic, different plumbing -- for every
-batch shape, for a ring that wraps many times (back-pressure), for both feature widths and both sample types, and
-match the float64 oracle within the north_star tolerance."""
+every CTA alternates between the MFCC of its next chunk of clips (features into its own L2-resident scratch) and the
+network on that chunk.  The logits must equal the two-kernel path (MFCC kernel, then network kernel) bit for bit --
+same arithmetic, different plumbing -- for every batch shape and chunk size (one clip per phase up to the whole
+range of a CTA), for both feature widths and both sample types, and match the float64 oracle within the north_star
+tolerance."""
 import os
 
 import numpy as np
@@ -25,52 +26,38 @@ def _spotter(numcep, nfilt, seed=0):
     return sd, KeywordSpotter(m.cuda(), AudioConfig(), numcep=numcep, nfilt=nfilt, device="cuda:0")
 
 
-@pytest.fixture
-def ring_env():
-    old = os.environ.get("KWS_RING_SLOTS")
-    yield
-    if old is None:
-        os.environ.pop("KWS_RING_SLOTS", None)
-    else:
-        os.environ["KWS_RING_SLOTS"] = old
-
-
 @pytest.mark.parametrize("numcep,nfilt", [(40, 40), (10, 26)])
 @pytest.mark.parametrize("B", [1, 2, 3, 5, 8, 149, 300, 1301])
-def test_single_launch_equals_two_kernels(numcep, nfilt, B, ring_env):
+def test_single_launch_equals_two_kernels(numcep, nfilt, B):
     sd, ks = _spotter(numcep, nfilt, seed=B)
     pcm = synth.parity_pcm(max(B, 8), seed=B)[:B].cuda()
     ks.configure_single_launch(min_clips=0)                  # two kernels back to back
     l0 = ks.model.launch_count()
     two = ks(pcm)
     assert ks.model.launch_count() - l0 == 2
-    for slots in ("1024", "8"):                              # a ring of 8 slots wraps B/8 times: back-pressure path
-        os.environ["KWS_RING_SLOTS"] = slots
-        ks.configure_single_launch(min_clips=1)
+    for chunk in (32, 1, 6, 4096):                           # many phase switches per CTA ... one chunk per CTA
+        ks.configure_single_launch(min_clips=1, chunk_clips=chunk)
         l0 = ks.model.launch_count()
         one = ks(pcm)
         assert ks.model.launch_count() - l0 == 1             # ONE kernel
-        assert torch.equal(one, two), (slots, (one - two).abs().max().item())
-    # and the ring must be reusable launch after launch (counters are reset per launch)
-    assert torch.equal(ks(pcm), two)
+        assert torch.equal(one, two), (chunk, (one - two).abs().max().item())
+    assert torch.equal(ks(pcm), two)                         # launch after launch on the same scratch
 
 
-def test_single_launch_int16_and_role_split(ring_env):
+def test_single_launch_int16():
     sd, ks = _spotter(40, 40, seed=3)
     g = torch.Generator().manual_seed(4)
     i16 = torch.randint(-32768, 32767, (2050, 16000), generator=g, dtype=torch.int16).cuda()
     ks.configure_single_launch(min_clips=0)
     two = ks(i16)
-    for share in (0.0, 0.05, 0.5, 0.9):                      # any split of the SMs gives the same logits
-        ks.configure_single_launch(min_clips=1, mfcc_share=share)
-        assert torch.equal(ks(i16), two), share
+    ks.configure_single_launch(min_clips=1, chunk_clips=32)
+    assert torch.equal(ks(i16), two)
     f32 = i16.float() / 32768.0
-    ks.configure_single_launch(min_clips=1)
     assert torch.equal(ks(f32), two)                         # x/32768 is exact: same bits as the float32 call
 
 
 def test_single_launch_against_oracle_default_threshold():
-    """Default configuration: an 8192-clip batch takes the single launch; parity set inside it vs the float64 oracle."""
+    """Default configuration (single launch at every batch size); parity set inside a big batch vs the float64 oracle."""
     sd, ks = _spotter(40, 40, seed=5)
     pcm = synth.uniform_pcm(8192, seed=6)
     pcm[:8] = synth.parity_pcm(8)

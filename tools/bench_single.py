@@ -34,20 +34,20 @@ def timed(fn, reps=5):
     return e0.elapsed_time(e1) / reps
 
 
-for numcep, nfilt, shares in ((40, 40, (0.0, 0.12, 0.14, 0.16, 0.18, 0.20, 0.22)), (10, 26, (0.0, 0.22, 0.26, 0.30, 0.34))):
+for numcep, nfilt in ((40, 40), (10, 26)):
     ks = KeywordSpotter(m, AudioConfig(), numcep=numcep, nfilt=nfilt, device="cuda:0")
     ks.configure_single_launch(min_clips=0)
     ms = timed(lambda: ks(pcm))
     print(f"F={numcep} B={B} two kernels: {ms:.3f} ms {B / ms / 1e3:.3f} M clips/s")
-    for sh in shares:
-        ks.configure_single_launch(min_clips=1, mfcc_share=sh)
+    for chunk in (8, 16, 32, 64, 128):
+        ks.configure_single_launch(min_clips=1, chunk_clips=chunk)
         ms = timed(lambda: ks(pcm))
-        print(f"F={numcep} B={B} single launch share={sh:.2f}: {ms:.3f} ms {B / ms / 1e3:.3f} M clips/s")
-for Bs in (256, 1024, 4096):
+        print(f"F={numcep} B={B} single launch chunk={chunk}: {ms:.3f} ms {B / ms / 1e3:.3f} M clips/s")
+for Bs in (256, 1024, 4096, 16384):
     ks = KeywordSpotter(m, AudioConfig(), numcep=40, nfilt=40, device="cuda:0")
     x = pcm[:Bs]
     ks.configure_single_launch(min_clips=0)
     a = timed(lambda: ks(x), 30)
-    ks.configure_single_launch(min_clips=1)
+    ks.configure_single_launch(min_clips=1, chunk_clips=32)
     b = timed(lambda: ks(x), 30)
     print(f"B={Bs}: two kernels {a * 1e3:.1f} us, single launch {b * 1e3:.1f} us")

@@ -1,0 +1,25 @@
+"""Timing of the single-launch kernel (optionally with one phase skipped via KWS_PHASE_SKIP): time_single.py [B] [chunk]"""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import kws_b200  # noqa: F401
+from kws_b200.audio_processor import AudioConfig
+from kws_b200.models import DepthwiseSeparableConv
+from kws_b200.pipeline import KeywordSpotter
+B = int(sys.argv[1]) if len(sys.argv) > 1 else 65536
+torch.manual_seed(0)
+m = DepthwiseSeparableConv().cuda()
+ks = KeywordSpotter(m, AudioConfig(), numcep=40, nfilt=40, device="cuda:0")
+ks.configure_single_launch(min_clips=1, chunk_clips=int(sys.argv[2]) if len(sys.argv) > 2 else 32)
+pcm = torch.rand(B, 16000, device="cuda") * 2 - 1
+for _ in range(2):
+    ks(pcm)
+torch.cuda.synchronize()
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+e0.record()
+for _ in range(5):
+    ks(pcm)
+e1.record()
+torch.cuda.synchronize()
+ms = e0.elapsed_time(e1) / 5
+print(f"skip={os.environ.get('KWS_PHASE_SKIP', '0')} B={B}: {ms:.3f} ms  {B / ms / 1e3:.3f} M clips/s")
