@@ -217,8 +217,11 @@ __device__ __forceinline__ void mfcc512_ws_body(const FastParams& p, unsigned ch
       const uint32_t bar = bar_full + 8u * (it & 1);
       T* raw = reinterpret_cast<T*>(smem + (size_t)(it & 1) * p.raw_stride);
       mbar_expect_tx(bar, bytes);
-      tma_load_1d(smem_u32(raw + (s0 >= kLead ? 0 : kLead)),
-                  reinterpret_cast<const T*>(p.pcm) + (size_t)(clip0 + clip) * p.stride + first, bytes, bar);
+      const T* src = reinterpret_cast<const T*>(p.pcm) + (size_t)(clip0 + clip) * p.stride + first;
+      if (CHUNK)  // the PCM streams through L2 once: it must not push the CTAs' feature scratch out (evict_first)
+        tma_load_1d_hint(smem_u32(raw + (s0 >= kLead ? 0 : kLead)), src, bytes, bar, l2_policy_evict_first());
+      else
+        tma_load_1d(smem_u32(raw + (s0 >= kLead ? 0 : kLead)), src, bytes, bar);
     };
     auto issue_mma = [&]() {  // converged warp, elected lane: D[128 x 48] = Ahi*Bhi + Alo*Bhi + Ahi*Blo over Kpad
       tc_fence_after();
@@ -277,6 +280,7 @@ __device__ __forceinline__ void mfcc512_ws_body(const FastParams& p, unsigned ch
         tc_fence_before();
         const int row = warp * 32 + lane;
         const int f = t * kTileFrames + row;
+        const uint64_t pol_keep = CHUNK ? l2_policy_evict_last() : 0ull;
 
         // c0 of this tile is read BEFORE warp 1 releases the accumulator: its release lets the next tile's MMAs
         // go, and their completion lets the compute warps overwrite this half of s_c0 two tiles on
@@ -291,7 +295,11 @@ __device__ __forceinline__ void mfcc512_ws_body(const FastParams& p, unsigned ch
           if ((p.ncep & 3) == 0) {
 #pragma unroll
             for (int c = 0; c < kDctN; c += 4)
-              if (c < p.ncep) *reinterpret_cast<float4*>(o + c) = make_float4(v[c], v[c + 1], v[c + 2], v[c + 3]);
+              if (c < p.ncep) {
+                const float4 q4 = make_float4(v[c], v[c + 1], v[c + 2], v[c + 3]);
+                if (CHUNK) st_global_v4_hint(o + c, q4, pol_keep);  // scratch: stays in L2 until the network phase reads it
+                else *reinterpret_cast<float4*>(o + c) = q4;
+              }
           } else {
 #pragma unroll
             for (int c = 0; c < kDctN; ++c)
