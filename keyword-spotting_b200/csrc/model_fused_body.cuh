@@ -177,6 +177,16 @@ constexpr int kCThreads = kFCWarps * 32;
 constexpr int kFThreads = (kFCWarps + 2) * 32;     // + one MMA-issue warp per clip slot
 template <>
 __device__ __forceinline__ void fused_sync<false>() { __syncthreads(); }
+// Phase barriers of the row loop (ids 5 = end of phase A, 6 = end of phase B).  Only the MMA-issue warps WAIT for a
+// phase to be complete (they may not issue a GEMM before every stencil has stored its B-tile rows); the compute warps
+// just ARRIVE and walk on into the next phase, whose first action is the mbarrier wait for the GEMMs that phase
+// depends on.  That wait bounds the skew between compute warps to less than one step (the GEMMs of step t + 1 are
+// issued only after every warp has arrived at the same barrier of step t), which is what the one-step delays of the
+// feature refill and of pool_fc below are sized for.
+template <int ID>
+__device__ __forceinline__ void phase_arrive() { asm volatile("bar.arrive %0, %1;" ::"n"(ID), "n"(kFThreads) : "memory"); }
+template <int ID>
+__device__ __forceinline__ void phase_sync() { asm volatile("bar.sync %0, %1;" ::"n"(ID), "n"(kFThreads) : "memory"); }
 template <>
 __device__ __forceinline__ void fused_sync<true>() { asm volatile("bar.sync 1, %0;" ::"n"(kFThreads) : "memory"); }
 constexpr int kRingCols = 64;                     // per layer: 2 row slots x (8 margin + 24) columns
@@ -277,7 +287,7 @@ __device__ __forceinline__ void fused_mma_warp(unsigned char* smem, uint32_t tme
   fused_sync<CHUNK>();  // features of the first pair loaded
   int tl = 0, n = 0;
   for (int tg = 0; tg < total; ++tg) {
-    fused_sync<CHUNK>();  // phase A written
+    phase_sync<5>();  // phase A written
     tc_fence_after();
     {
       StageRow r = stage_row(tl, n, my_pairs, per, 3, H0);
@@ -286,7 +296,7 @@ __device__ __forceinline__ void fused_mma_warp(unsigned char* smem, uint32_t tme
       if (r.on) issue_gemm<kKCp / 8>(d0 + 3 * kRingCols + (r.i & 1) * 32, ap[2], bp[2], kIdescF);
       tc_commit_elect(barO);
     }
-    fused_sync<CHUNK>();  // phase B written
+    phase_sync<6>();  // phase B written
     tc_fence_after();
     {
       StageRow r = stage_row(tl, n, my_pairs, per, 0, H0);
@@ -552,11 +562,13 @@ __device__ __forceinline__ void dscnn_fused_body(const FusedParams& p, unsigned 
       for (int x = 0; x < 4; ++x) P[l][x] = R[l][x] = fsplat(0.f);
     fused_sync<CHUNK>();
 
-    int tl = 0, n = 0, fc_n = -1;  // fc_n: group (CTA-local index) whose pooled sums wait in s_pool
+    int tl = 0, n = 0, fc_n = -1, fc_run = -1;  // fc_n / fc_run: group (CTA-local index) whose pooled sums wait in s_pool
     for (int tg = 0; tg < total; ++tg) {
       // ================= phase A: depthwise of blocks 1 and 3 =================
       float fl_v = 0.f;
-      const int fl_fr = 2 * tl - 4 + fl_r;
+      // rows conv1 left behind TWO steps ago: a compute warp may be up to one step ahead of the slowest one, whose
+      // im2col of the previous step still reads the two rows a one-step distance would overwrite
+      const int fl_fr = 2 * tl - 6 + fl_r;
       const bool fl_do = fl_on && n + 1 < my_pairs && fl_fr >= 0 && fl_fr < T;
       if (fl_do) {
         const long long clip = CL * ((long long)bid + (long long)(n + 1) * nblk) + fl_s;
@@ -583,14 +595,18 @@ __device__ __forceinline__ void dscnn_fused_body(const FusedParams& p, unsigned 
           dw_seg<W0 + 4, 1, PACK>(my_ld + (e3 & 0x1ffu), j, (e3 & kSchSt) != 0u, my_par + 2u * 48u * kFC,
                                   my_dst + (uint32_t)(2 * 2 * L::bp_stride), P[2], R[2]);
       }
+      if (fc_run >= 0) {  // pooled sums handed over two phase-A's ago: every warp's partial is in s_pool by now
+        pool_fc((long long)bid + (long long)fc_run * nblk);
+        fc_run = -1;
+      }
       if (fc_n >= 0) {
-        pool_fc((long long)bid + (long long)fc_n * nblk);
+        fc_run = fc_n;
         fc_n = -1;
       }
       if (fl_do) s_feat[fl_s * feat_stride + (fl_fr + 2) * FP + fl_c + 2] = to_tf32(fl_v);
       fence_proxy_async();
       tc_fence_before();
-      fused_sync<CHUNK>();
+      phase_arrive<5>();
       // ================= phase B: conv1 im2col, depthwise of blocks 2 and 4, pooling =================
       if (tg > 0) {  // the GEMMs issued after the previous phase B (conv1, pw2, pw4) have retired
         mbar_wait(barE, nE & 1);
@@ -654,7 +670,7 @@ __device__ __forceinline__ void dscnn_fused_body(const FusedParams& p, unsigned 
       }
       fence_proxy_async();
       tc_fence_before();
-      fused_sync<CHUNK>();
+      phase_arrive<6>();
       if (++tl == per) {
         tl = 0;
         ++n;
@@ -664,6 +680,8 @@ __device__ __forceinline__ void dscnn_fused_body(const FusedParams& p, unsigned 
     mbar_wait(barO, nO & 1);
     mbar_wait(barE, nE & 1);
     tc_fence_after();
+    asm volatile("bar.sync 2, %0;" ::"n"(kCThreads) : "memory");  // compute warps: every pooling partial is written
+    if (fc_run >= 0) pool_fc((long long)bid + (long long)fc_run * nblk);
     if (fc_n >= 0) pool_fc((long long)bid + (long long)fc_n * nblk);
   }
   tc_fence_before();
