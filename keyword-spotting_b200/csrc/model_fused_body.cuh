@@ -131,6 +131,8 @@ __device__ __forceinline__ void sts32(uint32_t a, uint32_t v) {  // a = base + c
   asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory");
 }
 
+__device__ __forceinline__ V relu2x(V a) { return __fadd2_rn(a, make_float2(fabsf(a.x), fabsf(a.y))); }
+
 template <int W, int SHIFT, int PACK>
 __device__ __forceinline__ void dw_seg(uint32_t taddr, int j, bool st, uint32_t par, uint32_t dst, V (&P)[4], V (&R)[4]) {
   const float4 w0 = lds128(par), w1 = lds128(par + 16u);
@@ -141,15 +143,14 @@ __device__ __forceinline__ void dw_seg(uint32_t taddr, int j, bool st, uint32_t 
   tc_ld16(taddr, ra);
   tc_ld8(taddr + 1u, rb);
   tc_wait_ld();
-#pragma unroll
-  for (int k = 0; k < 10; ++k) asm("max.f32 %0, %0, 0f00000000;" : "+f"(ra[k]));
-#pragma unroll
-  for (int k = 0; k < 8; ++k) asm("max.f32 %0, %0, 0f00000000;" : "+f"(rb[k]));
+  // ReLU of a PAIR in one packed instruction: x + |x| = 2 max(x, 0) exactly (FADD2 takes |.| as an operand modifier);
+  // the factor 2 is taken out of the depthwise taps, which are stored halved (a power of two: same bits as
+  // max(x, 0) * w).  Nine FADD2 on the FMA pipe instead of eighteen FMNMX on the ALU pipe per call.
   V E[5], O[4];
 #pragma unroll
-  for (int pp = 0; pp < 5; ++pp) E[pp] = make_float2(ra[2 * pp], ra[2 * pp + 1]);
+  for (int pp = 0; pp < 5; ++pp) E[pp] = relu2x(make_float2(ra[2 * pp], ra[2 * pp + 1]));
 #pragma unroll
-  for (int pp = 0; pp < 4; ++pp) O[pp] = make_float2(rb[2 * pp], rb[2 * pp + 1]);
+  for (int pp = 0; pp < 4; ++pp) O[pp] = relu2x(make_float2(rb[2 * pp], rb[2 * pp + 1]));
   // warp-uniform store predicates.  PACK = 1: pixels x < KL of the last valid segment JL, all pixels of the
   // segments before it; PACK = 2: per segment, from the compile-time validity of its eight columns
   constexpr int JL = (W - 1) / 8, KL = W - 8 * JL;
@@ -398,7 +399,7 @@ __device__ __forceinline__ void dscnn_fused_body(const FusedParams& p, unsigned 
   fused_sync<CHUNK>();
   for (int i = tid; i < 4 * kFC * 12; i += kFThreads) {
     const int l = i / (12 * kFC), ch = (i / 12) % kFC, k = i % 12;
-    s_par[i] = k < 9 ? p.dw_w[(l * 9 + k) * kFC + ch] : 0.f;
+    s_par[i] = k < 9 ? 0.5f * p.dw_w[(l * 9 + k) * kFC + ch] : 0.f;   // halved: the stencil's ReLU yields 2 max(x, 0)
   }
   uint2* s_sched = reinterpret_cast<uint2*>(smem + L::off_sched(T));
   for (int tl = tid; tl < H0 + 7; tl += kFThreads) {
