@@ -80,3 +80,20 @@ def test_single_launch_sliding_windows():
     ks.configure_single_launch(min_clips=1)
     one = ks.sliding_logits(rec, hop_samples=160)
     assert one.shape == (1200, 12) and torch.equal(one, two)
+
+
+def test_repeatable_bits_large_batch():
+    """The network kernel's compute warps run up to one row step apart (they only ARRIVE at the phase barriers) and
+    the single launch alternates phases on shared buffers: a race there would show up as run-to-run differences.
+    Twelve runs of a 20 000-clip batch, both paths, must give identical bits, equal to the two-kernel result."""
+    sd, ks = _spotter(40, 40, seed=9)
+    pcm = synth.uniform_pcm(20000, seed=10).cuda()
+    ks.configure_single_launch(min_clips=0)
+    ref = ks(pcm).clone()
+    feats = None
+    for rep in range(6):
+        assert torch.equal(ks(pcm), ref), ("two kernels", rep)
+    ks.configure_single_launch(min_clips=1, chunk_clips=32)
+    for rep in range(6):
+        assert torch.equal(ks(pcm), ref), ("single launch", rep)
+    del feats
