@@ -212,6 +212,18 @@ int kws_pcm_to_logits(kws_handle_t h, const float* pcm_dev, int64_t B, int64_t N
 /* min_clips: smallest batch that takes the single launch (default 1; < 1 disables it: always two kernels);
  * chunk_clips: clips per CTA and phase (default 32; 0 keeps the current value) */
 int kws_pcm_to_logits_configure(kws_handle_t h, int64_t min_clips, int chunk_clips);
+/* The same single-launch PCM -> logits call for callers that cannot allocate (CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  It has NO counterpart in the reference.
+ * It calls no cudaMalloc / cudaFree: the kernel's feature scratch is a 10 MiB static __device__ array that
+ * every GPU loading the library holds until the process exits, cut into one slice per SM.  Limits: the single-launch
+ * configurations only (reference network, 10 or 40 coefficients, aligned float32 PCM), and a clip's feature map must
+ * fit a slice at least twice (four times at 10 coefficients): nframes * ncep * 4 bytes * 2 (or 4) * SM count <= 10 MiB,
+ * i.e. up to 221 frames of 40 coefficients (2.2 s of audio) or 442 frames of 10 on a 148-SM B200; larger clips return
+ * KWS_ERR_INVALID with a message, and the batch size B is not limited.  Handle set-up (kws_features_configure, kws_model_finalize) still allocates and must
+ * happen before.  All calls share the array: calls that overlap on the GPU (streams, handles, threads) race --
+ * serialise them.  Logits are bit-identical to kws_pcm_to_logits. */
+int kws_pcm_to_logits_static(kws_handle_t h, const float* pcm_dev, int64_t B, int64_t N, int64_t pcm_stride,
+                             float* logits_dev, void* stream);
 int kws_pcm_to_logits_host(kws_handle_t h, const float* pcm_host, int64_t B, int64_t N,
                            float* logits_host);
 /* the same two calls fed 16-bit PCM (x/32768 = librosa.load, audio_processor.py:145, happens inside the

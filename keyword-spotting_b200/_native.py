@@ -87,6 +87,7 @@ SIGNATURES = {
     "kws_model_workspace_bytes": (_i64, [_vp, _i64, _i64, _i64]),
     "kws_pcm_to_logits_configure": (_i32, [_vp, _i64, _i32]),
     "kws_pcm_to_logits": (_i32, [_vp, _vp, _i64, _i64, _i64, _vp, _vp]),
+    "kws_pcm_to_logits_static": (_i32, [_vp, _vp, _i64, _i64, _i64, _vp, _vp]),
     "kws_pcm_to_logits_host": (_i32, [_vp, _vp, _i64, _i64, _vp]),
     "kws_pcm_to_logits_i16": (_i32, [_vp, _vp, _i64, _i64, _i64, _vp, _vp]),
     "kws_pcm_to_logits_host_i16": (_i32, [_vp, _vp, _i64, _i64, _vp]),

@@ -141,3 +141,104 @@ int launch_pcm_logits_fused(kws_handle_t h, const void* pcm_dev, bool is_i16, in
 }
 
 }  // namespace kws
+
+// ---------------------------------------------------------------------------------------------------------------
+// kws_pcm_to_logits_static: the same single-launch kernel with its feature scratch in a file-scope device array
+// instead of a cudaMalloc'ed buffer -- for callers that cannot allocate (CUDA graph capture, tight serving loops,
+// harnesses that forbid cudaMalloc).  No counterpart in the reference.
+//
+// The array is kStaticScratchBytes (10 MiB) on every GPU that loads the library, held until the process exits.  It is
+// cut into one slice per CTA; a CTA's chunk is as many clips as its slice holds (at 99 x 40 features on 148 SMs: 4
+// clips per CTA and phase instead of 32, ~3 % slower).  Clips whose feature map does not fit even one group of clips
+// per CTA are rejected with KWS_ERR_INVALID.  Nothing in the scratch has to start at zero: the MFCC phase writes every
+// feature value of a chunk before the network phase reads it.  Every call shares the array, so calls that overlap on
+// the GPU (two streams, two handles, two host threads on one device) race; serialise them.
+namespace kws {
+
+constexpr size_t kStaticScratchBytes = 10u << 20;
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+constexpr int kStaticMaxDevices = 64;
+
+// In host code `g_static_scratch` is only a host-side stand-in for the symbol: the device address comes from
+// cudaGetSymbolAddress, once per device, with that device current.
+static int static_scratch_ptr(int device, float** out) {
+  static float* ptrs[kStaticMaxDevices] = {};
+  if (device < 0 || device >= kStaticMaxDevices) return fail(KWS_ERR_INVALID, "device %d out of range", device);
+  if (!ptrs[device]) {
+    void* p = nullptr;
+    KWS_CUDA(cudaGetSymbolAddress(&p, g_static_scratch));
+    if (!p) return fail(KWS_ERR_CUDA, "cudaGetSymbolAddress returned a null address for the static scratch");
+    ptrs[device] = static_cast<float*>(p);
+  }
+  *out = ptrs[device];
+  return KWS_OK;
+}
+
+template <typename T, int F, int NPIX, int PACK>
+static int launch_static_t(kws_handle_t h, FastParams& mp, FusedParams& fp, size_t mfcc_smem, float* scratch,
+                           cudaStream_t stream) {
+  using L = FusedLayout<F, NPIX, PACK>;
+  // clips per CTA slice: a multiple of the network's group size, at most the default chunk
+  const size_t clip_bytes = (size_t)fp.T * F * sizeof(float);
+  long long chunk = (long long)(kStaticScratchBytes / ((size_t)h->sm_count * clip_bytes));
+  chunk = chunk / L::CL * L::CL;
+  if (chunk > 32) chunk = 32;
+  if (chunk < L::CL)
+    return fail(KWS_ERR_INVALID,
+                "kws_pcm_to_logits_static: %d frames x %d coefficients need %zu bytes of scratch for %d clips on each of "
+                "%d SMs, the static scratch holds %zu bytes; use kws_pcm_to_logits",
+                fp.T, F, (size_t)L::CL * clip_bytes, L::CL, h->sm_count, kStaticScratchBytes);
+  const size_t model_smem = L::smem_bytes(fp.T);
+  if (model_smem > 227 * 1024) return 0;
+  const size_t smem_bytes = mfcc_smem > model_smem ? mfcc_smem : model_smem;
+  const long long ngroups = (fp.B + L::CL - 1) / L::CL;
+  if (ngroups > 0x7fffffffLL / 64) return 0;
+  long long grid = h->sm_count;
+  if (grid > ngroups) grid = ngroups;
+  auto kern = pcm_logits_fused_kernel<T, F, NPIX, PACK>;
+  if (int rc = ensure_dyn_smem(kern, smem_bytes, true)) return rc;
+  kern<<<(unsigned)grid, kPipeThreads, smem_bytes, stream>>>(mp, fp, scratch, (int)chunk, 0);
+  KWS_CHECK_LAUNCH(h);
+  return 1;
+}
+
+}  // namespace kws
+
+extern "C" int kws_pcm_to_logits_static(kws_handle_t h, const float* pcm_dev, int64_t B, int64_t N, int64_t pcm_stride,
+                                        float* logits_dev, void* stream) {
+  using namespace kws;
+  if (!h) return fail(KWS_ERR_INVALID, "null handle");
+  if (!h->feat.ready) return fail(KWS_ERR_STATE, "features not configured");
+  if (!h->model.finalized) return fail(KWS_ERR_STATE, "model weights not finalized");
+  if (B < 0 || N < 1 || pcm_stride < 1) return fail(KWS_ERR_INVALID, "bad B/N/stride");
+  if (B == 0) return KWS_OK;
+  if (!pcm_dev || !logits_dev) return fail(KWS_ERR_INVALID, "null device pointer");
+  KWS_CUDA(cudaSetDevice(h->device));
+  float* scratch = nullptr;
+  if (int rc = static_scratch_ptr(h->device, &scratch)) return rc;
+  const FeatureTables& t = h->feat;
+  const int64_t nframes = kws_num_frames(N, t.cfg.frame_len, t.cfg.frame_step);
+  const int F = t.ncep;
+  FastParams mp;
+  size_t mfcc_smem = 0;
+  FusedParams fp;
+  int rc = 0;
+  if (h->model.path == 0 && (F == 40 || F == 10) &&
+      fill_fast_params(h, pcm_dev, false, B, N, pcm_stride, logits_dev, kModeMfcc, &mp, &mfcc_smem) &&
+      fill_fused_params(h, nullptr, B, nframes, F, logits_dev, &fp)) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (F == 40) {
+      rc = launch_static_t<float, 40, 24, 1>(h, mp, fp, mfcc_smem, scratch, st);
+    } else {
+      rc = launch_static_t<float, 10, 24, 2>(h, mp, fp, mfcc_smem, scratch, st);
+      if (rc == 0) rc = launch_static_t<float, 10, 16, 1>(h, mp, fp, mfcc_smem, scratch, st);
+    }
+  }
+  if (rc < 0) return rc;
+  if (rc == 0)
+    return fail(KWS_ERR_INVALID,
+                "kws_pcm_to_logits_static covers the single-launch configurations only (reference network 64 ch / 4 blocks, "
+                "10 or 40 coefficients, 400-sample frames, rectangular window, 16-byte aligned float32 PCM); use "
+                "kws_pcm_to_logits");
+  return KWS_OK;
+}
