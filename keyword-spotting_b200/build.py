@@ -12,7 +12,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libkws_b200.so")
-SOURCES = ["tables.cu", "mfcc.cu", "mfcc_ws.cu", "sigproc.cu", "model.cu", "model_fused.cu", "pcm_logits_fused.cu", "model_gemm.cu", "train.cu", "crnn.cu", "augment.cu", "streaming.cu", "probe.cu", "capi.cu"]
+SOURCES = ["tables.cu", "mfcc.cu", "mfcc_ws.cu", "sigproc.cu", "model.cu", "model_fused.cu", "pcm_logits_fused.cu", "model_gemm.cu", "train.cu", "train_tc.cu", "crnn.cu", "augment.cu", "streaming.cu", "probe.cu", "capi.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
     "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr",

@@ -167,6 +167,9 @@ int launch_pcm_logits_fused(kws_handle_t h, const void* pcm_dev, bool is_i16, in
 // model.cu: layered forward that keeps every activation (training), logits/pooled into the workspace
 int train_forward_layers(kws_handle_t h, const float* feats_dev, int64_t B, int T, int F, TrainWorkspace& w,
                          cudaStream_t st);
+// train_tc.cu: pointwise + ReLU backward of one 64-channel block on the tensor core (1 = launched, <0 = error)
+int launch_pw_bwd_tc(kws_handle_t h, const float* out, const float* dout, const float* dpooled, float inv_area, float* d_io,
+                     const float* w_flat, float* g_w, float* g_b, long long B, int H, int W, cudaStream_t st);
 // model.cu: conv 10x10 s2 p2 (one input channel) + ReLU, NHWC output [B, H1, W1, C]
 int launch_conv1_relu(kws_handle_t h, const float* in, float* out, const float* w_packed, const float* bias, int64_t B,
                       int T, int F, int H1, int W1, int C, cudaStream_t st);

@@ -17,6 +17,7 @@
 // then conv1_bwd_kernel (im2col outer products) and ce_fc_bwd_kernel (softmax, mean CE, fc grads,
 // gradient of the average pool).  Reductions use per-CTA register/shared partials and one atomicAdd
 // per partial, so results are deterministic only up to fp32 summation order.
+#include <cstdlib>
 #include <cstring>
 
 #include "mfcc_dev.cuh"
@@ -465,16 +466,28 @@ int kws_train_forward_backward(kws_handle_t h, const float* params_dev, const fl
   }
   const size_t pw_smem = kPwSmem;
   if (int rc_ = ensure_dyn_smem(pw_bwd_kernel, (size_t)pw_smem)) return rc_;
+  // KWS_TRAIN_TC=0 selects the CUDA-core pointwise backward (A/B and fallback for debugging); default: tensor core
+  static const bool use_tc = [] {
+    const char* e = std::getenv("KWS_TRAIN_TC");
+    return !(e && e[0] == '0');
+  }();
   const float* dout = nullptr;
   for (int l = nb - 1; l >= 0; --l) {
     const int H = H1 + 2 * l, W = W1 + 2 * l;  // block input size; output is (H+2) x (W+2)
     const long long ntiles = (B * (long long)(H + 2) * (W + 2) + kPwTP - 1) / kPwTP;
     long long g = ntiles < h->sm_count * 3LL ? ntiles : h->sm_count * 3LL;
     const bool last = (l == nb - 1);
-    pw_bwd_kernel<<<(unsigned)g, 256, pw_smem, st>>>(w.L[l + 1], dout, last ? w.dpooled : nullptr,
-                                                     1.0f / (float)((H + 2) * (W + 2)), w.D[l], params_dev + fl.pww(l),
-                                                     grads_dev + fl.pww(l), grads_dev + fl.pwb(l), B, H, W);
-    KWS_CHECK_LAUNCH(h);
+    if (use_tc) {  // tensor-core twin (train_tc.cu)
+      const int rc_tc = launch_pw_bwd_tc(h, w.L[l + 1], dout, last ? w.dpooled : nullptr, 1.0f / (float)((H + 2) * (W + 2)),
+                                         w.D[l], params_dev + fl.pww(l), grads_dev + fl.pww(l), grads_dev + fl.pwb(l), B, H, W,
+                                         st);
+      if (rc_tc < 0) return rc_tc;
+    } else {
+      pw_bwd_kernel<<<(unsigned)g, 256, pw_smem, st>>>(w.L[l + 1], dout, last ? w.dpooled : nullptr,
+                                                       1.0f / (float)((H + 2) * (W + 2)), w.D[l], params_dev + fl.pww(l),
+                                                       grads_dev + fl.pww(l), grads_dev + fl.pwb(l), B, H, W);
+      KWS_CHECK_LAUNCH(h);
+    }
     float* dx = w.dX[l & 1];
     const long long npix = B * (long long)H * W;
     long long g2 = (npix + 15) / 16;

@@ -1,0 +1,217 @@
+// Pointwise (1x1, padding=1) + ReLU backward of one block on the tensor core (tcgen05, kind::tf32 with the 3-term
+// hi/lo split = fp32-grade): the tensor-core twin of pw_bwd_kernel in train.cu (reference step body
+// kws/libs/training.py:285-297; layer kws/libs/models.py:104-119).
+//
+//   dY[px][co] = dOut[px][co] * (out[px][co] > 0)                  over the padded (H+2) x (W+2) output grid
+//   dD[px][ci] = sum_co dY[px][co] W[co][ci]                       dgrad, written for interior pixels only
+//   dW[co][ci] = sum_px dY[px][co] D[px][ci],  db[co] = sum_px dY  wgrad + bias gradient (D = 0 on the border)
+//
+// Tile = 64 consecutive pixels of the padded grid.  Both GEMMs are M = 64:
+//   dgrad  D1[px, ci]  = A1[px, K = co] . B1[ci, K = co]^T     A1 = dY (K-major as it lies in NHWC), B1 = W^T, built once
+//   wgrad  D2[co, ci+] = A2[co, K = px] . B2[ci+, K = px]^T    A2 = dY^T, B2 = D^T with an extra all-ones row (n = 64)
+//                                                             whose column of D2 is the bias gradient
+// kind::tf32 returns zeros for MN-major operands (tools/umma_probe_mn*.cu), so the K = px operands are staged
+// TRANSPOSED by the CUDA cores: thread = (16 pixels x 2 channel quads per warp), which makes both the K-major
+// 16-byte stores of A1 and the transposed 4-byte stores of A2 / B2 bank-conflict free with the 144-byte K-chunk pitch.
+// Every operand is split hi = rna_tf32(x), lo = rna_tf32(x - hi) and each GEMM is Ahi.Bhi + Alo.Bhi + Ahi.Blo.
+// The wgrad accumulator stays in tensor memory across all tiles of the CTA and is added to the global gradient once.
+#include "mfcc_dev.cuh"
+
+namespace kws {
+
+constexpr int kPC = 64;                        // channels
+constexpr int kPTile = 64;                     // pixels per tile
+constexpr int kPThreads = 512;
+constexpr int kPLbo = 144;                     // K-chunk pitch (16-byte chunks of 8 rows = 128 B, padded)
+constexpr int kPSbo = (64 / 4) * kPLbo;        // 8-row group pitch for K = 64
+constexpr int kPOp = 8 * kPSbo;                // one 64-row operand image (hi or lo): 18 432 B
+constexpr int kPOpB2 = 9 * kPSbo;              // B2: 72 rows (64 ci + ones row + 7 zero rows)
+constexpr int kPOffA1 = 0, kPOffB1 = 2 * kPOp, kPOffA2 = 4 * kPOp, kPOffB2 = 6 * kPOp;
+constexpr size_t kPSmem = 6 * (size_t)kPOp + 2 * (size_t)kPOpB2;
+constexpr int kPN2 = 72;
+constexpr uint32_t kPIdesc1 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(64 >> 3) << 17) | ((64u >> 4) << 24);
+constexpr uint32_t kPIdesc2 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(kPN2 >> 3) << 17) | ((64u >> 4) << 24);
+
+__device__ __forceinline__ uint32_t kmaj_off(int row, int k) {  // byte offset of element (row, k) in a K-major image
+  return (uint32_t)((row >> 3) * kPSbo + (k >> 2) * kPLbo + (row & 7) * 16 + (k & 3) * 4);
+}
+__device__ __forceinline__ void split_tf32(float x, float& hi, float& lo) {
+  hi = to_tf32(x);
+  lo = to_tf32(x - hi);
+}
+
+__global__ void __launch_bounds__(kPThreads, 1)
+pw_bwd_tc_kernel(const float* __restrict__ out, const float* __restrict__ dout, const float* __restrict__ dpooled,
+                 float inv_area, float* __restrict__ d_io, const float* __restrict__ w_flat /*[co][ci]*/,
+                 float* __restrict__ g_w, float* __restrict__ g_b, long long B, int H, int W) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  __shared__ __align__(8) unsigned long long s_bar;
+  __shared__ uint32_t s_tmem;
+  const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
+  const uint32_t bar = smem_u32(&s_bar);
+  const int Ho = H + 2, Wo = W + 2;
+  const long long npix = B * Ho * (long long)Wo, ntiles = (npix + kPTile - 1) / kPTile;
+  if (tid == 0) {
+    mbar_init(bar, 1);
+    fence_mbar_init();
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "n"(256));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  // B1 = W^T (rows ci, K = co), hi and lo; B2's constant rows: ones (n = 64) and zeros (n = 65..71)
+  for (int i = tid; i < kPC * kPC; i += kPThreads) {
+    const int co = i >> 6, ci = i & 63;
+    float hi, lo;
+    split_tf32(w_flat[i], hi, lo);
+    *reinterpret_cast<float*>(smem + kPOffB1 + kmaj_off(ci, co)) = hi;
+    *reinterpret_cast<float*>(smem + kPOffB1 + kPOp + kmaj_off(ci, co)) = lo;
+  }
+  for (int i = tid; i < 8 * kPTile; i += kPThreads) {
+    const int n = 64 + (i >> 6), k = i & 63;
+    *reinterpret_cast<float*>(smem + kPOffB2 + kmaj_off(n, k)) = (n == 64) ? 1.0f : 0.0f;
+    *reinterpret_cast<float*>(smem + kPOffB2 + kPOpB2 + kmaj_off(n, k)) = 0.0f;
+  }
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = s_tmem;
+  const uint32_t sbase = smem_u32(smem);
+
+  // staging item of this thread: 16 pixels x 2 channel quads per warp (see the header), two items per tile
+  const int pxl = lane & 15, q = 2 * (warp & 7) + (lane >> 4), pxb = (warp >> 3) * 16 + pxl;  // + 32 for the second item
+  uint32_t parity = 0;
+  bool first = true;
+  // The global loads of tile i + 1 are issued right after the MMAs of tile i and land in registers while those MMAs
+  // and the epilogue run (one CTA per SM: nothing else would hide the L2 / HBM latency): dy = masked upstream
+  // gradient, dv = saved depthwise output, per item.
+  float4 dy[2], dv[2];
+  auto load_tile = [&](long long tile) {
+#pragma unroll
+    for (int it = 0; it < 2; ++it) {
+      const long long gp = tile * kPTile + pxb + 32 * it;
+      dy[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+      dv[it] = dy[it];
+      if (gp < npix) {
+        int wo, ho;
+        long long b;
+        split_pixel(gp, Wo, Ho, &b, &ho, &wo);
+        const float4 o = reinterpret_cast<const float4*>(out + gp * kPC)[q];
+        float4 g;
+        if (dpooled) {
+          g = reinterpret_cast<const float4*>(dpooled + b * kPC)[q];
+          g.x *= inv_area; g.y *= inv_area; g.z *= inv_area; g.w *= inv_area;
+        } else {
+          g = reinterpret_cast<const float4*>(dout + gp * kPC)[q];
+        }
+        dy[it] = make_float4(o.x > 0.f ? g.x : 0.f, o.y > 0.f ? g.y : 0.f, o.z > 0.f ? g.z : 0.f, o.w > 0.f ? g.w : 0.f);
+        if (ho >= 1 && ho <= H && wo >= 1 && wo <= W)
+          dv[it] = reinterpret_cast<const float4*>(d_io + ((b * H + ho - 1) * W + wo - 1) * kPC)[q];
+      }
+    }
+  };
+  if ((long long)blockIdx.x < ntiles) load_tile(blockIdx.x);
+  for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+#pragma unroll
+    for (int it = 0; it < 2; ++it) {
+      const int px = pxb + 32 * it;
+      float yh[4], yl[4], dh[4], dl[4];
+      split_tf32(dy[it].x, yh[0], yl[0]); split_tf32(dy[it].y, yh[1], yl[1]); split_tf32(dy[it].z, yh[2], yl[2]); split_tf32(dy[it].w, yh[3], yl[3]);
+      split_tf32(dv[it].x, dh[0], dl[0]); split_tf32(dv[it].y, dh[1], dl[1]); split_tf32(dv[it].z, dh[2], dl[2]); split_tf32(dv[it].w, dh[3], dl[3]);
+      // A1 (rows px, K = co): one 16-byte chunk
+      const uint32_t o1 = kmaj_off(px, 4 * q);
+      *reinterpret_cast<float4*>(smem + kPOffA1 + o1) = make_float4(yh[0], yh[1], yh[2], yh[3]);
+      *reinterpret_cast<float4*>(smem + kPOffA1 + kPOp + o1) = make_float4(yl[0], yl[1], yl[2], yl[3]);
+      // A2 (rows co, K = px) and B2 (rows ci, K = px): transposed, 4-byte stores
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const uint32_t o2 = kmaj_off(4 * q + i, px);
+        *reinterpret_cast<float*>(smem + kPOffA2 + o2) = yh[i];
+        *reinterpret_cast<float*>(smem + kPOffA2 + kPOp + o2) = yl[i];
+        *reinterpret_cast<float*>(smem + kPOffB2 + o2) = dh[i];
+        *reinterpret_cast<float*>(smem + kPOffB2 + kPOpB2 + o2) = dl[i];
+      }
+    }
+    fence_proxy_async();  // generic-proxy writes of the operand images must be visible to the tensor core
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {  // converged warp, elected lane issues
+      tc_fence_after();
+#pragma unroll 1
+      for (int term = 0; term < 3; ++term) {
+        const uint32_t a1 = sbase + kPOffA1 + (term == 1 ? kPOp : 0), b1 = sbase + kPOffB1 + (term == 2 ? kPOp : 0);
+        for (int ks = 0; ks < 8; ++ks)
+          tc_mma_tf32_elect(tmem, umma_desc(a1 + ks * 2 * kPLbo, kPLbo, kPSbo), umma_desc(b1 + ks * 2 * kPLbo, kPLbo, kPSbo),
+                            kPIdesc1, (term | ks) != 0);
+      }
+#pragma unroll 1
+      for (int term = 0; term < 3; ++term) {
+        const uint32_t a2 = sbase + kPOffA2 + (term == 1 ? kPOp : 0), b2 = sbase + kPOffB2 + (term == 2 ? kPOpB2 : 0);
+        for (int ks = 0; ks < 8; ++ks)
+          tc_mma_tf32_elect(tmem + 64u, umma_desc(a2 + ks * 2 * kPLbo, kPLbo, kPSbo), umma_desc(b2 + ks * 2 * kPLbo, kPLbo, kPSbo),
+                            kPIdesc2, !(first && term == 0 && ks == 0));
+      }
+      tc_commit_elect(bar);
+    }
+    first = false;
+    if (tile + gridDim.x < ntiles) load_tile(tile + gridDim.x);  // in flight during the MMAs and the epilogue
+    mbar_wait(bar, parity);
+    parity ^= 1u;
+    tc_fence_after();
+    // dgrad epilogue: with M = 64 accumulator row r lives in TMEM lane 32 (r / 16) + r % 16: warp w reads the lane
+    // quarter w % 4 (rows 16 (w % 4) + lane, lanes 0..15) and the 16 columns (w / 4) * 16 ..
+    {
+      float v[16];
+      tc_ld16(tmem + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)((warp >> 2) * 16), v);
+      tc_wait_ld();
+      const long long gp = tile * kPTile + 16 * (warp & 3) + lane;
+      if (lane < 16 && gp < npix) {
+        int wo, ho;
+        long long b;
+        split_pixel(gp, Wo, Ho, &b, &ho, &wo);
+        if (ho >= 1 && ho <= H && wo >= 1 && wo <= W) {  // interior pixels only: the border's input is the zero padding
+          float4* dst = reinterpret_cast<float4*>(d_io + ((b * H + ho - 1) * W + wo - 1) * kPC + (warp >> 2) * 16);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) dst[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+        }
+      }
+    }
+    tc_fence_before();
+    // the next tile's staging overwrites the operand images (their MMAs have retired) and, before its MMAs are
+    // issued, passes the barrier above, which also orders this epilogue's TMEM reads before those MMAs
+  }
+  // wgrad + bias gradient: rows co (lane layout as above), columns ci 0..63 and the ones column 64
+  if (!first && warp < 4) {
+    float v[16];
+    const int co = 16 * warp + lane;
+#pragma unroll 1
+    for (int cb = 0; cb < 4; ++cb) {
+      tc_ld16(tmem + ((uint32_t)(warp * 32) << 16) + 64u + (uint32_t)(cb * 16), v);
+      tc_wait_ld();
+      if (lane < 16)
+#pragma unroll
+        for (int i = 0; i < 16; ++i) atomicAdd(&g_w[co * kPC + cb * 16 + i], v[i]);
+    }
+    float v8[8];
+    tc_ld8(tmem + ((uint32_t)(warp * 32) << 16) + 64u + 64u, v8);
+    tc_wait_ld();
+    if (lane < 16) atomicAdd(&g_b[co], v8[0]);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(256));
+}
+
+// 1 = launched, < 0 = error
+int launch_pw_bwd_tc(kws_handle_t h, const float* out, const float* dout, const float* dpooled, float inv_area, float* d_io,
+                     const float* w_flat, float* g_w, float* g_b, long long B, int H, int W, cudaStream_t st) {
+  if (int rc = ensure_dyn_smem(pw_bwd_tc_kernel, kPSmem)) return rc;
+  const long long ntiles = (B * (long long)(H + 2) * (W + 2) + kPTile - 1) / kPTile;
+  const long long g = ntiles < h->sm_count ? ntiles : h->sm_count;
+  pw_bwd_tc_kernel<<<(unsigned)g, kPThreads, kPSmem, st>>>(out, dout, dpooled, inv_area, d_io, w_flat, g_w, g_b, B, H, W);
+  KWS_CHECK_LAUNCH(h);
+  return 1;
+}
+
+}  // namespace kws
