@@ -179,7 +179,7 @@ int build_gemm_model(ModelWeights& m, const std::vector<float>& conv1_w, const s
                      const std::vector<const float*>& pw_b);
 void free_gemm_model(void* gm);
 int launch_dscnn_gemm(kws_handle_t h, const float* feats_dev, int64_t B, int T, int F, float* buf0, float* buf1,
-                      float** last_out, cudaStream_t st);
+                      float** last_out, int* last_rows, cudaStream_t st);
 // tables.cu
 int build_feature_tables(kws_handle_t h, const kws_feature_config* cfg);
 void free_feature_tables(FeatureTables& t);

@@ -679,11 +679,12 @@ int kws_model_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t
     const int64_t nbat = (B - b0 < chunk) ? B - b0 : chunk;
     if (m.path == 0 && m.gemm) {  // layer-by-layer tensor-core path (model_gemm.cu)
       float* last = nullptr;
-      const int rc = launch_dscnn_gemm(h, feats_dev + b0 * T * F, nbat, (int)T, (int)F, buf0, buf1, &last, st);
+      int last_rows = 0;  // rows of [C] per clip that pool_fc averages: pixels, or the last block's pooled partial sums
+      const int rc = launch_dscnn_gemm(h, feats_dev + b0 * T * F, nbat, (int)T, (int)F, buf0, buf1, &last, &last_rows, st);
       if (rc < 0) return rc;
       if (rc == 1) {
         long long g = nbat < h->sm_count * 8LL ? nbat : h->sm_count * 8LL;
-        pool_fc_kernel<<<(unsigned)g, kPoolThreads, pool_smem(C), st>>>(last, logits_dev + b0 * K, m.d_fc_w, m.d_fc_b, nbat, Hl * Wl, C, K,
+        pool_fc_kernel<<<(unsigned)g, kPoolThreads, pool_smem(C), st>>>(last, logits_dev + b0 * K, m.d_fc_w, m.d_fc_b, nbat, last_rows, C, K,
                                                         nullptr);
         KWS_CHECK_LAUNCH(h);
         continue;

@@ -38,6 +38,12 @@ struct GemmParams {
   int H, W, C, T, F;   // H x W: output (interior) grid of the layer
   int R, nbands;       // tile = R whole rows of one clip (R * W <= 128), nbands = ceil(H / R)
   int kvalid, npad, nh, nhalf, nchunks, tmem_cols, patch_bytes;
+  // last block only: instead of the activation, write per-tile channel sums (the global average pool's partial sums,
+  // scaled so that pool_fc_kernel's mean over nbands + 1 rows is the mean over the padded output) -- the largest
+  // activation of the network is never written or re-read
+  float* pool;           // [B][nbands + 1][C] or null
+  const float* border;   // [C] ReLU(pointwise bias): value of every border pixel of the padded output
+  float pool_scale;      // (nbands + 1) / ((H + 2) * (W + 2))
 };
 
 template <int MODE>
@@ -65,10 +71,11 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_gemm_kernel(const GemmParams p) 
   }
   const int kpad = p.nchunks * kGKC;
   if (MODE == 1)
-    for (int i = tid; i < 9 * kpad; i += kGT) {
-      const int t = i / kpad, k = i - t * kpad;
+    for (int i = tid; i < 9 * kpad; i += kGT) {  // [chunk][tap][32 channels]: a chunk's taps at immediate offsets
+      const int kcw = i / (9 * kGKC), r = i - kcw * 9 * kGKC, t = r >> 5, k = kcw * kGKC + (r & 31);
       sW[i] = k < p.C ? __ldg(p.dw_w + t * p.C + k) : 0.f;
     }
+  for (int i = tid; i < p.npad; i += kGT) (sW + 9 * kpad)[i] = i < p.C ? __ldg(p.bias + i) : 0.f;
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -88,56 +95,90 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_gemm_kernel(const GemmParams p) 
   // MODE 1 input staging: the (R+2) x W x 32-channel input patch of a chunk is copied to shared memory with
   // cp.async two chunks ahead of its use (3 patch buffers), so HBM/L2 latency is off the critical path and
   // every input element is fetched once per chunk (the 3x3 reuse happens in shared memory).
-  unsigned char* sP = reinterpret_cast<unsigned char*>(sW + 9 * kpad);
+  float* sBias = sW + 9 * kpad;                  // [npad] epilogue bias (filled before the first __syncthreads)
+  unsigned char* sP = reinterpret_cast<unsigned char*>(sBias + p.npad);
   const int patch_bytes = p.patch_bytes;
   const long long my_tiles = blockIdx.x < ntiles ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
   const long long total_chunks = my_tiles * p.nchunks;
   // this thread's (up to 4) 16-byte pieces of a patch are the same for every chunk: patch row, global
   // offset relative to the first patch row, channel quad
+  // The patch keeps one zero column on either side (W + 2 columns per row, written once here: the copies never
+  // touch them), so the stencil reads its three columns without edge predicates.
   constexpr int kPieces = 4;
-  int pf_row[kPieces], pf_off[kPieces];
-  const int np = (R + 2) * W * 8;
+  int pf_row[kPieces], pf_off[kPieces], pf_dst[kPieces];
+  const int np = (R + 2) * W * 8, prow_bytes = (W + 2) * 128;
 #pragma unroll
   for (int i = 0; i < kPieces; ++i) {
     const int e = tid + i * kProd, pxl = e >> 3, ii = pxl / W, xx = pxl - ii * W;
     pf_row[i] = (producer && e < np) ? ii : -1;
     pf_off[i] = (ii * W + xx) * C + 4 * (e & 7);
+    pf_dst[i] = ii * prow_bytes + (xx + 1) * 128 + (e & 7) * 16;
   }
-  auto prefetch_patch = [&](long long fc) {  // flat chunk index of this CTA
-    if (MODE == 1 && producer && fc < total_chunks) {
-      const long long lt = fc / p.nchunks;
-      const int kcp = (int)(fc - lt * p.nchunks);
-      const long long tl = blockIdx.x + lt * gridDim.x, bp = tl / p.nbands;
-      const int rp = (int)(tl - bp * p.nbands) * R;
-      const uint32_t dst0 = smem_u32(sP + (size_t)(fc % 3) * patch_bytes) + (uint32_t)tid * 16u;
-      const float* base = p.in + ((bp * H + rp - 1) * W) * (long long)C + kcp * kGKC;  // row rp - 1 (may lie outside)
-      const int kq = kcp * kGKC + 4 * (tid & 7);
+  if (MODE == 1)
+    for (int i = tid; i < 3 * (R + 2) * 16; i += kGT) {
+      const int slot = i / ((R + 2) * 16), r = i - slot * (R + 2) * 16, row = r >> 4, side = (r >> 3) & 1;
+      *reinterpret_cast<float4*>(sP + (size_t)slot * patch_bytes + row * prow_bytes + side * (W + 1) * 128 + (r & 7) * 16) =
+          make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  // stencil ownership of this thread: up to 3 output rows rl0.. of column x, channel quad q
+  const int rl0 = rg * RG, st_rows = (producer && rg < NG) ? min(RG, R - rl0) : 0;
+  const int st_patch = rl0 * prow_bytes + x * 128 + q * 16;  // padded column x = input column x - 1
+  int st_a[3];
+#pragma unroll
+  for (int ro = 0; ro < 3; ++ro) {
+    const int pp = (rl0 + ro) * W + x;
+    st_a[ro] = q * kGLboA + (pp >> 3) * kGSboA + (pp & 7) * 16;
+  }
+  // The prefetch stream runs two chunks ahead of the consumer; its position (chunk in tile, clip, band, patch slot)
+  // is stepped incrementally -- 64-bit divisions here cost more instructions than the stencil itself.
+  const int g_q = (int)(gridDim.x / (unsigned)p.nbands), g_r = (int)(gridDim.x % (unsigned)p.nbands);
+  long long pf_left = total_chunks, pf_b = (long long)(blockIdx.x / (unsigned)p.nbands);
+  int pf_kc = 0, pf_band = (int)(blockIdx.x % (unsigned)p.nbands), pf_slot = 0;
+  auto prefetch_patch = [&]() {
+    if (MODE == 1 && producer && pf_left > 0) {
+      const int rp = pf_band * R;
+      const uint32_t dst0 = smem_u32(sP + (size_t)pf_slot * patch_bytes);
+      const float* base = p.in + ((pf_b * H + rp - 1) * W) * (long long)C + pf_kc * kGKC;  // row rp - 1 (may lie outside)
+      const int kq = pf_kc * kGKC + 4 * (tid & 7);
 #pragma unroll
       for (int i = 0; i < kPieces; ++i) {
         if (pf_row[i] >= 0) {
           const int yy = rp - 1 + pf_row[i];
           const bool ok = yy >= 0 && yy < H && kq < C;
           const float* src = ok ? base + pf_off[i] : p.in;
-          asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst0 + (uint32_t)(i * kProd) * 16u), "l"(src),
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst0 + (uint32_t)pf_dst[i]), "l"(src),
                        "r"(ok ? 16 : 0)
                        : "memory");
         }
       }
     }
     asm volatile("cp.async.commit_group;" ::: "memory");  // always commit: keeps the group count in step
+    --pf_left;
+    pf_slot = pf_slot == 2 ? 0 : pf_slot + 1;
+    if (++pf_kc == p.nchunks) {  // next tile of this CTA: tile += gridDim.x
+      pf_kc = 0;
+      pf_b += g_q;
+      pf_band += g_r;
+      if (pf_band >= p.nbands) {
+        pf_band -= p.nbands;
+        ++pf_b;
+      }
+    }
   };
-  prefetch_patch(0);
-  prefetch_patch(1);
+  prefetch_patch();
+  prefetch_patch();
   asm volatile("cp.async.wait_group 1;" ::: "memory");
   __syncthreads();
   long long fchunk = 0;
+  int cslot = 0;                                 // patch slot of the chunk being consumed (= fchunk % 3)
+  long long b = (long long)(blockIdx.x / (unsigned)p.nbands);
+  int band = (int)(blockIdx.x % (unsigned)p.nbands);
 
   for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-    const long long b = tile / p.nbands;
-    const int r0 = (int)(tile - b * p.nbands) * R;
-    for (int kc = 0; kc < p.nchunks; ++kc, ++cnt, ++fchunk) {
+    const int r0 = band * R;
+    for (int kc = 0; kc < p.nchunks; ++kc, ++cnt, ++fchunk, cslot = cslot == 2 ? 0 : cslot + 1) {
       const int buf = cnt & 1;
-      prefetch_patch(fchunk + 2);
+      prefetch_patch();
       if (cnt >= 2) mbar_wait(bar0 + 8u * buf, ((cnt - 2) >> 1) & 1);  // the MMAs that read this buffer retired
       if (tid == kIssuer && cnt == 0) {  // first weight chunk (later ones are requested one chunk ahead, see below)
         mbar_expect_tx(barB, (uint32_t)bbytes);
@@ -145,62 +186,46 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_gemm_kernel(const GemmParams p) 
       }
       unsigned char* abuf = sA + buf * kGABytes;
       if (MODE == 1) {
-        // depthwise 3x3 (zero padding 1) of channels k..k+3 down this thread's column: every input row of the
-        // row group (<= 3 output rows + 2 halo rows) is fetched up front -- 3 coalesced float4 per row, all in
-        // flight together -- and accumulated into the output rows it feeds
-        const int k = kc * kGKC + 4 * q;
-        if (producer && rg < NG && k < p.kvalid) {
-          const int rl0 = rg * RG, rl1 = min(rl0 + RG, R);
-          const float4* patch = reinterpret_cast<const float4*>(sP + (size_t)(fchunk % 3) * patch_bytes);
-          float4 vin[5][3];
-#pragma unroll
-          for (int ii = 0; ii < 5; ++ii) {
-            const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
-            vin[ii][0] = vin[ii][1] = vin[ii][2] = z;
-            if (ii <= rl1 - rl0 + 1) {  // patch row rl0 + ii is input row r0 + rl0 - 1 + ii (zero-filled outside the image)
-              const float4* prow = patch + ((rl0 + ii) * W + x) * 8 + q;
-              vin[ii][1] = prow[0];
-              if (x > 0) vin[ii][0] = prow[-8];
-              if (x + 1 < W) vin[ii][2] = prow[8];
-            }
-          }
-          unsigned char* acol = abuf + q * kGLboA;
-          const float* wq = sW + kc * kGKC + 4 * q;
-          V wlo[9], whi[9];  // taps of channels (k, k+1) and (k+2, k+3): packed f32x2 FMAs over channel pairs
+        // depthwise 3x3 (zero padding 1) of channels k..k+3 down this thread's column: the 5 x 3 input window of
+        // the row group comes from the padded patch (no edge predicates; rows past a short group are read but
+        // never stored), 3 output rows are accumulated with packed f32x2 FMAs over channel pairs.  Channels past
+        // the channel count were zero-filled by the copy, so the K padding needs no special case; rows of A that
+        // no pixel owns keep stale data, which only reaches accumulator rows the epilogue never reads.
+        if (st_rows > 0) {
+          const unsigned char* pb = sP + (size_t)cslot * patch_bytes + st_patch;
+          const float4* w4 = reinterpret_cast<const float4*>(sW + kc * 9 * kGKC + 4 * q);
+          V wlo[9], whi[9];
 #pragma unroll
           for (int t = 0; t < 9; ++t) {
-            const float4 w = *reinterpret_cast<const float4*>(wq + t * kpad);
+            const float4 w = w4[t * 8];
             wlo[t] = make_float2(w.x, w.y);
             whi[t] = make_float2(w.z, w.w);
           }
+          float4 vin[5][3];
+#pragma unroll
+          for (int ii = 0; ii < 5; ++ii) {
+            const float4* prow = reinterpret_cast<const float4*>(pb + ii * prow_bytes);
+            vin[ii][0] = prow[0];
+            vin[ii][1] = prow[8];
+            vin[ii][2] = prow[16];
+          }
 #pragma unroll
           for (int ro = 0; ro < 3; ++ro) {  // output row rl0 + ro from input rows ro, ro+1, ro+2 of the group
-            if (rl0 + ro < rl1) {
-              V olo = fsplat(0.f), ohi = fsplat(0.f);
+            V olo = fsplat(0.f), ohi = fsplat(0.f);
 #pragma unroll
-              for (int i = 0; i < 3; ++i)
+            for (int i = 0; i < 3; ++i)
 #pragma unroll
-                for (int j = 0; j < 3; ++j) {
-                  const float4 a = vin[ro + i][j];
-                  olo = ffma(make_float2(a.x, a.y), wlo[i * 3 + j], olo);
-                  ohi = ffma(make_float2(a.z, a.w), whi[i * 3 + j], ohi);
-                }
-              const float4 o = make_float4(olo.x, olo.y, ohi.x, ohi.y);
-              const int pp = (rl0 + ro) * W + x;
-              uint4 r;  // tf32 round-to-nearest: add half an ulp of the 10-bit mantissa, the MMA drops the low 13 bits
-              const bool live = r0 + rl0 + ro < H;
-              r.x = live ? __float_as_uint(o.x) + 0x1000u : 0u;
-              r.y = live ? __float_as_uint(o.y) + 0x1000u : 0u;
-              r.z = live ? __float_as_uint(o.z) + 0x1000u : 0u;
-              r.w = live ? __float_as_uint(o.w) + 0x1000u : 0u;
-              *reinterpret_cast<uint4*>(acol + (pp >> 3) * kGSboA + (pp & 7) * 16) = r;
-            }
-          }
-        } else if (producer && rg < NG) {  // K padding beyond the channel count
-          const int rl0 = rg * RG, rl1 = min(rl0 + RG, R);
-          for (int ro = rl0; ro < rl1; ++ro) {
-            const int pp = ro * W + x;
-            *reinterpret_cast<uint4*>(abuf + q * kGLboA + (pp >> 3) * kGSboA + (pp & 7) * 16) = make_uint4(0, 0, 0, 0);
+              for (int j = 0; j < 3; ++j) {
+                const float4 a = vin[ro + i][j];
+                olo = ffma(make_float2(a.x, a.y), wlo[i * 3 + j], olo);
+                ohi = ffma(make_float2(a.z, a.w), whi[i * 3 + j], ohi);
+              }
+            uint4 r;  // tf32 round-to-nearest: add half an ulp of the 10-bit mantissa, the MMA drops the low 13 bits
+            r.x = __float_as_uint(olo.x) + 0x1000u;
+            r.y = __float_as_uint(olo.y) + 0x1000u;
+            r.z = __float_as_uint(ohi.x) + 0x1000u;
+            r.w = __float_as_uint(ohi.y) + 0x1000u;
+            if (ro < st_rows) *reinterpret_cast<uint4*>(abuf + st_a[ro]) = r;
           }
         }
       } else if (producer) {  // im2col of the 10x10 stride-2 padding-2 window: item = (pixel row, 8-wide K slice)
@@ -263,24 +288,38 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_gemm_kernel(const GemmParams p) 
       mbar_wait(bar0 + 8u * (last & 1), (last >> 1) & 1);
       tc_fence_after();
     }
-    if (warp < 8) {  // epilogue: lane = pixel row of the tile, warp / 4 = column half
-      const int row = (warp & 3) * 32 + lane, chalf = warp >> 2;
+    {  // epilogue on all 16 warps: lane = pixel row of the tile (TMEM lane quarter warp % 4), 16-column groups
+       // warp / 4, warp / 4 + 4, ...
+      const int row = (warp & 3) * 32 + lane;
       const int rl = row / W, xq = row - rl * W, y = r0 + rl;
       float* orow = nullptr;
       if (rl < R && y < H)
         orow = MODE == 1 ? p.out + ((b * (H + 2) + y + 1) * (W + 2) + xq + 1) * (long long)C
                          : p.out + ((b * H + y) * W + xq) * (long long)C;
-      const int c0 = chalf * (p.npad / 2), c1 = c0 + p.npad / 2;
       const uint32_t taddr = tmem + ((uint32_t)((warp & 3) * 32) << 16);
-      for (int c = c0; c < c1; c += 16) {
+      float* s_part = reinterpret_cast<float*>(sA);  // [4 lane quarters][npad] (the A buffers are idle: all MMAs retired)
+      for (int c = (warp >> 2) * 16; c < p.npad; c += 64) {
         float v[16];
         tc_ld16(taddr + (uint32_t)c, v);
         tc_wait_ld();
-        if (orow) {
+        if (MODE == 1 && p.pool) {  // channel sums over the tile's pixels: lanes without a pixel contribute zero
+#pragma unroll
+          for (int e = 0; e < 16; ++e) {
+            float r = orow ? fmaxf(v[e] + sBias[c + e], 0.f) : 0.f;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) r += __shfl_xor_sync(0xffffffffu, r, o);
+            v[e] = r;
+          }
+          if (lane == 0) {
+#pragma unroll
+            for (int e = 0; e < 16; e += 4)
+              *reinterpret_cast<float4*>(s_part + (warp & 3) * p.npad + c + e) = make_float4(v[e], v[e + 1], v[e + 2], v[e + 3]);
+          }
+        } else if (orow) {
 #pragma unroll
           for (int e = 0; e < 16; e += 4) {
             if (c + e < C) {
-              const float4 bz = __ldg(reinterpret_cast<const float4*>(p.bias + c + e));
+              const float4 bz = *reinterpret_cast<const float4*>(sBias + c + e);
               *reinterpret_cast<float4*>(orow + c + e) =
                   make_float4(fmaxf(v[e] + bz.x, 0.f), fmaxf(v[e + 1] + bz.y, 0.f), fmaxf(v[e + 2] + bz.z, 0.f),
                               fmaxf(v[e + 3] + bz.w, 0.f));
@@ -288,9 +327,25 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_gemm_kernel(const GemmParams p) 
           }
         }
       }
+      if (MODE == 1 && p.pool) {
+        __syncthreads();
+        float* prow = p.pool + (b * (p.nbands + 1) + band) * (long long)C;
+        for (int c = tid; c < C; c += kGT) {
+          prow[c] = ((s_part[c] + s_part[p.npad + c]) + (s_part[2 * p.npad + c] + s_part[3 * p.npad + c])) * p.pool_scale;
+          if (band == 0)  // one extra row per clip: the 2 (W + 2) + 2 H border pixels, all ReLU(bias)
+            p.pool[(b * (p.nbands + 1) + p.nbands) * (long long)C + c] =
+                (float)(2 * (W + 2) + 2 * H) * __ldg(p.border + c) * p.pool_scale;
+        }
+      }
     }
     tc_fence_before();
     __syncthreads();  // the next tile's first MMA overwrites the accumulator
+    b += g_q;
+    band += g_r;
+    if (band >= p.nbands) {
+      band -= p.nbands;
+      ++b;
+    }
   }
   tc_fence_before();
   __syncthreads();
@@ -407,23 +462,29 @@ int build_gemm_model(ModelWeights& m, const std::vector<float>& conv1_w, const s
 
 // 1 = handled, 0 = not applicable, < 0 = error.  buf0/buf1: ping-pong NHWC workspaces of the caller.
 int launch_dscnn_gemm(kws_handle_t h, const float* feats_dev, int64_t B, int T, int F, float* buf0, float* buf1,
-                      float** last_out, cudaStream_t st) {
+                      float** last_out, int* last_rows, cudaStream_t st) {
   ModelWeights& m = h->model;
   GemmModel* g = reinterpret_cast<GemmModel*>(m.gemm);
   if (!g) return 0;
   const int C = g->C, nb = g->nb;
   const int H1 = (T + 4 - 10) / 2 + 1, W1 = (F + 4 - 10) / 2 + 1;
   if (W1 + 2 * nb > 60) return 0;  // one thread column per pixel column (60 producer columns per CTA)
-  int patch_bytes = 0;  // largest (R + 2) x W x 32-channel input patch over the layers
+  // tile = R whole rows of one clip: at most 128 pixels, and at most 3 rows per row group of the stencil's thread map
+  auto rows_per_tile = [](int Hh, int Ww) {
+    const int ng = 60 / Ww > 0 ? 60 / Ww : 1;
+    int r = 128 / Ww > 0 ? 128 / Ww : 1;
+    if (r > 3 * ng) r = 3 * ng;
+    return r > Hh ? Hh : r;
+  };
+  int patch_bytes = 0, slack = 0;  // largest (R + 2) x (W + 2) x 32-channel input patch over the layers
   for (int l = 0; l < nb; ++l) {
     const int Ww = W1 + 2 * l, Hh = H1 + 2 * l;
-    int Rr = 128 / Ww > 0 ? 128 / Ww : 1;
-    if (Rr > Hh) Rr = Hh;
-    const int pb = (Rr + 2) * Ww * 128;
+    const int pb = (rows_per_tile(Hh, Ww) + 2) * (Ww + 2) * 128;
     if (pb > patch_bytes) patch_bytes = pb;
+    if (2 * (Ww + 2) * 128 > slack) slack = 2 * (Ww + 2) * 128;  // short row groups read (and drop) two rows past their band
   }
   const size_t smem_bytes = 2 * kGABytes + 2 * (size_t)(g->npad / 8) * kGSbo + (size_t)9 * ((C + kGKC - 1) / kGKC * kGKC) * 4 +
-                            (size_t)3 * patch_bytes;
+                            (size_t)g->npad * 4 + (size_t)3 * patch_bytes + slack;
   if (smem_bytes > 227 * 1024) return 0;
   if (int rc = ensure_dyn_smem(dscnn_gemm_kernel<0>, smem_bytes)) return rc;
   if (int rc = ensure_dyn_smem(dscnn_gemm_kernel<1>, smem_bytes)) return rc;
@@ -441,8 +502,7 @@ int launch_dscnn_gemm(kws_handle_t h, const float* feats_dev, int64_t B, int T, 
   auto set_grid = [&](int Hh, int Ww) {  // tile = R whole rows; returns the grid size
     p.H = Hh;
     p.W = Ww;
-    p.R = 128 / Ww > 0 ? 128 / Ww : 1;
-    if (p.R > Hh) p.R = Hh;
+    p.R = rows_per_tile(Hh, Ww);
     p.nbands = (Hh + p.R - 1) / p.R;
     const long long t = B * p.nbands, gmax = (long long)h->sm_count * ctas_per_sm;
     return (unsigned)(t < gmax ? t : gmax);
@@ -467,7 +527,18 @@ int launch_dscnn_gemm(kws_handle_t h, const float* feats_dev, int64_t B, int T, 
     p.bias = g->d_bias + (size_t)(l + 1) * C;
     p.kvalid = g->kvalid[l + 1];
     p.nchunks = g->nchunks[l + 1];
-    dscnn_gemm_kernel<1><<<set_grid(H, W), kGT, smem_bytes, st>>>(p);
+    const unsigned grid = set_grid(H, W);
+    if (l == nb - 1) {  // the pooled rows replace the last activation (see GemmParams::pool)
+      p.pool = nxt;
+      p.border = g->d_border + (size_t)l * C;
+      p.pool_scale = (float)(p.nbands + 1) / (float)((H + 2) * (W + 2));
+      dscnn_gemm_kernel<1><<<grid, kGT, smem_bytes, st>>>(p);
+      KWS_CHECK_LAUNCH(h);
+      *last_out = nxt;
+      *last_rows = p.nbands + 1;
+      return 1;
+    }
+    dscnn_gemm_kernel<1><<<grid, kGT, smem_bytes, st>>>(p);
     KWS_CHECK_LAUNCH(h);
     const long long nborder = B * (long long)(2 * (W + 2) + 2 * H) * (C / 4);
     long long gb = (nborder + 255) / 256;
@@ -480,7 +551,8 @@ int launch_dscnn_gemm(kws_handle_t h, const float* feats_dev, int64_t B, int T, 
     H += 2;
     W += 2;
   }
-  *last_out = cur;
+  *last_out = cur;  // no blocks: conv1 output [B, H1, W1, C]
+  *last_rows = H * W;
   return 1;
 }
 
