@@ -14,6 +14,7 @@
 // Epilogue: tcgen05.ld (lane = pixel) + bias + ReLU -> NHWC stores at the padded position (y+1, x+1) of the
 // (H+2) x (W+2) output; the border pixels, ReLU(pointwise bias) (models.py:104-106), are written by
 // border_fill_kernel.  The depthwise bias is folded through the pointwise weights on the host.
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -353,6 +354,311 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_gemm_kernel(const GemmParams p) 
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((uint32_t)p.tmem_cols));
 }
 
+// ---- warp-specialised block kernel ------------------------------------------------------------------------
+// One depthwise-separable block (depthwise 3x3 -> pointwise 1x1 -> bias -> ReLU) as an asynchronous pipeline; the
+// chunk-synchronous kernel above stays for conv1 (MODE 0) and for shapes outside this one's thread map.
+//
+// What bounds the block layers is the shared-memory / L1 data path, not the tensor core: a tf32 MMA of
+// M = 128, N = 144, K = 8 reads 8.6 KB of operands for 72 cycles of math, the weight chunks are written once and
+// read once per 128 pixels, and the chunk-synchronous kernel on top of that staged every input patch in shared
+// memory and read each element five times from there, with all 16 warps meeting at a CTA barrier per K chunk
+// (ncu: 4.9 K cycles per chunk, tensor pipe 16 % active, barrier + LSU-queue stalls on top).  Here:
+//   * no input patch in shared memory: a producer thread owns (channel quad, NC adjacent columns) of the tile and
+//     walks DOWN the rows with the 3x3 window in registers -- one 16-byte global load per input pixel and channel
+//     quad (NC + 2 per row, L1 catches the neighbour thread's overlap), each input row updates the three output
+//     rows it touches (out = P + w2.v, P = R + w1.v, R = w0.v), so nothing is read twice and nothing is exchanged;
+//   * five producer groups of 3 warps work on five DIFFERENT K chunks at the same time; group g owns A-ring stage g
+//     (full / empty mbarriers, tcgen05.commit releases a stage), so there is no CTA-wide barrier anywhere;
+//   * the issue warp streams the weight chunks through a 3-stage TMA ring and fires the chunk's MMAs in order;
+//   * one accumulator (N = 288 columns of the 512): its drain is spread over all 16 warps (lane quarter x column
+//     quarter) and placed where the ring is full anyway -- a warp drains tile t right after it has produced its
+//     first chunk of tile t + 1, so the MMAs of the next tile are already queued when the accumulator frees up.
+constexpr int kWsG = 5;     // producer groups = A-ring stages
+constexpr int kWsGT = 96;   // threads per group: 8 channel quads x 12 column groups
+constexpr int kWsBS = 3;    // weight-chunk ring stages
+
+template <int NC, int PF, bool WREG>
+__global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams p) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  __shared__ __align__(8) unsigned long long s_bar[2 * kWsG + 2 * kWsBS + 2];
+  __shared__ uint32_t s_tmem;
+  const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
+  const int bbytes = (p.npad / 8) * kGSbo;
+  unsigned char* sA = smem;                                  // [kWsG][kGABytes]
+  unsigned char* sB = smem + kWsG * kGABytes;                // [kWsBS][bbytes]
+  const int kpad = p.nchunks * kGKC;
+  float* sW = reinterpret_cast<float*>(sB + kWsBS * (size_t)bbytes);  // [chunk][tap][32 channels]
+  float* sBias = sW + 9 * kpad;                              // [npad]
+  const uint32_t bFull = smem_u32(&s_bar[0]), bEmpty = bFull + 8 * kWsG, bBfull = bEmpty + 8 * kWsG,
+                 bBempty = bBfull + 8 * kWsBS, bAccFull = bBempty + 8 * kWsBS, bAccFree = bAccFull + 8;
+  if (tid == 0) {
+    for (int g = 0; g < kWsG; ++g) {
+      mbar_init(bFull + 8 * g, 3);   // one arrival per producer warp of the group
+      mbar_init(bEmpty + 8 * g, 1);  // tcgen05.commit
+    }
+    for (int s = 0; s < kWsBS; ++s) {
+      mbar_init(bBfull + 8 * s, 1);
+      mbar_init(bBempty + 8 * s, 1);
+    }
+    mbar_init(bAccFull, 1);
+    mbar_init(bAccFree, kGT / 32);
+    fence_mbar_init();
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)),
+                 "r"((uint32_t)p.tmem_cols));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  for (int i = tid; i < 9 * kpad; i += kGT) {
+    const int kcw = i / (9 * kGKC), r = i - kcw * 9 * kGKC, t = r >> 5, k = kcw * kGKC + (r & 31);
+    sW[i] = k < p.C ? __ldg(p.dw_w + t * p.C + k) : 0.f;
+  }
+  for (int i = tid; i < p.npad; i += kGT) sBias[i] = i < p.C ? __ldg(p.bias + i) : 0.f;
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = s_tmem;
+  const int H = p.H, W = p.W, C = p.C, R = p.R, nch = p.nchunks;
+  const unsigned ntiles = (unsigned)(p.B * p.nbands);  // the host keeps B * nbands * nchunks below 2^31
+  const int my_tiles = blockIdx.x < ntiles ? (int)((ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x) : 0;
+  const int total = my_tiles * nch;  // work items (tile, K chunk) of this CTA, in issue order
+
+  // drain of tile j's accumulator by this warp: TMEM lane quarter warp % 4 (lane = pixel of the tile), column
+  // quarter warp / 4; bias + ReLU -> NHWC store at the padded position, or (last block) per-(tile, lane quarter)
+  // channel sums into the pool rows
+  auto epilogue = [&](int j) {
+    mbar_wait(bAccFull, (uint32_t)j & 1u);
+    tc_fence_after();
+    const unsigned tile = blockIdx.x + (unsigned)j * gridDim.x, b = tile / (unsigned)p.nbands;
+    const int band = (int)(tile - b * (unsigned)p.nbands), r0 = band * R;
+    const int lq = warp & 3, cs = warp >> 2;
+    const int pp = lq * 32 + lane, rl = pp / W, xq = pp - rl * W, y = r0 + rl;
+    const bool valid = rl < R && y < H;
+    const int ncol = p.npad >> 2, c0 = cs * ncol;
+    const uint32_t ta = tmem + ((uint32_t)(lq * 32) << 16) + (uint32_t)c0;
+    float* orow = p.out + (((long long)b * (H + 2) + y + 1) * (W + 2) + xq + 1) * (long long)C;
+    float* prow = p.pool ? p.pool + ((long long)b * (4 * p.nbands + 1) + band * 4 + lq) * (long long)C : nullptr;
+    auto emit = [&](float (&v)[8], int c) {
+      const float4 b0 = *reinterpret_cast<const float4*>(sBias + c), b1 = *reinterpret_cast<const float4*>(sBias + c + 4);
+      v[0] = fmaxf(v[0] + b0.x, 0.f); v[1] = fmaxf(v[1] + b0.y, 0.f); v[2] = fmaxf(v[2] + b0.z, 0.f); v[3] = fmaxf(v[3] + b0.w, 0.f);
+      v[4] = fmaxf(v[4] + b1.x, 0.f); v[5] = fmaxf(v[5] + b1.y, 0.f); v[6] = fmaxf(v[6] + b1.z, 0.f); v[7] = fmaxf(v[7] + b1.w, 0.f);
+      if (prow == nullptr) {
+        if (valid) {
+          if (c < C) *reinterpret_cast<float4*>(orow + c) = make_float4(v[0], v[1], v[2], v[3]);
+          if (c + 4 < C) *reinterpret_cast<float4*>(orow + c + 4) = make_float4(v[4], v[5], v[6], v[7]);
+        }
+      } else {
+        // channel sums over the warp's 32 pixels: halving butterfly (4 + 2 + 1 + 1 + 1 shuffles for 8 values, fixed
+        // order); lane l ends up with the sum of value (l >> 2) & 7
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[e] = valid ? v[e] : 0.f;
+        const bool h16 = lane & 16, h8 = lane & 8, h4 = lane & 4;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float keep = h16 ? v[e + 4] : v[e], send = h16 ? v[e] : v[e + 4];
+          v[e] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+        }
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const float keep = h8 ? v[e + 2] : v[e], send = h8 ? v[e] : v[e + 2];
+          v[e] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+        }
+        {
+          const float keep = h4 ? v[1] : v[0], send = h4 ? v[0] : v[1];
+          v[0] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+        }
+        v[0] += __shfl_xor_sync(0xffffffffu, v[0], 2);
+        v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
+        const int cc = c + ((lane >> 2) & 7);
+        if ((lane & 3) == 0 && cc < C) prow[cc] = v[0] * p.pool_scale;
+      }
+    };
+    for (int c = 0; c < ncol; c += 16) {
+      float v0[8], v1[8];
+      const bool two = c + 8 < ncol;
+      tc_ld8(ta + (uint32_t)c, v0);
+      if (two) tc_ld8(ta + (uint32_t)c + 8u, v1);
+      tc_wait_ld();
+      if (c + 16 >= ncol) {  // every value of the accumulator this warp needs is in registers: release it
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bAccFree);
+      }
+      emit(v0, c0 + c);
+      if (two) emit(v1, c0 + c + 8);
+    }
+    if (prow != nullptr && band == 0 && lq == 0)  // one extra row per clip: the 2 (W + 2) + 2 H border pixels, all ReLU(bias)
+      for (int c = c0 + lane; c < c0 + ncol && c < C; c += 32)
+        p.pool[((long long)b * (4 * p.nbands + 1) + 4 * p.nbands) * (long long)C + c] =
+            (float)(2 * (W + 2) + 2 * H) * __ldg(p.border + c) * p.pool_scale;
+  };
+
+  if (warp < kWsG * 3) {
+    // ---- producers ----
+    const int g = warp / 3, gt = tid - g * kWsGT;
+    const int q = gt & 7, cg = gt >> 3, x0 = cg * NC;
+    const bool act = x0 < W;
+    const uint32_t abase = smem_u32(sA + g * kGABytes) + (uint32_t)(q * kGLboA);
+    bool cv[NC + 2];
+#pragma unroll
+    for (int c = 0; c < NC + 2; ++c) cv[c] = act && x0 - 1 + c >= 0 && x0 - 1 + c < W;
+    const long long rowstride = (long long)W * C;
+    int epi_next = 0;
+    uint32_t k = 0;
+    for (int n = g; n < total; n += kWsG, ++k) {
+      const int j = n / nch, kc = n - j * nch;
+      const unsigned tile = blockIdx.x + (unsigned)j * gridDim.x, b = tile / (unsigned)p.nbands;
+      const int band = (int)(tile - b * (unsigned)p.nbands), r0 = band * R;
+      const int nrows = min(R, H - r0) + 2;  // input rows r0 - 1 .. of the band (rows outside the clip are zeros)
+      const int kq = kc * kGKC + 4 * q;
+      const bool kok = kq < C;
+      const float* src = p.in + (((long long)b * H + r0 - 1) * W + (x0 - 1)) * (long long)C + kq;
+      auto load_row = [&](int i, float4 (&v)[NC + 2]) {
+        const int y = r0 - 1 + i;
+        const bool rok = kok && y >= 0 && y < H;
+        const float* s = src + (long long)i * rowstride;
+#pragma unroll
+        for (int c = 0; c < NC + 2; ++c)
+          v[c] = (rok && cv[c]) ? __ldg(reinterpret_cast<const float4*>(s + (long long)c * C)) : make_float4(0.f, 0.f, 0.f, 0.f);
+      };
+      float4 vbuf[PF + 1][NC + 2];
+#pragma unroll
+      for (int r = 0; r < PF; ++r) load_row(r, vbuf[r]);
+      const float4* w4 = reinterpret_cast<const float4*>(sW + kc * 9 * kGKC + 4 * q);
+      V wlo[WREG ? 9 : 1], whi[WREG ? 9 : 1];
+      if (WREG) {
+#pragma unroll
+        for (int t = 0; t < (WREG ? 9 : 1); ++t) {
+          const float4 w = w4[t * 8];
+          wlo[t] = make_float2(w.x, w.y);
+          whi[t] = make_float2(w.z, w.w);
+        }
+      }
+      if (k >= 1) mbar_wait(bEmpty + 8 * g, (k - 1) & 1);  // the MMAs that read this group's stage have retired
+      V Plo[NC], Phi[NC], Rlo[NC], Rhi[NC];
+#pragma unroll
+      for (int c = 0; c < NC; ++c) Plo[c] = Phi[c] = Rlo[c] = Rhi[c] = fsplat(0.f);
+      // input row i of the band: finishes output row i - 2 (taps 6..8), continues i - 1 (3..5), starts i (0..2)
+      auto step = [&](int i, const float4 (&v)[NC + 2]) {
+        const int ro = i - 2;
+        const int pp0 = ro * W + x0;
+#pragma unroll
+        for (int dy = 2; dy >= 0; --dy) {
+          V tlo[3], thi[3];
+#pragma unroll
+          for (int d = 0; d < 3; ++d) {
+            if (WREG) {
+              tlo[d] = wlo[WREG ? dy * 3 + d : 0];
+              thi[d] = whi[WREG ? dy * 3 + d : 0];
+            } else {
+              const float4 w = w4[(dy * 3 + d) * 8];
+              tlo[d] = make_float2(w.x, w.y);
+              thi[d] = make_float2(w.z, w.w);
+            }
+          }
+#pragma unroll
+          for (int c = 0; c < NC; ++c) {
+            V alo, ahi;  // dy = 2: P -> finished output; dy = 1: R -> P; dy = 0: fresh R
+            if (dy == 2) { alo = Plo[c]; ahi = Phi[c]; }
+            if (dy == 1) { alo = Rlo[c]; ahi = Rhi[c]; }
+#pragma unroll
+            for (int d = 0; d < 3; ++d) {
+              const V lo = make_float2(v[c + d].x, v[c + d].y), hi = make_float2(v[c + d].z, v[c + d].w);
+              if (dy == 0 && d == 0) {
+                alo = fmul(lo, tlo[0]);
+                ahi = fmul(hi, thi[0]);
+              } else {
+                alo = ffma(lo, tlo[d], alo);
+                ahi = ffma(hi, thi[d], ahi);
+              }
+            }
+            if (dy == 2) {
+              if (ro >= 0 && x0 + c < W) {  // tf32 round-to-nearest: add half an ulp of the 10-bit mantissa
+                const int pp = pp0 + c;
+                const uint32_t a = abase + (uint32_t)((pp >> 3) * kGSboA + (pp & 7) * 16);
+                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(__float_as_uint(alo.x) + 0x1000u),
+                             "r"(__float_as_uint(alo.y) + 0x1000u), "r"(__float_as_uint(ahi.x) + 0x1000u),
+                             "r"(__float_as_uint(ahi.y) + 0x1000u)
+                             : "memory");
+              }
+            } else if (dy == 1) {
+              Plo[c] = alo; Phi[c] = ahi;
+            } else {
+              Rlo[c] = alo; Rhi[c] = ahi;
+            }
+          }
+        }
+      };
+      if (act) {
+        [&] {
+          int i = 0;
+          while (true) {  // PF + 1 row buffers in rotation: the loads run PF rows ahead of the arithmetic
+#pragma unroll
+            for (int r = 0; r <= PF; ++r) {
+              if (i + PF < nrows) load_row(i + PF, vbuf[(r + PF) % (PF + 1)]);
+              step(i, vbuf[r]);
+              if (++i >= nrows) return;
+            }
+          }
+        }();
+      }
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bFull + 8 * g);
+      while (epi_next < j) epilogue(epi_next++);
+    }
+    while (epi_next < my_tiles) epilogue(epi_next++);
+  } else {
+    // ---- issue warp: weight-chunk TMA ring, MMAs in item order, its own share of the drains ----
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(p.nhalf >> 3) << 17) | ((128u >> 4) << 24);
+    auto request_b = [&](int n, int kc) {  // weight chunk kc of item n into ring stage n % kWsBS
+      if (lane == 0) {
+        const uint32_t s = (uint32_t)(n % kWsBS);
+        mbar_expect_tx(bBfull + 8 * s, (uint32_t)bbytes);
+        tma_load_1d(smem_u32(sB + (size_t)s * bbytes), reinterpret_cast<const unsigned char*>(p.wimg) + (size_t)kc * bbytes,
+                    (uint32_t)bbytes, bBfull + 8 * s);
+      }
+      __syncwarp();
+    };
+    if (total > 0) request_b(0, 0);
+    if (total > 1) request_b(1, 1 % nch);
+    int j = 0, kc = 0;
+    for (int n = 0; n < total; ++n) {
+      const int g = n % kWsG, bs = n % kWsBS;
+      if (kc == 0 && j > 0) {  // tile boundary: the accumulator must be drained by all 16 warps before it is overwritten
+        epilogue(j - 1);
+        mbar_wait(bAccFree, (uint32_t)(j - 1) & 1u);
+      }
+      mbar_wait(bFull + 8 * g, (uint32_t)(n / kWsG) & 1u);
+      mbar_wait(bBfull + 8 * bs, (uint32_t)(n / kWsBS) & 1u);
+      tc_fence_after();
+      const uint32_t ab = smem_u32(sA + g * kGABytes), bb = smem_u32(sB + (size_t)bs * bbytes);
+#pragma unroll 1
+      for (int ks = 0; ks < kGKC / 8; ++ks)
+        for (int hf = 0; hf < p.nh; ++hf)
+          tc_mma_tf32_elect(tmem + (uint32_t)(hf * p.nhalf), umma_desc(ab + ks * 2u * kGLboA, kGLboA, kGSboA),
+                            umma_desc(bb + (uint32_t)(hf * (p.nhalf / 8)) * kGSbo + ks * 256u, 128u, kGSbo), idesc,
+                            (kc > 0 || ks > 0) ? 1u : 0u);
+      tc_commit_elect(bEmpty + 8 * g);
+      tc_commit_elect(bBempty + 8 * bs);
+      if (kc == nch - 1) tc_commit_elect(bAccFull);
+      if (n + 2 < total) {  // weights of item n + 2 go where item n - 1's were: wait until its MMAs have retired
+        if (n >= 1) mbar_wait(bBempty + 8 * ((n - 1) % kWsBS), (uint32_t)((n - 1) / kWsBS) & 1u);
+        request_b(n + 2, (kc + 2) % nch);
+      }
+      if (++kc == nch) {
+        kc = 0;
+        ++j;
+      }
+    }
+    if (my_tiles > 0) epilogue(my_tiles - 1);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0)
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((uint32_t)p.tmem_cols));
+}
+
 // border of a block output [B, Ho, Wo, C]: ReLU(pointwise bias)
 __global__ void border_fill_kernel(float* __restrict__ out, const float* __restrict__ relu_bias, long long B, int Ho,
                                    int Wo, int C) {
@@ -519,6 +825,17 @@ int launch_dscnn_gemm(kws_handle_t h, const float* feats_dev, int64_t B, int T, 
   KWS_CHECK_LAUNCH(h);
   float *cur = buf0, *nxt = buf1;
   int H = H1, W = W1;
+  // block layers: the warp-specialised kernel when its thread map (12 column groups of 2 or 3 columns) and its
+  // shared-memory rings fit, else the chunk-synchronous one (KWS_GEMM_WS=0 forces the latter, for A/B runs)
+  static const bool ws_env = [] { const char* e = std::getenv("KWS_GEMM_WS"); return !(e && e[0] == '0'); }();
+  const int nch_blk = (C + kGKC - 1) / kGKC;
+  const size_t smem_ws = (size_t)kWsG * kGABytes + (size_t)kWsBS * (g->npad / 8) * kGSbo + (size_t)9 * nch_blk * kGKC * 4 +
+                         (size_t)g->npad * 4;
+  const bool ws_fits = ws_env && smem_ws <= 227 * 1024;
+  if (ws_fits) {
+    if (int rc = ensure_dyn_smem(dscnn_block_ws_kernel<2, 2, true>, smem_ws)) return rc;
+    if (int rc = ensure_dyn_smem(dscnn_block_ws_kernel<3, 1, false>, smem_ws)) return rc;
+  }
   for (int l = 0; l < nb; ++l) {
     p.in = cur;
     p.out = nxt;
@@ -527,18 +844,36 @@ int launch_dscnn_gemm(kws_handle_t h, const float* feats_dev, int64_t B, int T, 
     p.bias = g->d_bias + (size_t)(l + 1) * C;
     p.kvalid = g->kvalid[l + 1];
     p.nchunks = g->nchunks[l + 1];
-    const unsigned grid = set_grid(H, W);
+    unsigned grid = set_grid(H, W);
+    bool ws = ws_fits && W <= 36;
+    if (ws) {  // tile = as many whole rows as fit 128 pixels; one persistent CTA per SM
+      p.R = 128 / W < H ? 128 / W : H;
+      p.nbands = (H + p.R - 1) / p.R;
+      const long long t = B * p.nbands;
+      if (t * p.nchunks >= 0x7fffffffLL) {
+        ws = false;
+        grid = set_grid(H, W);
+      } else {
+        grid = (unsigned)(t < h->sm_count ? t : h->sm_count);
+      }
+    }
+    const int pool_rows = ws ? 4 * p.nbands + 1 : p.nbands + 1;
+    auto launch_block = [&]() {
+      if (!ws) dscnn_gemm_kernel<1><<<grid, kGT, smem_bytes, st>>>(p);
+      else if (W <= 24) dscnn_block_ws_kernel<2, 2, true><<<grid, kGT, smem_ws, st>>>(p);
+      else dscnn_block_ws_kernel<3, 1, false><<<grid, kGT, smem_ws, st>>>(p);
+    };
     if (l == nb - 1) {  // the pooled rows replace the last activation (see GemmParams::pool)
       p.pool = nxt;
       p.border = g->d_border + (size_t)l * C;
-      p.pool_scale = (float)(p.nbands + 1) / (float)((H + 2) * (W + 2));
-      dscnn_gemm_kernel<1><<<grid, kGT, smem_bytes, st>>>(p);
+      p.pool_scale = (float)pool_rows / (float)((H + 2) * (W + 2));
+      launch_block();
       KWS_CHECK_LAUNCH(h);
       *last_out = nxt;
-      *last_rows = p.nbands + 1;
+      *last_rows = pool_rows;
       return 1;
     }
-    dscnn_gemm_kernel<1><<<grid, kGT, smem_bytes, st>>>(p);
+    launch_block();
     KWS_CHECK_LAUNCH(h);
     const long long nborder = B * (long long)(2 * (W + 2) + 2 * H) * (C / 4);
     long long gb = (nborder + 255) / 256;
