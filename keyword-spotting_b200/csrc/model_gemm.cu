@@ -425,69 +425,94 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
 
   // drain of tile j's accumulator by this warp: TMEM lane quarter warp % 4 (lane = pixel of the tile), column
   // quarter warp / 4; bias + ReLU -> NHWC store at the padded position, or (last block) per-(tile, lane quarter)
-  // channel sums into the pool rows
+  // channel sums into the pool rows.  The loads use the 16-lane x 256-bit shape: a thread gets rows lane/4 and
+  // lane/4 + 8 of the 16-lane half and columns 2 (lane % 4) + {0, 1} of every 8-column block, so the four threads
+  // of a quad hold 8 consecutive channels of one pixel; after one exchange between neighbouring lanes each of them
+  // stores 16 bytes of a 64-byte run per pixel (the 32x32b shape -- one pixel per thread -- made every store
+  // instruction touch 32 different 1104-byte-strided lines, 16 bytes each: 30 % of the kernel's L1 cycles).
   auto epilogue = [&](int j) {
     mbar_wait(bAccFull, (uint32_t)j & 1u);
     tc_fence_after();
     const unsigned tile = blockIdx.x + (unsigned)j * gridDim.x, b = tile / (unsigned)p.nbands;
     const int band = (int)(tile - b * (unsigned)p.nbands), r0 = band * R;
-    const int lq = warp & 3, cs = warp >> 2;
-    const int pp = lq * 32 + lane, rl = pp / W, xq = pp - rl * W, y = r0 + rl;
-    const bool valid = rl < R && y < H;
+    const int lq = warp & 3, cs = warp >> 2, tq = lane & 3, tr = lane >> 2;
     const int ncol = p.npad >> 2, c0 = cs * ncol;
-    const uint32_t ta = tmem + ((uint32_t)(lq * 32) << 16) + (uint32_t)c0;
-    float* orow = p.out + (((long long)b * (H + 2) + y + 1) * (W + 2) + xq + 1) * (long long)C;
-    float* prow = p.pool ? p.pool + ((long long)b * (4 * p.nbands + 1) + band * 4 + lq) * (long long)C : nullptr;
-    auto emit = [&](float (&v)[8], int c) {
-      const float4 b0 = *reinterpret_cast<const float4*>(sBias + c), b1 = *reinterpret_cast<const float4*>(sBias + c + 4);
-      v[0] = fmaxf(v[0] + b0.x, 0.f); v[1] = fmaxf(v[1] + b0.y, 0.f); v[2] = fmaxf(v[2] + b0.z, 0.f); v[3] = fmaxf(v[3] + b0.w, 0.f);
-      v[4] = fmaxf(v[4] + b1.x, 0.f); v[5] = fmaxf(v[5] + b1.y, 0.f); v[6] = fmaxf(v[6] + b1.z, 0.f); v[7] = fmaxf(v[7] + b1.w, 0.f);
-      if (prow == nullptr) {
-        if (valid) {
-          if (c < C) *reinterpret_cast<float4*>(orow + c) = make_float4(v[0], v[1], v[2], v[3]);
-          if (c + 4 < C) *reinterpret_cast<float4*>(orow + c + 4) = make_float4(v[4], v[5], v[6], v[7]);
-        }
-      } else {
-        // channel sums over the warp's 32 pixels: halving butterfly (4 + 2 + 1 + 1 + 1 shuffles for 8 values, fixed
-        // order); lane l ends up with the sum of value (l >> 2) & 7
+    const bool pool = p.pool != nullptr, odd = lane & 1;
+    float* orow[2][2];
+    bool valid[2][2];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) v[e] = valid ? v[e] : 0.f;
-        const bool h16 = lane & 16, h8 = lane & 8, h4 = lane & 4;
+    for (int hh = 0; hh < 2; ++hh)
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const float keep = h16 ? v[e + 4] : v[e], send = h16 ? v[e] : v[e + 4];
-          v[e] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
-        }
-#pragma unroll
-        for (int e = 0; e < 2; ++e) {
-          const float keep = h8 ? v[e + 2] : v[e], send = h8 ? v[e] : v[e + 2];
-          v[e] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
-        }
-        {
-          const float keep = h4 ? v[1] : v[0], send = h4 ? v[0] : v[1];
-          v[0] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
-        }
-        v[0] += __shfl_xor_sync(0xffffffffu, v[0], 2);
-        v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
-        const int cc = c + ((lane >> 2) & 7);
-        if ((lane & 3) == 0 && cc < C) prow[cc] = v[0] * p.pool_scale;
+      for (int ss = 0; ss < 2; ++ss) {
+        const int pp = lq * 32 + hh * 16 + ss * 8 + tr, rl = pp / W, xq = pp - rl * W, y = r0 + rl;
+        valid[hh][ss] = rl < R && y < H;
+        orow[hh][ss] = p.out + (((long long)b * (H + 2) + y + 1) * (W + 2) + xq + 1) * (long long)C;
       }
-    };
-    for (int c = 0; c < ncol; c += 16) {
-      float v0[8], v1[8];
-      const bool two = c + 8 < ncol;
-      tc_ld8(ta + (uint32_t)c, v0);
-      if (two) tc_ld8(ta + (uint32_t)c + 8u, v1);
+    float* prow = pool ? p.pool + ((long long)b * (4 * p.nbands + 1) + band * 4 + lq) * (long long)C : nullptr;
+    const uint32_t ta = tmem + ((uint32_t)(lq * 32) << 16) + (uint32_t)c0;
+    for (int cb = 0; cb < ncol; cb += 16) {
+      const bool two = cb + 8 < ncol;  // a pair of 8-column blocks, or the last single block
+      float v[2][8];
+#pragma unroll
+      for (int hh = 0; hh < 2; ++hh) {
+        const uint32_t t2 = ta + ((uint32_t)(hh * 16) << 16) + (uint32_t)cb;
+        if (two) {
+          tc_ld_16x256b_x2(t2, v[hh]);
+        } else {
+          tc_ld_16x256b_x1(t2, v[hh]);
+          v[hh][4] = v[hh][5] = v[hh][6] = v[hh][7] = 0.f;
+        }
+      }
       tc_wait_ld();
-      if (c + 16 >= ncol) {  // every value of the accumulator this warp needs is in registers: release it
+      if (cb + 16 >= ncol) {  // every value of the accumulator this warp needs is in registers: release it
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(bAccFree);
       }
-      emit(v0, c0 + c);
-      if (two) emit(v1, c0 + c + 8);
+      const int col = c0 + cb + 2 * tq;  // channel of register e = 0 of block 0 (block 1: + 8)
+      const float2 bz0 = *reinterpret_cast<const float2*>(sBias + col);
+      const float2 bz1 = two ? *reinterpret_cast<const float2*>(sBias + col + 8) : make_float2(0.f, 0.f);
+#pragma unroll
+      for (int hh = 0; hh < 2; ++hh)
+#pragma unroll
+        for (int ss = 0; ss < 2; ++ss) {
+          float* x = v[hh] + 2 * ss;  // registers [4 blk + 2 s + e]
+          x[0] = fmaxf(x[0] + bz0.x, 0.f);
+          x[1] = fmaxf(x[1] + bz0.y, 0.f);
+          x[4] = fmaxf(x[4] + bz1.x, 0.f);
+          x[5] = fmaxf(x[5] + bz1.y, 0.f);
+        }
+      if (!pool) {
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh)
+#pragma unroll
+          for (int ss = 0; ss < 2; ++ss) {
+            const float* x = v[hh] + 2 * ss;
+            if (two) {  // even lanes keep block 0 and take the neighbour's block 0, odd lanes likewise with block 1
+              const float k0 = odd ? x[4] : x[0], k1 = odd ? x[5] : x[1], s0 = odd ? x[0] : x[4], s1 = odd ? x[1] : x[5];
+              const float g0 = __shfl_xor_sync(0xffffffffu, s0, 1), g1 = __shfl_xor_sync(0xffffffffu, s1, 1);
+              const int cc = c0 + cb + (odd ? 8 + 2 * (tq - 1) : 2 * tq);
+              if (valid[hh][ss] && cc < C)
+                *reinterpret_cast<float4*>(orow[hh][ss] + cc) = odd ? make_float4(g0, g1, k0, k1) : make_float4(k0, k1, g0, g1);
+            } else if (valid[hh][ss] && col < C) {
+              *reinterpret_cast<float2*>(orow[hh][ss] + col) = make_float2(x[0], x[1]);
+            }
+          }
+      } else {  // channel sums over the warp's 32 pixels in a fixed order: 4 in the thread, then lanes 4, 8, 16 apart
+#pragma unroll
+        for (int be = 0; be < 4; ++be) {  // be = 2 blk + e
+          const int r = 4 * (be >> 1) + (be & 1);
+          float sum = ((valid[0][0] ? v[0][r] : 0.f) + (valid[0][1] ? v[0][r + 2] : 0.f)) +
+                      ((valid[1][0] ? v[1][r] : 0.f) + (valid[1][1] ? v[1][r + 2] : 0.f));
+          sum += __shfl_xor_sync(0xffffffffu, sum, 4);
+          sum += __shfl_xor_sync(0xffffffffu, sum, 8);
+          sum += __shfl_xor_sync(0xffffffffu, sum, 16);
+          const int cc = col + 8 * (be >> 1) + (be & 1);
+          if (tr == 0 && (two || be < 2) && cc < C) prow[cc] = sum * p.pool_scale;
+        }
+      }
     }
-    if (prow != nullptr && band == 0 && lq == 0)  // one extra row per clip: the 2 (W + 2) + 2 H border pixels, all ReLU(bias)
+    if (pool && band == 0 && lq == 0)  // one extra row per clip: the 2 (W + 2) + 2 H border pixels, all ReLU(bias)
       for (int c = c0 + lane; c < c0 + ncol && c < C; c += 32)
         p.pool[((long long)b * (4 * p.nbands + 1) + 4 * p.nbands) * (long long)C + c] =
             (float)(2 * (W + 2) + 2 * H) * __ldg(p.border + c) * p.pool_scale;
@@ -620,14 +645,34 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
       }
       __syncwarp();
     };
+    // The whole input patch of a tile (rows r0 - 1 .. r0 + R of one clip, all channels) is one contiguous range:
+    // pulled into L2 one tile ahead by bulk prefetches, one per row, so that the producers' register loads (two
+    // rows ahead of their arithmetic, which hides L2 latency but not DRAM latency under load) hit L2.
+    auto prefetch_tile = [&](int jj) {
+      if (jj < my_tiles) {
+        const unsigned tile = blockIdx.x + (unsigned)jj * gridDim.x, b = tile / (unsigned)p.nbands;
+        const int r0 = (int)(tile - b * (unsigned)p.nbands) * R;
+        const int y0 = r0 > 0 ? r0 - 1 : 0, y1 = r0 + R < H ? r0 + R : H - 1;
+        const uint32_t bytes = (uint32_t)(W * C * 4);
+        for (int y = y0 + lane; y <= y1; y += 32)
+          asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p.in + ((long long)b * H + y) * W * (long long)C), "r"(bytes)
+                       : "memory");
+      }
+      __syncwarp();
+    };
+    prefetch_tile(0);
+    prefetch_tile(1);
     if (total > 0) request_b(0, 0);
     if (total > 1) request_b(1, 1 % nch);
     int j = 0, kc = 0;
     for (int n = 0; n < total; ++n) {
       const int g = n % kWsG, bs = n % kWsBS;
-      if (kc == 0 && j > 0) {  // tile boundary: the accumulator must be drained by all 16 warps before it is overwritten
-        epilogue(j - 1);
-        mbar_wait(bAccFree, (uint32_t)(j - 1) & 1u);
+      if (kc == 0) {
+        if (j > 0) prefetch_tile(j + 1);
+        if (j > 0) {  // tile boundary: the accumulator must be drained by all 16 warps before it is overwritten
+          epilogue(j - 1);
+          mbar_wait(bAccFree, (uint32_t)(j - 1) & 1u);
+        }
       }
       mbar_wait(bFull + 8 * g, (uint32_t)(n / kWsG) & 1u);
       mbar_wait(bBfull + 8 * bs, (uint32_t)(n / kWsBS) & 1u);
