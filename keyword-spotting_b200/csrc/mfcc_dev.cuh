@@ -125,7 +125,7 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
 }
 // same, for a warp that expects to wait long (service warp): back off between probes so the
 // polling does not take issue slots from the compute warps
-__device__ __forceinline__ void mbar_wait_idle(uint32_t bar, uint32_t parity) {
+__device__ __forceinline__ void mbar_wait_idle(uint32_t bar, uint32_t parity, unsigned ns = 256) {
   uint32_t done = 0;
 #pragma unroll 1
   for (int spin = 0; spin < (1 << 22); ++spin) {
@@ -137,7 +137,7 @@ __device__ __forceinline__ void mbar_wait_idle(uint32_t bar, uint32_t parity) {
         : "r"(bar), "r"(parity)
         : "memory");
     if (done) return;
-    __nanosleep(256);
+    __nanosleep(ns);
   }
   __trap();
 }

@@ -44,6 +44,8 @@ struct GemmParams {
   // activation of the network is never written or re-read
   float* pool;           // [B][nbands + 1][C] or null
   const float* border;   // [C] ReLU(pointwise bias): value of every border pixel of the padded output
+  const float* zero_row; // [W][C] zeros (warp-specialised kernel: input rows outside the clip)
+  float* dump;           // [npad] write-only scratch row: where lanes of a tile without a pixel store
   float pool_scale;      // (nbands + 1) / ((H + 2) * (W + 2))
 };
 
@@ -358,7 +360,7 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_gemm_kernel(const GemmParams p) 
 // One depthwise-separable block (depthwise 3x3 -> pointwise 1x1 -> bias -> ReLU) as an asynchronous pipeline; the
 // chunk-synchronous kernel above stays for conv1 (MODE 0) and for shapes outside this one's thread map.
 //
-// What bounds the block layers is the shared-memory / L1 data path, not the tensor core: a tf32 MMA of
+// What bounds the block layers is the data path around the tensor core, not the tensor core: a tf32 MMA of
 // M = 128, N = 144, K = 8 reads 8.6 KB of operands for 72 cycles of math, the weight chunks are written once and
 // read once per 128 pixels, and the chunk-synchronous kernel on top of that staged every input patch in shared
 // memory and read each element five times from there, with all 16 warps meeting at a CTA barrier per K chunk
@@ -367,16 +369,31 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_gemm_kernel(const GemmParams p) 
 //     walks DOWN the rows with the 3x3 window in registers -- one 16-byte global load per input pixel and channel
 //     quad (NC + 2 per row, L1 catches the neighbour thread's overlap), each input row updates the three output
 //     rows it touches (out = P + w2.v, P = R + w1.v, R = w0.v), so nothing is read twice and nothing is exchanged;
-//   * five producer groups of 3 warps work on five DIFFERENT K chunks at the same time; group g owns A-ring stage g
+//     out-of-range columns load a clamped (valid) address and are zeroed by a 0/1 multiply when used, rows outside
+//     the clip take a warp-uniform branch: no per-load predicates or address selects in the row loop;
+//   * four producer groups of 3 warps work on four DIFFERENT K chunks at the same time; group g owns A-ring stage g
 //     (full / empty mbarriers, tcgen05.commit releases a stage), so there is no CTA-wide barrier anywhere;
-//   * the issue warp streams the weight chunks through a 3-stage TMA ring and fires the chunk's MMAs in order;
-//   * one accumulator (N = 288 columns of the 512): its drain is spread over all 16 warps (lane quarter x column
-//     quarter) and placed where the ring is full anyway -- a warp drains tile t right after it has produced its
-//     first chunk of tile t + 1, so the MMAs of the next tile are already queued when the accumulator frees up.
-constexpr int kWsG = 5;     // producer groups = A-ring stages
+//   * the issue warp streams the weight chunks through a 3-stage TMA ring, fires the chunk's MMAs in order, and
+//     pulls the next tile's whole input patch (one contiguous range) into L2 with bulk prefetches;
+//   * one accumulator (N = 288 columns of the 512), drained by warps 12..15, one TMEM lane quarter each (the issue
+//     warp takes the fourth: it has nothing to issue while the accumulator is busy).  The producers never touch the
+//     accumulator, so they run up to four chunks ahead into the next tile while it drains, and the MMAs catch up
+//     afterwards (a chunk multiplies faster than it is produced).
+constexpr int kWsG = 4;     // producer groups = A-ring stages
 constexpr int kWsGT = 96;   // threads per group: 8 channel quads x 12 column groups
 constexpr int kWsBS = 3;    // weight-chunk ring stages
+constexpr int kWsEpi = 4;   // draining warps: 12, 13, 14 and the issue warp 15 (TMEM lane quarter = warp % 4)
 
+#ifdef KWS_WS_PROFILE
+#include <cstdio>
+#define WSP_DECL(n) long long wsp_##n = 0
+#define WSP_T0() const long long wsp_t0 = clock64()
+#define WSP_ADD(n) wsp_##n += clock64() - wsp_t0
+#else
+#define WSP_DECL(n)
+#define WSP_T0()
+#define WSP_ADD(n)
+#endif
 template <int NC, int PF, bool WREG>
 __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams p) {
   extern __shared__ __align__(128) unsigned char smem[];
@@ -401,7 +418,7 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
       mbar_init(bBempty + 8 * s, 1);
     }
     mbar_init(bAccFull, 1);
-    mbar_init(bAccFree, kGT / 32);
+    mbar_init(bAccFree, kWsEpi);
     fence_mbar_init();
   }
   if (warp == 0) {
@@ -414,6 +431,10 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
     sW[i] = k < p.C ? __ldg(p.dw_w + t * p.C + k) : 0.f;
   }
   for (int i = tid; i < p.npad; i += kGT) sBias[i] = i < p.C ? __ldg(p.bias + i) : 0.f;
+  // A ring starts as zeros: rows no pixel owns and channel quads past the channel count are never written, and
+  // what the MMA reads there must be finite (it meets zero weight rows, or lands in accumulator rows nobody reads)
+  for (int i = tid; i < kWsG * kGABytes / 16; i += kGT) reinterpret_cast<float4*>(sA)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  fence_proxy_async();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -423,21 +444,23 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
   const int my_tiles = blockIdx.x < ntiles ? (int)((ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x) : 0;
   const int total = my_tiles * nch;  // work items (tile, K chunk) of this CTA, in issue order
 
-  // drain of tile j's accumulator by this warp: TMEM lane quarter warp % 4 (lane = pixel of the tile), column
-  // quarter warp / 4; bias + ReLU -> NHWC store at the padded position, or (last block) per-(tile, lane quarter)
-  // channel sums into the pool rows.  The loads use the 16-lane x 256-bit shape: a thread gets rows lane/4 and
-  // lane/4 + 8 of the 16-lane half and columns 2 (lane % 4) + {0, 1} of every 8-column block, so the four threads
-  // of a quad hold 8 consecutive channels of one pixel; after one exchange between neighbouring lanes each of them
-  // stores 16 bytes of a 64-byte run per pixel (the 32x32b shape -- one pixel per thread -- made every store
-  // instruction touch 32 different 1104-byte-strided lines, 16 bytes each: 30 % of the kernel's L1 cycles).
+  // drain of tile j's accumulator by this warp: all columns of TMEM lane quarter warp % 4 (lane = pixel of the
+  // tile); bias + ReLU -> NHWC store at the padded position, or (last block) per-(tile, lane quarter) channel sums
+  // into the pool rows.  The loads use the 16-lane x 256-bit shape: a thread gets rows lane/4 and lane/4 + 8 of
+  // the 16-lane half and columns 2 (lane % 4) + {0, 1} of every 8-column block, so the four threads of a quad hold
+  // 8 consecutive channels of one pixel; after one exchange between neighbouring lanes each of them stores 16
+  // bytes of a 64-byte run per pixel (the 32x32b shape -- one pixel per thread -- made every store instruction
+  // touch 32 different 1104-byte-strided lines, 16 bytes each: 30 % of the kernel's L1 cycles).
   auto epilogue = [&](int j) {
-    mbar_wait(bAccFull, (uint32_t)j & 1u);
+    mbar_wait_idle(bAccFull, (uint32_t)j & 1u, 32);
     tc_fence_after();
     const unsigned tile = blockIdx.x + (unsigned)j * gridDim.x, b = tile / (unsigned)p.nbands;
     const int band = (int)(tile - b * (unsigned)p.nbands), r0 = band * R;
-    const int lq = warp & 3, cs = warp >> 2, tq = lane & 3, tr = lane >> 2;
-    const int ncol = p.npad >> 2, c0 = cs * ncol;
+    const int lq = warp & 3, tq = lane & 3, tr = lane >> 2;
     const bool pool = p.pool != nullptr, odd = lane & 1;
+    // this thread's four pixels (16-lane half hh, row block ss); a lane without a pixel stores into a dump row, so
+    // that the stores of all rounds but the last need no predicate
+    const int coff = odd ? 8 + 2 * (tq - 1) : 2 * tq;  // first of this lane's four channels within a 16-channel pair
     float* orow[2][2];
     bool valid[2][2];
 #pragma unroll
@@ -446,74 +469,104 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
       for (int ss = 0; ss < 2; ++ss) {
         const int pp = lq * 32 + hh * 16 + ss * 8 + tr, rl = pp / W, xq = pp - rl * W, y = r0 + rl;
         valid[hh][ss] = rl < R && y < H;
-        orow[hh][ss] = p.out + (((long long)b * (H + 2) + y + 1) * (W + 2) + xq + 1) * (long long)C;
+        orow[hh][ss] = (valid[hh][ss] ? p.out + (((long long)b * (H + 2) + y + 1) * (W + 2) + xq + 1) * (long long)C : p.dump) + coff;
       }
     float* prow = pool ? p.pool + ((long long)b * (4 * p.nbands + 1) + band * 4 + lq) * (long long)C : nullptr;
-    const uint32_t ta = tmem + ((uint32_t)(lq * 32) << 16) + (uint32_t)c0;
-    for (int cb = 0; cb < ncol; cb += 16) {
-      const bool two = cb + 8 < ncol;  // a pair of 8-column blocks, or the last single block
-      float v[2][8];
+    const uint32_t ta = tmem + ((uint32_t)(lq * 32) << 16);
+    // 16-lane halves without a pixel (the tile's last rows of TMEM lanes, short last bands) are neither loaded nor stored
+    const int npix = min(R, H - r0) * W;
+    const bool hv0 = lq * 32 < npix, hv1 = lq * 32 + 16 < npix;
+    auto load_round = [&](float (&v)[2][2][8], int cb) {  // two pairs of 8-column blocks x two 16-lane halves
 #pragma unroll
-      for (int hh = 0; hh < 2; ++hh) {
-        const uint32_t t2 = ta + ((uint32_t)(hh * 16) << 16) + (uint32_t)cb;
-        if (two) {
-          tc_ld_16x256b_x2(t2, v[hh]);
-        } else {
-          tc_ld_16x256b_x1(t2, v[hh]);
-          v[hh][4] = v[hh][5] = v[hh][6] = v[hh][7] = 0.f;
-        }
+      for (int pr = 0; pr < 2; ++pr) {
+        if (hv0) tc_ld_16x256b_x2(ta + (uint32_t)(cb + 16 * pr), v[pr][0]);
+        if (hv1) tc_ld_16x256b_x2(ta + (16u << 16) + (uint32_t)(cb + 16 * pr), v[pr][1]);
       }
-      tc_wait_ld();
-      if (cb + 16 >= ncol) {  // every value of the accumulator this warp needs is in registers: release it
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(bAccFree);
-      }
-      const int col = c0 + cb + 2 * tq;  // channel of register e = 0 of block 0 (block 1: + 8)
-      const float2 bz0 = *reinterpret_cast<const float2*>(sBias + col);
-      const float2 bz1 = two ? *reinterpret_cast<const float2*>(sBias + col + 8) : make_float2(0.f, 0.f);
+    };
+    auto release = [&]() {  // the whole lane quarter is in registers: the accumulator may be overwritten
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bAccFree);
+    };
+    auto process = [&](float (&v)[2][2][8], int cb, const bool guard) {
 #pragma unroll
-      for (int hh = 0; hh < 2; ++hh)
-#pragma unroll
-        for (int ss = 0; ss < 2; ++ss) {
-          float* x = v[hh] + 2 * ss;  // registers [4 blk + 2 s + e]
-          x[0] = fmaxf(x[0] + bz0.x, 0.f);
-          x[1] = fmaxf(x[1] + bz0.y, 0.f);
-          x[4] = fmaxf(x[4] + bz1.x, 0.f);
-          x[5] = fmaxf(x[5] + bz1.y, 0.f);
-        }
-      if (!pool) {
+      for (int pr = 0; pr < 2; ++pr) {
+        const int col = cb + 16 * pr + 2 * tq;  // channel of register e = 0 of block 0 (block 1: + 8)
+        const float2 bz0 = *reinterpret_cast<const float2*>(sBias + col), bz1 = *reinterpret_cast<const float2*>(sBias + col + 8);
 #pragma unroll
         for (int hh = 0; hh < 2; ++hh)
 #pragma unroll
           for (int ss = 0; ss < 2; ++ss) {
-            const float* x = v[hh] + 2 * ss;
-            if (two) {  // even lanes keep block 0 and take the neighbour's block 0, odd lanes likewise with block 1
-              const float k0 = odd ? x[4] : x[0], k1 = odd ? x[5] : x[1], s0 = odd ? x[0] : x[4], s1 = odd ? x[1] : x[5];
-              const float g0 = __shfl_xor_sync(0xffffffffu, s0, 1), g1 = __shfl_xor_sync(0xffffffffu, s1, 1);
-              const int cc = c0 + cb + (odd ? 8 + 2 * (tq - 1) : 2 * tq);
-              if (valid[hh][ss] && cc < C)
-                *reinterpret_cast<float4*>(orow[hh][ss] + cc) = odd ? make_float4(g0, g1, k0, k1) : make_float4(k0, k1, g0, g1);
-            } else if (valid[hh][ss] && col < C) {
-              *reinterpret_cast<float2*>(orow[hh][ss] + col) = make_float2(x[0], x[1]);
+            float* x = v[pr][hh] + 2 * ss;  // registers [4 blk + 2 s + e]
+            x[0] = fmaxf(x[0] + bz0.x, 0.f);
+            x[1] = fmaxf(x[1] + bz0.y, 0.f);
+            x[4] = fmaxf(x[4] + bz1.x, 0.f);
+            x[5] = fmaxf(x[5] + bz1.y, 0.f);
+          }
+        if (!pool) {
+          const bool cok = !guard || cb + 16 * pr + coff < C;
+#pragma unroll
+          for (int hh = 0; hh < 2; ++hh) {
+            if (hh == 0 ? hv0 : hv1) {
+#pragma unroll
+              for (int ss = 0; ss < 2; ++ss) {  // even lanes keep block 0 and take the neighbour's, odd lanes block 1
+                const float* x = v[pr][hh] + 2 * ss;
+                const float k0 = odd ? x[4] : x[0], k1 = odd ? x[5] : x[1], s0 = odd ? x[0] : x[4], s1 = odd ? x[1] : x[5];
+                const float g0 = __shfl_xor_sync(0xffffffffu, s0, 1), g1 = __shfl_xor_sync(0xffffffffu, s1, 1);
+                const float4 o = odd ? make_float4(g0, g1, k0, k1) : make_float4(k0, k1, g0, g1);
+                if (!guard) *reinterpret_cast<float4*>(orow[hh][ss] + 16 * pr) = o;
+                else if (cok) *reinterpret_cast<float4*>(orow[hh][ss] + 16 * pr) = o;
+              }
             }
           }
-      } else {  // channel sums over the warp's 32 pixels in a fixed order: 4 in the thread, then lanes 4, 8, 16 apart
+        } else {  // channel sums over the warp's 32 pixels in a fixed order: 4 in the thread, then lanes 4, 8, 16 apart
 #pragma unroll
-        for (int be = 0; be < 4; ++be) {  // be = 2 blk + e
-          const int r = 4 * (be >> 1) + (be & 1);
-          float sum = ((valid[0][0] ? v[0][r] : 0.f) + (valid[0][1] ? v[0][r + 2] : 0.f)) +
-                      ((valid[1][0] ? v[1][r] : 0.f) + (valid[1][1] ? v[1][r + 2] : 0.f));
-          sum += __shfl_xor_sync(0xffffffffu, sum, 4);
-          sum += __shfl_xor_sync(0xffffffffu, sum, 8);
-          sum += __shfl_xor_sync(0xffffffffu, sum, 16);
-          const int cc = col + 8 * (be >> 1) + (be & 1);
-          if (tr == 0 && (two || be < 2) && cc < C) prow[cc] = sum * p.pool_scale;
+          for (int be = 0; be < 4; ++be) {  // be = 2 blk + e
+            const int r = 4 * (be >> 1) + (be & 1);
+            float sum = ((valid[0][0] ? v[pr][0][r] : 0.f) + (valid[0][1] ? v[pr][0][r + 2] : 0.f)) +
+                        ((valid[1][0] ? v[pr][1][r] : 0.f) + (valid[1][1] ? v[pr][1][r + 2] : 0.f));
+            sum += __shfl_xor_sync(0xffffffffu, sum, 4);
+            sum += __shfl_xor_sync(0xffffffffu, sum, 8);
+            sum += __shfl_xor_sync(0xffffffffu, sum, 16);
+            const int c1 = col + 8 * (be >> 1) + (be & 1);
+            if (tr == 0 && c1 < C) prow[c1] = sum * p.pool_scale;
+          }
         }
+      }
+#pragma unroll
+      for (int hh = 0; hh < 2; ++hh)
+#pragma unroll
+        for (int ss = 0; ss < 2; ++ss) orow[hh][ss] += 32;
+    };
+    if (!hv0 && !pool) {  // nothing of this tile lives in this lane quarter
+      release();
+    } else {  // two register sets in rotation: the next round's TMEM loads are in flight while a round is stored
+      float va[2][2][8], vb[2][2][8];
+      load_round(va, 0);
+      int cb = 0;
+      for (; cb + 64 < p.npad; cb += 64) {
+        tc_wait_ld();
+        load_round(vb, cb + 32);
+        process(va, cb, false);
+        tc_wait_ld();
+        load_round(va, cb + 64);
+        process(vb, cb + 32, false);
+      }
+      if (cb + 32 < p.npad) {
+        tc_wait_ld();
+        load_round(vb, cb + 32);
+        process(va, cb, false);
+        tc_wait_ld();
+        release();
+        process(vb, cb + 32, true);
+      } else {
+        tc_wait_ld();
+        release();
+        process(va, cb, true);
       }
     }
     if (pool && band == 0 && lq == 0)  // one extra row per clip: the 2 (W + 2) + 2 H border pixels, all ReLU(bias)
-      for (int c = c0 + lane; c < c0 + ncol && c < C; c += 32)
+      for (int c = lane; c < C; c += 32)
         p.pool[((long long)b * (4 * p.nbands + 1) + 4 * p.nbands) * (long long)C + c] =
             (float)(2 * (W + 2) + 2 * H) * __ldg(p.border + c) * p.pool_scale;
   };
@@ -522,105 +575,131 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
     // ---- producers ----
     const int g = warp / 3, gt = tid - g * kWsGT;
     const int q = gt & 7, cg = gt >> 3, x0 = cg * NC;
-    const bool act = x0 < W;
     const uint32_t abase = smem_u32(sA + g * kGABytes) + (uint32_t)(q * kGLboA);
-    bool cv[NC + 2];
+    // column c of the window = input column x0 - 1 + c: byte offset within a row (clamped into the row) and 0/1 mask
+    int coff[NC + 2];
+    V cm[NC + 2];
 #pragma unroll
-    for (int c = 0; c < NC + 2; ++c) cv[c] = act && x0 - 1 + c >= 0 && x0 - 1 + c < W;
-    const long long rowstride = (long long)W * C;
-    int epi_next = 0;
+    for (int c = 0; c < NC + 2; ++c) {
+      const int xx = x0 - 1 + c, xc = xx < 0 ? 0 : (xx >= W ? W - 1 : xx);
+      coff[c] = xc * C * 4;
+      cm[c] = fsplat(xx == xc ? 1.f : 0.f);
+    }
+    const long long rowbytes = (long long)W * C * 4;
     uint32_t k = 0;
+    WSP_DECL(pw);
+#ifdef KWS_WS_PROFILE
+    const long long wsp_start = clock64();
+#endif
     for (int n = g; n < total; n += kWsG, ++k) {
       const int j = n / nch, kc = n - j * nch;
       const unsigned tile = blockIdx.x + (unsigned)j * gridDim.x, b = tile / (unsigned)p.nbands;
       const int band = (int)(tile - b * (unsigned)p.nbands), r0 = band * R;
       const int nrows = min(R, H - r0) + 2;  // input rows r0 - 1 .. of the band (rows outside the clip are zeros)
       const int kq = kc * kGKC + 4 * q;
-      const bool kok = kq < C;
-      const float* src = p.in + (((long long)b * H + r0 - 1) * W + (x0 - 1)) * (long long)C + kq;
-      auto load_row = [&](int i, float4 (&v)[NC + 2]) {
-        const int y = r0 - 1 + i;
-        const bool rok = kok && y >= 0 && y < H;
-        const float* s = src + (long long)i * rowstride;
+      const bool act = x0 < W && kq < C;
+      // next row to load: row r0 - 1 of the clip, channel kq (the pointer may run outside the clip: never read there)
+      const char* rp = reinterpret_cast<const char*>(p.in + ((long long)b * H + r0 - 1) * W * (long long)C + kq);
+      int ynext = r0 - 1;
+      const char* zr = reinterpret_cast<const char*>(p.zero_row + kq);  // a row of zeros stands in for rows outside the clip
+      auto load_row = [&](float4 (&v)[NC + 2]) {
+        const char* r = (ynext >= 0 && ynext < H) ? rp : zr;
 #pragma unroll
-        for (int c = 0; c < NC + 2; ++c)
-          v[c] = (rok && cv[c]) ? __ldg(reinterpret_cast<const float4*>(s + (long long)c * C)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int c = 0; c < NC + 2; ++c) v[c] = __ldg(reinterpret_cast<const float4*>(r + coff[c]));
+        rp += rowbytes;
+        ++ynext;
       };
       float4 vbuf[PF + 1][NC + 2];
-#pragma unroll
-      for (int r = 0; r < PF; ++r) load_row(r, vbuf[r]);
       const float4* w4 = reinterpret_cast<const float4*>(sW + kc * 9 * kGKC + 4 * q);
       V wlo[WREG ? 9 : 1], whi[WREG ? 9 : 1];
-      if (WREG) {
+      if (act) {
 #pragma unroll
-        for (int t = 0; t < (WREG ? 9 : 1); ++t) {
-          const float4 w = w4[t * 8];
-          wlo[t] = make_float2(w.x, w.y);
-          whi[t] = make_float2(w.z, w.w);
+        for (int r = 0; r < PF; ++r) load_row(vbuf[r]);
+        if (WREG) {
+#pragma unroll
+          for (int t = 0; t < (WREG ? 9 : 1); ++t) {
+            const float4 w = w4[t * 8];
+            wlo[t] = make_float2(w.x, w.y);
+            whi[t] = make_float2(w.z, w.w);
+          }
         }
       }
-      if (k >= 1) mbar_wait(bEmpty + 8 * g, (k - 1) & 1);  // the MMAs that read this group's stage have retired
-      V Plo[NC], Phi[NC], Rlo[NC], Rhi[NC];
+      {
+        WSP_T0();
+        if (k >= 1) mbar_wait(bEmpty + 8 * g, (k - 1) & 1);  // the MMAs that read this group's stage have retired
+        WSP_ADD(pw);
+      }
+      if (act) {
+        V Plo[NC], Phi[NC], Rlo[NC], Rhi[NC];
 #pragma unroll
-      for (int c = 0; c < NC; ++c) Plo[c] = Phi[c] = Rlo[c] = Rhi[c] = fsplat(0.f);
-      // input row i of the band: finishes output row i - 2 (taps 6..8), continues i - 1 (3..5), starts i (0..2)
-      auto step = [&](int i, const float4 (&v)[NC + 2]) {
-        const int ro = i - 2;
-        const int pp0 = ro * W + x0;
+        for (int c = 0; c < NC; ++c) Plo[c] = Phi[c] = Rlo[c] = Rhi[c] = fsplat(0.f);
+        uint32_t sa = abase;  // shared address of A row (pixel) pp: tracked as (pp >> 3, pp & 7) of output row i - 2
+        int pp = -2 * W + x0;
+        // input row i of the band: finishes output row i - 2 (taps 6..8), continues i - 1 (3..5), starts i (0..2)
+        auto step = [&](int i, const float4 (&vin)[NC + 2]) {
+          V vlo[NC + 2], vhi[NC + 2];
 #pragma unroll
-        for (int dy = 2; dy >= 0; --dy) {
-          V tlo[3], thi[3];
-#pragma unroll
-          for (int d = 0; d < 3; ++d) {
-            if (WREG) {
-              tlo[d] = wlo[WREG ? dy * 3 + d : 0];
-              thi[d] = whi[WREG ? dy * 3 + d : 0];
-            } else {
-              const float4 w = w4[(dy * 3 + d) * 8];
-              tlo[d] = make_float2(w.x, w.y);
-              thi[d] = make_float2(w.z, w.w);
+          for (int c = 0; c < NC + 2; ++c) {
+            vlo[c] = make_float2(vin[c].x, vin[c].y);
+            vhi[c] = make_float2(vin[c].z, vin[c].w);
+            if (c != 1) {  // column x0 itself always exists
+              vlo[c] = fmul(vlo[c], cm[c]);
+              vhi[c] = fmul(vhi[c], cm[c]);
             }
           }
 #pragma unroll
-          for (int c = 0; c < NC; ++c) {
-            V alo, ahi;  // dy = 2: P -> finished output; dy = 1: R -> P; dy = 0: fresh R
-            if (dy == 2) { alo = Plo[c]; ahi = Phi[c]; }
-            if (dy == 1) { alo = Rlo[c]; ahi = Rhi[c]; }
+          for (int dy = 2; dy >= 0; --dy) {
+            V tlo[3], thi[3];
 #pragma unroll
             for (int d = 0; d < 3; ++d) {
-              const V lo = make_float2(v[c + d].x, v[c + d].y), hi = make_float2(v[c + d].z, v[c + d].w);
-              if (dy == 0 && d == 0) {
-                alo = fmul(lo, tlo[0]);
-                ahi = fmul(hi, thi[0]);
+              if (WREG) {
+                tlo[d] = wlo[WREG ? dy * 3 + d : 0];
+                thi[d] = whi[WREG ? dy * 3 + d : 0];
               } else {
-                alo = ffma(lo, tlo[d], alo);
-                ahi = ffma(hi, thi[d], ahi);
+                const float4 w = w4[(dy * 3 + d) * 8];
+                tlo[d] = make_float2(w.x, w.y);
+                thi[d] = make_float2(w.z, w.w);
               }
             }
-            if (dy == 2) {
-              if (ro >= 0 && x0 + c < W) {  // tf32 round-to-nearest: add half an ulp of the 10-bit mantissa
-                const int pp = pp0 + c;
-                const uint32_t a = abase + (uint32_t)((pp >> 3) * kGSboA + (pp & 7) * 16);
-                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(__float_as_uint(alo.x) + 0x1000u),
-                             "r"(__float_as_uint(alo.y) + 0x1000u), "r"(__float_as_uint(ahi.x) + 0x1000u),
-                             "r"(__float_as_uint(ahi.y) + 0x1000u)
-                             : "memory");
+#pragma unroll
+            for (int c = 0; c < NC; ++c) {
+              V alo, ahi;  // dy = 2: P -> finished output; dy = 1: R -> P; dy = 0: fresh R
+              if (dy == 2) { alo = Plo[c]; ahi = Phi[c]; }
+              if (dy == 1) { alo = Rlo[c]; ahi = Rhi[c]; }
+#pragma unroll
+              for (int d = 0; d < 3; ++d) {
+                if (dy == 0 && d == 0) {
+                  alo = fmul(vlo[c], tlo[0]);
+                  ahi = fmul(vhi[c], thi[0]);
+                } else {
+                  alo = ffma(vlo[c + d], tlo[d], alo);
+                  ahi = ffma(vhi[c + d], thi[d], ahi);
+                }
               }
-            } else if (dy == 1) {
-              Plo[c] = alo; Phi[c] = ahi;
-            } else {
-              Rlo[c] = alo; Rhi[c] = ahi;
+              if (dy == 2) {
+                if (i >= 2 && x0 + c < W) {  // tf32 round-to-nearest: add half an ulp of the 10-bit mantissa
+                  const int ppc = pp + c;
+                  const uint32_t a = sa + (uint32_t)((ppc >> 3) * kGSboA + (ppc & 7) * 16);
+                  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(__float_as_uint(alo.x) + 0x1000u),
+                               "r"(__float_as_uint(alo.y) + 0x1000u), "r"(__float_as_uint(ahi.x) + 0x1000u),
+                               "r"(__float_as_uint(ahi.y) + 0x1000u)
+                               : "memory");
+                }
+              } else if (dy == 1) {
+                Plo[c] = alo; Phi[c] = ahi;
+              } else {
+                Rlo[c] = alo; Rhi[c] = ahi;
+              }
             }
           }
-        }
-      };
-      if (act) {
+          pp += W;
+        };
         [&] {
           int i = 0;
           while (true) {  // PF + 1 row buffers in rotation: the loads run PF rows ahead of the arithmetic
 #pragma unroll
             for (int r = 0; r <= PF; ++r) {
-              if (i + PF < nrows) load_row(i + PF, vbuf[(r + PF) % (PF + 1)]);
+              if (i + PF < nrows) load_row(vbuf[(r + PF) % (PF + 1)]);
               step(i, vbuf[r]);
               if (++i >= nrows) return;
             }
@@ -630,15 +709,19 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
       fence_proxy_async();
       __syncwarp();
       if (lane == 0) mbar_arrive(bFull + 8 * g);
-      while (epi_next < j) epilogue(epi_next++);
     }
-    while (epi_next < my_tiles) epilogue(epi_next++);
+#ifdef KWS_WS_PROFILE
+    if (blockIdx.x == 3 && (tid % kWsGT) == 0) printf("producer group %d: total %lld wait_empty %lld items %u\n", g, clock64() - wsp_start, wsp_pw, k);
+#endif
+  } else if (warp < kGT / 32 - 1) {
+    // ---- warps 12..14: drain only ----
+    for (int j = 0; j < my_tiles; ++j) epilogue(j);
   } else {
-    // ---- issue warp: weight-chunk TMA ring, MMAs in item order, its own share of the drains ----
+    // ---- issue warp: weight-chunk TMA ring, MMAs in item order, L2 prefetch of the next tile, drain of lane quarter 3 ----
     const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(p.nhalf >> 3) << 17) | ((128u >> 4) << 24);
     auto request_b = [&](int n, int kc) {  // weight chunk kc of item n into ring stage n % kWsBS
       if (lane == 0) {
-        const uint32_t s = (uint32_t)(n % kWsBS);
+        const uint32_t s = (uint32_t)n % (uint32_t)kWsBS;
         mbar_expect_tx(bBfull + 8 * s, (uint32_t)bbytes);
         tma_load_1d(smem_u32(sB + (size_t)s * bbytes), reinterpret_cast<const unsigned char*>(p.wimg) + (size_t)kc * bbytes,
                     (uint32_t)bbytes, bBfull + 8 * s);
@@ -665,37 +748,57 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
     if (total > 0) request_b(0, 0);
     if (total > 1) request_b(1, 1 % nch);
     int j = 0, kc = 0;
+    WSP_DECL(epi); WSP_DECL(free); WSP_DECL(full); WSP_DECL(bfull); WSP_DECL(bempty);
+#ifdef KWS_WS_PROFILE
+    const long long wsp_start = clock64();
+#endif
+    // descriptors of ring stage 0; a stage / K step / N half only moves the 14-bit start-address field (>> 4)
+    const uint64_t adesc0 = umma_desc(smem_u32(sA), kGLboA, kGSboA), bdesc0 = umma_desc(smem_u32(sB), 128u, kGSbo);
+    const uint32_t a_stage = kGABytes >> 4, b_stage = (uint32_t)bbytes >> 4, b_half = (uint32_t)((p.nhalf / 8) * kGSbo) >> 4;
+    const bool two_halves = p.nh == 2;
+    const uint32_t tmem_h1 = tmem + (uint32_t)p.nhalf;
+    int bs = 0, pbs = 0, kc2 = 2 % nch;          // weight ring stage of item n and of item n - 1; K chunk of item n + 2
+    uint32_t bph = 0, pbph = 0;                   // their phases
     for (int n = 0; n < total; ++n) {
-      const int g = n % kWsG, bs = n % kWsBS;
-      if (kc == 0) {
-        if (j > 0) prefetch_tile(j + 1);
-        if (j > 0) {  // tile boundary: the accumulator must be drained by all 16 warps before it is overwritten
-          epilogue(j - 1);
-          mbar_wait(bAccFree, (uint32_t)(j - 1) & 1u);
-        }
+      const int g = n & (kWsG - 1);
+      if (kc == 0 && j > 0) {  // tile boundary: the accumulator must be drained by its four warps before it is overwritten
+        prefetch_tile(j + 1);
+        { WSP_T0(); epilogue(j - 1); WSP_ADD(epi); }
+        { WSP_T0(); mbar_wait(bAccFree, (uint32_t)(j - 1) & 1u); WSP_ADD(free); }
       }
-      mbar_wait(bFull + 8 * g, (uint32_t)(n / kWsG) & 1u);
-      mbar_wait(bBfull + 8 * bs, (uint32_t)(n / kWsBS) & 1u);
+      { WSP_T0(); mbar_wait(bFull + 8 * g, (uint32_t)(n >> 2) & 1u); WSP_ADD(full); }
+      { WSP_T0(); mbar_wait(bBfull + 8 * bs, bph); WSP_ADD(bfull); }
       tc_fence_after();
-      const uint32_t ab = smem_u32(sA + g * kGABytes), bb = smem_u32(sB + (size_t)bs * bbytes);
-#pragma unroll 1
-      for (int ks = 0; ks < kGKC / 8; ++ks)
-        for (int hf = 0; hf < p.nh; ++hf)
-          tc_mma_tf32_elect(tmem + (uint32_t)(hf * p.nhalf), umma_desc(ab + ks * 2u * kGLboA, kGLboA, kGSboA),
-                            umma_desc(bb + (uint32_t)(hf * (p.nhalf / 8)) * kGSbo + ks * 256u, 128u, kGSbo), idesc,
-                            (kc > 0 || ks > 0) ? 1u : 0u);
+      const uint64_t ad = adesc0 + (uint64_t)((uint32_t)g * a_stage), bd = bdesc0 + (uint64_t)((uint32_t)bs * b_stage);
+#pragma unroll
+      for (int ks = 0; ks < kGKC / 8; ++ks) {
+        const uint32_t acc = (kc > 0 || ks > 0) ? 1u : 0u;
+        tc_mma_tf32_elect(tmem, ad + (uint64_t)(ks * ((2 * kGLboA) >> 4)), bd + (uint64_t)(ks * 16), idesc, acc);
+        if (two_halves)
+          tc_mma_tf32_elect(tmem_h1, ad + (uint64_t)(ks * ((2 * kGLboA) >> 4)), bd + (uint64_t)(b_half + ks * 16), idesc, acc);
+      }
       tc_commit_elect(bEmpty + 8 * g);
       tc_commit_elect(bBempty + 8 * bs);
       if (kc == nch - 1) tc_commit_elect(bAccFull);
       if (n + 2 < total) {  // weights of item n + 2 go where item n - 1's were: wait until its MMAs have retired
-        if (n >= 1) mbar_wait(bBempty + 8 * ((n - 1) % kWsBS), (uint32_t)((n - 1) / kWsBS) & 1u);
-        request_b(n + 2, (kc + 2) % nch);
+        { WSP_T0(); if (n >= 1) mbar_wait(bBempty + 8 * pbs, pbph); WSP_ADD(bempty); }
+        request_b(n + 2, kc2);
       }
+      pbs = bs;
+      pbph = bph;
+      if (++bs == kWsBS) {
+        bs = 0;
+        bph ^= 1u;
+      }
+      if (++kc2 >= nch) kc2 = 0;
       if (++kc == nch) {
         kc = 0;
         ++j;
       }
     }
+#ifdef KWS_WS_PROFILE
+    if (blockIdx.x == 3 && lane == 0) printf("issuer: total %lld epilogue %lld wait_accfree %lld wait_full %lld wait_bfull %lld wait_bempty %lld tiles %d items %d\n", clock64() - wsp_start, wsp_epi, wsp_free, wsp_full, wsp_bfull, wsp_bempty, my_tiles, total);
+#endif
     if (my_tiles > 0) epilogue(my_tiles - 1);
   }
   tc_fence_before();
@@ -729,6 +832,8 @@ struct GemmModel {
   std::vector<int> kvalid, nchunks;
   float* d_bias = nullptr;      // [1 + nb][C]: conv1 bias, then pointwise bias with the depthwise bias folded through
   float* d_border = nullptr;    // [nb][C] ReLU(pointwise bias)
+  float* d_zero = nullptr;      // [36][C] zeros: one input row of the widest layer the warp-specialised kernel takes
+  float* d_dump = nullptr;      // [npad] write-only scratch (GemmParams::dump)
 };
 
 static float gemm_host_tf32(float x) {
@@ -746,6 +851,8 @@ void free_gemm_model(void* gm) {
     if (p) cudaFree(p);
   if (g->d_bias) cudaFree(g->d_bias);
   if (g->d_border) cudaFree(g->d_border);
+  if (g->d_zero) cudaFree(g->d_zero);
+  if (g->d_dump) cudaFree(g->d_dump);
   delete g;
 }
 
@@ -799,6 +906,9 @@ int build_gemm_model(ModelWeights& m, const std::vector<float>& conv1_w, const s
   }
   if (rc == KWS_OK && cudaMalloc((void**)&g->d_bias, bias.size() * 4) != cudaSuccess) rc = fail(KWS_ERR_CUDA, "cudaMalloc failed");
   if (rc == KWS_OK && cudaMalloc((void**)&g->d_border, border.size() * 4) != cudaSuccess) rc = fail(KWS_ERR_CUDA, "cudaMalloc failed");
+  if (rc == KWS_OK && (cudaMalloc((void**)&g->d_zero, (size_t)36 * C * 4) != cudaSuccess || cudaMemset(g->d_zero, 0, (size_t)36 * C * 4) != cudaSuccess))
+    rc = fail(KWS_ERR_CUDA, "cudaMalloc failed");
+  if (rc == KWS_OK && cudaMalloc((void**)&g->d_dump, (size_t)(g->npad + 32) * 4) != cudaSuccess) rc = fail(KWS_ERR_CUDA, "cudaMalloc failed");
   if (rc == KWS_OK) {
     cudaMemcpy(g->d_bias, bias.data(), bias.size() * 4, cudaMemcpyHostToDevice);
     cudaMemcpy(g->d_border, border.data(), border.size() * 4, cudaMemcpyHostToDevice);
@@ -849,6 +959,8 @@ int launch_dscnn_gemm(kws_handle_t h, const float* feats_dev, int64_t B, int T, 
   p.nhalf = g->nhalf;
   p.tmem_cols = g->tmem_cols;
   p.patch_bytes = patch_bytes;
+  p.zero_row = g->d_zero;
+  p.dump = g->d_dump;
   p.B = B;
   auto set_grid = [&](int Hh, int Ww) {  // tile = R whole rows; returns the grid size
     p.H = Hh;
@@ -878,7 +990,7 @@ int launch_dscnn_gemm(kws_handle_t h, const float* feats_dev, int64_t B, int T, 
                          (size_t)g->npad * 4;
   const bool ws_fits = ws_env && smem_ws <= 227 * 1024;
   if (ws_fits) {
-    if (int rc = ensure_dyn_smem(dscnn_block_ws_kernel<2, 2, true>, smem_ws)) return rc;
+    if (int rc = ensure_dyn_smem(dscnn_block_ws_kernel<2, 2, false>, smem_ws)) return rc;
     if (int rc = ensure_dyn_smem(dscnn_block_ws_kernel<3, 1, false>, smem_ws)) return rc;
   }
   for (int l = 0; l < nb; ++l) {
@@ -905,7 +1017,7 @@ int launch_dscnn_gemm(kws_handle_t h, const float* feats_dev, int64_t B, int T, 
     const int pool_rows = ws ? 4 * p.nbands + 1 : p.nbands + 1;
     auto launch_block = [&]() {
       if (!ws) dscnn_gemm_kernel<1><<<grid, kGT, smem_bytes, st>>>(p);
-      else if (W <= 24) dscnn_block_ws_kernel<2, 2, true><<<grid, kGT, smem_ws, st>>>(p);
+      else if (W <= 24) dscnn_block_ws_kernel<2, 2, false><<<grid, kGT, smem_ws, st>>>(p);
       else dscnn_block_ws_kernel<3, 1, false><<<grid, kGT, smem_ws, st>>>(p);
     };
     if (l == nb - 1) {  // the pooled rows replace the last activation (see GemmParams::pool)
