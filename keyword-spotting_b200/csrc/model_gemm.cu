@@ -807,6 +807,166 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((uint32_t)p.tmem_cols));
 }
 
+// ---- conv1 (10x10, stride 2, padding 2, one input channel) as an im2col GEMM with resident weights -------------------
+// K = 100 taps (+ 4 zero) = 13 MMA k-steps.  The whole weight image (4 chunks) is loaded into shared memory once per
+// CTA; a tile's A operand (128 pixels x 104) is gathered by all 16 warps in one pass: an item is (pixel, pair of kernel
+// rows 2m, 2m+1) = 20 consecutive k = exactly five 16-byte K quads, read as two runs of 10 features (the chunk-
+// synchronous kernel did this tap by tap with a division per element and streamed the weights for every tile: 1.28 ms
+// of the 11.5 ms forward at 2048 clips).  Production is ~60 instructions per thread and tile, so the tile loop is simply
+// gather -> barrier -> 26 MMAs -> drain by all warps (lane quarter x column quarter, 16x256b loads as in the block
+// kernel) -> barrier.
+__global__ void __launch_bounds__(kGT, 1) dscnn_conv1_kernel(const GemmParams p) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  __shared__ __align__(8) unsigned long long s_bar[2];  // [0] weights landed, [1] MMAs of the tile retired
+  __shared__ uint32_t s_tmem;
+  const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
+  const int bbytes = (p.npad / 8) * kGSbo;
+  unsigned char* sA = smem;                       // [4][kGABytes]
+  unsigned char* sB = smem + 4 * kGABytes;        // [4][bbytes]
+  float* sBias = reinterpret_cast<float*>(sB + 4 * (size_t)bbytes);
+  const uint32_t barB = smem_u32(&s_bar[0]), barM = barB + 8;
+  if (tid == 0) {
+    mbar_init(barB, 1);
+    mbar_init(barM, 1);
+    fence_mbar_init();
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)),
+                 "r"((uint32_t)p.tmem_cols));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  for (int i = tid; i < p.npad; i += kGT) sBias[i] = i < p.C ? __ldg(p.bias + i) : 0.f;
+  // K quads 25..31 of the last chunk are never written: zero once (quad 25 = k 100..103 is read by the 13th k-step)
+  for (int i = tid; i < 4 * kGABytes / 16; i += kGT) reinterpret_cast<float4*>(sA)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (tid == 0) {
+    mbar_expect_tx(barB, 4u * (uint32_t)bbytes);
+    for (int c = 0; c < 4; ++c)
+      tma_load_1d(smem_u32(sB + (size_t)c * bbytes), reinterpret_cast<const unsigned char*>(p.wimg) + (size_t)c * bbytes,
+                  (uint32_t)bbytes, barB);
+  }
+  const uint32_t tmem = s_tmem;
+  const int H = p.H, W = p.W, C = p.C, R = p.R, T = p.T, F = p.F;
+  const unsigned ntiles = (unsigned)(p.B * p.nbands);
+  const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(p.nhalf >> 3) << 17) | ((128u >> 4) << 24);
+  const uint64_t adesc0 = umma_desc(smem_u32(sA), kGLboA, kGSboA), bdesc0 = umma_desc(smem_u32(sB), 128u, kGSbo);
+  const uint32_t a_stage = kGABytes >> 4, b_stage = (uint32_t)bbytes >> 4, b_half = (uint32_t)((p.nhalf / 8) * kGSbo) >> 4;
+  const bool f_even = (F & 1) == 0;
+  // drain share of this warp: TMEM lane quarter warp % 4, column quarter warp / 4 (in pairs of 8-column blocks)
+  const int dr_pairs = p.npad >> 4, dr_cs = warp >> 2;
+  const int dr_n = dr_pairs / 4 + (dr_cs < (dr_pairs & 3) ? 1 : 0);
+  const int dr_c0 = 16 * (dr_cs * (dr_pairs / 4) + min(dr_cs, dr_pairs & 3)), dr_c1 = dr_c0 + 16 * dr_n;
+  uint32_t it = 0;
+  for (unsigned tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+    const unsigned b = tile / (unsigned)p.nbands;
+    const int band = (int)(tile - b * (unsigned)p.nbands), r0 = band * R;
+    const float* feat = p.in + (long long)b * T * F;
+    // ---- gather: item = (pixel pp, kernel row pair m) ----
+    for (int item = tid; item < 128 * 5; item += kGT) {
+      const int m = item >> 7, pp = item & 127;
+      const int rl = pp / W, xq = pp - rl * W, y = r0 + rl;
+      const bool valid = rl < R && y < H;
+      float v[20];
+#pragma unroll
+      for (int kr = 0; kr < 2; ++kr) {
+        const int fr = 2 * y - 2 + 2 * m + kr, fc0 = 2 * xq - 2;
+        const bool rok = valid && fr >= 0 && fr < T;
+        const float* row = feat + (long long)fr * F + fc0;
+        if (rok && f_even && fc0 >= 0 && fc0 + 10 <= F) {  // interior: five aligned 8-byte loads
+#pragma unroll
+          for (int e = 0; e < 5; ++e) {
+            const float2 t2 = __ldg(reinterpret_cast<const float2*>(row) + e);
+            v[kr * 10 + 2 * e] = t2.x;
+            v[kr * 10 + 2 * e + 1] = t2.y;
+          }
+        } else {
+#pragma unroll
+          for (int e = 0; e < 10; ++e) v[kr * 10 + e] = (rok && fc0 + e >= 0 && fc0 + e < F) ? __ldg(row + e) : 0.f;
+        }
+      }
+      const uint32_t a0 = smem_u32(sA) + (uint32_t)((pp >> 3) * kGSboA + (pp & 7) * 16);
+#pragma unroll
+      for (int e = 0; e < 5; ++e) {  // K quad 5 m + e: chunk (quad >> 3), quad in chunk (quad & 7)
+        const int quad = 5 * m + e;
+        const uint32_t a = a0 + (uint32_t)((quad >> 3) * kGABytes + (quad & 7) * kGLboA);
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(__float_as_uint(v[4 * e]) + 0x1000u),
+                     "r"(__float_as_uint(v[4 * e + 1]) + 0x1000u), "r"(__float_as_uint(v[4 * e + 2]) + 0x1000u),
+                     "r"(__float_as_uint(v[4 * e + 3]) + 0x1000u)
+                     : "memory");
+      }
+    }
+    fence_proxy_async();
+    __syncthreads();
+    if (warp == kGT / 32 - 1) {
+      if (it == 0) mbar_wait(barB, 0);
+      tc_fence_after();
+      for (int ks = 0; ks < 13; ++ks) {  // k-step ks: chunk ks / 4, step ks % 4 inside it
+        const uint64_t ad = adesc0 + (uint64_t)((uint32_t)(ks >> 2) * a_stage + (uint32_t)(ks & 3) * ((2 * kGLboA) >> 4));
+        const uint64_t bd = bdesc0 + (uint64_t)((uint32_t)(ks >> 2) * b_stage + (uint32_t)(ks & 3) * 16u);
+        tc_mma_tf32_elect(tmem, ad, bd, idesc, ks > 0 ? 1u : 0u);
+        if (p.nh == 2) tc_mma_tf32_elect(tmem + (uint32_t)p.nhalf, ad, bd + (uint64_t)b_half, idesc, ks > 0 ? 1u : 0u);
+      }
+      tc_commit_elect(barM);
+    }
+    mbar_wait(barM, it & 1u);
+    tc_fence_after();
+    {  // ---- drain: bias + ReLU -> NHWC [B, H, W, C] ----
+      const int lq = warp & 3, tq = lane & 3, tr = lane >> 2;
+      const bool odd = lane & 1;
+      const int coff = odd ? 8 + 2 * (tq - 1) : 2 * tq;
+      float* orow[2][2];
+      bool valid[2][2];
+#pragma unroll
+      for (int hh = 0; hh < 2; ++hh)
+#pragma unroll
+        for (int ss = 0; ss < 2; ++ss) {
+          const int pp = lq * 32 + hh * 16 + ss * 8 + tr, rl = pp / W, xq = pp - rl * W, y = r0 + rl;
+          valid[hh][ss] = rl < R && y < H;
+          orow[hh][ss] = p.out + (((long long)b * H + y) * W + xq) * (long long)C + coff + dr_c0;
+        }
+      const int npix = min(R, H - r0) * W;
+      const bool hv0 = lq * 32 < npix, hv1 = lq * 32 + 16 < npix;
+      const uint32_t ta = tmem + ((uint32_t)(lq * 32) << 16);
+      for (int cb = dr_c0; cb < dr_c1 && hv0; cb += 16) {
+        float v[2][8];
+        tc_ld_16x256b_x2(ta + (uint32_t)cb, v[0]);
+        if (hv1) tc_ld_16x256b_x2(ta + (16u << 16) + (uint32_t)cb, v[1]);
+        tc_wait_ld();
+        const int col = cb + 2 * tq;
+        const float2 bz0 = *reinterpret_cast<const float2*>(sBias + col), bz1 = *reinterpret_cast<const float2*>(sBias + col + 8);
+        const bool cok = cb + coff < C;
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+          if (hh == 0 || hv1) {
+#pragma unroll
+            for (int ss = 0; ss < 2; ++ss) {
+              float* x = v[hh] + 2 * ss;  // registers [4 blk + 2 s + e]
+              x[0] = fmaxf(x[0] + bz0.x, 0.f);
+              x[1] = fmaxf(x[1] + bz0.y, 0.f);
+              x[4] = fmaxf(x[4] + bz1.x, 0.f);
+              x[5] = fmaxf(x[5] + bz1.y, 0.f);
+              const float k0 = odd ? x[4] : x[0], k1 = odd ? x[5] : x[1], s0 = odd ? x[0] : x[4], s1 = odd ? x[1] : x[5];
+              const float g0 = __shfl_xor_sync(0xffffffffu, s0, 1), g1 = __shfl_xor_sync(0xffffffffu, s1, 1);
+              if (cok && valid[hh][ss])
+                *reinterpret_cast<float4*>(orow[hh][ss]) = odd ? make_float4(g0, g1, k0, k1) : make_float4(k0, k1, g0, g1);
+              orow[hh][ss] += 16;
+            }
+          }
+        }
+      }
+    }
+    tc_fence_before();
+    __syncthreads();  // the next tile's gather overwrites A, its first MMA the accumulator
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0)
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((uint32_t)p.tmem_cols));
+}
+
 // border of a block output [B, Ho, Wo, C]: ReLU(pointwise bias)
 __global__ void border_fill_kernel(float* __restrict__ out, const float* __restrict__ relu_bias, long long B, int Ho,
                                    int Wo, int C) {
@@ -978,7 +1138,22 @@ int launch_dscnn_gemm(kws_handle_t h, const float* feats_dev, int64_t B, int T, 
   p.bias = g->d_bias;
   p.kvalid = g->kvalid[0];
   p.nchunks = g->nchunks[0];
-  dscnn_gemm_kernel<0><<<set_grid(H1, W1), kGT, smem_bytes, st>>>(p);
+  {
+    // conv1: resident-weight im2col kernel when its shared memory (4 A chunks + the whole weight image) fits
+    const size_t smem_c1 = (size_t)4 * kGABytes + (size_t)4 * (g->npad / 8) * kGSbo + (size_t)g->npad * 4;
+    static const bool c1_env = [] { const char* e = std::getenv("KWS_GEMM_CONV1"); return !(e && e[0] == '0'); }();
+    if (c1_env && smem_c1 <= 227 * 1024 && W1 <= 128 && g->nchunks[0] == 4 && B * ((H1 + 127) / 1) < 0x7fffffffLL) {
+      if (int rc = ensure_dyn_smem(dscnn_conv1_kernel, smem_c1)) return rc;
+      p.H = H1;
+      p.W = W1;
+      p.R = 128 / W1 < H1 ? 128 / W1 : H1;
+      p.nbands = (H1 + p.R - 1) / p.R;
+      const long long t = B * p.nbands;
+      dscnn_conv1_kernel<<<(unsigned)(t < h->sm_count ? t : h->sm_count), kGT, smem_c1, st>>>(p);
+    } else {
+      dscnn_gemm_kernel<0><<<set_grid(H1, W1), kGT, smem_bytes, st>>>(p);
+    }
+  }
   KWS_CHECK_LAUNCH(h);
   float *cur = buf0, *nxt = buf1;
   int H = H1, W = W1;
