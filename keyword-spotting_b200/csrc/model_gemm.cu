@@ -854,7 +854,18 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_conv1_kernel(const GemmParams p)
   const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(p.nhalf >> 3) << 17) | ((128u >> 4) << 24);
   const uint64_t adesc0 = umma_desc(smem_u32(sA), kGLboA, kGSboA), bdesc0 = umma_desc(smem_u32(sB), 128u, kGSbo);
   const uint32_t a_stage = kGABytes >> 4, b_stage = (uint32_t)bbytes >> 4, b_half = (uint32_t)((p.nhalf / 8) * kGSbo) >> 4;
+  // operand descriptors of the 13 k-steps (chunk ks / 4, step ks % 4 inside it), built once: in the issue loop the
+  // uniform datapath that assembles a descriptor costs more than the MMA it feeds
+  uint64_t adv[13], bdv[13];
+#pragma unroll
+  for (int ks = 0; ks < 13; ++ks) {
+    adv[ks] = adesc0 + (uint64_t)((uint32_t)(ks >> 2) * a_stage + (uint32_t)(ks & 3) * ((2 * kGLboA) >> 4));
+    bdv[ks] = bdesc0 + (uint64_t)((uint32_t)(ks >> 2) * b_stage + (uint32_t)(ks & 3) * 16u);
+  }
+  const bool two_halves = p.nh == 2;
+  const uint32_t tmem_h1 = tmem + (uint32_t)p.nhalf;
   const bool f_even = (F & 1) == 0;
+  const bool pf_ok = (F & 3) == 0 && (reinterpret_cast<size_t>(p.in) & 15) == 0;  // bulk prefetch: 16-byte granules
   // drain share of this warp: TMEM lane quarter warp % 4, column quarter warp / 4 (in pairs of 8-column blocks)
   const int dr_pairs = p.npad >> 4, dr_cs = warp >> 2;
   const int dr_n = dr_pairs / 4 + (dr_cs < (dr_pairs & 3) ? 1 : 0);
@@ -864,6 +875,13 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_conv1_kernel(const GemmParams p)
     const unsigned b = tile / (unsigned)p.nbands;
     const int band = (int)(tile - b * (unsigned)p.nbands), r0 = band * R;
     const float* feat = p.in + (long long)b * T * F;
+    if (tid == 0 && pf_ok && tile + gridDim.x < ntiles) {  // the next tile's feature rows -> L2 while this tile is worked on
+      const unsigned tn = tile + gridDim.x, bn = tn / (unsigned)p.nbands;
+      const int rn = (int)(tn - bn * (unsigned)p.nbands) * R;
+      const int f0 = max(2 * rn - 2, 0), f1 = min(2 * (rn + R) + 6, T - 1);
+      asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p.in + ((long long)bn * T + f0) * F), "r"((uint32_t)((f1 - f0 + 1) * F * 4))
+                   : "memory");
+    }
     // ---- gather: item = (pixel pp, kernel row pair m) ----
     for (int item = tid; item < 128 * 5; item += kGT) {
       const int m = item >> 7, pp = item & 127;
@@ -903,11 +921,15 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_conv1_kernel(const GemmParams p)
     if (warp == kGT / 32 - 1) {
       if (it == 0) mbar_wait(barB, 0);
       tc_fence_after();
-      for (int ks = 0; ks < 13; ++ks) {  // k-step ks: chunk ks / 4, step ks % 4 inside it
-        const uint64_t ad = adesc0 + (uint64_t)((uint32_t)(ks >> 2) * a_stage + (uint32_t)(ks & 3) * ((2 * kGLboA) >> 4));
-        const uint64_t bd = bdesc0 + (uint64_t)((uint32_t)(ks >> 2) * b_stage + (uint32_t)(ks & 3) * 16u);
-        tc_mma_tf32_elect(tmem, ad, bd, idesc, ks > 0 ? 1u : 0u);
-        if (p.nh == 2) tc_mma_tf32_elect(tmem + (uint32_t)p.nhalf, ad, bd + (uint64_t)b_half, idesc, ks > 0 ? 1u : 0u);
+      if (two_halves) {
+#pragma unroll
+        for (int ks = 0; ks < 13; ++ks) {
+          tc_mma_tf32_elect(tmem, adv[ks], bdv[ks], idesc, ks > 0 ? 1u : 0u);
+          tc_mma_tf32_elect(tmem_h1, adv[ks], bdv[ks] + (uint64_t)b_half, idesc, ks > 0 ? 1u : 0u);
+        }
+      } else {
+#pragma unroll
+        for (int ks = 0; ks < 13; ++ks) tc_mma_tf32_elect(tmem, adv[ks], bdv[ks], idesc, ks > 0 ? 1u : 0u);
       }
       tc_commit_elect(barM);
     }
