@@ -542,7 +542,7 @@ def _extras(args, torch, dist, dev, rank, world, pcm, model, ks, proc, timed, ba
         cps = Bl / (ms * 1e-3)
         return {"workload": "mfcc40 features -> DS-CNN-L (276 ch, 5 blocks) forward, %d clips/GPU" % Bl,
                 "clips_per_s": world * cps, "ms": ms,
-                "roofline": roofline3(WORK["dscnn_l_model"], cps, peaks, fp32_tflops, "dscnn_gemm_kernel", ms)}
+                "roofline": roofline3(WORK["dscnn_l_model"], cps, peaks, fp32_tflops, "dscnn_conv1_kernel + dscnn_block_ws_kernel (x5)", ms)}
 
     def cfg4():   # BASELINE configs[3]: log-mel + CRNN/GRU, batch 16 384
         Bc = min(B, 16384)
