@@ -538,7 +538,11 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
 #pragma unroll
         for (int ss = 0; ss < 2; ++ss) orow[hh][ss] += 32;
     };
+#ifdef KWS_WS_NODRAIN  // timing experiment only (results are wrong): the pipeline without the accumulator's drain
+    if (true) {
+#else
     if (!hv0 && !pool) {  // nothing of this tile lives in this lane quarter
+#endif
       release();
     } else {  // two register sets in rotation: the next round's TMEM loads are in flight while a round is stored
       float va[2][2][8], vb[2][2][8];
