@@ -113,6 +113,29 @@ def test_tensor_core_gemm_path_any_channels(channels, blocks, T, F, B):
     np.testing.assert_allclose(fast, want, rtol=1e-3, atol=2e-4)
 
 
+@pytest.mark.parametrize("channels,blocks,T,F,B", [(276, 5, 99, 40, 301), (96, 3, 99, 40, 77), (64, 2, 61, 64, 9)])
+def test_tensor_core_gemm_path_many_tiles_and_repeatable(channels, blocks, T, F, B):
+    """The warp-specialised block kernel (model_gemm.cu) with several tiles per CTA (ring stages, weight ring and the
+    accumulator recycle many times; last bands shorter than a tile; 64 x 2 at F = 64 has layers 30 and 32 columns wide = the
+    3-column thread map): every clip against the layered fp32 kernels, bit-identical on a second run, and a clip's
+    logits independent of its position in the batch (tiles of different clips share a CTA's pipeline)."""
+    sd = dscnn_ref.init_state_dict(channels=channels, num_blocks=blocks, seed=3 * channels + blocks)
+    m = DepthwiseSeparableConv(channels=channels, num_blocks=blocks)
+    m.load_state_dict(sd)
+    m = m.cuda()
+    x = (torch.randn(B, 1, T, F, generator=torch.Generator().manual_seed(B)) * 3.0).cuda()
+    a = m(x)
+    b = m(x)
+    assert torch.equal(a, b)
+    perm = torch.randperm(B, generator=torch.Generator().manual_seed(7)).cuda()
+    c = m(x[perm].contiguous())
+    assert torch.equal(a[perm], c)
+    m.set_kernel_path("layered")
+    layered = m(x)
+    np.testing.assert_allclose(a.cpu().numpy(), layered.cpu().numpy(), rtol=1e-3, atol=2e-4)
+    assert (a.argmax(1) == layered.argmax(1)).float().mean() > 0.995
+
+
 def test_extension_channels_blocks():
     """'DS-CNN-L'-style generalisation (SURVEY a-X1): only channels/num_blocks change."""
     sd = dscnn_ref.init_state_dict(channels=96, num_blocks=5, seed=4)
