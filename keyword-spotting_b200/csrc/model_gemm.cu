@@ -380,7 +380,7 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_gemm_kernel(const GemmParams p) 
 //     accumulator, so they run up to four chunks ahead into the next tile while it drains, and the MMAs catch up
 //     afterwards (a chunk multiplies faster than it is produced).
 constexpr int kWsG = 4;     // producer groups = A-ring stages
-constexpr int kWsGT = 96;   // threads per group: 8 channel quads x 12 column groups
+constexpr int kWsGT = 96;   // threads per group: 16 channel pairs x 6 column groups
 constexpr int kWsBS = 3;    // weight-chunk ring stages
 constexpr int kWsEpi = 4;   // draining warps: 12, 13, 14 and the issue warp 15 (TMEM lane quarter = warp % 4)
 
@@ -460,7 +460,11 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
     const bool pool = p.pool != nullptr, odd = lane & 1;
     // this thread's four pixels (16-lane half hh, row block ss); a lane without a pixel stores into a dump row, so
     // that the stores of all rounds but the last need no predicate
+#ifdef KWS_WS_STG64
+    const int coff = 2 * tq;
+#else
     const int coff = odd ? 8 + 2 * (tq - 1) : 2 * tq;  // first of this lane's four channels within a 16-channel pair
+#endif
     float* orow[2][2];
     bool valid[2][2];
 #pragma unroll
@@ -489,6 +493,9 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
       if (lane == 0) mbar_arrive(bAccFree);
     };
     auto process = [&](float (&v)[2][2][8], int cb, const bool guard) {
+#ifdef KWS_WS_LDONLY  // timing experiment only: TMEM loads without the arithmetic and the stores
+      if (v[0][0][0] != 1.2345e30f) return;
+#endif
 #pragma unroll
       for (int pr = 0; pr < 2; ++pr) {
         const int col = cb + 16 * pr + 2 * tq;  // channel of register e = 0 of block 0 (block 1: + 8)
@@ -504,6 +511,21 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
             x[5] = fmaxf(x[5] + bz1.y, 0.f);
           }
         if (!pool) {
+#ifdef KWS_WS_STG64  // A/B: 8-byte stores straight from the load layout (32-byte runs per pixel, no exchange)
+          const bool cok0 = !guard || cb + 16 * pr + 2 * tq < C, cok1 = !guard || cb + 16 * pr + 8 + 2 * tq < C;
+#pragma unroll
+          for (int hh = 0; hh < 2; ++hh) {
+            if (hh == 0 ? hv0 : hv1) {
+#pragma unroll
+              for (int ss = 0; ss < 2; ++ss) {
+                const float* x = v[pr][hh] + 2 * ss;
+                float* o = orow[hh][ss] + 16 * pr;
+                if (cok0) *reinterpret_cast<float2*>(o) = make_float2(x[0], x[1]);
+                if (cok1) *reinterpret_cast<float2*>(o + 8) = make_float2(x[4], x[5]);
+              }
+            }
+          }
+#else
           const bool cok = !guard || cb + 16 * pr + coff < C;
 #pragma unroll
           for (int hh = 0; hh < 2; ++hh) {
@@ -514,11 +536,16 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
                 const float k0 = odd ? x[4] : x[0], k1 = odd ? x[5] : x[1], s0 = odd ? x[0] : x[4], s1 = odd ? x[1] : x[5];
                 const float g0 = __shfl_xor_sync(0xffffffffu, s0, 1), g1 = __shfl_xor_sync(0xffffffffu, s1, 1);
                 const float4 o = odd ? make_float4(g0, g1, k0, k1) : make_float4(k0, k1, g0, g1);
+#ifdef KWS_WS_NOSTORE  // timing experiment only (results are wrong): the drain without its global stores
+                if (o.x == 1.2345e30f) *reinterpret_cast<float4*>(orow[hh][ss] + 16 * pr) = o;
+#else
                 if (!guard) *reinterpret_cast<float4*>(orow[hh][ss] + 16 * pr) = o;
                 else if (cok) *reinterpret_cast<float4*>(orow[hh][ss] + 16 * pr) = o;
+#endif
               }
             }
           }
+#endif
         } else {  // channel sums over the warp's 32 pixels in a fixed order: 4 in the thread, then lanes 4, 8, 16 apart
 #pragma unroll
           for (int be = 0; be < 4; ++be) {  // be = 2 blk + e
@@ -577,17 +604,21 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
 
   if (warp < kWsG * 3) {
     // ---- producers ----
+    // thread = (channel PAIR d of the chunk, NC adjacent columns): 16 pairs x 6 column groups.  With two channels per
+    // thread the nine depthwise taps are 18 registers and stay resident for the item (four channels per thread had to
+    // re-read them from shared memory every row: 36 of its 44 wavefronts per row, which is what the MMAs' operand reads
+    // were competing with), and a row of the window is NC + 2 eight-byte loads.
     const int g = warp / 3, gt = tid - g * kWsGT;
-    const int q = gt & 7, cg = gt >> 3, x0 = cg * NC;
-    const uint32_t abase = smem_u32(sA + g * kGABytes) + (uint32_t)(q * kGLboA);
+    const int d = gt & 15, cg = gt >> 4, x0 = cg * NC;
+    const uint32_t abase = smem_u32(sA + g * kGABytes) + (uint32_t)((d >> 1) * kGLboA + (d & 1) * 8);
     // column c of the window = input column x0 - 1 + c: byte offset within a row (clamped into the row) and 0/1 mask
     int coff[NC + 2];
-    V cm[NC + 2];
+    float cm[NC + 2];
 #pragma unroll
     for (int c = 0; c < NC + 2; ++c) {
       const int xx = x0 - 1 + c, xc = xx < 0 ? 0 : (xx >= W ? W - 1 : xx);
       coff[c] = xc * C * 4;
-      cm[c] = fsplat(xx == xc ? 1.f : 0.f);
+      cm[c] = xx == xc ? 1.f : 0.f;
     }
     const long long rowbytes = (long long)W * C * 4;
     uint32_t k = 0;
@@ -600,33 +631,27 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
       const unsigned tile = blockIdx.x + (unsigned)j * gridDim.x, b = tile / (unsigned)p.nbands;
       const int band = (int)(tile - b * (unsigned)p.nbands), r0 = band * R;
       const int nrows = min(R, H - r0) + 2;  // input rows r0 - 1 .. of the band (rows outside the clip are zeros)
-      const int kq = kc * kGKC + 4 * q;
+      const int kq = kc * kGKC + 2 * d;
       const bool act = x0 < W && kq < C;
       // next row to load: row r0 - 1 of the clip, channel kq (the pointer may run outside the clip: never read there)
       const char* rp = reinterpret_cast<const char*>(p.in + ((long long)b * H + r0 - 1) * W * (long long)C + kq);
       int ynext = r0 - 1;
       const char* zr = reinterpret_cast<const char*>(p.zero_row + kq);  // a row of zeros stands in for rows outside the clip
-      auto load_row = [&](float4 (&v)[NC + 2]) {
+      auto load_row = [&](V (&v)[NC + 2]) {
         const char* r = (ynext >= 0 && ynext < H) ? rp : zr;
 #pragma unroll
-        for (int c = 0; c < NC + 2; ++c) v[c] = __ldg(reinterpret_cast<const float4*>(r + coff[c]));
+        for (int c = 0; c < NC + 2; ++c) v[c] = __ldg(reinterpret_cast<const float2*>(r + coff[c]));
         rp += rowbytes;
         ++ynext;
       };
-      float4 vbuf[PF + 1][NC + 2];
-      const float4* w4 = reinterpret_cast<const float4*>(sW + kc * 9 * kGKC + 4 * q);
-      V wlo[WREG ? 9 : 1], whi[WREG ? 9 : 1];
+      V vbuf[PF + 1][NC + 2];
+      V w[9];
       if (act) {
 #pragma unroll
         for (int r = 0; r < PF; ++r) load_row(vbuf[r]);
-        if (WREG) {
+        const float2* w2 = reinterpret_cast<const float2*>(sW + kc * 9 * kGKC + 2 * d);
 #pragma unroll
-          for (int t = 0; t < (WREG ? 9 : 1); ++t) {
-            const float4 w = w4[t * 8];
-            wlo[t] = make_float2(w.x, w.y);
-            whi[t] = make_float2(w.z, w.w);
-          }
-        }
+        for (int t = 0; t < 9; ++t) w[t] = w2[t * 16];
       }
       {
         WSP_T0();
@@ -634,66 +659,32 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
         WSP_ADD(pw);
       }
       if (act) {
-        V Plo[NC], Phi[NC], Rlo[NC], Rhi[NC];
+        V P[NC], Rr[NC];
 #pragma unroll
-        for (int c = 0; c < NC; ++c) Plo[c] = Phi[c] = Rlo[c] = Rhi[c] = fsplat(0.f);
-        uint32_t sa = abase;  // shared address of A row (pixel) pp: tracked as (pp >> 3, pp & 7) of output row i - 2
-        int pp = -2 * W + x0;
+        for (int c = 0; c < NC; ++c) P[c] = Rr[c] = fsplat(0.f);
+        int pp = -2 * W + x0;  // A row (pixel of the tile) of output row i - 2, column x0
         // input row i of the band: finishes output row i - 2 (taps 6..8), continues i - 1 (3..5), starts i (0..2)
-        auto step = [&](int i, const float4 (&vin)[NC + 2]) {
-          V vlo[NC + 2], vhi[NC + 2];
+        auto step = [&](int i, const V (&vin)[NC + 2]) {
+          V v[NC + 2];
 #pragma unroll
-          for (int c = 0; c < NC + 2; ++c) {
-            vlo[c] = make_float2(vin[c].x, vin[c].y);
-            vhi[c] = make_float2(vin[c].z, vin[c].w);
-            if (c != 1) {  // column x0 itself always exists
-              vlo[c] = fmul(vlo[c], cm[c]);
-              vhi[c] = fmul(vhi[c], cm[c]);
+          for (int c = 0; c < NC + 2; ++c) v[c] = c == 1 ? vin[c] : fmul(vin[c], fsplat(cm[c]));  // column x0 always exists
+#pragma unroll
+          for (int c = 0; c < NC; ++c) {
+            V o = P[c], q1 = Rr[c], q0;
+#pragma unroll
+            for (int dx = 0; dx < 3; ++dx) {
+              o = ffma(v[c + dx], w[6 + dx], o);
+              q1 = ffma(v[c + dx], w[3 + dx], q1);
+              q0 = dx == 0 ? fmul(v[c], w[0]) : ffma(v[c + dx], w[dx], q0);
             }
-          }
-#pragma unroll
-          for (int dy = 2; dy >= 0; --dy) {
-            V tlo[3], thi[3];
-#pragma unroll
-            for (int d = 0; d < 3; ++d) {
-              if (WREG) {
-                tlo[d] = wlo[WREG ? dy * 3 + d : 0];
-                thi[d] = whi[WREG ? dy * 3 + d : 0];
-              } else {
-                const float4 w = w4[(dy * 3 + d) * 8];
-                tlo[d] = make_float2(w.x, w.y);
-                thi[d] = make_float2(w.z, w.w);
-              }
-            }
-#pragma unroll
-            for (int c = 0; c < NC; ++c) {
-              V alo, ahi;  // dy = 2: P -> finished output; dy = 1: R -> P; dy = 0: fresh R
-              if (dy == 2) { alo = Plo[c]; ahi = Phi[c]; }
-              if (dy == 1) { alo = Rlo[c]; ahi = Rhi[c]; }
-#pragma unroll
-              for (int d = 0; d < 3; ++d) {
-                if (dy == 0 && d == 0) {
-                  alo = fmul(vlo[c], tlo[0]);
-                  ahi = fmul(vhi[c], thi[0]);
-                } else {
-                  alo = ffma(vlo[c + d], tlo[d], alo);
-                  ahi = ffma(vhi[c + d], thi[d], ahi);
-                }
-              }
-              if (dy == 2) {
-                if (i >= 2 && x0 + c < W) {  // tf32 round-to-nearest: add half an ulp of the 10-bit mantissa
-                  const int ppc = pp + c;
-                  const uint32_t a = sa + (uint32_t)((ppc >> 3) * kGSboA + (ppc & 7) * 16);
-                  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(__float_as_uint(alo.x) + 0x1000u),
-                               "r"(__float_as_uint(alo.y) + 0x1000u), "r"(__float_as_uint(ahi.x) + 0x1000u),
-                               "r"(__float_as_uint(ahi.y) + 0x1000u)
-                               : "memory");
-                }
-              } else if (dy == 1) {
-                Plo[c] = alo; Phi[c] = ahi;
-              } else {
-                Rlo[c] = alo; Rhi[c] = ahi;
-              }
+            P[c] = q1;
+            Rr[c] = q0;
+            if (i >= 2 && x0 + c < W) {  // tf32 round-to-nearest: add half an ulp of the 10-bit mantissa
+              const int ppc = pp + c;
+              const uint32_t a = abase + (uint32_t)((ppc >> 3) * kGSboA + (ppc & 7) * 16);
+              asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(a), "r"(__float_as_uint(o.x) + 0x1000u),
+                           "r"(__float_as_uint(o.y) + 0x1000u)
+                           : "memory");
             }
           }
           pp += W;
@@ -776,6 +767,9 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
       const uint64_t ad = adesc0 + (uint64_t)((uint32_t)g * a_stage), bd = bdesc0 + (uint64_t)((uint32_t)bs * b_stage);
 #pragma unroll
       for (int ks = 0; ks < kGKC / 8; ++ks) {
+#ifdef KWS_WS_NOMMA  // timing experiment only (results are wrong): one K step of MMAs per item instead of four
+        if (ks > 0) break;
+#endif
         const uint32_t acc = (kc > 0 || ks > 0) ? 1u : 0u;
         tc_mma_tf32_elect(tmem, ad + (uint64_t)(ks * ((2 * kGLboA) >> 4)), bd + (uint64_t)(ks * 16), idesc, acc);
         if (two_halves)
@@ -1191,8 +1185,9 @@ int launch_dscnn_gemm(kws_handle_t h, const float* feats_dev, int64_t B, int T, 
                          (size_t)g->npad * 4;
   const bool ws_fits = ws_env && smem_ws <= 227 * 1024;
   if (ws_fits) {
-    if (int rc = ensure_dyn_smem(dscnn_block_ws_kernel<2, 2, false>, smem_ws)) return rc;
-    if (int rc = ensure_dyn_smem(dscnn_block_ws_kernel<3, 1, false>, smem_ws)) return rc;
+    if (int rc = ensure_dyn_smem(dscnn_block_ws_kernel<4, 2, true>, smem_ws)) return rc;
+    if (int rc = ensure_dyn_smem(dscnn_block_ws_kernel<5, 2, true>, smem_ws)) return rc;
+    if (int rc = ensure_dyn_smem(dscnn_block_ws_kernel<6, 1, true>, smem_ws)) return rc;
   }
   for (int l = 0; l < nb; ++l) {
     p.in = cur;
@@ -1218,8 +1213,9 @@ int launch_dscnn_gemm(kws_handle_t h, const float* feats_dev, int64_t B, int T, 
     const int pool_rows = ws ? 4 * p.nbands + 1 : p.nbands + 1;
     auto launch_block = [&]() {
       if (!ws) dscnn_gemm_kernel<1><<<grid, kGT, smem_bytes, st>>>(p);
-      else if (W <= 24) dscnn_block_ws_kernel<2, 2, false><<<grid, kGT, smem_ws, st>>>(p);
-      else dscnn_block_ws_kernel<3, 1, false><<<grid, kGT, smem_ws, st>>>(p);
+      else if (W <= 24) dscnn_block_ws_kernel<4, 2, true><<<grid, kGT, smem_ws, st>>>(p);
+      else if (W <= 30) dscnn_block_ws_kernel<5, 2, true><<<grid, kGT, smem_ws, st>>>(p);
+      else dscnn_block_ws_kernel<6, 1, true><<<grid, kGT, smem_ws, st>>>(p);
     };
     if (l == nb - 1) {  // the pooled rows replace the last activation (see GemmParams::pool)
       p.pool = nxt;
