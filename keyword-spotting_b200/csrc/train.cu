@@ -322,6 +322,98 @@ __global__ void __launch_bounds__(256) dw_bwd_kernel(const float* __restrict__ x
 }
 
 
+// Depthwise 3x3 backward, row-walking form: thread = (clip, column, row segment, channel PAIR); it walks down its rows with
+// the 3 x 3 window of dd in registers (three 8-byte loads of dd and one of x per pixel instead of nine 16-byte gathers with
+// bounds tests and a pixel-index division: the gather kernel above spends ~100 instructions per pixel and channel pair,
+// this one ~40, all arithmetic packed f32x2).  Lanes = the 32 channel pairs of a pixel: every access is one 256-byte run.
+constexpr int kDwSeg = 2;  // row segments per column (more CTAs for the narrow layers; one halo row each side)
+__global__ void __launch_bounds__(256) dw_bwd_rows_kernel(const float* __restrict__ x, const float* __restrict__ dd,
+                                                          float* __restrict__ dx, const float* __restrict__ w_packed /*[9][C]*/,
+                                                          float* __restrict__ g_w /*[C][9]*/, float* __restrict__ g_b,
+                                                          long long B, int H, int W) {
+  constexpr int C = kTC;
+  __shared__ float s_red[8][32 * 20];
+  const int tid = threadIdx.x, cp = tid & 31, slot = tid >> 5;
+  const long long ncol = B * W * (long long)kDwSeg;
+  float2 wv[9], wacc[9], bacc = make_float2(0.f, 0.f);
+#pragma unroll
+  for (int t = 0; t < 9; ++t) {
+    wv[t] = reinterpret_cast<const float2*>(w_packed + t * C)[cp];
+    wacc[t] = make_float2(0.f, 0.f);
+  }
+  const float2 z2 = make_float2(0.f, 0.f);
+  const int seg_rows = (H + kDwSeg - 1) / kDwSeg;
+  for (long long col = blockIdx.x * 8LL + slot; col < ncol; col += gridDim.x * 8LL) {
+    const unsigned c32 = (unsigned)col;  // B * W * kDwSeg < 2^31 (the host checks)
+    const unsigned seg = c32 % (unsigned)kDwSeg, bx = c32 / (unsigned)kDwSeg, xx = bx % (unsigned)W, b = bx / (unsigned)W;
+    const int y0 = (int)seg * seg_rows, y1 = min(H, y0 + seg_rows);
+    const bool hasl = xx > 0, hasr = (int)xx + 1 < W;
+    const float2* ddc = reinterpret_cast<const float2*>(dd + ((long long)b * H * W + xx) * C) + cp;  // row 0 of this column
+    const float2* xc = reinterpret_cast<const float2*>(x + ((long long)b * H * W + xx) * C) + cp;
+    float2* dxc = reinterpret_cast<float2*>(dx + ((long long)b * H * W + xx) * C) + cp;
+    const int rs = W * (C / 2), cs = C / 2;  // row / column stride in float2
+    auto load3 = [&](int y, float2 (&r)[3]) {  // dd[y][xx-1 .. xx+1], zeros outside the layer
+      const bool ok = y >= 0 && y < H;
+      const float2* q = ddc + (long long)y * rs;
+      r[0] = ok && hasl ? __ldg(q - cs) : z2;
+      r[1] = ok ? __ldg(q) : z2;
+      r[2] = ok && hasr ? __ldg(q + cs) : z2;
+    };
+    float2 ra[3], rb[3], rc[3];  // rows y - 1, y, y + 1 in rotation
+    load3(y0 - 1, ra);
+    load3(y0, rb);
+    float2 xv = y0 < y1 ? __ldg(xc + (long long)y0 * rs) : z2;
+    // one pixel: m = row y - 1, c = row y, n = row y + 1
+    auto pixel = [&](int y, const float2 (&m)[3], const float2 (&c)[3], const float2 (&n)[3], float2 xcur) {
+      float2 acc = z2;
+#pragma unroll
+      for (int j = 0; j < 3; ++j) {  // tap (i, j) reads dd[y + 1 - i][xx + 1 - j]
+        acc = __ffma2_rn(n[2 - j], wv[j], acc);
+        acc = __ffma2_rn(c[2 - j], wv[3 + j], acc);
+        acc = __ffma2_rn(m[2 - j], wv[6 + j], acc);
+        wacc[j] = __ffma2_rn(n[2 - j], xcur, wacc[j]);
+        wacc[3 + j] = __ffma2_rn(c[2 - j], xcur, wacc[3 + j]);
+        wacc[6 + j] = __ffma2_rn(m[2 - j], xcur, wacc[6 + j]);
+      }
+      bacc = __fadd2_rn(bacc, c[1]);
+      dxc[(long long)y * rs] = acc;
+    };
+    for (int y = y0; y < y1; y += 3) {
+      float2 xn;
+      load3(y + 1, rc);
+      xn = y + 1 < y1 ? __ldg(xc + (long long)(y + 1) * rs) : z2;
+      pixel(y, ra, rb, rc, xv);
+      if (y + 1 >= y1) break;
+      load3(y + 2, ra);
+      xv = y + 2 < y1 ? __ldg(xc + (long long)(y + 2) * rs) : z2;
+      pixel(y + 1, rb, rc, ra, xn);
+      if (y + 2 >= y1) break;
+      load3(y + 3, rb);
+      xn = y + 3 < y1 ? __ldg(xc + (long long)(y + 3) * rs) : z2;
+      pixel(y + 2, rc, ra, rb, xv);
+      xv = xn;
+    }
+  }
+  // reduce the 8 columns of the CTA that share a channel pair, then one atomic per value
+  float* mine = &s_red[slot][cp * 20];
+#pragma unroll
+  for (int t = 0; t < 9; ++t) {
+    mine[2 * t] = wacc[t].x;
+    mine[2 * t + 1] = wacc[t].y;
+  }
+  mine[18] = bacc.x;
+  mine[19] = bacc.y;
+  __syncthreads();
+  for (int i = tid; i < 32 * 20; i += 256) {
+    float sum = 0.f;
+#pragma unroll
+    for (int sl = 0; sl < 8; ++sl) sum += s_red[sl][i];
+    const int pr = i / 20, r = i - pr * 20, ch = 2 * pr + (r & 1);
+    if (r < 18) atomicAdd(&g_w[ch * 9 + (r >> 1)], sum);
+    else atomicAdd(&g_b[ch], sum);
+  }
+}
+
 // conv1 (10x10, stride 2, padding 2, one input channel) + ReLU backward: dW[c][tap] += dY[px][c] * patch[px][tap]
 //   l0 [B,H1,W1,C] saved conv1 output, dl0 gradient w.r.t. it (pre-mask), feats [B,T,F]
 __global__ void __launch_bounds__(256) conv1_bwd_kernel(const float* __restrict__ l0, const float* __restrict__ dl0,
@@ -490,10 +582,19 @@ int kws_train_forward_backward(kws_handle_t h, const float* params_dev, const fl
     }
     float* dx = w.dX[l & 1];
     const long long npix = B * (long long)H * W;
-    long long g2 = (npix + 15) / 16;
-    if (g2 > h->sm_count * 8LL) g2 = h->sm_count * 8LL;
-    dw_bwd_kernel<<<(unsigned)g2, 256, 0, st>>>(w.L[l], w.D[l], dx, m.d_dw_w + (size_t)l * 9 * C, grads_dev + fl.dww(l),
-                                                grads_dev + fl.dwb(l), B, H, W);
+    static const bool dw_rows = [] { const char* e = std::getenv("KWS_TRAIN_DWROWS"); return !(e && e[0] == '0'); }();
+    const long long ncol = B * (long long)W * kDwSeg;
+    if (dw_rows && ncol < 0x7fffffffLL) {
+      long long g2 = (ncol + 7) / 8;
+      if (g2 > h->sm_count * 16LL) g2 = h->sm_count * 16LL;
+      dw_bwd_rows_kernel<<<(unsigned)g2, 256, 0, st>>>(w.L[l], w.D[l], dx, m.d_dw_w + (size_t)l * 9 * C, grads_dev + fl.dww(l),
+                                                       grads_dev + fl.dwb(l), B, H, W);
+    } else {
+      long long g2 = (npix + 15) / 16;
+      if (g2 > h->sm_count * 8LL) g2 = h->sm_count * 8LL;
+      dw_bwd_kernel<<<(unsigned)g2, 256, 0, st>>>(w.L[l], w.D[l], dx, m.d_dw_w + (size_t)l * 9 * C, grads_dev + fl.dww(l),
+                                                  grads_dev + fl.dwb(l), B, H, W);
+    }
     KWS_CHECK_LAUNCH(h);
     dout = dx;
   }
