@@ -170,6 +170,9 @@ int train_forward_layers(kws_handle_t h, const float* feats_dev, int64_t B, int 
 // train_tc.cu: pointwise + ReLU backward of one 64-channel block on the tensor core (1 = launched, <0 = error)
 int launch_pw_bwd_tc(kws_handle_t h, const float* out, const float* dout, const float* dpooled, float inv_area, float* d_io,
                      const float* w_flat, float* g_w, float* g_b, long long B, int H, int W, cudaStream_t st);
+// train_tc.cu: pointwise + bias + ReLU forward of one 64-channel block on the tensor core, from the saved depthwise output
+int launch_pw_fwd_tc(kws_handle_t h, const float* d, float* out, const float* w_kmaj, const float* bias, long long B, int H,
+                     int W, cudaStream_t st);
 // model.cu: conv 10x10 s2 p2 (one input channel) + ReLU, NHWC output [B, H1, W1, C]
 int launch_conv1_relu(kws_handle_t h, const float* in, float* out, const float* w_packed, const float* bias, int64_t B,
                       int T, int F, int H1, int W1, int C, cudaStream_t st);

@@ -6,6 +6,7 @@
 //
 // Layer-by-layer fp32 path: activations NHWC [B, H, W, C] in a ping-pong workspace.
 // Weights are repacked at kws_model_finalize() so the channel index is innermost.
+#include <cstdlib>
 #include <cuda_runtime.h>
 
 #include <cstring>
@@ -170,12 +171,71 @@ __global__ void pool_fc_kernel(const float* __restrict__ in, float* __restrict__
 constexpr int kPoolThreads = 256;
 static size_t pool_smem(int C) { return (size_t)((C <= kPoolThreads ? kPoolThreads / C : 1) + 1) * C * 4; }
 
+// Depthwise 3x3 (padding 1) + bias of one 64-channel block, row-walking form (training forward): thread = (clip, column,
+// row segment, channel PAIR) walks down its rows with the 3 x 3 window of the input in registers: three 8-byte loads and
+// nine packed FMAs per pixel, every access a 256-byte run across the warp.  Writes the depthwise output the backward
+// pass needs anyway; dsblock64_kernel<true> then reads it instead of gathering the window nine times per pixel.
+constexpr int kDwfSeg = 2;
+__global__ void __launch_bounds__(256) dw_fwd_rows_kernel(const float* __restrict__ x, float* __restrict__ d,
+                                                          const float* __restrict__ w_packed /*[9][64]*/,
+                                                          const float* __restrict__ bias, long long B, int H, int W) {
+  constexpr int C = 64;
+  const int tid = threadIdx.x, cp = tid & 31, slot = tid >> 5;
+  const long long ncol = B * W * (long long)kDwfSeg;
+  float2 wv[9];
+#pragma unroll
+  for (int t = 0; t < 9; ++t) wv[t] = __ldg(reinterpret_cast<const float2*>(w_packed + t * C) + cp);
+  const float2 bv = __ldg(reinterpret_cast<const float2*>(bias) + cp), z2 = make_float2(0.f, 0.f);
+  const int seg_rows = (H + kDwfSeg - 1) / kDwfSeg, rs = W * (C / 2), cs = C / 2;
+  for (long long col = blockIdx.x * 8LL + slot; col < ncol; col += gridDim.x * 8LL) {
+    const unsigned c32 = (unsigned)col;
+    const unsigned seg = c32 % (unsigned)kDwfSeg, bx = c32 / (unsigned)kDwfSeg, xx = bx % (unsigned)W, b = bx / (unsigned)W;
+    const int y0 = (int)seg * seg_rows, y1 = min(H, y0 + seg_rows);
+    const bool hasl = xx > 0, hasr = (int)xx + 1 < W;
+    const float2* xc = reinterpret_cast<const float2*>(x + ((long long)b * H * W + xx) * C) + cp;
+    float2* dc = reinterpret_cast<float2*>(d + ((long long)b * H * W + xx) * C) + cp;
+    auto load3 = [&](int y, float2 (&r)[3]) {  // x[y][xx-1 .. xx+1], zeros outside the layer
+      const bool ok = y >= 0 && y < H;
+      const float2* q = xc + (long long)y * rs;
+      r[0] = ok && hasl ? __ldg(q - cs) : z2;
+      r[1] = ok ? __ldg(q) : z2;
+      r[2] = ok && hasr ? __ldg(q + cs) : z2;
+    };
+    auto pixel = [&](int y, const float2 (&m)[3], const float2 (&c)[3], const float2 (&n)[3]) {
+      float2 acc = bv;
+#pragma unroll
+      for (int j = 0; j < 3; ++j) {  // tap (i, j) reads x[y + i - 1][xx + j - 1]
+        acc = __ffma2_rn(m[j], wv[j], acc);
+        acc = __ffma2_rn(c[j], wv[3 + j], acc);
+        acc = __ffma2_rn(n[j], wv[6 + j], acc);
+      }
+      dc[(long long)y * rs] = acc;
+    };
+    float2 ra[3], rb[3], rc[3];  // rows y - 1, y, y + 1 in rotation
+    load3(y0 - 1, ra);
+    load3(y0, rb);
+    for (int y = y0; y < y1; y += 3) {
+      load3(y + 1, rc);
+      pixel(y, ra, rb, rc);
+      if (y + 1 >= y1) break;
+      load3(y + 2, ra);
+      pixel(y + 1, rb, rc, ra);
+      if (y + 2 >= y1) break;
+      load3(y + 3, rb);
+      pixel(y + 2, rc, ra, rb);
+    }
+  }
+}
+
 // Training forward of one block for C = 64 (the reference network): depthwise 3x3 into a transposed shared
 // tile, then the pointwise 1x1 as a register-tiled fp32 GEMM (4 px x 8 co per thread, packed f32x2 FMAs,
 // weights in shared memory).  Same results as dsblock_kernel up to fp32 summation order; saves the depthwise
 // output for the backward pass.
 constexpr int kB64Pix = 128;
 constexpr size_t kB64Smem = (size_t)(64 * 64 + 64 * kB64Pix) * 4;
+// DLOAD = true: the depthwise output was computed by dw_fwd_rows_kernel into `dsave`; this kernel only reads it (one
+// coalesced 16-byte load per item instead of nine gathers) and runs the pointwise GEMM.
+template <bool DLOAD>
 __global__ void __launch_bounds__(256, 3) dsblock64_kernel(const float* __restrict__ in, float* __restrict__ out,
                                                         const float* __restrict__ dw_w /*[9][64]*/,
                                                         const float* __restrict__ dw_b,
@@ -210,6 +270,9 @@ __global__ void __launch_bounds__(256, 3) dsblock64_kernel(const float* __restri
         split_pixel(pix, Wo, Ho, &b, &ho, &wo);
         if (ho >= 1 && ho <= H && wo >= 1 && wo <= W) {
           const int h = ho - 1, wc = wo - 1;
+          if (DLOAD) {
+            d = __ldg(reinterpret_cast<const float4*>(dsave + ((b * H + h) * W + wc) * C) + q);
+          } else {
           d = kb;
 #pragma unroll
           for (int i = 0; i < 3; ++i) {
@@ -226,6 +289,7 @@ __global__ void __launch_bounds__(256, 3) dsblock64_kernel(const float* __restri
             }
           }
           if (dsave) reinterpret_cast<float4*>(dsave + ((b * H + h) * W + wc) * C)[q] = d;
+          }
         }
       }
       const int pls = pl ^ (4 * (q & 7));
@@ -459,10 +523,31 @@ int train_forward_layers(kws_handle_t h, const float* feats_dev, int64_t B, int 
     if (C == 64) {
       const long long nt = (npix + kB64Pix - 1) / kB64Pix;
       const long long g64 = nt < h->sm_count * 3LL ? nt : h->sm_count * 3LL;
-      if (int rc_ = ensure_dyn_smem(dsblock64_kernel, (size_t)kB64Smem)) return rc_;
-      dsblock64_kernel<<<(unsigned)g64, 256, kB64Smem, st>>>(w.L[i], w.L[i + 1], m.d_dw_w + (size_t)i * 9 * C,
-                                                            m.d_dw_b + (size_t)i * C, m.d_pw_w + (size_t)i * C * C,
-                                                            m.d_pw_b + (size_t)i * C, B, H, W, w.D[i]);
+      static const bool dw_rows = [] { const char* e = std::getenv("KWS_TRAIN_DWROWS"); return !(e && e[0] == '0'); }();
+      const long long ncol = B * (long long)W * kDwfSeg;
+      if (dw_rows && w.D[i] && ncol < 0x7fffffffLL) {  // depthwise by the row-walking kernel, then the GEMM kernel on its output
+        long long g2 = (ncol + 7) / 8;
+        if (g2 > h->sm_count * 16LL) g2 = h->sm_count * 16LL;
+        dw_fwd_rows_kernel<<<(unsigned)g2, 256, 0, st>>>(w.L[i], w.D[i], m.d_dw_w + (size_t)i * 9 * C, m.d_dw_b + (size_t)i * C, B, H, W);
+        KWS_CHECK_LAUNCH(h);
+        static const bool fwd_tc = [] { const char* e = std::getenv("KWS_TRAIN_TC"); return !(e && e[0] == '0'); }();
+        if (fwd_tc) {  // pointwise + bias + ReLU on the tensor core (train_tc.cu)
+          const int rc_tc = launch_pw_fwd_tc(h, w.D[i], w.L[i + 1], m.d_pw_w + (size_t)i * C * C, m.d_pw_b + (size_t)i * C, B, H, W, st);
+          if (rc_tc < 0) return rc_tc;
+          H += 2;
+          W += 2;
+          continue;
+        }
+        if (int rc_ = ensure_dyn_smem(dsblock64_kernel<true>, (size_t)kB64Smem)) return rc_;
+        dsblock64_kernel<true><<<(unsigned)g64, 256, kB64Smem, st>>>(w.L[i], w.L[i + 1], m.d_dw_w + (size_t)i * 9 * C,
+                                                                    m.d_dw_b + (size_t)i * C, m.d_pw_w + (size_t)i * C * C,
+                                                                    m.d_pw_b + (size_t)i * C, B, H, W, w.D[i]);
+      } else {
+        if (int rc_ = ensure_dyn_smem(dsblock64_kernel<false>, (size_t)kB64Smem)) return rc_;
+        dsblock64_kernel<false><<<(unsigned)g64, 256, kB64Smem, st>>>(w.L[i], w.L[i + 1], m.d_dw_w + (size_t)i * 9 * C,
+                                                                     m.d_dw_b + (size_t)i * C, m.d_pw_w + (size_t)i * C * C,
+                                                                     m.d_pw_b + (size_t)i * C, B, H, W, w.D[i]);
+      }
     } else {
       int threads = kBlkPix * cq;
       if (threads > 512) threads = 512;

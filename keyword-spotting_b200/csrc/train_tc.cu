@@ -203,6 +203,149 @@ pw_bwd_tc_kernel(const float* __restrict__ out, const float* __restrict__ dout, 
   if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(256));
 }
 
+// ---- forward twin: pointwise 1x1 (padding = 1) + bias + ReLU of one block on the tensor core -------------------------------
+//   out[px][co] = ReLU(b[co] + sum_ci D[px][ci] W[ci][co])   over the padded (H+2) x (W+2) grid; D = 0 on the border, so a
+//   border pixel comes out as ReLU(b) (the padding = 1 quirk, models.py:104-106) with no special case.
+// D is the depthwise output dw_fwd_rows_kernel has just written (it is saved for the backward pass anyway).  Tile = 128
+// consecutive pixels of the padded grid = one M = 128, N = 64, K = 64 GEMM; both operands are K-major as they lie in memory
+// (NHWC rows, [ci][co] weights read transposed once), fp32-grade through the 3-term tf32 split (24 MMAs per tile).  110 KB
+// of shared memory and 64 TMEM columns per CTA: two CTAs per SM overlap one's loads and drain with the other's MMAs.
+constexpr int kFTile = 128;
+constexpr int kFOpA = (kFTile / 8) * kPSbo;  // one 128-row A image (hi or lo): 36 864 B
+constexpr size_t kFSmem = 2 * (size_t)kFOpA + 2 * (size_t)kPOp + 64 * 4;
+constexpr uint32_t kFIdesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(64 >> 3) << 17) | ((128u >> 4) << 24);
+
+__global__ void __launch_bounds__(kPThreads, 2)
+pw_fwd_tc_kernel(const float* __restrict__ d, float* __restrict__ out, const float* __restrict__ w_kmaj /*[ci][co]*/,
+                 const float* __restrict__ bias, long long B, int H, int W) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  __shared__ __align__(8) unsigned long long s_bar;
+  __shared__ uint32_t s_tmem;
+  const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
+  const uint32_t bar = smem_u32(&s_bar);
+  const int Ho = H + 2, Wo = W + 2;
+  const long long npix = B * Ho * (long long)Wo, ntiles = (npix + kFTile - 1) / kFTile;
+  unsigned char* sAh = smem;
+  unsigned char* sAl = smem + kFOpA;
+  unsigned char* sBh = smem + 2 * kFOpA;
+  unsigned char* sBl = sBh + kPOp;
+  float* sBias = reinterpret_cast<float*>(sBl + kPOp);
+  if (tid == 0) {
+    mbar_init(bar, 1);
+    fence_mbar_init();
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "n"(64));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  for (int i = tid; i < kPC * kPC; i += kPThreads) {  // B rows = co, K = ci
+    const int ci = i >> 6, co = i & 63;
+    float hi, lo;
+    split_tf32(__ldg(w_kmaj + i), hi, lo);
+    *reinterpret_cast<float*>(sBh + kmaj_off(co, ci)) = hi;
+    *reinterpret_cast<float*>(sBl + kmaj_off(co, ci)) = lo;
+  }
+  if (tid < kPC) sBias[tid] = __ldg(bias + tid);
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = s_tmem;
+  const uint32_t aH = smem_u32(sAh), aL = smem_u32(sAl), bH = smem_u32(sBh), bL = smem_u32(sBl);
+  // staging items of this thread: channel quad q of pixels px0 + 32 it; the next tile's loads are in flight while this
+  // tile multiplies and drains
+  const int q = tid & 15, px0 = tid >> 4;
+  float4 dv[4];
+  auto load_tile = [&](long long tile) {
+#pragma unroll
+    for (int it = 0; it < 4; ++it) {
+      const long long gp = tile * kFTile + px0 + 32 * it;
+      dv[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (gp < npix) {
+        int wo, ho;
+        long long b;
+        split_pixel(gp, Wo, Ho, &b, &ho, &wo);
+        if (ho >= 1 && ho <= H && wo >= 1 && wo <= W)
+          dv[it] = __ldg(reinterpret_cast<const float4*>(d + ((b * H + ho - 1) * W + wo - 1) * kPC) + q);
+      }
+    }
+  };
+  if ((long long)blockIdx.x < ntiles) load_tile(blockIdx.x);
+  uint32_t parity = 0;
+  for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+#pragma unroll
+    for (int it = 0; it < 4; ++it) {
+      float h4[4], l4[4];
+      split_tf32(dv[it].x, h4[0], l4[0]); split_tf32(dv[it].y, h4[1], l4[1]);
+      split_tf32(dv[it].z, h4[2], l4[2]); split_tf32(dv[it].w, h4[3], l4[3]);
+      const uint32_t o = kmaj_off(px0 + 32 * it, 4 * q);
+      *reinterpret_cast<float4*>(sAh + o) = make_float4(h4[0], h4[1], h4[2], h4[3]);
+      *reinterpret_cast<float4*>(sAl + o) = make_float4(l4[0], l4[1], l4[2], l4[3]);
+    }
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {  // converged warp, elected lane issues: Ahi.Bhi + Alo.Bhi + Ahi.Blo
+      tc_fence_after();
+#pragma unroll 1
+      for (int term = 0; term < 3; ++term) {
+        const uint32_t a = term == 1 ? aL : aH, b = term == 2 ? bL : bH;
+        for (int ks = 0; ks < 8; ++ks)
+          tc_mma_tf32_elect(tmem, umma_desc(a + ks * 2 * kPLbo, kPLbo, kPSbo), umma_desc(b + ks * 2 * kPLbo, kPLbo, kPSbo), kFIdesc,
+                            (term | ks) != 0);
+      }
+      tc_commit_elect(bar);
+    }
+    if (tile + gridDim.x < ntiles) load_tile(tile + gridDim.x);
+    mbar_wait(bar, parity);
+    parity ^= 1u;
+    tc_fence_after();
+    {  // drain: TMEM lane quarter warp % 4, channels 16 (warp / 4) ..; 16x256b loads + one lane exchange (see model_gemm.cu)
+      const int lq = warp & 3, tq = lane & 3, tr = lane >> 2, c0 = (warp >> 2) * 16;
+      const bool odd = lane & 1;
+      const int coff = odd ? 8 + 2 * (tq - 1) : 2 * tq;
+      float v[2][8];
+      const uint32_t ta = tmem + ((uint32_t)(lq * 32) << 16) + (uint32_t)c0;
+      tc_ld_16x256b_x2(ta, v[0]);
+      tc_ld_16x256b_x2(ta + (16u << 16), v[1]);
+      tc_wait_ld();
+      const float2 bz0 = *reinterpret_cast<const float2*>(sBias + c0 + 2 * tq), bz1 = *reinterpret_cast<const float2*>(sBias + c0 + 8 + 2 * tq);
+#pragma unroll
+      for (int hh = 0; hh < 2; ++hh)
+#pragma unroll
+        for (int ss = 0; ss < 2; ++ss) {
+          float* x = v[hh] + 2 * ss;  // registers [4 blk + 2 s + e]
+          x[0] = fmaxf(x[0] + bz0.x, 0.f);
+          x[1] = fmaxf(x[1] + bz0.y, 0.f);
+          x[4] = fmaxf(x[4] + bz1.x, 0.f);
+          x[5] = fmaxf(x[5] + bz1.y, 0.f);
+          const float k0 = odd ? x[4] : x[0], k1 = odd ? x[5] : x[1], s0 = odd ? x[0] : x[4], s1 = odd ? x[1] : x[5];
+          const float g0 = __shfl_xor_sync(0xffffffffu, s0, 1), g1 = __shfl_xor_sync(0xffffffffu, s1, 1);
+          const long long gp = tile * kFTile + lq * 32 + hh * 16 + ss * 8 + tr;
+          if (gp < npix)
+            *reinterpret_cast<float4*>(out + gp * kPC + c0 + coff) = odd ? make_float4(g0, g1, k0, k1) : make_float4(k0, k1, g0, g1);
+        }
+    }
+    tc_fence_before();
+    // the next tile's staging overwrites the A images (their MMAs have retired); the barrier above orders this drain's
+    // TMEM reads before the next tile's MMAs
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(64));
+}
+
+// 1 = launched, < 0 = error
+int launch_pw_fwd_tc(kws_handle_t h, const float* d, float* out, const float* w_kmaj, const float* bias, long long B, int H,
+                     int W, cudaStream_t st) {
+  if (int rc = ensure_dyn_smem(pw_fwd_tc_kernel, kFSmem)) return rc;
+  const long long ntiles = (B * (long long)(H + 2) * (W + 2) + kFTile - 1) / kFTile;
+  const long long g = ntiles < 2LL * h->sm_count ? ntiles : 2LL * h->sm_count;
+  pw_fwd_tc_kernel<<<(unsigned)g, kPThreads, kFSmem, st>>>(d, out, w_kmaj, bias, B, H, W);
+  KWS_CHECK_LAUNCH(h);
+  return 1;
+}
+
 // 1 = launched, < 0 = error
 int launch_pw_bwd_tc(kws_handle_t h, const float* out, const float* dout, const float* dpooled, float inv_area, float* d_io,
                      const float* w_flat, float* g_w, float* g_b, long long B, int H, int W, cudaStream_t st) {
