@@ -78,6 +78,10 @@ pw_bwd_tc_kernel(const float* __restrict__ out, const float* __restrict__ dout, 
   tc_fence_after();
   const uint32_t tmem = s_tmem;
   const uint32_t sbase = smem_u32(smem);
+  const uint64_t dA1h = umma_desc(sbase + kPOffA1, kPLbo, kPSbo), dA1l = umma_desc(sbase + kPOffA1 + kPOp, kPLbo, kPSbo);
+  const uint64_t dB1h = umma_desc(sbase + kPOffB1, kPLbo, kPSbo), dB1l = umma_desc(sbase + kPOffB1 + kPOp, kPLbo, kPSbo);
+  const uint64_t dA2h = umma_desc(sbase + kPOffA2, kPLbo, kPSbo), dA2l = umma_desc(sbase + kPOffA2 + kPOp, kPLbo, kPSbo);
+  const uint64_t dB2h = umma_desc(sbase + kPOffB2, kPLbo, kPSbo), dB2l = umma_desc(sbase + kPOffB2 + kPOpB2, kPLbo, kPSbo);
 
   // staging item of this thread: 16 pixels x 2 channel quads per warp (see the header), two items per tile
   const int pxl = lane & 15, q = 2 * (warp & 7) + (lane >> 4), pxb = (warp >> 3) * 16 + pxl;  // + 32 for the second item
@@ -138,19 +142,23 @@ pw_bwd_tc_kernel(const float* __restrict__ out, const float* __restrict__ dout, 
     __syncthreads();
     if (warp == 0) {  // converged warp, elected lane issues
       tc_fence_after();
-#pragma unroll 1
+      // descriptors = tile-invariant bases (built once, above) + a K step's 18 sixteen-byte units: assembling a descriptor
+      // per MMA on the uniform datapath cost more than the MMA (48 per tile)
+#pragma unroll
       for (int term = 0; term < 3; ++term) {
-        const uint32_t a1 = sbase + kPOffA1 + (term == 1 ? kPOp : 0), b1 = sbase + kPOffB1 + (term == 2 ? kPOp : 0);
+        const uint64_t a1 = term == 1 ? dA1l : dA1h, b1 = term == 2 ? dB1l : dB1h;
+#pragma unroll
         for (int ks = 0; ks < 8; ++ks)
-          tc_mma_tf32_elect(tmem, umma_desc(a1 + ks * 2 * kPLbo, kPLbo, kPSbo), umma_desc(b1 + ks * 2 * kPLbo, kPLbo, kPSbo),
-                            kPIdesc1, (term | ks) != 0);
+          tc_mma_tf32_elect(tmem, a1 + (uint64_t)(ks * ((2 * kPLbo) >> 4)), b1 + (uint64_t)(ks * ((2 * kPLbo) >> 4)), kPIdesc1,
+                            (term | ks) != 0);
       }
-#pragma unroll 1
+#pragma unroll
       for (int term = 0; term < 3; ++term) {
-        const uint32_t a2 = sbase + kPOffA2 + (term == 1 ? kPOp : 0), b2 = sbase + kPOffB2 + (term == 2 ? kPOpB2 : 0);
+        const uint64_t a2 = term == 1 ? dA2l : dA2h, b2 = term == 2 ? dB2l : dB2h;
+#pragma unroll
         for (int ks = 0; ks < 8; ++ks)
-          tc_mma_tf32_elect(tmem + 64u, umma_desc(a2 + ks * 2 * kPLbo, kPLbo, kPSbo), umma_desc(b2 + ks * 2 * kPLbo, kPLbo, kPSbo),
-                            kPIdesc2, !(first && term == 0 && ks == 0));
+          tc_mma_tf32_elect(tmem + 64u, a2 + (uint64_t)(ks * ((2 * kPLbo) >> 4)), b2 + (uint64_t)(ks * ((2 * kPLbo) >> 4)), kPIdesc2,
+                            !(first && term == 0 && ks == 0));
       }
       tc_commit_elect(bar);
     }
@@ -251,7 +259,8 @@ pw_fwd_tc_kernel(const float* __restrict__ d, float* __restrict__ out, const flo
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = s_tmem;
-  const uint32_t aH = smem_u32(sAh), aL = smem_u32(sAl), bH = smem_u32(sBh), bL = smem_u32(sBl);
+  const uint64_t dAh = umma_desc(smem_u32(sAh), kPLbo, kPSbo), dAl = umma_desc(smem_u32(sAl), kPLbo, kPSbo);
+  const uint64_t dBh = umma_desc(smem_u32(sBh), kPLbo, kPSbo), dBl = umma_desc(smem_u32(sBl), kPLbo, kPSbo);
   // staging items of this thread: channel quad q of pixels px0 + 32 it; the next tile's loads are in flight while this
   // tile multiplies and drains
   const int q = tid & 15, px0 = tid >> 4;
@@ -287,11 +296,12 @@ pw_fwd_tc_kernel(const float* __restrict__ d, float* __restrict__ out, const flo
     __syncthreads();
     if (warp == 0) {  // converged warp, elected lane issues: Ahi.Bhi + Alo.Bhi + Ahi.Blo
       tc_fence_after();
-#pragma unroll 1
+#pragma unroll
       for (int term = 0; term < 3; ++term) {
-        const uint32_t a = term == 1 ? aL : aH, b = term == 2 ? bL : bH;
+        const uint64_t a = term == 1 ? dAl : dAh, b = term == 2 ? dBl : dBh;
+#pragma unroll
         for (int ks = 0; ks < 8; ++ks)
-          tc_mma_tf32_elect(tmem, umma_desc(a + ks * 2 * kPLbo, kPLbo, kPSbo), umma_desc(b + ks * 2 * kPLbo, kPLbo, kPSbo), kFIdesc,
+          tc_mma_tf32_elect(tmem, a + (uint64_t)(ks * ((2 * kPLbo) >> 4)), b + (uint64_t)(ks * ((2 * kPLbo) >> 4)), kFIdesc,
                             (term | ks) != 0);
       }
       tc_commit_elect(bar);
