@@ -379,7 +379,9 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_gemm_kernel(const GemmParams p) 
 //     warp takes the fourth: it has nothing to issue while the accumulator is busy).  The producers never touch the
 //     accumulator, so they run up to four chunks ahead into the next tile while it drains, and the MMAs catch up
 //     afterwards (a chunk multiplies faster than it is produced).
-constexpr int kWsG = 4;     // producer groups = A-ring stages
+constexpr int kWsG = 4;     // producer groups
+constexpr int kWsS = 5;     // A-ring stages (item n uses stage n % kWsS: one more than groups, so that production runs on
+                            // while the accumulator drains and the MMAs of the four waiting chunks catch up)
 constexpr int kWsGT = 96;   // threads per group: 16 channel pairs x 6 column groups
 constexpr int kWsBS = 3;    // weight-chunk ring stages
 constexpr int kWsEpi = 4;   // draining warps: 12, 13, 14 and the issue warp 15 (TMEM lane quarter = warp % 4)
@@ -397,19 +399,19 @@ constexpr int kWsEpi = 4;   // draining warps: 12, 13, 14 and the issue warp 15 
 template <int NC, int PF, bool WREG>
 __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams p) {
   extern __shared__ __align__(128) unsigned char smem[];
-  __shared__ __align__(8) unsigned long long s_bar[2 * kWsG + 2 * kWsBS + 2];
+  __shared__ __align__(8) unsigned long long s_bar[2 * kWsS + 2 * kWsBS + 2];
   __shared__ uint32_t s_tmem;
   const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
   const int bbytes = (p.npad / 8) * kGSbo;
-  unsigned char* sA = smem;                                  // [kWsG][kGABytes]
-  unsigned char* sB = smem + kWsG * kGABytes;                // [kWsBS][bbytes]
+  unsigned char* sA = smem;                                  // [kWsS][kGABytes]
+  unsigned char* sB = smem + kWsS * kGABytes;                // [kWsBS][bbytes]
   const int kpad = p.nchunks * kGKC;
   float* sW = reinterpret_cast<float*>(sB + kWsBS * (size_t)bbytes);  // [chunk][tap][32 channels]
   float* sBias = sW + 9 * kpad;                              // [npad]
-  const uint32_t bFull = smem_u32(&s_bar[0]), bEmpty = bFull + 8 * kWsG, bBfull = bEmpty + 8 * kWsG,
+  const uint32_t bFull = smem_u32(&s_bar[0]), bEmpty = bFull + 8 * kWsS, bBfull = bEmpty + 8 * kWsS,
                  bBempty = bBfull + 8 * kWsBS, bAccFull = bBempty + 8 * kWsBS, bAccFree = bAccFull + 8;
   if (tid == 0) {
-    for (int g = 0; g < kWsG; ++g) {
+    for (int g = 0; g < kWsS; ++g) {
       mbar_init(bFull + 8 * g, 3);   // one arrival per producer warp of the group
       mbar_init(bEmpty + 8 * g, 1);  // tcgen05.commit
     }
@@ -433,7 +435,7 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
   for (int i = tid; i < p.npad; i += kGT) sBias[i] = i < p.C ? __ldg(p.bias + i) : 0.f;
   // A ring starts as zeros: rows no pixel owns and channel quads past the channel count are never written, and
   // what the MMA reads there must be finite (it meets zero weight rows, or lands in accumulator rows nobody reads)
-  for (int i = tid; i < kWsG * kGABytes / 16; i += kGT) reinterpret_cast<float4*>(sA)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int i = tid; i < kWsS * kGABytes / 16; i += kGT) reinterpret_cast<float4*>(sA)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   fence_proxy_async();
   tc_fence_before();
   __syncthreads();
@@ -610,7 +612,7 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
     // were competing with), and a row of the window is NC + 2 eight-byte loads.
     const int g = warp / 3, gt = tid - g * kWsGT;
     const int d = gt & 15, cg = gt >> 4, x0 = cg * NC;
-    const uint32_t abase = smem_u32(sA + g * kGABytes) + (uint32_t)((d >> 1) * kGLboA + (d & 1) * 8);
+    const uint32_t abase0 = smem_u32(sA) + (uint32_t)((d >> 1) * kGLboA + (d & 1) * 8);
     // column c of the window = input column x0 - 1 + c: byte offset within a row (clamped into the row) and 0/1 mask
     int coff[NC + 2];
     float cm[NC + 2];
@@ -628,6 +630,8 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
 #endif
     for (int n = g; n < total; n += kWsG, ++k) {
       const int j = n / nch, kc = n - j * nch;
+      const int stage = n % kWsS, use = n / kWsS;  // ring stage of the item and how often it has been used before
+      const uint32_t abase = abase0 + (uint32_t)(stage * kGABytes);
       const unsigned tile = blockIdx.x + (unsigned)j * gridDim.x, b = tile / (unsigned)p.nbands;
       const int band = (int)(tile - b * (unsigned)p.nbands), r0 = band * R;
       const int nrows = min(R, H - r0) + 2;  // input rows r0 - 1 .. of the band (rows outside the clip are zeros)
@@ -655,7 +659,7 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
       }
       {
         WSP_T0();
-        if (k >= 1) mbar_wait(bEmpty + 8 * g, (k - 1) & 1);  // the MMAs that read this group's stage have retired
+        if (use >= 1) mbar_wait(bEmpty + 8 * stage, (uint32_t)(use - 1) & 1u);  // the MMAs that read this stage last have retired
         WSP_ADD(pw);
       }
       if (act) {
@@ -703,7 +707,7 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
       }
       fence_proxy_async();
       __syncwarp();
-      if (lane == 0) mbar_arrive(bFull + 8 * g);
+      if (lane == 0) mbar_arrive(bFull + 8 * stage);
     }
 #ifdef KWS_WS_PROFILE
     if (blockIdx.x == 3 && (tid % kWsGT) == 0) printf("producer group %d: total %lld wait_empty %lld items %u\n", g, clock64() - wsp_start, wsp_pw, k);
@@ -755,13 +759,13 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
     int bs = 0, pbs = 0, kc2 = 2 % nch;          // weight ring stage of item n and of item n - 1; K chunk of item n + 2
     uint32_t bph = 0, pbph = 0;                   // their phases
     for (int n = 0; n < total; ++n) {
-      const int g = n & (kWsG - 1);
+      const int g = n % kWsS;  // A ring stage of the item
       if (kc == 0 && j > 0) {  // tile boundary: the accumulator must be drained by its four warps before it is overwritten
         prefetch_tile(j + 1);
         { WSP_T0(); epilogue(j - 1); WSP_ADD(epi); }
         { WSP_T0(); mbar_wait(bAccFree, (uint32_t)(j - 1) & 1u); WSP_ADD(free); }
       }
-      { WSP_T0(); mbar_wait(bFull + 8 * g, (uint32_t)(n >> 2) & 1u); WSP_ADD(full); }
+      { WSP_T0(); mbar_wait(bFull + 8 * g, (uint32_t)(n / kWsS) & 1u); WSP_ADD(full); }
       { WSP_T0(); mbar_wait(bBfull + 8 * bs, bph); WSP_ADD(bfull); }
       tc_fence_after();
       const uint64_t ad = adesc0 + (uint64_t)((uint32_t)g * a_stage), bd = bdesc0 + (uint64_t)((uint32_t)bs * b_stage);
@@ -1181,7 +1185,7 @@ int launch_dscnn_gemm(kws_handle_t h, const float* feats_dev, int64_t B, int T, 
   // shared-memory rings fit, else the chunk-synchronous one (KWS_GEMM_WS=0 forces the latter, for A/B runs)
   static const bool ws_env = [] { const char* e = std::getenv("KWS_GEMM_WS"); return !(e && e[0] == '0'); }();
   const int nch_blk = (C + kGKC - 1) / kGKC;
-  const size_t smem_ws = (size_t)kWsG * kGABytes + (size_t)kWsBS * (g->npad / 8) * kGSbo + (size_t)9 * nch_blk * kGKC * 4 +
+  const size_t smem_ws = (size_t)kWsS * kGABytes + (size_t)kWsBS * (g->npad / 8) * kGSbo + (size_t)9 * nch_blk * kGKC * 4 +
                          (size_t)g->npad * 4;
   const bool ws_fits = ws_env && smem_ws <= 227 * 1024;
   if (ws_fits) {
