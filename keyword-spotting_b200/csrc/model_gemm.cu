@@ -744,8 +744,8 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
     };
     prefetch_tile(0);
     prefetch_tile(1);
-    if (total > 0) request_b(0, 0);
-    if (total > 1) request_b(1, 1 % nch);
+    for (int i = 0; i < kWsBS - 1; ++i)
+      if (total > i) request_b(i, i % nch);
     int j = 0, kc = 0;
     WSP_DECL(epi); WSP_DECL(free); WSP_DECL(full); WSP_DECL(bfull); WSP_DECL(bempty);
 #ifdef KWS_WS_PROFILE
@@ -756,7 +756,7 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
     const uint32_t a_stage = kGABytes >> 4, b_stage = (uint32_t)bbytes >> 4, b_half = (uint32_t)((p.nhalf / 8) * kGSbo) >> 4;
     const bool two_halves = p.nh == 2;
     const uint32_t tmem_h1 = tmem + (uint32_t)p.nhalf;
-    int bs = 0, pbs = 0, kc2 = 2 % nch;          // weight ring stage of item n and of item n - 1; K chunk of item n + 2
+    int bs = 0, pbs = 0, kc2 = (kWsBS - 1) % nch;  // weight ring stage of item n and of item n - 1; K chunk of item n + kWsBS - 1
     uint32_t bph = 0, pbph = 0;                   // their phases
     for (int n = 0; n < total; ++n) {
       const int g = n % kWsS;  // A ring stage of the item
@@ -782,9 +782,9 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
       tc_commit_elect(bEmpty + 8 * g);
       tc_commit_elect(bBempty + 8 * bs);
       if (kc == nch - 1) tc_commit_elect(bAccFull);
-      if (n + 2 < total) {  // weights of item n + 2 go where item n - 1's were: wait until its MMAs have retired
+      if (n + kWsBS - 1 < total) {  // weights of item n + kWsBS - 1 go where item n - 1's were: wait until its MMAs have retired
         { WSP_T0(); if (n >= 1) mbar_wait(bBempty + 8 * pbs, pbph); WSP_ADD(bempty); }
-        request_b(n + 2, kc2);
+        request_b(n + kWsBS - 1, kc2);
       }
       pbs = bs;
       pbph = bph;
