@@ -446,8 +446,9 @@ __global__ void __launch_bounds__(256) conv1_bwd_kernel(const float* __restrict_
       const long long gp = tile * TP + px;
       float v = 0.f;
       if (gp < npix) {
-        const int wo = (int)(gp % W1), ho = (int)((gp / W1) % H1);
-        const long long b = gp / ((long long)W1 * H1);
+        int wo, ho;  // 32-bit division when the index fits: the 64-bit % and / here cost more than the gradient's FMAs
+        long long b;
+        split_pixel(gp, W1, H1, &b, &ho, &wo);
         const int fr = 2 * ho - 2 + ki, fc = 2 * wo - 2 + kj;
         if (fr >= 0 && fr < T && fc >= 0 && fc < F) v = feats[(b * T + fr) * F + fc];
       }
