@@ -416,21 +416,21 @@ __global__ void __launch_bounds__(256) dw_bwd_rows_kernel(const float* __restric
 
 // conv1 (10x10, stride 2, padding 2, one input channel) + ReLU backward: dW[c][tap] += dY[px][c] * patch[px][tap]
 //   l0 [B,H1,W1,C] saved conv1 output, dl0 gradient w.r.t. it (pre-mask), feats [B,T,F]
-__global__ void __launch_bounds__(256) conv1_bwd_kernel(const float* __restrict__ l0, const float* __restrict__ dl0,
+__global__ void __launch_bounds__(320) conv1_bwd_kernel(const float* __restrict__ l0, const float* __restrict__ dl0,
                                                         const float* __restrict__ feats, float* __restrict__ g_w /*[C][100]*/,
                                                         float* __restrict__ g_b, long long B, int T, int F, int H1, int W1) {
   constexpr int C = kTC, TP = 32;
   __shared__ __align__(16) float s_dy[TP * C];
-  __shared__ float s_col[TP * 100];
+  __shared__ __align__(16) float s_col[TP * 100];
   const int tid = threadIdx.x, c = tid & 63, tg = tid >> 6;
-  float acc[25];
+  float acc[20];  // 64 channels x 5 groups of 20 taps: a group's taps of a pixel are five 16-byte shared-memory reads
 #pragma unroll
-  for (int i = 0; i < 25; ++i) acc[i] = 0.f;
+  for (int i = 0; i < 20; ++i) acc[i] = 0.f;
   float accb = 0.f;
   const long long npix = B * H1 * (long long)W1, ntiles = (npix + TP - 1) / TP;
   for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     __syncthreads();
-    for (int idx = tid; idx < TP * (C / 4); idx += 256) {
+    for (int idx = tid; idx < TP * (C / 4); idx += 320) {
       const int px = idx >> 4, q = idx & 15;
       const long long gp = tile * TP + px;
       float4 dy = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -441,7 +441,7 @@ __global__ void __launch_bounds__(256) conv1_bwd_kernel(const float* __restrict_
       }
       reinterpret_cast<float4*>(s_dy + px * C)[q] = dy;
     }
-    for (int idx = tid; idx < TP * 100; idx += 256) {
+    for (int idx = tid; idx < TP * 100; idx += 320) {
       const int px = idx / 100, tap = idx - px * 100, ki = tap / 10, kj = tap - ki * 10;
       const long long gp = tile * TP + px;
       float v = 0.f;
@@ -459,12 +459,19 @@ __global__ void __launch_bounds__(256) conv1_bwd_kernel(const float* __restrict_
     for (int px = 0; px < TP; ++px) {
       const float a = s_dy[px * C + c];
       if (tg == 0) accb += a;
+      const float4* col = reinterpret_cast<const float4*>(s_col + px * 100 + tg * 20);
 #pragma unroll
-      for (int i = 0; i < 25; ++i) acc[i] = fmaf(a, s_col[px * 100 + tg * 25 + i], acc[i]);
+      for (int i = 0; i < 5; ++i) {
+        const float4 v = col[i];
+        acc[4 * i] = fmaf(a, v.x, acc[4 * i]);
+        acc[4 * i + 1] = fmaf(a, v.y, acc[4 * i + 1]);
+        acc[4 * i + 2] = fmaf(a, v.z, acc[4 * i + 2]);
+        acc[4 * i + 3] = fmaf(a, v.w, acc[4 * i + 3]);
+      }
     }
   }
 #pragma unroll
-  for (int i = 0; i < 25; ++i) atomicAdd(&g_w[c * 100 + tg * 25 + i], acc[i]);
+  for (int i = 0; i < 20; ++i) atomicAdd(&g_w[c * 100 + tg * 20 + i], acc[i]);
   if (tg == 0) atomicAdd(&g_b[c], accb);
 }
 
@@ -602,7 +609,7 @@ int kws_train_forward_backward(kws_handle_t h, const float* params_dev, const fl
   {
     const long long ntiles = (B * (long long)H1 * W1 + 31) / 32;
     long long g = ntiles < h->sm_count * 4LL ? ntiles : h->sm_count * 4LL;
-    conv1_bwd_kernel<<<(unsigned)g, 256, 0, st>>>(w.L[0], dout, feats_dev, grads_dev + fl.c1w(), grads_dev + fl.c1b(), B,
+    conv1_bwd_kernel<<<(unsigned)g, 320, 0, st>>>(w.L[0], dout, feats_dev, grads_dev + fl.c1w(), grads_dev + fl.c1b(), B,
                                                   (int)T, (int)F, H1, W1);
     KWS_CHECK_LAUNCH(h);
   }
