@@ -90,38 +90,38 @@ pw_bwd_tc_kernel(const float* __restrict__ out, const float* __restrict__ dout, 
   // The global loads of tile i + 1 are issued right after the MMAs of tile i and land in registers while those MMAs
   // and the epilogue run (one CTA per SM: nothing else would hide the L2 / HBM latency): dy = masked upstream
   // gradient, dv = saved depthwise output, per item.
-  float4 dy[2], dv[2];
+  // The loaded values are kept RAW (layer output ro, upstream gradient rg): masking them here would make the thread wait
+  // for its own loads right after issuing them (ncu: 40 % of the kernel's warp samples sat on that select).
+  float4 ro[2], rg[2], dv[2];
   auto load_tile = [&](long long tile) {
 #pragma unroll
     for (int it = 0; it < 2; ++it) {
       const long long gp = tile * kPTile + pxb + 32 * it;
-      dy[it] = make_float4(0.f, 0.f, 0.f, 0.f);
-      dv[it] = dy[it];
+      ro[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+      rg[it] = ro[it];
+      dv[it] = ro[it];
       if (gp < npix) {
         int wo, ho;
         long long b;
         split_pixel(gp, Wo, Ho, &b, &ho, &wo);
-        const float4 o = reinterpret_cast<const float4*>(out + gp * kPC)[q];
-        float4 g;
-        if (dpooled) {
-          g = reinterpret_cast<const float4*>(dpooled + b * kPC)[q];
-          g.x *= inv_area; g.y *= inv_area; g.z *= inv_area; g.w *= inv_area;
-        } else {
-          g = reinterpret_cast<const float4*>(dout + gp * kPC)[q];
-        }
-        dy[it] = make_float4(o.x > 0.f ? g.x : 0.f, o.y > 0.f ? g.y : 0.f, o.z > 0.f ? g.z : 0.f, o.w > 0.f ? g.w : 0.f);
+        ro[it] = reinterpret_cast<const float4*>(out + gp * kPC)[q];
+        rg[it] = dpooled ? reinterpret_cast<const float4*>(dpooled + b * kPC)[q] : reinterpret_cast<const float4*>(dout + gp * kPC)[q];
         if (ho >= 1 && ho <= H && wo >= 1 && wo <= W)
           dv[it] = reinterpret_cast<const float4*>(d_io + ((b * H + ho - 1) * W + wo - 1) * kPC)[q];
       }
     }
   };
+  const float gscale = dpooled ? inv_area : 1.0f;
   if ((long long)blockIdx.x < ntiles) load_tile(blockIdx.x);
   for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
 #pragma unroll
     for (int it = 0; it < 2; ++it) {
       const int px = pxb + 32 * it;
       float yh[4], yl[4], dh[4], dl[4];
-      split_tf32(dy[it].x, yh[0], yl[0]); split_tf32(dy[it].y, yh[1], yl[1]); split_tf32(dy[it].z, yh[2], yl[2]); split_tf32(dy[it].w, yh[3], yl[3]);
+      const float4 o = ro[it], g = rg[it];  // dY = upstream gradient where the layer's output is positive
+      const float4 dyv = make_float4(o.x > 0.f ? g.x * gscale : 0.f, o.y > 0.f ? g.y * gscale : 0.f, o.z > 0.f ? g.z * gscale : 0.f,
+                                     o.w > 0.f ? g.w * gscale : 0.f);
+      split_tf32(dyv.x, yh[0], yl[0]); split_tf32(dyv.y, yh[1], yl[1]); split_tf32(dyv.z, yh[2], yl[2]); split_tf32(dyv.w, yh[3], yl[3]);
       split_tf32(dv[it].x, dh[0], dl[0]); split_tf32(dv[it].y, dh[1], dl[1]); split_tf32(dv[it].z, dh[2], dl[2]); split_tf32(dv[it].w, dh[3], dl[3]);
       // A1 (rows px, K = co): one 16-byte chunk
       const uint32_t o1 = kmaj_off(px, 4 * q);
