@@ -35,6 +35,11 @@ constexpr uint32_t kPIdesc2 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(k
 __device__ __forceinline__ uint32_t kmaj_off(int row, int k) {  // byte offset of element (row, k) in a K-major image
   return (uint32_t)((row >> 3) * kPSbo + (k >> 2) * kPLbo + (row & 7) * 16 + (k & 3) * 4);
 }
+// pull [ptr, ptr + bytes) into L2 (bytes a multiple of 16, ptr 16-byte aligned): the register loads that follow one tile
+// later then see L2 latency, which the MMAs and the drain of a tile do hide, instead of DRAM latency, which they do not
+__device__ __forceinline__ void l2_prefetch(const void* ptr, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(ptr), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ void split_tf32(float x, float& hi, float& lo) {
   hi = to_tf32(x);
   lo = to_tf32(x - hi);
@@ -112,8 +117,25 @@ pw_bwd_tc_kernel(const float* __restrict__ out, const float* __restrict__ dout, 
     }
   };
   const float gscale = dpooled ? inv_area : 1.0f;
+  // tile t's inputs are contiguous ranges: 64 pixels of out / dout, and the interior pixels among them of d_io
+  auto prefetch_tile = [&](long long tile) {
+    if (tid == 0 && tile < ntiles) {
+      const long long gp0 = tile * kPTile;
+      const uint32_t bytes = (uint32_t)(min((long long)kPTile, npix - gp0) * kPC * 4);
+      l2_prefetch(out + gp0 * kPC, bytes);
+      if (!dpooled) l2_prefetch(dout + gp0 * kPC, bytes);
+      int wo, ho;
+      long long b;
+      split_pixel(gp0, Wo, Ho, &b, &ho, &wo);
+      const int hi = min(max(ho - 1, 0), H - 1), wi = min(max(wo - 1, 0), W - 1);
+      const long long d0 = (b * H + hi) * W + wi, dn = min((long long)kPTile, B * H * (long long)W - d0);
+      l2_prefetch(d_io + d0 * kPC, (uint32_t)(dn * kPC * 4));
+    }
+  };
   if ((long long)blockIdx.x < ntiles) load_tile(blockIdx.x);
+  prefetch_tile((long long)blockIdx.x + gridDim.x);
   for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    prefetch_tile(tile + 2LL * gridDim.x);
 #pragma unroll
     for (int it = 0; it < 2; ++it) {
       const int px = pxb + 32 * it;
@@ -279,9 +301,21 @@ pw_fwd_tc_kernel(const float* __restrict__ d, float* __restrict__ out, const flo
       }
     }
   };
+  auto prefetch_tile = [&](long long tile) {  // the interior pixels of a tile are (nearly) one contiguous range of d
+    if (tid == 0 && tile < ntiles) {
+      int wo, ho;
+      long long b;
+      split_pixel(tile * kFTile, Wo, Ho, &b, &ho, &wo);
+      const int hi = min(max(ho - 1, 0), H - 1), wi = min(max(wo - 1, 0), W - 1);
+      const long long d0 = (b * H + hi) * W + wi, dn = min((long long)kFTile, B * H * (long long)W - d0);
+      l2_prefetch(d + d0 * kPC, (uint32_t)(dn * kPC * 4));
+    }
+  };
   if ((long long)blockIdx.x < ntiles) load_tile(blockIdx.x);
+  prefetch_tile((long long)blockIdx.x + gridDim.x);
   uint32_t parity = 0;
   for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    prefetch_tile(tile + 2LL * gridDim.x);
 #pragma unroll
     for (int it = 0; it < 4; ++it) {
       float h4[4], l4[4];
