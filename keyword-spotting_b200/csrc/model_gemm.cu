@@ -39,6 +39,7 @@ struct GemmParams {
   int H, W, C, T, F;   // H x W: output (interior) grid of the layer
   int R, nbands;       // tile = R whole rows of one clip (R * W <= 128), nbands = ceil(H / R)
   int kvalid, npad, nh, nhalf, nchunks, tmem_cols, patch_bytes;
+  int nslots;  // dscnn_block_ws_kernel: accumulator slots of nhalf TMEM columns
   // last block only: instead of the activation, write per-tile channel sums (the global average pool's partial sums,
   // scaled so that pool_fc_kernel's mean over nbands + 1 rows is the mean over the padded output) -- the largest
   // activation of the network is never written or re-read
@@ -375,16 +376,21 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_gemm_kernel(const GemmParams p) 
 //     (full / empty mbarriers, tcgen05.commit releases a stage), so there is no CTA-wide barrier anywhere;
 //   * the issue warp streams the weight chunks through a 3-stage TMA ring, fires the chunk's MMAs in order, and
 //     pulls the next tile's whole input patch (one contiguous range) into L2 with bulk prefetches;
-//   * one accumulator (N = 288 columns of the 512), drained by warps 12..15, one TMEM lane quarter each (the issue
-//     warp takes the fourth: it has nothing to issue while the accumulator is busy).  The producers never touch the
-//     accumulator, so they run up to four chunks ahead into the next tile while it drains, and the MMAs catch up
-//     afterwards (a chunk multiplies faster than it is produced).
+//   * the accumulator is drained by four warps of their own (12..15, one TMEM lane quarter each) out of a ring of
+//     accumulator slots, so the issue warp (16) never drains and a tile's MMAs overlap the previous tile's drain:
+//     with two N halves of 144 columns three half-slots fit the 512 TMEM columns (tile j's halves in slots 2j % 3
+//     and (2j + 1) % 3), one-half layers get two whole slots, halves wider than 170 columns two half-slots (each
+//     half then waits for the previous tile's same half only).  17 warps x 120 registers fill the register file.
 constexpr int kWsG = 4;     // producer groups
 constexpr int kWsS = 5;     // A-ring stages (item n uses stage n % kWsS: one more than groups, so that production runs on
                             // while the accumulator drains and the MMAs of the four waiting chunks catch up)
 constexpr int kWsGT = 96;   // threads per group: 16 channel pairs x 6 column groups
 constexpr int kWsBS = 3;    // weight-chunk ring stages
-constexpr int kWsEpi = 4;   // draining warps: 12, 13, 14 and the issue warp 15 (TMEM lane quarter = warp % 4)
+constexpr int kWsEpi = 4;   // draining warps 12..15 (TMEM lane quarter = warp % 4)
+constexpr int kWsT = 640;   // five warpgroups: 12 producer warps | 4 drain warps | the issue warp + 3 idle warps.  Every
+                            // SM sub-partition holds 3 producer warps, a drain warp and a warp of the last group: launched
+                            // at 96 registers, the last group shrinks to 40 (setmaxnreg) and the producers grow to 112, the
+                            // drain warps to 104 (3 x 112 + 104 + 40 = 480 = 5 x 96 per sub-partition lane)
 
 #ifdef KWS_WS_PROFILE
 #include <cstdio>
@@ -397,9 +403,9 @@ constexpr int kWsEpi = 4;   // draining warps: 12, 13, 14 and the issue warp 15 
 #define WSP_ADD(n)
 #endif
 template <int NC, int PF, bool WREG>
-__global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams p) {
+__global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParams p) {
   extern __shared__ __align__(128) unsigned char smem[];
-  __shared__ __align__(8) unsigned long long s_bar[2 * kWsS + 2 * kWsBS + 2];
+  __shared__ __align__(8) unsigned long long s_bar[2 * kWsS + 2 * kWsBS + 2 + 3];
   __shared__ uint32_t s_tmem;
   const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
   const int bbytes = (p.npad / 8) * kGSbo;
@@ -409,7 +415,7 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
   float* sW = reinterpret_cast<float*>(sB + kWsBS * (size_t)bbytes);  // [chunk][tap][32 channels]
   float* sBias = sW + 9 * kpad;                              // [npad]
   const uint32_t bFull = smem_u32(&s_bar[0]), bEmpty = bFull + 8 * kWsS, bBfull = bEmpty + 8 * kWsS,
-                 bBempty = bBfull + 8 * kWsBS, bAccFull = bBempty + 8 * kWsBS, bAccFree = bAccFull + 8;
+                 bBempty = bBfull + 8 * kWsBS, bAccFull = bBempty + 8 * kWsBS, bFreeS = bAccFull + 16;
   if (tid == 0) {
     for (int g = 0; g < kWsS; ++g) {
       mbar_init(bFull + 8 * g, 3);   // one arrival per producer warp of the group
@@ -419,8 +425,9 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
       mbar_init(bBfull + 8 * s, 1);
       mbar_init(bBempty + 8 * s, 1);
     }
-    mbar_init(bAccFull, 1);
-    mbar_init(bAccFree, kWsEpi);
+    mbar_init(bAccFull, 1);  // MMAs of an even / odd tile retired
+    mbar_init(bAccFull + 8, 1);
+    for (int s = 0; s < 3; ++s) mbar_init(bFreeS + 8 * s, kWsEpi);  // accumulator slot read out by its four warps
     fence_mbar_init();
   }
   if (warp == 0) {
@@ -428,14 +435,14 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
                  "r"((uint32_t)p.tmem_cols));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
   }
-  for (int i = tid; i < 9 * kpad; i += kGT) {
+  for (int i = tid; i < 9 * kpad; i += kWsT) {
     const int kcw = i / (9 * kGKC), r = i - kcw * 9 * kGKC, t = r >> 5, k = kcw * kGKC + (r & 31);
     sW[i] = k < p.C ? __ldg(p.dw_w + t * p.C + k) : 0.f;
   }
-  for (int i = tid; i < p.npad; i += kGT) sBias[i] = i < p.C ? __ldg(p.bias + i) : 0.f;
+  for (int i = tid; i < p.npad; i += kWsT) sBias[i] = i < p.C ? __ldg(p.bias + i) : 0.f;
   // A ring starts as zeros: rows no pixel owns and channel quads past the channel count are never written, and
   // what the MMA reads there must be finite (it meets zero weight rows, or lands in accumulator rows nobody reads)
-  for (int i = tid; i < kWsS * kGABytes / 16; i += kGT) reinterpret_cast<float4*>(sA)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int i = tid; i < kWsS * kGABytes / 16; i += kWsT) reinterpret_cast<float4*>(sA)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   fence_proxy_async();
   tc_fence_before();
   __syncthreads();
@@ -453,9 +460,19 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
   // 8 consecutive channels of one pixel; after one exchange between neighbouring lanes each of them stores 16
   // bytes of a 64-byte run per pixel (the 32x32b shape -- one pixel per thread -- made every store instruction
   // touch 32 different 1104-byte-strided lines, 16 bytes each: 30 % of the kernel's L1 cycles).
+  // Accumulator slots: N half h (counted over the CTA's tiles: h = nh j, nh j + 1) lives in slot h % ns at columns
+  // (h % ns) nhalf; its MMAs wait until the slot's previous tenant has been read out (bFreeS[slot], one phase per use).
+  const int ns = p.nslots;
+  const int dr_hp = p.nhalf >> 4;                                       // 16-column pairs per N half
+  const int dr_nr = p.npad >> 5;                                        // rounds of two pairs
+  const int dr_ra = p.nh == 2 ? (dr_hp - 1) >> 1 : -1;                  // round whose loads complete the first of two halves
   auto epilogue = [&](int j) {
-    mbar_wait_idle(bAccFull, (uint32_t)j & 1u, 32);
+    mbar_wait_idle(bAccFull + 8 * (uint32_t)(j & 1), (uint32_t)(j >> 1) & 1u, 32);
     tc_fence_after();
+    const int s0 = (p.nh * j) % ns, s1 = (p.nh * j + 1) % ns;
+    const uint32_t col0 = (uint32_t)(s0 * p.nhalf), col1 = (uint32_t)(s1 * p.nhalf);
+    const uint32_t bar_a = bFreeS + 8 * (uint32_t)s0, bar_b = bFreeS + 8 * (uint32_t)(p.nh == 2 ? s1 : s0);
+    const int rs = 0, re = dr_nr;
     const unsigned tile = blockIdx.x + (unsigned)j * gridDim.x, b = tile / (unsigned)p.nbands;
     const int band = (int)(tile - b * (unsigned)p.nbands), r0 = band * R;
     const int lq = warp & 3, tq = lane & 3, tr = lane >> 2;
@@ -475,26 +492,35 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
       for (int ss = 0; ss < 2; ++ss) {
         const int pp = lq * 32 + hh * 16 + ss * 8 + tr, rl = pp / W, xq = pp - rl * W, y = r0 + rl;
         valid[hh][ss] = rl < R && y < H;
-        orow[hh][ss] = (valid[hh][ss] ? p.out + (((long long)b * (H + 2) + y + 1) * (W + 2) + xq + 1) * (long long)C : p.dump) + coff;
+        orow[hh][ss] = (valid[hh][ss] ? p.out + (((long long)b * (H + 2) + y + 1) * (W + 2) + xq + 1) * (long long)C : p.dump) + coff + 32 * rs;
       }
     float* prow = pool ? p.pool + ((long long)b * (4 * p.nbands + 1) + band * 4 + lq) * (long long)C : nullptr;
     const uint32_t ta = tmem + ((uint32_t)(lq * 32) << 16);
     // 16-lane halves without a pixel (the tile's last rows of TMEM lanes, short last bands) are neither loaded nor stored
     const int npix = min(R, H - r0) * W;
     const bool hv0 = lq * 32 < npix, hv1 = lq * 32 + 16 < npix;
-    auto load_round = [&](float (&v)[2][2][8], int cb) {  // two pairs of 8-column blocks x two 16-lane halves
+    auto load_round = [&](float (&v)[2][2][8], int r) {  // round r = pairs 2r, 2r + 1 of 8-column blocks x two 16-lane halves
 #pragma unroll
       for (int pr = 0; pr < 2; ++pr) {
-        if (hv0) tc_ld_16x256b_x2(ta + (uint32_t)(cb + 16 * pr), v[pr][0]);
-        if (hv1) tc_ld_16x256b_x2(ta + (16u << 16) + (uint32_t)(cb + 16 * pr), v[pr][1]);
+        const int i = 2 * r + pr;  // pair i holds channels 16 i ..: first or second N half
+        const uint32_t tc = i < dr_hp ? col0 + 16u * (uint32_t)i : col1 + 16u * (uint32_t)(i - dr_hp);
+        if (hv0) tc_ld_16x256b_x2(ta + tc, v[pr][0]);
+        if (hv1) tc_ld_16x256b_x2(ta + (16u << 16) + tc, v[pr][1]);
       }
     };
-    auto release = [&]() {  // the whole lane quarter is in registers: the accumulator may be overwritten
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bAccFree);
+    auto release = [&](int r) {  // after the loads of round r have landed in registers
+      if (r == dr_ra || r == dr_nr - 1) {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) {
+          if (r == dr_ra) mbar_arrive(bar_a);
+          if (r == dr_nr - 1) mbar_arrive(bar_b);
+        }
+      }
     };
-    auto process = [&](float (&v)[2][2][8], int cb, const bool guard) {
+    auto process = [&](float (&v)[2][2][8], int r) {
+      const int cb = 32 * r;
+      const bool guard = cb + 32 > C;  // only the round that holds the channel count's end needs a store predicate
 #ifdef KWS_WS_LDONLY  // timing experiment only: TMEM loads without the arithmetic and the stores
       if (v[0][0][0] != 1.2345e30f) return;
 #endif
@@ -567,35 +593,22 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
 #pragma unroll
         for (int ss = 0; ss < 2; ++ss) orow[hh][ss] += 32;
     };
-#ifdef KWS_WS_NODRAIN  // timing experiment only (results are wrong): the pipeline without the accumulator's drain
-    if (true) {
-#else
     if (!hv0 && !pool) {  // nothing of this tile lives in this lane quarter
-#endif
-      release();
-    } else {  // two register sets in rotation: the next round's TMEM loads are in flight while a round is stored
+      for (int r = rs; r < re; ++r) release(r);
+    } else if (rs < re) {  // two register sets in rotation: the next round's TMEM loads are in flight while a round is stored
       float va[2][2][8], vb[2][2][8];
-      load_round(va, 0);
-      int cb = 0;
-      for (; cb + 64 < p.npad; cb += 64) {
+      load_round(va, rs);
+      for (int r = rs;; r += 2) {
         tc_wait_ld();
-        load_round(vb, cb + 32);
-        process(va, cb, false);
+        if (r + 1 < re) load_round(vb, r + 1);
+        release(r);
+        process(va, r);
+        if (r + 1 >= re) break;
         tc_wait_ld();
-        load_round(va, cb + 64);
-        process(vb, cb + 32, false);
-      }
-      if (cb + 32 < p.npad) {
-        tc_wait_ld();
-        load_round(vb, cb + 32);
-        process(va, cb, false);
-        tc_wait_ld();
-        release();
-        process(vb, cb + 32, true);
-      } else {
-        tc_wait_ld();
-        release();
-        process(va, cb, true);
+        if (r + 2 < re) load_round(va, r + 2);
+        release(r + 1);
+        process(vb, r + 1);
+        if (r + 2 >= re) break;
       }
     }
     if (pool && band == 0 && lq == 0)  // one extra row per clip: the 2 (W + 2) + 2 H border pixels, all ReLU(bias)
@@ -605,6 +618,7 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
   };
 
   if (warp < kWsG * 3) {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 120;");
     // ---- producers ----
     // thread = (channel PAIR d of the chunk, NC adjacent columns): 16 pairs x 6 column groups.  With two channels per
     // thread the nine depthwise taps are 18 registers and stay resident for the item (four channels per thread had to
@@ -712,11 +726,14 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
 #ifdef KWS_WS_PROFILE
     if (blockIdx.x == 3 && (tid % kWsGT) == 0) printf("producer group %d: total %lld wait_empty %lld items %u\n", g, clock64() - wsp_start, wsp_pw, k);
 #endif
-  } else if (warp < kGT / 32 - 1) {
-    // ---- warps 12..14: drain only ----
+  } else if (warp < kWsG * 3 + kWsEpi) {
+    // ---- warps 12..15: drain only ----
     for (int j = 0; j < my_tiles; ++j) epilogue(j);
+  } else if (warp > kWsG * 3 + kWsEpi) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 24;");  // idle: they only complete the issue warp's warpgroup
   } else {
-    // ---- issue warp: weight-chunk TMA ring, MMAs in item order, L2 prefetch of the next tile, drain of lane quarter 3 ----
+    // ---- issue warp: weight-chunk TMA ring, MMAs in item order, L2 prefetch of the next tile ----
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 24;");
     const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(p.nhalf >> 3) << 17) | ((128u >> 4) << 24);
     auto request_b = [&](int n, int kc) {  // weight chunk kc of item n into ring stage n % kWsBS
       if (lane == 0) {
@@ -755,15 +772,20 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
     const uint64_t adesc0 = umma_desc(smem_u32(sA), kGLboA, kGSboA), bdesc0 = umma_desc(smem_u32(sB), 128u, kGSbo);
     const uint32_t a_stage = kGABytes >> 4, b_stage = (uint32_t)bbytes >> 4, b_half = (uint32_t)((p.nhalf / 8) * kGSbo) >> 4;
     const bool two_halves = p.nh == 2;
-    const uint32_t tmem_h1 = tmem + (uint32_t)p.nhalf;
+    uint32_t tmem_h0 = tmem, tmem_h1 = tmem + (uint32_t)p.nhalf;  // this tile's accumulator slots
     int bs = 0, pbs = 0, kc2 = (kWsBS - 1) % nch;  // weight ring stage of item n and of item n - 1; K chunk of item n + kWsBS - 1
     uint32_t bph = 0, pbph = 0;                   // their phases
     for (int n = 0; n < total; ++n) {
       const int g = n % kWsS;  // A ring stage of the item
-      if (kc == 0 && j > 0) {  // tile boundary: the accumulator must be drained by its four warps before it is overwritten
-        prefetch_tile(j + 1);
-        { WSP_T0(); epilogue(j - 1); WSP_ADD(epi); }
-        { WSP_T0(); mbar_wait(bAccFree, (uint32_t)(j - 1) & 1u); WSP_ADD(free); }
+      if (kc == 0) {  // tile boundary: this tile's accumulator slots must have been read out by their four warps
+        if (j > 0) prefetch_tile(j + 1);
+        const int h = p.nh * j, s0 = h % ns, s1 = (h + 1) % ns, u0 = h / ns, u1 = (h + 1) / ns;
+        WSP_T0();
+        if (u0 > 0) mbar_wait(bFreeS + 8 * (uint32_t)s0, (uint32_t)(u0 - 1) & 1u);
+        if (two_halves && u1 > 0) mbar_wait(bFreeS + 8 * (uint32_t)s1, (uint32_t)(u1 - 1) & 1u);
+        WSP_ADD(free);
+        tmem_h0 = tmem + (uint32_t)(s0 * p.nhalf);
+        tmem_h1 = tmem + (uint32_t)(s1 * p.nhalf);
       }
       { WSP_T0(); mbar_wait(bFull + 8 * g, (uint32_t)(n / kWsS) & 1u); WSP_ADD(full); }
       { WSP_T0(); mbar_wait(bBfull + 8 * bs, bph); WSP_ADD(bfull); }
@@ -775,13 +797,14 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
         if (ks > 0) break;
 #endif
         const uint32_t acc = (kc > 0 || ks > 0) ? 1u : 0u;
-        tc_mma_tf32_elect(tmem, ad + (uint64_t)(ks * ((2 * kGLboA) >> 4)), bd + (uint64_t)(ks * 16), idesc, acc);
+        tc_mma_tf32_elect(tmem_h0, ad + (uint64_t)(ks * ((2 * kGLboA) >> 4)), bd + (uint64_t)(ks * 16), idesc, acc);
         if (two_halves)
           tc_mma_tf32_elect(tmem_h1, ad + (uint64_t)(ks * ((2 * kGLboA) >> 4)), bd + (uint64_t)(b_half + ks * 16), idesc, acc);
       }
       tc_commit_elect(bEmpty + 8 * g);
       tc_commit_elect(bBempty + 8 * bs);
-      if (kc == nch - 1) tc_commit_elect(bAccFull);
+      if (kc == nch - 1) tc_commit_elect(bAccFull + 8 * (uint32_t)(j & 1));
+
       if (n + kWsBS - 1 < total) {  // weights of item n + kWsBS - 1 go where item n - 1's were: wait until its MMAs have retired
         { WSP_T0(); if (n >= 1) mbar_wait(bBempty + 8 * pbs, pbph); WSP_ADD(bempty); }
         request_b(n + kWsBS - 1, kc2);
@@ -801,7 +824,6 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_block_ws_kernel(const GemmParams
 #ifdef KWS_WS_PROFILE
     if (blockIdx.x == 3 && lane == 0) printf("issuer: total %lld epilogue %lld wait_accfree %lld wait_full %lld wait_bfull %lld wait_bempty %lld tiles %d items %d\n", clock64() - wsp_start, wsp_epi, wsp_free, wsp_full, wsp_bfull, wsp_bempty, my_tiles, total);
 #endif
-    if (my_tiles > 0) epilogue(my_tiles - 1);
   }
   tc_fence_before();
   __syncthreads();
@@ -1203,7 +1225,11 @@ int launch_dscnn_gemm(kws_handle_t h, const float* feats_dev, int64_t B, int T, 
     p.nchunks = g->nchunks[l + 1];
     unsigned grid = set_grid(H, W);
     bool ws = ws_fits && W <= 36;
+    p.tmem_cols = g->tmem_cols;
     if (ws) {  // tile = as many whole rows as fit 128 pixels; one persistent CTA per SM
+      p.nslots = g->nh == 2 && 3 * g->nhalf <= 512 ? 3 : 2;
+      p.tmem_cols = 32;
+      while (p.tmem_cols < p.nslots * g->nhalf) p.tmem_cols *= 2;
       p.R = 128 / W < H ? 128 / W : H;
       p.nbands = (H + p.R - 1) / p.R;
       const long long t = B * p.nbands;
@@ -1217,9 +1243,9 @@ int launch_dscnn_gemm(kws_handle_t h, const float* feats_dev, int64_t B, int T, 
     const int pool_rows = ws ? 4 * p.nbands + 1 : p.nbands + 1;
     auto launch_block = [&]() {
       if (!ws) dscnn_gemm_kernel<1><<<grid, kGT, smem_bytes, st>>>(p);
-      else if (W <= 24) dscnn_block_ws_kernel<4, 2, true><<<grid, kGT, smem_ws, st>>>(p);
-      else if (W <= 30) dscnn_block_ws_kernel<5, 2, true><<<grid, kGT, smem_ws, st>>>(p);
-      else dscnn_block_ws_kernel<6, 1, true><<<grid, kGT, smem_ws, st>>>(p);
+      else if (W <= 24) dscnn_block_ws_kernel<4, 2, true><<<grid, kWsT, smem_ws, st>>>(p);
+      else if (W <= 30) dscnn_block_ws_kernel<5, 2, true><<<grid, kWsT, smem_ws, st>>>(p);
+      else dscnn_block_ws_kernel<6, 1, true><<<grid, kWsT, smem_ws, st>>>(p);
     };
     if (l == nb - 1) {  // the pooled rows replace the last activation (see GemmParams::pool)
       p.pool = nxt;
