@@ -402,11 +402,18 @@ constexpr int kWsT = 640;   // five warpgroups: 12 producer warps | 4 drain warp
 #define WSP_T0()
 #define WSP_ADD(n)
 #endif
+// waits of the issue warp / the drain warps (A/B hook: try_wait with a 2 us suspendTimeHint instead of polling took the
+// polling instructions off the schedulers but woke up late: 207 K -> 201 K clips/s)
+#define WS_WAIT(bar, par) mbar_wait(bar, par)
+#define WS_WAIT_ACC(bar, par) mbar_wait_idle(bar, par, 32)
 template <int NC, int PF, bool WREG>
 __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParams p) {
   extern __shared__ __align__(128) unsigned char smem[];
   __shared__ __align__(8) unsigned long long s_bar[2 * kWsS + 2 * kWsBS + 2 + 3];
   __shared__ uint32_t s_tmem;
+#ifdef KWS_WS_PROFILE
+  __shared__ long long s_prof[8];
+#endif
   const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
   const int bbytes = (p.npad / 8) * kGSbo;
   unsigned char* sA = smem;                                  // [kWsS][kGABytes]
@@ -466,8 +473,9 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
   const int dr_hp = p.nhalf >> 4;                                       // 16-column pairs per N half
   const int dr_nr = p.npad >> 5;                                        // rounds of two pairs
   const int dr_ra = p.nh == 2 ? (dr_hp - 1) >> 1 : -1;                  // round whose loads complete the first of two halves
+  WSP_DECL(aw);
   auto epilogue = [&](int j) {
-    mbar_wait_idle(bAccFull + 8 * (uint32_t)(j & 1), (uint32_t)(j >> 1) & 1u, 32);
+    { WSP_T0(); WS_WAIT_ACC(bAccFull + 8 * (uint32_t)(j & 1), (uint32_t)(j >> 1) & 1u); WSP_ADD(aw); }
     tc_fence_after();
     const int s0 = (p.nh * j) % ns, s1 = (p.nh * j + 1) % ns;
     const uint32_t col0 = (uint32_t)(s0 * p.nhalf), col1 = (uint32_t)(s1 * p.nhalf);
@@ -626,7 +634,8 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
     // were competing with), and a row of the window is NC + 2 eight-byte loads.
     const int g = warp / 3, gt = tid - g * kWsGT;
     const int d = gt & 15, cg = gt >> 4, x0 = cg * NC;
-    const uint32_t abase0 = smem_u32(sA) + (uint32_t)((d >> 1) * kGLboA + (d & 1) * 8);
+    uint32_t abase0 = smem_u32(sA) + (uint32_t)((d >> 1) * kGLboA + (d & 1) * 8);
+    asm volatile("" : "+r"(abase0));  // opaque, like coff[] below
     // column c of the window = input column x0 - 1 + c: byte offset within a row (clamped into the row) and 0/1 mask
     int coff[NC + 2];
     float cm[NC + 2];
@@ -635,6 +644,7 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
       const int xx = x0 - 1 + c, xc = xx < 0 ? 0 : (xx >= W ? W - 1 : xx);
       coff[c] = xc * C * 4;
       cm[c] = xx == xc ? 1.f : 0.f;
+      asm volatile("" : "+r"(coff[c]));  // opaque: keeps ptxas from recomputing the offset at every load (-5 % time)
     }
     const long long rowbytes = (long long)W * C * 4;
     uint32_t k = 0;
@@ -728,7 +738,13 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
 #endif
   } else if (warp < kWsG * 3 + kWsEpi) {
     // ---- warps 12..15: drain only ----
+#ifdef KWS_WS_PROFILE
+    const long long wsp_start = clock64();
+#endif
     for (int j = 0; j < my_tiles; ++j) epilogue(j);
+#ifdef KWS_WS_PROFILE
+    if (blockIdx.x == 3 && lane == 0) printf("drain warp %d: total %lld wait_accfull %lld\n", warp, clock64() - wsp_start, wsp_aw);
+#endif
   } else if (warp > kWsG * 3 + kWsEpi) {
     asm volatile("setmaxnreg.dec.sync.aligned.u32 24;");  // idle: they only complete the issue warp's warpgroup
   } else {
@@ -759,12 +775,14 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
       }
       __syncwarp();
     };
-    prefetch_tile(0);
-    prefetch_tile(1);
+#ifndef KWS_WS_PFAHEAD
+#define KWS_WS_PFAHEAD 1
+#endif
+    for (int jj = 0; jj <= KWS_WS_PFAHEAD; ++jj) prefetch_tile(jj);
     for (int i = 0; i < kWsBS - 1; ++i)
       if (total > i) request_b(i, i % nch);
     int j = 0, kc = 0;
-    WSP_DECL(epi); WSP_DECL(free); WSP_DECL(full); WSP_DECL(bfull); WSP_DECL(bempty);
+    WSP_DECL(free); WSP_DECL(full); WSP_DECL(bfull); WSP_DECL(bempty);
 #ifdef KWS_WS_PROFILE
     const long long wsp_start = clock64();
 #endif
@@ -778,17 +796,17 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
     for (int n = 0; n < total; ++n) {
       const int g = n % kWsS;  // A ring stage of the item
       if (kc == 0) {  // tile boundary: this tile's accumulator slots must have been read out by their four warps
-        if (j > 0) prefetch_tile(j + 1);
+        if (j > 0) prefetch_tile(j + KWS_WS_PFAHEAD);
         const int h = p.nh * j, s0 = h % ns, s1 = (h + 1) % ns, u0 = h / ns, u1 = (h + 1) / ns;
         WSP_T0();
-        if (u0 > 0) mbar_wait(bFreeS + 8 * (uint32_t)s0, (uint32_t)(u0 - 1) & 1u);
-        if (two_halves && u1 > 0) mbar_wait(bFreeS + 8 * (uint32_t)s1, (uint32_t)(u1 - 1) & 1u);
+        if (u0 > 0) WS_WAIT(bFreeS + 8 * (uint32_t)s0, (uint32_t)(u0 - 1) & 1u);
+        if (two_halves && u1 > 0) WS_WAIT(bFreeS + 8 * (uint32_t)s1, (uint32_t)(u1 - 1) & 1u);
         WSP_ADD(free);
         tmem_h0 = tmem + (uint32_t)(s0 * p.nhalf);
         tmem_h1 = tmem + (uint32_t)(s1 * p.nhalf);
       }
-      { WSP_T0(); mbar_wait(bFull + 8 * g, (uint32_t)(n / kWsS) & 1u); WSP_ADD(full); }
-      { WSP_T0(); mbar_wait(bBfull + 8 * bs, bph); WSP_ADD(bfull); }
+      { WSP_T0(); WS_WAIT(bFull + 8 * g, (uint32_t)(n / kWsS) & 1u); WSP_ADD(full); }
+      { WSP_T0(); WS_WAIT(bBfull + 8 * bs, bph); WSP_ADD(bfull); }
       tc_fence_after();
       const uint64_t ad = adesc0 + (uint64_t)((uint32_t)g * a_stage), bd = bdesc0 + (uint64_t)((uint32_t)bs * b_stage);
 #pragma unroll
@@ -806,7 +824,7 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
       if (kc == nch - 1) tc_commit_elect(bAccFull + 8 * (uint32_t)(j & 1));
 
       if (n + kWsBS - 1 < total) {  // weights of item n + kWsBS - 1 go where item n - 1's were: wait until its MMAs have retired
-        { WSP_T0(); if (n >= 1) mbar_wait(bBempty + 8 * pbs, pbph); WSP_ADD(bempty); }
+        { WSP_T0(); if (n >= 1) WS_WAIT(bBempty + 8 * pbs, pbph); WSP_ADD(bempty); }
         request_b(n + kWsBS - 1, kc2);
       }
       pbs = bs;
@@ -822,11 +840,16 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
       }
     }
 #ifdef KWS_WS_PROFILE
-    if (blockIdx.x == 3 && lane == 0) printf("issuer: total %lld epilogue %lld wait_accfree %lld wait_full %lld wait_bfull %lld wait_bempty %lld tiles %d items %d\n", clock64() - wsp_start, wsp_epi, wsp_free, wsp_full, wsp_bfull, wsp_bempty, my_tiles, total);
+    if (lane == 0) {  // printed by a drain warp after the last barrier (printf does not fit this warp's 24 registers)
+      s_prof[0] = clock64() - wsp_start; s_prof[1] = wsp_free; s_prof[2] = wsp_full; s_prof[3] = wsp_bfull; s_prof[4] = wsp_bempty;
+    }
 #endif
   }
   tc_fence_before();
   __syncthreads();
+#ifdef KWS_WS_PROFILE
+  if (blockIdx.x == 3 && tid == kWsG * kWsGT) printf("issuer: total %lld wait_accfree %lld wait_full %lld wait_bfull %lld wait_bempty %lld tiles %d items %d\n", s_prof[0], s_prof[1], s_prof[2], s_prof[3], s_prof[4], my_tiles, total);
+#endif
   if (warp == 0)
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((uint32_t)p.tmem_cols));
 }
