@@ -382,10 +382,22 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_gemm_kernel(const GemmParams p) 
 //     and (2j + 1) % 3), one-half layers get two whole slots, halves wider than 170 columns two half-slots (each
 //     half then waits for the previous tile's same half only).  17 warps x 120 registers fill the register file.
 constexpr int kWsG = 4;     // producer groups
-constexpr int kWsS = 5;     // A-ring stages (item n uses stage n % kWsS: one more than groups, so that production runs on
+#ifndef KWS_WS_S
+#define KWS_WS_S 5
+#define KWS_WS_BS 3
+#endif
+constexpr int kWsS = KWS_WS_S;     // A-ring stages (item n uses stage n % kWsS: one more than groups, so that production runs on
                             // while the accumulator drains and the MMAs of the four waiting chunks catch up)
 constexpr int kWsGT = 96;   // threads per group: 16 channel pairs x 6 column groups
-constexpr int kWsBS = 3;    // weight-chunk ring stages
+constexpr int kWsBS = KWS_WS_BS;    // weight-chunk ring stages
+// A-ring stage layout (K-major, no swizzle): K quad q of pixel p at q * kWsLbo + 16 p -- the 8-row core matrices of a
+// quad are contiguous along M (SBO = 128), so a producer's NC adjacent pixels are NC adjacent 16-byte slots and its
+// store address is one register + an immediate (the chunk-synchronous kernel's layout, quads 144 bytes apart inside an
+// 8-row group, cost 8 address instructions per store); the quads are 16 bytes more than 2048 apart so that the
+// 16 channel pairs of a warp's store (8 quads x 2 halves) cover all 32 banks.
+constexpr int kWsLbo = 16 * 128 + 16;
+constexpr int kWsSbo = 128;
+constexpr int kWsABytes = (kGKC / 4) * kWsLbo;  // 16512
 constexpr int kWsEpi = 4;   // draining warps 12..15 (TMEM lane quarter = warp % 4)
 constexpr int kWsT = 640;   // five warpgroups: 12 producer warps | 4 drain warps | the issue warp + 3 idle warps.  Every
                             // SM sub-partition holds 3 producer warps, a drain warp and a warp of the last group: launched
@@ -404,7 +416,11 @@ constexpr int kWsT = 640;   // five warpgroups: 12 producer warps | 4 drain warp
 #endif
 // waits of the issue warp / the drain warps (A/B hook: try_wait with a 2 us suspendTimeHint instead of polling took the
 // polling instructions off the schedulers but woke up late: 207 K -> 201 K clips/s)
+#ifdef KWS_WS_ISSUEIDLE
+#define WS_WAIT(bar, par) mbar_wait_idle(bar, par, KWS_WS_ISSUEIDLE)
+#else
 #define WS_WAIT(bar, par) mbar_wait(bar, par)
+#endif
 #define WS_WAIT_ACC(bar, par) mbar_wait_idle(bar, par, 32)
 template <int NC, int PF, bool WREG>
 __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParams p) {
@@ -416,8 +432,8 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
 #endif
   const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
   const int bbytes = (p.npad / 8) * kGSbo;
-  unsigned char* sA = smem;                                  // [kWsS][kGABytes]
-  unsigned char* sB = smem + kWsS * kGABytes;                // [kWsBS][bbytes]
+  unsigned char* sA = smem;                                  // [kWsS][kWsABytes]
+  unsigned char* sB = smem + kWsS * kWsABytes;                // [kWsBS][bbytes]
   const int kpad = p.nchunks * kGKC;
   float* sW = reinterpret_cast<float*>(sB + kWsBS * (size_t)bbytes);  // [chunk][tap][32 channels]
   float* sBias = sW + 9 * kpad;                              // [npad]
@@ -449,7 +465,7 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
   for (int i = tid; i < p.npad; i += kWsT) sBias[i] = i < p.C ? __ldg(p.bias + i) : 0.f;
   // A ring starts as zeros: rows no pixel owns and channel quads past the channel count are never written, and
   // what the MMA reads there must be finite (it meets zero weight rows, or lands in accumulator rows nobody reads)
-  for (int i = tid; i < kWsS * kGABytes / 16; i += kWsT) reinterpret_cast<float4*>(sA)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int i = tid; i < kWsS * kWsABytes / 16; i += kWsT) reinterpret_cast<float4*>(sA)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   fence_proxy_async();
   tc_fence_before();
   __syncthreads();
@@ -634,15 +650,16 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
     // were competing with), and a row of the window is NC + 2 eight-byte loads.
     const int g = warp / 3, gt = tid - g * kWsGT;
     const int d = gt & 15, cg = gt >> 4, x0 = cg * NC;
-    uint32_t abase0 = smem_u32(sA) + (uint32_t)((d >> 1) * kGLboA + (d & 1) * 8);
+    uint32_t abase0 = smem_u32(sA) + (uint32_t)((d >> 1) * kWsLbo + (d & 1) * 8);
     asm volatile("" : "+r"(abase0));  // opaque, like coff[] below
     // column c of the window = input column x0 - 1 + c: byte offset within a row (clamped into the row) and 0/1 mask
-    int coff[NC + 2];
+    // the loads are (warp-uniform row pointer) + (this thread's 32-bit offset): no 64-bit address arithmetic per load
+    uint32_t coff[NC + 2];
     float cm[NC + 2];
 #pragma unroll
     for (int c = 0; c < NC + 2; ++c) {
       const int xx = x0 - 1 + c, xc = xx < 0 ? 0 : (xx >= W ? W - 1 : xx);
-      coff[c] = xc * C * 4;
+      coff[c] = (uint32_t)(xc * C * 4 + d * 8);
       cm[c] = xx == xc ? 1.f : 0.f;
       asm volatile("" : "+r"(coff[c]));  // opaque: keeps ptxas from recomputing the offset at every load (-5 % time)
     }
@@ -655,16 +672,17 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
     for (int n = g; n < total; n += kWsG, ++k) {
       const int j = n / nch, kc = n - j * nch;
       const int stage = n % kWsS, use = n / kWsS;  // ring stage of the item and how often it has been used before
-      const uint32_t abase = abase0 + (uint32_t)(stage * kGABytes);
+      const uint32_t abase = abase0 + (uint32_t)(stage * kWsABytes);
       const unsigned tile = blockIdx.x + (unsigned)j * gridDim.x, b = tile / (unsigned)p.nbands;
       const int band = (int)(tile - b * (unsigned)p.nbands), r0 = band * R;
       const int nrows = min(R, H - r0) + 2;  // input rows r0 - 1 .. of the band (rows outside the clip are zeros)
       const int kq = kc * kGKC + 2 * d;
       const bool act = x0 < W && kq < C;
-      // next row to load: row r0 - 1 of the clip, channel kq (the pointer may run outside the clip: never read there)
-      const char* rp = reinterpret_cast<const char*>(p.in + ((long long)b * H + r0 - 1) * W * (long long)C + kq);
+      // next row to load: row r0 - 1 of the clip, first channel of the chunk (the pointer may run outside the clip:
+      // never read there); all of this is warp-uniform
+      const char* rp = reinterpret_cast<const char*>(p.in + ((long long)b * H + r0 - 1) * W * (long long)C + kc * kGKC);
       int ynext = r0 - 1;
-      const char* zr = reinterpret_cast<const char*>(p.zero_row + kq);  // a row of zeros stands in for rows outside the clip
+      const char* zr = reinterpret_cast<const char*>(p.zero_row + kc * kGKC);  // a row of zeros stands in for rows outside the clip
       auto load_row = [&](V (&v)[NC + 2]) {
         const char* r = (ynext >= 0 && ynext < H) ? rp : zr;
 #pragma unroll
@@ -690,7 +708,7 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
         V P[NC], Rr[NC];
 #pragma unroll
         for (int c = 0; c < NC; ++c) P[c] = Rr[c] = fsplat(0.f);
-        int pp = -2 * W + x0;  // A row (pixel of the tile) of output row i - 2, column x0
+        uint32_t arow = abase + 16u * (uint32_t)(-2 * W + x0);  // A-ring slot of (output row i - 2, column x0)
         // input row i of the band: finishes output row i - 2 (taps 6..8), continues i - 1 (3..5), starts i (0..2)
         auto step = [&](int i, const V (&vin)[NC + 2]) {
           V v[NC + 2];
@@ -708,14 +726,12 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
             P[c] = q1;
             Rr[c] = q0;
             if (i >= 2 && x0 + c < W) {  // tf32 round-to-nearest: add half an ulp of the 10-bit mantissa
-              const int ppc = pp + c;
-              const uint32_t a = abase + (uint32_t)((ppc >> 3) * kGSboA + (ppc & 7) * 16);
-              asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(a), "r"(__float_as_uint(o.x) + 0x1000u),
+              asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(arow + 16u * (uint32_t)c), "r"(__float_as_uint(o.x) + 0x1000u),
                            "r"(__float_as_uint(o.y) + 0x1000u)
                            : "memory");
             }
           }
-          pp += W;
+          arow += 16u * (uint32_t)W;
         };
         [&] {
           int i = 0;
@@ -787,8 +803,8 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
     const long long wsp_start = clock64();
 #endif
     // descriptors of ring stage 0; a stage / K step / N half only moves the 14-bit start-address field (>> 4)
-    const uint64_t adesc0 = umma_desc(smem_u32(sA), kGLboA, kGSboA), bdesc0 = umma_desc(smem_u32(sB), 128u, kGSbo);
-    const uint32_t a_stage = kGABytes >> 4, b_stage = (uint32_t)bbytes >> 4, b_half = (uint32_t)((p.nhalf / 8) * kGSbo) >> 4;
+    const uint64_t adesc0 = umma_desc(smem_u32(sA), kWsLbo, kWsSbo), bdesc0 = umma_desc(smem_u32(sB), 128u, kGSbo);
+    const uint32_t a_stage = kWsABytes >> 4, b_stage = (uint32_t)bbytes >> 4, b_half = (uint32_t)((p.nhalf / 8) * kGSbo) >> 4;
     const bool two_halves = p.nh == 2;
     uint32_t tmem_h0 = tmem, tmem_h1 = tmem + (uint32_t)p.nhalf;  // this tile's accumulator slots
     int bs = 0, pbs = 0, kc2 = (kWsBS - 1) % nch;  // weight ring stage of item n and of item n - 1; K chunk of item n + kWsBS - 1
@@ -815,9 +831,9 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
         if (ks > 0) break;
 #endif
         const uint32_t acc = (kc > 0 || ks > 0) ? 1u : 0u;
-        tc_mma_tf32_elect(tmem_h0, ad + (uint64_t)(ks * ((2 * kGLboA) >> 4)), bd + (uint64_t)(ks * 16), idesc, acc);
+        tc_mma_tf32_elect(tmem_h0, ad + (uint64_t)(ks * ((2 * kWsLbo) >> 4)), bd + (uint64_t)(ks * 16), idesc, acc);
         if (two_halves)
-          tc_mma_tf32_elect(tmem_h1, ad + (uint64_t)(ks * ((2 * kGLboA) >> 4)), bd + (uint64_t)(b_half + ks * 16), idesc, acc);
+          tc_mma_tf32_elect(tmem_h1, ad + (uint64_t)(ks * ((2 * kWsLbo) >> 4)), bd + (uint64_t)(b_half + ks * 16), idesc, acc);
       }
       tc_commit_elect(bEmpty + 8 * g);
       tc_commit_elect(bBempty + 8 * bs);
@@ -1230,7 +1246,7 @@ int launch_dscnn_gemm(kws_handle_t h, const float* feats_dev, int64_t B, int T, 
   // shared-memory rings fit, else the chunk-synchronous one (KWS_GEMM_WS=0 forces the latter, for A/B runs)
   static const bool ws_env = [] { const char* e = std::getenv("KWS_GEMM_WS"); return !(e && e[0] == '0'); }();
   const int nch_blk = (C + kGKC - 1) / kGKC;
-  const size_t smem_ws = (size_t)kWsS * kGABytes + (size_t)kWsBS * (g->npad / 8) * kGSbo + (size_t)9 * nch_blk * kGKC * 4 +
+  const size_t smem_ws = (size_t)kWsS * kWsABytes + (size_t)kWsBS * (g->npad / 8) * kGSbo + (size_t)9 * nch_blk * kGKC * 4 +
                          (size_t)g->npad * 4;
   const bool ws_fits = ws_env && smem_ws <= 227 * 1024;
   if (ws_fits) {
