@@ -383,7 +383,7 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_gemm_kernel(const GemmParams p) 
 //     half then waits for the previous tile's same half only).  17 warps x 120 registers fill the register file.
 constexpr int kWsG = 4;     // producer groups
 #ifndef KWS_WS_S
-#define KWS_WS_S 5
+#define KWS_WS_S 6
 #define KWS_WS_BS 3
 #endif
 constexpr int kWsS = KWS_WS_S;     // A-ring stages (item n uses stage n % kWsS: one more than groups, so that production runs on
