@@ -421,7 +421,11 @@ constexpr int kWsT = 640;   // five warpgroups: 12 producer warps | 4 drain warp
 #else
 #define WS_WAIT(bar, par) mbar_wait(bar, par)
 #endif
+#ifdef KWS_WS_ACCSPIN
+#define WS_WAIT_ACC(bar, par) mbar_wait(bar, par)
+#else
 #define WS_WAIT_ACC(bar, par) mbar_wait_idle(bar, par, 32)
+#endif
 template <int NC, int PF, bool WREG>
 __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParams p) {
   extern __shared__ __align__(128) unsigned char smem[];
@@ -641,6 +645,21 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
             (float)(2 * (W + 2) + 2 * H) * __ldg(p.border + c) * p.pool_scale;
   };
 
+  // The whole input patch of a tile (rows r0 - 1 .. r0 + R of one clip, all channels) is one contiguous range:
+  // pulled into L2 one tile ahead by bulk prefetches, one per row, so that the producers' register loads (two
+  // rows ahead of their arithmetic, which hides L2 latency but not DRAM latency under load) hit L2.
+  auto prefetch_tile = [&](int jj) {
+    if (jj < my_tiles) {
+      const unsigned tile = blockIdx.x + (unsigned)jj * gridDim.x, b = tile / (unsigned)p.nbands;
+      const int r0 = (int)(tile - b * (unsigned)p.nbands) * R;
+      const int y0 = r0 > 0 ? r0 - 1 : 0, y1 = r0 + R < H ? r0 + R : H - 1;
+      const uint32_t bytes = (uint32_t)(W * C * 4);
+      for (int y = y0 + lane; y <= y1; y += 32)
+        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p.in + ((long long)b * H + y) * W * (long long)C), "r"(bytes)
+                     : "memory");
+    }
+    __syncwarp();
+  };
   if (warp < kWsG * 3) {
     asm volatile("setmaxnreg.inc.sync.aligned.u32 120;");
     // ---- producers ----
@@ -761,44 +780,36 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
 #ifdef KWS_WS_PROFILE
     if (blockIdx.x == 3 && lane == 0) printf("drain warp %d: total %lld wait_accfull %lld\n", warp, clock64() - wsp_start, wsp_aw);
 #endif
-  } else if (warp > kWsG * 3 + kWsEpi) {
+  } else if (warp > kWsG * 3 + kWsEpi + 1) {
     asm volatile("setmaxnreg.dec.sync.aligned.u32 24;");  // idle: they only complete the issue warp's warpgroup
+  } else if (warp == kWsG * 3 + kWsEpi + 1) {
+    // ---- loader warp: weight chunks through the TMA ring, as far ahead as the ring allows (~45 instructions and the
+    // wait for the ring stage off every item of the issue loop: 1.1 K -> 0.9 K cycles per item)
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 24;");
+    int kc = 0, bs = 0;
+    uint32_t bph = 1;  // parity of the phase before the stage's current use
+    for (int n = 0; n < total; ++n) {
+      if (n >= kWsBS) mbar_wait_idle(bBempty + 8 * bs, bph, 64);  // the MMAs that read this stage last have retired
+      if (lane == 0) {
+        mbar_expect_tx(bBfull + 8 * bs, (uint32_t)bbytes);
+        tma_load_1d(smem_u32(sB + (size_t)bs * bbytes), reinterpret_cast<const unsigned char*>(p.wimg) + (size_t)kc * bbytes,
+                    (uint32_t)bbytes, bBfull + 8 * bs);
+      }
+      __syncwarp();
+      if (++bs == kWsBS) {
+        bs = 0;
+        bph ^= 1u;
+      }
+      if (++kc == nch) kc = 0;
+    }
   } else {
-    // ---- issue warp: weight-chunk TMA ring, MMAs in item order, L2 prefetch of the next tile ----
+    // ---- issue warp: MMAs in item order, L2 prefetch of the next tile ----
     asm volatile("setmaxnreg.dec.sync.aligned.u32 24;");
     const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(p.nhalf >> 3) << 17) | ((128u >> 4) << 24);
-    auto request_b = [&](int n, int kc) {  // weight chunk kc of item n into ring stage n % kWsBS
-      if (lane == 0) {
-        const uint32_t s = (uint32_t)n % (uint32_t)kWsBS;
-        mbar_expect_tx(bBfull + 8 * s, (uint32_t)bbytes);
-        tma_load_1d(smem_u32(sB + (size_t)s * bbytes), reinterpret_cast<const unsigned char*>(p.wimg) + (size_t)kc * bbytes,
-                    (uint32_t)bbytes, bBfull + 8 * s);
-      }
-      __syncwarp();
-    };
-    // The whole input patch of a tile (rows r0 - 1 .. r0 + R of one clip, all channels) is one contiguous range:
-    // pulled into L2 one tile ahead by bulk prefetches, one per row, so that the producers' register loads (two
-    // rows ahead of their arithmetic, which hides L2 latency but not DRAM latency under load) hit L2.
-    auto prefetch_tile = [&](int jj) {
-      if (jj < my_tiles) {
-        const unsigned tile = blockIdx.x + (unsigned)jj * gridDim.x, b = tile / (unsigned)p.nbands;
-        const int r0 = (int)(tile - b * (unsigned)p.nbands) * R;
-        const int y0 = r0 > 0 ? r0 - 1 : 0, y1 = r0 + R < H ? r0 + R : H - 1;
-        const uint32_t bytes = (uint32_t)(W * C * 4);
-        for (int y = y0 + lane; y <= y1; y += 32)
-          asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p.in + ((long long)b * H + y) * W * (long long)C), "r"(bytes)
-                       : "memory");
-      }
-      __syncwarp();
-    };
-#ifndef KWS_WS_PFAHEAD
-#define KWS_WS_PFAHEAD 1
-#endif
-    for (int jj = 0; jj <= KWS_WS_PFAHEAD; ++jj) prefetch_tile(jj);
-    for (int i = 0; i < kWsBS - 1; ++i)
-      if (total > i) request_b(i, i % nch);
+    prefetch_tile(0);
+    prefetch_tile(1);
     int j = 0, kc = 0;
-    WSP_DECL(free); WSP_DECL(full); WSP_DECL(bfull); WSP_DECL(bempty);
+    WSP_DECL(free); WSP_DECL(full); WSP_DECL(bfull);
 #ifdef KWS_WS_PROFILE
     const long long wsp_start = clock64();
 #endif
@@ -807,12 +818,12 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
     const uint32_t a_stage = kWsABytes >> 4, b_stage = (uint32_t)bbytes >> 4, b_half = (uint32_t)((p.nhalf / 8) * kGSbo) >> 4;
     const bool two_halves = p.nh == 2;
     uint32_t tmem_h0 = tmem, tmem_h1 = tmem + (uint32_t)p.nhalf;  // this tile's accumulator slots
-    int bs = 0, pbs = 0, kc2 = (kWsBS - 1) % nch;  // weight ring stage of item n and of item n - 1; K chunk of item n + kWsBS - 1
-    uint32_t bph = 0, pbph = 0;                   // their phases
+    int bs = 0;        // weight ring stage of item n
+    uint32_t bph = 0;  // and its phase
     for (int n = 0; n < total; ++n) {
       const int g = n % kWsS;  // A ring stage of the item
       if (kc == 0) {  // tile boundary: this tile's accumulator slots must have been read out by their four warps
-        if (j > 0) prefetch_tile(j + KWS_WS_PFAHEAD);
+        if (j > 0) prefetch_tile(j + 1);  // (by the loader warp, which runs up to three chunks ahead: 3 % slower)
         const int h = p.nh * j, s0 = h % ns, s1 = (h + 1) % ns, u0 = h / ns, u1 = (h + 1) / ns;
         WSP_T0();
         if (u0 > 0) WS_WAIT(bFreeS + 8 * (uint32_t)s0, (uint32_t)(u0 - 1) & 1u);
@@ -838,18 +849,10 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
       tc_commit_elect(bEmpty + 8 * g);
       tc_commit_elect(bBempty + 8 * bs);
       if (kc == nch - 1) tc_commit_elect(bAccFull + 8 * (uint32_t)(j & 1));
-
-      if (n + kWsBS - 1 < total) {  // weights of item n + kWsBS - 1 go where item n - 1's were: wait until its MMAs have retired
-        { WSP_T0(); if (n >= 1) WS_WAIT(bBempty + 8 * pbs, pbph); WSP_ADD(bempty); }
-        request_b(n + kWsBS - 1, kc2);
-      }
-      pbs = bs;
-      pbph = bph;
       if (++bs == kWsBS) {
         bs = 0;
         bph ^= 1u;
       }
-      if (++kc2 >= nch) kc2 = 0;
       if (++kc == nch) {
         kc = 0;
         ++j;
@@ -857,7 +860,7 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
     }
 #ifdef KWS_WS_PROFILE
     if (lane == 0) {  // printed by a drain warp after the last barrier (printf does not fit this warp's 24 registers)
-      s_prof[0] = clock64() - wsp_start; s_prof[1] = wsp_free; s_prof[2] = wsp_full; s_prof[3] = wsp_bfull; s_prof[4] = wsp_bempty;
+      s_prof[0] = clock64() - wsp_start; s_prof[1] = wsp_free; s_prof[2] = wsp_full; s_prof[3] = wsp_bfull; s_prof[4] = 0;
     }
 #endif
   }
