@@ -113,11 +113,13 @@ def test_tensor_core_gemm_path_any_channels(channels, blocks, T, F, B):
     np.testing.assert_allclose(fast, want, rtol=1e-3, atol=2e-4)
 
 
-@pytest.mark.parametrize("channels,blocks,T,F,B", [(276, 5, 99, 40, 301), (96, 3, 99, 40, 77), (64, 2, 61, 64, 9)])
+@pytest.mark.parametrize("channels,blocks,T,F,B", [(276, 5, 99, 40, 301), (96, 3, 99, 40, 77), (64, 2, 61, 64, 9),
+                                                  (172, 4, 99, 40, 150), (256, 2, 49, 40, 90)])
 def test_tensor_core_gemm_path_many_tiles_and_repeatable(channels, blocks, T, F, B):
     """The warp-specialised block kernel (model_gemm.cu) with several tiles per CTA (ring stages, weight ring and the
     accumulator recycle many times; last bands shorter than a tile; 64 x 2 at F = 64 has layers 30 and 32 columns wide = the
-    3-column thread map): every clip against the layered fp32 kernels, bit-identical on a second run, and a clip's
+    3-column thread map; 276 channels = three half-accumulator slots, 172 = 'DS-CNN-M' and 256 = two whole slots, 256 filling
+    all 512 TMEM columns): every clip against the layered fp32 kernels, bit-identical on a second run, and a clip's
     logits independent of its position in the batch (tiles of different clips share a CTA's pipeline)."""
     sd = dscnn_ref.init_state_dict(channels=channels, num_blocks=blocks, seed=3 * channels + blocks)
     m = DepthwiseSeparableConv(channels=channels, num_blocks=blocks)
