@@ -546,7 +546,14 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
         }
       }
     };
-    auto process = [&](float (&v)[2][2][8], int r) {
+    // bias of a round for this thread: block 0 / block 1 of the two pairs.  Read before the wait for the round's TMEM
+    // loads, so that the shared-memory latency is not paid in front of the first add
+    auto load_bias = [&](float2 (&bz)[4], int r) {
+      const float* b = sBias + 32 * r + 2 * tq;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) bz[i] = *reinterpret_cast<const float2*>(b + 8 * i);
+    };
+    auto process = [&](float (&v)[2][2][8], int r, const float2 (&bz)[4]) {
       const int cb = 32 * r;
       const bool guard = cb + 32 > C;  // only the round that holds the channel count's end needs a store predicate
 #ifdef KWS_WS_LDONLY  // timing experiment only: TMEM loads without the arithmetic and the stores
@@ -555,7 +562,7 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
 #pragma unroll
       for (int pr = 0; pr < 2; ++pr) {
         const int col = cb + 16 * pr + 2 * tq;  // channel of register e = 0 of block 0 (block 1: + 8)
-        const float2 bz0 = *reinterpret_cast<const float2*>(sBias + col), bz1 = *reinterpret_cast<const float2*>(sBias + col + 8);
+        const float2 bz0 = bz[2 * pr], bz1 = bz[2 * pr + 1];
 #pragma unroll
         for (int hh = 0; hh < 2; ++hh)
 #pragma unroll
@@ -583,14 +590,24 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
           }
 #else
           const bool cok = !guard || cb + 16 * pr + coff < C;
+          // even lanes keep block 0 and take the neighbour's, odd lanes block 1: the eight shuffles of the pair are
+          // issued back to back, then the four 16-byte stores (one shuffle latency per pair instead of one per store)
+          float g[2][2][2];
+#pragma unroll
+          for (int hh = 0; hh < 2; ++hh)
+#pragma unroll
+            for (int ss = 0; ss < 2; ++ss) {
+              const float* x = v[pr][hh] + 2 * ss;
+              g[hh][ss][0] = __shfl_xor_sync(0xffffffffu, odd ? x[0] : x[4], 1);
+              g[hh][ss][1] = __shfl_xor_sync(0xffffffffu, odd ? x[1] : x[5], 1);
+            }
 #pragma unroll
           for (int hh = 0; hh < 2; ++hh) {
             if (hh == 0 ? hv0 : hv1) {
 #pragma unroll
-              for (int ss = 0; ss < 2; ++ss) {  // even lanes keep block 0 and take the neighbour's, odd lanes block 1
+              for (int ss = 0; ss < 2; ++ss) {
                 const float* x = v[pr][hh] + 2 * ss;
-                const float k0 = odd ? x[4] : x[0], k1 = odd ? x[5] : x[1], s0 = odd ? x[0] : x[4], s1 = odd ? x[1] : x[5];
-                const float g0 = __shfl_xor_sync(0xffffffffu, s0, 1), g1 = __shfl_xor_sync(0xffffffffu, s1, 1);
+                const float k0 = odd ? x[4] : x[0], k1 = odd ? x[5] : x[1], g0 = g[hh][ss][0], g1 = g[hh][ss][1];
                 const float4 o = odd ? make_float4(g0, g1, k0, k1) : make_float4(k0, k1, g0, g1);
 #ifdef KWS_WS_NOSTORE  // timing experiment only (results are wrong): the drain without its global stores
                 if (o.x == 1.2345e30f) *reinterpret_cast<float4*>(orow[hh][ss] + 16 * pr) = o;
@@ -625,17 +642,20 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
       for (int r = rs; r < re; ++r) release(r);
     } else if (rs < re) {  // two register sets in rotation: the next round's TMEM loads are in flight while a round is stored
       float va[2][2][8], vb[2][2][8];
+      float2 bz[4];
       load_round(va, rs);
       for (int r = rs;; r += 2) {
+        load_bias(bz, r);
         tc_wait_ld();
         if (r + 1 < re) load_round(vb, r + 1);
         release(r);
-        process(va, r);
+        process(va, r, bz);
         if (r + 1 >= re) break;
+        load_bias(bz, r + 1);
         tc_wait_ld();
         if (r + 2 < re) load_round(va, r + 2);
         release(r + 1);
-        process(vb, r + 1);
+        process(vb, r + 1, bz);
         if (r + 2 >= re) break;
       }
     }
