@@ -426,7 +426,9 @@ constexpr int kWsT = 640;   // five warpgroups: 12 producer warps | 4 drain warp
 #else
 #define WS_WAIT_ACC(bar, par) mbar_wait_idle(bar, par, 32)
 #endif
-template <int NC, int PF, bool WREG>
+// NC = adjacent columns per producer thread, PF = rows the loads run ahead, POOL = last block (channel sums instead of
+// the activation; its own instantiation keeps the other's drain code small: the kernel is 60 KB of SASS run by five roles)
+template <int NC, int PF, bool POOL>
 __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParams p) {
   extern __shared__ __align__(128) unsigned char smem[];
   __shared__ __align__(8) unsigned long long s_bar[2 * kWsS + 2 * kWsBS + 2 + 3];
@@ -504,7 +506,8 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
     const unsigned tile = blockIdx.x + (unsigned)j * gridDim.x, b = tile / (unsigned)p.nbands;
     const int band = (int)(tile - b * (unsigned)p.nbands), r0 = band * R;
     const int lq = warp & 3, tq = lane & 3, tr = lane >> 2;
-    const bool pool = p.pool != nullptr, odd = lane & 1;
+    constexpr bool pool = POOL;
+    const bool odd = lane & 1;
     // this thread's four pixels (16-lane half hh, row block ss); a lane without a pixel stores into a dump row, so
     // that the stores of all rounds but the last need no predicate
 #ifdef KWS_WS_STG64
@@ -1273,6 +1276,9 @@ int launch_dscnn_gemm(kws_handle_t h, const float* feats_dev, int64_t B, int T, 
                          (size_t)g->npad * 4;
   const bool ws_fits = ws_env && smem_ws <= 227 * 1024;
   if (ws_fits) {
+    if (int rc = ensure_dyn_smem(dscnn_block_ws_kernel<4, 2, false>, smem_ws)) return rc;
+    if (int rc = ensure_dyn_smem(dscnn_block_ws_kernel<5, 2, false>, smem_ws)) return rc;
+    if (int rc = ensure_dyn_smem(dscnn_block_ws_kernel<6, 1, false>, smem_ws)) return rc;
     if (int rc = ensure_dyn_smem(dscnn_block_ws_kernel<4, 2, true>, smem_ws)) return rc;
     if (int rc = ensure_dyn_smem(dscnn_block_ws_kernel<5, 2, true>, smem_ws)) return rc;
     if (int rc = ensure_dyn_smem(dscnn_block_ws_kernel<6, 1, true>, smem_ws)) return rc;
@@ -1305,9 +1311,15 @@ int launch_dscnn_gemm(kws_handle_t h, const float* feats_dev, int64_t B, int T, 
     const int pool_rows = ws ? 4 * p.nbands + 1 : p.nbands + 1;
     auto launch_block = [&]() {
       if (!ws) dscnn_gemm_kernel<1><<<grid, kGT, smem_bytes, st>>>(p);
-      else if (W <= 24) dscnn_block_ws_kernel<4, 2, true><<<grid, kWsT, smem_ws, st>>>(p);
-      else if (W <= 30) dscnn_block_ws_kernel<5, 2, true><<<grid, kWsT, smem_ws, st>>>(p);
-      else dscnn_block_ws_kernel<6, 1, true><<<grid, kWsT, smem_ws, st>>>(p);
+      else if (p.pool) {
+        if (W <= 24) dscnn_block_ws_kernel<4, 2, true><<<grid, kWsT, smem_ws, st>>>(p);
+        else if (W <= 30) dscnn_block_ws_kernel<5, 2, true><<<grid, kWsT, smem_ws, st>>>(p);
+        else dscnn_block_ws_kernel<6, 1, true><<<grid, kWsT, smem_ws, st>>>(p);
+      } else {
+        if (W <= 24) dscnn_block_ws_kernel<4, 2, false><<<grid, kWsT, smem_ws, st>>>(p);
+        else if (W <= 30) dscnn_block_ws_kernel<5, 2, false><<<grid, kWsT, smem_ws, st>>>(p);
+        else dscnn_block_ws_kernel<6, 1, false><<<grid, kWsT, smem_ws, st>>>(p);
+      }
     };
     if (l == nb - 1) {  // the pooled rows replace the last activation (see GemmParams::pool)
       p.pool = nxt;
