@@ -615,8 +615,7 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
 #ifdef KWS_WS_NOSTORE  // timing experiment only (results are wrong): the drain without its global stores
                 if (o.x == 1.2345e30f) *reinterpret_cast<float4*>(orow[hh][ss] + 16 * pr) = o;
 #else
-                if (!guard) *reinterpret_cast<float4*>(orow[hh][ss] + 16 * pr) = o;
-                else if (cok) *reinterpret_cast<float4*>(orow[hh][ss] + 16 * pr) = o;
+                if (cok) *reinterpret_cast<float4*>(orow[hh][ss] + 16 * pr) = o;
 #endif
               }
             }
@@ -677,6 +676,7 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
       const int r0 = (int)(tile - b * (unsigned)p.nbands) * R;
       const int y0 = r0 > 0 ? r0 - 1 : 0, y1 = r0 + R < H ? r0 + R : H - 1;
       const uint32_t bytes = (uint32_t)(W * C * 4);
+#pragma unroll 1
       for (int y = y0 + lane; y <= y1; y += 32)
         asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p.in + ((long long)b * H + y) * W * (long long)C), "r"(bytes)
                      : "memory");
@@ -829,8 +829,8 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
     // ---- issue warp: MMAs in item order, L2 prefetch of the next tile ----
     asm volatile("setmaxnreg.dec.sync.aligned.u32 24;");
     const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(p.nhalf >> 3) << 17) | ((128u >> 4) << 24);
-    prefetch_tile(0);
-    prefetch_tile(1);
+#pragma unroll 1
+    for (int jj = 0; jj < 2; ++jj) prefetch_tile(jj);
     int j = 0, kc = 0;
     WSP_DECL(free); WSP_DECL(full); WSP_DECL(bfull);
 #ifdef KWS_WS_PROFILE
