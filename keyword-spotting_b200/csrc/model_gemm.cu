@@ -832,6 +832,7 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
 #pragma unroll 1
     for (int jj = 0; jj < 2; ++jj) prefetch_tile(jj);
     int j = 0, kc = 0;
+    const int pf_kc = nch > 1 ? (nch + 1) / 2 : 0;
     WSP_DECL(free); WSP_DECL(full); WSP_DECL(bfull);
 #ifdef KWS_WS_PROFILE
     const long long wsp_start = clock64();
@@ -846,7 +847,6 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
     for (int n = 0; n < total; ++n) {
       const int g = n % kWsS;  // A ring stage of the item
       if (kc == 0) {  // tile boundary: this tile's accumulator slots must have been read out by their four warps
-        if (j > 0) prefetch_tile(j + 1);  // (by the loader warp, which runs up to three chunks ahead: 3 % slower)
         const int h = p.nh * j, s0 = h % ns, s1 = (h + 1) % ns, u0 = h / ns, u1 = (h + 1) / ns;
         WSP_T0();
         if (u0 > 0) WS_WAIT(bFreeS + 8 * (uint32_t)s0, (uint32_t)(u0 - 1) & 1u);
@@ -855,6 +855,10 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
         tmem_h0 = tmem + (uint32_t)(s0 * p.nhalf);
         tmem_h1 = tmem + (uint32_t)(s1 * p.nhalf);
       }
+      // the next tile's input into L2 half a tile ahead: the producers start on it about four chunks before this warp
+      // does.  Timing matters: at the tile's first chunk 245 K clips/s, third 253 K, fifth 255 K, seventh 245 K, never
+      // 230 K; from the loader warp (three chunks earlier still) or two tiles ahead it is slower than at the first chunk
+      if (kc == pf_kc && j > 0) prefetch_tile(j + 1);
       { WSP_T0(); WS_WAIT(bFull + 8 * g, (uint32_t)(n / kWsS) & 1u); WSP_ADD(full); }
       { WSP_T0(); WS_WAIT(bBfull + 8 * bs, bph); WSP_ADD(bfull); }
       tc_fence_after();
