@@ -832,7 +832,7 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
 #pragma unroll 1
     for (int jj = 0; jj < 2; ++jj) prefetch_tile(jj);
     int j = 0, kc = 0;
-    const int pf_kc = nch > 1 ? (nch + 1) / 2 : 0;
+    const int pf_kc = nch / 2;
     WSP_DECL(free); WSP_DECL(full); WSP_DECL(bfull);
 #ifdef KWS_WS_PROFILE
     const long long wsp_start = clock64();
@@ -856,7 +856,7 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
         tmem_h1 = tmem + (uint32_t)(s1 * p.nhalf);
       }
       // the next tile's input into L2 half a tile ahead: the producers start on it about four chunks before this warp
-      // does.  Timing matters: at the tile's first chunk 245 K clips/s, third 253 K, fifth 255 K, seventh 245 K, never
+      // does.  Timing matters: at the tile's first chunk 245 K clips/s, third 253 K, fourth / fifth 255 K, seventh 245 K, never
       // 230 K; from the loader warp (three chunks earlier still) or two tiles ahead it is slower than at the first chunk
       if (kc == pf_kc && j > 0) prefetch_tile(j + 1);
       { WSP_T0(); WS_WAIT(bFull + 8 * g, (uint32_t)(n / kWsS) & 1u); WSP_ADD(full); }
