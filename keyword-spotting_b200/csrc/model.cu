@@ -727,7 +727,7 @@ int64_t kws_model_workspace_bytes(kws_handle_t h, int64_t B, int64_t T, int64_t 
   conv_out_hw((int)T, (int)F, h->model.num_blocks, &H1, &W1, &Hl, &Wl);
   if (H1 < 1 || W1 < 1) return fail(KWS_ERR_INVALID, "input %lldx%lld too small for conv1", (long long)T, (long long)F);
   const int64_t chunk = B < kModelChunk ? B : kModelChunk;
-  return 2 * chunk * Hl * Wl * h->model.channels * 4;
+  return 2 * chunk * Hl * Wl * ((h->model.channels + 31) / 32 * 32) * 4;  // the tensor-core path may pad a pixel to 32 channels
 }
 
 int kws_model_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t T, int64_t F,
@@ -758,7 +758,7 @@ int kws_model_forward(kws_handle_t h, const float* feats_dev, int64_t B, int64_t
   }
   const int64_t chunk = B < kModelChunk ? B : kModelChunk;
   float* buf0 = (float*)m.d_ws;
-  float* buf1 = buf0 + chunk * Hl * Wl * C;
+  float* buf1 = buf0 + chunk * Hl * Wl * ((C + 31) / 32 * 32);
   const int cq = C / 4;
   for (int64_t b0 = 0; b0 < B; b0 += chunk) {
     const int64_t nbat = (B - b0 < chunk) ? B - b0 : chunk;

@@ -40,6 +40,7 @@ struct GemmParams {
   int R, nbands;       // tile = R whole rows of one clip (R * W <= 128), nbands = ceil(H / R)
   int kvalid, npad, nh, nhalf, nchunks, tmem_cols, patch_bytes;
   int nslots;  // dscnn_block_ws_kernel: accumulator slots of nhalf TMEM columns
+  int ldc;     // floats between consecutive pixels of the activations (C, or C padded to a multiple of 32: see launch_dscnn_gemm)
   // last block only: instead of the activation, write per-tile channel sums (the global average pool's partial sums,
   // scaled so that pool_fc_kernel's mean over nbands + 1 rows is the mean over the padded output) -- the largest
   // activation of the network is never written or re-read
@@ -523,7 +524,7 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
       for (int ss = 0; ss < 2; ++ss) {
         const int pp = lq * 32 + hh * 16 + ss * 8 + tr, rl = pp / W, xq = pp - rl * W, y = r0 + rl;
         valid[hh][ss] = rl < R && y < H;
-        orow[hh][ss] = (valid[hh][ss] ? p.out + (((long long)b * (H + 2) + y + 1) * (W + 2) + xq + 1) * (long long)C : p.dump) + coff + 32 * rs;
+        orow[hh][ss] = (valid[hh][ss] ? p.out + (((long long)b * (H + 2) + y + 1) * (W + 2) + xq + 1) * (long long)p.ldc : p.dump) + coff + 32 * rs;
       }
     float* prow = pool ? p.pool + ((long long)b * (4 * p.nbands + 1) + band * 4 + lq) * (long long)C : nullptr;
     const uint32_t ta = tmem + ((uint32_t)(lq * 32) << 16);
@@ -675,10 +676,10 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
       const unsigned tile = blockIdx.x + (unsigned)jj * gridDim.x, b = tile / (unsigned)p.nbands;
       const int r0 = (int)(tile - b * (unsigned)p.nbands) * R;
       const int y0 = r0 > 0 ? r0 - 1 : 0, y1 = r0 + R < H ? r0 + R : H - 1;
-      const uint32_t bytes = (uint32_t)(W * C * 4);
+      const uint32_t bytes = (uint32_t)(W * p.ldc * 4);
 #pragma unroll 1
       for (int y = y0 + lane; y <= y1; y += 32)
-        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p.in + ((long long)b * H + y) * W * (long long)C), "r"(bytes)
+        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p.in + ((long long)b * H + y) * W * (long long)p.ldc), "r"(bytes)
                      : "memory");
     }
     __syncwarp();
@@ -701,11 +702,11 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
 #pragma unroll
     for (int c = 0; c < NC + 2; ++c) {
       const int xx = x0 - 1 + c, xc = xx < 0 ? 0 : (xx >= W ? W - 1 : xx);
-      coff[c] = (uint32_t)(xc * C * 4 + d * 8);
+      coff[c] = (uint32_t)(xc * p.ldc * 4 + d * 8);
       cm[c] = xx == xc ? 1.f : 0.f;
       asm volatile("" : "+r"(coff[c]));  // opaque: keeps ptxas from recomputing the offset at every load (-5 % time)
     }
-    const long long rowbytes = (long long)W * C * 4;
+    const long long rowbytes = (long long)W * p.ldc * 4;
     uint32_t k = 0;
     WSP_DECL(pw);
 #ifdef KWS_WS_PROFILE
@@ -722,7 +723,7 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
       const bool act = x0 < W && kq < C;
       // next row to load: row r0 - 1 of the clip, first channel of the chunk (the pointer may run outside the clip:
       // never read there); all of this is warp-uniform
-      const char* rp = reinterpret_cast<const char*>(p.in + ((long long)b * H + r0 - 1) * W * (long long)C + kc * kGKC);
+      const char* rp = reinterpret_cast<const char*>(p.in + ((long long)b * H + r0 - 1) * W * (long long)p.ldc + kc * kGKC);
       int ynext = r0 - 1;
       const char* zr = reinterpret_cast<const char*>(p.zero_row + kc * kGKC);  // a row of zeros stands in for rows outside the clip
       auto load_row = [&](V (&v)[NC + 2]) {
@@ -1040,7 +1041,7 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_conv1_kernel(const GemmParams p)
         for (int ss = 0; ss < 2; ++ss) {
           const int pp = lq * 32 + hh * 16 + ss * 8 + tr, rl = pp / W, xq = pp - rl * W, y = r0 + rl;
           valid[hh][ss] = rl < R && y < H;
-          orow[hh][ss] = p.out + (((long long)b * H + y) * W + xq) * (long long)C + coff + dr_c0;
+          orow[hh][ss] = p.out + (((long long)b * H + y) * W + xq) * (long long)p.ldc + coff + dr_c0;
         }
       const int npix = min(R, H - r0) * W;
       const bool hv0 = lq * 32 < npix, hv1 = lq * 32 + 16 < npix;
@@ -1084,7 +1085,7 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_conv1_kernel(const GemmParams p)
 
 // border of a block output [B, Ho, Wo, C]: ReLU(pointwise bias)
 __global__ void border_fill_kernel(float* __restrict__ out, const float* __restrict__ relu_bias, long long B, int Ho,
-                                   int Wo, int C) {
+                                   int Wo, int C, int ld) {
   const int cq = C / 4, nb = 2 * Wo + 2 * (Ho - 2);
   const long long total = B * nb * (long long)cq;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -1095,7 +1096,7 @@ __global__ void border_fill_kernel(float* __restrict__ out, const float* __restr
     if (e < Wo) { y = 0; x = e; }
     else if (e < 2 * Wo) { y = Ho - 1; x = e - Wo; }
     else { const int r = e - 2 * Wo; y = 1 + (r >> 1); x = (r & 1) ? Wo - 1 : 0; }
-    reinterpret_cast<float4*>(out + ((b * Ho + y) * Wo + x) * C)[q] = reinterpret_cast<const float4*>(relu_bias)[q];
+    reinterpret_cast<float4*>(out + ((b * Ho + y) * Wo + x) * ld)[q] = reinterpret_cast<const float4*>(relu_bias)[q];
   }
 }
 
@@ -1181,7 +1182,7 @@ int build_gemm_model(ModelWeights& m, const std::vector<float>& conv1_w, const s
   }
   if (rc == KWS_OK && cudaMalloc((void**)&g->d_bias, bias.size() * 4) != cudaSuccess) rc = fail(KWS_ERR_CUDA, "cudaMalloc failed");
   if (rc == KWS_OK && cudaMalloc((void**)&g->d_border, border.size() * 4) != cudaSuccess) rc = fail(KWS_ERR_CUDA, "cudaMalloc failed");
-  if (rc == KWS_OK && (cudaMalloc((void**)&g->d_zero, (size_t)36 * C * 4) != cudaSuccess || cudaMemset(g->d_zero, 0, (size_t)36 * C * 4) != cudaSuccess))
+  if (rc == KWS_OK && (cudaMalloc((void**)&g->d_zero, (size_t)36 * g->npad * 4) != cudaSuccess || cudaMemset(g->d_zero, 0, (size_t)36 * g->npad * 4) != cudaSuccess))
     rc = fail(KWS_ERR_CUDA, "cudaMalloc failed");
   if (rc == KWS_OK && cudaMalloc((void**)&g->d_dump, (size_t)(g->npad + 32) * 4) != cudaSuccess) rc = fail(KWS_ERR_CUDA, "cudaMalloc failed");
   if (rc == KWS_OK) {
@@ -1253,11 +1254,31 @@ int launch_dscnn_gemm(kws_handle_t h, const float* feats_dev, int64_t B, int T, 
   p.bias = g->d_bias;
   p.kvalid = g->kvalid[0];
   p.nchunks = g->nchunks[0];
+  // conv1: resident-weight im2col kernel when its shared memory (4 A chunks + the whole weight image) fits
+  const size_t smem_c1 = (size_t)4 * kGABytes + (size_t)4 * (g->npad / 8) * kGSbo + (size_t)g->npad * 4;
+  static const bool c1_env = [] { const char* e = std::getenv("KWS_GEMM_CONV1"); return !(e && e[0] == '0'); }();
+  const bool c1_fast = c1_env && smem_c1 <= 227 * 1024 && W1 <= 128 && g->nchunks[0] == 4 && B * ((H1 + 127) / 1) < 0x7fffffffLL;
+  // block layers: the warp-specialised kernel when its thread map (6 column groups of up to 6 columns) and its
+  // shared-memory rings fit, else the chunk-synchronous one (KWS_GEMM_WS=0 forces the latter, for A/B runs)
+  static const bool ws_env = [] { const char* e = std::getenv("KWS_GEMM_WS"); return !(e && e[0] == '0'); }();
+  const int nch_blk = (C + kGKC - 1) / kGKC;
+  const size_t smem_ws = (size_t)kWsS * kWsABytes + (size_t)kWsBS * (g->npad / 8) * kGSbo + (size_t)9 * nch_blk * kGKC * 4 +
+                         (size_t)g->npad * 4;
+  const bool ws_fits = ws_env && smem_ws <= 227 * 1024;
+  // Pixel pitch of the activations.  With 276 channels a pixel is 1104 bytes: every 128-byte K-chunk segment a producer
+  // warp loads straddles two cache lines and the drain's 64-byte runs start at any multiple of 16 bytes -- ncu showed the
+  // L1 -> crossbar request path 60 % busy.  When every layer runs the two fast kernels (only they know the pitch) and the
+  // padding is at most an eighth of the traffic, pixels are npad floats apart (a multiple of 128 bytes): one request per
+  // segment, and the padding channels are never written or read.  KWS_GEMM_PAD=0: A/B.
+  static const bool pad_env = [] { const char* e = std::getenv("KWS_GEMM_PAD"); return !(e && e[0] == '0'); }();
+  bool all_fast = c1_fast && ws_fits && nb >= 1;
+  for (int l = 0; l < nb && all_fast; ++l) {
+    const int Hh = H1 + 2 * l, Ww = W1 + 2 * l, Rr = 128 / Ww < Hh ? 128 / Ww : Hh;
+    if (Ww > 36 || B * ((Hh + Rr - 1) / Rr) * (long long)nch_blk >= 0x7fffffffLL) all_fast = false;
+  }
+  p.ldc = (all_fast && pad_env && g->npad != C && (g->npad - C) * 8 <= C) ? g->npad : C;
   {
-    // conv1: resident-weight im2col kernel when its shared memory (4 A chunks + the whole weight image) fits
-    const size_t smem_c1 = (size_t)4 * kGABytes + (size_t)4 * (g->npad / 8) * kGSbo + (size_t)g->npad * 4;
-    static const bool c1_env = [] { const char* e = std::getenv("KWS_GEMM_CONV1"); return !(e && e[0] == '0'); }();
-    if (c1_env && smem_c1 <= 227 * 1024 && W1 <= 128 && g->nchunks[0] == 4 && B * ((H1 + 127) / 1) < 0x7fffffffLL) {
+    if (c1_fast) {
       if (int rc = ensure_dyn_smem(dscnn_conv1_kernel, smem_c1)) return rc;
       p.H = H1;
       p.W = W1;
@@ -1272,13 +1293,6 @@ int launch_dscnn_gemm(kws_handle_t h, const float* feats_dev, int64_t B, int T, 
   KWS_CHECK_LAUNCH(h);
   float *cur = buf0, *nxt = buf1;
   int H = H1, W = W1;
-  // block layers: the warp-specialised kernel when its thread map (12 column groups of 2 or 3 columns) and its
-  // shared-memory rings fit, else the chunk-synchronous one (KWS_GEMM_WS=0 forces the latter, for A/B runs)
-  static const bool ws_env = [] { const char* e = std::getenv("KWS_GEMM_WS"); return !(e && e[0] == '0'); }();
-  const int nch_blk = (C + kGKC - 1) / kGKC;
-  const size_t smem_ws = (size_t)kWsS * kWsABytes + (size_t)kWsBS * (g->npad / 8) * kGSbo + (size_t)9 * nch_blk * kGKC * 4 +
-                         (size_t)g->npad * 4;
-  const bool ws_fits = ws_env && smem_ws <= 227 * 1024;
   if (ws_fits) {
     if (int rc = ensure_dyn_smem(dscnn_block_ws_kernel<4, 2, false>, smem_ws)) return rc;
     if (int rc = ensure_dyn_smem(dscnn_block_ws_kernel<5, 2, false>, smem_ws)) return rc;
@@ -1340,7 +1354,7 @@ int launch_dscnn_gemm(kws_handle_t h, const float* feats_dev, int64_t B, int T, 
     const long long nborder = B * (long long)(2 * (W + 2) + 2 * H) * (C / 4);
     long long gb = (nborder + 255) / 256;
     if (gb > h->sm_count * 8LL) gb = h->sm_count * 8LL;
-    border_fill_kernel<<<(unsigned)gb, 256, 0, st>>>(nxt, g->d_border + (size_t)l * C, B, H + 2, W + 2, C);
+    border_fill_kernel<<<(unsigned)gb, 256, 0, st>>>(nxt, g->d_border + (size_t)l * C, B, H + 2, W + 2, C, p.ldc);
     KWS_CHECK_LAUNCH(h);
     float* t = cur;
     cur = nxt;
