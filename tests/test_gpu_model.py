@@ -96,10 +96,13 @@ def test_fused_streams_clip_pairs_back_to_back(T, F, B):
 
 
 @pytest.mark.parametrize("channels,blocks,T,F,B", [(276, 5, 99, 40, 3), (64, 4, 99, 13, 9), (32, 2, 49, 26, 5),
-                                                  (100, 3, 31, 40, 2), (512, 1, 20, 12, 2)])
+                                                  (100, 3, 31, 40, 2), (512, 1, 20, 12, 2), (172, 3, 31, 64, 4),
+                                                  (172, 2, 31, 76, 5)])
 def test_tensor_core_gemm_path_any_channels(channels, blocks, T, F, B):
     """Layer-by-layer tcgen05 path (model_gemm.cu; BASELINE config 2 'DS-CNN-L' = 276 channels, 5 blocks)
-    against the layered fp32 kernels and the float64 oracle."""
+    against the layered fp32 kernels and the float64 oracle.  276 and 172 channels run with the padded pixel pitch
+    (288 / 192 floats) when every layer takes the fast kernels; 172 x 2 at F = 76 has a second block 38 columns wide,
+    which the warp-specialised kernel does not take: mixed kernels, unpadded pitch."""
     sd = dscnn_ref.init_state_dict(channels=channels, num_blocks=blocks, seed=channels + blocks)
     m = DepthwiseSeparableConv(channels=channels, num_blocks=blocks)
     m.load_state_dict(sd)
