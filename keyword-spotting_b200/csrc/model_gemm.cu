@@ -964,52 +964,67 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_conv1_kernel(const GemmParams p)
   const int dr_pairs = p.npad >> 4, dr_cs = warp >> 2;
   const int dr_n = dr_pairs / 4 + (dr_cs < (dr_pairs & 3) ? 1 : 0);
   const int dr_c0 = 16 * (dr_cs * (dr_pairs / 4) + min(dr_cs, dr_pairs & 3)), dr_c1 = dr_c0 + 16 * dr_n;
+  // gather: item = (pixel pp, kernel row pair m), 128 x 5 items = one per thread + a second one for threads 0..127.
+  // The loads of tile i + 1 are issued right after tile i's MMAs and land in registers while the MMAs execute and the
+  // accumulator is drained (the gather used to load and store in one go at the top of the tile: ncu had 60 % of the
+  // warps' time on that scoreboard); the stores into the A operand follow after the drain.
+  auto gather_load = [&](unsigned tl, int item, float (&v)[20]) {
+    const unsigned b = tl / (unsigned)p.nbands;
+    const int r0 = (int)(tl - b * (unsigned)p.nbands) * R;
+    const float* feat = p.in + (long long)b * T * F;
+    const int m = item >> 7, pp = item & 127;
+    const int rl = pp / W, xq = pp - rl * W, y = r0 + rl;
+    const bool valid = rl < R && y < H;
+#pragma unroll
+    for (int kr = 0; kr < 2; ++kr) {
+      const int fr = 2 * y - 2 + 2 * m + kr, fc0 = 2 * xq - 2;
+      const bool rok = valid && fr >= 0 && fr < T;
+      const float* row = feat + (long long)fr * F + fc0;
+      if (rok && f_even && fc0 >= 0 && fc0 + 10 <= F) {  // interior: five aligned 8-byte loads
+#pragma unroll
+        for (int e = 0; e < 5; ++e) {
+          const float2 t2 = __ldg(reinterpret_cast<const float2*>(row) + e);
+          v[kr * 10 + 2 * e] = t2.x;
+          v[kr * 10 + 2 * e + 1] = t2.y;
+        }
+      } else {
+#pragma unroll
+        for (int e = 0; e < 10; ++e) v[kr * 10 + e] = (rok && fc0 + e >= 0 && fc0 + e < F) ? __ldg(row + e) : 0.f;
+      }
+    }
+  };
+  auto gather_store = [&](int item, const float (&v)[20]) {
+    const int m = item >> 7, pp = item & 127;
+    const uint32_t a0 = smem_u32(sA) + (uint32_t)((pp >> 3) * kGSboA + (pp & 7) * 16);
+#pragma unroll
+    for (int e = 0; e < 5; ++e) {  // K quad 5 m + e: chunk (quad >> 3), quad in chunk (quad & 7)
+      const int quad = 5 * m + e;
+      const uint32_t a = a0 + (uint32_t)((quad >> 3) * kGABytes + (quad & 7) * kGLboA);
+      asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(__float_as_uint(v[4 * e]) + 0x1000u),
+                   "r"(__float_as_uint(v[4 * e + 1]) + 0x1000u), "r"(__float_as_uint(v[4 * e + 2]) + 0x1000u),
+                   "r"(__float_as_uint(v[4 * e + 3]) + 0x1000u)
+                   : "memory");
+    }
+  };
+  static_assert(128 * 5 == kGT + 128, "gather item map");
+  float ga[20], gb[20];
+  if (blockIdx.x < ntiles) {
+    gather_load(blockIdx.x, tid, ga);
+    if (tid < 128) gather_load(blockIdx.x, kGT + tid, gb);
+  }
   uint32_t it = 0;
   for (unsigned tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
     const unsigned b = tile / (unsigned)p.nbands;
     const int band = (int)(tile - b * (unsigned)p.nbands), r0 = band * R;
-    const float* feat = p.in + (long long)b * T * F;
-    if (tid == 0 && pf_ok && tile + gridDim.x < ntiles) {  // the next tile's feature rows -> L2 while this tile is worked on
-      const unsigned tn = tile + gridDim.x, bn = tn / (unsigned)p.nbands;
+    if (tid == 0 && pf_ok && tile + 2 * gridDim.x < ntiles) {  // the feature rows of the tile after next -> L2
+      const unsigned tn = tile + 2 * gridDim.x, bn = tn / (unsigned)p.nbands;
       const int rn = (int)(tn - bn * (unsigned)p.nbands) * R;
       const int f0 = max(2 * rn - 2, 0), f1 = min(2 * (rn + R) + 6, T - 1);
       asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p.in + ((long long)bn * T + f0) * F), "r"((uint32_t)((f1 - f0 + 1) * F * 4))
                    : "memory");
     }
-    // ---- gather: item = (pixel pp, kernel row pair m) ----
-    for (int item = tid; item < 128 * 5; item += kGT) {
-      const int m = item >> 7, pp = item & 127;
-      const int rl = pp / W, xq = pp - rl * W, y = r0 + rl;
-      const bool valid = rl < R && y < H;
-      float v[20];
-#pragma unroll
-      for (int kr = 0; kr < 2; ++kr) {
-        const int fr = 2 * y - 2 + 2 * m + kr, fc0 = 2 * xq - 2;
-        const bool rok = valid && fr >= 0 && fr < T;
-        const float* row = feat + (long long)fr * F + fc0;
-        if (rok && f_even && fc0 >= 0 && fc0 + 10 <= F) {  // interior: five aligned 8-byte loads
-#pragma unroll
-          for (int e = 0; e < 5; ++e) {
-            const float2 t2 = __ldg(reinterpret_cast<const float2*>(row) + e);
-            v[kr * 10 + 2 * e] = t2.x;
-            v[kr * 10 + 2 * e + 1] = t2.y;
-          }
-        } else {
-#pragma unroll
-          for (int e = 0; e < 10; ++e) v[kr * 10 + e] = (rok && fc0 + e >= 0 && fc0 + e < F) ? __ldg(row + e) : 0.f;
-        }
-      }
-      const uint32_t a0 = smem_u32(sA) + (uint32_t)((pp >> 3) * kGSboA + (pp & 7) * 16);
-#pragma unroll
-      for (int e = 0; e < 5; ++e) {  // K quad 5 m + e: chunk (quad >> 3), quad in chunk (quad & 7)
-        const int quad = 5 * m + e;
-        const uint32_t a = a0 + (uint32_t)((quad >> 3) * kGABytes + (quad & 7) * kGLboA);
-        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(__float_as_uint(v[4 * e]) + 0x1000u),
-                     "r"(__float_as_uint(v[4 * e + 1]) + 0x1000u), "r"(__float_as_uint(v[4 * e + 2]) + 0x1000u),
-                     "r"(__float_as_uint(v[4 * e + 3]) + 0x1000u)
-                     : "memory");
-      }
-    }
+    gather_store(tid, ga);
+    if (tid < 128) gather_store(kGT + tid, gb);
     fence_proxy_async();
     __syncthreads();
     if (warp == kGT / 32 - 1) {
@@ -1026,6 +1041,10 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_conv1_kernel(const GemmParams p)
         for (int ks = 0; ks < 13; ++ks) tc_mma_tf32_elect(tmem, adv[ks], bdv[ks], idesc, ks > 0 ? 1u : 0u);
       }
       tc_commit_elect(barM);
+    }
+    if (tile + gridDim.x < ntiles) {  // the next tile's features: in flight during the MMAs and the drain
+      gather_load(tile + gridDim.x, tid, ga);
+      if (tid < 128) gather_load(tile + gridDim.x, kGT + tid, gb);
     }
     mbar_wait(barM, it & 1u);
     tc_fence_after();
