@@ -540,9 +540,17 @@ def _extras(args, torch, dist, dev, rank, world, pcm, model, ks, proc, timed, ba
         feats = proc.extract_features(pcm[:Bl], numcep=NUMCEP, nfilt=NFILT).unsqueeze(1)
         ms = timed(lambda: big(feats), 3, warm=1)
         cps = Bl / (ms * 1e-3)
+        # what the LAYERED design moves through HBM per clip (fp32 NHWC activations, 288-float pixel pitch, every
+        # activation written once and read once; the last block's output is pooled on chip): its own floor, next to
+        # the algorithmic roofline of a fully fused network that roofline3 reports
+        h1, w1 = (NFRAMES + 4 - 10) // 2 + 1, (NUMCEP + 4 - 10) // 2 + 1
+        px = h1 * w1 + sum((h1 + 2 * l) * (w1 + 2 * l) for l in range(5)) + sum((h1 + 2 * l + 2) * (w1 + 2 * l + 2) for l in range(4))
+        layered = px * 288 * 4
         return {"workload": "mfcc40 features -> DS-CNN-L (276 ch, 5 blocks) forward, %d clips/GPU" % Bl,
                 "clips_per_s": world * cps, "ms": ms,
-                "roofline": roofline3(WORK["dscnn_l_model"], cps, peaks, fp32_tflops, "dscnn_conv1_kernel + dscnn_block_ws_kernel (x5)", ms)}
+                "roofline": roofline3(WORK["dscnn_l_model"], cps, peaks, fp32_tflops, "dscnn_conv1_kernel + dscnn_block_ws_kernel (x5)", ms),
+                "layered_hbm": {"bytes_per_clip": layered, "achieved_gbs": cps * layered / 1e9, "peak_gbs": peaks["hbm_gbs"],
+                                "frac": cps * layered / 1e9 / peaks["hbm_gbs"]}}
 
     def cfg4():   # BASELINE configs[3]: log-mel + CRNN/GRU, batch 16 384
         Bc = min(B, 16384)
