@@ -40,6 +40,7 @@ struct GemmParams {
   int R, nbands;       // tile = R whole rows of one clip (R * W <= 128), nbands = ceil(H / R)
   int kvalid, npad, nh, nhalf, nchunks, tmem_cols, patch_bytes;
   int nslots;  // dscnn_block_ws_kernel: accumulator slots of nhalf TMEM columns
+  int fill_border;  // dscnn_block_ws_kernel writes the border pixels itself (warps 18, 19)
   int ldc;     // floats between consecutive pixels of the activations (C, or C padded to a multiple of 32: see launch_dscnn_gemm)
   // last block only: instead of the activation, write per-tile channel sums (the global average pool's partial sums,
   // scaled so that pool_fc_kernel's mean over nbands + 1 rows is the mean over the padded output) -- the largest
@@ -434,6 +435,7 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
   extern __shared__ __align__(128) unsigned char smem[];
   __shared__ __align__(8) unsigned long long s_bar[2 * kWsS + 2 * kWsBS + 2 + 3];
   __shared__ uint32_t s_tmem;
+  __shared__ volatile int s_tile;  // tile the issue warp has reached: paces the border warps
 #ifdef KWS_WS_PROFILE
   __shared__ long long s_prof[8];
 #endif
@@ -455,6 +457,7 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
       mbar_init(bBfull + 8 * s, 1);
       mbar_init(bBempty + 8 * s, 1);
     }
+    s_tile = -1;
     mbar_init(bAccFull, 1);  // MMAs of an even / odd tile retired
     mbar_init(bAccFull + 8, 1);
     for (int s = 0; s < 3; ++s) mbar_init(bFreeS + 8 * s, kWsEpi);  // accumulator slot read out by its four warps
@@ -805,7 +808,38 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
     if (blockIdx.x == 3 && lane == 0) printf("drain warp %d: total %lld wait_accfull %lld\n", warp, clock64() - wsp_start, wsp_aw);
 #endif
   } else if (warp > kWsG * 3 + kWsEpi + 1) {
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 24;");  // idle: they only complete the issue warp's warpgroup
+    // ---- warps 18, 19 (they complete the issue warp's warpgroup): the output's border pixels, ReLU(bias) each (the
+    // padding = 1 quirk), a tile's border while the issue warp is on that tile (written all at once at the start of the
+    // kernel they cost the pipeline as much as the separate border_fill launches they replace) ----
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 24;");
+    if (!POOL && p.fill_border) {
+      const int cq = C >> 2;
+      for (int j = warp - (kWsG * 3 + kWsEpi + 2); j < my_tiles; j += 2) {
+        while (s_tile < j) __nanosleep(500);
+        const unsigned tile = blockIdx.x + (unsigned)j * gridDim.x, b = tile / (unsigned)p.nbands;
+        const int band = (int)(tile - b * (unsigned)p.nbands), r0 = band * R, nr = min(R, H - r0);
+        float* obase = p.out + (long long)b * (H + 2) * (W + 2) * (long long)p.ldc;
+        // rows r0 + 1 .. r0 + nr: columns 0 and W + 1; the whole top row with the first band, the bottom row with the last
+        const int nside = 2 * nr, ntop = band == 0 ? W + 2 : 0, nbot = r0 + nr == H ? W + 2 : 0;
+#pragma unroll 1
+        for (int e = 0; e < nside + ntop + nbot; ++e) {
+          int y, x;
+          if (e < nside) {
+            y = r0 + 1 + (e >> 1);
+            x = (e & 1) ? W + 1 : 0;
+          } else if (e < nside + ntop) {
+            y = 0;
+            x = e - nside;
+          } else {
+            y = H + 1;
+            x = e - nside - ntop;
+          }
+          float4* dst = reinterpret_cast<float4*>(obase + ((long long)y * (W + 2) + x) * p.ldc);
+#pragma unroll 1
+          for (int q = lane; q < cq; q += 32) dst[q] = __ldg(reinterpret_cast<const float4*>(p.border) + q);
+        }
+      }
+    }
   } else if (warp == kWsG * 3 + kWsEpi + 1) {
     // ---- loader warp: weight chunks through the TMA ring, as far ahead as the ring allows (~45 instructions and the
     // wait for the ring stage off every item of the issue loop: 1.1 K -> 0.9 K cycles per item)
@@ -848,6 +882,7 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
     for (int n = 0; n < total; ++n) {
       const int g = n % kWsS;  // A ring stage of the item
       if (kc == 0) {  // tile boundary: this tile's accumulator slots must have been read out by their four warps
+        if (lane == 0) s_tile = j;
         const int h = p.nh * j, s0 = h % ns, s1 = (h + 1) % ns, u0 = h / ns, u1 = (h + 1) / ns;
         WSP_T0();
         if (u0 > 0) WS_WAIT(bFreeS + 8 * (uint32_t)s0, (uint32_t)(u0 - 1) & 1u);
@@ -1358,9 +1393,11 @@ int launch_dscnn_gemm(kws_handle_t h, const float* feats_dev, int64_t B, int T, 
         else dscnn_block_ws_kernel<6, 1, false><<<grid, kWsT, smem_ws, st>>>(p);
       }
     };
+    static const bool bf_env = [] { const char* e = std::getenv("KWS_GEMM_BORDER"); return !(e && e[0] == '0'); }();
+    p.border = g->d_border + (size_t)l * C;
+    p.fill_border = ws && bf_env ? 1 : 0;
     if (l == nb - 1) {  // the pooled rows replace the last activation (see GemmParams::pool)
       p.pool = nxt;
-      p.border = g->d_border + (size_t)l * C;
       p.pool_scale = (float)pool_rows / (float)((H + 2) * (W + 2));
       launch_block();
       KWS_CHECK_LAUNCH(h);
@@ -1370,11 +1407,13 @@ int launch_dscnn_gemm(kws_handle_t h, const float* feats_dev, int64_t B, int T, 
     }
     launch_block();
     KWS_CHECK_LAUNCH(h);
-    const long long nborder = B * (long long)(2 * (W + 2) + 2 * H) * (C / 4);
-    long long gb = (nborder + 255) / 256;
-    if (gb > h->sm_count * 8LL) gb = h->sm_count * 8LL;
-    border_fill_kernel<<<(unsigned)gb, 256, 0, st>>>(nxt, g->d_border + (size_t)l * C, B, H + 2, W + 2, C, p.ldc);
-    KWS_CHECK_LAUNCH(h);
+    if (!p.fill_border) {
+      const long long nborder = B * (long long)(2 * (W + 2) + 2 * H) * (C / 4);
+      long long gb = (nborder + 255) / 256;
+      if (gb > h->sm_count * 8LL) gb = h->sm_count * 8LL;
+      border_fill_kernel<<<(unsigned)gb, 256, 0, st>>>(nxt, g->d_border + (size_t)l * C, B, H + 2, W + 2, C, p.ldc);
+      KWS_CHECK_LAUNCH(h);
+    }
     float* t = cur;
     cur = nxt;
     nxt = t;
