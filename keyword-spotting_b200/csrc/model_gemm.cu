@@ -879,6 +879,8 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
     uint32_t tmem_h0 = tmem, tmem_h1 = tmem + (uint32_t)p.nhalf;  // this tile's accumulator slots
     int bs = 0;        // weight ring stage of item n
     uint32_t bph = 0;  // and its phase
+    bool wait_s1 = false;
+    uint32_t bar_s1 = 0, par_s1 = 0;
     for (int n = 0; n < total; ++n) {
       const int g = n % kWsS;  // A ring stage of the item
       if (kc == 0) {  // tile boundary: this tile's accumulator slots must have been read out by their four warps
@@ -886,8 +888,12 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
         const int h = p.nh * j, s0 = h % ns, s1 = (h + 1) % ns, u0 = h / ns, u1 = (h + 1) / ns;
         WSP_T0();
         if (u0 > 0) WS_WAIT(bFreeS + 8 * (uint32_t)s0, (uint32_t)(u0 - 1) & 1u);
-        if (two_halves && u1 > 0) WS_WAIT(bFreeS + 8 * (uint32_t)s1, (uint32_t)(u1 - 1) & 1u);
         WSP_ADD(free);
+        // the second half's slot (the previous tile's first half, still being read out) is waited for after the first
+        // half's MMAs of the tile's first chunk have been issued
+        wait_s1 = two_halves && u1 > 0;
+        bar_s1 = bFreeS + 8 * (uint32_t)s1;
+        par_s1 = (uint32_t)(u1 - 1) & 1u;
         tmem_h0 = tmem + (uint32_t)(s0 * p.nhalf);
         tmem_h1 = tmem + (uint32_t)(s1 * p.nhalf);
       }
@@ -904,10 +910,22 @@ __global__ void __launch_bounds__(kWsT, 1) dscnn_block_ws_kernel(const GemmParam
 #ifdef KWS_WS_NOMMA  // timing experiment only (results are wrong): one K step of MMAs per item instead of four
         if (ks > 0) break;
 #endif
-        const uint32_t acc = (kc > 0 || ks > 0) ? 1u : 0u;
-        tc_mma_tf32_elect(tmem_h0, ad + (uint64_t)(ks * ((2 * kWsLbo) >> 4)), bd + (uint64_t)(ks * 16), idesc, acc);
-        if (two_halves)
-          tc_mma_tf32_elect(tmem_h1, ad + (uint64_t)(ks * ((2 * kWsLbo) >> 4)), bd + (uint64_t)(b_half + ks * 16), idesc, acc);
+        tc_mma_tf32_elect(tmem_h0, ad + (uint64_t)(ks * ((2 * kWsLbo) >> 4)), bd + (uint64_t)(ks * 16), idesc, (kc > 0 || ks > 0) ? 1u : 0u);
+      }
+      if (two_halves) {
+        if (wait_s1) {
+          WSP_T0();
+          WS_WAIT(bar_s1, par_s1);
+          WSP_ADD(free);
+          wait_s1 = false;
+        }
+#pragma unroll
+        for (int ks = 0; ks < kGKC / 8; ++ks) {
+#ifdef KWS_WS_NOMMA
+          if (ks > 0) break;
+#endif
+          tc_mma_tf32_elect(tmem_h1, ad + (uint64_t)(ks * ((2 * kWsLbo) >> 4)), bd + (uint64_t)(b_half + ks * 16), idesc, (kc > 0 || ks > 0) ? 1u : 0u);
+        }
       }
       tc_commit_elect(bEmpty + 8 * g);
       tc_commit_elect(bBempty + 8 * bs);
