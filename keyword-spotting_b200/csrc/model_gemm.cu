@@ -368,21 +368,24 @@ __global__ void __launch_bounds__(kGT, 1) dscnn_gemm_kernel(const GemmParams p) 
 // read once per 128 pixels, and the chunk-synchronous kernel on top of that staged every input patch in shared
 // memory and read each element five times from there, with all 16 warps meeting at a CTA barrier per K chunk
 // (ncu: 4.9 K cycles per chunk, tensor pipe 16 % active, barrier + LSU-queue stalls on top).  Here:
-//   * no input patch in shared memory: a producer thread owns (channel quad, NC adjacent columns) of the tile and
-//     walks DOWN the rows with the 3x3 window in registers -- one 16-byte global load per input pixel and channel
-//     quad (NC + 2 per row, L1 catches the neighbour thread's overlap), each input row updates the three output
+//   * no input patch in shared memory: a producer thread owns (channel pair, NC adjacent columns) of the tile and
+//     walks DOWN the rows with the 3x3 window in registers -- one 8-byte global load per input pixel and channel
+//     pair (NC + 2 per row, L1 catches the neighbour thread's overlap), each input row updates the three output
 //     rows it touches (out = P + w2.v, P = R + w1.v, R = w0.v), so nothing is read twice and nothing is exchanged;
 //     out-of-range columns load a clamped (valid) address and are zeroed by a 0/1 multiply when used, rows outside
 //     the clip take a warp-uniform branch: no per-load predicates or address selects in the row loop;
-//   * four producer groups of 3 warps work on four DIFFERENT K chunks at the same time; group g owns A-ring stage g
-//     (full / empty mbarriers, tcgen05.commit releases a stage), so there is no CTA-wide barrier anywhere;
-//   * the issue warp streams the weight chunks through a 3-stage TMA ring, fires the chunk's MMAs in order, and
-//     pulls the next tile's whole input patch (one contiguous range) into L2 with bulk prefetches;
+//   * four producer groups of 3 warps work on four DIFFERENT K chunks at the same time; item n goes into A-ring stage
+//     n % 6 (full / empty mbarriers, tcgen05.commit releases a stage), so there is no CTA-wide barrier anywhere;
+//   * the issue warp (16) fires a chunk's MMAs -- the first N half's four, then the second half's -- and pulls the next
+//     tile's whole input patch (one contiguous range) into L2 with bulk prefetches half a tile ahead; the loader warp
+//     (17) streams the weight chunks through a 3-stage TMA ring; the two spare warps of that warpgroup (18, 19) write
+//     the output's border pixels;
 //   * the accumulator is drained by four warps of their own (12..15, one TMEM lane quarter each) out of a ring of
 //     accumulator slots, so the issue warp (16) never drains and a tile's MMAs overlap the previous tile's drain:
 //     with two N halves of 144 columns three half-slots fit the 512 TMEM columns (tile j's halves in slots 2j % 3
 //     and (2j + 1) % 3), one-half layers get two whole slots, halves wider than 170 columns two half-slots (each
-//     half then waits for the previous tile's same half only).  17 warps x 120 registers fill the register file.
+//     half then waits for the previous tile's same half only).  Five warps per SM sub-partition: 96 registers each at
+//     launch, rebalanced with setmaxnreg to 120 (producers) / 96 (drain) / 24 (the last warpgroup).
 constexpr int kWsG = 4;     // producer groups
 #ifndef KWS_WS_S
 #define KWS_WS_S 6
